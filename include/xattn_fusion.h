@@ -1,0 +1,213 @@
+/*
+ * xattn_fusion.h — C ABI of the B200-native (sm_100a) cross-attention fusion head.
+ *
+ * The reference (Wionerlol/MultimodalEmotionRecognition) has NO native/FFI interface: the path is a
+ * Python nn.Module (src/models/fusion.py:187-437).  This header is therefore the boundary a
+ * maintainer binds with ctypes; every entry point names the reference code
+ * it replaces.  Plain pointers and sizes only; no torch types.
+ *
+ * Conventions
+ *  - every entry point returns int: 0 = XATTN_OK, otherwise an xattn_status code; the text of the
+ *    last failure on the calling thread is returned by xattn_last_error().  Nothing aborts, no C++
+ *    exception crosses the ABI.  There is NO CPU fallback: a non-sm_100 device is XATTN_ERR_ARCH.
+ *  - all data pointers are DEVICE pointers owned by the caller (PyTorch's allocator); the library
+ *    allocates nothing persistent and frees nothing.  Calls are asynchronous on `stream`
+ *    (a cudaStream_t passed as void*).
+ *  - parameters live in ONE flat fp32 buffer whose layout (offset/size per xattn_param_id, in
+ *    floats) is defined by xattn_param_layout(); gradients use the same layout.  The Python module
+ *    keeps the reference's state_dict names as views into that buffer.
+ */
+#ifndef XATTN_FUSION_H_
+#define XATTN_FUSION_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define XATTN_ABI_VERSION 3
+
+#if defined(__GNUC__)
+#define XATTN_API __attribute__((visibility("default")))
+#else
+#define XATTN_API
+#endif
+
+typedef enum xattn_status {
+  XATTN_OK = 0,
+  XATTN_ERR_SHAPE = 1,     /* unsupported or inconsistent dimensions (-> ValueError) */
+  XATTN_ERR_DTYPE = 2,     /* unknown dtype / precision code          (-> ValueError) */
+  XATTN_ERR_ALIGN = 3,     /* pointer not 16-byte aligned             (-> ValueError) */
+  XATTN_ERR_ARCH = 4,      /* device is not sm_100                    (-> RuntimeError) */
+  XATTN_ERR_CUDA = 5,      /* a CUDA call failed                      (-> RuntimeError) */
+  XATTN_ERR_WORKSPACE = 6, /* workspace too small                     (-> RuntimeError) */
+  XATTN_ERR_NULL = 7       /* required pointer is NULL                (-> ValueError) */
+} xattn_status;
+
+enum { XATTN_HEAD_CONCAT = 0, XATTN_HEAD_GATED = 1 };
+enum { XATTN_DTYPE_F32 = 0, XATTN_DTYPE_BF16 = 1 };
+
+/* Problem description.  Field meaning follows FusionModel.__init__ (fusion.py:188-213). */
+typedef struct xattn_config {
+  int32_t B;            /* clips in this call                                        */
+  int32_t T;            /* video tokens per clip (frames)                            */
+  int32_t Ta;           /* audio tokens per clip (WavLM frames, 149 for 3 s)         */
+  int32_t Dv;           /* video embedding dim   (video_model.embedding_dim, 512)    */
+  int32_t Da;           /* audio sequence dim    (audio_model.sequence_dim, 768)     */
+  int32_t E;            /* d_model                                                   */
+  int32_t H;            /* num_heads                                                 */
+  int32_t prior_dim;    /* xattn_emotion_prior_dim                                   */
+  int32_t prior_hidden; /* xattn_emotion_prior_hidden_dim                            */
+  int32_t common_dim;   /* hidden width of the concat head (fusion.py:313)           */
+  int32_t C;            /* num_classes                                               */
+  int32_t head_kind;    /* XATTN_HEAD_CONCAT | XATTN_HEAD_GATED (fusion.py:311/318)  */
+  int32_t use_prior;    /* xattn_use_emotion_prior                                   */
+  int32_t io_dtype;     /* dtype of video_emb / audio_emb: XATTN_DTYPE_*             */
+  int32_t precision;    /* XATTN_DTYPE_F32: fp32 SIMT kernels (parity + training path)
+                           XATTN_DTYPE_BF16: tcgen05 bf16 kernels, fp32 accumulate   */
+  int32_t training;     /* 1: dropouts active (Philox) and activations saved for
+                           xattn_backward; 0: eval                                   */
+  int32_t save_for_backward; /* 1: keep activations in the workspace even in eval mode
+                                (gradient parity in eval mode)            */
+  float p_attn;         /* attention dropout            (fusion.py:277,280)          */
+  float p_path;         /* stochastic depth             (fusion.py:282-283)          */
+  float p_head;         /* head Dropout(0.2)            (fusion.py:315,322)          */
+  float p_prior;        /* prior_net Dropout            (fusion.py:161)              */
+  uint64_t seed;        /* Philox seed for the dropouts                               */
+  uint64_t offset;      /* Philox offset (advance per step)                           */
+} xattn_config;
+
+/* Parameter ids: order of the flat parameter / gradient buffer.  Names are the reference's
+ * state_dict keys.  audio_time_conv.* is deliberately absent: it is unused on the
+ * WavLM path and receives no gradient (fusion.py:273, :379-384). */
+typedef enum xattn_param_id {
+  XP_V_IN_W = 0,   /* v_in_proj.weight            [E,Dv]   */
+  XP_V_IN_B,       /* v_in_proj.bias              [E]      */
+  XP_A_IN_W,       /* a_in_proj.weight            [E,E]    */
+  XP_A_IN_B,       /* a_in_proj.bias              [E]      */
+  XP_SEQ_W,        /* audio_seq_proj.weight       [E,Da]   */
+  XP_SEQ_B,        /* audio_seq_proj.bias         [E]      */
+  XP_V2A_IN_W,     /* v2a_attn.in_proj_weight     [3E,E]   */
+  XP_V2A_IN_B,     /* v2a_attn.in_proj_bias       [3E]     */
+  XP_V2A_OUT_W,    /* v2a_attn.out_proj.weight    [E,E]    */
+  XP_V2A_OUT_B,    /* v2a_attn.out_proj.bias      [E]      */
+  XP_A2V_IN_W,     /* a2v_attn.in_proj_weight     [3E,E]   */
+  XP_A2V_IN_B,     /* a2v_attn.in_proj_bias       [3E]     */
+  XP_A2V_OUT_W,    /* a2v_attn.out_proj.weight    [E,E]    */
+  XP_A2V_OUT_B,    /* a2v_attn.out_proj.bias      [E]      */
+  XP_VN_W,         /* v_norm.weight               [E]      */
+  XP_VN_B,         /* v_norm.bias                 [E]      */
+  XP_AN_W,         /* a_norm.weight               [E]      */
+  XP_AN_B,         /* a_norm.bias                 [E]      */
+  XP_HEAD0_W,      /* xattn_mlp.0.weight [common,2E]   | xattn_gate.0.weight [E,2E] */
+  XP_HEAD0_B,      /* xattn_mlp.0.bias   [common]      | xattn_gate.0.bias   [E]    */
+  XP_HEAD1_W,      /* xattn_mlp.3.weight [C,common]    | xattn_gate.3.weight [1,E]  */
+  XP_HEAD1_B,      /* xattn_mlp.3.bias   [C]           | xattn_gate.3.bias   [1]    */
+  XP_CLS_W,        /* (gated) xattn_classifier.weight [C,E]; size 0 for concat      */
+  XP_CLS_B,        /* (gated) xattn_classifier.bias   [C];   size 0 for concat      */
+  XP_PRIOR0_W,     /* emotion_prior_bias.prior_net.0.weight [Hd,2E] (size 0 if !use_prior, also below) */
+  XP_PRIOR0_B,     /* emotion_prior_bias.prior_net.0.bias   [Hd]     */
+  XP_PRIOR3_W,     /* emotion_prior_bias.prior_net.3.weight [P,Hd]   */
+  XP_PRIOR3_B,     /* emotion_prior_bias.prior_net.3.bias   [P]      */
+  XP_VQ_W,         /* emotion_prior_bias.v_query_bias.weight [1,E+P] */
+  XP_VQ_B,         /* emotion_prior_bias.v_query_bias.bias   [1]     */
+  XP_AK_W,         /* emotion_prior_bias.a_key_bias.weight   [1,E+P] */
+  XP_AK_B,         /* emotion_prior_bias.a_key_bias.bias     [1]     */
+  XP_AQ_W,         /* emotion_prior_bias.a_query_bias.weight [1,E+P] */
+  XP_AQ_B,         /* emotion_prior_bias.a_query_bias.bias   [1]     */
+  XP_VK_W,         /* emotion_prior_bias.v_key_bias.weight   [1,E+P] */
+  XP_VK_B,         /* emotion_prior_bias.v_key_bias.bias     [1]     */
+  XP_BIAS_SCALE,   /* emotion_prior_bias.bias_scale          []      */
+  XP_COUNT
+} xattn_param_id;
+
+/* ---- library info ------------------------------------------------------------------------ */
+XATTN_API int xattn_abi_version(void);
+/* Text of the last error raised on this thread ("" if none). */
+XATTN_API const char* xattn_last_error(void);
+
+/* ---- layout queries (host only, no CUDA) --------------------------------------------------- */
+/* Fills offsets[XP_COUNT] / sizes[XP_COUNT] (in floats; each offset is a multiple of 4 floats so
+ * every tensor is 16-byte aligned) and *total_floats.  Replaces: the nn.Parameter tree built at
+ * fusion.py:269-326 (state_dict layout). */
+XATTN_API int xattn_param_layout(const xattn_config* cfg, int64_t* offsets, int64_t* sizes, int64_t* total_floats);
+/* Bytes of scratch/activation workspace xattn_forward needs for cfg (depends on B, precision,
+ * training/save_for_backward). */
+XATTN_API int xattn_workspace_bytes(const xattn_config* cfg, int64_t* bytes);
+/* Bytes of the derived ("packed") bf16 weight buffer used by precision == BF16. */
+XATTN_API int xattn_packed_bytes(const xattn_config* cfg, int64_t* bytes);
+
+/* ---- forward ------------------------------------------------------------------------------- */
+/* Derives the bf16 operand set (rounded weights, the audio_seq_proj∘a_in_proj fold of SURVEY 3.1
+ * fact 2, pre-multiplied attention weights) from the flat fp32 parameters.  Call once per weight
+ * update; inference callers cache the result. */
+XATTN_API int xattn_pack_weights(const xattn_config* cfg, const float* params, void* packed, void* stream);
+
+/* logits[B,C] (fp32) = FusionModel.forward for mode="xattn", from the point where the frozen
+ * backbones have produced video_emb [B,T,Dv] and audio_emb [B,Ta,Da] (dtype cfg->io_dtype,
+ * contiguous).  Replaces fusion.py:372-411 (+ :170-184, :351-354, temporal.py:108-109).
+ * `packed` may be NULL when precision == F32. */
+XATTN_API int xattn_forward(const xattn_config* cfg, const float* params, const void* packed, const void* video_emb,
+                  const void* audio_emb, float* logits, void* workspace, int64_t workspace_bytes, void* stream);
+
+/* Backward of the same head for the Stage-1 step (frozen backbones => no input gradients).
+ * `workspace` must be the buffer a preceding xattn_forward (same cfg, training or
+ * save_for_backward set) filled.  grads (flat, xattn_param_layout) is OVERWRITTEN.
+ * Replaces: loss.backward() over the fusion parameters at train.py:227. */
+XATTN_API int xattn_backward(const xattn_config* cfg, const float* params, const void* video_emb, const void* audio_emb,
+                   const float* dlogits, float* grads, void* workspace, int64_t workspace_bytes, void* stream);
+
+/* ---- loss / optimizer ------------------------------------------------------------------------ */
+/* Mean-reduced cross entropy with label smoothing + its gradient w.r.t. logits.
+ * Replaces nn.CrossEntropyLoss(label_smoothing) at train.py:1033 / :218.  loss_out: 1 float.
+ * labels: int64[B]. grad_scale multiplies dlogits (1/world_size under data parallelism). */
+XATTN_API int xattn_ce_loss_fwd_bwd(const float* logits, const int64_t* labels, int32_t B, int32_t C, float label_smoothing,
+                          float grad_scale, float* loss_out, float* dlogits, void* stream);
+
+/* One fused Adam step over n floats.  decoupled == 0: torch.optim.Adam(weight_decay) — coupled L2,
+ * what the reference runs (train.py:872); decoupled == 1: AdamW.  step is 1-based. */
+XATTN_API int xattn_adam_step(float* params, const float* grads, float* exp_avg, float* exp_avg_sq, int64_t n, float lr,
+                    float beta1, float beta2, float eps, float weight_decay, int32_t step, int32_t decoupled,
+                    void* stream);
+
+/* ---- flat concat / gated heads (BASELINE config 5) -------------------------------------------- */
+typedef struct flat_head_config {
+  int32_t B, T, Ta, Dv, Da; /* sequence inputs [B,T,Dv], [B,Ta,Da]; T == Ta == 1 for pre-pooled inputs */
+  int32_t align_dim;        /* ClipStyleAlignment width (fusion.py:132-133); 0 = no alignment           */
+  int32_t common_dim;       /* audio_proj/video_proj width (fusion.py:240-241)                          */
+  int32_t C;
+  int32_t gated;            /* 0: mode="concat" (fusion.py:243-248), 1: mode="gated" (:252-259)         */
+  int32_t io_dtype;
+} flat_head_config;
+
+typedef enum flat_param_id {
+  FP_ALIGN_A_W = 0, /* semantic_alignment.audio_proj.weight [align,Da] */
+  FP_ALIGN_A_B,
+  FP_ALIGN_V_W,     /* semantic_alignment.video_proj.weight [align,Dv] */
+  FP_ALIGN_V_B,
+  FP_AUDIO_W,       /* audio_proj.weight [common, align|Da] */
+  FP_AUDIO_B,
+  FP_VIDEO_W,       /* video_proj.weight [common, align|Dv] */
+  FP_VIDEO_B,
+  FP_H0_W,          /* fusion.0.weight | gate.0.weight [common, 2*common] */
+  FP_H0_B,
+  FP_H1_W,          /* fusion.3.weight [C,common] | gate.3.weight [1,common] */
+  FP_H1_B,
+  FP_CLS_W,         /* (gated) classifier.weight [C,common] */
+  FP_CLS_B,
+  FP_COUNT
+} flat_param_id;
+
+XATTN_API int flat_head_param_layout(const flat_head_config* cfg, int64_t* offsets, int64_t* sizes, int64_t* total_floats);
+XATTN_API int flat_head_workspace_bytes(const flat_head_config* cfg, int64_t* bytes);
+/* logits[B,C] for mode in {"concat","gated"} with the temporal mean (the parameter-free last step
+ * of audio_model.encode / video_model.encode, fusion.py:414-415) fused in.  Replaces
+ * fusion.py:413-435 (+ :137-139).  Eval mode (ModalityDropout / Dropout identity). */
+XATTN_API int flat_head_forward(const flat_head_config* cfg, const float* params, const void* video_emb, const void* audio_emb,
+                      float* logits, void* workspace, int64_t workspace_bytes, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* XATTN_FUSION_H_ */

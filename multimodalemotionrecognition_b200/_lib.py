@@ -1,0 +1,170 @@
+"""ctypes binding of ``libxattn_fusion.so`` (C ABI: ``include/xattn_fusion.h``).
+
+There is no CPU or PyTorch-eager fallback: if the shared library has not been built
+(``python __graft_entry__.py build`` or ``make -C multimodalemotionrecognition_b200/csrc``) loading raises,
+and every entry point refuses non-sm_100 devices with ``XATTN_ERR_ARCH``.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+from pathlib import Path
+
+LIB_NAME = "libxattn_fusion.so"
+LIB_PATH = Path(__file__).resolve().parent / LIB_NAME
+ABI_VERSION = 3
+
+# xattn_status
+OK, ERR_SHAPE, ERR_DTYPE, ERR_ALIGN, ERR_ARCH, ERR_CUDA, ERR_WORKSPACE, ERR_NULL = range(8)
+HEAD_CONCAT, HEAD_GATED = 0, 1
+DTYPE_F32, DTYPE_BF16 = 0, 1
+
+# xattn_param_id -> reference state_dict key (None: resolved per head kind)
+XP_NAMES = [
+    "v_in_proj.weight", "v_in_proj.bias", "a_in_proj.weight", "a_in_proj.bias",
+    "audio_seq_proj.weight", "audio_seq_proj.bias",
+    "v2a_attn.in_proj_weight", "v2a_attn.in_proj_bias", "v2a_attn.out_proj.weight", "v2a_attn.out_proj.bias",
+    "a2v_attn.in_proj_weight", "a2v_attn.in_proj_bias", "a2v_attn.out_proj.weight", "a2v_attn.out_proj.bias",
+    "v_norm.weight", "v_norm.bias", "a_norm.weight", "a_norm.bias",
+    "HEAD0.weight", "HEAD0.bias", "HEAD1.weight", "HEAD1.bias", "xattn_classifier.weight", "xattn_classifier.bias",
+    "emotion_prior_bias.prior_net.0.weight", "emotion_prior_bias.prior_net.0.bias",
+    "emotion_prior_bias.prior_net.3.weight", "emotion_prior_bias.prior_net.3.bias",
+    "emotion_prior_bias.v_query_bias.weight", "emotion_prior_bias.v_query_bias.bias",
+    "emotion_prior_bias.a_key_bias.weight", "emotion_prior_bias.a_key_bias.bias",
+    "emotion_prior_bias.a_query_bias.weight", "emotion_prior_bias.a_query_bias.bias",
+    "emotion_prior_bias.v_key_bias.weight", "emotion_prior_bias.v_key_bias.bias",
+    "emotion_prior_bias.bias_scale",
+]
+XP_COUNT = len(XP_NAMES)
+
+FP_NAMES = [
+    "semantic_alignment.audio_proj.weight", "semantic_alignment.audio_proj.bias",
+    "semantic_alignment.video_proj.weight", "semantic_alignment.video_proj.bias",
+    "audio_proj.weight", "audio_proj.bias", "video_proj.weight", "video_proj.bias",
+    "H0.weight", "H0.bias", "H1.weight", "H1.bias", "classifier.weight", "classifier.bias",
+]
+FP_COUNT = len(FP_NAMES)
+
+
+def xattn_param_names(head: str) -> list[str]:
+    """state_dict key of every xattn_param_id for the given head kind (reference fusion.py:311-326)."""
+    h0, h1 = ("xattn_mlp.0", "xattn_mlp.3") if head == "concat" else ("xattn_gate.0", "xattn_gate.3")
+    return [n.replace("HEAD0", h0).replace("HEAD1", h1) for n in XP_NAMES]
+
+
+def flat_param_names(gated: bool) -> list[str]:
+    h0, h1 = ("gate.0", "gate.3") if gated else ("fusion.0", "fusion.3")
+    return [n.replace("H0", h0).replace("H1", h1) for n in FP_NAMES]
+
+
+class XAttnConfig(C.Structure):
+    _fields_ = [(n, C.c_int32) for n in (
+        "B", "T", "Ta", "Dv", "Da", "E", "H", "prior_dim", "prior_hidden", "common_dim", "C", "head_kind",
+        "use_prior", "io_dtype", "precision", "training", "save_for_backward")] + [
+        ("p_attn", C.c_float), ("p_path", C.c_float), ("p_head", C.c_float), ("p_prior", C.c_float),
+        ("seed", C.c_uint64), ("offset", C.c_uint64)]
+
+
+class FlatHeadConfig(C.Structure):
+    _fields_ = [(n, C.c_int32) for n in ("B", "T", "Ta", "Dv", "Da", "align_dim", "common_dim", "C", "gated", "io_dtype")]
+
+
+_EXPORTS = {
+    # name: (restype, argtypes)
+    "xattn_abi_version": (C.c_int, []),
+    "xattn_last_error": (C.c_char_p, []),
+    "xattn_launch_count": (C.c_ulonglong, []),
+    "xattn_param_layout": (C.c_int, [C.POINTER(XAttnConfig), C.POINTER(C.c_int64), C.POINTER(C.c_int64), C.POINTER(C.c_int64)]),
+    "xattn_workspace_bytes": (C.c_int, [C.POINTER(XAttnConfig), C.POINTER(C.c_int64)]),
+    "xattn_packed_bytes": (C.c_int, [C.POINTER(XAttnConfig), C.POINTER(C.c_int64)]),
+    "xattn_pack_weights": (C.c_int, [C.POINTER(XAttnConfig), C.c_void_p, C.c_void_p, C.c_void_p]),
+    "xattn_forward": (C.c_int, [C.POINTER(XAttnConfig), C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
+                                C.c_void_p, C.c_int64, C.c_void_p]),
+    "xattn_backward": (C.c_int, [C.POINTER(XAttnConfig), C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
+                                 C.c_void_p, C.c_int64, C.c_void_p]),
+    "xattn_ce_loss_fwd_bwd": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_float, C.c_float, C.c_void_p,
+                                        C.c_void_p, C.c_void_p]),
+    "xattn_adam_step": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_float, C.c_float,
+                                  C.c_float, C.c_float, C.c_float, C.c_int32, C.c_int32, C.c_void_p]),
+    "flat_head_param_layout": (C.c_int, [C.POINTER(FlatHeadConfig), C.POINTER(C.c_int64), C.POINTER(C.c_int64),
+                                         C.POINTER(C.c_int64)]),
+    "flat_head_workspace_bytes": (C.c_int, [C.POINTER(FlatHeadConfig), C.POINTER(C.c_int64)]),
+    "flat_head_forward": (C.c_int, [C.POINTER(FlatHeadConfig), C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
+                                    C.c_int64, C.c_void_p]),
+}
+EXPORTED_SYMBOLS = tuple(_EXPORTS)
+
+_lib = None
+
+
+def load() -> C.CDLL:
+    """Load the extension once.  Raises RuntimeError when it is missing — by design there is no fallback."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    path = Path(os.environ.get("XATTN_FUSION_LIB", str(LIB_PATH)))
+    if not path.exists():
+        raise RuntimeError(
+            f"{path} not found: the CUDA extension is not built. Run `python __graft_entry__.py build` "
+            "(or `make -C multimodalemotionrecognition_b200/csrc`). There is no CPU fallback.")
+    lib = C.CDLL(str(path))
+    for name, (res, args) in _EXPORTS.items():
+        fn = getattr(lib, name)
+        fn.restype = res
+        fn.argtypes = args
+    if lib.xattn_abi_version() != ABI_VERSION:
+        raise RuntimeError(f"{path}: ABI version {lib.xattn_abi_version()} != expected {ABI_VERSION}; rebuild")
+    _lib = lib
+    return lib
+
+
+def last_error() -> str:
+    return load().xattn_last_error().decode("utf-8", "replace")
+
+
+def check(status: int) -> None:
+    """Map an xattn_status to the reference's error convention (ValueError for bad arguments)."""
+    if status == OK:
+        return
+    msg = f"xattn_fusion: {last_error()} (status {status})"
+    if status in (ERR_SHAPE, ERR_DTYPE, ERR_ALIGN, ERR_NULL):
+        raise ValueError(msg)
+    raise RuntimeError(msg)
+
+
+def launch_count() -> int:
+    return int(load().xattn_launch_count())
+
+
+def xattn_param_layout(cfg: XAttnConfig):
+    off = (C.c_int64 * XP_COUNT)()
+    size = (C.c_int64 * XP_COUNT)()
+    total = C.c_int64(0)
+    check(load().xattn_param_layout(C.byref(cfg), off, size, C.byref(total)))
+    return list(off), list(size), int(total.value)
+
+
+def flat_param_layout(cfg: FlatHeadConfig):
+    off = (C.c_int64 * FP_COUNT)()
+    size = (C.c_int64 * FP_COUNT)()
+    total = C.c_int64(0)
+    check(load().flat_head_param_layout(C.byref(cfg), off, size, C.byref(total)))
+    return list(off), list(size), int(total.value)
+
+
+def workspace_bytes(cfg: XAttnConfig) -> int:
+    n = C.c_int64(0)
+    check(load().xattn_workspace_bytes(C.byref(cfg), C.byref(n)))
+    return int(n.value)
+
+
+def packed_bytes(cfg: XAttnConfig) -> int:
+    n = C.c_int64(0)
+    check(load().xattn_packed_bytes(C.byref(cfg), C.byref(n)))
+    return int(n.value)
+
+
+def flat_workspace_bytes(cfg: FlatHeadConfig) -> int:
+    n = C.c_int64(0)
+    check(load().flat_head_workspace_bytes(C.byref(cfg), C.byref(n)))
+    return int(n.value)

@@ -1,0 +1,469 @@
+// fp32 backward of the xattn fusion head for the Stage-1 step (reference train.py:227: loss.backward()
+// with both backbones frozen, train.py:808-812 — so no gradient flows into video_emb / audio_emb).
+// Hand-derived reverse of fwd_f32.cu; activations come from the forward's workspace, dropout masks are
+// regenerated from the same Philox counters.
+#include "gemm_simt.cuh"
+#include "kernels_f32.cuh"
+
+namespace xf {
+
+// ---- db[N] += column sums ----------------------------------------------------------------------------------
+__global__ void colsum_kernel(const float* __restrict__ dY, int64_t ldy, int M, int N, float* __restrict__ db, int rows_per_block) {
+  const int n = blockIdx.x * blockDim.x + threadIdx.x;
+  if (n >= N) return;
+  const int r0 = blockIdx.y * rows_per_block, r1 = min(M, r0 + rows_per_block);
+  float s = 0.f;
+  for (int r = r0; r < r1; ++r) s += dY[(int64_t)r * ldy + n];
+  atomicAdd(db + n, s);
+}
+void launch_colsum(cudaStream_t st, const float* dY, int64_t ldy, int M, int N, float* db) {
+  if (M <= 0 || N <= 0) return;
+  const int rpb = 256;
+  dim3 grid((N + 127) / 128, (M + rpb - 1) / rpb);
+  colsum_kernel<<<grid, 128, 0, st>>>(dY, ldy, M, N, db, rpb);
+  count_launch();
+}
+
+// ---- head: gradient w.r.t. the hidden pre-activation (and the gated blend) ---------------------------------
+// concat: d_hh = (dlogits·W1) ⊙ relu'/dropout mask.
+// gated : dfused given; dg = <dfused, v̄-ā>; dz = dg·g(1-g); d_pooled = [g·dfused, (1-g)·dfused]; d_hh = dz·w3 ⊙ mask.
+__global__ void __launch_bounds__(256) head_bwd_mid_kernel(const float* __restrict__ dlogits, const float* __restrict__ w1,
+                                                           const float* __restrict__ hhid, const float* __restrict__ pooled,
+                                                           const float* __restrict__ gate, const float* __restrict__ dfused,
+                                                           float* __restrict__ d_hh, float* __restrict__ d_pooled,
+                                                           float* __restrict__ d_z, int E, int HW, int C, int gated, float inv_keep) {
+  const int b = blockIdx.x, tid = threadIdx.x;
+  __shared__ float red[32];
+  __shared__ float s_dz;
+  if (!gated) {
+    for (int h = tid; h < HW; h += blockDim.x) {
+      float s = 0.f;
+      for (int c = 0; c < C; ++c) s = fmaf(dlogits[(int64_t)b * C + c], w1[(int64_t)c * HW + h], s);
+      d_hh[(int64_t)b * HW + h] = hhid[(int64_t)b * HW + h] > 0.f ? s * inv_keep : 0.f;
+    }
+    return;
+  }
+  const float g = gate[b];
+  float part = 0.f;
+  for (int e = tid; e < E; e += blockDim.x) {
+    const float df = dfused[(int64_t)b * E + e];
+    part = fmaf(df, pooled[(int64_t)b * 2 * E + e] - pooled[(int64_t)b * 2 * E + E + e], part);
+    d_pooled[(int64_t)b * 2 * E + e] = g * df;
+    d_pooled[(int64_t)b * 2 * E + E + e] = (1.f - g) * df;
+  }
+  part = warp_sum(part);
+  if ((tid & 31) == 0) red[tid >> 5] = part;
+  __syncthreads();
+  if (tid == 0) {
+    float s = 0.f;
+    for (int i = 0; i < (int)(blockDim.x >> 5); ++i) s += red[i];
+    s_dz = s * g * (1.f - g);
+    d_z[b] = s_dz;
+  }
+  __syncthreads();
+  const float dz = s_dz;
+  for (int h = tid; h < HW; h += blockDim.x)
+    d_hh[(int64_t)b * HW + h] = hhid[(int64_t)b * HW + h] > 0.f ? dz * w1[h] * inv_keep : 0.f;
+}
+
+// ---- LayerNorm backward -------------------------------------------------------------------------------------
+// dy = dy_full (optional) + dy_pool[b]/L (optional; gradient of the temporal mean).  dx -> dx_out,
+// dx·dpf[b] -> dbranch (gradient into the drop-path branch).  dgamma/dbeta accumulated atomically.
+constexpr int LN_MAXK = 16;  // E <= 512
+__global__ void __launch_bounds__(256) ln_bwd_kernel(const float* __restrict__ dy_full, const float* __restrict__ dy_pool,
+                                                     int64_t pool_ld, float inv_L, const float* __restrict__ s,
+                                                     const float* __restrict__ mean, const float* __restrict__ rstd,
+                                                     const float* __restrict__ gamma, const float* __restrict__ dpf,
+                                                     float* __restrict__ dx_out, float* __restrict__ dbranch,
+                                                     float* __restrict__ dgamma, float* __restrict__ dbeta, int rows, int L, int E) {
+  const int lane = threadIdx.x & 31;
+  const int wpb = blockDim.x >> 5;
+  float ag[LN_MAXK], ab[LN_MAXK];
+#pragma unroll
+  for (int k = 0; k < LN_MAXK; ++k) ag[k] = ab[k] = 0.f;
+  for (int row = blockIdx.x * wpb + (threadIdx.x >> 5); row < rows; row += gridDim.x * wpb) {
+    const int b = row / L;
+    const float mu = mean[row], rs = rstd[row];
+    float s1 = 0.f, s2 = 0.f;
+#pragma unroll
+    for (int k = 0; k < LN_MAXK; ++k) {
+      const int e = lane + 32 * k;
+      if (e < E) {
+        float dy = dy_full ? dy_full[(int64_t)row * E + e] : 0.f;
+        if (dy_pool) dy += dy_pool[(int64_t)b * pool_ld + e] * inv_L;
+        const float xh = (s[(int64_t)row * E + e] - mu) * rs;
+        const float dyg = dy * gamma[e];
+        s1 += dyg;
+        s2 = fmaf(dyg, xh, s2);
+        ag[k] = fmaf(dy, xh, ag[k]);
+        ab[k] += dy;
+      }
+    }
+    s1 = warp_sum(s1) / (float)E;
+    s2 = warp_sum(s2) / (float)E;
+    const float f = dpf ? dpf[b] : 1.f;
+#pragma unroll
+    for (int k = 0; k < LN_MAXK; ++k) {
+      const int e = lane + 32 * k;
+      if (e < E) {
+        float dy = dy_full ? dy_full[(int64_t)row * E + e] : 0.f;
+        if (dy_pool) dy += dy_pool[(int64_t)b * pool_ld + e] * inv_L;
+        const float xh = (s[(int64_t)row * E + e] - mu) * rs;
+        const float dx = rs * (dy * gamma[e] - s1 - xh * s2);
+        dx_out[(int64_t)row * E + e] = dx;
+        dbranch[(int64_t)row * E + e] = dx * f;
+      }
+    }
+  }
+#pragma unroll
+  for (int k = 0; k < LN_MAXK; ++k) {
+    const int e = lane + 32 * k;
+    if (e < E) {
+      atomicAdd(dgamma + e, ag[k]);
+      atomicAdd(dbeta + e, ab[k]);
+    }
+  }
+}
+
+// ---- attention backward ---------------------------------------------------------------------------------------
+// Per clip, heads in sequence.  With Pd = dropout(P):  dV = Pd^T dO ; dPd = dO V^T ; dP = dPd ⊙ mask ;
+// dS = P ⊙ (dP - rowsum(dP ⊙ P)) ; dQ = scale · dS K ; dK = dS^T (scale·Q) ; dBias = Σ_h dS_h and through
+// bias = tanh(qs_l + ks_s)·β :  g = dBias·β·(1 - tanh²) ; dqs_l = Σ_s g ; dks_s = Σ_l g ; dβ = Σ dBias·tanh.
+__global__ void __launch_bounds__(256) attn_bwd_kernel(AttnBwdArgs a) {
+  extern __shared__ float sm[];
+  const int b = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nw = blockDim.x >> 5;
+  const int L = a.L, S = a.S, E = a.E, H = a.H, dh = E / H, dp = dh + 1;
+  float* Qs = sm;                  // [L][dp]  (scaled q)
+  float* Ks = Qs + L * dp;         // [S][dp]
+  float* Vs = Ks + S * dp;         // [S][dp]
+  float* dOs = Vs + S * dp;        // [L][dp]
+  float* dSs = dOs + L * dp;       // [L][S]
+  float* Pds = dSs + L * S;        // [L][S]
+  float* dBs = Pds + L * S;        // [L][S]  Σ_h dS
+  __shared__ float red[32];
+  const float* q = a.q + (int64_t)b * L * E;
+  const float* kv = a.kv + (int64_t)b * S * 2 * E;
+  const float* dO = a.dO + (int64_t)b * L * E;
+  for (int i = tid; i < L * S; i += blockDim.x) dBs[i] = 0.f;
+  for (int h = 0; h < H; ++h) {
+    for (int i = tid; i < L * dh; i += blockDim.x) {
+      const int l = i / dh, d = i - l * dh;
+      Qs[l * dp + d] = q[(int64_t)l * E + h * dh + d] * a.scale;
+      dOs[l * dp + d] = dO[(int64_t)l * E + h * dh + d];
+    }
+    for (int i = tid; i < S * dh; i += blockDim.x) {
+      const int s = i / dh, d = i - s * dh;
+      Ks[s * dp + d] = kv[(int64_t)s * 2 * E + h * dh + d];
+      Vs[s * dp + d] = kv[(int64_t)s * 2 * E + E + h * dh + d];
+    }
+    __syncthreads();
+    for (int l = warp; l < L; l += nw) {
+      const int64_t pbase = (((int64_t)b * H + h) * L + l) * S;
+      float rowdot = 0.f;
+      for (int s = lane; s < S; s += 32) {
+        const float p = a.P[pbase + s];
+        const float f = a.p_drop > 0.f ? drop_factor(a.p_drop, a.seed, a.offset, a.rng_stream, (uint64_t)(pbase + s)) : 1.f;
+        float dpd = 0.f;
+        for (int d = 0; d < dh; ++d) dpd = fmaf(dOs[l * dp + d], Vs[s * dp + d], dpd);
+        const float dP = dpd * f;
+        Pds[l * S + s] = p * f;
+        dSs[l * S + s] = dP;          // holds dP until the row dot is known
+        rowdot = fmaf(dP, p, rowdot);
+      }
+      rowdot = warp_sum(rowdot);
+      for (int s = lane; s < S; s += 32) {
+        const float p = a.P[pbase + s];
+        dSs[l * S + s] = p * (dSs[l * S + s] - rowdot);
+      }
+    }
+    __syncthreads();
+    // dV, dK : [S, dh]
+    for (int i = tid; i < S * dh; i += blockDim.x) {
+      const int s = i / dh, d = i - s * dh;
+      float dv = 0.f, dk = 0.f;
+      for (int l = 0; l < L; ++l) {
+        dv = fmaf(Pds[l * S + s], dOs[l * dp + d], dv);
+        dk = fmaf(dSs[l * S + s], Qs[l * dp + d], dk);
+      }
+      a.dkv[((int64_t)b * S + s) * 2 * E + h * dh + d] = dk;
+      a.dkv[((int64_t)b * S + s) * 2 * E + E + h * dh + d] = dv;
+    }
+    // dQ : [L, dh]
+    for (int i = tid; i < L * dh; i += blockDim.x) {
+      const int l = i / dh, d = i - l * dh;
+      float dq = 0.f;
+      for (int s = 0; s < S; ++s) dq = fmaf(dSs[l * S + s], Ks[s * dp + d], dq);
+      a.dq[((int64_t)b * L + l) * E + h * dh + d] = dq * a.scale;
+    }
+    for (int i = tid; i < L * S; i += blockDim.x) dBs[i] += dSs[i];
+    __syncthreads();
+  }
+  if (a.qs == nullptr) return;
+  const float* qs = a.qs + (int64_t)b * L;
+  const float* ks = a.ks + (int64_t)b * S;
+  const float bscale = a.bias_scale[0];
+  float dscale = 0.f;
+  for (int i = tid; i < L * S; i += blockDim.x) {
+    const int l = i / S, s = i - l * S;
+    const float t = tanhf(qs[l] + ks[s]);
+    const float db = dBs[i];
+    dscale = fmaf(db, t, dscale);
+    dBs[i] = db * bscale * (1.f - t * t);
+  }
+  dscale = warp_sum(dscale);
+  if (lane == 0) red[warp] = dscale;
+  __syncthreads();
+  if (tid == 0) {
+    float s = 0.f;
+    for (int i = 0; i < nw; ++i) s += red[i];
+    atomicAdd(a.dbias_scale, s);
+  }
+  for (int l = warp; l < L; l += nw) {
+    float s = 0.f;
+    for (int j = lane; j < S; j += 32) s += dBs[l * S + j];
+    s = warp_sum(s);
+    if (lane == 0) a.dqs[(int64_t)b * L + l] = s;
+  }
+  for (int j = tid; j < S; j += blockDim.x) {
+    float s = 0.f;
+    for (int l = 0; l < L; ++l) s += dBs[l * S + j];
+    a.dks[(int64_t)b * S + j] = s;
+  }
+}
+
+static int launch_attn_bwd(cudaStream_t st, const AttnBwdArgs& a, int B) {
+  const int dh = a.E / a.H;
+  const size_t smem = sizeof(float) * ((size_t)(2 * a.L + 2 * a.S) * (dh + 1) + 3 * (size_t)a.L * a.S);
+  if (smem > 200 * 1024) XF_FAIL(XATTN_ERR_SHAPE, "attention backward tile needs %zu B of shared memory (> 200 KiB)", smem);
+  static size_t configured = 0;
+  if (smem > 48 * 1024 && smem > configured) {
+    XF_CUDA(cudaFuncSetAttribute(attn_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    configured = smem;
+  }
+  attn_bwd_kernel<<<B, 256, smem, st>>>(a);
+  count_launch();
+  XF_LAUNCH_CHECK();
+  return XATTN_OK;
+}
+
+// ---- emotion prior backward -------------------------------------------------------------------------------------
+struct PriorBwdArgs {
+  const float *v0, *a0, *phid, *prior, *w0, *w3;
+  const float* wh[4];
+  const float *d_qv, *d_ka, *d_qa, *d_kvs;
+  float *d_v0, *d_a0, *d_prior, *d_phid;
+  float* g_wh[4];
+  float* g_bh[4];
+  int T, Ta, E, P, Hd;
+  float inv_keep;
+};
+__global__ void __launch_bounds__(256) prior_bwd_kernel(PriorBwdArgs a) {
+  extern __shared__ float sm[];
+  const int b = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nw = blockDim.x >> 5;
+  const int E = a.E, P = a.P, Hd = a.Hd, T = a.T, Ta = a.Ta;
+  float* sq = sm;               // [4]
+  float* dprior = sq + 4;       // [P]
+  float* dphid = dprior + P;    // [Hd]
+  float* dpool = dphid + Hd;    // [2E]
+  const float* dsc[4] = {a.d_qv + (int64_t)b * T, a.d_ka + (int64_t)b * Ta, a.d_qa + (int64_t)b * Ta, a.d_kvs + (int64_t)b * T};
+  const int len[4] = {T, Ta, Ta, T};
+  if (warp < 4) {
+    float s = 0.f;
+    for (int i = lane; i < len[warp]; i += 32) s += dsc[warp][i];
+    s = warp_sum(s);
+    if (lane == 0) sq[warp] = s;
+  }
+  __syncthreads();
+  for (int p = tid; p < P; p += blockDim.x) {
+    float s = 0.f;
+    for (int k = 0; k < 4; ++k) s = fmaf(sq[k], a.wh[k][E + p], s);
+    dprior[p] = s;
+    a.d_prior[(int64_t)b * P + p] = s;
+    const float pr = a.prior[(int64_t)b * P + p];
+    for (int k = 0; k < 4; ++k) atomicAdd(a.g_wh[k] + E + p, sq[k] * pr);
+  }
+  if (tid < 4) atomicAdd(a.g_bh[tid], sq[tid]);
+  __syncthreads();
+  for (int h = tid; h < Hd; h += blockDim.x) {
+    float s = 0.f;
+    for (int p = 0; p < P; ++p) s = fmaf(dprior[p], a.w3[(int64_t)p * Hd + h], s);
+    s = a.phid[(int64_t)b * Hd + h] > 0.f ? s * a.inv_keep : 0.f;
+    dphid[h] = s;
+    a.d_phid[(int64_t)b * Hd + h] = s;
+  }
+  __syncthreads();
+  for (int k = tid; k < 2 * E; k += blockDim.x) {
+    float s = 0.f;
+    for (int h = 0; h < Hd; ++h) s = fmaf(dphid[h], a.w0[(int64_t)h * 2 * E + k], s);
+    dpool[k] = s;
+  }
+  __syncthreads();
+  const float* v0 = a.v0 + (int64_t)b * T * E;
+  const float* a0 = a.a0 + (int64_t)b * Ta * E;
+  float* dv0 = a.d_v0 + (int64_t)b * T * E;
+  float* da0 = a.d_a0 + (int64_t)b * Ta * E;
+  // token gradients + the token part of the score-head weights (block-local reduction, then one atomic per e)
+  for (int e = tid; e < E; e += blockDim.x) {
+    const float w_vq = a.wh[0][e], w_ak = a.wh[1][e], w_aq = a.wh[2][e], w_vk = a.wh[3][e];
+    const float pv = dpool[e] / (float)T, pa = dpool[E + e] / (float)Ta;
+    float g0 = 0.f, g1 = 0.f, g2 = 0.f, g3 = 0.f;
+    for (int i = 0; i < T; ++i) {
+      const float dq = dsc[0][i], dk = dsc[3][i], x = v0[(int64_t)i * E + e];
+      dv0[(int64_t)i * E + e] += dq * w_vq + dk * w_vk + pv;
+      g0 = fmaf(dq, x, g0);
+      g3 = fmaf(dk, x, g3);
+    }
+    for (int j = 0; j < Ta; ++j) {
+      const float dk = dsc[1][j], dq = dsc[2][j], x = a0[(int64_t)j * E + e];
+      da0[(int64_t)j * E + e] += dk * w_ak + dq * w_aq + pa;
+      g1 = fmaf(dk, x, g1);
+      g2 = fmaf(dq, x, g2);
+    }
+    atomicAdd(a.g_wh[0] + e, g0);
+    atomicAdd(a.g_wh[1] + e, g1);
+    atomicAdd(a.g_wh[2] + e, g2);
+    atomicAdd(a.g_wh[3] + e, g3);
+  }
+}
+
+// ---- orchestration ------------------------------------------------------------------------------------------------
+template <typename TIO>
+static int backward_f32_impl(const xattn_config& c, const float* params, const TIO* xv, const TIO* xa, const float* dlogits,
+                             float* grads, float* ws, cudaStream_t st) {
+  ParamLayout pl;
+  compute_param_layout(c, pl);
+  WsF32 w;
+  compute_ws_f32(c, w);
+  auto P = [&](int id) { return params + pl.off[id]; };
+  auto G = [&](int id) { return grads + pl.off[id]; };
+  const int B = c.B, T = c.T, Ta = c.Ta, E = c.E, H = c.H, C = c.C;
+  const bool train = c.training != 0;
+  const float p_attn = train ? c.p_attn : 0.f, p_head = train ? c.p_head : 0.f, p_prior = train ? c.p_prior : 0.f;
+  const bool gated = c.head_kind == XATTN_HEAD_GATED;
+  const int HW = gated ? E : c.common_dim;
+  const float scale = 1.0f / sqrtf((float)(E / H));
+
+  XF_CUDA(cudaMemsetAsync(grads, 0, sizeof(float) * pl.total, st));
+
+  // ---- head (fusion.py:405-411) ----
+  if (!gated) {
+    linear_bwd_dw<float>(st, dlogits, C, ws + w.hhid, HW, G(XP_HEAD1_W), B, C, HW);
+    launch_colsum(st, dlogits, C, B, C, G(XP_HEAD1_B));
+    head_bwd_mid_kernel<<<B, 256, 0, st>>>(dlogits, P(XP_HEAD1_W), ws + w.hhid, nullptr, nullptr, nullptr, ws + w.d_hh, nullptr,
+                                           nullptr, E, HW, C, 0, 1.f / (1.f - p_head));
+    count_launch();
+    linear_bwd_dw<float>(st, ws + w.d_hh, HW, ws + w.pooled, 2 * E, G(XP_HEAD0_W), B, HW, 2 * E);
+    launch_colsum(st, ws + w.d_hh, HW, B, HW, G(XP_HEAD0_B));
+    linear_bwd_dx(st, ws + w.d_hh, HW, P(XP_HEAD0_W), ws + w.d_pooled, B, HW, 2 * E, false);
+  } else {
+    linear_bwd_dw<float>(st, dlogits, C, ws + w.fusedg, E, G(XP_CLS_W), B, C, E);
+    launch_colsum(st, dlogits, C, B, C, G(XP_CLS_B));
+    linear_bwd_dx(st, dlogits, C, P(XP_CLS_W), ws + w.d_fused, B, C, E, false);
+    head_bwd_mid_kernel<<<B, 256, 0, st>>>(nullptr, P(XP_HEAD1_W), ws + w.hhid, ws + w.pooled, ws + w.gate, ws + w.d_fused,
+                                           ws + w.d_hh, ws + w.d_pooled, ws + w.d_z, E, HW, C, 1, 1.f / (1.f - p_head));
+    count_launch();
+    linear_bwd_dw<float>(st, ws + w.d_z, 1, ws + w.hhid, HW, G(XP_HEAD1_W), B, 1, HW);
+    launch_colsum(st, ws + w.d_z, 1, B, 1, G(XP_HEAD1_B));
+    linear_bwd_dw<float>(st, ws + w.d_hh, HW, ws + w.pooled, 2 * E, G(XP_HEAD0_W), B, HW, 2 * E);
+    launch_colsum(st, ws + w.d_hh, HW, B, HW, G(XP_HEAD0_B));
+    linear_bwd_dx(st, ws + w.d_hh, HW, P(XP_HEAD0_W), ws + w.d_pooled, B, HW, 2 * E, true);
+  }
+  XF_LAUNCH_CHECK();
+
+  const int ln_grid = 4 * num_sms();
+  // ---- a_norm backward (fusion.py:399) + mean pool (temporal.py:108-109) ----
+  ln_bwd_kernel<<<ln_grid, 256, 0, st>>>(nullptr, ws + w.d_pooled + E, 2 * E, 1.f / (float)Ta, ws + w.s2, ws + w.mean2, ws + w.rstd2,
+                                         P(XP_AN_W), ws + w.dp2, ws + w.d_a0, ws + w.d_br2, G(XP_AN_W), G(XP_AN_B), B * Ta, Ta, E);
+  count_launch();
+  // a2v out_proj
+  linear_bwd_dw<float>(st, ws + w.d_br2, E, ws + w.o2, E, G(XP_A2V_OUT_W), B * Ta, E, E);
+  launch_colsum(st, ws + w.d_br2, E, B * Ta, E, G(XP_A2V_OUT_B));
+  linear_bwd_dx(st, ws + w.d_br2, E, P(XP_A2V_OUT_W), ws + w.d_o2, B * Ta, E, E, false);
+  XF_LAUNCH_CHECK();
+  {
+    AttnBwdArgs aa;
+    aa.q = ws + w.q2; aa.kv = ws + w.kv2;
+    aa.qs = c.use_prior ? ws + w.qa : nullptr; aa.ks = c.use_prior ? ws + w.kvs : nullptr;
+    aa.bias_scale = c.use_prior ? P(XP_BIAS_SCALE) : nullptr; aa.P = ws + w.p2; aa.dO = ws + w.d_o2;
+    aa.dq = ws + w.d_q2; aa.dkv = ws + w.d_kv2; aa.dqs = ws + w.d_qa; aa.dks = ws + w.d_kvs;
+    aa.dbias_scale = c.use_prior ? G(XP_BIAS_SCALE) : nullptr;
+    aa.L = Ta; aa.S = T; aa.E = E; aa.H = H; aa.scale = scale; aa.p_drop = p_attn; aa.seed = c.seed; aa.offset = c.offset;
+    aa.rng_stream = RS_ATTN2;
+    XF_TRY(launch_attn_bwd(st, aa, B));
+  }
+  // a2v in_proj: q from a0, k|v from v1
+  linear_bwd_dw<float>(st, ws + w.d_q2, E, ws + w.a0, E, G(XP_A2V_IN_W), B * Ta, E, E);
+  launch_colsum(st, ws + w.d_q2, E, B * Ta, E, G(XP_A2V_IN_B));
+  linear_bwd_dx(st, ws + w.d_q2, E, P(XP_A2V_IN_W), ws + w.d_a0, B * Ta, E, E, true);
+  linear_bwd_dw<float>(st, ws + w.d_kv2, 2 * E, ws + w.v1, E, G(XP_A2V_IN_W) + (int64_t)E * E, B * T, 2 * E, E);
+  launch_colsum(st, ws + w.d_kv2, 2 * E, B * T, 2 * E, G(XP_A2V_IN_B) + E);
+  linear_bwd_dx(st, ws + w.d_kv2, 2 * E, P(XP_A2V_IN_W) + (int64_t)E * E, ws + w.d_v1, B * T, 2 * E, E, false);
+  XF_LAUNCH_CHECK();
+  // ---- v_norm backward (fusion.py:395) ----
+  ln_bwd_kernel<<<ln_grid, 256, 0, st>>>(ws + w.d_v1, ws + w.d_pooled, 2 * E, 1.f / (float)T, ws + w.s1, ws + w.mean1, ws + w.rstd1,
+                                         P(XP_VN_W), ws + w.dp1, ws + w.d_v0, ws + w.d_br1, G(XP_VN_W), G(XP_VN_B), B * T, T, E);
+  count_launch();
+  linear_bwd_dw<float>(st, ws + w.d_br1, E, ws + w.o1, E, G(XP_V2A_OUT_W), B * T, E, E);
+  launch_colsum(st, ws + w.d_br1, E, B * T, E, G(XP_V2A_OUT_B));
+  linear_bwd_dx(st, ws + w.d_br1, E, P(XP_V2A_OUT_W), ws + w.d_o1, B * T, E, E, false);
+  XF_LAUNCH_CHECK();
+  {
+    AttnBwdArgs aa;
+    aa.q = ws + w.q1; aa.kv = ws + w.kv1;
+    aa.qs = c.use_prior ? ws + w.qv : nullptr; aa.ks = c.use_prior ? ws + w.ka : nullptr;
+    aa.bias_scale = c.use_prior ? P(XP_BIAS_SCALE) : nullptr; aa.P = ws + w.p1; aa.dO = ws + w.d_o1;
+    aa.dq = ws + w.d_q1; aa.dkv = ws + w.d_kv1; aa.dqs = ws + w.d_qv; aa.dks = ws + w.d_ka;
+    aa.dbias_scale = c.use_prior ? G(XP_BIAS_SCALE) : nullptr;
+    aa.L = T; aa.S = Ta; aa.E = E; aa.H = H; aa.scale = scale; aa.p_drop = p_attn; aa.seed = c.seed; aa.offset = c.offset;
+    aa.rng_stream = RS_ATTN1;
+    XF_TRY(launch_attn_bwd(st, aa, B));
+  }
+  linear_bwd_dw<float>(st, ws + w.d_q1, E, ws + w.v0, E, G(XP_V2A_IN_W), B * T, E, E);
+  launch_colsum(st, ws + w.d_q1, E, B * T, E, G(XP_V2A_IN_B));
+  linear_bwd_dx(st, ws + w.d_q1, E, P(XP_V2A_IN_W), ws + w.d_v0, B * T, E, E, true);
+  linear_bwd_dw<float>(st, ws + w.d_kv1, 2 * E, ws + w.a0, E, G(XP_V2A_IN_W) + (int64_t)E * E, B * Ta, 2 * E, E);
+  launch_colsum(st, ws + w.d_kv1, 2 * E, B * Ta, 2 * E, G(XP_V2A_IN_B) + E);
+  linear_bwd_dx(st, ws + w.d_kv1, 2 * E, P(XP_V2A_IN_W) + (int64_t)E * E, ws + w.d_a0, B * Ta, 2 * E, E, true);
+  XF_LAUNCH_CHECK();
+
+  // ---- emotion prior (fusion.py:170-184) ----
+  if (c.use_prior) {
+    PriorBwdArgs pa;
+    pa.v0 = ws + w.v0; pa.a0 = ws + w.a0; pa.phid = ws + w.phid; pa.prior = ws + w.prior;
+    pa.w0 = P(XP_PRIOR0_W); pa.w3 = P(XP_PRIOR3_W);
+    pa.wh[0] = P(XP_VQ_W); pa.wh[1] = P(XP_AK_W); pa.wh[2] = P(XP_AQ_W); pa.wh[3] = P(XP_VK_W);
+    pa.g_wh[0] = G(XP_VQ_W); pa.g_wh[1] = G(XP_AK_W); pa.g_wh[2] = G(XP_AQ_W); pa.g_wh[3] = G(XP_VK_W);
+    pa.g_bh[0] = G(XP_VQ_B); pa.g_bh[1] = G(XP_AK_B); pa.g_bh[2] = G(XP_AQ_B); pa.g_bh[3] = G(XP_VK_B);
+    pa.d_qv = ws + w.d_qv; pa.d_ka = ws + w.d_ka; pa.d_qa = ws + w.d_qa; pa.d_kvs = ws + w.d_kvs;
+    pa.d_v0 = ws + w.d_v0; pa.d_a0 = ws + w.d_a0; pa.d_prior = ws + w.d_prior; pa.d_phid = ws + w.d_phid;
+    pa.T = T; pa.Ta = Ta; pa.E = E; pa.P = c.prior_dim; pa.Hd = c.prior_hidden; pa.inv_keep = 1.f / (1.f - p_prior);
+    const size_t smem = sizeof(float) * (4 + c.prior_dim + c.prior_hidden + 2 * E);
+    prior_bwd_kernel<<<B, 256, smem, st>>>(pa);
+    count_launch();
+    linear_bwd_dw<float>(st, ws + w.d_prior, c.prior_dim, ws + w.phid, c.prior_hidden, G(XP_PRIOR3_W), B, c.prior_dim, c.prior_hidden);
+    launch_colsum(st, ws + w.d_prior, c.prior_dim, B, c.prior_dim, G(XP_PRIOR3_B));
+    linear_bwd_dw<float>(st, ws + w.d_phid, c.prior_hidden, ws + w.pooled0, 2 * E, G(XP_PRIOR0_W), B, c.prior_hidden, 2 * E);
+    launch_colsum(st, ws + w.d_phid, c.prior_hidden, B, c.prior_hidden, G(XP_PRIOR0_B));
+    XF_LAUNCH_CHECK();
+  }
+
+  // ---- input projections (fusion.py:386, :378, :372); the inputs are frozen embeddings: no dX ----
+  linear_bwd_dw<float>(st, ws + w.d_a0, E, ws + w.aseq, E, G(XP_A_IN_W), B * Ta, E, E);
+  launch_colsum(st, ws + w.d_a0, E, B * Ta, E, G(XP_A_IN_B));
+  linear_bwd_dx(st, ws + w.d_a0, E, P(XP_A_IN_W), ws + w.d_aseq, B * Ta, E, E, false);
+  linear_bwd_dw<TIO>(st, ws + w.d_aseq, E, xa, c.Da, G(XP_SEQ_W), B * Ta, E, c.Da);
+  launch_colsum(st, ws + w.d_aseq, E, B * Ta, E, G(XP_SEQ_B));
+  linear_bwd_dw<TIO>(st, ws + w.d_v0, E, xv, c.Dv, G(XP_V_IN_W), B * T, E, c.Dv);
+  launch_colsum(st, ws + w.d_v0, E, B * T, E, G(XP_V_IN_B));
+  XF_LAUNCH_CHECK();
+  return XATTN_OK;
+}
+
+int backward_f32(const xattn_config& c, const float* params, const void* xv, const void* xa, const float* dlogits, float* grads,
+                 void* ws, cudaStream_t st) {
+  if (c.io_dtype == XATTN_DTYPE_BF16)
+    return backward_f32_impl<__nv_bfloat16>(c, params, (const __nv_bfloat16*)xv, (const __nv_bfloat16*)xa, dlogits, grads, (float*)ws, st);
+  return backward_f32_impl<float>(c, params, (const float*)xv, (const float*)xa, dlogits, grads, (float*)ws, st);
+}
+
+}  // namespace xf

@@ -1,0 +1,129 @@
+// Host-side plumbing: error text, config validation, parameter + workspace layouts.
+#include "common.cuh"
+
+#include <stdarg.h>
+#include <string.h>
+
+namespace xf {
+
+static thread_local char g_err[512] = "";
+unsigned long long g_launch_count = 0;
+
+void set_error(const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+}
+const char* last_error() { return g_err; }
+
+int check_device_sm100() {
+  int dev = 0;
+  XF_CUDA(cudaGetDevice(&dev));
+  static int cached_dev = -1, cached_major = 0;
+  if (cached_dev != dev) {
+    int major = 0;
+    XF_CUDA(cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, dev));
+    cached_major = major;
+    cached_dev = dev;
+  }
+  if (cached_major != 10) XF_FAIL(XATTN_ERR_ARCH, "device %d is sm_%d0; this library is built for sm_100a only (no fallback)", dev, cached_major);
+  return XATTN_OK;
+}
+
+int num_sms() {
+  static int n = 0;
+  if (n == 0) {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
+    if (n <= 0) n = 148;
+  }
+  return n;
+}
+
+int validate_config(const xattn_config* c) {
+  if (c == nullptr) XF_FAIL(XATTN_ERR_NULL, "cfg is NULL");
+  if (c->B < 0 || c->T <= 0 || c->Ta <= 0 || c->Dv <= 0 || c->Da <= 0 || c->E <= 0 || c->H <= 0 || c->C <= 0)
+    XF_FAIL(XATTN_ERR_SHAPE, "non-positive dimension in cfg (B=%d T=%d Ta=%d Dv=%d Da=%d E=%d H=%d C=%d)", c->B, c->T, c->Ta,
+            c->Dv, c->Da, c->E, c->H, c->C);
+  if (c->E % c->H != 0) XF_FAIL(XATTN_ERR_SHAPE, "embed_dim must be divisible by num_heads (E=%d H=%d)", c->E, c->H);
+  if (c->E > 512) XF_FAIL(XATTN_ERR_SHAPE, "d_model %d > 512 is not supported", c->E);
+  if (c->head_kind != XATTN_HEAD_CONCAT && c->head_kind != XATTN_HEAD_GATED)
+    XF_FAIL(XATTN_ERR_SHAPE, "unknown head_kind %d", c->head_kind);
+  if (c->head_kind == XATTN_HEAD_CONCAT && c->common_dim <= 0) XF_FAIL(XATTN_ERR_SHAPE, "common_dim must be positive");
+  if (c->use_prior && (c->prior_dim <= 0 || c->prior_hidden <= 0))
+    XF_FAIL(XATTN_ERR_SHAPE, "emotion prior needs positive prior_dim / prior_hidden");
+  if (c->io_dtype != XATTN_DTYPE_F32 && c->io_dtype != XATTN_DTYPE_BF16) XF_FAIL(XATTN_ERR_DTYPE, "unknown io_dtype %d", c->io_dtype);
+  if (c->precision != XATTN_DTYPE_F32 && c->precision != XATTN_DTYPE_BF16)
+    XF_FAIL(XATTN_ERR_DTYPE, "unknown precision %d", c->precision);
+  if ((int64_t)c->B * c->Ta * c->Da >= ((int64_t)1 << 40)) XF_FAIL(XATTN_ERR_SHAPE, "input too large");
+  return XATTN_OK;
+}
+
+static inline int64_t al4(int64_t n) { return (n + 3) & ~(int64_t)3; }
+
+void compute_param_layout(const xattn_config& c, ParamLayout& L) {
+  const int64_t E = c.E, P = c.prior_dim, Hd = c.prior_hidden;
+  const bool gated = c.head_kind == XATTN_HEAD_GATED;
+  const int64_t HW = gated ? E : c.common_dim;
+  int64_t sz[XP_COUNT];
+  memset(sz, 0, sizeof(sz));
+  sz[XP_V_IN_W] = E * c.Dv; sz[XP_V_IN_B] = E;
+  sz[XP_A_IN_W] = E * E; sz[XP_A_IN_B] = E;
+  sz[XP_SEQ_W] = E * c.Da; sz[XP_SEQ_B] = E;
+  sz[XP_V2A_IN_W] = 3 * E * E; sz[XP_V2A_IN_B] = 3 * E; sz[XP_V2A_OUT_W] = E * E; sz[XP_V2A_OUT_B] = E;
+  sz[XP_A2V_IN_W] = 3 * E * E; sz[XP_A2V_IN_B] = 3 * E; sz[XP_A2V_OUT_W] = E * E; sz[XP_A2V_OUT_B] = E;
+  sz[XP_VN_W] = E; sz[XP_VN_B] = E; sz[XP_AN_W] = E; sz[XP_AN_B] = E;
+  sz[XP_HEAD0_W] = HW * 2 * E; sz[XP_HEAD0_B] = HW;
+  sz[XP_HEAD1_W] = gated ? HW : (int64_t)c.C * HW; sz[XP_HEAD1_B] = gated ? 1 : c.C;
+  sz[XP_CLS_W] = gated ? (int64_t)c.C * E : 0; sz[XP_CLS_B] = gated ? c.C : 0;
+  if (c.use_prior) {
+    sz[XP_PRIOR0_W] = Hd * 2 * E; sz[XP_PRIOR0_B] = Hd; sz[XP_PRIOR3_W] = P * Hd; sz[XP_PRIOR3_B] = P;
+    sz[XP_VQ_W] = sz[XP_AK_W] = sz[XP_AQ_W] = sz[XP_VK_W] = E + P;
+    sz[XP_VQ_B] = sz[XP_AK_B] = sz[XP_AQ_B] = sz[XP_VK_B] = 1;
+    sz[XP_BIAS_SCALE] = 1;
+  }
+  int64_t off = 0;
+  for (int i = 0; i < XP_COUNT; ++i) {
+    L.off[i] = off;
+    L.size[i] = sz[i];
+    off += al4(sz[i]);
+  }
+  L.total = off;
+}
+
+void compute_ws_f32(const xattn_config& c, WsF32& w) {
+  const int64_t B = c.B, T = c.T, Ta = c.Ta, E = c.E, H = c.H, P = c.prior_dim > 0 ? c.prior_dim : 1,
+                Hd = c.prior_hidden > 0 ? c.prior_hidden : 1;
+  const int64_t HW = c.head_kind == XATTN_HEAD_GATED ? E : c.common_dim;
+  const bool bwd = c.training || c.save_for_backward;
+  int64_t off = 0;
+  auto take = [&](int64_t n) {
+    int64_t o = off;
+    off += al4(n);
+    return o;
+  };
+  w.v0 = take(B * T * E); w.aseq = take(B * Ta * E); w.a0 = take(B * Ta * E);
+  w.q1 = take(B * T * E); w.kv1 = take(B * Ta * 2 * E);
+  w.p1 = bwd ? take(B * H * T * Ta) : 0;
+  w.o1 = take(B * T * E); w.s1 = take(B * T * E); w.mean1 = take(B * T); w.rstd1 = take(B * T); w.v1 = take(B * T * E);
+  w.q2 = take(B * Ta * E); w.kv2 = take(B * T * 2 * E);
+  w.p2 = bwd ? take(B * H * Ta * T) : 0;
+  w.o2 = take(B * Ta * E); w.s2 = take(B * Ta * E); w.mean2 = take(B * Ta); w.rstd2 = take(B * Ta); w.a1 = take(B * Ta * E);
+  w.pooled0 = take(B * 2 * E); w.phid = take(B * Hd); w.prior = take(B * P);
+  w.qv = take(B * T); w.ka = take(B * Ta); w.qa = take(B * Ta); w.kvs = take(B * T);
+  w.pooled = take(B * 2 * E); w.hhid = take(B * HW); w.gate = take(B); w.fusedg = take(B * E);
+  w.dp1 = take(B); w.dp2 = take(B);
+  if (bwd) {
+    w.d_pooled = take(B * 2 * E); w.d_hh = take(B * HW); w.d_z = take(B); w.d_fused = take(B * E);
+    w.d_a0 = take(B * Ta * E); w.d_br2 = take(B * Ta * E); w.d_o2 = take(B * Ta * E); w.d_q2 = take(B * Ta * E);
+    w.d_kv2 = take(B * T * 2 * E); w.d_v1 = take(B * T * E); w.d_v0 = take(B * T * E); w.d_br1 = take(B * T * E);
+    w.d_o1 = take(B * T * E); w.d_q1 = take(B * T * E); w.d_kv1 = take(B * Ta * 2 * E); w.d_aseq = take(B * Ta * E);
+    w.d_qv = take(B * T); w.d_ka = take(B * Ta); w.d_qa = take(B * Ta); w.d_kvs = take(B * T);
+    w.d_prior = take(B * P); w.d_phid = take(B * Hd);
+  }
+  w.total = off;
+}
+
+}  // namespace xf

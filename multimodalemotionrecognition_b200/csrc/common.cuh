@@ -1,0 +1,121 @@
+// Shared helpers for the xattn fusion kernels (sm_100a only).
+#pragma once
+#include <cuda_bf16.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+
+#include "../../include/xattn_fusion.h"
+
+namespace xf {
+
+// ---- error plumbing (thread-local text behind xattn_last_error) -------------------------------
+void set_error(const char* fmt, ...);
+const char* last_error();
+
+#define XF_FAIL(code, ...)     \
+  do {                         \
+    xf::set_error(__VA_ARGS__); \
+    return (code);             \
+  } while (0)
+
+#define XF_CUDA(expr)                                                                         \
+  do {                                                                                        \
+    cudaError_t _e = (expr);                                                                  \
+    if (_e != cudaSuccess) {                                                                  \
+      xf::set_error("%s failed: %s (%s:%d)", #expr, cudaGetErrorString(_e), __FILE__, __LINE__); \
+      return XATTN_ERR_CUDA;                                                                  \
+    }                                                                                         \
+  } while (0)
+
+#define XF_TRY(expr)            \
+  do {                          \
+    int _s = (expr);            \
+    if (_s != XATTN_OK) return _s; \
+  } while (0)
+
+#define XF_LAUNCH_CHECK()                                                                  \
+  do {                                                                                     \
+    cudaError_t _e = cudaGetLastError();                                                   \
+    if (_e != cudaSuccess) {                                                               \
+      xf::set_error("kernel launch failed: %s (%s:%d)", cudaGetErrorString(_e), __FILE__, __LINE__); \
+      return XATTN_ERR_CUDA;                                                               \
+    }                                                                                      \
+  } while (0)
+
+int check_device_sm100();           // XATTN_ERR_ARCH unless the current device is sm_100
+int validate_config(const xattn_config* cfg);
+int num_sms();
+
+// Count of kernels this library launched since process start (bench.py's gpu_launches claim).
+extern unsigned long long g_launch_count;
+inline void count_launch(int n = 1) { g_launch_count += (unsigned long long)n; }
+
+// ---- parameter layout ----------------------------------------------------------------------------
+struct ParamLayout {
+  int64_t off[XP_COUNT];
+  int64_t size[XP_COUNT];
+  int64_t total;
+};
+void compute_param_layout(const xattn_config& c, ParamLayout& L);
+
+// ---- fp32 workspace layout (activations saved for backward; floats) -------------------------------
+struct WsF32 {
+  // token tensors
+  int64_t v0, aseq, a0, q1, kv1, p1, o1, s1, mean1, rstd1, v1, q2, kv2, p2, o2, s2, mean2, rstd2, a1;
+  // per-clip vectors
+  int64_t pooled0, phid, prior, qv, ka, qa, kvs, pooled, hhid, gate, fusedg, dp1, dp2;
+  // backward scratch (only laid out when training / save_for_backward)
+  int64_t d_pooled, d_hh, d_z, d_fused, d_a0, d_br2, d_o2, d_q2, d_kv2, d_v1, d_v0, d_br1, d_o1, d_q1, d_kv1, d_aseq;
+  int64_t d_qv, d_ka, d_qa, d_kvs, d_prior, d_phid;
+  int64_t total;  // floats
+};
+void compute_ws_f32(const xattn_config& c, WsF32& w);
+
+// ---- device helpers ------------------------------------------------------------------------------------
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+__device__ __forceinline__ float warp_max(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+  return v;
+}
+
+__device__ __forceinline__ float to_f32(float x) { return x; }
+__device__ __forceinline__ float to_f32(__nv_bfloat16 x) { return __bfloat162float(x); }
+
+// Philox4x32-10 counter RNG: uniform in [0,1) for (seed, stream, index).  Used for every dropout so
+// the backward kernels regenerate the forward's masks instead of storing them.
+__device__ __forceinline__ uint4 philox4x32(uint64_t seed, uint64_t ctr_hi, uint64_t ctr_lo) {
+  uint32_t k0 = (uint32_t)seed, k1 = (uint32_t)(seed >> 32);
+  uint32_t c0 = (uint32_t)ctr_lo, c1 = (uint32_t)(ctr_lo >> 32), c2 = (uint32_t)ctr_hi, c3 = (uint32_t)(ctr_hi >> 32);
+#pragma unroll
+  for (int r = 0; r < 10; ++r) {
+    uint32_t hi0 = __umulhi(0xD2511F53u, c0), lo0 = 0xD2511F53u * c0;
+    uint32_t hi1 = __umulhi(0xCD9E8D57u, c2), lo1 = 0xCD9E8D57u * c2;
+    c0 = hi1 ^ c1 ^ k0;
+    c1 = lo1;
+    c2 = hi0 ^ c3 ^ k1;
+    c3 = lo0;
+    k0 += 0x9E3779B9u;
+    k1 += 0xBB67AE85u;
+  }
+  return make_uint4(c0, c1, c2, c3);
+}
+__device__ __forceinline__ float rng_uniform(uint64_t seed, uint64_t offset, uint32_t stream, uint64_t idx) {
+  uint4 r = philox4x32(seed, (offset << 8) | stream, idx >> 2);
+  uint32_t x = (idx & 3) == 0 ? r.x : (idx & 3) == 1 ? r.y : (idx & 3) == 2 ? r.z : r.w;
+  return (float)(x >> 8) * (1.0f / 16777216.0f);
+}
+// multiplicative dropout factor: 0 or 1/keep
+__device__ __forceinline__ float drop_factor(float p, uint64_t seed, uint64_t offset, uint32_t stream, uint64_t idx) {
+  if (p <= 0.f) return 1.f;
+  if (p >= 1.f) return 0.f;
+  return rng_uniform(seed, offset, stream, idx) < p ? 0.f : 1.f / (1.f - p);
+}
+enum : uint32_t { RS_ATTN1 = 1, RS_ATTN2 = 2, RS_PATH1 = 3, RS_PATH2 = 4, RS_HEAD = 5, RS_PRIOR = 6 };
+
+}  // namespace xf

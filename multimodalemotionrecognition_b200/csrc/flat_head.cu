@@ -1,0 +1,197 @@
+// Flat concat / gated fusion heads (BASELINE config 5; reference src/models/fusion.py:226-260, :413-435) with the
+// CLIP-style alignment projections (:127-139).  The temporal mean that ends audio_model.encode /
+// video_model.encode (:414-415) is fused in as the first kernel, so the inputs are the same [B,T,Dv] /
+// [B,Ta,Da] embeddings the xattn head reads — an HBM-bound streaming reduction with 128-bit loads.
+// Eval-mode forward (ModalityDropout and Dropout are identity; the alignment loss is a training-only output).
+#include "gemm_simt.cuh"
+
+namespace xf {
+
+struct FlatLayout {
+  int64_t off[FP_COUNT], size[FP_COUNT], total;
+};
+static inline int64_t al4(int64_t n) { return (n + 3) & ~(int64_t)3; }
+
+static void flat_layout(const flat_head_config& c, FlatLayout& L) {
+  const int64_t A = c.align_dim, Cm = c.common_dim;
+  const int64_t in_a = A > 0 ? A : c.Da, in_v = A > 0 ? A : c.Dv;
+  int64_t sz[FP_COUNT] = {0};
+  if (A > 0) {
+    sz[FP_ALIGN_A_W] = A * c.Da; sz[FP_ALIGN_A_B] = A; sz[FP_ALIGN_V_W] = A * c.Dv; sz[FP_ALIGN_V_B] = A;
+  }
+  sz[FP_AUDIO_W] = Cm * in_a; sz[FP_AUDIO_B] = Cm; sz[FP_VIDEO_W] = Cm * in_v; sz[FP_VIDEO_B] = Cm;
+  sz[FP_H0_W] = Cm * 2 * Cm; sz[FP_H0_B] = Cm;
+  sz[FP_H1_W] = c.gated ? Cm : (int64_t)c.C * Cm; sz[FP_H1_B] = c.gated ? 1 : c.C;
+  sz[FP_CLS_W] = c.gated ? (int64_t)c.C * Cm : 0; sz[FP_CLS_B] = c.gated ? c.C : 0;
+  int64_t off = 0;
+  for (int i = 0; i < FP_COUNT; ++i) {
+    L.off[i] = off;
+    L.size[i] = sz[i];
+    off += al4(sz[i]);
+  }
+  L.total = off;
+}
+
+static int flat_validate(const flat_head_config* c) {
+  if (!c) XF_FAIL(XATTN_ERR_NULL, "cfg is NULL");
+  if (c->B < 0 || c->T <= 0 || c->Ta <= 0 || c->Dv <= 0 || c->Da <= 0 || c->common_dim <= 0 || c->C <= 0 || c->align_dim < 0)
+    XF_FAIL(XATTN_ERR_SHAPE, "bad flat head dimensions");
+  if (c->io_dtype != XATTN_DTYPE_F32 && c->io_dtype != XATTN_DTYPE_BF16) XF_FAIL(XATTN_ERR_DTYPE, "unknown io_dtype %d", c->io_dtype);
+  return XATTN_OK;
+}
+
+struct FlatWs {
+  int64_t a_pool, v_pool, a_al, v_al, cat, hid, z, total;
+};
+static void flat_ws(const flat_head_config& c, FlatWs& w) {
+  const int64_t B = c.B, A = c.align_dim > 0 ? c.align_dim : 1, Cm = c.common_dim;
+  int64_t off = 0;
+  auto take = [&](int64_t n) { int64_t o = off; off += al4(n); return o; };
+  w.a_pool = take(B * c.Da); w.v_pool = take(B * c.Dv); w.a_al = take(B * A); w.v_al = take(B * A);
+  w.cat = take(B * 2 * Cm); w.hid = take(B * Cm); w.z = take(B);
+  w.total = off;
+}
+
+// Temporal mean over [B,L,D] -> [B,D]; each thread owns VEC consecutive channels (one 128-bit load per row),
+// a CTA covers one clip's channel slab; rows unrolled x4 for memory-level parallelism.
+template <typename TIO>
+__global__ void __launch_bounds__(128) temporal_mean_kernel(const TIO* __restrict__ x, float* __restrict__ out, int L, int D) {
+  constexpr int VEC = 16 / sizeof(TIO);
+  const int b = blockIdx.y;
+  const int c0 = (blockIdx.x * blockDim.x + threadIdx.x) * VEC;
+  if (c0 >= D) return;
+  const TIO* base = x + (int64_t)b * L * D + c0;
+  float acc[VEC];
+#pragma unroll
+  for (int i = 0; i < VEC; ++i) acc[i] = 0.f;
+  if (c0 + VEC <= D && (D % VEC) == 0) {
+    int l = 0;
+    for (; l + 4 <= L; l += 4) {
+      uint4 r[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) r[u] = __ldg(reinterpret_cast<const uint4*>(base + (int64_t)(l + u) * D));
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const TIO* e = reinterpret_cast<const TIO*>(&r[u]);
+#pragma unroll
+        for (int i = 0; i < VEC; ++i) acc[i] += to_f32(e[i]);
+      }
+    }
+    for (; l < L; ++l) {
+      const uint4 r = __ldg(reinterpret_cast<const uint4*>(base + (int64_t)l * D));
+      const TIO* e = reinterpret_cast<const TIO*>(&r);
+#pragma unroll
+      for (int i = 0; i < VEC; ++i) acc[i] += to_f32(e[i]);
+    }
+  } else {
+    for (int l = 0; l < L; ++l)
+      for (int i = 0; i < VEC && c0 + i < D; ++i) acc[i] += to_f32(base[(int64_t)l * D + i]);
+  }
+  const float inv = 1.f / (float)L;
+  for (int i = 0; i < VEC && c0 + i < D; ++i) out[(int64_t)b * D + c0 + i] = acc[i] * inv;
+}
+
+template <typename TIO>
+static void launch_mean(cudaStream_t st, const TIO* x, float* out, int B, int L, int D) {
+  constexpr int VEC = 16 / sizeof(TIO);
+  const int threads_needed = (D + VEC - 1) / VEC;
+  dim3 grid((threads_needed + 127) / 128, B);
+  temporal_mean_kernel<TIO><<<grid, 128, 0, st>>>(x, out, L, D);
+  count_launch();
+}
+
+// gated blend + classifier: g = sigmoid(z); fused = g*a + (1-g)*v (fusion.py:433-435)
+__global__ void __launch_bounds__(256) flat_gate_cls_kernel(const float* __restrict__ cat, const float* __restrict__ z,
+                                                            const float* __restrict__ wc, const float* __restrict__ bc,
+                                                            float* __restrict__ logits, int Cm, int C) {
+  extern __shared__ float fused[];
+  const int b = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nw = blockDim.x >> 5;
+  const float g = 1.f / (1.f + expf(-z[b]));
+  for (int e = tid; e < Cm; e += blockDim.x)
+    fused[e] = g * cat[(int64_t)b * 2 * Cm + e] + (1.f - g) * cat[(int64_t)b * 2 * Cm + Cm + e];
+  __syncthreads();
+  for (int c = warp; c < C; c += nw) {
+    float s = 0.f;
+    for (int k = lane; k < Cm; k += 32) s = fmaf(wc[(int64_t)c * Cm + k], fused[k], s);
+    s = warp_sum(s);
+    if (lane == 0) logits[(int64_t)b * C + c] = s + bc[c];
+  }
+}
+
+template <typename TIO>
+static int flat_forward_impl(const flat_head_config& c, const float* params, const TIO* xv, const TIO* xa, float* logits, float* ws,
+                             cudaStream_t st) {
+  FlatLayout pl;
+  flat_layout(c, pl);
+  FlatWs w;
+  flat_ws(c, w);
+  auto P = [&](int id) { return params + pl.off[id]; };
+  const int B = c.B, Cm = c.common_dim, A = c.align_dim;
+  launch_mean<TIO>(st, xa, ws + w.a_pool, B, c.Ta, c.Da);
+  launch_mean<TIO>(st, xv, ws + w.v_pool, B, c.T, c.Dv);
+  const float* a_in = ws + w.a_pool;
+  const float* v_in = ws + w.v_pool;
+  int in_a = c.Da, in_v = c.Dv;
+  if (A > 0) {  // ClipStyleAlignment projections, fusion.py:138-139
+    linear_fwd<float>(st, a_in, P(FP_ALIGN_A_W), P(FP_ALIGN_A_B), ws + w.a_al, B, A, c.Da);
+    linear_fwd<float>(st, v_in, P(FP_ALIGN_V_W), P(FP_ALIGN_V_B), ws + w.v_al, B, A, c.Dv);
+    a_in = ws + w.a_al; v_in = ws + w.v_al; in_a = in_v = A;
+  }
+  // audio_proj / video_proj written side by side: cat = [a | v] (fusion.py:421-425)
+  launch_gemm<float, float>(st, a_in, in_a, 1, P(FP_AUDIO_W), 1, in_a, ws + w.cat, 2 * Cm, B, Cm, in_a, P(FP_AUDIO_B), 0);
+  launch_gemm<float, float>(st, v_in, in_v, 1, P(FP_VIDEO_W), 1, in_v, ws + w.cat + Cm, 2 * Cm, B, Cm, in_v, P(FP_VIDEO_B), 0);
+  linear_fwd<float>(st, ws + w.cat, P(FP_H0_W), P(FP_H0_B), ws + w.hid, B, Cm, 2 * Cm, true);
+  if (!c.gated) {
+    linear_fwd<float>(st, ws + w.hid, P(FP_H1_W), P(FP_H1_B), logits, B, c.C, Cm);
+  } else {
+    linear_fwd<float>(st, ws + w.hid, P(FP_H1_W), P(FP_H1_B), ws + w.z, B, 1, Cm);
+    flat_gate_cls_kernel<<<B, 256, sizeof(float) * Cm, st>>>(ws + w.cat, ws + w.z, P(FP_CLS_W), P(FP_CLS_B), logits, Cm, c.C);
+    count_launch();
+  }
+  XF_LAUNCH_CHECK();
+  return XATTN_OK;
+}
+
+}  // namespace xf
+
+using namespace xf;
+
+extern "C" XATTN_API int flat_head_param_layout(const flat_head_config* cfg, int64_t* offsets, int64_t* sizes, int64_t* total_floats) {
+  XF_TRY(flat_validate(cfg));
+  FlatLayout L;
+  flat_layout(*cfg, L);
+  for (int i = 0; i < FP_COUNT; ++i) {
+    if (offsets) offsets[i] = L.off[i];
+    if (sizes) sizes[i] = L.size[i];
+  }
+  if (total_floats) *total_floats = L.total;
+  return XATTN_OK;
+}
+
+extern "C" XATTN_API int flat_head_workspace_bytes(const flat_head_config* cfg, int64_t* bytes) {
+  XF_TRY(flat_validate(cfg));
+  if (!bytes) XF_FAIL(XATTN_ERR_NULL, "bytes is NULL");
+  FlatWs w;
+  flat_ws(*cfg, w);
+  *bytes = w.total * (int64_t)sizeof(float);
+  return XATTN_OK;
+}
+
+extern "C" XATTN_API int flat_head_forward(const flat_head_config* cfg, const float* params, const void* video_emb, const void* audio_emb,
+                                 float* logits, void* workspace, int64_t workspace_bytes, void* stream) {
+  XF_TRY(flat_validate(cfg));
+  if (!params || !video_emb || !audio_emb || !logits || !workspace) XF_FAIL(XATTN_ERR_NULL, "NULL pointer argument");
+  if (((uintptr_t)video_emb | (uintptr_t)audio_emb | (uintptr_t)params | (uintptr_t)workspace) & 15)
+    XF_FAIL(XATTN_ERR_ALIGN, "pointers must be 16-byte aligned");
+  XF_TRY(check_device_sm100());
+  FlatWs w;
+  flat_ws(*cfg, w);
+  if (workspace_bytes < w.total * (int64_t)sizeof(float))
+    XF_FAIL(XATTN_ERR_WORKSPACE, "workspace too small: %lld < %lld bytes", (long long)workspace_bytes, (long long)(w.total * 4));
+  if (cfg->B == 0) return XATTN_OK;
+  cudaStream_t st = (cudaStream_t)stream;
+  if (cfg->io_dtype == XATTN_DTYPE_BF16)
+    return flat_forward_impl<__nv_bfloat16>(*cfg, params, (const __nv_bfloat16*)video_emb, (const __nv_bfloat16*)audio_emb, logits,
+                                            (float*)workspace, st);
+  return flat_forward_impl<float>(*cfg, params, (const float*)video_emb, (const float*)audio_emb, logits, (float*)workspace, st);
+}

@@ -1,0 +1,402 @@
+// fp32 forward of the xattn fusion head (parity + training path).
+// Stage map (reference src/models/fusion.py):
+//   v_in_proj :372 | audio_seq_proj :378 | a_in_proj :386 | EmotionPriorBiasAdapter :170-184 |
+//   v2a_attn :394 | v_norm(v + drop_path(v2)) :395 | a2v_attn :398 | a_norm :399 | mean pool :401-402
+//   (temporal.py:108-109) | head :405-411.
+// Every intermediate the backward needs is kept in the caller's workspace (layout: compute_ws_f32).
+#include "gemm_simt.cuh"
+#include "kernels_f32.cuh"
+
+namespace xf {
+
+// ---------------------------------------------------------------------------------------------------------
+// Emotion prior (fusion.py:178-184): pooled means -> prior_net -> prior[P]; then the four token scores
+//   qv[i] = w_vq[:E]·v_i + w_vq[E:]·prior + c_vq     ka[j] = w_ak[:E]·a_j + w_ak[E:]·prior + c_ak
+//   qa[j] = w_aq[:E]·a_j + ...                        kvs[i] = w_vk[:E]·v_i + ...
+// (the reference builds these by expand+cat+Linear(E+P -> 1), :171-174; the sum decomposes).
+// One CTA per clip.
+// ---------------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) prior_fwd_kernel(PriorArgs a) {
+  extern __shared__ float sm[];
+  const int b = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nw = blockDim.x >> 5;
+  const int E = a.E, P = a.P, Hd = a.Hd, T = a.T, Ta = a.Ta;
+  float* pooled = sm;            // [2E]
+  float* hid = pooled + 2 * E;   // [Hd]
+  float* prior = hid + Hd;       // [P]
+  float* pc = prior + P;         // [4] prior contribution + bias of the four score heads
+  const float* v0 = a.v0 + (int64_t)b * T * E;
+  const float* a0 = a.a0 + (int64_t)b * Ta * E;
+  for (int e = tid; e < E; e += blockDim.x) {
+    float s = 0.f;
+    for (int t = 0; t < T; ++t) s += v0[(int64_t)t * E + e];
+    pooled[e] = s / (float)T;
+    float s2 = 0.f;
+    for (int t = 0; t < Ta; ++t) s2 += a0[(int64_t)t * E + e];
+    pooled[E + e] = s2 / (float)Ta;
+  }
+  __syncthreads();
+  for (int e = tid; e < 2 * E; e += blockDim.x) a.pooled0[(int64_t)b * 2 * E + e] = pooled[e];
+  for (int h = warp; h < Hd; h += nw) {
+    const float* w = a.w0 + (int64_t)h * 2 * E;
+    float s = 0.f;
+    for (int k = lane; k < 2 * E; k += 32) s = fmaf(w[k], pooled[k], s);
+    s = warp_sum(s);
+    if (lane == 0) {
+      float r = fmaxf(s + a.b0[h], 0.f);
+      r *= drop_factor(a.p_drop, a.seed, a.offset, RS_PRIOR, (uint64_t)b * Hd + h);
+      hid[h] = r;
+      a.phid[(int64_t)b * Hd + h] = r;
+    }
+  }
+  __syncthreads();
+  for (int p = warp; p < P; p += nw) {
+    const float* w = a.w3 + (int64_t)p * Hd;
+    float s = 0.f;
+    for (int k = lane; k < Hd; k += 32) s = fmaf(w[k], hid[k], s);
+    s = warp_sum(s);
+    if (lane == 0) {
+      prior[p] = s + a.b3[p];
+      a.prior[(int64_t)b * P + p] = s + a.b3[p];
+    }
+  }
+  __syncthreads();
+  if (tid < 4) {
+    const float* w = a.wh[tid] + E;
+    float s = a.bh[tid][0];
+    for (int p = 0; p < P; ++p) s = fmaf(w[p], prior[p], s);
+    pc[tid] = s;
+  }
+  __syncthreads();
+  // video tokens: heads 0 (v_query -> qv) and 3 (v_key -> kvs); audio tokens: heads 1 (a_key -> ka), 2 (a_query -> qa)
+  for (int i = warp; i < T + Ta; i += nw) {
+    const bool is_v = i < T;
+    const float* tok = is_v ? v0 + (int64_t)i * E : a0 + (int64_t)(i - T) * E;
+    const float* wA = is_v ? a.wh[0] : a.wh[1];
+    const float* wB = is_v ? a.wh[3] : a.wh[2];
+    float sA = 0.f, sB = 0.f;
+    for (int e = lane; e < E; e += 32) {
+      const float x = tok[e];
+      sA = fmaf(wA[e], x, sA);
+      sB = fmaf(wB[e], x, sB);
+    }
+    sA = warp_sum(sA);
+    sB = warp_sum(sB);
+    if (lane == 0) {
+      if (is_v) {
+        a.qv[(int64_t)b * T + i] = sA + pc[0];
+        a.kvs[(int64_t)b * T + i] = sB + pc[3];
+      } else {
+        a.ka[(int64_t)b * Ta + (i - T)] = sA + pc[1];
+        a.qa[(int64_t)b * Ta + (i - T)] = sB + pc[2];
+      }
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// Attention core of nn.MultiheadAttention (need_weights branch of F.multi_head_attention_forward):
+//   S_h = (Q_h / sqrt(dh)) K_h^T + bias ;  P_h = softmax(S_h) ;  O_h = dropout(P_h) V_h
+// with bias[l,s] = tanh(qs[l] + ks[s]) * bias_scale computed on the fly (fusion.py:175-176; identical for
+// every head, :351-354 — the reference materialises it H times).  One CTA per clip, heads in sequence.
+// ---------------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) attn_fwd_kernel(AttnArgs a) {
+  extern __shared__ float sm[];
+  const int b = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nw = blockDim.x >> 5;
+  const int L = a.L, S = a.S, E = a.E, H = a.H, dh = E / H, dp = dh + 1;
+  float* Qs = sm;                 // [L][dp]
+  float* Ks = Qs + L * dp;        // [S][dp]
+  float* Vs = Ks + S * dp;        // [S][dp]
+  float* prow = Vs + S * dp;      // [nw][S]
+  const float* q = a.q + (int64_t)b * L * E;
+  const float* kv = a.kv + (int64_t)b * S * 2 * E;
+  const float bscale = a.bias_scale ? a.bias_scale[0] : 0.f;
+  const float* qs = a.qs ? a.qs + (int64_t)b * L : nullptr;
+  const float* ks = a.ks ? a.ks + (int64_t)b * S : nullptr;
+  for (int h = 0; h < H; ++h) {
+    for (int i = tid; i < L * dh; i += blockDim.x) {
+      const int l = i / dh, d = i - l * dh;
+      Qs[l * dp + d] = q[(int64_t)l * E + h * dh + d] * a.scale;   // q scaled before the product, as torch does
+    }
+    for (int i = tid; i < S * dh; i += blockDim.x) {
+      const int s = i / dh, d = i - s * dh;
+      Ks[s * dp + d] = kv[(int64_t)s * 2 * E + h * dh + d];
+      Vs[s * dp + d] = kv[(int64_t)s * 2 * E + E + h * dh + d];
+    }
+    __syncthreads();
+    float* pr = prow + warp * S;
+    for (int l = warp; l < L; l += nw) {
+      float mx = -INFINITY;
+      for (int s = lane; s < S; s += 32) {
+        float acc = 0.f;
+        for (int d = 0; d < dh; ++d) acc = fmaf(Qs[l * dp + d], Ks[s * dp + d], acc);
+        if (qs) acc += tanhf(qs[l] + ks[s]) * bscale;
+        pr[s] = acc;
+        mx = fmaxf(mx, acc);
+      }
+      mx = warp_max(mx);
+      float sum = 0.f;
+      for (int s = lane; s < S; s += 32) {
+        const float e = expf(pr[s] - mx);
+        pr[s] = e;
+        sum += e;
+      }
+      sum = warp_sum(sum);
+      const float inv = 1.f / sum;
+      const int64_t prow_idx = (((int64_t)b * H + h) * L + l) * S;
+      for (int s = lane; s < S; s += 32) {
+        float p = pr[s] * inv;
+        if (a.P) a.P[prow_idx + s] = p;
+        if (a.p_drop > 0.f) p *= drop_factor(a.p_drop, a.seed, a.offset, a.rng_stream, (uint64_t)(prow_idx + s));
+        pr[s] = p;
+      }
+      __syncwarp();
+      for (int d = lane; d < dh; d += 32) {
+        float acc = 0.f;
+        for (int s = 0; s < S; ++s) acc = fmaf(pr[s], Vs[s * dp + d], acc);
+        a.O[((int64_t)b * L + l) * E + h * dh + d] = acc;
+      }
+      __syncwarp();
+    }
+    __syncthreads();
+  }
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// s = x + drop_path(y) ; out = LayerNorm(s) (fusion.py:395 / :399).  One warp per token row.  `y` is
+// overwritten with s (the backward needs it) and mean / rstd are saved.
+// ---------------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) residual_ln_fwd_kernel(const float* __restrict__ x, float* __restrict__ y,
+                                                              const float* __restrict__ gamma, const float* __restrict__ beta,
+                                                              float* __restrict__ out, float* __restrict__ mean_out,
+                                                              float* __restrict__ rstd_out, float* __restrict__ dpf_out,
+                                                              int rows, int L, int E, float p_path, uint64_t seed,
+                                                              uint64_t offset, uint32_t stream) {
+  const int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  const int lane = threadIdx.x & 31;
+  if (row >= rows) return;
+  const int b = row / L;
+  const float f = drop_factor(p_path, seed, offset, stream, (uint64_t)b);
+  if (dpf_out && lane == 0 && row % L == 0) dpf_out[b] = f;
+  const float* xr = x + (int64_t)row * E;
+  float* yr = y + (int64_t)row * E;
+  float sum = 0.f;
+  for (int e = lane; e < E; e += 32) {
+    const float s = xr[e] + f * yr[e];
+    yr[e] = s;
+    sum += s;
+  }
+  const float mu = warp_sum(sum) / (float)E;
+  float var = 0.f;
+  for (int e = lane; e < E; e += 32) {
+    const float d = yr[e] - mu;
+    var = fmaf(d, d, var);
+  }
+  const float rstd = rsqrtf(warp_sum(var) / (float)E + 1e-5f);
+  for (int e = lane; e < E; e += 32) out[(int64_t)row * E + e] = (yr[e] - mu) * rstd * gamma[e] + beta[e];
+  if (lane == 0) {
+    mean_out[row] = mu;
+    rstd_out[row] = rstd;
+  }
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// Temporal mean pooling (temporal.py:108-109) + classifier head (fusion.py:405-411).  One CTA per clip.
+// ---------------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) pool_head_fwd_kernel(HeadArgs a) {
+  extern __shared__ float sm[];
+  const int b = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nw = blockDim.x >> 5;
+  const int E = a.E, T = a.T, Ta = a.Ta, HW = a.HW, C = a.C;
+  float* pooled = sm;            // [2E]
+  float* hid = pooled + 2 * E;   // [HW]
+  float* fused = hid + HW;       // [E] (gated)
+  __shared__ float s_gate;
+  const float* v1 = a.v1 + (int64_t)b * T * E;
+  const float* a1 = a.a1 + (int64_t)b * Ta * E;
+  for (int e = tid; e < E; e += blockDim.x) {
+    float s = 0.f;
+    for (int t = 0; t < T; ++t) s += v1[(int64_t)t * E + e];
+    pooled[e] = s / (float)T;
+    float s2 = 0.f;
+    for (int t = 0; t < Ta; ++t) s2 += a1[(int64_t)t * E + e];
+    pooled[E + e] = s2 / (float)Ta;
+  }
+  __syncthreads();
+  if (a.pooled)
+    for (int e = tid; e < 2 * E; e += blockDim.x) a.pooled[(int64_t)b * 2 * E + e] = pooled[e];
+  for (int h = warp; h < HW; h += nw) {
+    const float* w = a.w0 + (int64_t)h * 2 * E;
+    float s = 0.f;
+    for (int k = lane; k < 2 * E; k += 32) s = fmaf(w[k], pooled[k], s);
+    s = warp_sum(s);
+    if (lane == 0) {
+      float r = fmaxf(s + a.b0[h], 0.f);
+      r *= drop_factor(a.p_drop, a.seed, a.offset, RS_HEAD, (uint64_t)b * HW + h);
+      hid[h] = r;
+      if (a.hhid) a.hhid[(int64_t)b * HW + h] = r;
+    }
+  }
+  __syncthreads();
+  if (!a.gated) {
+    for (int c = warp; c < C; c += nw) {
+      const float* w = a.w1 + (int64_t)c * HW;
+      float s = 0.f;
+      for (int k = lane; k < HW; k += 32) s = fmaf(w[k], hid[k], s);
+      s = warp_sum(s);
+      if (lane == 0) a.logits[(int64_t)b * C + c] = s + a.b1[c];
+    }
+    return;
+  }
+  if (warp == 0) {
+    float s = 0.f;
+    for (int k = lane; k < HW; k += 32) s = fmaf(a.w1[k], hid[k], s);
+    s = warp_sum(s);
+    if (lane == 0) {
+      const float g = 1.f / (1.f + expf(-(s + a.b1[0])));
+      s_gate = g;
+      if (a.gate) a.gate[b] = g;
+    }
+  }
+  __syncthreads();
+  const float g = s_gate;
+  for (int e = tid; e < E; e += blockDim.x) {
+    const float f = g * pooled[e] + (1.f - g) * pooled[E + e];
+    fused[e] = f;
+    if (a.fusedg) a.fusedg[(int64_t)b * E + e] = f;
+  }
+  __syncthreads();
+  for (int c = warp; c < C; c += nw) {
+    const float* w = a.wc + (int64_t)c * E;
+    float s = 0.f;
+    for (int k = lane; k < E; k += 32) s = fmaf(w[k], fused[k], s);
+    s = warp_sum(s);
+    if (lane == 0) a.logits[(int64_t)b * C + c] = s + a.bc[c];
+  }
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// launch helpers shared with bwd_f32.cu
+// ---------------------------------------------------------------------------------------------------------
+size_t attn_smem_bytes(int L, int S, int dh, int nwarps) { return sizeof(float) * ((size_t)(L + 2 * S) * (dh + 1) + (size_t)nwarps * S); }
+
+int launch_attn_fwd(cudaStream_t st, const AttnArgs& a, int B) {
+  const size_t smem = attn_smem_bytes(a.L, a.S, a.E / a.H, 8);
+  if (smem > 200 * 1024) XF_FAIL(XATTN_ERR_SHAPE, "attention tile needs %zu B of shared memory (> 200 KiB)", smem);
+  static size_t configured = 0;
+  if (smem > 48 * 1024 && smem > configured) {
+    XF_CUDA(cudaFuncSetAttribute(attn_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    configured = smem;
+  }
+  attn_fwd_kernel<<<B, 256, smem, st>>>(a);
+  count_launch();
+  XF_LAUNCH_CHECK();
+  return XATTN_OK;
+}
+
+template <typename TIO>
+static int forward_f32_impl(const xattn_config& c, const float* params, const TIO* xv, const TIO* xa, float* logits, float* ws,
+                            cudaStream_t st) {
+  ParamLayout pl;
+  compute_param_layout(c, pl);
+  WsF32 w;
+  compute_ws_f32(c, w);
+  auto P = [&](int id) { return params + pl.off[id]; };
+  const int B = c.B, T = c.T, Ta = c.Ta, E = c.E, H = c.H;
+  const bool train = c.training != 0;
+  const bool save = train || c.save_for_backward;
+  const float p_attn = train ? c.p_attn : 0.f, p_path = train ? c.p_path : 0.f, p_head = train ? c.p_head : 0.f,
+              p_prior = train ? c.p_prior : 0.f;
+
+  // projections (fusion.py:372, :378, :386)
+  linear_fwd<TIO>(st, xv, P(XP_V_IN_W), P(XP_V_IN_B), ws + w.v0, B * T, E, c.Dv);
+  linear_fwd<TIO>(st, xa, P(XP_SEQ_W), P(XP_SEQ_B), ws + w.aseq, B * Ta, E, c.Da);
+  linear_fwd<float>(st, ws + w.aseq, P(XP_A_IN_W), P(XP_A_IN_B), ws + w.a0, B * Ta, E, E);
+  XF_LAUNCH_CHECK();
+
+  if (c.use_prior) {
+    PriorArgs pa;
+    pa.v0 = ws + w.v0; pa.a0 = ws + w.a0;
+    pa.w0 = P(XP_PRIOR0_W); pa.b0 = P(XP_PRIOR0_B); pa.w3 = P(XP_PRIOR3_W); pa.b3 = P(XP_PRIOR3_B);
+    pa.wh[0] = P(XP_VQ_W); pa.bh[0] = P(XP_VQ_B); pa.wh[1] = P(XP_AK_W); pa.bh[1] = P(XP_AK_B);
+    pa.wh[2] = P(XP_AQ_W); pa.bh[2] = P(XP_AQ_B); pa.wh[3] = P(XP_VK_W); pa.bh[3] = P(XP_VK_B);
+    pa.pooled0 = ws + w.pooled0; pa.phid = ws + w.phid; pa.prior = ws + w.prior;
+    pa.qv = ws + w.qv; pa.ka = ws + w.ka; pa.qa = ws + w.qa; pa.kvs = ws + w.kvs;
+    pa.T = T; pa.Ta = Ta; pa.E = E; pa.P = c.prior_dim; pa.Hd = c.prior_hidden;
+    pa.p_drop = p_prior; pa.seed = c.seed; pa.offset = c.offset;
+    const size_t smem = sizeof(float) * (2 * E + c.prior_hidden + c.prior_dim + 4);
+    prior_fwd_kernel<<<B, 256, smem, st>>>(pa);
+    count_launch();
+    XF_LAUNCH_CHECK();
+  }
+
+  const float scale = 1.0f / sqrtf((float)(E / H));
+  // ---- video queries audio (fusion.py:394) ----
+  linear_fwd<float>(st, ws + w.v0, P(XP_V2A_IN_W), P(XP_V2A_IN_B), ws + w.q1, B * T, E, E);
+  linear_fwd<float>(st, ws + w.a0, P(XP_V2A_IN_W) + (int64_t)E * E, P(XP_V2A_IN_B) + E, ws + w.kv1, B * Ta, 2 * E, E);
+  {
+    AttnArgs aa;
+    aa.q = ws + w.q1; aa.kv = ws + w.kv1;
+    aa.qs = c.use_prior ? ws + w.qv : nullptr; aa.ks = c.use_prior ? ws + w.ka : nullptr;
+    aa.bias_scale = c.use_prior ? P(XP_BIAS_SCALE) : nullptr;
+    aa.P = save ? ws + w.p1 : nullptr; aa.O = ws + w.o1;
+    aa.L = T; aa.S = Ta; aa.E = E; aa.H = H; aa.scale = scale;
+    aa.p_drop = p_attn; aa.seed = c.seed; aa.offset = c.offset; aa.rng_stream = RS_ATTN1;
+    XF_TRY(launch_attn_fwd(st, aa, B));
+  }
+  linear_fwd<float>(st, ws + w.o1, P(XP_V2A_OUT_W), P(XP_V2A_OUT_B), ws + w.s1, B * T, E, E);
+  {
+    const int rows = B * T;
+    residual_ln_fwd_kernel<<<(rows + 7) / 8, 256, 0, st>>>(ws + w.v0, ws + w.s1, P(XP_VN_W), P(XP_VN_B), ws + w.v1,
+                                                          ws + w.mean1, ws + w.rstd1, ws + w.dp1, rows, T, E, p_path, c.seed,
+                                                          c.offset, RS_PATH1);
+    count_launch();
+    XF_LAUNCH_CHECK();
+  }
+  // ---- audio queries the UPDATED video (fusion.py:398) ----
+  linear_fwd<float>(st, ws + w.a0, P(XP_A2V_IN_W), P(XP_A2V_IN_B), ws + w.q2, B * Ta, E, E);
+  linear_fwd<float>(st, ws + w.v1, P(XP_A2V_IN_W) + (int64_t)E * E, P(XP_A2V_IN_B) + E, ws + w.kv2, B * T, 2 * E, E);
+  {
+    AttnArgs aa;
+    aa.q = ws + w.q2; aa.kv = ws + w.kv2;
+    aa.qs = c.use_prior ? ws + w.qa : nullptr; aa.ks = c.use_prior ? ws + w.kvs : nullptr;
+    aa.bias_scale = c.use_prior ? P(XP_BIAS_SCALE) : nullptr;
+    aa.P = save ? ws + w.p2 : nullptr; aa.O = ws + w.o2;
+    aa.L = Ta; aa.S = T; aa.E = E; aa.H = H; aa.scale = scale;
+    aa.p_drop = p_attn; aa.seed = c.seed; aa.offset = c.offset; aa.rng_stream = RS_ATTN2;
+    XF_TRY(launch_attn_fwd(st, aa, B));
+  }
+  linear_fwd<float>(st, ws + w.o2, P(XP_A2V_OUT_W), P(XP_A2V_OUT_B), ws + w.s2, B * Ta, E, E);
+  {
+    const int rows = B * Ta;
+    residual_ln_fwd_kernel<<<(rows + 7) / 8, 256, 0, st>>>(ws + w.a0, ws + w.s2, P(XP_AN_W), P(XP_AN_B), ws + w.a1,
+                                                          ws + w.mean2, ws + w.rstd2, ws + w.dp2, rows, Ta, E, p_path, c.seed,
+                                                          c.offset, RS_PATH2);
+    count_launch();
+    XF_LAUNCH_CHECK();
+  }
+  // ---- pool + head (fusion.py:401-411) ----
+  {
+    HeadArgs ha;
+    ha.v1 = ws + w.v1; ha.a1 = ws + w.a1;
+    ha.w0 = P(XP_HEAD0_W); ha.b0 = P(XP_HEAD0_B); ha.w1 = P(XP_HEAD1_W); ha.b1 = P(XP_HEAD1_B);
+    ha.wc = P(XP_CLS_W); ha.bc = P(XP_CLS_B);
+    ha.pooled = ws + w.pooled; ha.hhid = ws + w.hhid; ha.gate = ws + w.gate; ha.fusedg = ws + w.fusedg;
+    ha.logits = logits;
+    ha.T = T; ha.Ta = Ta; ha.E = E; ha.C = c.C; ha.gated = c.head_kind == XATTN_HEAD_GATED;
+    ha.HW = ha.gated ? E : c.common_dim;
+    ha.p_drop = p_head; ha.seed = c.seed; ha.offset = c.offset;
+    const size_t smem = sizeof(float) * (3 * E + ha.HW);
+    pool_head_fwd_kernel<<<B, 256, smem, st>>>(ha);
+    count_launch();
+    XF_LAUNCH_CHECK();
+  }
+  return XATTN_OK;
+}
+
+int forward_f32(const xattn_config& c, const float* params, const void* xv, const void* xa, float* logits, void* ws,
+                cudaStream_t st) {
+  if (c.io_dtype == XATTN_DTYPE_BF16)
+    return forward_f32_impl<__nv_bfloat16>(c, params, (const __nv_bfloat16*)xv, (const __nv_bfloat16*)xa, logits, (float*)ws, st);
+  return forward_f32_impl<float>(c, params, (const float*)xv, (const float*)xa, logits, (float*)ws, st);
+}
+
+}  // namespace xf

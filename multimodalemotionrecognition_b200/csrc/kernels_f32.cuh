@@ -1,0 +1,65 @@
+// Argument blocks + entry declarations of the fp32 kernels (fwd_f32.cu / bwd_f32.cu).
+#pragma once
+#include "common.cuh"
+
+namespace xf {
+
+struct PriorArgs {
+  const float *v0, *a0;                 // [B,T,E], [B,Ta,E] pre-attention tokens
+  const float *w0, *b0, *w3, *b3;       // prior_net.0 / .3
+  const float* wh[4];                   // score heads: 0 v_query, 1 a_key, 2 a_query, 3 v_key   ([E+P])
+  const float* bh[4];
+  float *pooled0, *phid, *prior;        // [B,2E], [B,Hd] (post ReLU+dropout), [B,P]
+  float *qv, *ka, *qa, *kvs;            // [B,T], [B,Ta], [B,Ta], [B,T]
+  int T, Ta, E, P, Hd;
+  float p_drop;
+  uint64_t seed, offset;
+};
+
+struct AttnArgs {
+  const float* q;        // [B,L,E]
+  const float* kv;       // [B,S,2E]  (K | V)
+  const float* qs;       // [B,L] query-side prior score or nullptr
+  const float* ks;       // [B,S]
+  const float* bias_scale;
+  float* P;              // [B,H,L,S] softmax probabilities (pre-dropout) or nullptr
+  float* O;              // [B,L,E]
+  int L, S, E, H;
+  float scale, p_drop;
+  uint64_t seed, offset;
+  uint32_t rng_stream;
+};
+
+struct AttnBwdArgs {
+  const float *q, *kv, *qs, *ks, *bias_scale, *P;
+  const float* dO;       // [B,L,E]
+  float* dq;             // [B,L,E]
+  float* dkv;            // [B,S,2E]
+  float* dqs;            // [B,L]  (nullptr without prior)
+  float* dks;            // [B,S]
+  float* dbias_scale;    // scalar, atomically accumulated
+  int L, S, E, H;
+  float scale, p_drop;
+  uint64_t seed, offset;
+  uint32_t rng_stream;
+};
+
+struct HeadArgs {
+  const float *v1, *a1;                 // [B,T,E], [B,Ta,E] post-LN tokens
+  const float *w0, *b0, *w1, *b1, *wc, *bc;
+  float *pooled, *hhid, *gate, *fusedg; // saved: [B,2E], [B,HW], [B], [B,E]
+  float* logits;
+  int T, Ta, E, HW, C, gated;
+  float p_drop;
+  uint64_t seed, offset;
+};
+
+size_t attn_smem_bytes(int L, int S, int dh, int nwarps);
+int launch_attn_fwd(cudaStream_t st, const AttnArgs& a, int B);
+
+int forward_f32(const xattn_config& c, const float* params, const void* xv, const void* xa, float* logits, void* ws,
+                cudaStream_t st);
+int backward_f32(const xattn_config& c, const float* params, const void* xv, const void* xa, const float* dlogits,
+                 float* grads, void* ws, cudaStream_t st);
+
+}  // namespace xf

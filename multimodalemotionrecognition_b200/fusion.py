@@ -1,0 +1,543 @@
+"""Host-side mirror of the reference's fusion module, backed by the sm_100a kernels.
+
+``XAttnFusionHead`` is the hot path proper: ``forward(video_emb [B,T,512], audio_emb [B,Ta,768]) -> logits [B,C]``
+(reference ``src/models/fusion.py:372-411``).  ``FusionModel`` keeps the reference constructor and
+``forward(video, audio)`` signature (``fusion.py:188-213``, ``:356``) so it drops into ``src/train.py:211``,
+``src/eval.py:50``, ``src/optimized_runtime.py:106`` and ``backend/app/infer.py:98``: the two backbones run in
+PyTorch exactly as the reference calls them (``fusion.py:368-370``, ``:377``) and everything after runs in the
+CUDA extension.
+
+Parameters are created by the same ``nn`` containers, in the same order and under the same names as
+``fusion.py:269-326``, so ``state_dict()`` is key- and shape-identical and same-seed initialisation is
+bit-identical.  At first use they are re-pointed into one flat fp32 buffer (layout: ``xattn_param_layout`` in
+``include/xattn_fusion.h``), which is what the kernels, the gradient all-reduce and the fused Adam consume.
+
+No fallback: inputs must be CUDA tensors on an sm_100 device, otherwise the call raises.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import math
+from typing import Optional
+
+import torch
+from torch import nn
+
+from . import _lib
+
+_XATTN_MODES = {"xattn", "xattn_concat", "xattn_gated"}
+
+
+def _ptr(t: Optional[torch.Tensor]):
+    return None if t is None else C.c_void_p(t.data_ptr())
+
+
+def _stream_ptr(device) -> C.c_void_p:
+    return C.c_void_p(torch.cuda.current_stream(device).cuda_stream)
+
+
+def _io_dtype(t: torch.Tensor) -> int:
+    if t.dtype == torch.float32:
+        return _lib.DTYPE_F32
+    if t.dtype == torch.bfloat16:
+        return _lib.DTYPE_BF16
+    raise ValueError(f"embeddings must be float32 or bfloat16, got {t.dtype}")
+
+
+class StochasticDepth(nn.Module):
+    """Placeholder kept so module names match the reference (``fusion.py:11-26``); the drop-path itself is
+    applied inside the residual+LayerNorm kernel from ``drop_prob``."""
+
+    def __init__(self, drop_prob: float = 0.0) -> None:
+        super().__init__()
+        self.drop_prob = float(max(0.0, min(1.0, drop_prob)))
+
+    def forward(self, x: torch.Tensor) -> torch.Tensor:  # pragma: no cover - not on the kernel path
+        raise RuntimeError("StochasticDepth is fused into the CUDA residual+LayerNorm kernel")
+
+
+class TemporalPooler(nn.Module):
+    """Mean pooling only (``temporal.py:91-92, 108-109``); carries no parameters.  ``attn`` / ``transformer`` modes are
+    SURVEY 8(f) rank 3 and raise."""
+
+    def __init__(self, dim: int, mode: str = "mean", **_unused) -> None:
+        super().__init__()
+        if mode != "mean":
+            raise ValueError(f"Unsupported temporal pooling mode for the B200 xattn path: {mode} (only 'mean')")
+        self.mode = mode
+        self.pool = None
+
+
+class EmotionPriorBiasAdapter(nn.Module):
+    """Parameter container with the reference's names and init order (``fusion.py:156-168``)."""
+
+    def __init__(self, token_dim: int, prior_dim: int, hidden_dim: int, dropout: float = 0.1) -> None:
+        super().__init__()
+        self.prior_net = nn.Sequential(
+            nn.Linear(token_dim * 2, hidden_dim), nn.ReLU(inplace=True), nn.Dropout(dropout), nn.Linear(hidden_dim, prior_dim))
+        self.v_query_bias = nn.Linear(token_dim + prior_dim, 1)
+        self.a_key_bias = nn.Linear(token_dim + prior_dim, 1)
+        self.a_query_bias = nn.Linear(token_dim + prior_dim, 1)
+        self.v_key_bias = nn.Linear(token_dim + prior_dim, 1)
+        self.bias_scale = nn.Parameter(torch.tensor(1.0, dtype=torch.float32))
+        self.dropout_p = float(dropout)
+
+
+class _XAttnFunction(torch.autograd.Function):
+    """Autograd bridge: forward saves activations in the kernel workspace, backward calls ``xattn_backward``."""
+
+    @staticmethod
+    def forward(ctx, owner, video_emb, audio_emb, *params):
+        logits, state = owner._launch_forward(video_emb, audio_emb, save=True)
+        ctx.owner = owner
+        ctx.state = state
+        ctx.params = params
+        return logits
+
+    @staticmethod
+    def backward(ctx, dlogits):
+        owner = ctx.owner
+        gflat = owner._launch_backward(ctx.state, dlogits.contiguous().float())
+        grads = []
+        for p, (off, n) in zip(ctx.params, owner._xattn_slices):
+            grads.append(gflat[off:off + n].view_as(p) if n > 0 else None)
+        ctx.state = None
+        return (None, None, None, *grads)
+
+
+class XAttnKernelsMixin:
+    """Builds the xattn parameters under the reference's names and runs them through the C ABI."""
+
+    # ---- construction (mirrors fusion.py:263-327) -------------------------------------------------------------
+    def _build_xattn(self, *, v_dim: int, audio_sequence_dim: int, num_classes: int, common_dim: int, xattn_head: str,
+                     d_model: int, num_heads: int, audio_n_mels: int, xattn_attn_dropout: float,
+                     xattn_stochastic_depth: float, temporal_pooling: str, use_emotion_prior: bool, prior_dim: int,
+                     prior_hidden: int, prior_dropout: float, precision: str = "auto") -> None:
+        if xattn_head not in ("concat", "gated"):
+            raise ValueError(f"Unknown xattn head: {xattn_head}")
+        if precision not in ("auto", "fp32", "bf16"):
+            raise ValueError(f"precision must be auto|fp32|bf16, got {precision}")
+        self.v_dim = v_dim
+        self.audio_sequence_dim = audio_sequence_dim
+        self.a_dim = d_model
+        self.d_model = d_model
+        self.num_heads = num_heads
+        self.num_classes = num_classes
+        self.common_dim = common_dim
+        self.precision = precision
+        self.v_in_proj = nn.Linear(self.v_dim, d_model)
+        self.a_in_proj = nn.Linear(self.a_dim, d_model)
+        # kept for state_dict parity; unused on the WavLM path (fusion.py:273, :379-384)
+        self.audio_time_conv = nn.Conv1d(in_channels=audio_n_mels, out_channels=self.a_dim, kernel_size=3, padding=1)
+        self.audio_seq_proj = nn.Linear(self.audio_sequence_dim, self.a_dim)
+        self.v2a_attn = nn.MultiheadAttention(embed_dim=d_model, num_heads=num_heads, dropout=xattn_attn_dropout, batch_first=True)
+        self.a2v_attn = nn.MultiheadAttention(embed_dim=d_model, num_heads=num_heads, dropout=xattn_attn_dropout, batch_first=True)
+        self.v_drop_path = StochasticDepth(drop_prob=xattn_stochastic_depth)
+        self.a_drop_path = StochasticDepth(drop_prob=xattn_stochastic_depth)
+        self.v_norm = nn.LayerNorm(d_model)
+        self.a_norm = nn.LayerNorm(d_model)
+        if use_emotion_prior:
+            self.emotion_prior_bias = EmotionPriorBiasAdapter(d_model, prior_dim, prior_hidden, prior_dropout)
+        else:
+            self.emotion_prior_bias = None
+        self.v_temporal_pool = TemporalPooler(dim=d_model, mode=temporal_pooling)
+        self.a_temporal_pool = TemporalPooler(dim=d_model, mode=temporal_pooling)
+        self.xattn_head = xattn_head
+        if xattn_head == "concat":
+            self.xattn_mlp = nn.Sequential(
+                nn.Linear(d_model * 2, common_dim), nn.ReLU(inplace=True), nn.Dropout(0.2), nn.Linear(common_dim, num_classes))
+        else:
+            self.xattn_gate = nn.Sequential(
+                nn.Linear(d_model * 2, d_model), nn.ReLU(inplace=True), nn.Dropout(0.2), nn.Linear(d_model, 1), nn.Sigmoid())
+            self.xattn_classifier = nn.Linear(d_model, num_classes)
+            with torch.no_grad():  # fusion.py:338-344 — every Linear of the gate except the final Sigmoid module
+                for layer in self.xattn_gate:
+                    if isinstance(layer, nn.Linear):
+                        layer.bias.fill_(-1.0)
+        self.xattn_attn_dropout = float(xattn_attn_dropout)
+        self.xattn_stochastic_depth = float(max(0.0, min(1.0, xattn_stochastic_depth)))
+        self.xattn_head_dropout = 0.2
+        self.xattn_prior_dropout = float(prior_dropout)
+        self._prior_dim = int(prior_dim) if use_emotion_prior else 0
+        self._prior_hidden = int(prior_hidden) if use_emotion_prior else 0
+        # kernel-side state
+        self._xattn_flat: Optional[torch.Tensor] = None
+        self._xattn_grad_flat: Optional[torch.Tensor] = None
+        self._xattn_slices: list[tuple[int, int]] = []
+        self._xattn_packed: Optional[torch.Tensor] = None
+        self._xattn_packed_key = None
+        self._xattn_epoch = 0
+        self._rng_offset = 0
+
+    # ---- config / parameter plumbing ------------------------------------------------------------------------------
+    def _xattn_named_params(self) -> list[Optional[nn.Parameter]]:
+        own = dict(self.named_parameters(recurse=True))
+        out = []
+        for name in _lib.xattn_param_names(self.xattn_head):
+            out.append(own.get(name))
+        return out
+
+    def _make_cfg(self, B: int, T: int, Ta: int, io_dtype: int, precision: int, training: bool, save: bool) -> _lib.XAttnConfig:
+        cfg = _lib.XAttnConfig()
+        cfg.B, cfg.T, cfg.Ta, cfg.Dv, cfg.Da = B, T, Ta, self.v_dim, self.audio_sequence_dim
+        cfg.E, cfg.H = self.d_model, self.num_heads
+        cfg.prior_dim, cfg.prior_hidden = self._prior_dim, self._prior_hidden
+        cfg.common_dim, cfg.C = self.common_dim, self.num_classes
+        cfg.head_kind = _lib.HEAD_CONCAT if self.xattn_head == "concat" else _lib.HEAD_GATED
+        cfg.use_prior = 1 if self.emotion_prior_bias is not None else 0
+        cfg.io_dtype, cfg.precision = io_dtype, precision
+        cfg.training, cfg.save_for_backward = int(training), int(save)
+        cfg.p_attn, cfg.p_path = self.xattn_attn_dropout, self.xattn_stochastic_depth
+        cfg.p_head, cfg.p_prior = self.xattn_head_dropout, self.xattn_prior_dropout
+        cfg.seed = torch.initial_seed() & 0xFFFFFFFFFFFFFFFF
+        cfg.offset = self._rng_offset
+        return cfg
+
+    def flat_parameters(self) -> torch.Tensor:
+        """The flat fp32 parameter buffer (creating / refreshing it if parameters were moved or replaced)."""
+        params = self._xattn_named_params()
+        ref = next(p for p in params if p is not None)
+        dev = ref.device
+        cfg = self._make_cfg(0, 1, 1, _lib.DTYPE_F32, _lib.DTYPE_F32, False, False)
+        offs, sizes, total = _lib.xattn_param_layout(cfg)
+        flat = self._xattn_flat
+        ok = flat is not None and flat.device == dev and flat.numel() == total
+        if ok:
+            base = flat.data_ptr()
+            for p, off, n in zip(params, offs, sizes):
+                if n == 0:
+                    continue
+                if p is None or p.dtype != torch.float32 or p.numel() != n or p.data_ptr() != base + 4 * off or not p.is_contiguous():
+                    ok = False
+                    break
+        if not ok:
+            flat = torch.zeros(total, dtype=torch.float32, device=dev)
+            with torch.no_grad():
+                for p, off, n, name in zip(params, offs, sizes, _lib.xattn_param_names(self.xattn_head)):
+                    if n == 0:
+                        continue
+                    if p is None or p.numel() != n:
+                        raise ValueError(f"parameter {name} missing or wrong size (expected {n} elements)")
+                    view = flat[off:off + n].view(p.shape)
+                    view.copy_(p.detach().to(torch.float32))
+                    p.data = view
+            self._xattn_flat = flat
+            self._xattn_grad_flat = None
+            self._xattn_epoch += 1
+        self._xattn_slices = list(zip(offs, sizes))
+        return self._xattn_flat
+
+    def flat_gradients(self, attach: bool = True) -> torch.Tensor:
+        """Flat gradient buffer (same layout); with ``attach`` every parameter's ``.grad`` is a view into it."""
+        flat = self.flat_parameters()
+        g = self._xattn_grad_flat
+        if g is None or g.device != flat.device or g.numel() != flat.numel():
+            g = torch.zeros_like(flat)
+            self._xattn_grad_flat = g
+        if attach:
+            for p, (off, n) in zip(self._xattn_named_params(), self._xattn_slices):
+                if p is not None and n > 0 and p.requires_grad:
+                    p.grad = g[off:off + n].view(p.shape)
+        return g
+
+    def mark_parameters_updated(self) -> None:
+        """Call after modifying the flat buffer directly (fused Adam) so derived bf16 weights are re-packed."""
+        self._xattn_epoch += 1
+
+    def _packed_weights(self, cfg: _lib.XAttnConfig, flat: torch.Tensor) -> torch.Tensor:
+        params = self._xattn_named_params()
+        key = (flat.data_ptr(), self._xattn_epoch, tuple(0 if p is None else p._version for p in params))
+        if self._xattn_packed is None or self._xattn_packed_key != key or self._xattn_packed.device != flat.device:
+            nbytes = _lib.packed_bytes(cfg)
+            packed = torch.empty(nbytes, dtype=torch.uint8, device=flat.device)
+            _lib.check(_lib.load().xattn_pack_weights(C.byref(cfg), _ptr(flat), _ptr(packed), _stream_ptr(flat.device)))
+            self._xattn_packed, self._xattn_packed_key = packed, key
+        return self._xattn_packed
+
+    # ---- launches ------------------------------------------------------------------------------------------------------
+    def _check_inputs(self, video_emb: torch.Tensor, audio_emb: torch.Tensor) -> None:
+        if video_emb.ndim != 3 or audio_emb.ndim != 3:
+            raise ValueError(
+                f"xattn head expects video_emb [B,T,{self.v_dim}] and audio_emb [B,Ta,{self.audio_sequence_dim}], got "
+                f"shapes {tuple(video_emb.shape)} and {tuple(audio_emb.shape)}")
+        if video_emb.shape[0] != audio_emb.shape[0]:
+            raise ValueError("video_emb and audio_emb disagree on the batch size")
+        if video_emb.shape[2] != self.v_dim or audio_emb.shape[2] != self.audio_sequence_dim:
+            raise ValueError(
+                f"embedding dims ({video_emb.shape[2]}, {audio_emb.shape[2]}) != ({self.v_dim}, {self.audio_sequence_dim})")
+        if not (video_emb.is_cuda and audio_emb.is_cuda):
+            raise RuntimeError("the B200 xattn fusion head has no CPU path: inputs must be CUDA tensors on an sm_100 device")
+        if video_emb.dtype != audio_emb.dtype:
+            raise ValueError("video_emb and audio_emb must share a dtype")
+
+    def _pick_precision(self, io_dtype: int, need_grad: bool) -> int:
+        if need_grad or self.precision == "fp32":
+            return _lib.DTYPE_F32
+        if self.precision == "bf16":
+            return _lib.DTYPE_BF16
+        return _lib.DTYPE_BF16 if io_dtype == _lib.DTYPE_BF16 else _lib.DTYPE_F32
+
+    def _launch_forward(self, video_emb: torch.Tensor, audio_emb: torch.Tensor, save: bool, training: Optional[bool] = None):
+        self._check_inputs(video_emb, audio_emb)
+        video_emb = video_emb.contiguous()
+        audio_emb = audio_emb.contiguous()
+        dev = video_emb.device
+        training = self.training if training is None else training
+        B, T, _ = video_emb.shape
+        Ta = audio_emb.shape[1]
+        io = _io_dtype(video_emb)
+        precision = self._pick_precision(io, save or training)
+        with torch.cuda.device(dev):
+            flat = self.flat_parameters()
+            if flat.device != dev:
+                raise RuntimeError(f"parameters live on {flat.device}, inputs on {dev}")
+            if training:
+                self._rng_offset += 1
+            cfg = self._make_cfg(B, T, Ta, io, precision, training, save)
+            packed = self._packed_weights(cfg, flat) if precision == _lib.DTYPE_BF16 else None
+            ws = torch.empty(_lib.workspace_bytes(cfg), dtype=torch.uint8, device=dev)
+            logits = torch.empty((B, self.num_classes), dtype=torch.float32, device=dev)
+            _lib.check(_lib.load().xattn_forward(C.byref(cfg), _ptr(flat), _ptr(packed), _ptr(video_emb), _ptr(audio_emb),
+                                                 _ptr(logits), _ptr(ws), ws.numel(), _stream_ptr(dev)))
+        return logits, (cfg, video_emb, audio_emb, ws)
+
+    def _launch_backward(self, state, dlogits: torch.Tensor, grads: Optional[torch.Tensor] = None) -> torch.Tensor:
+        cfg, video_emb, audio_emb, ws = state
+        dev = video_emb.device
+        with torch.cuda.device(dev):
+            flat = self.flat_parameters()
+            if grads is None:
+                grads = torch.empty_like(flat)
+            _lib.check(_lib.load().xattn_backward(C.byref(cfg), _ptr(flat), _ptr(video_emb), _ptr(audio_emb), _ptr(dlogits),
+                                                  _ptr(grads), _ptr(ws), ws.numel(), _stream_ptr(dev)))
+        return grads
+
+    def xattn_forward_embeddings(self, video_emb: torch.Tensor, audio_emb: torch.Tensor) -> torch.Tensor:
+        """logits from backbone embeddings; differentiable w.r.t. the fusion parameters (not the embeddings)."""
+        params = self._xattn_named_params()
+        need_grad = torch.is_grad_enabled() and any(p is not None and p.requires_grad for p in params)
+        if need_grad:
+            self.flat_parameters()
+            live = [p if p is not None else torch.empty(0) for p in params]
+            return _XAttnFunction.apply(self, video_emb, audio_emb, *live)
+        logits, _ = self._launch_forward(video_emb, audio_emb, save=False)
+        return logits
+
+
+class XAttnFusionHead(XAttnKernelsMixin, nn.Module):
+    """The hot path as a stand-alone module: ``forward(video_emb, audio_emb) -> logits``.
+
+    Same parameter names/shapes as the non-backbone part of the reference's ``FusionModel`` in ``mode="xattn"``
+    (SURVEY 8b), so a reference checkpoint's fusion keys load with ``load_state_dict(strict=True)`` after
+    filtering out ``audio_model.*`` / ``video_model.*``.
+    """
+
+    def __init__(self, num_classes: int = 8, video_dim: int = 512, audio_dim: int = 768, common_dim: int = 256,
+                 xattn_head: str = "concat", d_model: int = 128, num_heads: int = 4, audio_n_mels: int = 64,
+                 xattn_attn_dropout: float = 0.1, xattn_stochastic_depth: float = 0.1, temporal_pooling: str = "mean",
+                 xattn_use_emotion_prior: bool = False, xattn_emotion_prior_dim: int = 8,
+                 xattn_emotion_prior_hidden_dim: int = 64, xattn_emotion_prior_dropout: float = 0.1,
+                 precision: str = "auto") -> None:
+        super().__init__()
+        self.mode = "xattn"
+        self._build_xattn(v_dim=video_dim, audio_sequence_dim=audio_dim, num_classes=num_classes, common_dim=common_dim,
+                          xattn_head=xattn_head, d_model=d_model, num_heads=num_heads, audio_n_mels=audio_n_mels,
+                          xattn_attn_dropout=xattn_attn_dropout, xattn_stochastic_depth=xattn_stochastic_depth,
+                          temporal_pooling=temporal_pooling, use_emotion_prior=xattn_use_emotion_prior,
+                          prior_dim=xattn_emotion_prior_dim, prior_hidden=xattn_emotion_prior_hidden_dim,
+                          prior_dropout=xattn_emotion_prior_dropout, precision=precision)
+
+    def forward(self, video_emb: torch.Tensor, audio_emb: torch.Tensor) -> torch.Tensor:
+        return self.xattn_forward_embeddings(video_emb, audio_emb)
+
+    @torch.no_grad()
+    def predict_probs(self, video_emb: torch.Tensor, audio_emb: torch.Tensor) -> torch.Tensor:
+        """Batch-path helper mirroring ``TorchModelRunner.predict_probs`` (``optimized_runtime.py:99-108``)."""
+        return torch.softmax(self.forward(video_emb, audio_emb), dim=1)
+
+
+class ClipStyleAlignment(nn.Module):
+    """Parameter container for the CLIP-style alignment (``fusion.py:127-135``); the projections run in the flat-head
+    kernels, the contrastive loss (training only, B x B) in ``FlatHeadKernelsMixin.alignment_loss_from``."""
+
+    def __init__(self, audio_dim: int, video_dim: int, align_dim: int, init_temperature: float = 0.07) -> None:
+        super().__init__()
+        self.audio_proj = nn.Linear(audio_dim, align_dim)
+        self.video_proj = nn.Linear(video_dim, align_dim)
+        safe_temp = max(float(init_temperature), 1e-3)
+        self.logit_scale = nn.Parameter(torch.tensor(math.log(1.0 / safe_temp), dtype=torch.float32))
+
+
+class FlatHeadKernelsMixin:
+    """``mode in {"concat","gated"}`` heads (``fusion.py:226-260``, ``:413-435``) on the CUDA extension (eval forward)."""
+
+    def _build_flat(self, *, audio_dim: int, video_dim: int, num_classes: int, common_dim: int, mode: str,
+                    fusion_align_mode: str, fusion_align_dim: int, fusion_align_temperature: float) -> None:
+        self._flat_audio_dim, self._flat_video_dim = audio_dim, video_dim
+        self._flat_common, self._flat_classes = common_dim, num_classes
+        fusion_audio_dim, fusion_video_dim = audio_dim, video_dim
+        if fusion_align_mode == "clip":
+            self.semantic_alignment = ClipStyleAlignment(audio_dim, video_dim, fusion_align_dim, fusion_align_temperature)
+            fusion_audio_dim = fusion_video_dim = fusion_align_dim
+            self._flat_align = fusion_align_dim
+        else:
+            self.semantic_alignment = None
+            self._flat_align = 0
+        self.audio_proj = nn.Linear(fusion_audio_dim, common_dim)
+        self.video_proj = nn.Linear(fusion_video_dim, common_dim)
+        if mode == "concat":
+            self.fusion = nn.Sequential(
+                nn.Linear(common_dim * 2, common_dim), nn.ReLU(inplace=True), nn.Dropout(0.2), nn.Linear(common_dim, num_classes))
+        else:
+            self.gate = nn.Sequential(
+                nn.Linear(common_dim * 2, common_dim), nn.ReLU(inplace=True), nn.Dropout(0.2), nn.Linear(common_dim, 1), nn.Sigmoid())
+            self.classifier = nn.Linear(common_dim, num_classes)
+            with torch.no_grad():  # fusion.py:329-336
+                for layer in self.gate:
+                    if isinstance(layer, nn.Linear):
+                        layer.bias.fill_(-1.0)
+        self._flat_gated = mode == "gated"
+        self._flat_buf: Optional[torch.Tensor] = None
+
+    def _flat_cfg(self, B: int, T: int, Ta: int, io_dtype: int) -> _lib.FlatHeadConfig:
+        cfg = _lib.FlatHeadConfig()
+        cfg.B, cfg.T, cfg.Ta, cfg.Dv, cfg.Da = B, T, Ta, self._flat_video_dim, self._flat_audio_dim
+        cfg.align_dim, cfg.common_dim, cfg.C = self._flat_align, self._flat_common, self._flat_classes
+        cfg.gated, cfg.io_dtype = int(self._flat_gated), io_dtype
+        return cfg
+
+    def _flat_params(self, dev) -> torch.Tensor:
+        own = dict(self.named_parameters(recurse=True))
+        names = _lib.flat_param_names(self._flat_gated)
+        offs, sizes, total = _lib.flat_param_layout(self._flat_cfg(0, 1, 1, _lib.DTYPE_F32))
+        flat = self._flat_buf
+        ok = flat is not None and flat.device == dev and flat.numel() == total
+        if ok:
+            for name, off, n in zip(names, offs, sizes):
+                if n and (own[name].data_ptr() != flat.data_ptr() + 4 * off or own[name].dtype != torch.float32):
+                    ok = False
+                    break
+        if not ok:
+            flat = torch.zeros(total, dtype=torch.float32, device=dev)
+            with torch.no_grad():
+                for name, off, n in zip(names, offs, sizes):
+                    if n == 0:
+                        continue
+                    p = own[name]
+                    view = flat[off:off + n].view(p.shape)
+                    view.copy_(p.detach().to(device=dev, dtype=torch.float32))
+                    p.data = view
+            self._flat_buf = flat
+        return self._flat_buf
+
+    def flat_forward_sequences(self, video_emb: torch.Tensor, audio_emb: torch.Tensor) -> torch.Tensor:
+        """logits from sequence embeddings [B,T,Dv] / [B,Ta,Da]; the temporal mean is fused into the kernels."""
+        if video_emb.ndim != 3 or audio_emb.ndim != 3:
+            raise ValueError("expected video_emb [B,T,Dv] and audio_emb [B,Ta,Da]")
+        if not (video_emb.is_cuda and audio_emb.is_cuda):
+            raise RuntimeError("the B200 flat fusion heads have no CPU path: inputs must be CUDA tensors")
+        if video_emb.shape[2] != self._flat_video_dim or audio_emb.shape[2] != self._flat_audio_dim:
+            raise ValueError("embedding dims do not match the head")
+        if video_emb.dtype != audio_emb.dtype or video_emb.shape[0] != audio_emb.shape[0]:
+            raise ValueError("video_emb / audio_emb must share dtype and batch size")
+        video_emb, audio_emb = video_emb.contiguous(), audio_emb.contiguous()
+        dev = video_emb.device
+        with torch.cuda.device(dev):
+            cfg = self._flat_cfg(video_emb.shape[0], video_emb.shape[1], audio_emb.shape[1], _io_dtype(video_emb))
+            flat = self._flat_params(dev)
+            ws = torch.empty(_lib.flat_workspace_bytes(cfg), dtype=torch.uint8, device=dev)
+            logits = torch.empty((cfg.B, cfg.C), dtype=torch.float32, device=dev)
+            _lib.check(_lib.load().flat_head_forward(C.byref(cfg), _ptr(flat), _ptr(video_emb), _ptr(audio_emb), _ptr(logits),
+                                                     _ptr(ws), ws.numel(), _stream_ptr(dev)))
+        return logits
+
+    def flat_forward_pooled(self, audio_pooled: torch.Tensor, video_pooled: torch.Tensor) -> torch.Tensor:
+        """logits from already pooled [B,Da] / [B,Dv] embeddings (what ``audio_model.encode`` returns)."""
+        return self.flat_forward_sequences(video_pooled.unsqueeze(1), audio_pooled.unsqueeze(1))
+
+
+class FlatFusionHead(FlatHeadKernelsMixin, nn.Module):
+    """Stand-alone concat / gated head with the reference's parameter names (BASELINE config 5)."""
+
+    def __init__(self, num_classes: int = 8, video_dim: int = 512, audio_dim: int = 768, common_dim: int = 256,
+                 mode: str = "concat", fusion_align_mode: str = "clip", fusion_align_dim: int = 256,
+                 fusion_align_temperature: float = 0.07) -> None:
+        super().__init__()
+        if mode not in ("concat", "gated"):
+            raise ValueError(f"Unknown fusion mode: {mode}")
+        self.mode = mode
+        self._build_flat(audio_dim=audio_dim, video_dim=video_dim, num_classes=num_classes, common_dim=common_dim, mode=mode,
+                         fusion_align_mode=fusion_align_mode, fusion_align_dim=fusion_align_dim,
+                         fusion_align_temperature=fusion_align_temperature)
+
+    def forward(self, video_emb: torch.Tensor, audio_emb: torch.Tensor) -> torch.Tensor:
+        return self.flat_forward_sequences(video_emb, audio_emb)
+
+
+class FusionModel(XAttnKernelsMixin, FlatHeadKernelsMixin, nn.Module):
+    """Drop-in for the reference ``FusionModel`` (``src/models/fusion.py:187-437``): same constructor arguments, same
+    ``forward(video, audio)``, same ``state_dict`` keys, ``pop_alignment_loss()`` (``:346-349``).
+
+    The backbones (``video_model.backbone``, ``audio_model.encode_sequence`` / ``.encode``) stay PyTorch modules the
+    caller supplies; everything downstream runs in the sm_100a kernels.
+    """
+
+    def __init__(self, audio_model: nn.Module, video_model: nn.Module, num_classes: int, mode: str = "late",
+                 common_dim: int = 256, xattn_head: str = "concat", d_model: int = 128, num_heads: int = 4,
+                 audio_n_mels: int = 64, xattn_attn_dropout: float = 0.1, xattn_stochastic_depth: float = 0.1,
+                 temporal_pooling: str = "mean", temporal_num_heads: int = 4, temporal_num_layers: int = 1,
+                 temporal_dropout: float = 0.1, fusion_align_mode: str = "none", fusion_align_dim: int = 256,
+                 fusion_align_temperature: float = 0.07, xattn_use_emotion_prior: bool = False,
+                 xattn_emotion_prior_dim: int = 8, xattn_emotion_prior_hidden_dim: int = 64,
+                 xattn_emotion_prior_dropout: float = 0.1, precision: str = "auto") -> None:
+        super().__init__()
+        self.audio_model = audio_model
+        self.video_model = video_model
+        self.mode = mode
+        self.d_model = d_model
+        self.num_heads = num_heads
+        self.audio_n_mels = audio_n_mels
+        self.fusion_align_mode = fusion_align_mode
+        self.alignment_loss = None
+        self.semantic_alignment = None
+        self.xattn_use_emotion_prior = xattn_use_emotion_prior
+        if mode in {"concat", "gated"}:
+            self._build_flat(audio_dim=audio_model.embedding_dim, video_dim=video_model.embedding_dim, num_classes=num_classes,
+                             common_dim=common_dim, mode=mode, fusion_align_mode=fusion_align_mode,
+                             fusion_align_dim=fusion_align_dim, fusion_align_temperature=fusion_align_temperature)
+        if mode in _XATTN_MODES:
+            self._build_xattn(v_dim=getattr(video_model, "embedding_dim", 512),
+                              audio_sequence_dim=getattr(audio_model, "sequence_dim", d_model), num_classes=num_classes,
+                              common_dim=common_dim, xattn_head=xattn_head, d_model=d_model, num_heads=num_heads,
+                              audio_n_mels=audio_n_mels, xattn_attn_dropout=xattn_attn_dropout,
+                              xattn_stochastic_depth=xattn_stochastic_depth, temporal_pooling=temporal_pooling,
+                              use_emotion_prior=xattn_use_emotion_prior, prior_dim=xattn_emotion_prior_dim,
+                              prior_hidden=xattn_emotion_prior_hidden_dim, prior_dropout=xattn_emotion_prior_dropout,
+                              precision=precision)
+
+    def pop_alignment_loss(self):
+        loss = self.alignment_loss
+        self.alignment_loss = None
+        return loss
+
+    def forward(self, video: torch.Tensor, audio: torch.Tensor):
+        self.alignment_loss = None
+        if self.mode == "late":  # fusion.py:358-363 — backbone-only, no fusion math
+            a_probs = torch.softmax(self.audio_model(audio), dim=1)
+            v_probs = torch.softmax(self.video_model(video), dim=1)
+            return (a_probs + v_probs) / 2.0
+        if self.mode in _XATTN_MODES:
+            b, t, c, h, w = video.shape
+            v_feat = self.video_model.backbone(video.view(b * t, c, h, w)).view(b, t, self.v_dim)   # fusion.py:368-370
+            if not hasattr(self.audio_model, "encode_sequence"):
+                raise ValueError("the B200 xattn path needs audio_model.encode_sequence (WavLM path, fusion.py:374-378); "
+                                 "the mel/audio_time_conv fallback (:379-384) is not built")
+            a_seq = self.audio_model.encode_sequence(audio)                                          # fusion.py:377
+            return self.xattn_forward_embeddings(v_feat, a_seq)
+        if self.mode in {"concat", "gated"}:
+            if self.training:
+                raise RuntimeError("the B200 flat concat/gated heads are inference-only (eval forward, BASELINE config 5)")
+            a_emb = self.audio_model.encode(audio)                                                   # fusion.py:414-415
+            v_emb = self.video_model.encode(video)
+            return self.flat_forward_pooled(a_emb, v_emb)
+        raise ValueError(f"Unknown fusion mode: {self.mode}")

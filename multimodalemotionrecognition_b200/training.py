@@ -1,0 +1,116 @@
+"""Stage-1 training step (frozen backbones, fusion head only) on the sm_100a kernels.
+
+Mirrors the loop body of the reference's ``train_one_epoch`` (``src/train.py:204-228``) for the Stage-1 policy
+(``src/train.py:808-812``: both backbones frozen; ``:848-851``/``:872``: one Adam group over the fusion parameters):
+
+    optimizer.zero_grad(); outputs = model(video, audio); loss = CrossEntropyLoss(label_smoothing)(outputs, labels)
+    loss.backward(); optimizer.step()
+
+Here one step is: xattn_forward (training) -> xattn_ce_loss_fwd_bwd -> xattn_backward (writes ONE flat fp32 gradient
+bucket) -> NCCL all-reduce of that bucket when ``torch.distributed`` is initialised (data parallel over clips,
+SURVEY 8e) -> xattn_adam_step over the flat parameter buffer.  No Python-side autograd graph is built.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import Optional
+
+import torch
+import torch.distributed as dist
+
+from . import _lib
+from .fusion import XAttnKernelsMixin, _ptr, _stream_ptr
+
+
+def shard_range(total: int, rank: int, world: int) -> tuple[int, int]:
+    """Contiguous clip range of ``rank``: B//G each, remainder to the low ranks."""
+    base, rem = divmod(total, world)
+    start = rank * base + min(rank, rem)
+    return start, start + base + (1 if rank < rem else 0)
+
+
+class Stage1Trainer:
+    """Fused fwd + CE + bwd + (all-reduce) + Adam for an ``XAttnFusionHead`` / xattn ``FusionModel``.
+
+    ``decoupled=False`` is ``torch.optim.Adam(weight_decay=wd)`` — what the reference runs (``train.py:872``);
+    ``decoupled=True`` is AdamW (named by BASELINE.json).  Only parameters that receive gradients live in the flat
+    buffer: ``audio_time_conv.*`` gets no gradient on the WavLM path, so torch skips it (no decay either) and so do we.
+    """
+
+    def __init__(self, head: XAttnKernelsMixin, lr: float = 1e-3, weight_decay: float = 1e-4, betas=(0.9, 0.999),
+                 eps: float = 1e-8, label_smoothing: float = 0.0, decoupled: bool = False,
+                 process_group: Optional["dist.ProcessGroup"] = None) -> None:
+        self.head = head
+        self.lr, self.weight_decay, self.betas, self.eps = float(lr), float(weight_decay), betas, float(eps)
+        self.label_smoothing = float(label_smoothing)
+        self.decoupled = bool(decoupled)
+        self.group = process_group
+        self.step_count = 0
+        self.exp_avg: Optional[torch.Tensor] = None
+        self.exp_avg_sq: Optional[torch.Tensor] = None
+        self._loss = None
+
+    def _world(self) -> int:
+        return dist.get_world_size(self.group) if dist.is_available() and dist.is_initialized() else 1
+
+    def forward_backward(self, video_emb: torch.Tensor, audio_emb: torch.Tensor, labels: torch.Tensor,
+                         training: bool = True) -> torch.Tensor:
+        """Forward + loss + backward into the flat gradient bucket (no optimizer step).  Returns the loss (0-dim)."""
+        head = self.head
+        dev = video_emb.device
+        logits, state = head._launch_forward(video_emb, audio_emb, save=True, training=training)
+        grads = head.flat_gradients(attach=True)
+        B, Cn = logits.shape
+        loss = torch.empty((), dtype=torch.float32, device=dev)
+        dlogits = torch.empty_like(logits)
+        labels = labels.to(device=dev, dtype=torch.int64).contiguous()
+        with torch.cuda.device(dev):
+            _lib.check(_lib.load().xattn_ce_loss_fwd_bwd(_ptr(logits), _ptr(labels), B, Cn, self.label_smoothing,
+                                                         1.0 / self._world(), _ptr(loss), _ptr(dlogits), _stream_ptr(dev)))
+        head._launch_backward(state, dlogits, grads)
+        self._logits = logits
+        return loss
+
+    def allreduce_gradients(self) -> None:
+        """Sum the flat gradient bucket over ranks (each rank's loss gradient is pre-scaled by 1/world)."""
+        if self._world() > 1:
+            dist.all_reduce(self.head.flat_gradients(attach=False), op=dist.ReduceOp.SUM, group=self.group)
+
+    def optimizer_step(self) -> None:
+        head = self.head
+        flat = head.flat_parameters()
+        grads = head.flat_gradients(attach=False)
+        if self.exp_avg is None or self.exp_avg.numel() != flat.numel() or self.exp_avg.device != flat.device:
+            self.exp_avg = torch.zeros_like(flat)
+            self.exp_avg_sq = torch.zeros_like(flat)
+        self.step_count += 1
+        dev = flat.device
+        with torch.cuda.device(dev):
+            _lib.check(_lib.load().xattn_adam_step(_ptr(flat), _ptr(grads), _ptr(self.exp_avg), _ptr(self.exp_avg_sq),
+                                                   flat.numel(), self.lr, self.betas[0], self.betas[1], self.eps,
+                                                   self.weight_decay, self.step_count, int(self.decoupled), _stream_ptr(dev)))
+        head.mark_parameters_updated()
+
+    def step(self, video_emb: torch.Tensor, audio_emb: torch.Tensor, labels: torch.Tensor, training: bool = True) -> torch.Tensor:
+        """One full Stage-1 step; returns this rank's mean loss as a 0-dim CUDA tensor (no host sync)."""
+        loss = self.forward_backward(video_emb, audio_emb, labels, training=training)
+        self.allreduce_gradients()
+        self.optimizer_step()
+        return loss
+
+
+def gather_logits(local_logits: torch.Tensor, total: int, group=None) -> torch.Tensor:
+    """Inference-side collective: all-gather of per-rank [B_r, C] logits into [total, C] (ragged shards padded)."""
+    if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size(group) == 1:
+        return local_logits
+    world = dist.get_world_size(group)
+    per = (total + world - 1) // world
+    pad = torch.zeros((per, local_logits.shape[1]), dtype=local_logits.dtype, device=local_logits.device)
+    pad[: local_logits.shape[0]] = local_logits
+    out = torch.empty((world * per, local_logits.shape[1]), dtype=local_logits.dtype, device=local_logits.device)
+    dist.all_gather_into_tensor(out, pad, group=group)
+    pieces = []
+    for r in range(world):
+        s, e = shard_range(total, r, world)
+        pieces.append(out[r * per: r * per + (e - s)])
+    return torch.cat(pieces, dim=0)

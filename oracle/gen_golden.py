@@ -1,0 +1,189 @@
+"""Generates tests/golden/*.npz by running the UNMODIFIED reference module in the build container.
+
+TEST INFRASTRUCTURE ONLY.  Imports ``/root/reference/src/models/fusion.py`` (pure torch; nothing is copied into the
+repo), runs it on seeded synthetic inputs and stores inputs / weights (small cases) or SHA-256 digests of them
+(BASELINE config 1, whose weights come from ``torch.manual_seed(0)`` in reference constructor order and inputs from
+``torch.Generator().manual_seed(1)``) together with the reference's logits, loss, gradients and
+post-Adam parameters.  ``/root/reference`` does not exist on the GPU box, hence the committed fixtures.
+
+    PYTHONDONTWRITEBYTECODE=1 python oracle/gen_golden.py
+"""
+from __future__ import annotations
+
+import hashlib
+import os
+import sys
+from pathlib import Path
+
+import numpy as np
+import torch
+from torch import nn
+
+REF = os.environ.get("XATTN_REFERENCE_ROOT", "/root/reference")
+OUT = Path(__file__).resolve().parents[1] / "tests" / "golden"
+
+
+def sha(t) -> str:
+    a = t.detach().cpu().contiguous().numpy() if isinstance(t, torch.Tensor) else np.ascontiguousarray(t)
+    return hashlib.sha256(a.tobytes()).hexdigest()
+
+
+class StubVideo(nn.Module):
+    """Backbone stand-in: the 'frames' already are the embeddings ([B*T, Dv, 1, 1] -> same)."""
+
+    def __init__(self, dim: int) -> None:
+        super().__init__()
+        self.embedding_dim = dim
+        self.backbone = nn.Identity()
+
+    def encode(self, x):
+        return x
+
+
+class StubAudio(nn.Module):
+    def __init__(self, dim: int) -> None:
+        super().__init__()
+        self.sequence_dim = dim
+        self.embedding_dim = dim
+
+    def encode_sequence(self, x):
+        return x
+
+    def encode(self, x):
+        return x
+
+
+def build_ref(FusionModel, *, dv, da, d_model, heads, head, prior, common=256, prior_dim=8, prior_hidden=64, classes=8,
+              mode="xattn", align="none"):
+    return FusionModel(StubAudio(da), StubVideo(dv), classes, mode=mode, common_dim=common, xattn_head=head, d_model=d_model,
+                       num_heads=heads, audio_n_mels=da, xattn_use_emotion_prior=prior, xattn_emotion_prior_dim=prior_dim,
+                       xattn_emotion_prior_hidden_dim=prior_hidden, fusion_align_mode=align, fusion_align_dim=256)
+
+
+def fusion_state(model) -> dict:
+    return {k: v.detach().clone() for k, v in model.state_dict().items()
+            if not (k.startswith("audio_model.") or k.startswith("video_model."))}
+
+
+def grads_of(model) -> dict:
+    return {k: p.grad.detach().clone() for k, p in model.named_parameters() if p.grad is not None}
+
+
+def digest(t: torch.Tensor) -> np.ndarray:
+    t = t.detach().double().flatten()
+    idx = torch.linspace(0, t.numel() - 1, steps=8).long()   # 8 evenly spaced samples (repeats for tiny tensors)
+    return np.concatenate([[t.sum().item(), t.abs().sum().item(), t.norm().item()], t[idx].numpy()])
+
+
+def run_case(model, xv, xa, labels, lr=1e-3, wd=1e-4):
+    """eval-mode forward, CE, backward, one torch.optim.Adam step (train.py:204-228 with dropouts identity)."""
+    model.eval()
+    with torch.no_grad():
+        logits = model(xv[..., None, None], xa)
+    params = [p for n, p in model.named_parameters()]
+    opt = torch.optim.Adam(params, lr=lr, weight_decay=wd)
+    opt.zero_grad()
+    out = model(xv[..., None, None], xa)
+    loss = nn.functional.cross_entropy(out, labels)
+    loss.backward()
+    grads = grads_of(model)
+    opt.step()
+    after = fusion_state(model)
+    return logits, loss.detach(), grads, after
+
+
+def main() -> None:
+    sys.path.insert(0, REF)
+    sys.dont_write_bytecode = True
+    from src.models.fusion import FusionModel  # the reference, unmodified
+
+    OUT.mkdir(parents=True, exist_ok=True)
+    torch.set_num_threads(1)
+
+    # ---- tiny case: everything stored in full (d_model=8, heads=2 as the reference's own shape tests) -------------
+    for head in ("concat", "gated"):
+        for prior in (True, False):
+            torch.manual_seed(10)
+            m = build_ref(FusionModel, dv=16, da=8, d_model=8, heads=2, head=head, prior=prior, common=16, prior_dim=4,
+                          prior_hidden=8)
+            g = torch.Generator().manual_seed(11)
+            xv = torch.randn(3, 4, 16, generator=g)
+            xa = torch.randn(3, 12, 8, generator=g)
+            labels = torch.tensor([1, 7, 3])
+            sd0 = fusion_state(m)
+            logits, loss, grads, after = run_case(m, xv, xa, labels)
+            blob = {"xv": xv.numpy(), "xa": xa.numpy(), "labels": labels.numpy(), "logits": logits.numpy(),
+                    "loss": loss.numpy()}
+            blob.update({"w:" + k: v.numpy() for k, v in sd0.items()})
+            blob.update({"g:" + k: v.numpy() for k, v in grads.items()})
+            blob.update({"a:" + k: v.numpy() for k, v in after.items()})
+            np.savez_compressed(OUT / f"xattn_tiny_{head}_{'prior' if prior else 'noprior'}.npz", **blob)
+
+    # ---- BASELINE config 1: B=8, [8,16,512] + [8,149,768]; digests of weights/inputs, full logits ------------------
+    blob = {}
+    g = torch.Generator().manual_seed(1)
+    xv = torch.randn(8, 16, 512, generator=g)
+    xa = torch.randn(8, 149, 768, generator=g)
+    labels = torch.randint(0, 8, (8,), generator=g)
+    blob["labels"] = labels.numpy()
+    blob["sha_xv"] = np.array(sha(xv))
+    blob["sha_xa"] = np.array(sha(xa))
+    for head in ("concat", "gated"):
+        for prior in (True, False):
+            tag = f"{head}_{'prior' if prior else 'noprior'}"
+            torch.manual_seed(0)
+            m = build_ref(FusionModel, dv=512, da=768, d_model=128, heads=4, head=head, prior=prior)
+            sd0 = fusion_state(m)
+            logits, loss, grads, after = run_case(m, xv, xa, labels)
+            blob[f"{tag}:logits"] = logits.numpy()
+            blob[f"{tag}:loss"] = loss.numpy()
+            blob[f"{tag}:keys"] = np.array(sorted(sd0))
+            blob[f"{tag}:shapes"] = np.array([str(tuple(sd0[k].shape)) for k in sorted(sd0)])
+            blob[f"{tag}:sha"] = np.array([sha(sd0[k]) for k in sorted(sd0)])
+            blob[f"{tag}:gkeys"] = np.array(sorted(grads))
+            blob[f"{tag}:gdigest"] = np.stack([digest(grads[k]) for k in sorted(grads)])
+            blob[f"{tag}:adigest"] = np.stack([digest(after[k]) for k in sorted(grads)])
+    np.savez_compressed(OUT / "xattn_config1.npz", **blob)
+
+    # ---- flat concat/gated heads with CLIP-style alignment (config 5), pooled inputs ----------------------------------
+    blob = {}
+    g = torch.Generator().manual_seed(3)
+    ap = torch.randn(6, 768, generator=g)
+    vp = torch.randn(6, 512, generator=g)
+    blob["sha_ap"] = np.array(sha(ap))
+    blob["sha_vp"] = np.array(sha(vp))
+    for mode in ("concat", "gated"):
+        torch.manual_seed(0)
+        m = build_ref(FusionModel, dv=512, da=768, d_model=128, heads=4, head="concat", prior=False, mode=mode, align="clip")
+        m.eval()
+        sd0 = fusion_state(m)
+        with torch.no_grad():
+            logits = m(vp, ap)
+            loss = m.pop_alignment_loss()
+        blob[f"{mode}:logits"] = logits.numpy()
+        blob[f"{mode}:align_loss"] = loss.numpy()
+        blob[f"{mode}:keys"] = np.array(sorted(sd0))
+        blob[f"{mode}:sha"] = np.array([sha(sd0[k]) for k in sorted(sd0)])
+    # small fully-stored flat case
+    for mode in ("concat", "gated"):
+        torch.manual_seed(20)
+        m = build_ref(FusionModel, dv=12, da=10, d_model=8, heads=2, head="concat", prior=False, mode=mode, align="clip", common=16)
+        m.eval()
+        g2 = torch.Generator().manual_seed(21)
+        xa = torch.randn(3, 5, 10, generator=g2)
+        xv = torch.randn(3, 4, 12, generator=g2)
+        with torch.no_grad():
+            logits = m(xv.mean(dim=1), xa.mean(dim=1))
+            loss = m.pop_alignment_loss()
+        sd0 = fusion_state(m)
+        small = {"xa": xa.numpy(), "xv": xv.numpy(), "logits": logits.numpy(), "align_loss": loss.numpy()}
+        small.update({"w:" + k: v.numpy() for k, v in sd0.items()})
+        np.savez_compressed(OUT / f"flat_tiny_{mode}.npz", **small)
+    np.savez_compressed(OUT / "flat_config5.npz", **blob)
+    print("golden fixtures written to", OUT)
+    for f in sorted(OUT.glob("*.npz")):
+        print(f"  {f.name}: {f.stat().st_size} bytes")
+
+
+if __name__ == "__main__":
+    main()

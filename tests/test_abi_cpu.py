@@ -1,0 +1,155 @@
+"""CPU-side checks of the boundary: the C-ABI library loads and exports every symbol include/xattn_fusion.h declares,
+host-only layout queries work without a GPU, the module mirrors the reference's state_dict, and there is no CPU
+fallback.  No compute entry point is called here."""
+import ctypes as C
+import re
+from pathlib import Path
+
+import numpy as np
+import pytest
+import torch
+
+from helpers import load_npz, make_head, sha
+
+ROOT = Path(__file__).resolve().parents[1]
+
+
+def _declared_symbols():
+    text = (ROOT / "include" / "xattn_fusion.h").read_text()
+    return sorted(set(re.findall(r"XATTN_API\s+[\w\s\*]+?\b((?:xattn|flat_head)_\w+)\s*\(", text)))
+
+
+def test_library_exports_every_declared_symbol():
+    from multimodalemotionrecognition_b200 import _lib
+
+    lib = _lib.load()
+    declared = _declared_symbols()
+    assert len(declared) >= 13, declared
+    for name in declared:
+        assert hasattr(lib, name), f"{name} declared in include/xattn_fusion.h but not exported"
+        assert name in _lib.EXPORTED_SYMBOLS, f"{name} has no ctypes prototype"
+    assert lib.xattn_abi_version() == 3
+
+
+def test_param_layout_matches_state_dict_shapes():
+    from multimodalemotionrecognition_b200 import _lib
+
+    for head in ("concat", "gated"):
+        for prior in (True, False):
+            m = make_head(head, prior)
+            cfg = m._make_cfg(8, 16, 149, _lib.DTYPE_F32, _lib.DTYPE_F32, False, False)
+            offs, sizes, total = _lib.xattn_param_layout(cfg)
+            sd = m.state_dict()
+            used = 0
+            for name, off, n in zip(_lib.xattn_param_names(head), offs, sizes):
+                assert off % 4 == 0
+                if n == 0:
+                    assert name not in sd or not prior or head == "concat"
+                    continue
+                assert sd[name].numel() == n, name
+                used += n
+            assert used == (398581 if prior and head == "concat" else used)
+            assert total >= used
+            # every fusion parameter except the unused audio_time_conv is in the flat buffer
+            in_flat = {n for n, s in zip(_lib.xattn_param_names(head), sizes) if s}
+            assert set(sd) - in_flat == {"audio_time_conv.weight", "audio_time_conv.bias"}
+
+
+def test_workspace_queries_and_config_validation():
+    from multimodalemotionrecognition_b200 import _lib
+
+    m = make_head("concat", True)
+    small = _lib.workspace_bytes(m._make_cfg(8, 16, 149, 0, 0, False, False))
+    train = _lib.workspace_bytes(m._make_cfg(8, 16, 149, 0, 0, True, True))
+    assert train > small > 0
+    assert _lib.workspace_bytes(m._make_cfg(16, 16, 149, 0, 0, False, False)) > small
+    bad = m._make_cfg(8, 16, 149, 0, 0, False, False)
+    bad.H = 3   # 128 % 3 != 0 -> same complaint nn.MultiheadAttention raises at construction
+    with pytest.raises(ValueError, match="divisible"):
+        _lib.workspace_bytes(bad)
+    bad = m._make_cfg(8, 16, 149, 7, 0, False, False)
+    with pytest.raises(ValueError):
+        _lib.workspace_bytes(bad)
+    assert _lib.load().xattn_workspace_bytes(None, None) == _lib.ERR_NULL
+    assert "NULL" in _lib.last_error()
+
+
+def test_no_cpu_fallback():
+    m = make_head("concat", True).eval()
+    with pytest.raises(RuntimeError, match="no CPU path"):
+        m(torch.zeros(2, 16, 512), torch.zeros(2, 149, 768))
+    with pytest.raises(ValueError):
+        m(torch.zeros(2, 512), torch.zeros(2, 149, 768))
+
+
+def test_missing_library_fails_loudly(monkeypatch, tmp_path):
+    from multimodalemotionrecognition_b200 import _lib
+
+    monkeypatch.setattr(_lib, "_lib", None)
+    monkeypatch.setenv("XATTN_FUSION_LIB", str(tmp_path / "nope.so"))
+    with pytest.raises(RuntimeError, match="not built"):
+        _lib.load()
+
+
+def test_unsupported_reference_options_raise_cleanly():
+    from multimodalemotionrecognition_b200 import XAttnFusionHead
+
+    with pytest.raises(ValueError, match="temporal pooling"):
+        XAttnFusionHead(temporal_pooling="transformer")
+    with pytest.raises(ValueError):
+        XAttnFusionHead(xattn_head="nope")
+
+
+def test_reference_shape_test_configuration_builds():
+    """The reference's own xattn test builds d_model=8, num_heads=2 (tests/test_attention_integration.py:83-91)."""
+    from multimodalemotionrecognition_b200 import FusionModel, _lib
+
+    class V(torch.nn.Module):
+        embedding_dim = 16
+
+        def __init__(self):
+            super().__init__()
+            self.backbone = torch.nn.Identity()
+
+    class A(torch.nn.Module):
+        sequence_dim = 8
+
+        def encode_sequence(self, x):
+            return x
+
+    fm = FusionModel(A(), V(), num_classes=8, mode="xattn", d_model=8, num_heads=2, audio_n_mels=64).eval()
+    cfg = fm._make_cfg(2, 4, 12, _lib.DTYPE_F32, _lib.DTYPE_F32, False, False)
+    assert _lib.workspace_bytes(cfg) > 0
+    assert fm.mode == "xattn" and fm.pop_alignment_loss() is None
+    assert "v2a_attn.in_proj_weight" in fm.state_dict() and "audio_time_conv.weight" in fm.state_dict()
+
+
+@pytest.mark.parametrize("mode", ["concat", "gated"])
+def test_flat_head_seed0_init_matches_reference(mode):
+    from multimodalemotionrecognition_b200 import FlatFusionHead, _lib
+
+    blob = load_npz("flat_config5.npz")
+    torch.manual_seed(0)
+    m = FlatFusionHead(num_classes=8, video_dim=512, audio_dim=768, common_dim=256, mode=mode)
+    sd = m.state_dict()
+    assert sorted(sd) == list(blob[f"{mode}:keys"])
+    for k, d in zip(blob[f"{mode}:keys"], blob[f"{mode}:sha"]):
+        assert sha(sd[str(k)]) == str(d), k
+    offs, sizes, total = _lib.flat_param_layout(m._flat_cfg(4, 16, 149, 0))
+    for name, n in zip(_lib.flat_param_names(mode == "gated"), sizes):
+        if n:
+            assert sd[name].numel() == n, name
+    assert "semantic_alignment.logit_scale" in sd
+
+
+def test_flat_parameter_views_follow_load_state_dict():
+    m = make_head("concat", True)
+    flat = m.flat_parameters()
+    assert flat.numel() >= 398581
+    sd = {k: torch.full_like(v, 0.5) for k, v in m.state_dict().items()}
+    m.load_state_dict(sd)
+    assert m.flat_parameters() is flat          # views survived the in-place load
+    off, n = m._xattn_slices[0]
+    assert torch.all(flat[off:off + n] == 0.5)
+    g = m.flat_gradients()
+    assert m.v_in_proj.weight.grad.data_ptr() == g.data_ptr() + 4 * off

@@ -1,0 +1,321 @@
+"""GPU parity tests (``-m gpu``): the CUDA path, called through the C ABI (ctypes, ``_lib``), against the oracle and
+the committed reference fixtures.  Tolerances are BASELINE.json's: fp32 <= 1e-4 max-abs logit error, bf16 <= 1e-2."""
+import numpy as np
+import pytest
+import torch
+
+from helpers import config1_inputs, digest, fusion_state_np, load_npz, make_head, tiny_head
+from oracle import torch_port, xattn_oracle
+
+pytestmark = pytest.mark.gpu
+
+FP32_TOL = 1e-4   # north_star: within 1e-4 max-abs logit error in fp32
+BF16_TOL = 1e-2   # north_star: 1e-2 in bf16
+VARIANTS = [(h, p) for h in ("concat", "gated") for p in (True, False)]
+
+
+def _tag(head, prior):
+    return f"{head}_{'prior' if prior else 'noprior'}"
+
+
+def test_extension_is_loaded_from_tree():
+    from multimodalemotionrecognition_b200 import _lib
+
+    lib = _lib.load()
+    assert lib.xattn_abi_version() == _lib.ABI_VERSION
+    assert _lib.LIB_PATH.exists()
+
+
+@pytest.mark.parametrize("head,prior", VARIANTS)
+def test_fp32_forward_tiny_matches_reference(cuda_device, head, prior):
+    blob = load_npz(f"xattn_tiny_{_tag(head, prior)}.npz")
+    m = tiny_head(blob, head, prior).to(cuda_device).eval()
+    with torch.no_grad():
+        out = m(torch.from_numpy(blob["xv"]).to(cuda_device), torch.from_numpy(blob["xa"]).to(cuda_device))
+    assert out.shape == (3, 8) and out.dtype == torch.float32
+    np.testing.assert_allclose(out.cpu().numpy(), blob["logits"], atol=1e-5, rtol=0)
+
+
+@pytest.mark.parametrize("head,prior", VARIANTS)
+def test_fp32_forward_config1_matches_reference(cuda_device, head, prior):
+    """BASELINE config 1 (B=8, [8,16,512] + [8,149,768]) against the reference module's own logits."""
+    blob = load_npz("xattn_config1.npz")
+    xv, xa, _ = config1_inputs()
+    m = make_head(head, prior, seed=0).to(cuda_device).eval()
+    with torch.no_grad():
+        out = m(xv.to(cuda_device), xa.to(cuda_device)).cpu().numpy()
+    err = np.abs(out - blob[f"{_tag(head, prior)}:logits"]).max()
+    assert err <= FP32_TOL, err
+    assert err <= 5e-6, f"fp32 path drifted from the reference more than expected: {err}"
+
+
+@pytest.mark.parametrize("B,T,Ta", [(1, 16, 149), (3, 8, 100), (5, 1, 1), (2, 33, 7), (257, 16, 149)])
+def test_fp32_forward_ragged_shapes_vs_oracle(cuda_device, B, T, Ta):
+    m = make_head("concat", True, seed=3).to(cuda_device).eval()
+    g = torch.Generator().manual_seed(100 + B)
+    xv = torch.randn(B, T, 512, generator=g)
+    xa = torch.randn(B, Ta, 768, generator=g)
+    with torch.no_grad():
+        out = m(xv.to(cuda_device), xa.to(cuda_device)).cpu().numpy()
+    n = min(B, 16)   # the fp64 oracle is slow; check a prefix and a suffix
+    sd = fusion_state_np(m)
+    ref_a = xattn_oracle.xattn_forward(sd, xv[:n].numpy(), xa[:n].numpy(), num_heads=4, head="concat", use_prior=True)
+    ref_b = xattn_oracle.xattn_forward(sd, xv[-n:].numpy(), xa[-n:].numpy(), num_heads=4, head="concat", use_prior=True)
+    assert np.abs(out[:n] - ref_a).max() <= FP32_TOL
+    assert np.abs(out[-n:] - ref_b).max() <= FP32_TOL
+
+
+def test_empty_batch(cuda_device):
+    m = make_head("concat", True).to(cuda_device).eval()
+    with torch.no_grad():
+        out = m(torch.zeros(0, 16, 512, device=cuda_device), torch.zeros(0, 149, 768, device=cuda_device))
+    assert out.shape == (0, 8)
+
+
+def test_error_conventions(cuda_device):
+    m = make_head("concat", False).to(cuda_device).eval()
+    with pytest.raises(ValueError):   # reference: TemporalPooler raises ValueError for ndim != 3 (temporal.py:106-107)
+        m(torch.zeros(4, 512, device=cuda_device), torch.zeros(4, 149, 768, device=cuda_device))
+    with pytest.raises(ValueError):
+        m(torch.zeros(4, 16, 500, device=cuda_device), torch.zeros(4, 149, 768, device=cuda_device))
+    with pytest.raises(ValueError):
+        m(torch.zeros(4, 16, 512, device=cuda_device, dtype=torch.float16), torch.zeros(4, 149, 768, device=cuda_device, dtype=torch.float16))
+    with pytest.raises(RuntimeError):  # no CPU path
+        m.cpu()(torch.zeros(4, 16, 512), torch.zeros(4, 149, 768))
+
+
+def test_fp32_kernels_with_bf16_inputs(cuda_device):
+    """io_dtype=bf16 with fp32 arithmetic equals the oracle fed the same bf16-rounded inputs."""
+    m = make_head("gated", True, seed=5, precision="fp32").to(cuda_device).eval()
+    xv, xa, _ = config1_inputs()
+    xvb, xab = xv.bfloat16(), xa.bfloat16()
+    with torch.no_grad():
+        out = m(xvb.to(cuda_device), xab.to(cuda_device)).cpu().numpy()
+    ref = xattn_oracle.xattn_forward(fusion_state_np(m), xvb.float().numpy(), xab.float().numpy(), num_heads=4, head="gated")
+    assert np.abs(out - ref).max() <= FP32_TOL
+
+
+def test_clip_independence_and_determinism_full_size(cuda_device):
+    """Size-independent property at BASELINE's full B=4096: every clip is independent, so any shard of the
+    batch gives the same rows, and repeated launches are bit-identical."""
+    m = make_head("concat", True, seed=1).to(cuda_device).eval()
+    g = torch.Generator(device=cuda_device).manual_seed(7)
+    B = 4096
+    xv = torch.randn(B, 16, 512, device=cuda_device, generator=g)
+    xa = torch.randn(B, 149, 768, device=cuda_device, generator=g)
+    with torch.no_grad():
+        full = m(xv, xa)
+        again = m(xv, xa)
+        part = m(xv[1000:1100], xa[1000:1100])
+        tail = m(xv[4090:], xa[4090:])
+    assert torch.equal(full, again)
+    assert torch.equal(full[1000:1100], part)
+    assert torch.equal(full[4090:], tail)
+    # spot-check against the fp32 CPU port of the reference on a slice
+    ref = torch_port.xattn_forward({k: v.cpu() for k, v in m.state_dict().items()}, xv[:32].cpu(), xa[:32].cpu(), num_heads=4)
+    assert (full[:32].cpu() - ref).abs().max() <= FP32_TOL
+    assert (full[:32].cpu().argmax(1) == ref.argmax(1)).all()
+
+
+@pytest.mark.parametrize("head,prior", VARIANTS)
+def test_backward_tiny_matches_reference_gradients(cuda_device, head, prior):
+    blob = load_npz(f"xattn_tiny_{_tag(head, prior)}.npz")
+    m = tiny_head(blob, head, prior).to(cuda_device).eval()   # eval: dropouts identity, autograd on
+    out = m(torch.from_numpy(blob["xv"]).to(cuda_device), torch.from_numpy(blob["xa"]).to(cuda_device))
+    loss = torch.nn.functional.cross_entropy(out, torch.from_numpy(blob["labels"]).to(cuda_device))
+    assert abs(float(loss) - float(blob["loss"])) < 1e-5
+    loss.backward()
+    named = dict(m.named_parameters())
+    n = 0
+    for k, v in blob.items():
+        if k.startswith("g:"):
+            g = named[k[2:]].grad
+            assert g is not None, k
+            np.testing.assert_allclose(g.cpu().numpy(), v, atol=2e-6, rtol=1e-4, err_msg=k)
+            n += 1
+    assert n >= 20
+    assert named["audio_time_conv.weight"].grad is None
+
+
+@pytest.mark.parametrize("head,prior", VARIANTS)
+def test_backward_config1_matches_port_autograd_and_reference_digests(cuda_device, head, prior):
+    blob = load_npz("xattn_config1.npz")
+    tag = _tag(head, prior)
+    xv, xa, labels = config1_inputs()
+    m = make_head(head, prior, seed=0).to(cuda_device).eval()
+    out = m(xv.to(cuda_device), xa.to(cuda_device))
+    loss = torch.nn.functional.cross_entropy(out, labels.to(cuda_device))
+    loss.backward()
+    assert abs(float(loss) - float(blob[f"{tag}:loss"])) < 1e-5
+    named = dict(m.named_parameters())
+    # (1) digests of the reference's own gradients
+    for k, d in zip(blob[f"{tag}:gkeys"], blob[f"{tag}:gdigest"]):
+        np.testing.assert_allclose(digest(named[str(k)].grad), d, atol=5e-6, rtol=2e-4, err_msg=str(k))
+    # (2) element-wise against autograd through the CPU port
+    sdt = {k: v.detach().cpu().clone().requires_grad_(True) for k, v in m.state_dict().items()}
+    ref = torch_port.xattn_forward(sdt, xv, xa, num_heads=4, head=head, use_prior=prior)
+    torch.nn.functional.cross_entropy(ref, labels).backward()
+    for k, p in named.items():
+        if sdt[k].grad is None:
+            assert p.grad is None, k
+            continue
+        np.testing.assert_allclose(p.grad.cpu().numpy(), sdt[k].grad.numpy(), atol=3e-6, rtol=2e-4, err_msg=k)
+
+
+def test_ce_loss_kernel_vs_oracle(cuda_device):
+    import ctypes as C
+
+    from multimodalemotionrecognition_b200 import _lib
+    from multimodalemotionrecognition_b200.fusion import _ptr, _stream_ptr
+
+    g = torch.Generator().manual_seed(9)
+    for B, Cn, eps in [(1, 8, 0.0), (37, 8, 0.1), (1024, 8, 0.05), (5, 3, 0.0)]:
+        logits = torch.randn(B, Cn, generator=g) * 3
+        labels = torch.randint(0, Cn, (B,), generator=g)
+        ref_loss, ref_d = xattn_oracle.cross_entropy(logits.numpy(), labels.numpy(), eps)
+        lg, lb = logits.to(cuda_device), labels.to(cuda_device)
+        loss = torch.empty((), device=cuda_device)
+        d = torch.empty_like(lg)
+        _lib.check(_lib.load().xattn_ce_loss_fwd_bwd(_ptr(lg), _ptr(lb), B, Cn, eps, 1.0, _ptr(loss), _ptr(d), _stream_ptr(cuda_device)))
+        assert abs(float(loss) - ref_loss) < 1e-5
+        np.testing.assert_allclose(d.cpu().numpy(), ref_d, atol=1e-7, rtol=1e-5)
+        tl = torch.nn.functional.cross_entropy(logits, labels, label_smoothing=eps)
+        assert abs(float(loss) - float(tl)) < 1e-5
+
+
+@pytest.mark.parametrize("decoupled", [False, True])
+def test_adam_kernel_vs_oracle_and_torch(cuda_device, decoupled):
+    from multimodalemotionrecognition_b200 import _lib
+    from multimodalemotionrecognition_b200.fusion import _ptr, _stream_ptr
+
+    n = 10007
+    g = torch.Generator().manual_seed(4)
+    p0 = torch.randn(n, generator=g)
+    p = p0.clone().to(cuda_device)
+    m = torch.zeros(n, device=cuda_device)
+    v = torch.zeros(n, device=cuda_device)
+    pt = torch.nn.Parameter(p0.clone())
+    opt = (torch.optim.AdamW if decoupled else torch.optim.Adam)([pt], lr=1e-3, weight_decay=1e-2)
+    po, mo, vo = p0.double().numpy(), np.zeros(n), np.zeros(n)
+    for step in range(1, 6):
+        grad = torch.randn(n, generator=g)
+        gd = grad.to(cuda_device)
+        _lib.check(_lib.load().xattn_adam_step(_ptr(p), _ptr(gd), _ptr(m), _ptr(v), n, 1e-3, 0.9, 0.999, 1e-8, 1e-2, step,
+                                               int(decoupled), _stream_ptr(cuda_device)))
+        pt.grad = grad.clone()
+        opt.step()
+        po, mo, vo = xattn_oracle.adam_step(po, grad.numpy(), mo, vo, step=step, lr=1e-3, weight_decay=1e-2, decoupled=decoupled)
+    np.testing.assert_allclose(p.cpu().numpy(), po, atol=2e-6, rtol=0)
+    np.testing.assert_allclose(p.cpu().numpy(), pt.detach().numpy(), atol=2e-6, rtol=0)
+
+
+@pytest.mark.parametrize("head,prior", [("concat", True), ("gated", False)])
+def test_stage1_step_matches_reference_adam_step(cuda_device, head, prior):
+    """Fused step (fwd + CE + bwd + Adam, eval-mode dropouts) against the reference's post-step parameters."""
+    from multimodalemotionrecognition_b200.training import Stage1Trainer
+
+    blob = load_npz(f"xattn_tiny_{_tag(head, prior)}.npz")
+    m = tiny_head(blob, head, prior).to(cuda_device)
+    tr = Stage1Trainer(m, lr=1e-3, weight_decay=1e-4, decoupled=False)
+    loss = tr.step(torch.from_numpy(blob["xv"]).to(cuda_device), torch.from_numpy(blob["xa"]).to(cuda_device),
+                   torch.from_numpy(blob["labels"]).to(cuda_device), training=False)
+    assert abs(float(loss) - float(blob["loss"])) < 1e-5
+    sd = m.state_dict()
+    for k, v in blob.items():
+        if k.startswith("a:") and ("g:" + k[2:]) in blob:
+            np.testing.assert_allclose(sd[k[2:]].cpu().numpy(), v, atol=3e-6, rtol=0, err_msg=k)
+    # audio_time_conv receives no gradient -> untouched (no weight decay either), as in torch
+    np.testing.assert_array_equal(sd["audio_time_conv.weight"].cpu().numpy(), blob["w:audio_time_conv.weight"])
+
+
+def test_training_mode_dropout_statistics(cuda_device):
+    """Training-mode RNG cannot match torch bit-for-bit; check determinism under a fixed seed/offset,
+    that masks differ between steps, and that the expectation stays close to the eval output."""
+    m = make_head("concat", True, seed=2).to(cuda_device)
+    xv, xa, _ = config1_inputs()
+    xv, xa = xv.to(cuda_device).repeat(64, 1, 1), xa.to(cuda_device).repeat(64, 1, 1)
+    m.eval()
+    with torch.no_grad():
+        ref = m(xv, xa)
+    m.train()
+    outs = []
+    with torch.no_grad():
+        for _ in range(3):
+            logits, _ = m._launch_forward(xv, xa, save=False, training=True)
+            outs.append(logits)
+    assert not torch.equal(outs[0], outs[1])
+    assert torch.isfinite(outs[0]).all()
+    # same clip repeated 64x with independent masks: the mean over repeats approaches the eval logits
+    mean_train = torch.stack(outs).mean(0).view(64, 8, 8).mean(0)
+    assert (mean_train - ref[:8]).abs().max() < 0.1
+    m._rng_offset = 0
+    a, _ = m._launch_forward(xv, xa, save=False, training=True)
+    m._rng_offset = 0
+    b, _ = m._launch_forward(xv, xa, save=False, training=True)
+    assert torch.equal(a, b)
+
+
+def test_fusion_model_drop_in_with_stub_backbones(cuda_device):
+    """FusionModel keeps the reference's forward(video, audio) contract (fusion.py:356-411)."""
+    from multimodalemotionrecognition_b200 import FusionModel
+
+    class StubVideo(torch.nn.Module):
+        embedding_dim = 512
+
+        def __init__(self):
+            super().__init__()
+            self.backbone = torch.nn.Identity()
+
+    class StubAudio(torch.nn.Module):
+        sequence_dim = 768
+        embedding_dim = 768
+        called = False
+
+        def encode_sequence(self, x):
+            self.called = True
+            return x
+
+    torch.manual_seed(0)
+    audio = StubAudio()
+    fm = FusionModel(audio, StubVideo(), 8, mode="xattn", xattn_head="concat", d_model=128, num_heads=4, audio_n_mels=768,
+                     xattn_use_emotion_prior=True).to(cuda_device).eval()
+    blob = load_npz("xattn_config1.npz")
+    xv, xa, _ = config1_inputs()
+    with torch.no_grad():
+        out = fm(xv.to(cuda_device)[..., None, None], xa.to(cuda_device))
+    assert audio.called
+    assert np.abs(out.cpu().numpy() - blob["concat_prior:logits"]).max() <= FP32_TOL
+    assert fm.pop_alignment_loss() is None
+    assert sorted(k for k in fm.state_dict()) == list(blob["concat_prior:keys"])
+
+
+@pytest.mark.parametrize("mode", ["concat", "gated"])
+def test_flat_heads_match_reference(cuda_device, mode):
+    from multimodalemotionrecognition_b200 import FlatFusionHead
+
+    blob = load_npz(f"flat_tiny_{mode}.npz")
+    m = FlatFusionHead(num_classes=8, video_dim=12, audio_dim=10, common_dim=16, mode=mode, fusion_align_mode="clip",
+                       fusion_align_dim=256)
+    m.load_state_dict({k[2:]: torch.from_numpy(v) for k, v in blob.items() if k.startswith("w:")}, strict=True)
+    m = m.to(cuda_device).eval()
+    with torch.no_grad():
+        out = m(torch.from_numpy(blob["xv"]).to(cuda_device), torch.from_numpy(blob["xa"]).to(cuda_device))
+    np.testing.assert_allclose(out.cpu().numpy(), blob["logits"], atol=1e-5, rtol=0)
+    # config-5 dimensions, seed-0 init identical to the reference (digests), pooled inputs
+    big = load_npz("flat_config5.npz")
+    torch.manual_seed(0)
+    mm = FlatFusionHead(num_classes=8, video_dim=512, audio_dim=768, common_dim=256, mode=mode).to(cuda_device).eval()
+    g = torch.Generator().manual_seed(3)
+    ap = torch.randn(6, 768, generator=g)
+    vp = torch.randn(6, 512, generator=g)
+    with torch.no_grad():
+        out = mm.flat_forward_pooled(ap.to(cuda_device), vp.to(cuda_device))
+    assert np.abs(out.cpu().numpy() - big[f"{mode}:logits"]).max() <= FP32_TOL
+    # bf16 sequence inputs with the fused temporal mean vs the oracle on the same rounded inputs
+    xa = torch.randn(9, 149, 768, generator=g).bfloat16()
+    xv = torch.randn(9, 16, 512, generator=g).bfloat16()
+    with torch.no_grad():
+        out = mm(xv.to(cuda_device), xa.to(cuda_device)).cpu().numpy()
+    sd = {k: v.cpu().numpy() for k, v in mm.state_dict().items()}
+    ref = xattn_oracle.flat_head_forward(sd, xa.float().numpy().mean(1), xv.float().numpy().mean(1), mode=mode)
+    assert np.abs(out - ref).max() <= FP32_TOL
