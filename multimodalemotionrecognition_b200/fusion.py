@@ -297,8 +297,13 @@ class XAttnKernelsMixin:
             packed = self._packed_weights(cfg, flat) if precision == _lib.DTYPE_BF16 else None
             ws = torch.empty(_lib.workspace_bytes(cfg), dtype=torch.uint8, device=dev)
             logits = torch.empty((B, self.num_classes), dtype=torch.float32, device=dev)
-            _lib.check(_lib.load().xattn_forward(C.byref(cfg), _ptr(flat), _ptr(packed), _ptr(video_emb), _ptr(audio_emb),
-                                                 _ptr(logits), _ptr(ws), ws.numel(), _stream_ptr(dev)))
+            if B == 0:   # empty tensors have a NULL data_ptr; the ABI wants non-NULL pointers even when B == 0
+                dummy = torch.empty(16, dtype=torch.uint8, device=dev)
+                pv = pa = pl = _ptr(dummy)
+            else:
+                pv, pa, pl = _ptr(video_emb), _ptr(audio_emb), _ptr(logits)
+            _lib.check(_lib.load().xattn_forward(C.byref(cfg), _ptr(flat), _ptr(packed), pv, pa, pl, _ptr(ws), ws.numel(),
+                                                 _stream_ptr(dev)))
         return logits, (cfg, video_emb, audio_emb, ws)
 
     def _launch_backward(self, state, dlogits: torch.Tensor, grads: Optional[torch.Tensor] = None) -> torch.Tensor:
