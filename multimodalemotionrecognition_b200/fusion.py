@@ -277,7 +277,8 @@ class XAttnKernelsMixin:
             return _lib.DTYPE_BF16
         return _lib.DTYPE_BF16 if io_dtype == _lib.DTYPE_BF16 else _lib.DTYPE_F32
 
-    def _launch_forward(self, video_emb: torch.Tensor, audio_emb: torch.Tensor, save: bool, training: Optional[bool] = None):
+    def _launch_forward(self, video_emb: torch.Tensor, audio_emb: torch.Tensor, save: bool, training: Optional[bool] = None,
+                        out: Optional[torch.Tensor] = None):
         self._check_inputs(video_emb, audio_emb)
         video_emb = video_emb.contiguous()
         audio_emb = audio_emb.contiguous()
@@ -296,7 +297,7 @@ class XAttnKernelsMixin:
             cfg = self._make_cfg(B, T, Ta, io, precision, training, save)
             packed = self._packed_weights(cfg, flat) if precision == _lib.DTYPE_BF16 else None
             ws = torch.empty(_lib.workspace_bytes(cfg), dtype=torch.uint8, device=dev)
-            logits = torch.empty((B, self.num_classes), dtype=torch.float32, device=dev)
+            logits = out if out is not None else torch.empty((B, self.num_classes), dtype=torch.float32, device=dev)
             if B == 0:   # empty tensors have a NULL data_ptr; the ABI wants non-NULL pointers even when B == 0
                 dummy = torch.empty(16, dtype=torch.uint8, device=dev)
                 pv = pa = pl = _ptr(dummy)
@@ -316,6 +317,61 @@ class XAttnKernelsMixin:
             _lib.check(_lib.load().xattn_backward(C.byref(cfg), _ptr(flat), _ptr(video_emb), _ptr(audio_emb), _ptr(dlogits),
                                                   _ptr(grads), _ptr(ws), ws.numel(), _stream_ptr(dev)))
         return grads
+
+    @torch.no_grad()
+    def predict_host(self, video_host: torch.Tensor, audio_host: torch.Tensor, chunk: int = 1024,
+                     probs: bool = False) -> torch.Tensor:
+        """Batch path with HOST buffers, mirroring ``TorchModelRunner.predict_probs`` (``optimized_runtime.py:99-108``:
+        ``.to(device)`` -> model -> ``softmax`` -> ``.cpu()``) and the worker's ``torch.stack(...).to(device)``
+        (``inference_worker.py:131-134``).  The host batch (pinned memory for full PCIe rate) is cut into ``chunk``-clip
+        pieces that are copied on a side stream into two device staging slots while the previous piece is computed;
+        returns host logits (or probabilities) ``[B,C]`` after synchronising on the final device->host copy."""
+        if video_host.is_cuda or audio_host.is_cuda:
+            raise ValueError("predict_host takes host tensors; call forward() for device tensors")
+        if video_host.ndim != 3 or audio_host.ndim != 3 or video_host.shape[0] != audio_host.shape[0]:
+            raise ValueError("expected video [B,T,Dv] and audio [B,Ta,Da] host tensors with the same B")
+        if video_host.dtype != audio_host.dtype:
+            raise ValueError("video_emb and audio_emb must share a dtype")
+        dev = next(p for p in self._xattn_named_params() if p is not None).device
+        if dev.type != "cuda":
+            raise RuntimeError("the B200 xattn fusion head has no CPU path: move the module to an sm_100 device")
+        B, T_, Dv = video_host.shape
+        Ta_, Da = audio_host.shape[1], audio_host.shape[2]
+        key = (dev, chunk, T_, Dv, Ta_, Da, video_host.dtype)
+        pipe = getattr(self, "_host_pipe", None)
+        if pipe is None or pipe["key"] != key:
+            pipe = {"key": key, "stream": torch.cuda.Stream(dev),
+                    "v": [torch.empty((chunk, T_, Dv), dtype=video_host.dtype, device=dev) for _ in range(2)],
+                    "a": [torch.empty((chunk, Ta_, Da), dtype=audio_host.dtype, device=dev) for _ in range(2)],
+                    "ready": [torch.cuda.Event() for _ in range(2)], "done": [torch.cuda.Event() for _ in range(2)],
+                    "out": None}
+            self._host_pipe = pipe
+        if pipe["out"] is None or pipe["out"].shape[0] < B:
+            pipe["out"] = torch.empty((max(B, 1), self.num_classes), dtype=torch.float32).pin_memory()
+        with torch.cuda.device(dev):
+            cur = torch.cuda.current_stream(dev)
+            side = pipe["stream"]
+            side.wait_stream(cur)
+            logits = torch.empty((B, self.num_classes), dtype=torch.float32, device=dev)
+            for i, s in enumerate(range(0, B, chunk)):
+                e = min(B, s + chunk)
+                slot = i & 1
+                with torch.cuda.stream(side):
+                    if i >= 2:
+                        side.wait_event(pipe["done"][slot])
+                    pipe["v"][slot][: e - s].copy_(video_host[s:e], non_blocking=True)
+                    pipe["a"][slot][: e - s].copy_(audio_host[s:e], non_blocking=True)
+                    pipe["ready"][slot].record(side)
+                cur.wait_event(pipe["ready"][slot])
+                self._launch_forward(pipe["v"][slot][: e - s], pipe["a"][slot][: e - s], save=False, training=False,
+                                     out=logits[s:e])
+                pipe["done"][slot].record(cur)
+            if probs:
+                logits = torch.softmax(logits, dim=1)
+            host = pipe["out"][:B]
+            host.copy_(logits, non_blocking=True)
+            cur.synchronize()
+        return host
 
     def xattn_forward_embeddings(self, video_emb: torch.Tensor, audio_emb: torch.Tensor) -> torch.Tensor:
         """logits from backbone embeddings; differentiable w.r.t. the fusion parameters (not the embeddings)."""
