@@ -26,7 +26,7 @@
 extern "C" {
 #endif
 
-#define XATTN_ABI_VERSION 3
+#define XATTN_ABI_VERSION 4
 
 #if defined(__GNUC__)
 #define XATTN_API __attribute__((visibility("default")))
@@ -206,6 +206,15 @@ XATTN_API int flat_head_workspace_bytes(const flat_head_config* cfg, int64_t* by
  * fusion.py:413-435 (+ :137-139).  Eval mode (ModalityDropout / Dropout identity). */
 XATTN_API int flat_head_forward(const flat_head_config* cfg, const float* params, const void* video_emb, const void* audio_emb,
                       float* logits, void* workspace, int64_t workspace_bytes, void* stream);
+
+/* ---- diagnostics ---------------------------------------------------------------------------------- */
+/* Kernel launches issued by this library since process start (bench.py's gpu_launches evidence). */
+XATTN_API unsigned long long xattn_launch_count(void);
+/* The tcgen05/TMA projection GEMM on its own: Y[M,N] = X[M,K]·W[N,K]^T + bias (X, W bf16; Y bf16 or fp32 with row
+ * pitch out_pitch in elements; N % 128 == 0, K % 64 == 0).  This is the kernel behind v_in_proj (fusion.py:372) and
+ * a_in_proj∘audio_seq_proj (:378, :386) in xattn_forward(precision = BF16); exported so tests can pin it in isolation. */
+XATTN_API int xattn_debug_gemm_tc(const void* X, const void* W, const float* bias, void* Y, int32_t out_bf16, int64_t out_pitch,
+                        int32_t M, int32_t N, int32_t K, void* stream);
 
 #ifdef __cplusplus
 }

@@ -1,6 +1,7 @@
 // extern "C" entry points declared in include/xattn_fusion.h.
 #include "kernels_bf16.cuh"
 #include "kernels_f32.cuh"
+#include "gemm_tc.cuh"
 
 namespace xf {
 int ce_loss_fwd_bwd(const float* logits, const int64_t* labels, int B, int C, float label_smoothing, float grad_scale,
@@ -115,4 +116,12 @@ extern "C" XATTN_API int xattn_adam_step(float* params, const float* grads, floa
     XF_FAIL(XATTN_ERR_ALIGN, "pointers must be 16-byte aligned");
   XF_TRY(check_device_sm100());
   return adam_step(params, grads, exp_avg, exp_avg_sq, n, lr, beta1, beta2, eps, weight_decay, step, decoupled, (cudaStream_t)stream);
+}
+
+extern "C" XATTN_API int xattn_debug_gemm_tc(const void* X, const void* W, const float* bias, void* Y, int32_t out_bf16, int64_t out_pitch,
+                                   int32_t M, int32_t N, int32_t K, void* stream) {
+  if (!X || !W || !bias || !Y) XF_FAIL(XATTN_ERR_NULL, "NULL pointer argument");
+  if (misaligned(X) || misaligned(W) || misaligned(Y)) XF_FAIL(XATTN_ERR_ALIGN, "pointers must be 16-byte aligned");
+  XF_TRY(check_device_sm100());
+  return gemm_tc_bf16((cudaStream_t)stream, X, W, bias, Y, out_bf16 != 0, out_pitch, M, N, K);
 }

@@ -28,7 +28,7 @@ def test_library_exports_every_declared_symbol():
     for name in declared:
         assert hasattr(lib, name), f"{name} declared in include/xattn_fusion.h but not exported"
         assert name in _lib.EXPORTED_SYMBOLS, f"{name} has no ctypes prototype"
-    assert lib.xattn_abi_version() == 3
+    assert lib.xattn_abi_version() == _lib.ABI_VERSION
 
 
 def test_param_layout_matches_state_dict_shapes():
