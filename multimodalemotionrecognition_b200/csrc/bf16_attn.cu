@@ -1,0 +1,464 @@
+// The two fused per-clip attention kernels of the bf16 path.  One CTA owns one clip; the clip's audio tokens a0
+// [Ta,128] (bf16) are pulled into shared memory once by a bulk async copy (cp.async.bulk + mbarrier) and serve as BOTH
+// the key and the value operand, because the K/V projections are folded into the small per-clip operands Qt / Kt / Vt.
+// The whole score tile lives in registers: bias add (tanh of the emotion-prior token scores, fusion.py:175-176),
+// warp-shuffle softmax, and the P·V product run in one pass with bf16 mma.sync (fp32 accumulate, fp32 softmax/LayerNorm).
+//   v2a_attn_kernel : video queries audio (fusion.py:394) + the emotion prior network (:178-181)
+//   a2v_attn_kernel : audio queries the updated video (:398), residual + LayerNorm (:399), temporal mean (:402)
+#include "bf16_layout.cuh"
+#include "frag.cuh"
+
+namespace xf {
+
+namespace {
+
+constexpr int kA0Bytes = BTAP * BEP * 2;   // 43,520
+constexpr int kOpBytes = 64 * BEP * 2;     // 17,408  (Qt / Kt / Vt)
+
+struct V2AArgs {
+  const __nv_bfloat16* a0;   // [B*Ta, BEP]
+  const __nv_bfloat16* qt;   // [B,64,BEP]
+  const float *meanv, *tqv;  // [B,E], [B,16]
+  const float *pw0, *pb0, *pw3, *pb3;   // prior_net.0 / .3
+  const float* wh[4];        // v_query, a_key, a_query, v_key bias heads: weight [E+P]
+  const float* bh[4];
+  const float* bias_scale;
+  __nv_bfloat16* u;          // [B,64,E]
+  float *tqa, *pc;           // [B,BTAP], [B,4]
+  int B, Ta, T, P, Hd, use_prior;
+};
+
+__global__ void __launch_bounds__(128, 3) v2a_attn_kernel(V2AArgs a) {
+  extern __shared__ __align__(128) uint8_t sm[];
+  __nv_bfloat16* a0s = reinterpret_cast<__nv_bfloat16*>(sm);
+  __nv_bfloat16* qts = reinterpret_cast<__nv_bfloat16*>(sm + kA0Bytes);
+  __nv_bfloat16* wsc = reinterpret_cast<__nv_bfloat16*>(sm + kA0Bytes + kOpBytes);   // [8][BEP]: rows 0,1 = w_ak, w_aq
+  float* fsm = reinterpret_cast<float*>(sm + kA0Bytes + kOpBytes + 8 * BEP * 2);
+  float* ka_s = fsm;             // [160] raw a_key token scores
+  float* pooled0 = ka_s + BTAP;  // [256]
+  float* hid = pooled0 + 2 * BE; // [128]
+  float* prior = hid + 128;      // [32]
+  float* pc_s = prior + 32;      // [4]
+  float* qv_s = pc_s + 4;        // [16]
+  uint64_t* bar = reinterpret_cast<uint64_t*>(qv_s + 16);
+  const int c = blockIdx.x, tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, g = lane >> 2, t = lane & 3;
+  const int Ta = a.Ta;
+  if (tid == 0) {
+    tc::mbar_init(bar, 1);
+    tc::fence_barrier_init();
+  }
+  __syncthreads();
+  if (tid == 0) {
+    const uint32_t nb = (uint32_t)Ta * BEP * 2;
+    tc::mbar_expect_tx(bar, nb + kOpBytes);
+    tc::bulk_load_1d(a0s, a.a0 + (int64_t)c * Ta * BEP, nb, bar);
+    tc::bulk_load_1d(qts, a.qt + (int64_t)c * 64 * BEP, kOpBytes, bar);
+  }
+  {   // zero the padding token rows and build the 8 x 128 score-weight tile while the copy is in flight
+    uint4* z = reinterpret_cast<uint4*>(a0s + Ta * BEP);
+    const int nz = (BTAP - Ta) * BEP * 2 / 16;
+    for (int i = tid; i < nz; i += blockDim.x) z[i] = make_uint4(0, 0, 0, 0);
+    for (int i = tid; i < 8 * BEP; i += blockDim.x) {
+      const int r = i / BEP, e = i - r * BEP;
+      float w = 0.f;
+      if (a.use_prior && r < 2 && e < BE) w = a.wh[r + 1][e];
+      wsc[i] = __float2bfloat16(w);
+    }
+    if (a.use_prior) {
+      for (int i = tid; i < BE; i += blockDim.x) pooled0[i] = a.meanv[(int64_t)c * BE + i];
+      if (tid < 16) qv_s[tid] = a.tqv[(int64_t)c * 16 + tid];
+    }
+  }
+  __syncthreads();
+  tc::mbar_wait(bar, 0);
+  const uint32_t a0b = tc::smem_u32(a0s), qtb = tc::smem_u32(qts);
+
+  if (a.use_prior) {
+    // token scores w_ak·a0_j, w_aq·a0_j as a 160 x 8 product on the tensor cores (columns 0,1 used)
+    for (int mt = warp; mt < BTAP / 16; mt += 4) {
+      float d[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+      for (int ks = 0; ks < 8; ks += 2) {
+        uint32_t x0[4], x1[4], b[4];
+        fr::ldA(a0b, 16 * mt, ks, lane, x0);
+        fr::ldA(a0b, 16 * mt, ks + 1, lane, x1);
+        fr::ldB_nk(tc::smem_u32(wsc), 0, ks, lane, b);
+        tc::mma_bf16(d, x0, b[0], b[1]);
+        tc::mma_bf16(d, x1, b[2], b[3]);
+      }
+      if (t == 0) {
+        const int j = 16 * mt + g;
+        ka_s[j] = d[0]; ka_s[j + 8] = d[2];
+        a.tqa[(int64_t)c * BTAP + j] = d[1];
+        a.tqa[(int64_t)c * BTAP + j + 8] = d[3];
+      }
+    }
+    {   // mean_t a0  (fusion.py:180)
+      float s = 0.f;
+      for (int j = 0; j < Ta; ++j) s += __bfloat162float(a0s[j * BEP + tid]);
+      pooled0[BE + tid] = s / (float)Ta;
+    }
+    __syncthreads();
+    // prior_net: Linear(2E -> Hd), ReLU, (Dropout: eval identity), Linear(Hd -> P)   (fusion.py:158-163)
+    for (int uo = warp; uo < a.Hd; uo += 4) {
+      const float* w = a.pw0 + (int64_t)uo * 2 * BE;
+      float s = 0.f;
+#pragma unroll
+      for (int k = 0; k < 2 * BE / 32; ++k) s = fmaf(__ldg(w + lane + 32 * k), pooled0[lane + 32 * k], s);
+      s = warp_sum(s);
+      if (lane == 0) hid[uo] = fmaxf(s + a.pb0[uo], 0.f);
+    }
+    __syncthreads();
+    for (int p = warp; p < a.P; p += 4) {
+      const float* w = a.pw3 + (int64_t)p * a.Hd;
+      float s = 0.f;
+      for (int k = lane; k < a.Hd; k += 32) s = fmaf(__ldg(w + k), hid[k], s);
+      s = warp_sum(s);
+      if (lane == 0) prior[p] = s + a.pb3[p];
+    }
+    __syncthreads();
+    if (tid < 4) {   // prior part + bias of the four Linear(E+P -> 1) heads (fusion.py:171-174 decomposed)
+      const float* w = a.wh[tid] + BE;
+      float s = a.bh[tid][0];
+      for (int p = 0; p < a.P; ++p) s = fmaf(w[p], prior[p], s);
+      pc_s[tid] = s;
+      a.pc[(int64_t)c * 4 + tid] = s;
+    }
+    __syncthreads();
+  }
+
+  // ---- scores of head `warp`: S[i, j] = Qt_h[i,:]·a0[j,:]  (+ bias), i < 16, j < 160 ----
+  const int h = warp;
+  uint32_t pa[BTAP / 16][4];   // softmax numerators as A fragments (bf16), filled below
+  float inv0, inv1;
+  {
+    float s[BTAP / 8][4];
+    uint32_t aq[8][4];
+#pragma unroll
+    for (int ks = 0; ks < 8; ++ks) fr::ldA(qtb, 16 * h, ks, lane, aq[ks]);
+#pragma unroll
+    for (int nt = 0; nt < BTAP / 8; ++nt) {
+      s[nt][0] = s[nt][1] = s[nt][2] = s[nt][3] = 0.f;
+#pragma unroll
+      for (int ks = 0; ks < 8; ks += 2) {
+        uint32_t b[4];
+        fr::ldB_nk(a0b, nt, ks, lane, b);
+        tc::mma_bf16(s[nt], aq[ks], b[0], b[1]);
+        tc::mma_bf16(s[nt], aq[ks + 1], b[2], b[3]);
+      }
+    }
+    float m0 = -INFINITY, m1 = -INFINITY;
+    const float bsc = a.use_prior ? a.bias_scale[0] : 0.f;
+    const float q0 = a.use_prior ? qv_s[g] + pc_s[0] : 0.f, q1 = a.use_prior ? qv_s[g + 8] + pc_s[0] : 0.f;
+    const float kc = a.use_prior ? pc_s[1] : 0.f;
+#pragma unroll
+    for (int nt = 0; nt < BTAP / 8; ++nt) {
+#pragma unroll
+      for (int e = 0; e < 2; ++e) {
+        const int j = nt * 8 + 2 * t + e;
+        if (j < Ta) {
+          if (a.use_prior) {
+            const float kj = ka_s[j] + kc;
+            s[nt][e] += tc::tanh_fast(q0 + kj) * bsc;
+            s[nt][2 + e] += tc::tanh_fast(q1 + kj) * bsc;
+          }
+        } else {
+          s[nt][e] = -INFINITY;
+          s[nt][2 + e] = -INFINITY;
+        }
+        m0 = fmaxf(m0, s[nt][e]);
+        m1 = fmaxf(m1, s[nt][2 + e]);
+      }
+    }
+    m0 = fmaxf(m0, __shfl_xor_sync(0xffffffffu, m0, 1)); m0 = fmaxf(m0, __shfl_xor_sync(0xffffffffu, m0, 2));
+    m1 = fmaxf(m1, __shfl_xor_sync(0xffffffffu, m1, 1)); m1 = fmaxf(m1, __shfl_xor_sync(0xffffffffu, m1, 2));
+    float l0 = 0.f, l1 = 0.f;
+#pragma unroll
+    for (int nt = 0; nt < BTAP / 8; ++nt) {
+      s[nt][0] = __expf(s[nt][0] - m0); s[nt][1] = __expf(s[nt][1] - m0);
+      s[nt][2] = __expf(s[nt][2] - m1); s[nt][3] = __expf(s[nt][3] - m1);
+      l0 += s[nt][0] + s[nt][1];
+      l1 += s[nt][2] + s[nt][3];
+    }
+    l0 += __shfl_xor_sync(0xffffffffu, l0, 1); l0 += __shfl_xor_sync(0xffffffffu, l0, 2);
+    l1 += __shfl_xor_sync(0xffffffffu, l1, 1); l1 += __shfl_xor_sync(0xffffffffu, l1, 2);
+    inv0 = 1.f / l0;
+    inv1 = 1.f / l1;
+#pragma unroll
+    for (int kk = 0; kk < BTAP / 16; ++kk) fr::c2a(s[2 * kk], s[2 * kk + 1], pa[kk]);
+  }
+  // ---- U_h = softmax(S_h) · a0   [16,128] ----
+  float o[16][4];
+#pragma unroll
+  for (int nt = 0; nt < 16; ++nt) o[nt][0] = o[nt][1] = o[nt][2] = o[nt][3] = 0.f;
+#pragma unroll
+  for (int kk = 0; kk < BTAP / 16; ++kk) {
+#pragma unroll
+    for (int nt2 = 0; nt2 < 8; ++nt2) {
+      uint32_t b[4];
+      fr::ldB_kn(a0b, 16 * kk, nt2, lane, b);
+      tc::mma_bf16(o[2 * nt2], pa[kk], b[0], b[1]);
+      tc::mma_bf16(o[2 * nt2 + 1], pa[kk], b[2], b[3]);
+    }
+  }
+  __nv_bfloat16* up = a.u + ((int64_t)c * 64 + h * 16 + g) * BE + 2 * t;
+#pragma unroll
+  for (int nt = 0; nt < 16; ++nt) {
+    *reinterpret_cast<uint32_t*>(up + nt * 8) = tc::pack_bf16(o[nt][0] * inv0, o[nt][1] * inv0);
+    *reinterpret_cast<uint32_t*>(up + nt * 8 + 8 * BE) = tc::pack_bf16(o[nt][2] * inv1, o[nt][3] * inv1);
+  }
+}
+
+struct A2VArgs {
+  const __nv_bfloat16 *a0, *kt, *vt;   // [B*Ta,BEP], [B,64,BEP] x2
+  const float *tqa, *tkv, *pc, *cv;    // [B,BTAP], [B,16], [B,4], [B,64]
+  const float *bo2, *gam, *bet, *bias_scale;
+  float* pooled;                       // [B,2E] (second E = pooled_a)
+  int B, Ta, T, use_prior;
+};
+
+__global__ void __launch_bounds__(160, 2) a2v_attn_kernel(A2VArgs a) {
+  extern __shared__ __align__(128) uint8_t sm[];
+  __nv_bfloat16* a0s = reinterpret_cast<__nv_bfloat16*>(sm);
+  __nv_bfloat16* kts = reinterpret_cast<__nv_bfloat16*>(sm + kA0Bytes);
+  __nv_bfloat16* vts = reinterpret_cast<__nv_bfloat16*>(sm + kA0Bytes + kOpBytes);
+  float* fsm = reinterpret_cast<float*>(sm + kA0Bytes + 2 * kOpBytes);
+  float* qa_s = fsm;            // [160] a_query token scores + prior part
+  float* kv_s = qa_s + BTAP;    // [16]  v_key token scores + prior part
+  float* cv_s = kv_s + 16;      // [64]  scale * K2_h[i]·bq2_h
+  float* bo_s = cv_s + 64;      // [128]
+  float* ga_s = bo_s + BE;      // [128]
+  float* be_s = ga_s + BE;      // [128]
+  float* pool_s = be_s + BE;    // [128]
+  uint64_t* bar = reinterpret_cast<uint64_t*>(pool_s + BE);
+  const int c = blockIdx.x, tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, g = lane >> 2, t = lane & 3;
+  const int Ta = a.Ta, T = a.T;
+  if (tid == 0) {
+    tc::mbar_init(bar, 1);
+    tc::fence_barrier_init();
+  }
+  __syncthreads();
+  if (tid == 0) {
+    const uint32_t nb = (uint32_t)Ta * BEP * 2;
+    tc::mbar_expect_tx(bar, nb + 2 * kOpBytes);
+    tc::bulk_load_1d(a0s, a.a0 + (int64_t)c * Ta * BEP, nb, bar);
+    tc::bulk_load_1d(kts, a.kt + (int64_t)c * 64 * BEP, kOpBytes, bar);
+    tc::bulk_load_1d(vts, a.vt + (int64_t)c * 64 * BEP, kOpBytes, bar);
+  }
+  {
+    uint4* z = reinterpret_cast<uint4*>(a0s + Ta * BEP);
+    const int nz = (BTAP - Ta) * BEP * 2 / 16;
+    for (int i = tid; i < nz; i += blockDim.x) z[i] = make_uint4(0, 0, 0, 0);
+    const float pq = a.use_prior ? a.pc[(int64_t)c * 4 + 2] : 0.f, pk = a.use_prior ? a.pc[(int64_t)c * 4 + 3] : 0.f;
+    for (int i = tid; i < BTAP; i += blockDim.x) qa_s[i] = (a.use_prior && i < Ta) ? a.tqa[(int64_t)c * BTAP + i] + pq : 0.f;
+    if (tid < 16) kv_s[tid] = a.use_prior ? a.tkv[(int64_t)c * 16 + tid] + pk : 0.f;
+    if (tid < 64) cv_s[tid] = a.cv[(int64_t)c * 64 + tid];
+    for (int i = tid; i < BE; i += blockDim.x) {
+      bo_s[i] = a.bo2[i]; ga_s[i] = a.gam[i]; be_s[i] = a.bet[i]; pool_s[i] = 0.f;
+    }
+  }
+  __syncthreads();
+  tc::mbar_wait(bar, 0);
+  const uint32_t a0b = tc::smem_u32(a0s), ktb = tc::smem_u32(kts), vtb = tc::smem_u32(vts);
+  const float bsc = a.use_prior ? a.bias_scale[0] : 0.f;
+  float pool[16][2];
+#pragma unroll
+  for (int nt = 0; nt < 16; ++nt) pool[nt][0] = pool[nt][1] = 0.f;
+
+#pragma unroll 1
+  for (int mt = 2 * warp; mt < 2 * warp + 2; ++mt) {
+    const int j0 = 16 * mt + g, j1 = j0 + 8;
+    // ---- S[j, (h,i)] = a0[j,:]·Kt[(h,i),:] + c_hi + bias ----
+    uint32_t pf[4][4];
+    {
+      float s[8][4];
+#pragma unroll
+      for (int nt = 0; nt < 8; ++nt) s[nt][0] = s[nt][1] = s[nt][2] = s[nt][3] = 0.f;
+#pragma unroll
+      for (int ks = 0; ks < 8; ks += 2) {
+        uint32_t x0[4], x1[4];
+        fr::ldA(a0b, 16 * mt, ks, lane, x0);
+        fr::ldA(a0b, 16 * mt, ks + 1, lane, x1);
+#pragma unroll
+        for (int nt = 0; nt < 8; ++nt) {
+          uint32_t b[4];
+          fr::ldB_nk(ktb, nt, ks, lane, b);
+          tc::mma_bf16(s[nt], x0, b[0], b[1]);
+          tc::mma_bf16(s[nt], x1, b[2], b[3]);
+        }
+      }
+      const float qa0 = qa_s[j0], qa1 = qa_s[j1];
+#pragma unroll
+      for (int hh = 0; hh < BH; ++hh) {
+        float m0 = -INFINITY, m1 = -INFINITY;
+#pragma unroll
+        for (int n2 = 0; n2 < 2; ++n2) {
+          const int nt = 2 * hh + n2;
+#pragma unroll
+          for (int e = 0; e < 2; ++e) {
+            const int i = n2 * 8 + 2 * t + e;
+            if (i < T) {
+              const float cc = cv_s[hh * 16 + i];
+              float b0 = 0.f, b1 = 0.f;
+              if (a.use_prior) {
+                b0 = tc::tanh_fast(qa0 + kv_s[i]) * bsc;
+                b1 = tc::tanh_fast(qa1 + kv_s[i]) * bsc;
+              }
+              s[nt][e] += cc + b0;
+              s[nt][2 + e] += cc + b1;
+            } else {
+              s[nt][e] = -INFINITY;
+              s[nt][2 + e] = -INFINITY;
+            }
+            m0 = fmaxf(m0, s[nt][e]);
+            m1 = fmaxf(m1, s[nt][2 + e]);
+          }
+        }
+        m0 = fmaxf(m0, __shfl_xor_sync(0xffffffffu, m0, 1)); m0 = fmaxf(m0, __shfl_xor_sync(0xffffffffu, m0, 2));
+        m1 = fmaxf(m1, __shfl_xor_sync(0xffffffffu, m1, 1)); m1 = fmaxf(m1, __shfl_xor_sync(0xffffffffu, m1, 2));
+        float l0 = 0.f, l1 = 0.f;
+#pragma unroll
+        for (int n2 = 0; n2 < 2; ++n2) {
+          const int nt = 2 * hh + n2;
+          s[nt][0] = __expf(s[nt][0] - m0); s[nt][1] = __expf(s[nt][1] - m0);
+          s[nt][2] = __expf(s[nt][2] - m1); s[nt][3] = __expf(s[nt][3] - m1);
+          l0 += s[nt][0] + s[nt][1];
+          l1 += s[nt][2] + s[nt][3];
+        }
+        l0 += __shfl_xor_sync(0xffffffffu, l0, 1); l0 += __shfl_xor_sync(0xffffffffu, l0, 2);
+        l1 += __shfl_xor_sync(0xffffffffu, l1, 1); l1 += __shfl_xor_sync(0xffffffffu, l1, 2);
+        const float i0 = 1.f / l0, i1 = 1.f / l1;
+#pragma unroll
+        for (int n2 = 0; n2 < 2; ++n2) {
+          const int nt = 2 * hh + n2;
+          s[nt][0] *= i0; s[nt][1] *= i0; s[nt][2] *= i1; s[nt][3] *= i1;
+        }
+        fr::c2a(s[2 * hh], s[2 * hh + 1], pf[hh]);
+      }
+    }
+    // ---- out = P · Vt  (out_proj already folded into Vt) ----
+    float o[16][4];
+#pragma unroll
+    for (int nt = 0; nt < 16; ++nt) o[nt][0] = o[nt][1] = o[nt][2] = o[nt][3] = 0.f;
+#pragma unroll
+    for (int kk = 0; kk < 4; ++kk) {
+#pragma unroll
+      for (int nt2 = 0; nt2 < 8; ++nt2) {
+        uint32_t b[4];
+        fr::ldB_kn(vtb, 16 * kk, nt2, lane, b);
+        tc::mma_bf16(o[2 * nt2], pf[kk], b[0], b[1]);
+        tc::mma_bf16(o[2 * nt2 + 1], pf[kk], b[2], b[3]);
+      }
+    }
+    // ---- a1 = LayerNorm(a0 + out + bo2) (fusion.py:399), accumulated into the temporal mean (:402) ----
+    float s0 = 0.f, s1 = 0.f;
+#pragma unroll
+    for (int nt = 0; nt < 16; ++nt) {
+      const int col = nt * 8 + 2 * t;
+      const __nv_bfloat162 r0 = *reinterpret_cast<const __nv_bfloat162*>(a0s + j0 * BEP + col);
+      const __nv_bfloat162 r1 = *reinterpret_cast<const __nv_bfloat162*>(a0s + j1 * BEP + col);
+      o[nt][0] += bo_s[col] + __low2float(r0);
+      o[nt][1] += bo_s[col + 1] + __high2float(r0);
+      o[nt][2] += bo_s[col] + __low2float(r1);
+      o[nt][3] += bo_s[col + 1] + __high2float(r1);
+      s0 += o[nt][0] + o[nt][1];
+      s1 += o[nt][2] + o[nt][3];
+    }
+    s0 += __shfl_xor_sync(0xffffffffu, s0, 1); s0 += __shfl_xor_sync(0xffffffffu, s0, 2);
+    s1 += __shfl_xor_sync(0xffffffffu, s1, 1); s1 += __shfl_xor_sync(0xffffffffu, s1, 2);
+    const float mu0 = s0 * (1.f / BE), mu1 = s1 * (1.f / BE);
+    float q0 = 0.f, q1 = 0.f;
+#pragma unroll
+    for (int nt = 0; nt < 16; ++nt) {
+      float d;
+      d = o[nt][0] - mu0; q0 = fmaf(d, d, q0);
+      d = o[nt][1] - mu0; q0 = fmaf(d, d, q0);
+      d = o[nt][2] - mu1; q1 = fmaf(d, d, q1);
+      d = o[nt][3] - mu1; q1 = fmaf(d, d, q1);
+    }
+    q0 += __shfl_xor_sync(0xffffffffu, q0, 1); q0 += __shfl_xor_sync(0xffffffffu, q0, 2);
+    q1 += __shfl_xor_sync(0xffffffffu, q1, 1); q1 += __shfl_xor_sync(0xffffffffu, q1, 2);
+    const float r0 = (j0 < Ta) ? rsqrtf(q0 * (1.f / BE) + 1e-5f) : 0.f;   // padded token rows contribute nothing
+    const float r1 = (j1 < Ta) ? rsqrtf(q1 * (1.f / BE) + 1e-5f) : 0.f;
+#pragma unroll
+    for (int nt = 0; nt < 16; ++nt) {
+      pool[nt][0] += (o[nt][0] - mu0) * r0 + (o[nt][2] - mu1) * r1;
+      pool[nt][1] += (o[nt][1] - mu0) * r0 + (o[nt][3] - mu1) * r1;
+    }
+  }
+  // pooled_a[e] = gamma[e] * mean_j xhat[j,e] + beta[e]
+#pragma unroll
+  for (int nt = 0; nt < 16; ++nt) {
+    float p0 = pool[nt][0], p1 = pool[nt][1];
+#pragma unroll
+    for (int o2 = 4; o2 <= 16; o2 <<= 1) {
+      p0 += __shfl_xor_sync(0xffffffffu, p0, o2);
+      p1 += __shfl_xor_sync(0xffffffffu, p1, o2);
+    }
+    if (g == 0) {
+      atomicAdd(&pool_s[nt * 8 + 2 * t], p0);
+      atomicAdd(&pool_s[nt * 8 + 2 * t + 1], p1);
+    }
+  }
+  __syncthreads();
+  if (tid < BE) a.pooled[(int64_t)c * 2 * BE + BE + tid] = ga_s[tid] * (pool_s[tid] / (float)Ta) + be_s[tid];
+}
+
+}  // namespace
+
+int launch_v2a_attn(const Bf16Ctx& x) {
+  const xattn_config& c = *x.cfg;
+  auto P = [&](int id) { return x.params + x.pl.off[id]; };
+  V2AArgs a;
+  a.a0 = reinterpret_cast<const __nv_bfloat16*>(x.ws + x.w.a0);
+  a.qt = reinterpret_cast<const __nv_bfloat16*>(x.ws + x.w.qt);
+  a.meanv = reinterpret_cast<const float*>(x.ws + x.w.meanv);
+  a.tqv = reinterpret_cast<const float*>(x.ws + x.w.tqv);
+  a.pw0 = P(XP_PRIOR0_W); a.pb0 = P(XP_PRIOR0_B); a.pw3 = P(XP_PRIOR3_W); a.pb3 = P(XP_PRIOR3_B);
+  a.wh[0] = P(XP_VQ_W); a.bh[0] = P(XP_VQ_B); a.wh[1] = P(XP_AK_W); a.bh[1] = P(XP_AK_B);
+  a.wh[2] = P(XP_AQ_W); a.bh[2] = P(XP_AQ_B); a.wh[3] = P(XP_VK_W); a.bh[3] = P(XP_VK_B);
+  a.bias_scale = P(XP_BIAS_SCALE);
+  a.u = reinterpret_cast<__nv_bfloat16*>(x.ws + x.w.u);
+  a.tqa = reinterpret_cast<float*>(x.ws + x.w.tqa);
+  a.pc = reinterpret_cast<float*>(x.ws + x.w.pc);
+  a.B = c.B; a.Ta = c.Ta; a.T = c.T; a.P = c.prior_dim; a.Hd = c.prior_hidden; a.use_prior = c.use_prior;
+  const int smem = kA0Bytes + kOpBytes + 8 * BEP * 2 + (BTAP + 2 * BE + 128 + 32 + 4 + 16) * 4 + 16;
+  static bool configured = false;
+  if (!configured) {
+    XF_CUDA(cudaFuncSetAttribute(v2a_attn_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    configured = true;
+  }
+  v2a_attn_kernel<<<c.B, 128, smem, x.st>>>(a);
+  count_launch();
+  XF_LAUNCH_CHECK();
+  return XATTN_OK;
+}
+
+int launch_a2v_attn(const Bf16Ctx& x) {
+  const xattn_config& c = *x.cfg;
+  auto P = [&](int id) { return x.params + x.pl.off[id]; };
+  A2VArgs a;
+  a.a0 = reinterpret_cast<const __nv_bfloat16*>(x.ws + x.w.a0);
+  a.kt = reinterpret_cast<const __nv_bfloat16*>(x.ws + x.w.kt);
+  a.vt = reinterpret_cast<const __nv_bfloat16*>(x.ws + x.w.vt);
+  a.tqa = reinterpret_cast<const float*>(x.ws + x.w.tqa);
+  a.tkv = reinterpret_cast<const float*>(x.ws + x.w.tkv);
+  a.pc = reinterpret_cast<const float*>(x.ws + x.w.pc);
+  a.cv = reinterpret_cast<const float*>(x.ws + x.w.cv);
+  a.bo2 = P(XP_A2V_OUT_B); a.gam = P(XP_AN_W); a.bet = P(XP_AN_B);
+  a.bias_scale = P(XP_BIAS_SCALE);
+  a.pooled = reinterpret_cast<float*>(x.ws + x.w.pooled);
+  a.B = c.B; a.Ta = c.Ta; a.T = c.T; a.use_prior = c.use_prior;
+  const int smem = kA0Bytes + 2 * kOpBytes + (BTAP + 16 + 64 + 4 * BE) * 4 + 16;
+  static bool configured = false;
+  if (!configured) {
+    XF_CUDA(cudaFuncSetAttribute(a2v_attn_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    configured = true;
+  }
+  a2v_attn_kernel<<<c.B, 160, smem, x.st>>>(a);
+  count_launch();
+  XF_LAUNCH_CHECK();
+  return XATTN_OK;
+}
+
+}  // namespace xf

@@ -1,0 +1,156 @@
+// Layouts of the bf16 path and xattn_pack_weights: derives the bf16 operand set from the flat fp32 parameters.
+//  * W_fold = a_in_proj.weight · audio_seq_proj.weight, b_fold = a_in_proj.weight · audio_seq_proj.bias + a_in_proj.bias
+//    (fusion.py:378 then :386 are two Linears with nothing in between — SURVEY 3.1 fact 2); folded in fp32, rounded once.
+//  * the eight 128x128 attention matrices (slices of in_proj_weight / out_proj.weight, fusion.py:276-281) as bf16 with
+//    a 136-element row pitch; * head layer 0 transposed for coalesced reads.
+#include "bf16_layout.cuh"
+#include "gemm_simt.cuh"
+#include "kernels_bf16.cuh"
+
+namespace xf {
+
+static inline int64_t al256(int64_t n) { return (n + 255) & ~(int64_t)255; }
+
+int bf16_supported(const xattn_config& c) {
+  if (c.E != BE || c.H != BH) XF_FAIL(XATTN_ERR_SHAPE, "bf16 path is specialised for d_model=128, num_heads=4 (got E=%d H=%d)", c.E, c.H);
+  if (c.T > BTP || c.Ta > BTAP)
+    XF_FAIL(XATTN_ERR_SHAPE, "bf16 path holds the whole score tile on chip: needs T <= 16 and Ta <= 160 (got T=%d Ta=%d)", c.T, c.Ta);
+  if (c.Dv % 64 != 0 || c.Da % 64 != 0) XF_FAIL(XATTN_ERR_SHAPE, "bf16 path needs Dv, Da multiples of 64 (got %d, %d)", c.Dv, c.Da);
+  if (c.io_dtype != XATTN_DTYPE_BF16) XF_FAIL(XATTN_ERR_DTYPE, "bf16 path reads bf16 embeddings (io_dtype must be bf16)");
+  const int HW = c.head_kind == XATTN_HEAD_GATED ? c.E : c.common_dim;
+  if (HW > 256 || c.C > 16) XF_FAIL(XATTN_ERR_SHAPE, "bf16 path head supports hidden width <= 256 and <= 16 classes");
+  if (c.use_prior && (c.prior_hidden > 128 || c.prior_dim > 32))
+    XF_FAIL(XATTN_ERR_SHAPE, "bf16 path supports prior_hidden <= 128, prior_dim <= 32");
+  return XATTN_OK;
+}
+
+void compute_pack_bf16(const xattn_config& c, PackBf16& p) {
+  const int64_t E = c.E;
+  const int64_t HW = c.head_kind == XATTN_HEAD_GATED ? E : c.common_dim;
+  int64_t off = 0;
+  auto take = [&](int64_t bytes) {
+    int64_t o = off;
+    off += al256(bytes);
+    return o;
+  };
+  p.Wv = take(E * c.Dv * 2);
+  p.Wfold = take(E * c.Da * 2);
+  p.bfold = take(E * 4);
+  p.Wq1 = take(E * BEP * 2); p.Wk1 = take(E * BEP * 2); p.Wv1 = take(E * BEP * 2); p.Wo1 = take(E * BEP * 2);
+  p.Wk2 = take(E * BEP * 2); p.Wv2 = take(E * BEP * 2); p.Wq2 = take(E * BEP * 2); p.Wo2 = take(E * BEP * 2);
+  p.W0T = take(2 * E * HW * 4);
+  p.scratch = take(E * c.Da * 4);
+  p.total = off;
+}
+
+void compute_ws_bf16(const xattn_config& c, WsBf16& w) {
+  const int64_t B = c.B, E = c.E;
+  int64_t off = 0;
+  auto take = [&](int64_t bytes) {
+    int64_t o = off;
+    off += al256(bytes);
+    return o;
+  };
+  w.v0 = take(B * c.T * E * 4);
+  w.a0 = take(B * c.Ta * BEP * 2);
+  w.qt = take(B * 64 * BEP * 2);
+  w.meanv = take(B * E * 4);
+  w.tqv = take(B * 16 * 4);
+  w.tkv = take(B * 16 * 4);
+  w.u = take(B * 64 * E * 2);
+  w.tqa = take(B * BTAP * 4);
+  w.pc = take(B * 4 * 4);
+  w.kt = take(B * 64 * BEP * 2);
+  w.vt = take(B * 64 * BEP * 2);
+  w.cv = take(B * 64 * 4);
+  w.pooled = take(B * 2 * E * 4);
+  w.total = off + 256;
+}
+
+int packed_bytes_bf16(const xattn_config& c, int64_t* bytes) {
+  if (c.E != BE || c.H != BH) {   // unsupported configs never reach the bf16 kernels; a token size keeps callers simple
+    *bytes = 256;
+    return XATTN_OK;
+  }
+  PackBf16 p;
+  compute_pack_bf16(c, p);
+  *bytes = p.total;
+  return XATTN_OK;
+}
+
+int workspace_bytes_bf16(const xattn_config& c, int64_t* bytes) {
+  XF_TRY(bf16_supported(c));
+  WsBf16 w;
+  compute_ws_bf16(c, w);
+  *bytes = w.total;
+  return XATTN_OK;
+}
+
+// dst[r, 0..cols) (pitch dpitch, bf16) = src[r, 0..cols) (pitch spitch, fp32); pad columns zeroed.
+__global__ void cvt_rows_bf16_kernel(const float* __restrict__ src, int64_t spitch, __nv_bfloat16* __restrict__ dst,
+                                     int64_t dpitch, int rows, int cols) {
+  const int64_t n = (int64_t)rows * dpitch;
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t r = i / dpitch, cidx = i - r * dpitch;
+    dst[i] = __float2bfloat16(cidx < cols ? src[r * spitch + cidx] : 0.f);
+  }
+}
+// out[e] = W_in[e,:]·b_seq + b_in[e]
+__global__ void fold_bias_kernel(const float* __restrict__ w_in, const float* __restrict__ b_seq, const float* __restrict__ b_in,
+                                 float* __restrict__ out, int E) {
+  const int e = blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= E) return;
+  float s = b_in[e];
+  for (int m = 0; m < E; ++m) s = fmaf(w_in[(int64_t)e * E + m], b_seq[m], s);
+  out[e] = s;
+}
+// dst[k, n] = src[n, k]   (src [N,K] fp32)
+__global__ void transpose_f32_kernel(const float* __restrict__ src, float* __restrict__ dst, int N, int K) {
+  const int64_t total = (int64_t)N * K;
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t k = i / N, n = i - k * N;
+    dst[i] = src[n * K + k];
+  }
+}
+
+int pack_weights_bf16(const xattn_config& c, const float* params, void* packed_v, cudaStream_t st) {
+  if (c.E != BE || c.H != BH) XF_FAIL(XATTN_ERR_SHAPE, "bf16 path is specialised for d_model=128, num_heads=4 (got E=%d H=%d)", c.E, c.H);
+  ParamLayout pl;
+  compute_param_layout(c, pl);
+  PackBf16 pk;
+  compute_pack_bf16(c, pk);
+  uint8_t* packed = reinterpret_cast<uint8_t*>(packed_v);
+  auto P = [&](int id) { return params + pl.off[id]; };
+  auto BF = [&](int64_t off) { return reinterpret_cast<__nv_bfloat16*>(packed + off); };
+  const int E = c.E;
+  auto cvt = [&](const float* src, int64_t spitch, int64_t dst_off, int64_t dpitch, int rows, int cols) {
+    const int64_t n = (int64_t)rows * dpitch;
+    const int blocks = (int)((n + 255) / 256 < 1024 ? (n + 255) / 256 : 1024);
+    cvt_rows_bf16_kernel<<<blocks, 256, 0, st>>>(src, spitch, BF(dst_off), dpitch, rows, cols);
+    count_launch();
+  };
+  cvt(P(XP_V_IN_W), c.Dv, pk.Wv, c.Dv, E, c.Dv);
+  // W_fold[e,k] = sum_m W_in[e,m] W_seq[m,k]   (fp32 SIMT GEMM: A(m,k)=W_in[e*E+m], B(k,n)=W_seq[m*Da+n])
+  float* scratch = reinterpret_cast<float*>(packed + pk.scratch);
+  launch_gemm<float, float>(st, P(XP_A_IN_W), E, 1, P(XP_SEQ_W), c.Da, 1, scratch, c.Da, E, c.Da, E, nullptr, 0);
+  cvt(scratch, c.Da, pk.Wfold, c.Da, E, c.Da);
+  fold_bias_kernel<<<(E + 127) / 128, 128, 0, st>>>(P(XP_A_IN_W), P(XP_SEQ_B), P(XP_A_IN_B), reinterpret_cast<float*>(packed + pk.bfold), E);
+  count_launch();
+  const float* in1 = P(XP_V2A_IN_W);
+  const float* in2 = P(XP_A2V_IN_W);
+  cvt(in1, E, pk.Wq1, BEP, E, E);
+  cvt(in1 + (int64_t)E * E, E, pk.Wk1, BEP, E, E);
+  cvt(in1 + (int64_t)2 * E * E, E, pk.Wv1, BEP, E, E);
+  cvt(P(XP_V2A_OUT_W), E, pk.Wo1, BEP, E, E);
+  cvt(in2, E, pk.Wq2, BEP, E, E);
+  cvt(in2 + (int64_t)E * E, E, pk.Wk2, BEP, E, E);
+  cvt(in2 + (int64_t)2 * E * E, E, pk.Wv2, BEP, E, E);
+  cvt(P(XP_A2V_OUT_W), E, pk.Wo2, BEP, E, E);
+  const int HW = c.head_kind == XATTN_HEAD_GATED ? E : c.common_dim;
+  transpose_f32_kernel<<<64, 256, 0, st>>>(P(XP_HEAD0_W), reinterpret_cast<float*>(packed + pk.W0T), HW, 2 * E);
+  count_launch();
+  XF_LAUNCH_CHECK();
+  return XATTN_OK;
+}
+
+}  // namespace xf

@@ -270,12 +270,22 @@ class XAttnKernelsMixin:
         if video_emb.dtype != audio_emb.dtype:
             raise ValueError("video_emb and audio_emb must share a dtype")
 
-    def _pick_precision(self, io_dtype: int, need_grad: bool) -> int:
+    def _bf16_supported(self, T: int, Ta: int) -> bool:
+        """Shapes the bf16 tensor-core kernels are specialised for (csrc/bf16_pack.cu: bf16_supported)."""
+        hw = self.d_model if self.xattn_head == "gated" else self.common_dim
+        return (self.d_model == 128 and self.num_heads == 4 and T <= 16 and Ta <= 160 and self.v_dim % 64 == 0
+                and self.audio_sequence_dim % 64 == 0 and hw <= 256 and self.num_classes <= 16
+                and self._prior_hidden <= 128 and self._prior_dim <= 32)
+
+    def _pick_precision(self, io_dtype: int, need_grad: bool, T: int = 16, Ta: int = 149) -> int:
+        """fp32 SIMT kernels for training / gradient parity and for shapes outside the bf16 specialisation; the bf16
+        tcgen05 + mma.sync path for bf16 embeddings at inference (``precision="bf16"`` forces it and raises on
+        unsupported shapes).  Both are CUDA paths of this library — there is no eager fallback."""
         if need_grad or self.precision == "fp32":
             return _lib.DTYPE_F32
         if self.precision == "bf16":
             return _lib.DTYPE_BF16
-        return _lib.DTYPE_BF16 if io_dtype == _lib.DTYPE_BF16 else _lib.DTYPE_F32
+        return _lib.DTYPE_BF16 if (io_dtype == _lib.DTYPE_BF16 and self._bf16_supported(T, Ta)) else _lib.DTYPE_F32
 
     def _launch_forward(self, video_emb: torch.Tensor, audio_emb: torch.Tensor, save: bool, training: Optional[bool] = None,
                         out: Optional[torch.Tensor] = None):
@@ -287,7 +297,9 @@ class XAttnKernelsMixin:
         B, T, _ = video_emb.shape
         Ta = audio_emb.shape[1]
         io = _io_dtype(video_emb)
-        precision = self._pick_precision(io, save or training)
+        precision = self._pick_precision(io, save or training, T, Ta)
+        if precision == _lib.DTYPE_BF16 and io != _lib.DTYPE_BF16:   # precision="bf16" forced on fp32 embeddings
+            video_emb, audio_emb, io = video_emb.bfloat16(), audio_emb.bfloat16(), _lib.DTYPE_BF16
         with torch.cuda.device(dev):
             flat = self.flat_parameters()
             if flat.device != dev:
