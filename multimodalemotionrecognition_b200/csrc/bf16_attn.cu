@@ -229,8 +229,8 @@ __global__ void __launch_bounds__(160, 2) a2v_attn_kernel(A2VArgs a) {
   float* bo_s = cv_s + 64;      // [128]
   float* ga_s = bo_s + BE;      // [128]
   float* be_s = ga_s + BE;      // [128]
-  float* pool_s = be_s + BE;    // [128]
-  uint64_t* bar = reinterpret_cast<uint64_t*>(pool_s + BE);
+  float* pool_s = be_s + BE;    // [5][128] per-warp partial sums (summed in a fixed order: deterministic)
+  uint64_t* bar = reinterpret_cast<uint64_t*>(pool_s + 5 * BE);
   const int c = blockIdx.x, tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, g = lane >> 2, t = lane & 3;
   const int Ta = a.Ta, T = a.T;
   if (tid == 0) {
@@ -254,7 +254,7 @@ __global__ void __launch_bounds__(160, 2) a2v_attn_kernel(A2VArgs a) {
     if (tid < 16) kv_s[tid] = a.use_prior ? a.tkv[(int64_t)c * 16 + tid] + pk : 0.f;
     if (tid < 64) cv_s[tid] = a.cv[(int64_t)c * 64 + tid];
     for (int i = tid; i < BE; i += blockDim.x) {
-      bo_s[i] = a.bo2[i]; ga_s[i] = a.gam[i]; be_s[i] = a.bet[i]; pool_s[i] = 0.f;
+      bo_s[i] = a.bo2[i]; ga_s[i] = a.gam[i]; be_s[i] = a.bet[i];
     }
   }
   __syncthreads();
@@ -396,12 +396,15 @@ __global__ void __launch_bounds__(160, 2) a2v_attn_kernel(A2VArgs a) {
       p1 += __shfl_xor_sync(0xffffffffu, p1, o2);
     }
     if (g == 0) {
-      atomicAdd(&pool_s[nt * 8 + 2 * t], p0);
-      atomicAdd(&pool_s[nt * 8 + 2 * t + 1], p1);
+      pool_s[warp * BE + nt * 8 + 2 * t] = p0;
+      pool_s[warp * BE + nt * 8 + 2 * t + 1] = p1;
     }
   }
   __syncthreads();
-  if (tid < BE) a.pooled[(int64_t)c * 2 * BE + BE + tid] = ga_s[tid] * (pool_s[tid] / (float)Ta) + be_s[tid];
+  if (tid < BE) {
+    const float tot = (((pool_s[tid] + pool_s[BE + tid]) + pool_s[2 * BE + tid]) + pool_s[3 * BE + tid]) + pool_s[4 * BE + tid];
+    a.pooled[(int64_t)c * 2 * BE + BE + tid] = ga_s[tid] * (tot / (float)Ta) + be_s[tid];
+  }
 }
 
 }  // namespace
@@ -449,7 +452,7 @@ int launch_a2v_attn(const Bf16Ctx& x) {
   a.bias_scale = P(XP_BIAS_SCALE);
   a.pooled = reinterpret_cast<float*>(x.ws + x.w.pooled);
   a.B = c.B; a.Ta = c.Ta; a.T = c.T; a.use_prior = c.use_prior;
-  const int smem = kA0Bytes + 2 * kOpBytes + (BTAP + 16 + 64 + 4 * BE) * 4 + 16;
+  const int smem = kA0Bytes + 2 * kOpBytes + (BTAP + 16 + 64 + 8 * BE) * 4 + 16;
   static bool configured = false;
   if (!configured) {
     XF_CUDA(cudaFuncSetAttribute(a2v_attn_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));

@@ -35,10 +35,15 @@ __global__ void __launch_bounds__(256) head_pooled_kernel(HeadPooledArgs a) {
     float acc[kHeadClips];
 #pragma unroll
     for (int cc = 0; cc < kHeadClips; ++cc) acc[cc] = 0.f;
-    for (int k = 0; k < 2 * BE; ++k) {
-      const float w = __ldg(a.w0t + (int64_t)k * a.HW + tid);
+    for (int k0 = 0; k0 < 2 * BE; k0 += 16) {   // 16 independent weight loads in flight per thread
+      float w[16];
 #pragma unroll
-      for (int cc = 0; cc < kHeadClips; ++cc) acc[cc] = fmaf(w, pooled[cc][k], acc[cc]);
+      for (int u = 0; u < 16; ++u) w[u] = __ldg(a.w0t + (int64_t)(k0 + u) * a.HW + tid);
+#pragma unroll
+      for (int u = 0; u < 16; ++u) {
+#pragma unroll
+        for (int cc = 0; cc < kHeadClips; ++cc) acc[cc] = fmaf(w[u], pooled[cc][k0 + u], acc[cc]);
+      }
     }
     const float b = a.b0[tid];
 #pragma unroll

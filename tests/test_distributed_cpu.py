@@ -1,0 +1,66 @@
+"""Host-side multi-rank logic on CPU (gloo, world_size 2): batch sharding, the ragged logits gather, and the gradient
+bucket all-reduce convention of Stage1Trainer (loss gradients pre-scaled by 1/world, bucket summed).  The compute path
+itself needs a B200 and is covered by the ``-m gpu`` tests; nothing here launches a kernel."""
+import os
+import socket
+
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+from multimodalemotionrecognition_b200.training import Stage1Trainer, gather_logits, shard_range
+
+
+def _free_port() -> int:
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
+
+
+class _FakeHead:
+    """Just the flat-buffer surface Stage1Trainer.allreduce_gradients touches."""
+
+    def __init__(self, grads):
+        self._g = grads
+
+    def flat_gradients(self, attach=True):
+        return self._g
+
+
+def _worker(rank: int, world: int, port: int, total: int):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        # 1. contiguous shards cover the batch exactly once, remainder to the low ranks
+        s, e = shard_range(total, rank, world)
+        full = torch.arange(total * 8, dtype=torch.float32).view(total, 8)
+        local = full[s:e].clone()
+        # 2. ragged gather reproduces the single-process logits on every rank
+        got = gather_logits(local, total)
+        assert torch.equal(got, full), (rank, got.shape)
+        # 3. gradient bucket: each rank's gradient of its local mean loss scaled by 1/world, summed == global mean
+        g_local = torch.full((10,), float(rank + 1)) / world
+        tr = Stage1Trainer(_FakeHead(g_local))
+        assert tr._world() == world
+        tr.allreduce_gradients()
+        expect = sum(float(r + 1) for r in range(world)) / world
+        assert torch.allclose(g_local, torch.full((10,), expect))
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("total", [8, 7, 1])
+def test_world2_gloo_shard_gather_allreduce(total):
+    mp.spawn(_worker, args=(2, _free_port(), total), nprocs=2, join=True)
+
+
+def test_shard_range_partitions():
+    for total in (0, 1, 5, 4096, 16385):
+        for world in (1, 2, 3, 8):
+            spans = [shard_range(total, r, world) for r in range(world)]
+            assert spans[0][0] == 0 and spans[-1][1] == total
+            for (a, b), (c, d) in zip(spans, spans[1:]):
+                assert b == c and b - a >= d - c >= 0
+            assert max(b - a for a, b in spans) - min(b - a for a, b in spans) <= 1

@@ -115,7 +115,7 @@ def test_bf16_forward_ragged_shapes(cuda_device, B, T, Ta):
 
 def test_bf16_unsupported_shapes_raise_or_route(cuda_device):
     m = make_head("concat", True, precision="bf16").to(cuda_device).eval()
-    with pytest.raises(ValueError):     # forced bf16 on a shape outside the specialisation: clean error, no fallback
+    with pytest.raises(ValueError), torch.no_grad():   # forced bf16 outside the specialisation: clean error, no fallback
         m(torch.zeros(2, 17, 512, device=cuda_device, dtype=torch.bfloat16), torch.zeros(2, 149, 768, device=cuda_device, dtype=torch.bfloat16))
     auto = make_head("concat", True, precision="auto").to(cuda_device).eval()
     with torch.no_grad():               # auto: the fp32 kernels take shapes the bf16 kernels do not
