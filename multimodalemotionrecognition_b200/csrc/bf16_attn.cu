@@ -19,7 +19,9 @@ struct V2AArgs {
   const __nv_bfloat16* a0;   // [B*Ta, BEP]
   const __nv_bfloat16* qt;   // [B,64,BEP]
   const float *meanv, *tqv;  // [B,E], [B,16]
-  const float *pw0, *pb0, *pw3, *pb3;   // prior_net.0 / .3
+  const __nv_bfloat16* pw0b;            // prior_net.0.weight as bf16 [Hd,2E]
+  const __nv_bfloat16* wsc;             // [8,BEP] score-weight tile (rows 0,1 = w_ak, w_aq)
+  const float *pb0, *pw3, *pb3;         // prior_net.0 bias, prior_net.3
   const float* wh[4];        // v_query, a_key, a_query, v_key bias heads: weight [E+P]
   const float* bh[4];
   const float* bias_scale;
@@ -50,20 +52,15 @@ __global__ void __launch_bounds__(128, 3) v2a_attn_kernel(V2AArgs a) {
   __syncthreads();
   if (tid == 0) {
     const uint32_t nb = (uint32_t)Ta * BEP * 2;
-    tc::mbar_expect_tx(bar, nb + kOpBytes);
+    tc::mbar_expect_tx(bar, nb + kOpBytes + 8 * BEP * 2);
     tc::bulk_load_1d(a0s, a.a0 + (int64_t)c * Ta * BEP, nb, bar);
     tc::bulk_load_1d(qts, a.qt + (int64_t)c * 64 * BEP, kOpBytes, bar);
+    tc::bulk_load_1d(wsc, a.wsc, 8 * BEP * 2, bar);
   }
-  {   // zero the padding token rows and build the 8 x 128 score-weight tile while the copy is in flight
+  {   // zero the padding token rows while the copy is in flight
     uint4* z = reinterpret_cast<uint4*>(a0s + Ta * BEP);
     const int nz = (BTAP - Ta) * BEP * 2 / 16;
     for (int i = tid; i < nz; i += blockDim.x) z[i] = make_uint4(0, 0, 0, 0);
-    for (int i = tid; i < 8 * BEP; i += blockDim.x) {
-      const int r = i / BEP, e = i - r * BEP;
-      float w = 0.f;
-      if (a.use_prior && r < 2 && e < BE) w = a.wh[r + 1][e];
-      wsc[i] = __float2bfloat16(w);
-    }
     if (a.use_prior) {
       for (int i = tid; i < BE; i += blockDim.x) pooled0[i] = a.meanv[(int64_t)c * BE + i];
       if (tid < 16) qv_s[tid] = a.tqv[(int64_t)c * 16 + tid];
@@ -93,20 +90,48 @@ __global__ void __launch_bounds__(128, 3) v2a_attn_kernel(V2AArgs a) {
         a.tqa[(int64_t)c * BTAP + j + 8] = d[3];
       }
     }
-    {   // mean_t a0  (fusion.py:180)
-      float s = 0.f;
-      for (int j = 0; j < Ta; ++j) s += __bfloat162float(a0s[j * BEP + tid]);
-      pooled0[BE + tid] = s / (float)Ta;
+    {   // mean_t a0 (fusion.py:180) on the tensor cores: ones[16 x Ta] · a0 — every result row is the column sum
+      const uint32_t ones[4] = {0x3F803F80u, 0x3F803F80u, 0x3F803F80u, 0x3F803F80u};
+      float d[4][4];
+#pragma unroll
+      for (int n = 0; n < 4; ++n) d[n][0] = d[n][1] = d[n][2] = d[n][3] = 0.f;
+#pragma unroll
+      for (int kk = 0; kk < BTAP / 16; ++kk) {
+#pragma unroll
+        for (int n2 = 0; n2 < 2; ++n2) {
+          uint32_t b[4];
+          fr::ldB_kn(a0b, 16 * kk, 2 * warp + n2, lane, b);
+          tc::mma_bf16(d[2 * n2], ones, b[0], b[1]);
+          tc::mma_bf16(d[2 * n2 + 1], ones, b[2], b[3]);
+        }
+      }
+      if (g == 0) {
+        const float inv = 1.f / (float)Ta;
+#pragma unroll
+        for (int n = 0; n < 4; ++n) {
+          pooled0[BE + (4 * warp + n) * 8 + 2 * t] = d[n][0] * inv;
+          pooled0[BE + (4 * warp + n) * 8 + 2 * t + 1] = d[n][1] * inv;
+        }
+      }
     }
     __syncthreads();
     // prior_net: Linear(2E -> Hd), ReLU, (Dropout: eval identity), Linear(Hd -> P)   (fusion.py:158-163)
-    for (int uo = warp; uo < a.Hd; uo += 4) {
-      const float* w = a.pw0 + (int64_t)uo * 2 * BE;
-      float s = 0.f;
+    {
+      float x[8];
 #pragma unroll
-      for (int k = 0; k < 2 * BE / 32; ++k) s = fmaf(__ldg(w + lane + 32 * k), pooled0[lane + 32 * k], s);
-      s = warp_sum(s);
-      if (lane == 0) hid[uo] = fmaxf(s + a.pb0[uo], 0.f);
+      for (int k = 0; k < 8; ++k) x[k] = pooled0[lane * 8 + k];
+      for (int uo = warp; uo < a.Hd; uo += 4) {
+        const uint4 wv = __ldg(reinterpret_cast<const uint4*>(a.pw0b + (int64_t)uo * 2 * BE) + lane);
+        const __nv_bfloat162* w2 = reinterpret_cast<const __nv_bfloat162*>(&wv);
+        float sacc = 0.f;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+          sacc = fmaf(__low2float(w2[k]), x[2 * k], sacc);
+          sacc = fmaf(__high2float(w2[k]), x[2 * k + 1], sacc);
+        }
+        sacc = warp_sum(sacc);
+        if (lane == 0) hid[uo] = fmaxf(sacc + a.pb0[uo], 0.f);
+      }
     }
     __syncthreads();
     for (int p = warp; p < a.P; p += 4) {
@@ -201,11 +226,17 @@ __global__ void __launch_bounds__(128, 3) v2a_attn_kernel(V2AArgs a) {
       tc::mma_bf16(o[2 * nt2 + 1], pa[kk], b[2], b[3]);
     }
   }
-  __nv_bfloat16* up = a.u + ((int64_t)c * 64 + h * 16 + g) * BE + 2 * t;
+  // U leaves in A-FRAGMENT order: lane (g,t) of head h writes the 32 registers it would feed to mma.sync as the A operand
+  // of the next product (video_update reads them back with eight 16-byte loads): [clip][head][lane][ks][4] x bf16x2.
+  uint4* up = reinterpret_cast<uint4*>(a.u) + (((int64_t)c * BH + h) * 32 + lane) * 8;
 #pragma unroll
-  for (int nt = 0; nt < 16; ++nt) {
-    *reinterpret_cast<uint32_t*>(up + nt * 8) = tc::pack_bf16(o[nt][0] * inv0, o[nt][1] * inv0);
-    *reinterpret_cast<uint32_t*>(up + nt * 8 + 8 * BE) = tc::pack_bf16(o[nt][2] * inv1, o[nt][3] * inv1);
+  for (int ks = 0; ks < 8; ++ks) {
+    uint4 v;
+    v.x = tc::pack_bf16(o[2 * ks][0] * inv0, o[2 * ks][1] * inv0);
+    v.y = tc::pack_bf16(o[2 * ks][2] * inv1, o[2 * ks][3] * inv1);
+    v.z = tc::pack_bf16(o[2 * ks + 1][0] * inv0, o[2 * ks + 1][1] * inv0);
+    v.w = tc::pack_bf16(o[2 * ks + 1][2] * inv1, o[2 * ks + 1][3] * inv1);
+    up[ks] = v;
   }
 }
 
@@ -264,6 +295,7 @@ __global__ void __launch_bounds__(160, 2) a2v_attn_kernel(A2VArgs a) {
   float pool[16][2];
 #pragma unroll
   for (int nt = 0; nt < 16; ++nt) pool[nt][0] = pool[nt][1] = 0.f;
+  float poolc = 0.f;   // sum over this thread's rows of mu_j * r_j (same for every column)
 
 #pragma unroll 1
   for (int mt = 2 * warp; mt < 2 * warp + 2; ++mt) {
@@ -287,47 +319,47 @@ __global__ void __launch_bounds__(160, 2) a2v_attn_kernel(A2VArgs a) {
           tc::mma_bf16(s[nt], x1, b[2], b[3]);
         }
       }
-      const float qa0 = qa_s[j0], qa1 = qa_s[j1];
+      // the prior bias tanh(qa_j + kv_i)·scale is the same for every head (fusion.py:351-354): once per (row, key)
+      float bia0[4], bia1[4];
+      {
+        const float qa0 = qa_s[j0], qa1 = qa_s[j1];
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          const int i = (q >> 1) * 8 + 2 * t + (q & 1);
+          const float kvv = kv_s[i];
+          bia0[q] = a.use_prior ? tc::tanh_fast(qa0 + kvv) * bsc : 0.f;
+          bia1[q] = a.use_prior ? tc::tanh_fast(qa1 + kvv) * bsc : 0.f;
+          if (i >= T) bia0[q] = bia1[q] = -INFINITY;   // padded video tokens never receive probability mass
+        }
+      }
+      constexpr float kL2E = 1.4426950408889634f;
 #pragma unroll
       for (int hh = 0; hh < BH; ++hh) {
         float m0 = -INFINITY, m1 = -INFINITY;
 #pragma unroll
-        for (int n2 = 0; n2 < 2; ++n2) {
-          const int nt = 2 * hh + n2;
-#pragma unroll
-          for (int e = 0; e < 2; ++e) {
-            const int i = n2 * 8 + 2 * t + e;
-            if (i < T) {
-              const float cc = cv_s[hh * 16 + i];
-              float b0 = 0.f, b1 = 0.f;
-              if (a.use_prior) {
-                b0 = tc::tanh_fast(qa0 + kv_s[i]) * bsc;
-                b1 = tc::tanh_fast(qa1 + kv_s[i]) * bsc;
-              }
-              s[nt][e] += cc + b0;
-              s[nt][2 + e] += cc + b1;
-            } else {
-              s[nt][e] = -INFINITY;
-              s[nt][2 + e] = -INFINITY;
-            }
-            m0 = fmaxf(m0, s[nt][e]);
-            m1 = fmaxf(m1, s[nt][2 + e]);
-          }
+        for (int q = 0; q < 4; ++q) {
+          const int nt = 2 * hh + (q >> 1), e = q & 1;
+          const float cc = cv_s[hh * 16 + (q >> 1) * 8 + 2 * t + e];
+          s[nt][e] += cc + bia0[q];
+          s[nt][2 + e] += cc + bia1[q];
+          m0 = fmaxf(m0, s[nt][e]);
+          m1 = fmaxf(m1, s[nt][2 + e]);
         }
         m0 = fmaxf(m0, __shfl_xor_sync(0xffffffffu, m0, 1)); m0 = fmaxf(m0, __shfl_xor_sync(0xffffffffu, m0, 2));
         m1 = fmaxf(m1, __shfl_xor_sync(0xffffffffu, m1, 1)); m1 = fmaxf(m1, __shfl_xor_sync(0xffffffffu, m1, 2));
+        const float n0 = -m0 * kL2E, n1 = -m1 * kL2E;
         float l0 = 0.f, l1 = 0.f;
 #pragma unroll
         for (int n2 = 0; n2 < 2; ++n2) {
           const int nt = 2 * hh + n2;
-          s[nt][0] = __expf(s[nt][0] - m0); s[nt][1] = __expf(s[nt][1] - m0);
-          s[nt][2] = __expf(s[nt][2] - m1); s[nt][3] = __expf(s[nt][3] - m1);
+          s[nt][0] = exp2f(fmaf(s[nt][0], kL2E, n0)); s[nt][1] = exp2f(fmaf(s[nt][1], kL2E, n0));
+          s[nt][2] = exp2f(fmaf(s[nt][2], kL2E, n1)); s[nt][3] = exp2f(fmaf(s[nt][3], kL2E, n1));
           l0 += s[nt][0] + s[nt][1];
           l1 += s[nt][2] + s[nt][3];
         }
         l0 += __shfl_xor_sync(0xffffffffu, l0, 1); l0 += __shfl_xor_sync(0xffffffffu, l0, 2);
         l1 += __shfl_xor_sync(0xffffffffu, l1, 1); l1 += __shfl_xor_sync(0xffffffffu, l1, 2);
-        const float i0 = 1.f / l0, i1 = 1.f / l1;
+        const float i0 = __frcp_rn(l0), i1 = __frcp_rn(l1);
 #pragma unroll
         for (int n2 = 0; n2 < 2; ++n2) {
           const int nt = 2 * hh + n2;
@@ -351,25 +383,26 @@ __global__ void __launch_bounds__(160, 2) a2v_attn_kernel(A2VArgs a) {
       }
     }
     // ---- a1 = LayerNorm(a0 + out + bo2) (fusion.py:399), accumulated into the temporal mean (:402) ----
-    float s0 = 0.f, s1 = 0.f;
+    // mean_j xhat_j = sum_j r_j s_j - sum_j r_j mu_j : the rows are never normalised element by element.
+    float s0 = 0.f, s1 = 0.f, q0 = 0.f, q1 = 0.f;
 #pragma unroll
     for (int nt = 0; nt < 16; ++nt) {
       const int col = nt * 8 + 2 * t;
       const __nv_bfloat162 r0 = *reinterpret_cast<const __nv_bfloat162*>(a0s + j0 * BEP + col);
       const __nv_bfloat162 r1 = *reinterpret_cast<const __nv_bfloat162*>(a0s + j1 * BEP + col);
-      o[nt][0] += bo_s[col] + __low2float(r0);
-      o[nt][1] += bo_s[col + 1] + __high2float(r0);
-      o[nt][2] += bo_s[col] + __low2float(r1);
-      o[nt][3] += bo_s[col + 1] + __high2float(r1);
+      const float2 bo = *reinterpret_cast<const float2*>(bo_s + col);
+      o[nt][0] += bo.x + __low2float(r0);
+      o[nt][1] += bo.y + __high2float(r0);
+      o[nt][2] += bo.x + __low2float(r1);
+      o[nt][3] += bo.y + __high2float(r1);
       s0 += o[nt][0] + o[nt][1];
       s1 += o[nt][2] + o[nt][3];
     }
     s0 += __shfl_xor_sync(0xffffffffu, s0, 1); s0 += __shfl_xor_sync(0xffffffffu, s0, 2);
     s1 += __shfl_xor_sync(0xffffffffu, s1, 1); s1 += __shfl_xor_sync(0xffffffffu, s1, 2);
     const float mu0 = s0 * (1.f / BE), mu1 = s1 * (1.f / BE);
-    float q0 = 0.f, q1 = 0.f;
 #pragma unroll
-    for (int nt = 0; nt < 16; ++nt) {
+    for (int nt = 0; nt < 16; ++nt) {   // two-pass variance (as torch LayerNorm): sum (x - mu)^2
       float d;
       d = o[nt][0] - mu0; q0 = fmaf(d, d, q0);
       d = o[nt][1] - mu0; q0 = fmaf(d, d, q0);
@@ -380,13 +413,16 @@ __global__ void __launch_bounds__(160, 2) a2v_attn_kernel(A2VArgs a) {
     q1 += __shfl_xor_sync(0xffffffffu, q1, 1); q1 += __shfl_xor_sync(0xffffffffu, q1, 2);
     const float r0 = (j0 < Ta) ? rsqrtf(q0 * (1.f / BE) + 1e-5f) : 0.f;   // padded token rows contribute nothing
     const float r1 = (j1 < Ta) ? rsqrtf(q1 * (1.f / BE) + 1e-5f) : 0.f;
+    poolc += mu0 * r0 + mu1 * r1;
 #pragma unroll
     for (int nt = 0; nt < 16; ++nt) {
-      pool[nt][0] += (o[nt][0] - mu0) * r0 + (o[nt][2] - mu1) * r1;
-      pool[nt][1] += (o[nt][1] - mu0) * r0 + (o[nt][3] - mu1) * r1;
+      pool[nt][0] = fmaf(o[nt][0], r0, fmaf(o[nt][2], r1, pool[nt][0]));
+      pool[nt][1] = fmaf(o[nt][1], r0, fmaf(o[nt][3], r1, pool[nt][1]));
     }
   }
   // pooled_a[e] = gamma[e] * mean_j xhat[j,e] + beta[e]
+#pragma unroll
+  for (int o2 = 4; o2 <= 16; o2 <<= 1) poolc += __shfl_xor_sync(0xffffffffu, poolc, o2);
 #pragma unroll
   for (int nt = 0; nt < 16; ++nt) {
     float p0 = pool[nt][0], p1 = pool[nt][1];
@@ -396,8 +432,8 @@ __global__ void __launch_bounds__(160, 2) a2v_attn_kernel(A2VArgs a) {
       p1 += __shfl_xor_sync(0xffffffffu, p1, o2);
     }
     if (g == 0) {
-      pool_s[warp * BE + nt * 8 + 2 * t] = p0;
-      pool_s[warp * BE + nt * 8 + 2 * t + 1] = p1;
+      pool_s[warp * BE + nt * 8 + 2 * t] = p0 - poolc;
+      pool_s[warp * BE + nt * 8 + 2 * t + 1] = p1 - poolc;
     }
   }
   __syncthreads();
@@ -417,7 +453,9 @@ int launch_v2a_attn(const Bf16Ctx& x) {
   a.qt = reinterpret_cast<const __nv_bfloat16*>(x.ws + x.w.qt);
   a.meanv = reinterpret_cast<const float*>(x.ws + x.w.meanv);
   a.tqv = reinterpret_cast<const float*>(x.ws + x.w.tqv);
-  a.pw0 = P(XP_PRIOR0_W); a.pb0 = P(XP_PRIOR0_B); a.pw3 = P(XP_PRIOR3_W); a.pb3 = P(XP_PRIOR3_B);
+  a.pw0b = reinterpret_cast<const __nv_bfloat16*>(x.packed + x.pk.pW0);
+  a.wsc = reinterpret_cast<const __nv_bfloat16*>(x.packed + x.pk.wsc);
+  a.pb0 = P(XP_PRIOR0_B); a.pw3 = P(XP_PRIOR3_W); a.pb3 = P(XP_PRIOR3_B);
   a.wh[0] = P(XP_VQ_W); a.bh[0] = P(XP_VQ_B); a.wh[1] = P(XP_AK_W); a.bh[1] = P(XP_AK_B);
   a.wh[2] = P(XP_AQ_W); a.bh[2] = P(XP_AQ_B); a.wh[3] = P(XP_VK_W); a.bh[3] = P(XP_VK_B);
   a.bias_scale = P(XP_BIAS_SCALE);

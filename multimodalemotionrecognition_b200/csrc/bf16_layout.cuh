@@ -29,7 +29,9 @@ constexpr int BTAP = 160;  // audio tokens padded to ten m16 tiles
 struct PackBf16 {
   int64_t Wv, Wfold, bfold;                          // bf16 [E,Dv], bf16 [E,Da], f32 [E]
   int64_t Wq1, Wk1, Wv1, Wo1, Wk2, Wv2, Wq2, Wo2;    // bf16 [E,BEP] each (torch [out,in] layout, padded pitch)
-  int64_t W0T;                                       // f32 [2E,HW]: head layer 0 transposed (coalesced over hidden units)
+  int64_t W0b;                                       // bf16 [HW,2E]: head layer 0 (xattn_mlp.0 / xattn_gate.0) weight
+  int64_t pW0;                                       // bf16 [Hd,2E]: prior_net.0.weight (0 bytes without the prior)
+  int64_t wsc;                                       // bf16 [8,BEP]: rows 0,1 = a_key / a_query score weights (first E entries)
   int64_t scratch;                                   // f32 [E,Da] temp of the fold
   int64_t total;
 };

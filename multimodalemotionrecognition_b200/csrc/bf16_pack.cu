@@ -18,7 +18,8 @@ int bf16_supported(const xattn_config& c) {
   if (c.Dv % 64 != 0 || c.Da % 64 != 0) XF_FAIL(XATTN_ERR_SHAPE, "bf16 path needs Dv, Da multiples of 64 (got %d, %d)", c.Dv, c.Da);
   if (c.io_dtype != XATTN_DTYPE_BF16) XF_FAIL(XATTN_ERR_DTYPE, "bf16 path reads bf16 embeddings (io_dtype must be bf16)");
   const int HW = c.head_kind == XATTN_HEAD_GATED ? c.E : c.common_dim;
-  if (HW > 256 || c.C > 16) XF_FAIL(XATTN_ERR_SHAPE, "bf16 path head supports hidden width <= 256 and <= 16 classes");
+  if (HW > 256 || HW % 64 != 0 || c.C > 16)
+    XF_FAIL(XATTN_ERR_SHAPE, "bf16 path head supports hidden widths 64/128/192/256 and <= 16 classes (got %d, %d)", HW, c.C);
   if (c.use_prior && (c.prior_hidden > 128 || c.prior_dim > 32))
     XF_FAIL(XATTN_ERR_SHAPE, "bf16 path supports prior_hidden <= 128, prior_dim <= 32");
   return XATTN_OK;
@@ -38,7 +39,9 @@ void compute_pack_bf16(const xattn_config& c, PackBf16& p) {
   p.bfold = take(E * 4);
   p.Wq1 = take(E * BEP * 2); p.Wk1 = take(E * BEP * 2); p.Wv1 = take(E * BEP * 2); p.Wo1 = take(E * BEP * 2);
   p.Wk2 = take(E * BEP * 2); p.Wv2 = take(E * BEP * 2); p.Wq2 = take(E * BEP * 2); p.Wo2 = take(E * BEP * 2);
-  p.W0T = take(2 * E * HW * 4);
+  p.W0b = take(HW * 2 * E * 2);
+  p.pW0 = take((int64_t)(c.use_prior ? c.prior_hidden : 0) * 2 * E * 2);
+  p.wsc = take(8 * BEP * 2);
   p.scratch = take(E * c.Da * 4);
   p.total = off;
 }
@@ -104,15 +107,6 @@ __global__ void fold_bias_kernel(const float* __restrict__ w_in, const float* __
   for (int m = 0; m < E; ++m) s = fmaf(w_in[(int64_t)e * E + m], b_seq[m], s);
   out[e] = s;
 }
-// dst[k, n] = src[n, k]   (src [N,K] fp32)
-__global__ void transpose_f32_kernel(const float* __restrict__ src, float* __restrict__ dst, int N, int K) {
-  const int64_t total = (int64_t)N * K;
-  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
-    const int64_t k = i / N, n = i - k * N;
-    dst[i] = src[n * K + k];
-  }
-}
-
 int pack_weights_bf16(const xattn_config& c, const float* params, void* packed_v, cudaStream_t st) {
   if (c.E != BE || c.H != BH) XF_FAIL(XATTN_ERR_SHAPE, "bf16 path is specialised for d_model=128, num_heads=4 (got E=%d H=%d)", c.E, c.H);
   ParamLayout pl;
@@ -147,8 +141,13 @@ int pack_weights_bf16(const xattn_config& c, const float* params, void* packed_v
   cvt(in2 + (int64_t)2 * E * E, E, pk.Wv2, BEP, E, E);
   cvt(P(XP_A2V_OUT_W), E, pk.Wo2, BEP, E, E);
   const int HW = c.head_kind == XATTN_HEAD_GATED ? E : c.common_dim;
-  transpose_f32_kernel<<<64, 256, 0, st>>>(P(XP_HEAD0_W), reinterpret_cast<float*>(packed + pk.W0T), HW, 2 * E);
-  count_launch();
+  cvt(P(XP_HEAD0_W), 2 * E, pk.W0b, 2 * E, HW, 2 * E);
+  XF_CUDA(cudaMemsetAsync(packed + pk.wsc, 0, 8 * BEP * 2, st));
+  if (c.use_prior) {
+    cvt(P(XP_PRIOR0_W), 2 * E, pk.pW0, 2 * E, c.prior_hidden, 2 * E);
+    cvt(P(XP_AK_W), E, pk.wsc, BEP, 1, E);                 // row 0: a_key_bias.weight[:E]
+    cvt(P(XP_AQ_W), E, pk.wsc + BEP * 2, BEP, 1, E);       // row 1: a_query_bias.weight[:E]
+  }
   XF_LAUNCH_CHECK();
   return XATTN_OK;
 }

@@ -23,7 +23,7 @@ struct VideoPreArgs {
   float scale;
 };
 
-__global__ void __launch_bounds__(256, 1) video_pre_kernel(VideoPreArgs a) {
+__global__ void __launch_bounds__(256, 2) video_pre_kernel(VideoPreArgs a) {
   extern __shared__ __align__(16) uint8_t sm[];
   __nv_bfloat16* Wq1s = reinterpret_cast<__nv_bfloat16*>(sm);
   __nv_bfloat16* Wk1s = reinterpret_cast<__nv_bfloat16*>(sm + kWBytes);
@@ -90,30 +90,31 @@ __global__ void __launch_bounds__(256, 1) video_pre_kernel(VideoPreArgs a) {
       a.tqv[(int64_t)c * 16 + g] = sq0; a.tqv[(int64_t)c * 16 + g + 8] = sq1;
       a.tkv[(int64_t)c * 16 + g] = sk0; a.tkv[(int64_t)c * 16 + g + 8] = sk1;
     }
-    // Q~ = (v0 · Wq1^T + bq1) * 1/sqrt(dh)     (torch scales q before the product: F.multi_head_attention_forward)
-    float acc[16][4];
-#pragma unroll
-    for (int nt = 0; nt < 16; ++nt) {
-      acc[nt][0] = acc[nt][1] = acc[nt][2] = acc[nt][3] = 0.f;
-#pragma unroll
-      for (int ks = 0; ks < 8; ks += 2) {
-        uint32_t b[4];
-        fr::ldB_nk(wq, nt, ks, lane, b);
-        tc::mma_bf16(acc[nt], af[ks], b[0], b[1]);
-        tc::mma_bf16(acc[nt], af[ks + 1], b[2], b[3]);
-      }
-      const int col = nt * 8 + 2 * t;
-      acc[nt][0] = (acc[nt][0] + bq1s[col]) * a.scale;
-      acc[nt][1] = (acc[nt][1] + bq1s[col + 1]) * a.scale;
-      acc[nt][2] = (acc[nt][2] + bq1s[col]) * a.scale;
-      acc[nt][3] = (acc[nt][3] + bq1s[col + 1]) * a.scale;
-    }
-    // Qt_h[i, e] = sum_d Q~[i, 32h+d] * Wk1[32h+d, e]
-#pragma unroll
+    // per head: Q~_h = (v0 · Wq1_h^T + bq1_h) / sqrt(dh)  (torch scales q before the product), then
+    // Qt_h[i, e] = sum_d Q~_h[i, d] * Wk1[32h+d, e]
+#pragma unroll 1
     for (int h = 0; h < BH; ++h) {
+      float acc[4][4];
+#pragma unroll
+      for (int n = 0; n < 4; ++n) {
+        const int nt = 4 * h + n;
+        acc[n][0] = acc[n][1] = acc[n][2] = acc[n][3] = 0.f;
+#pragma unroll
+        for (int ks = 0; ks < 8; ks += 2) {
+          uint32_t b[4];
+          fr::ldB_nk(wq, nt, ks, lane, b);
+          tc::mma_bf16(acc[n], af[ks], b[0], b[1]);
+          tc::mma_bf16(acc[n], af[ks + 1], b[2], b[3]);
+        }
+        const int col = nt * 8 + 2 * t;
+        acc[n][0] = (acc[n][0] + bq1s[col]) * a.scale;
+        acc[n][1] = (acc[n][1] + bq1s[col + 1]) * a.scale;
+        acc[n][2] = (acc[n][2] + bq1s[col]) * a.scale;
+        acc[n][3] = (acc[n][3] + bq1s[col + 1]) * a.scale;
+      }
       uint32_t aq[2][4];
-      fr::c2a(acc[4 * h], acc[4 * h + 1], aq[0]);
-      fr::c2a(acc[4 * h + 2], acc[4 * h + 3], aq[1]);
+      fr::c2a(acc[0], acc[1], aq[0]);
+      fr::c2a(acc[2], acc[3], aq[1]);
       __nv_bfloat16* q0 = a.qt + ((int64_t)c * 64 + h * 16 + g) * BEP + 2 * t;
 #pragma unroll
       for (int nt2 = 0; nt2 < 8; ++nt2) {
@@ -135,7 +136,7 @@ __global__ void __launch_bounds__(256, 1) video_pre_kernel(VideoPreArgs a) {
 }
 
 struct VideoUpdArgs {
-  const __nv_bfloat16* u;    // [B,64,E]  U_h = softmax(S_h) · a0 (rows h*16+i)
+  const __nv_bfloat16* u;    // [B,4,32,8,4] bf16x2: U_h = softmax(S_h) · a0 in mma A-fragment order (see v2a_attn_kernel)
   const float* v0;           // [B,T,E]
   const __nv_bfloat16* W[6]; // Wv1, Wo1, Wk2, Wv2, Wq2, Wo2
   const float* vec[7];       // bv1, bo1, bk2, bv2, bq2, v_norm.weight, v_norm.bias
@@ -163,7 +164,28 @@ __device__ __forceinline__ void proj128(float (&acc)[16][4], const uint32_t (&af
   }
 }
 
-__global__ void __launch_bounds__(256, 1) video_update_kernel(VideoUpdArgs a) {
+constexpr int kUpdWarps = 16;
+
+// 4 n-tiles (32 output columns [32h, 32h+32)) of A(16 x 128) · W^T, + bias
+__device__ __forceinline__ void proj32(float (&acc)[4][4], const uint32_t (&af)[8][4], uint32_t w, const float* bias, int h, int lane) {
+  const int t = lane & 3;
+#pragma unroll
+  for (int n = 0; n < 4; ++n) {
+    const int nt = 4 * h + n;
+    acc[n][0] = acc[n][1] = acc[n][2] = acc[n][3] = 0.f;
+#pragma unroll
+    for (int ks = 0; ks < 8; ks += 2) {
+      uint32_t b[4];
+      fr::ldB_nk(w, nt, ks, lane, b);
+      tc::mma_bf16(acc[n], af[ks], b[0], b[1]);
+      tc::mma_bf16(acc[n], af[ks + 1], b[2], b[3]);
+    }
+    const float b0 = bias[nt * 8 + 2 * t], b1 = bias[nt * 8 + 2 * t + 1];
+    acc[n][0] += b0; acc[n][1] += b1; acc[n][2] += b0; acc[n][3] += b1;
+  }
+}
+
+__global__ void __launch_bounds__(kUpdWarps * 32, 1) video_update_kernel(VideoUpdArgs a) {
   extern __shared__ __align__(16) uint8_t sm[];
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, g = lane >> 2, t = lane & 3;
 #pragma unroll
@@ -177,39 +199,25 @@ __global__ void __launch_bounds__(256, 1) video_update_kernel(VideoUpdArgs a) {
               *gam = vecs + 5 * BE, *bet = vecs + 6 * BE;
   const int T = a.T;
   const float invT = 1.f / (float)T;
-  for (int c = blockIdx.x * 8 + warp; c < a.B; c += gridDim.x * 8) {
-    // ---- attention output of v2a: O[i, 32h+d] = sum_e U_h[i,e] Wv1[32h+d, e] + bv1   (softmax rows sum to 1) ----
-    float acc[16][4];
+  for (int c = blockIdx.x * kUpdWarps + warp; c < a.B; c += gridDim.x * kUpdWarps) {
+    // ---- attention output of v2a, head by head: O[i, 32h+d] = sum_e U_h[i,e] Wv1[32h+d, e] + bv1 (softmax rows sum to 1) ----
+    uint32_t af[8][4];   // first the A fragments of O (k-steps 2h, 2h+1 <- head h), later those of v1
 #pragma unroll
     for (int h = 0; h < BH; ++h) {
-      const uint32_t* up = reinterpret_cast<const uint32_t*>(a.u + ((int64_t)c * 64 + h * 16 + g) * BE);
+      const uint4* up = reinterpret_cast<const uint4*>(a.u) + (((int64_t)c * BH + h) * 32 + lane) * 8;   // fragment order
       uint32_t au[8][4];
 #pragma unroll
       for (int ks = 0; ks < 8; ++ks) {
-        const int w2 = (ks * 16 + 2 * t) >> 1;
-        au[ks][0] = __ldg(up + w2);
-        au[ks][1] = __ldg(up + w2 + 8 * BE / 2);
-        au[ks][2] = __ldg(up + w2 + 4);
-        au[ks][3] = __ldg(up + w2 + 4 + 8 * BE / 2);
+        const uint4 v = __ldg(up + ks);
+        au[ks][0] = v.x; au[ks][1] = v.y; au[ks][2] = v.z; au[ks][3] = v.w;
       }
-#pragma unroll
-      for (int n = 4 * h; n < 4 * h + 4; ++n) {
-        acc[n][0] = acc[n][1] = acc[n][2] = acc[n][3] = 0.f;
-#pragma unroll
-        for (int ks = 0; ks < 8; ks += 2) {
-          uint32_t b[4];
-          fr::ldB_nk(wv1, n, ks, lane, b);
-          tc::mma_bf16(acc[n], au[ks], b[0], b[1]);
-          tc::mma_bf16(acc[n], au[ks + 1], b[2], b[3]);
-        }
-        const float b0 = bv1[n * 8 + 2 * t], b1 = bv1[n * 8 + 2 * t + 1];
-        acc[n][0] += b0; acc[n][1] += b1; acc[n][2] += b0; acc[n][3] += b1;
-      }
+      float o4[4][4];
+      proj32(o4, au, wv1, bv1, h, lane);
+      fr::c2a(o4[0], o4[1], af[2 * h]);
+      fr::c2a(o4[2], o4[3], af[2 * h + 1]);
     }
-    uint32_t af[8][4];
-#pragma unroll
-    for (int ks = 0; ks < 8; ++ks) fr::c2a(acc[2 * ks], acc[2 * ks + 1], af[ks]);
     // ---- out_proj, residual, LayerNorm (fusion.py:395) ----
+    float acc[16][4];
     proj128(acc, af, wo1, bo1, lane);
     const float* v = a.v0 + (int64_t)c * T * BE;
     float s0 = 0.f, s1 = 0.f;
@@ -265,19 +273,20 @@ __global__ void __launch_bounds__(256, 1) video_update_kernel(VideoUpdArgs a) {
     }
 #pragma unroll
     for (int ks = 0; ks < 8; ++ks) fr::c2a(acc[2 * ks], acc[2 * ks + 1], af[ks]);   // v1 as the A operand
-    // ---- keys of a2v: K2 = v1·Wk2^T + bk2 ; Kt_h = scale·K2_h·Wq2_h ; c_hi = scale·K2_h[i]·bq2_h ----
-    proj128(acc, af, wk2, bk2, lane);
-#pragma unroll
+    // ---- keys of a2v, head by head: K2_h = v1·Wk2_h^T + bk2_h ; Kt_h = scale·K2_h·Wq2_h ; c_hi = scale·K2_h[i]·bq2_h ----
+#pragma unroll 1
     for (int h = 0; h < BH; ++h) {
+      float k4[4][4];
+      proj32(k4, af, wk2, bk2, h, lane);
       uint32_t aq[2][4];
-      fr::c2a(acc[4 * h], acc[4 * h + 1], aq[0]);
-      fr::c2a(acc[4 * h + 2], acc[4 * h + 3], aq[1]);
+      fr::c2a(k4[0], k4[1], aq[0]);
+      fr::c2a(k4[2], k4[3], aq[1]);
       float c0 = 0.f, c1 = 0.f;
 #pragma unroll
-      for (int n = 4 * h; n < 4 * h + 4; ++n) {
-        const float w0 = bq2[n * 8 + 2 * t], w1 = bq2[n * 8 + 2 * t + 1];
-        c0 += acc[n][0] * w0 + acc[n][1] * w1;
-        c1 += acc[n][2] * w0 + acc[n][3] * w1;
+      for (int n = 0; n < 4; ++n) {
+        const float w0 = bq2[(4 * h + n) * 8 + 2 * t], w1 = bq2[(4 * h + n) * 8 + 2 * t + 1];
+        c0 += k4[n][0] * w0 + k4[n][1] * w1;
+        c1 += k4[n][2] * w0 + k4[n][3] * w1;
       }
       c0 += __shfl_xor_sync(0xffffffffu, c0, 1); c0 += __shfl_xor_sync(0xffffffffu, c0, 2);
       c1 += __shfl_xor_sync(0xffffffffu, c1, 1); c1 += __shfl_xor_sync(0xffffffffu, c1, 2);
@@ -302,13 +311,14 @@ __global__ void __launch_bounds__(256, 1) video_update_kernel(VideoUpdArgs a) {
         *reinterpret_cast<uint32_t*>(k0 + nt2 * 16 + 8 + 8 * BEP) = tc::pack_bf16(d1[2] * a.scale, d1[3] * a.scale);
       }
     }
-    // ---- values of a2v with out_proj folded in: V2 = v1·Wv2^T + bv2 ; Vt_h[i, e'] = sum_d V2[i,32h+d] Wo2[e', 32h+d] ----
-    proj128(acc, af, wv2, bv2, lane);
-#pragma unroll
+    // ---- values of a2v with out_proj folded in: V2_h = v1·Wv2_h^T + bv2_h ; Vt_h[i, e'] = sum_d V2_h[i,d] Wo2[e', 32h+d] ----
+#pragma unroll 1
     for (int h = 0; h < BH; ++h) {
+      float v4[4][4];
+      proj32(v4, af, wv2, bv2, h, lane);
       uint32_t aq[2][4];
-      fr::c2a(acc[4 * h], acc[4 * h + 1], aq[0]);
-      fr::c2a(acc[4 * h + 2], acc[4 * h + 3], aq[1]);
+      fr::c2a(v4[0], v4[1], aq[0]);
+      fr::c2a(v4[2], v4[3], aq[1]);
       __nv_bfloat16* v0p = a.vt + ((int64_t)c * 64 + h * 16 + g) * BEP + 2 * t;
 #pragma unroll
       for (int nt = 0; nt < 16; ++nt) {
@@ -326,10 +336,10 @@ __global__ void __launch_bounds__(256, 1) video_update_kernel(VideoUpdArgs a) {
 
 }  // namespace
 
-static int video_grid(int B) {
-  const int need = (B + 7) / 8;
-  const int sms = num_sms();
-  return need < sms ? need : sms;
+static int video_grid(int B, int ctas_per_sm, int warps = 8) {
+  const int need = (B + warps - 1) / warps;
+  const int cap = num_sms() * ctas_per_sm;
+  return need < cap ? need : cap;
 }
 
 int launch_video_pre(const Bf16Ctx& x) {
@@ -354,7 +364,7 @@ int launch_video_pre(const Bf16Ctx& x) {
     XF_CUDA(cudaFuncSetAttribute(video_pre_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
     configured = true;
   }
-  video_pre_kernel<<<video_grid(c.B), 256, smem, x.st>>>(a);
+  video_pre_kernel<<<video_grid(c.B, 2), 256, smem, x.st>>>(a);
   count_launch();
   XF_LAUNCH_CHECK();
   return XATTN_OK;
@@ -387,7 +397,7 @@ int launch_video_update(const Bf16Ctx& x) {
     XF_CUDA(cudaFuncSetAttribute(video_update_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
     configured = true;
   }
-  video_update_kernel<<<video_grid(c.B), 256, smem, x.st>>>(a);
+  video_update_kernel<<<video_grid(c.B, 1, kUpdWarps), kUpdWarps * 32, smem, x.st>>>(a);
   count_launch();
   XF_LAUNCH_CHECK();
   return XATTN_OK;

@@ -4,12 +4,14 @@
 //   v_in_proj :372                         X = video_emb [B*T, 512],  W = v_in_proj.weight
 //   a_in_proj ∘ audio_seq_proj :378 + :386 X = audio_emb [B*Ta, 768], W = W_in · W_seq (folded at pack time)
 //
-// Kernel shape: one 128(M) x 128(N) output tile per CTA, K in 64-element (128-byte) chunks.
-//   warp 0    : TMA producer — cp.async.bulk.tensor (SWIZZLE_128B boxes of 64 x 128) into a kStages-deep smem ring
-//   warp 1    : allocates 128 TMEM columns, one elected lane issues tcgen05.mma (M=128, N=128, K=16) x4 per stage and
-//               tcgen05.commit's the stage back to the producer; a final commit signals the epilogue
-//   warps 2-5 : epilogue — tcgen05.ld (32 lanes x 32 columns), + bias, convert, 16-byte global stores
-// 96 KB of smem per CTA => two CTAs per SM, so one CTA's epilogue overlaps the other's main loop.
+// Persistent, warp-specialised kernel: one CTA per SM loops over 128(M) x 128(N) output tiles.
+//   warp 0    : TMA producer — cp.async.bulk.tensor (SWIZZLE_128B boxes of 64 x 128 bf16) into a 5-stage smem ring that
+//               keeps running across tile boundaries (the HBM stream never drains between tiles)
+//   warp 1    : one elected lane issues tcgen05.mma (M=128, N=128, K=16; 4 per stage) into one of TWO 128-column TMEM
+//               accumulators; tcgen05.commit frees the smem stage / publishes the accumulator
+//   warps 2-5 : epilogue — tcgen05.ld (32 lanes x 32 columns), + bias, convert; the bf16 tile is staged in smem as the
+//               exact global image (rows at the output pitch are contiguous) and leaves with ONE cp.async.bulk store,
+//               while the MMA warp already fills the other accumulator with the next tile.
 #include <cuda.h>
 
 #include "common.cuh"
@@ -21,26 +23,37 @@ namespace xf {
 namespace {
 
 constexpr int BM = 128, BN = 128, BK = 64;
-constexpr int kStages = 3;
+constexpr int kStages = 5;
 constexpr int kStageBytes = (BM * BK + BN * BK) * 2;   // 32 KB
 constexpr int kGemmThreads = 192;
-constexpr int kSmemBytes = kStages * kStageBytes + 1024 /*align slack*/ + 256 /*barriers*/;
+constexpr int kMaxStagePitch = 160;                    // staged (bulk-store) epilogue supports pitches up to this
+constexpr int kBarBytes = 256;
 
-template <bool OUT_BF16>
-__global__ void __launch_bounds__(kGemmThreads) gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA,
-                                                               const __grid_constant__ CUtensorMap tmB,
-                                                               const float* __restrict__ bias, void* __restrict__ out,
-                                                               int64_t out_pitch, int M, int N, int K) {
+__host__ __device__ constexpr int gemm_smem_bytes(bool staged, int pitch) {
+  return kStages * kStageBytes + (staged ? BM * pitch * 2 : 0) + BN * 4 + kBarBytes + 1024;
+}
+
+// OUT_BF16: output dtype.  STAGED: N == 128 and bf16 -> smem image + one bulk store per tile.
+template <bool OUT_BF16, bool STAGED>
+__global__ void __launch_bounds__(kGemmThreads, 1) gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA,
+                                                                  const __grid_constant__ CUtensorMap tmB,
+                                                                  const float* __restrict__ bias, void* __restrict__ out,
+                                                                  int64_t out_pitch, int M, int N, int K) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
-  uint64_t* full = reinterpret_cast<uint64_t*>(smem + kStages * kStageBytes);
+  uint8_t* stage_out = smem + kStages * kStageBytes;                                   // [128][pitch] bf16 (STAGED)
+  float* bias_s = reinterpret_cast<float*>(stage_out + (STAGED ? BM * (int)out_pitch * 2 : 0));
+  uint64_t* full = reinterpret_cast<uint64_t*>(bias_s + BN);
   uint64_t* empty = full + kStages;
-  uint64_t* acc_full = empty + kStages;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_full + 1);
+  uint64_t* acc_full = empty + kStages;    // [2]
+  uint64_t* acc_empty = acc_full + 2;      // [2]
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_empty + 2);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int m0 = blockIdx.x * BM, n0 = blockIdx.y * BN;
   const int KB = K / BK;
+  const int tiles_n = N / BN;
+  const int tiles_m = (M + BM - 1) / BM;
+  const int num_tiles = tiles_m * tiles_n;
 
   if (warp == 0 && lane == 0) {
     tc::tma_prefetch_desc(&tmA);
@@ -49,88 +62,135 @@ __global__ void __launch_bounds__(kGemmThreads) gemm_tc_kernel(const __grid_cons
       tc::mbar_init(&full[s], 1);
       tc::mbar_init(&empty[s], 1);
     }
-    tc::mbar_init(acc_full, 1);
+    for (int b = 0; b < 2; ++b) {
+      tc::mbar_init(&acc_full[b], 1);
+      tc::mbar_init(&acc_empty[b], 4);   // one arrival per epilogue warp
+    }
     tc::fence_barrier_init();
   }
-  if (warp == 1) tc::tmem_alloc(tmem_slot, BN);
+  if (warp == 1) tc::tmem_alloc(tmem_slot, 2 * BN);
   tc::tc_fence_before();
   __syncthreads();
   tc::tc_fence_after();
-  const uint32_t tmem_acc = *tmem_slot;
+  const uint32_t tmem_base = *tmem_slot;
 
   if (warp == 0) {
     if (lane == 0) {
-      for (int kb = 0; kb < KB; ++kb) {
-        const int s = kb % kStages;
-        const uint32_t ph = (uint32_t)(kb / kStages) & 1u;
-        tc::mbar_wait(&empty[s], ph ^ 1u);
-        tc::mbar_expect_tx(&full[s], kStageBytes);
-        uint8_t* a = smem + s * kStageBytes;
-        tc::tma_load_2d(a, &tmA, &full[s], kb * BK, m0);
-        tc::tma_load_2d(a + BM * BK * 2, &tmB, &full[s], kb * BK, n0);
+      uint32_t it = 0;   // global k-iteration counter: the ring does not restart at tile boundaries
+      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+        const int m0 = (tile / tiles_n) * BM, n0 = (tile % tiles_n) * BN;
+        for (int kb = 0; kb < KB; ++kb, ++it) {
+          const int s = it % kStages;
+          const uint32_t ph = (it / kStages) & 1u;
+          tc::mbar_wait(&empty[s], ph ^ 1u);
+          tc::mbar_expect_tx(&full[s], kStageBytes);
+          uint8_t* a = smem + s * kStageBytes;
+          tc::tma_load_2d(a, &tmA, &full[s], kb * BK, m0);
+          tc::tma_load_2d(a + BM * BK * 2, &tmB, &full[s], kb * BK, n0);
+        }
       }
     }
   } else if (warp == 1) {
     if (lane == 0) {
       constexpr uint32_t idesc = tc::umma_idesc_bf16(BM, BN);
-      for (int kb = 0; kb < KB; ++kb) {
-        const int s = kb % kStages;
-        const uint32_t ph = (uint32_t)(kb / kStages) & 1u;
-        tc::mbar_wait(&full[s], ph);
+      uint32_t it = 0, lt = 0;
+      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++lt) {
+        const uint32_t ab = lt & 1u, aph = (lt >> 1) & 1u;
+        tc::mbar_wait(&acc_empty[ab], aph ^ 1u);   // epilogue has drained this accumulator (passes on first use)
         tc::tc_fence_after();
-        const uint32_t a_addr = tc::smem_u32(smem + s * kStageBytes);
-        const uint64_t da = tc::umma_desc_k_sw128(a_addr);
-        const uint64_t db = tc::umma_desc_k_sw128(a_addr + BM * BK * 2);
+        const uint32_t tmem_acc = tmem_base + ab * BN;
+        for (int kb = 0; kb < KB; ++kb, ++it) {
+          const int s = it % kStages;
+          const uint32_t ph = (it / kStages) & 1u;
+          tc::mbar_wait(&full[s], ph);
+          tc::tc_fence_after();
+          const uint32_t a_addr = tc::smem_u32(smem + s * kStageBytes);
+          const uint64_t da = tc::umma_desc_k_sw128(a_addr);
+          const uint64_t db = tc::umma_desc_k_sw128(a_addr + BM * BK * 2);
 #pragma unroll
-        for (int k = 0; k < BK / 16; ++k)   // +32 bytes (= 2 in the >>4 address field) per K=16 step inside the swizzle atom
-          tc::umma_bf16(tmem_acc, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), idesc, (kb | k) != 0);
-        tc::umma_commit(&empty[s]);
+          for (int k = 0; k < BK / 16; ++k)   // +32 bytes (= 2 in the >>4 address field) per K=16 step inside the swizzle atom
+            tc::umma_bf16(tmem_acc, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), idesc, (kb | k) != 0);
+          tc::umma_commit(&empty[s]);
+        }
+        tc::umma_commit(&acc_full[ab]);
       }
-      tc::umma_commit(acc_full);
     }
   } else {
-    // epilogue: warp w may only touch TMEM lanes [32*(w%4), +32)
+    // ---- epilogue warps: warp w may only touch TMEM lanes [32*(w%4), +32) ----
     const int q = warp & 3;
     const int row = q * 32 + lane;
-    const int m = m0 + row;
-    tc::mbar_wait(acc_full, 0);
-    tc::tc_fence_after();
+    const int et = threadIdx.x - 64;
+    const bool leader = et == 0;
+    if (STAGED) {   // pad columns of the staged image are written as zeros
+      __nv_bfloat16* r = reinterpret_cast<__nv_bfloat16*>(stage_out) + (int64_t)row * out_pitch;
+      for (int cidx = BN; cidx < (int)out_pitch; ++cidx) r[cidx] = __float2bfloat16(0.f);
+    }
+    uint32_t lt = 0;
+    int cur_n0 = -1;
+    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++lt) {
+      const int m0 = (tile / tiles_n) * BM, n0 = (tile % tiles_n) * BN;
+      const uint32_t ab = lt & 1u, aph = (lt >> 1) & 1u;
+      if (n0 != cur_n0) {   // (re)load the bias slice; all epilogue threads pass the barrier below before reading it
+        tc::named_bar_sync(2, 128);
+        bias_s[et] = __ldg(bias + n0 + et);
+        cur_n0 = n0;
+      }
+      if (STAGED && leader) tc::bulk_store_wait_read();   // previous tile's image has left smem
+      tc::named_bar_sync(1, 128);
+      tc::mbar_wait(&acc_full[ab], aph);
+      tc::tc_fence_after();
+      const int m = m0 + row;
 #pragma unroll 1
-    for (int c = 0; c < BN; c += 32) {
-      uint32_t r[32];
-      tc::tmem_ld_32x32(tmem_acc + ((uint32_t)(q * 32) << 16) + (uint32_t)c, r);
-      tc::tmem_ld_wait();
-      if (m < M) {
-        const float* bp = bias + n0 + c;
+      for (int c = 0; c < BN; c += 32) {
+        uint32_t r[32];
+        tc::tmem_ld_32x32(tmem_base + ab * BN + ((uint32_t)(q * 32) << 16) + (uint32_t)c, r);
+        tc::tmem_ld_wait();
         if (OUT_BF16) {
-          __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(out) + (int64_t)m * out_pitch + n0 + c;
+          __nv_bfloat16* o = STAGED ? reinterpret_cast<__nv_bfloat16*>(stage_out) + (int64_t)row * out_pitch + c
+                                    : reinterpret_cast<__nv_bfloat16*>(out) + (int64_t)m * out_pitch + n0 + c;
+          if (STAGED || m < M) {
 #pragma unroll
-          for (int v = 0; v < 4; ++v) {
-            uint4 pk;
-            pk.x = tc::pack_bf16(__uint_as_float(r[8 * v + 0]) + __ldg(bp + 8 * v + 0), __uint_as_float(r[8 * v + 1]) + __ldg(bp + 8 * v + 1));
-            pk.y = tc::pack_bf16(__uint_as_float(r[8 * v + 2]) + __ldg(bp + 8 * v + 2), __uint_as_float(r[8 * v + 3]) + __ldg(bp + 8 * v + 3));
-            pk.z = tc::pack_bf16(__uint_as_float(r[8 * v + 4]) + __ldg(bp + 8 * v + 4), __uint_as_float(r[8 * v + 5]) + __ldg(bp + 8 * v + 5));
-            pk.w = tc::pack_bf16(__uint_as_float(r[8 * v + 6]) + __ldg(bp + 8 * v + 6), __uint_as_float(r[8 * v + 7]) + __ldg(bp + 8 * v + 7));
-            *reinterpret_cast<uint4*>(o + 8 * v) = pk;
+            for (int v = 0; v < 4; ++v) {
+              uint4 pk;
+              pk.x = tc::pack_bf16(__uint_as_float(r[8 * v + 0]) + bias_s[c + 8 * v + 0], __uint_as_float(r[8 * v + 1]) + bias_s[c + 8 * v + 1]);
+              pk.y = tc::pack_bf16(__uint_as_float(r[8 * v + 2]) + bias_s[c + 8 * v + 2], __uint_as_float(r[8 * v + 3]) + bias_s[c + 8 * v + 3]);
+              pk.z = tc::pack_bf16(__uint_as_float(r[8 * v + 4]) + bias_s[c + 8 * v + 4], __uint_as_float(r[8 * v + 5]) + bias_s[c + 8 * v + 5]);
+              pk.w = tc::pack_bf16(__uint_as_float(r[8 * v + 6]) + bias_s[c + 8 * v + 6], __uint_as_float(r[8 * v + 7]) + bias_s[c + 8 * v + 7]);
+              *reinterpret_cast<uint4*>(o + 8 * v) = pk;
+            }
           }
-        } else {
+        } else if (m < M) {
           float* o = reinterpret_cast<float*>(out) + (int64_t)m * out_pitch + n0 + c;
 #pragma unroll
           for (int v = 0; v < 8; ++v) {
             float4 f;
-            f.x = __uint_as_float(r[4 * v + 0]) + __ldg(bp + 4 * v + 0);
-            f.y = __uint_as_float(r[4 * v + 1]) + __ldg(bp + 4 * v + 1);
-            f.z = __uint_as_float(r[4 * v + 2]) + __ldg(bp + 4 * v + 2);
-            f.w = __uint_as_float(r[4 * v + 3]) + __ldg(bp + 4 * v + 3);
+            f.x = __uint_as_float(r[4 * v + 0]) + bias_s[c + 4 * v + 0];
+            f.y = __uint_as_float(r[4 * v + 1]) + bias_s[c + 4 * v + 1];
+            f.z = __uint_as_float(r[4 * v + 2]) + bias_s[c + 4 * v + 2];
+            f.w = __uint_as_float(r[4 * v + 3]) + bias_s[c + 4 * v + 3];
             *reinterpret_cast<float4*>(o + 4 * v) = f;
           }
         }
       }
+      // accumulator fully read: hand it back to the MMA warp
+      tc::tc_fence_before();
+      __syncwarp();
+      if (lane == 0) tc::mbar_arrive(&acc_empty[ab]);
+      if (STAGED) {
+        tc::fence_proxy_async();          // generic-proxy smem writes -> visible to the bulk (async proxy) store
+        tc::named_bar_sync(1, 128);
+        if (leader) {
+          const int rows = min(BM, M - m0);
+          tc::bulk_store_1d(reinterpret_cast<__nv_bfloat16*>(out) + (int64_t)m0 * out_pitch, stage_out,
+                            (uint32_t)(rows * out_pitch * 2));
+        }
+      }
     }
+    if (STAGED && leader) tc::bulk_store_wait_all();
   }
   tc::tc_fence_before();
   __syncthreads();
-  if (warp == 1) tc::tmem_dealloc(tmem_acc, BN);
+  if (warp == 1) tc::tmem_dealloc(tmem_base, 2 * BN);
 }
 
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
@@ -146,6 +206,23 @@ EncodeTiledFn encode_tiled_fn() {
       fn = reinterpret_cast<EncodeTiledFn>(p);
   }
   return fn;
+}
+
+template <bool OUT_BF16, bool STAGED>
+int launch_gemm_tc(cudaStream_t st, const CUtensorMap& tmA, const CUtensorMap& tmB, const float* bias, void* out, int64_t pitch,
+                   int M, int N, int K) {
+  const int smem = gemm_smem_bytes(STAGED, (int)pitch);
+  static int configured = 0;
+  if (smem > configured) {
+    XF_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<OUT_BF16, STAGED>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    configured = smem;
+  }
+  const int tiles = ((M + BM - 1) / BM) * (N / BN);
+  const int grid = tiles < num_sms() ? tiles : num_sms();
+  gemm_tc_kernel<OUT_BF16, STAGED><<<grid, kGemmThreads, smem, st>>>(tmA, tmB, bias, out, pitch, M, N, K);
+  count_launch();
+  XF_LAUNCH_CHECK();
+  return XATTN_OK;
 }
 
 }  // namespace
@@ -170,23 +247,14 @@ int gemm_tc_bf16(cudaStream_t st, const void* X, const void* W, const float* bia
   if (M <= 0) return XATTN_OK;
   if (N % BN != 0 || K % BK != 0)
     XF_FAIL(XATTN_ERR_SHAPE, "tcgen05 projection GEMM needs N %% 128 == 0 and K %% 64 == 0 (N=%d K=%d)", N, K);
+  if (out_pitch < N || (out_bf16 && out_pitch % 8 != 0) || (!out_bf16 && out_pitch % 4 != 0))
+    XF_FAIL(XATTN_ERR_SHAPE, "output pitch %lld must be >= N and keep rows 16-byte aligned", (long long)out_pitch);
   alignas(64) CUtensorMap tmA, tmB;
   XF_TRY(make_tmap_bf16_2d(&tmA, X, M, K, BM, BK));
   XF_TRY(make_tmap_bf16_2d(&tmB, W, N, K, BN, BK));
-  static bool configured = false;
-  if (!configured) {
-    XF_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
-    XF_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
-    configured = true;
-  }
-  dim3 grid((M + BM - 1) / BM, N / BN);
-  if (out_bf16)
-    gemm_tc_kernel<true><<<grid, kGemmThreads, kSmemBytes, st>>>(tmA, tmB, bias, out, out_pitch, M, N, K);
-  else
-    gemm_tc_kernel<false><<<grid, kGemmThreads, kSmemBytes, st>>>(tmA, tmB, bias, out, out_pitch, M, N, K);
-  count_launch();
-  XF_LAUNCH_CHECK();
-  return XATTN_OK;
+  if (out_bf16 && N == BN && out_pitch <= kMaxStagePitch) return launch_gemm_tc<true, true>(st, tmA, tmB, bias, out, out_pitch, M, N, K);
+  if (out_bf16) return launch_gemm_tc<true, false>(st, tmA, tmB, bias, out, out_pitch, M, N, K);
+  return launch_gemm_tc<false, false>(st, tmA, tmB, bias, out, out_pitch, M, N, K);
 }
 
 }  // namespace xf

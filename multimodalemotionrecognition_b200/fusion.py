@@ -274,7 +274,7 @@ class XAttnKernelsMixin:
         """Shapes the bf16 tensor-core kernels are specialised for (csrc/bf16_pack.cu: bf16_supported)."""
         hw = self.d_model if self.xattn_head == "gated" else self.common_dim
         return (self.d_model == 128 and self.num_heads == 4 and T <= 16 and Ta <= 160 and self.v_dim % 64 == 0
-                and self.audio_sequence_dim % 64 == 0 and hw <= 256 and self.num_classes <= 16
+                and self.audio_sequence_dim % 64 == 0 and hw <= 256 and hw % 64 == 0 and self.num_classes <= 16
                 and self._prior_hidden <= 128 and self._prior_dim <= 32)
 
     def _pick_precision(self, io_dtype: int, need_grad: bool, T: int = 16, Ta: int = 149) -> int:

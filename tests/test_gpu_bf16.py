@@ -85,7 +85,17 @@ def _stage_report(m, xvb, xab, head, prior, dev):
     rep["a0"] = np.abs(w["a0"][:, :128].reshape(B, Ta, 128) - taps["a"]).max()
     _, p1 = xattn_oracle.multihead_attention(sd, "v2a_attn.", taps["v"], taps["a"], 4, taps["v2a_bias"], return_probs=True)
     u_ref = np.einsum("bhls,bse->bhle", p1, taps["a"])                       # U_h = P_h · a0
-    rep["u"] = np.abs(w["u"].reshape(B, 4, 16, 128)[:, :, :T] - u_ref).max()
+    # U is stored in mma A-fragment order [clip][head][lane][ks][reg] x (2 bf16): lane = 4g+t, reg r -> row g+8(r&1),
+    # cols 16ks + 2t + 8(r>>1) + {0,1}
+    f = w["u"].reshape(B, 4, 32, 8, 4, 2)
+    u_got = np.zeros((B, 4, 16, 128), dtype=np.float32)
+    for lane in range(32):
+        g_, t_ = lane >> 2, lane & 3
+        for ks in range(8):
+            for r in range(4):
+                col = 16 * ks + 2 * t_ + 8 * (r >> 1)
+                u_got[:, :, g_ + 8 * (r & 1), col:col + 2] = f[:, :, lane, ks, r, :]
+    rep["u"] = np.abs(u_got[:, :, :T] - u_ref).max()
     rep["pooled_v"] = np.abs(w["pooled"][:, :128] - taps["v_emb"]).max()
     rep["pooled_a"] = np.abs(w["pooled"][:, 128:] - taps["a_emb"]).max()
     rep["logits"] = np.abs(logits.cpu().numpy() - ref).max()
