@@ -26,7 +26,7 @@
 extern "C" {
 #endif
 
-#define XATTN_ABI_VERSION 4
+#define XATTN_ABI_VERSION 5
 
 #if defined(__GNUC__)
 #define XATTN_API __attribute__((visibility("default")))
@@ -210,6 +210,13 @@ XATTN_API int flat_head_forward(const flat_head_config* cfg, const float* params
 /* ---- diagnostics ---------------------------------------------------------------------------------- */
 /* Kernel launches issued by this library since process start (bench.py's gpu_launches evidence). */
 XATTN_API unsigned long long xattn_launch_count(void);
+/* Per-kernel timing of xattn_forward(precision = BF16).  While enabled, every kernel of the forward is bracketed by a
+ * pair of CUDA events recorded on the caller's stream; xattn_stage_timing_read waits for them, writes the summed
+ * milliseconds and bracket counts of up to `cap` stages (order: xattn_stage_name(i)), clears the record and returns
+ * the number of stages.  bench.py's roofline durations come from here.  Not thread-safe; leave off in production. */
+XATTN_API int xattn_stage_timing(int32_t enable);
+XATTN_API int xattn_stage_timing_read(double* ms_total, int64_t* launches, int32_t cap);
+XATTN_API const char* xattn_stage_name(int32_t i);
 /* The tcgen05/TMA projection GEMM on its own: Y[M,N] = X[M,K]·W[N,K]^T + bias (X, W bf16; Y bf16 or fp32 with row
  * pitch out_pitch in elements; N % 128 == 0, K % 64 == 0).  This is the kernel behind v_in_proj (fusion.py:372) and
  * a_in_proj∘audio_seq_proj (:378, :386) in xattn_forward(precision = BF16); exported so tests can pin it in isolation. */

@@ -12,7 +12,7 @@ from pathlib import Path
 
 LIB_NAME = "libxattn_fusion.so"
 LIB_PATH = Path(__file__).resolve().parent / LIB_NAME
-ABI_VERSION = 4
+ABI_VERSION = 5
 
 # xattn_status
 OK, ERR_SHAPE, ERR_DTYPE, ERR_ALIGN, ERR_ARCH, ERR_CUDA, ERR_WORKSPACE, ERR_NULL = range(8)
@@ -74,6 +74,9 @@ _EXPORTS = {
     "xattn_abi_version": (C.c_int, []),
     "xattn_last_error": (C.c_char_p, []),
     "xattn_launch_count": (C.c_ulonglong, []),
+    "xattn_stage_timing": (C.c_int, [C.c_int32]),
+    "xattn_stage_timing_read": (C.c_int, [C.POINTER(C.c_double), C.POINTER(C.c_int64), C.c_int32]),
+    "xattn_stage_name": (C.c_char_p, [C.c_int32]),
     "xattn_param_layout": (C.c_int, [C.POINTER(XAttnConfig), C.POINTER(C.c_int64), C.POINTER(C.c_int64), C.POINTER(C.c_int64)]),
     "xattn_workspace_bytes": (C.c_int, [C.POINTER(XAttnConfig), C.POINTER(C.c_int64)]),
     "xattn_packed_bytes": (C.c_int, [C.POINTER(XAttnConfig), C.POINTER(C.c_int64)]),
@@ -132,6 +135,20 @@ def check(status: int) -> None:
     if status in (ERR_SHAPE, ERR_DTYPE, ERR_ALIGN, ERR_NULL):
         raise ValueError(msg)
     raise RuntimeError(msg)
+
+
+def stage_timing(enable: bool) -> None:
+    """Turn the per-kernel CUDA-event brackets of the bf16 forward on or off (diagnostics; see xattn_stage_timing)."""
+    check(load().xattn_stage_timing(1 if enable else 0))
+
+
+def stage_timing_read() -> dict:
+    """{stage name: (total ms, brackets)} since the last enable/read; waits for the recorded events."""
+    lib = load()
+    ms = (C.c_double * 16)()
+    n = (C.c_int64 * 16)()
+    k = lib.xattn_stage_timing_read(ms, n, 16)
+    return {lib.xattn_stage_name(i).decode(): (float(ms[i]), int(n[i])) for i in range(k)}
 
 
 def launch_count() -> int:

@@ -20,6 +20,12 @@ extern "C" XATTN_API const char* xattn_last_error(void) { return xf::last_error(
 // gpu_launches evidence).
 extern "C" XATTN_API unsigned long long xattn_launch_count(void) { return xf::g_launch_count; }
 
+extern "C" XATTN_API int xattn_stage_timing(int32_t enable) { return xf::stage_timing_enable(enable); }
+extern "C" XATTN_API int xattn_stage_timing_read(double* ms_total, int64_t* launches, int32_t cap) {
+  return xf::stage_timing_read(ms_total, launches, cap);
+}
+extern "C" XATTN_API const char* xattn_stage_name(int32_t i) { return xf::stage_name(i); }
+
 extern "C" XATTN_API int xattn_param_layout(const xattn_config* cfg, int64_t* offsets, int64_t* sizes, int64_t* total_floats) {
   XF_TRY(validate_config(cfg));
   ParamLayout L;

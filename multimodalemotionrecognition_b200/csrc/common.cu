@@ -4,10 +4,53 @@
 #include <stdarg.h>
 #include <string.h>
 
+#include <vector>
+
 namespace xf {
 
 static thread_local char g_err[512] = "";
 unsigned long long g_launch_count = 0;
+
+bool g_stage_timing = false;
+static std::vector<cudaEvent_t> g_stage_ev[ST_COUNT][2];
+static const char* const kStageNames[ST_COUNT] = {"gemm_v0", "gemm_a0", "video_pre", "v2a_attn", "video_update", "a2v_attn", "head"};
+
+static void stage_drop() {
+  for (int s = 0; s < ST_COUNT; ++s)
+    for (int e = 0; e < 2; ++e) {
+      for (cudaEvent_t ev : g_stage_ev[s][e]) cudaEventDestroy(ev);
+      g_stage_ev[s][e].clear();
+    }
+}
+void stage_mark(int stage, int end, cudaStream_t st) {
+  cudaEvent_t ev;
+  if (cudaEventCreate(&ev) != cudaSuccess) return;
+  cudaEventRecord(ev, st);
+  g_stage_ev[stage][end].push_back(ev);
+}
+int stage_timing_enable(int on) {
+  stage_drop();
+  g_stage_timing = on != 0;
+  return XATTN_OK;
+}
+const char* stage_name(int i) { return i >= 0 && i < ST_COUNT ? kStageNames[i] : ""; }
+// Sums the elapsed time of every bracket recorded since the last enable/read; waits for the events.
+int stage_timing_read(double* ms, int64_t* launches, int cap) {
+  for (int s = 0; s < ST_COUNT && s < cap; ++s) {
+    double tot = 0.0;
+    const size_t n = g_stage_ev[s][1].size() < g_stage_ev[s][0].size() ? g_stage_ev[s][1].size() : g_stage_ev[s][0].size();
+    for (size_t i = 0; i < n; ++i) {
+      float t = 0.f;
+      XF_CUDA(cudaEventSynchronize(g_stage_ev[s][1][i]));
+      XF_CUDA(cudaEventElapsedTime(&t, g_stage_ev[s][0][i], g_stage_ev[s][1][i]));
+      tot += t;
+    }
+    if (ms) ms[s] = tot;
+    if (launches) launches[s] = (int64_t)n;
+  }
+  stage_drop();
+  return ST_COUNT;
+}
 
 void set_error(const char* fmt, ...) {
   va_list ap;

@@ -51,6 +51,24 @@ int num_sms();
 extern unsigned long long g_launch_count;
 inline void count_launch(int n = 1) { g_launch_count += (unsigned long long)n; }
 
+// Optional per-stage CUDA-event timing of the bf16 forward (xattn_stage_timing): bench.py's live per-kernel durations.
+enum { ST_GEMM_V0 = 0, ST_GEMM_A0, ST_VIDEO_PRE, ST_V2A, ST_VIDEO_UPD, ST_A2V, ST_HEAD, ST_COUNT };
+extern bool g_stage_timing;
+void stage_mark(int stage, int end, cudaStream_t st);   // records an event on st (no-op unless timing is on)
+struct StageScope {
+  int s;
+  cudaStream_t st;
+  StageScope(int stage, cudaStream_t stream) : s(stage), st(stream) {
+    if (g_stage_timing) stage_mark(s, 0, st);
+  }
+  ~StageScope() {
+    if (g_stage_timing) stage_mark(s, 1, st);
+  }
+};
+int stage_timing_enable(int on);
+int stage_timing_read(double* ms, int64_t* launches, int cap);
+const char* stage_name(int i);
+
 // ---- parameter layout ----------------------------------------------------------------------------
 struct ParamLayout {
   int64_t off[XP_COUNT];

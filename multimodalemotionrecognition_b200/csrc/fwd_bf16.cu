@@ -21,53 +21,87 @@ struct HeadPooledArgs {
 
 // concat head: Linear(2E->HW), ReLU, (Dropout eval), Linear(HW->C)                       (fusion.py:405-407)
 // gated head : g = sigmoid(Linear(E->1)(ReLU(Linear(2E->E)))), fused = g*v + (1-g)*a, Linear(E->C)   (:408-411)
+// Layer 0 runs on bf16 mma.sync with M = the 16 clips of the CTA.  The fp32 activations are split once into a hi + lo bf16
+// pair (two MMAs per step) so only the weights are rounded, as everywhere else on this path.  Row pitches are chosen so
+// that the eight rows a fragment load touches fall in different banks.
+constexpr int kXP = 2 * BE + 8;    // bf16 pitch of the split activations (528 B: row g -> bank 4g)
+constexpr int kHP = 256 + 4;       // fp32 pitch of hid / final-layer weights
 __global__ void __launch_bounds__(256) head_pooled_kernel(HeadPooledArgs a) {
-  __shared__ __align__(16) float pooled[kHeadClips][2 * BE];
-  __shared__ __align__(16) float hid[kHeadClips][256];
+  // xhi/xlo (layer-0 operands) and wl (final linear, [C][K]) are live in different phases and share one region.
+  __shared__ __align__(16) unsigned char region[2 * kHeadClips * kXP * 2 > 16 * kHP * 4 ? 2 * kHeadClips * kXP * 2 : 16 * kHP * 4];
+  __shared__ __align__(16) float hid[kHeadClips][kHP];
+  auto xhi = reinterpret_cast<__nv_bfloat16(*)[kXP]>(region);
+  auto xlo = reinterpret_cast<__nv_bfloat16(*)[kXP]>(region + kHeadClips * kXP * 2);
+  auto wl = reinterpret_cast<float(*)[kHP]>(region);
   __shared__ float gate[kHeadClips];
   const int tid = threadIdx.x, c0 = blockIdx.x * kHeadClips;
   const int nc = min(kHeadClips, a.B - c0);
-  for (int i = tid; i < kHeadClips * 2 * BE; i += blockDim.x) {
-    const int cc = i / (2 * BE);
-    pooled[cc][i % (2 * BE)] = cc < nc ? a.pooled[(int64_t)(c0 + cc) * 2 * BE + (i % (2 * BE))] : 0.f;
+  const float* wfin = a.gated ? a.wc : a.w1;
+  const float* bfin = a.gated ? a.bc : a.b1;
+  const int K = a.gated ? BE : a.HW;
+  for (int i = tid; i < kHeadClips * 2 * BE / 2; i += blockDim.x) {
+    const int cc = i / BE, k = (i % BE) * 2;
+    float2 x = make_float2(0.f, 0.f);
+    if (cc < nc) x = *reinterpret_cast<const float2*>(a.pooled + (int64_t)(c0 + cc) * 2 * BE + k);
+    const __nv_bfloat162 h = __floats2bfloat162_rn(x.x, x.y);
+    *reinterpret_cast<__nv_bfloat162*>(&xhi[cc][k]) = h;
+    *reinterpret_cast<__nv_bfloat162*>(&xlo[cc][k]) = __floats2bfloat162_rn(x.x - __low2float(h), x.y - __high2float(h));
+  }
+  float4 wpre[4];   // final-layer weights, fetched now and parked in smem once layer 0 is done with the region (C*K <= 4096)
+#pragma unroll
+  for (int r = 0; r < 4; ++r) {
+    const int i = tid + r * 256;
+    wpre[r] = i < a.C * K / 4 ? __ldg(reinterpret_cast<const float4*>(wfin) + i) : make_float4(0.f, 0.f, 0.f, 0.f);
   }
   __syncthreads();
   {
-    // hid = relu(pooled · W0^T + b0) with bf16 mma.sync: M = the 16 clips, N = HW, K = 2E.  The fp32 activations are fed as
-    // a hi + lo bf16 pair (two MMAs) so only the weights are rounded, as everywhere else on this path.
     const int warp = tid >> 5, lane = tid & 31, g = lane >> 2, t = lane & 3;
     const int ntw = a.HW / 64;   // n-tiles per warp (8 warps)
+    // The weight fragments of a tile are fetched with volatile loads, all 32 in flight at once and one tile ahead of the
+    // MMAs that use them; left to the compiler they trail their use by two steps and every step waits out an L2 round trip.
+    auto fetch = [&](uint32_t (&b)[2 * BE / 16][2], int nt) {
+      const __nv_bfloat16* wrow = a.w0b + (int64_t)(nt * 8 + g) * (2 * BE) + 2 * t;
+#pragma unroll
+      for (int ks = 0; ks < 2 * BE / 16; ++ks) {
+        asm volatile("ld.global.nc.b32 %0, [%1];" : "=r"(b[ks][0]) : "l"(wrow + ks * 16));
+        asm volatile("ld.global.nc.b32 %0, [%1];" : "=r"(b[ks][1]) : "l"(wrow + ks * 16 + 8));
+      }
+    };
+    uint32_t b[2 * BE / 16][2], bn[2 * BE / 16][2];
+    fetch(b, warp * ntw);
     for (int n = 0; n < ntw; ++n) {
       const int nt = warp * ntw + n;
-      const __nv_bfloat16* wrow = a.w0b + (int64_t)(nt * 8 + g) * (2 * BE);
-      float d[4] = {0.f, 0.f, 0.f, 0.f};
-#pragma unroll 4
+      if (n + 1 < ntw) fetch(bn, nt + 1);
+      float d[4] = {0.f, 0.f, 0.f, 0.f}, e[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
       for (int ks = 0; ks < 2 * BE / 16; ++ks) {
         const int col = ks * 16 + 2 * t;
-        const uint32_t b0 = __ldg(reinterpret_cast<const uint32_t*>(wrow + col));
-        const uint32_t b1 = __ldg(reinterpret_cast<const uint32_t*>(wrow + col + 8));
-        const float2 x[4] = {*reinterpret_cast<const float2*>(&pooled[g][col]), *reinterpret_cast<const float2*>(&pooled[g + 8][col]),
-                             *reinterpret_cast<const float2*>(&pooled[g][col + 8]),
-                             *reinterpret_cast<const float2*>(&pooled[g + 8][col + 8])};
         uint32_t hi[4], lo[4];
-#pragma unroll
-        for (int i = 0; i < 4; ++i) {
-          const __nv_bfloat16 hx = __float2bfloat16(x[i].x), hy = __float2bfloat16(x[i].y);
-          hi[i] = tc::pack_bf16(x[i].x, x[i].y);
-          lo[i] = tc::pack_bf16(x[i].x - __bfloat162float(hx), x[i].y - __bfloat162float(hy));
-        }
-        tc::mma_bf16(d, hi, b0, b1);
-        tc::mma_bf16(d, lo, b0, b1);
+        hi[0] = *reinterpret_cast<const uint32_t*>(&xhi[g][col]);      hi[1] = *reinterpret_cast<const uint32_t*>(&xhi[g + 8][col]);
+        hi[2] = *reinterpret_cast<const uint32_t*>(&xhi[g][col + 8]);  hi[3] = *reinterpret_cast<const uint32_t*>(&xhi[g + 8][col + 8]);
+        lo[0] = *reinterpret_cast<const uint32_t*>(&xlo[g][col]);      lo[1] = *reinterpret_cast<const uint32_t*>(&xlo[g + 8][col]);
+        lo[2] = *reinterpret_cast<const uint32_t*>(&xlo[g][col + 8]);  lo[3] = *reinterpret_cast<const uint32_t*>(&xlo[g + 8][col + 8]);
+        tc::mma_bf16(d, hi, b[ks][0], b[ks][1]);
+        tc::mma_bf16(e, lo, b[ks][0], b[ks][1]);
       }
       const int col = nt * 8 + 2 * t;
-      const float c0 = a.b0[col], c1 = a.b0[col + 1];
-      hid[g][col] = fmaxf(d[0] + c0, 0.f);
-      hid[g][col + 1] = fmaxf(d[1] + c1, 0.f);
-      hid[g + 8][col] = fmaxf(d[2] + c0, 0.f);
-      hid[g + 8][col + 1] = fmaxf(d[3] + c1, 0.f);
+      const float c0b = a.b0[col], c1b = a.b0[col + 1];
+      hid[g][col] = fmaxf(d[0] + e[0] + c0b, 0.f);
+      hid[g][col + 1] = fmaxf(d[1] + e[1] + c1b, 0.f);
+      hid[g + 8][col] = fmaxf(d[2] + e[2] + c0b, 0.f);
+      hid[g + 8][col + 1] = fmaxf(d[3] + e[3] + c1b, 0.f);
+      if (n + 1 < ntw) {
+#pragma unroll
+        for (int ks = 0; ks < 2 * BE / 16; ++ks) { b[ks][0] = bn[ks][0]; b[ks][1] = bn[ks][1]; }
+      }
     }
   }
   __syncthreads();
+#pragma unroll
+  for (int r = 0; r < 4; ++r) {
+    const int i = tid + r * 256;
+    if (i < a.C * K / 4) *reinterpret_cast<float4*>(&wl[(i * 4) / K][(i * 4) % K]) = wpre[r];
+  }
   if (a.gated) {
     if (tid < kHeadClips) {
       float s = a.b1[0];
@@ -77,23 +111,24 @@ __global__ void __launch_bounds__(256) head_pooled_kernel(HeadPooledArgs a) {
     __syncthreads();
     for (int i = tid; i < kHeadClips * BE; i += blockDim.x) {   // fused overwrites hid[:, :E]
       const int cc = i / BE, e = i % BE;
-      hid[cc][e] = gate[cc] * pooled[cc][e] + (1.f - gate[cc]) * pooled[cc][BE + e];
+      float pv = 0.f, pa = 0.f;
+      if (cc < nc) {
+        pv = a.pooled[(int64_t)(c0 + cc) * 2 * BE + e];
+        pa = a.pooled[(int64_t)(c0 + cc) * 2 * BE + BE + e];
+      }
+      hid[cc][e] = gate[cc] * pv + (1.f - gate[cc]) * pa;
     }
-    __syncthreads();
   }
-  const float* w = a.gated ? a.wc : a.w1;
-  const float* b = a.gated ? a.bc : a.b1;
-  const int K = a.gated ? BE : a.HW;
+  __syncthreads();
   for (int o = tid; o < nc * a.C; o += blockDim.x) {
     const int cc = o / a.C, cls = o % a.C;
-    float s0 = b[cls], s1 = 0.f, s2 = 0.f, s3 = 0.f;
+    float s0 = bfin[cls], s1 = 0.f, s2 = 0.f, s3 = 0.f;
     for (int k = 0; k < K; k += 4) {
-      const float4 wv = __ldg(reinterpret_cast<const float4*>(w + (int64_t)cls * K + k));
+      const float4 wv = *reinterpret_cast<const float4*>(&wl[cls][k]);
       const float4 hv = *reinterpret_cast<const float4*>(&hid[cc][k]);
       s0 = fmaf(wv.x, hv.x, s0); s1 = fmaf(wv.y, hv.y, s1); s2 = fmaf(wv.z, hv.z, s2); s3 = fmaf(wv.w, hv.w, s3);
     }
-    const float s = (s0 + s1) + (s2 + s3);
-    a.logits[(int64_t)(c0 + cc) * a.C + cls] = s;
+    a.logits[(int64_t)(c0 + cc) * a.C + cls] = (s0 + s1) + (s2 + s3);
   }
 }
 
@@ -128,14 +163,20 @@ int forward_bf16(const xattn_config& c, const float* params, const void* packed,
   compute_ws_bf16(c, x.w);
   x.st = st;
   // v_in_proj (fusion.py:372) and a_in_proj∘audio_seq_proj (:378, :386) on tcgen05
-  XF_TRY(gemm_tc_bf16(st, xv, x.packed + x.pk.Wv, params + x.pl.off[XP_V_IN_B], x.ws + x.w.v0, false, BE, c.B * c.T, BE, c.Dv));
-  XF_TRY(gemm_tc_bf16(st, xa, x.packed + x.pk.Wfold, reinterpret_cast<const float*>(x.packed + x.pk.bfold), x.ws + x.w.a0, true,
-                      BEP, c.B * c.Ta, BE, c.Da));
-  XF_TRY(launch_video_pre(x));
-  XF_TRY(launch_v2a_attn(x));
-  XF_TRY(launch_video_update(x));
-  XF_TRY(launch_a2v_attn(x));
-  XF_TRY(launch_head_pooled(x, logits));
+  {
+    StageScope t(ST_GEMM_V0, st);
+    XF_TRY(gemm_tc_bf16(st, xv, x.packed + x.pk.Wv, params + x.pl.off[XP_V_IN_B], x.ws + x.w.v0, false, BE, c.B * c.T, BE, c.Dv));
+  }
+  {
+    StageScope t(ST_GEMM_A0, st);
+    XF_TRY(gemm_tc_bf16(st, xa, x.packed + x.pk.Wfold, reinterpret_cast<const float*>(x.packed + x.pk.bfold), x.ws + x.w.a0, true,
+                        BEP, c.B * c.Ta, BE, c.Da));
+  }
+  { StageScope t(ST_VIDEO_PRE, st); XF_TRY(launch_video_pre(x)); }
+  { StageScope t(ST_V2A, st); XF_TRY(launch_v2a_attn(x)); }
+  { StageScope t(ST_VIDEO_UPD, st); XF_TRY(launch_video_update(x)); }
+  { StageScope t(ST_A2V, st); XF_TRY(launch_a2v_attn(x)); }
+  { StageScope t(ST_HEAD, st); XF_TRY(launch_head_pooled(x, logits)); }
   return XATTN_OK;
 }
 
