@@ -47,9 +47,10 @@ def stage_model():
     qt = 4 * T * E_ * 2                        # one folded per-clip operand [H*T, E] bf16
     return {
         "gemm_v0": {"bytes": T * DV * 2 + T * E_ * 4, "flops": 2 * T * DV * E_},
-        "gemm_a0": {"bytes": TA * DA * 2 + TA * E_ * 2, "flops": 2 * TA * DA * E_},
+        "gemm_a0": {"bytes": TA * DA * 2 + TA * E_ * 2 + TA * 8, "flops": 2 * TA * DA * E_ + 4 * TA * E_},
         "video_pre": {"bytes": T * E_ * 4 + qt, "flops": 2 * tee},
-        "v2a_attn": {"bytes": TA * E_ * 2 + 2 * qt, "flops": 2 * (2 * H_ * T * TA * E_) + 4 * TA * E_},
+        "prior": {"bytes": 4 * E_ * 4 + E_ * 4 + 16, "flops": 2 * (2 * E_ * 64 + 64 * 8)},
+        "v2a_attn": {"bytes": TA * E_ * 2 + 2 * qt, "flops": 2 * (2 * H_ * T * TA * E_)},
         "video_update": {"bytes": 3 * qt + T * E_ * 4 + E_ * 4, "flops": 7 * tee},
         "a2v_attn": {"bytes": TA * E_ * 2 + 2 * qt + E_ * 4, "flops": 2 * (2 * TA * H_ * T * E_)},
         "head": {"bytes": 2 * E_ * 4 + NCLS * 4, "flops": 2 * (2 * E_ * HW_ + HW_ * NCLS)},

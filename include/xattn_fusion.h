@@ -26,7 +26,7 @@
 extern "C" {
 #endif
 
-#define XATTN_ABI_VERSION 5
+#define XATTN_ABI_VERSION 6
 
 #if defined(__GNUC__)
 #define XATTN_API __attribute__((visibility("default")))
@@ -222,6 +222,14 @@ XATTN_API const char* xattn_stage_name(int32_t i);
  * a_in_proj∘audio_seq_proj (:378, :386) in xattn_forward(precision = BF16); exported so tests can pin it in isolation. */
 XATTN_API int xattn_debug_gemm_tc(const void* X, const void* W, const float* bias, void* Y, int32_t out_bf16, int64_t out_pitch,
                         int32_t M, int32_t N, int32_t K, void* stream);
+
+/* Hardware probe of the tcgen05 features the attention kernels use (M = 64 accumulators in both halves of a TMEM
+ * sub-partition, MN-major B operand, hand-swizzled operand tiles, 16x256b TMEM loads): two products in one CTA,
+ * D_lo = A[0:64]·op(B[0]), D_hi = A[64:128]·op(B[1]); A [128,K] bf16; mode 0: B [2,N,K] (K-major), mode 1: B [2,K,N]
+ * (MN-major).  out32 [128,N] = raw TMEM lanes x columns (32x32b loads), out16 [2,4,32,64] = raw 16x256b.x16 registers
+ * (N >= 128).  Test-only; not on the product path. */
+XATTN_API int xattn_debug_umma_probe(const void* A, const void* B, float* out32, float* out16, int32_t N, int32_t K,
+                           int32_t mode, void* stream);
 
 #ifdef __cplusplus
 }

@@ -10,6 +10,9 @@ int adam_step(float* p, const float* g, float* m, float* v, int64_t n, float lr,
               int step, int decoupled, cudaStream_t st);
 }  // namespace xf
 
+namespace xf {
+int umma_probe(cudaStream_t st, const void* A, const void* B, float* out32, float* out16, int N, int K, int mode);
+}
 using namespace xf;
 
 static inline bool misaligned(const void* p) { return ((uintptr_t)p & 15) != 0; }
@@ -130,4 +133,11 @@ extern "C" XATTN_API int xattn_debug_gemm_tc(const void* X, const void* W, const
   if (misaligned(X) || misaligned(W) || misaligned(Y)) XF_FAIL(XATTN_ERR_ALIGN, "pointers must be 16-byte aligned");
   XF_TRY(check_device_sm100());
   return gemm_tc_bf16((cudaStream_t)stream, X, W, bias, Y, out_bf16 != 0, out_pitch, M, N, K);
+}
+
+extern "C" XATTN_API int xattn_debug_umma_probe(const void* A, const void* B, float* out32, float* out16, int32_t N, int32_t K,
+                                                int32_t mode, void* stream) {
+  XF_TRY(check_device_sm100());
+  if (!A || !B || !out32 || !out16) XF_FAIL(XATTN_ERR_NULL, "xattn_debug_umma_probe: null pointer");
+  return umma_probe(reinterpret_cast<cudaStream_t>(stream), A, B, out32, out16, N, K, mode);
 }

@@ -3,7 +3,7 @@
 // the key and the value operand, because the K/V projections are folded into the small per-clip operands Qt / Kt / Vt.
 // The whole score tile lives in registers: bias add (tanh of the emotion-prior token scores, fusion.py:175-176),
 // warp-shuffle softmax, and the P·V product run in one pass with bf16 mma.sync (fp32 accumulate, fp32 softmax/LayerNorm).
-//   v2a_attn_kernel : video queries audio (fusion.py:394) + the emotion prior network (:178-181)
+//   v2a_attn_kernel : video queries audio (fusion.py:394)
 //   a2v_attn_kernel : audio queries the updated video (:398), residual + LayerNorm (:399), temporal mean (:402)
 #include "bf16_layout.cuh"
 #include "frag.cuh"
@@ -18,30 +18,19 @@ constexpr int kOpBytes = 64 * BEP * 2;     // 17,408  (Qt / Kt / Vt)
 struct V2AArgs {
   const __nv_bfloat16* a0;   // [B*Ta, BEP]
   const __nv_bfloat16* qt;   // [B,64,BEP]
-  const float *meanv, *tqv;  // [B,E], [B,16]
-  const __nv_bfloat16* pw0b;            // prior_net.0.weight as bf16 [Hd,2E]
-  const __nv_bfloat16* wsc;             // [8,BEP] score-weight tile (rows 0,1 = w_ak, w_aq)
-  const float *pb0, *pw3, *pb3;         // prior_net.0 bias, prior_net.3
-  const float* wh[4];        // v_query, a_key, a_query, v_key bias heads: weight [E+P]
-  const float* bh[4];
+  const float *tqv, *tok, *pc;   // [B,16] w_vq·v0_i ; [B*Ta,2] (w_ak·a0_j, w_aq·a0_j) ; [B,4] prior parts of the bias heads
   const float* bias_scale;
   __nv_bfloat16* u;          // [B,64,E]
-  float *tqa, *pc;           // [B,BTAP], [B,4]
-  int B, Ta, T, P, Hd, use_prior;
+  int B, Ta, T, use_prior;
 };
 
 __global__ void __launch_bounds__(128, 3) v2a_attn_kernel(V2AArgs a) {
   extern __shared__ __align__(128) uint8_t sm[];
   __nv_bfloat16* a0s = reinterpret_cast<__nv_bfloat16*>(sm);
   __nv_bfloat16* qts = reinterpret_cast<__nv_bfloat16*>(sm + kA0Bytes);
-  __nv_bfloat16* wsc = reinterpret_cast<__nv_bfloat16*>(sm + kA0Bytes + kOpBytes);   // [8][BEP]: rows 0,1 = w_ak, w_aq
-  float* fsm = reinterpret_cast<float*>(sm + kA0Bytes + kOpBytes + 8 * BEP * 2);
-  float* ka_s = fsm;             // [160] raw a_key token scores
-  float* pooled0 = ka_s + BTAP;  // [256]
-  float* hid = pooled0 + 2 * BE; // [128]
-  float* prior = hid + 128;      // [32]
-  float* pc_s = prior + 32;      // [4]
-  float* qv_s = pc_s + 4;        // [16]
+  float* fsm = reinterpret_cast<float*>(sm + kA0Bytes + kOpBytes);
+  float* ka_s = fsm;             // [160] a_key token scores + prior part
+  float* qv_s = ka_s + BTAP;     // [16]  v_query token scores + prior part
   uint64_t* bar = reinterpret_cast<uint64_t*>(qv_s + 16);
   const int c = blockIdx.x, tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, g = lane >> 2, t = lane & 3;
   const int Ta = a.Ta;
@@ -52,105 +41,23 @@ __global__ void __launch_bounds__(128, 3) v2a_attn_kernel(V2AArgs a) {
   __syncthreads();
   if (tid == 0) {
     const uint32_t nb = (uint32_t)Ta * BEP * 2;
-    tc::mbar_expect_tx(bar, nb + kOpBytes + 8 * BEP * 2);
+    tc::mbar_expect_tx(bar, nb + kOpBytes);
     tc::bulk_load_1d(a0s, a.a0 + (int64_t)c * Ta * BEP, nb, bar);
     tc::bulk_load_1d(qts, a.qt + (int64_t)c * 64 * BEP, kOpBytes, bar);
-    tc::bulk_load_1d(wsc, a.wsc, 8 * BEP * 2, bar);
   }
   {   // zero the padding token rows while the copy is in flight
     uint4* z = reinterpret_cast<uint4*>(a0s + Ta * BEP);
     const int nz = (BTAP - Ta) * BEP * 2 / 16;
     for (int i = tid; i < nz; i += blockDim.x) z[i] = make_uint4(0, 0, 0, 0);
     if (a.use_prior) {
-      for (int i = tid; i < BE; i += blockDim.x) pooled0[i] = a.meanv[(int64_t)c * BE + i];
-      if (tid < 16) qv_s[tid] = a.tqv[(int64_t)c * 16 + tid];
+      const float pq = a.pc[(int64_t)c * 4 + 0], pk = a.pc[(int64_t)c * 4 + 1];
+      for (int i = tid; i < Ta; i += blockDim.x) ka_s[i] = a.tok[((int64_t)c * Ta + i) * 2] + pk;
+      if (tid < 16) qv_s[tid] = a.tqv[(int64_t)c * 16 + tid] + pq;
     }
   }
   __syncthreads();
   tc::mbar_wait(bar, 0);
   const uint32_t a0b = tc::smem_u32(a0s), qtb = tc::smem_u32(qts);
-
-  if (a.use_prior) {
-    // token scores w_ak·a0_j, w_aq·a0_j as a 160 x 8 product on the tensor cores (columns 0,1 used)
-    for (int mt = warp; mt < BTAP / 16; mt += 4) {
-      float d[4] = {0.f, 0.f, 0.f, 0.f};
-#pragma unroll
-      for (int ks = 0; ks < 8; ks += 2) {
-        uint32_t x0[4], x1[4], b[4];
-        fr::ldA(a0b, 16 * mt, ks, lane, x0);
-        fr::ldA(a0b, 16 * mt, ks + 1, lane, x1);
-        fr::ldB_nk(tc::smem_u32(wsc), 0, ks, lane, b);
-        tc::mma_bf16(d, x0, b[0], b[1]);
-        tc::mma_bf16(d, x1, b[2], b[3]);
-      }
-      if (t == 0) {
-        const int j = 16 * mt + g;
-        ka_s[j] = d[0]; ka_s[j + 8] = d[2];
-        a.tqa[(int64_t)c * BTAP + j] = d[1];
-        a.tqa[(int64_t)c * BTAP + j + 8] = d[3];
-      }
-    }
-    {   // mean_t a0 (fusion.py:180) on the tensor cores: ones[16 x Ta] · a0 — every result row is the column sum
-      const uint32_t ones[4] = {0x3F803F80u, 0x3F803F80u, 0x3F803F80u, 0x3F803F80u};
-      float d[4][4];
-#pragma unroll
-      for (int n = 0; n < 4; ++n) d[n][0] = d[n][1] = d[n][2] = d[n][3] = 0.f;
-#pragma unroll
-      for (int kk = 0; kk < BTAP / 16; ++kk) {
-#pragma unroll
-        for (int n2 = 0; n2 < 2; ++n2) {
-          uint32_t b[4];
-          fr::ldB_kn(a0b, 16 * kk, 2 * warp + n2, lane, b);
-          tc::mma_bf16(d[2 * n2], ones, b[0], b[1]);
-          tc::mma_bf16(d[2 * n2 + 1], ones, b[2], b[3]);
-        }
-      }
-      if (g == 0) {
-        const float inv = 1.f / (float)Ta;
-#pragma unroll
-        for (int n = 0; n < 4; ++n) {
-          pooled0[BE + (4 * warp + n) * 8 + 2 * t] = d[n][0] * inv;
-          pooled0[BE + (4 * warp + n) * 8 + 2 * t + 1] = d[n][1] * inv;
-        }
-      }
-    }
-    __syncthreads();
-    // prior_net: Linear(2E -> Hd), ReLU, (Dropout: eval identity), Linear(Hd -> P)   (fusion.py:158-163)
-    {
-      float x[8];
-#pragma unroll
-      for (int k = 0; k < 8; ++k) x[k] = pooled0[lane * 8 + k];
-      for (int uo = warp; uo < a.Hd; uo += 4) {
-        const uint4 wv = __ldg(reinterpret_cast<const uint4*>(a.pw0b + (int64_t)uo * 2 * BE) + lane);
-        const __nv_bfloat162* w2 = reinterpret_cast<const __nv_bfloat162*>(&wv);
-        float sacc = 0.f;
-#pragma unroll
-        for (int k = 0; k < 4; ++k) {
-          sacc = fmaf(__low2float(w2[k]), x[2 * k], sacc);
-          sacc = fmaf(__high2float(w2[k]), x[2 * k + 1], sacc);
-        }
-        sacc = warp_sum(sacc);
-        if (lane == 0) hid[uo] = fmaxf(sacc + a.pb0[uo], 0.f);
-      }
-    }
-    __syncthreads();
-    for (int p = warp; p < a.P; p += 4) {
-      const float* w = a.pw3 + (int64_t)p * a.Hd;
-      float s = 0.f;
-      for (int k = lane; k < a.Hd; k += 32) s = fmaf(__ldg(w + k), hid[k], s);
-      s = warp_sum(s);
-      if (lane == 0) prior[p] = s + a.pb3[p];
-    }
-    __syncthreads();
-    if (tid < 4) {   // prior part + bias of the four Linear(E+P -> 1) heads (fusion.py:171-174 decomposed)
-      const float* w = a.wh[tid] + BE;
-      float s = a.bh[tid][0];
-      for (int p = 0; p < a.P; ++p) s = fmaf(w[p], prior[p], s);
-      pc_s[tid] = s;
-      a.pc[(int64_t)c * 4 + tid] = s;
-    }
-    __syncthreads();
-  }
 
   // ---- scores of head `warp`: S[i, j] = Qt_h[i,:]·a0[j,:]  (+ bias), i < 16, j < 160 ----
   const int h = warp;
@@ -174,8 +81,7 @@ __global__ void __launch_bounds__(128, 3) v2a_attn_kernel(V2AArgs a) {
     }
     float m0 = -INFINITY, m1 = -INFINITY;
     const float bsc = a.use_prior ? a.bias_scale[0] : 0.f;
-    const float q0 = a.use_prior ? qv_s[g] + pc_s[0] : 0.f, q1 = a.use_prior ? qv_s[g + 8] + pc_s[0] : 0.f;
-    const float kc = a.use_prior ? pc_s[1] : 0.f;
+    const float q0 = a.use_prior ? qv_s[g] : 0.f, q1 = a.use_prior ? qv_s[g + 8] : 0.f;
 #pragma unroll
     for (int nt = 0; nt < BTAP / 8; ++nt) {
 #pragma unroll
@@ -183,7 +89,7 @@ __global__ void __launch_bounds__(128, 3) v2a_attn_kernel(V2AArgs a) {
         const int j = nt * 8 + 2 * t + e;
         if (j < Ta) {
           if (a.use_prior) {
-            const float kj = ka_s[j] + kc;
+            const float kj = ka_s[j];
             s[nt][e] += tc::tanh_fast(q0 + kj) * bsc;
             s[nt][2 + e] += tc::tanh_fast(q1 + kj) * bsc;
           }
@@ -242,7 +148,7 @@ __global__ void __launch_bounds__(128, 3) v2a_attn_kernel(V2AArgs a) {
 
 struct A2VArgs {
   const __nv_bfloat16 *a0, *kt, *vt;   // [B*Ta,BEP], [B,64,BEP] x2
-  const float *tqa, *tkv, *pc, *cv;    // [B,BTAP], [B,16], [B,4], [B,64]
+  const float *tok, *tkv, *pc, *cv;    // [B*Ta,2], [B,16], [B,4], [B,64]
   const float *bo2, *gam, *bet, *bias_scale;
   float* pooled;                       // [B,2E] (second E = pooled_a)
   int B, Ta, T, use_prior;
@@ -281,7 +187,7 @@ __global__ void __launch_bounds__(160, 2) a2v_attn_kernel(A2VArgs a) {
     const int nz = (BTAP - Ta) * BEP * 2 / 16;
     for (int i = tid; i < nz; i += blockDim.x) z[i] = make_uint4(0, 0, 0, 0);
     const float pq = a.use_prior ? a.pc[(int64_t)c * 4 + 2] : 0.f, pk = a.use_prior ? a.pc[(int64_t)c * 4 + 3] : 0.f;
-    for (int i = tid; i < BTAP; i += blockDim.x) qa_s[i] = (a.use_prior && i < Ta) ? a.tqa[(int64_t)c * BTAP + i] + pq : 0.f;
+    for (int i = tid; i < BTAP; i += blockDim.x) qa_s[i] = (a.use_prior && i < Ta) ? a.tok[((int64_t)c * Ta + i) * 2 + 1] + pq : 0.f;
     if (tid < 16) kv_s[tid] = a.use_prior ? a.tkv[(int64_t)c * 16 + tid] + pk : 0.f;
     if (tid < 64) cv_s[tid] = a.cv[(int64_t)c * 64 + tid];
     for (int i = tid; i < BE; i += blockDim.x) {
@@ -451,19 +357,13 @@ int launch_v2a_attn(const Bf16Ctx& x) {
   V2AArgs a;
   a.a0 = reinterpret_cast<const __nv_bfloat16*>(x.ws + x.w.a0);
   a.qt = reinterpret_cast<const __nv_bfloat16*>(x.ws + x.w.qt);
-  a.meanv = reinterpret_cast<const float*>(x.ws + x.w.meanv);
   a.tqv = reinterpret_cast<const float*>(x.ws + x.w.tqv);
-  a.pw0b = reinterpret_cast<const __nv_bfloat16*>(x.packed + x.pk.pW0);
-  a.wsc = reinterpret_cast<const __nv_bfloat16*>(x.packed + x.pk.wsc);
-  a.pb0 = P(XP_PRIOR0_B); a.pw3 = P(XP_PRIOR3_W); a.pb3 = P(XP_PRIOR3_B);
-  a.wh[0] = P(XP_VQ_W); a.bh[0] = P(XP_VQ_B); a.wh[1] = P(XP_AK_W); a.bh[1] = P(XP_AK_B);
-  a.wh[2] = P(XP_AQ_W); a.bh[2] = P(XP_AQ_B); a.wh[3] = P(XP_VK_W); a.bh[3] = P(XP_VK_B);
+  a.tok = reinterpret_cast<const float*>(x.ws + x.w.tok);
+  a.pc = reinterpret_cast<const float*>(x.ws + x.w.pc);
   a.bias_scale = P(XP_BIAS_SCALE);
   a.u = reinterpret_cast<__nv_bfloat16*>(x.ws + x.w.u);
-  a.tqa = reinterpret_cast<float*>(x.ws + x.w.tqa);
-  a.pc = reinterpret_cast<float*>(x.ws + x.w.pc);
-  a.B = c.B; a.Ta = c.Ta; a.T = c.T; a.P = c.prior_dim; a.Hd = c.prior_hidden; a.use_prior = c.use_prior;
-  const int smem = kA0Bytes + kOpBytes + 8 * BEP * 2 + (BTAP + 2 * BE + 128 + 32 + 4 + 16) * 4 + 16;
+  a.B = c.B; a.Ta = c.Ta; a.T = c.T; a.use_prior = c.use_prior;
+  const int smem = kA0Bytes + kOpBytes + (BTAP + 16) * 4 + 16;
   static bool configured = false;
   if (!configured) {
     XF_CUDA(cudaFuncSetAttribute(v2a_attn_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
@@ -482,7 +382,7 @@ int launch_a2v_attn(const Bf16Ctx& x) {
   a.a0 = reinterpret_cast<const __nv_bfloat16*>(x.ws + x.w.a0);
   a.kt = reinterpret_cast<const __nv_bfloat16*>(x.ws + x.w.kt);
   a.vt = reinterpret_cast<const __nv_bfloat16*>(x.ws + x.w.vt);
-  a.tqa = reinterpret_cast<const float*>(x.ws + x.w.tqa);
+  a.tok = reinterpret_cast<const float*>(x.ws + x.w.tok);
   a.tkv = reinterpret_cast<const float*>(x.ws + x.w.tkv);
   a.pc = reinterpret_cast<const float*>(x.ws + x.w.pc);
   a.cv = reinterpret_cast<const float*>(x.ws + x.w.cv);

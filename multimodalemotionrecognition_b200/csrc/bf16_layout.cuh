@@ -3,9 +3,11 @@
 // Data flow per clip (reference src/models/fusion.py:372-411), B clips per launch:
 //   gemm_tc   v0  = video_emb · Wv^T + b                      [T,128]  fp32           :372
 //   gemm_tc   a0  = audio_emb · (W_in·W_seq)^T + b_fold         [Ta,128] bf16, row pitch 136       :378 + :386 folded
+//               + epilogue extras: token scores (w_ak·a0_j, w_aq·a0_j) and per-clip column sums of a0 (-> mean_t a0, :180)
 //   video_pre   Qt_h = (scale·(v0·Wq1^T + bq1))_h · Wk1_h       [64,128] bf16 — so that  Q_h·K_h^T = Qt_h · a0^T   (:394)
 //               + mean_t v0, w_vq·v0_i, w_vk·v0_i  (emotion prior inputs, :171-181)
-//   v2a_attn    prior MLP + bias, S = Qt·a0^T + tanh(qv_i+ka_j)·s, softmax, U_h = P_h · a0             [64,128] bf16
+//   prior       prior_net([mean_t v0 ; mean_t a0]) and the prior parts of the four bias heads, 16 clips per CTA  (:158-181)
+//   v2a_attn    S = Qt·a0^T + tanh(qv_i+ka_j)·s, softmax, U_h = P_h · a0                               [64,128] bf16
 //   video_upd   O = U_h·Wv1_h^T + bv1 ; out_proj ; v1 = LN(v0 + ·) (:395) ; pooled_v ; K2,V2 = v1·W^T+b ;
 //               Kt_h = scale·K2_h·Wq2_h , c_hi = scale·K2_h[i]·bq2_h , Vt_h = V2_h·Wo2_h^T              [64,128] bf16 each
 //   a2v_attn    S = a0·Kt^T + c + tanh(qa_j+kv_i)·s, softmax over the 16 keys of each head, out = P·Vt + bo2,
@@ -31,7 +33,7 @@ struct PackBf16 {
   int64_t Wq1, Wk1, Wv1, Wo1, Wk2, Wv2, Wq2, Wo2;    // bf16 [E,BEP] each (torch [out,in] layout, padded pitch)
   int64_t W0b;                                       // bf16 [HW,2E]: head layer 0 (xattn_mlp.0 / xattn_gate.0) weight
   int64_t pW0;                                       // bf16 [Hd,2E]: prior_net.0.weight (0 bytes without the prior)
-  int64_t wsc;                                       // bf16 [8,BEP]: rows 0,1 = a_key / a_query score weights (first E entries)
+  int64_t scw;                                       // f32 [2,E]: a_key_bias / a_query_bias weights, token part (first E entries)
   int64_t scratch;                                   // f32 [E,Da] temp of the fold
   int64_t total;
 };
@@ -45,7 +47,8 @@ struct WsBf16 {
   int64_t meanv;    // f32  [B,E]
   int64_t tqv, tkv; // f32  [B,16]
   int64_t u;        // bf16 [B,64,E]
-  int64_t tqa;      // f32  [B,BTAP]
+  int64_t tok;      // f32  [B*Ta,2]   (w_ak·a0_j, w_aq·a0_j) from the a0 GEMM epilogue
+  int64_t acol;     // f32  [B,3,E]    column sums of a0 per clip and output tile (gemm_tc.cuh)
   int64_t pc;       // f32  [B,4]
   int64_t kt, vt;   // bf16 [B,64,BEP]
   int64_t cv;       // f32  [B,64]
@@ -68,6 +71,7 @@ struct Bf16Ctx {
   cudaStream_t st;
 };
 int launch_video_pre(const Bf16Ctx& x);
+int launch_prior(const Bf16Ctx& x);
 int launch_v2a_attn(const Bf16Ctx& x);
 int launch_video_update(const Bf16Ctx& x);
 int launch_a2v_attn(const Bf16Ctx& x);

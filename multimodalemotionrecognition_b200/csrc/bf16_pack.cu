@@ -41,7 +41,7 @@ void compute_pack_bf16(const xattn_config& c, PackBf16& p) {
   p.Wk2 = take(E * BEP * 2); p.Wv2 = take(E * BEP * 2); p.Wq2 = take(E * BEP * 2); p.Wo2 = take(E * BEP * 2);
   p.W0b = take(HW * 2 * E * 2);
   p.pW0 = take((int64_t)(c.use_prior ? c.prior_hidden : 0) * 2 * E * 2);
-  p.wsc = take(8 * BEP * 2);
+  p.scw = take(2 * E * 4);
   p.scratch = take(E * c.Da * 4);
   p.total = off;
 }
@@ -61,7 +61,8 @@ void compute_ws_bf16(const xattn_config& c, WsBf16& w) {
   w.tqv = take(B * 16 * 4);
   w.tkv = take(B * 16 * 4);
   w.u = take(B * 64 * E * 2);
-  w.tqa = take(B * BTAP * 4);
+  w.tok = take(B * c.Ta * 2 * 4);
+  w.acol = take(B * 3 * E * 4);
   w.pc = take(B * 4 * 4);
   w.kt = take(B * 64 * BEP * 2);
   w.vt = take(B * 64 * BEP * 2);
@@ -142,11 +143,11 @@ int pack_weights_bf16(const xattn_config& c, const float* params, void* packed_v
   cvt(P(XP_A2V_OUT_W), E, pk.Wo2, BEP, E, E);
   const int HW = c.head_kind == XATTN_HEAD_GATED ? E : c.common_dim;
   cvt(P(XP_HEAD0_W), 2 * E, pk.W0b, 2 * E, HW, 2 * E);
-  XF_CUDA(cudaMemsetAsync(packed + pk.wsc, 0, 8 * BEP * 2, st));
+  XF_CUDA(cudaMemsetAsync(packed + pk.scw, 0, 2 * E * 4, st));
   if (c.use_prior) {
     cvt(P(XP_PRIOR0_W), 2 * E, pk.pW0, 2 * E, c.prior_hidden, 2 * E);
-    cvt(P(XP_AK_W), E, pk.wsc, BEP, 1, E);                 // row 0: a_key_bias.weight[:E]
-    cvt(P(XP_AQ_W), E, pk.wsc + BEP * 2, BEP, 1, E);       // row 1: a_query_bias.weight[:E]
+    XF_CUDA(cudaMemcpyAsync(packed + pk.scw, P(XP_AK_W), E * 4, cudaMemcpyDeviceToDevice, st));           // a_key_bias.weight[:E]
+    XF_CUDA(cudaMemcpyAsync(packed + pk.scw + E * 4, P(XP_AQ_W), E * 4, cudaMemcpyDeviceToDevice, st));   // a_query_bias.weight[:E]
   }
   XF_LAUNCH_CHECK();
   return XATTN_OK;

@@ -13,7 +13,7 @@ unsigned long long g_launch_count = 0;
 
 bool g_stage_timing = false;
 static std::vector<cudaEvent_t> g_stage_ev[ST_COUNT][2];
-static const char* const kStageNames[ST_COUNT] = {"gemm_v0", "gemm_a0", "video_pre", "v2a_attn", "video_update", "a2v_attn", "head"};
+static const char* const kStageNames[ST_COUNT] = {"gemm_v0", "gemm_a0", "video_pre", "prior", "v2a_attn", "video_update", "a2v_attn", "head"};
 
 static void stage_drop() {
   for (int s = 0; s < ST_COUNT; ++s)

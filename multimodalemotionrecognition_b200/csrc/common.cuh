@@ -52,7 +52,7 @@ extern unsigned long long g_launch_count;
 inline void count_launch(int n = 1) { g_launch_count += (unsigned long long)n; }
 
 // Optional per-stage CUDA-event timing of the bf16 forward (xattn_stage_timing): bench.py's live per-kernel durations.
-enum { ST_GEMM_V0 = 0, ST_GEMM_A0, ST_VIDEO_PRE, ST_V2A, ST_VIDEO_UPD, ST_A2V, ST_HEAD, ST_COUNT };
+enum { ST_GEMM_V0 = 0, ST_GEMM_A0, ST_VIDEO_PRE, ST_PRIOR, ST_V2A, ST_VIDEO_UPD, ST_A2V, ST_HEAD, ST_COUNT };
 extern bool g_stage_timing;
 void stage_mark(int stage, int end, cudaStream_t st);   // records an event on st (no-op unless timing is on)
 struct StageScope {

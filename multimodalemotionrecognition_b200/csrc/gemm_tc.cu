@@ -7,11 +7,16 @@
 // Persistent, warp-specialised kernel: one CTA per SM loops over 128(M) x 128(N) output tiles.
 //   warp 0    : TMA producer — cp.async.bulk.tensor (SWIZZLE_128B boxes of 64 x 128 bf16) into a 5-stage smem ring that
 //               keeps running across tile boundaries (the HBM stream never drains between tiles)
-//   warp 1    : one elected lane issues tcgen05.mma (M=128, N=128, K=16; 4 per stage) into one of TWO 128-column TMEM
+//   warp 1    : one elected lane issues tcgen05.mma (M=128, N=128, K=16; 4 per stage) into one of FOUR 128-column TMEM
 //               accumulators; tcgen05.commit frees the smem stage / publishes the accumulator
 //   warps 2-5 : epilogue — tcgen05.ld (32 lanes x 32 columns), + bias, convert; the bf16 tile is staged in smem as the
 //               exact global image (rows at the output pitch are contiguous) and leaves with ONE cp.async.bulk store,
 //               while the MMA warp already fills the other accumulator with the next tile.
+// EXTRAS (the a0 projection): the epilogue also emits, from data it already holds,
+//   tok[m] = (w_ak·y_m, w_aq·y_m)   the token parts of a_key_bias / a_query_bias (fusion.py:173-174), from the fp32 row
+//   colsum[clip][slot][n]           column sums of the tile's rows that belong to `clip` (rows are clips of seg_len tokens);
+//                                   slot = tile - first tile of the clip, so a reader adds <= 3 partials in a fixed order
+//                                   (the temporal mean that feeds prior_net, fusion.py:180)
 #include <cuda.h>
 
 #include "common.cuh"
@@ -24,30 +29,40 @@ namespace {
 
 constexpr int BM = 128, BN = 128, BK = 64;
 constexpr int kStages = 5;
+constexpr int kAccs = 4;                               // TMEM accumulators (4 x 128 columns = all of TMEM): the MMA warp can run 3 tiles ahead of the epilogue
 constexpr int kStageBytes = (BM * BK + BN * BK) * 2;   // 32 KB
 constexpr int kGemmThreads = 192;
 constexpr int kMaxStagePitch = 160;                    // staged (bulk-store) epilogue supports pitches up to this
 constexpr int kBarBytes = 256;
 
 __host__ __device__ constexpr int gemm_smem_bytes(bool staged, int pitch) {
-  return kStages * kStageBytes + (staged ? BM * pitch * 2 : 0) + BN * 4 + kBarBytes + 1024;
+  return kStages * kStageBytes + (staged ? BM * pitch * 2 : 0) + 3 * BN * 4 + kBarBytes + 1024;
 }
 
+struct GemmExtras {
+  const float* sc_w;   // [2][128] fp32 score weights
+  float* tok;          // [M][2]
+  float* colsum;       // [M / seg_len][kColsumSlots][128]
+  int seg_len;
+};
+
 // OUT_BF16: output dtype.  STAGED: N == 128 and bf16 -> smem image + one bulk store per tile.
-template <bool OUT_BF16, bool STAGED>
+template <bool OUT_BF16, bool STAGED, bool EXTRAS>
 __global__ void __launch_bounds__(kGemmThreads, 1) gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA,
                                                                   const __grid_constant__ CUtensorMap tmB,
                                                                   const float* __restrict__ bias, void* __restrict__ out,
-                                                                  int64_t out_pitch, int M, int N, int K) {
+                                                                  int64_t out_pitch, int M, int N, int K, GemmExtras ex) {
+  static_assert(!EXTRAS || STAGED, "the extras read the staged tile");
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
   uint8_t* stage_out = smem + kStages * kStageBytes;                                   // [128][pitch] bf16 (STAGED)
   float* bias_s = reinterpret_cast<float*>(stage_out + (STAGED ? BM * (int)out_pitch * 2 : 0));
-  uint64_t* full = reinterpret_cast<uint64_t*>(bias_s + BN);
+  float2* scw_s = reinterpret_cast<float2*>(bias_s + BN);   // [128] (w_ak[n], w_aq[n])
+  uint64_t* full = reinterpret_cast<uint64_t*>(bias_s + 3 * BN);
   uint64_t* empty = full + kStages;
-  uint64_t* acc_full = empty + kStages;    // [2]
-  uint64_t* acc_empty = acc_full + 2;      // [2]
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_empty + 2);
+  uint64_t* acc_full = empty + kStages;        // [kAccs]
+  uint64_t* acc_empty = acc_full + kAccs;      // [kAccs]
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_empty + kAccs);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int KB = K / BK;
@@ -62,13 +77,13 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_tc_kernel(const __grid_c
       tc::mbar_init(&full[s], 1);
       tc::mbar_init(&empty[s], 1);
     }
-    for (int b = 0; b < 2; ++b) {
+    for (int b = 0; b < kAccs; ++b) {
       tc::mbar_init(&acc_full[b], 1);
       tc::mbar_init(&acc_empty[b], 4);   // one arrival per epilogue warp
     }
     tc::fence_barrier_init();
   }
-  if (warp == 1) tc::tmem_alloc(tmem_slot, 2 * BN);
+  if (warp == 1) tc::tmem_alloc(tmem_slot, kAccs * BN);
   tc::tc_fence_before();
   __syncthreads();
   tc::tc_fence_after();
@@ -95,7 +110,7 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_tc_kernel(const __grid_c
       constexpr uint32_t idesc = tc::umma_idesc_bf16(BM, BN);
       uint32_t it = 0, lt = 0;
       for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++lt) {
-        const uint32_t ab = lt & 1u, aph = (lt >> 1) & 1u;
+        const uint32_t ab = lt % kAccs, aph = (lt / kAccs) & 1u;
         tc::mbar_wait(&acc_empty[ab], aph ^ 1u);   // epilogue has drained this accumulator (passes on first use)
         tc::tc_fence_after();
         const uint32_t tmem_acc = tmem_base + ab * BN;
@@ -125,11 +140,12 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_tc_kernel(const __grid_c
       __nv_bfloat16* r = reinterpret_cast<__nv_bfloat16*>(stage_out) + (int64_t)row * out_pitch;
       for (int cidx = BN; cidx < (int)out_pitch; ++cidx) r[cidx] = __float2bfloat16(0.f);
     }
+    if (EXTRAS) scw_s[et] = make_float2(__ldg(ex.sc_w + et), __ldg(ex.sc_w + BN + et));
     uint32_t lt = 0;
     int cur_n0 = -1;
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++lt) {
       const int m0 = (tile / tiles_n) * BM, n0 = (tile % tiles_n) * BN;
-      const uint32_t ab = lt & 1u, aph = (lt >> 1) & 1u;
+      const uint32_t ab = lt % kAccs, aph = (lt / kAccs) & 1u;
       if (n0 != cur_n0) {   // (re)load the bias slice; all epilogue threads pass the barrier below before reading it
         tc::named_bar_sync(2, 128);
         bias_s[et] = __ldg(bias + n0 + et);
@@ -140,11 +156,21 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_tc_kernel(const __grid_c
       tc::mbar_wait(&acc_full[ab], aph);
       tc::tc_fence_after();
       const int m = m0 + row;
+      float sc0 = 0.f, sc1 = 0.f;
 #pragma unroll 1
       for (int c = 0; c < BN; c += 32) {
         uint32_t r[32];
         tc::tmem_ld_32x32(tmem_base + ab * BN + ((uint32_t)(q * 32) << 16) + (uint32_t)c, r);
         tc::tmem_ld_wait();
+        if (EXTRAS) {
+#pragma unroll
+          for (int i = 0; i < 32; ++i) {
+            const float y = __uint_as_float(r[i]) + bias_s[c + i];
+            const float2 w = scw_s[c + i];
+            sc0 = fmaf(y, w.x, sc0);
+            sc1 = fmaf(y, w.y, sc1);
+          }
+        }
         if (OUT_BF16) {
           __nv_bfloat16* o = STAGED ? reinterpret_cast<__nv_bfloat16*>(stage_out) + (int64_t)row * out_pitch + c
                                     : reinterpret_cast<__nv_bfloat16*>(out) + (int64_t)m * out_pitch + n0 + c;
@@ -176,13 +202,30 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_tc_kernel(const __grid_c
       tc::tc_fence_before();
       __syncwarp();
       if (lane == 0) tc::mbar_arrive(&acc_empty[ab]);
+      if (EXTRAS && m < M) *reinterpret_cast<float2*>(ex.tok + (int64_t)m * 2) = make_float2(sc0, sc1);
       if (STAGED) {
         tc::fence_proxy_async();          // generic-proxy smem writes -> visible to the bulk (async proxy) store
         tc::named_bar_sync(1, 128);
-        if (leader) {
-          const int rows = min(BM, M - m0);
+        const int rows = min(BM, M - m0);
+        if (leader)
           tc::bulk_store_1d(reinterpret_cast<__nv_bfloat16*>(out) + (int64_t)m0 * out_pitch, stage_out,
                             (uint32_t)(rows * out_pitch * 2));
+        if (EXTRAS) {   // thread `et` owns column et: sum it over the rows of each clip present in this tile
+          const int L = ex.seg_len;
+          const __nv_bfloat16* colp = reinterpret_cast<const __nv_bfloat16*>(stage_out) + et;
+          const int clip_last = (m0 + rows - 1) / L;
+          for (int clip = m0 / L; clip <= clip_last; ++clip) {
+            const int r0 = max(clip * L, m0) - m0, r1 = min((clip + 1) * L, m0 + rows) - m0;
+            float s0 = 0.f, s1 = 0.f;
+            int rr = r0;
+            for (; rr + 1 < r1; rr += 2) {
+              s0 += __bfloat162float(colp[(int64_t)rr * out_pitch]);
+              s1 += __bfloat162float(colp[(int64_t)(rr + 1) * out_pitch]);
+            }
+            if (rr < r1) s0 += __bfloat162float(colp[(int64_t)rr * out_pitch]);
+            const int slot = m0 / BM - (clip * L) / BM;
+            ex.colsum[((int64_t)clip * kColsumSlots + slot) * BN + et] = s0 + s1;
+          }
         }
       }
     }
@@ -190,7 +233,7 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_tc_kernel(const __grid_c
   }
   tc::tc_fence_before();
   __syncthreads();
-  if (warp == 1) tc::tmem_dealloc(tmem_base, 2 * BN);
+  if (warp == 1) tc::tmem_dealloc(tmem_base, kAccs * BN);
 }
 
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
@@ -208,18 +251,18 @@ EncodeTiledFn encode_tiled_fn() {
   return fn;
 }
 
-template <bool OUT_BF16, bool STAGED>
+template <bool OUT_BF16, bool STAGED, bool EXTRAS>
 int launch_gemm_tc(cudaStream_t st, const CUtensorMap& tmA, const CUtensorMap& tmB, const float* bias, void* out, int64_t pitch,
-                   int M, int N, int K) {
+                   int M, int N, int K, const GemmExtras& ex) {
   const int smem = gemm_smem_bytes(STAGED, (int)pitch);
   static int configured = 0;
   if (smem > configured) {
-    XF_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<OUT_BF16, STAGED>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    XF_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<OUT_BF16, STAGED, EXTRAS>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
     configured = smem;
   }
   const int tiles = ((M + BM - 1) / BM) * (N / BN);
   const int grid = tiles < num_sms() ? tiles : num_sms();
-  gemm_tc_kernel<OUT_BF16, STAGED><<<grid, kGemmThreads, smem, st>>>(tmA, tmB, bias, out, pitch, M, N, K);
+  gemm_tc_kernel<OUT_BF16, STAGED, EXTRAS><<<grid, kGemmThreads, smem, st>>>(tmA, tmB, bias, out, pitch, M, N, K, ex);
   count_launch();
   XF_LAUNCH_CHECK();
   return XATTN_OK;
@@ -243,8 +286,13 @@ int make_tmap_bf16_2d(void* tmap_out, const void* base, int64_t rows, int64_t co
 }
 
 int gemm_tc_bf16(cudaStream_t st, const void* X, const void* W, const float* bias, void* out, bool out_bf16, int64_t out_pitch,
-                 int M, int N, int K) {
+                 int M, int N, int K, const float* sc_w, float* tok, float* colsum, int seg_len) {
   if (M <= 0) return XATTN_OK;
+  const bool extras = sc_w != nullptr;
+  if (extras && !(out_bf16 && N == BN && out_pitch <= kMaxStagePitch && seg_len > 0 && M % seg_len == 0 &&
+                  (seg_len + BM - 2) / BM + 1 <= kColsumSlots))
+    XF_FAIL(XATTN_ERR_SHAPE, "projection GEMM extras need bf16 output, N == 128 and rows in clips of <= 256 tokens");
+  GemmExtras ex{sc_w, tok, colsum, seg_len};
   if (N % BN != 0 || K % BK != 0)
     XF_FAIL(XATTN_ERR_SHAPE, "tcgen05 projection GEMM needs N %% 128 == 0 and K %% 64 == 0 (N=%d K=%d)", N, K);
   if (out_pitch < N || (out_bf16 && out_pitch % 8 != 0) || (!out_bf16 && out_pitch % 4 != 0))
@@ -252,9 +300,11 @@ int gemm_tc_bf16(cudaStream_t st, const void* X, const void* W, const float* bia
   alignas(64) CUtensorMap tmA, tmB;
   XF_TRY(make_tmap_bf16_2d(&tmA, X, M, K, BM, BK));
   XF_TRY(make_tmap_bf16_2d(&tmB, W, N, K, BN, BK));
-  if (out_bf16 && N == BN && out_pitch <= kMaxStagePitch) return launch_gemm_tc<true, true>(st, tmA, tmB, bias, out, out_pitch, M, N, K);
-  if (out_bf16) return launch_gemm_tc<true, false>(st, tmA, tmB, bias, out, out_pitch, M, N, K);
-  return launch_gemm_tc<false, false>(st, tmA, tmB, bias, out, out_pitch, M, N, K);
+  if (extras) return launch_gemm_tc<true, true, true>(st, tmA, tmB, bias, out, out_pitch, M, N, K, ex);
+  if (out_bf16 && N == BN && out_pitch <= kMaxStagePitch)
+    return launch_gemm_tc<true, true, false>(st, tmA, tmB, bias, out, out_pitch, M, N, K, ex);
+  if (out_bf16) return launch_gemm_tc<true, false, false>(st, tmA, tmB, bias, out, out_pitch, M, N, K, ex);
+  return launch_gemm_tc<false, false, false>(st, tmA, tmB, bias, out, out_pitch, M, N, K, ex);
 }
 
 }  // namespace xf

@@ -5,7 +5,12 @@
 namespace xf {
 // Y[M,N] = X[M,K]·W[N,K]^T + bias.  X, W: bf16, K contiguous, 16-byte aligned.  out: bf16 or fp32 with row pitch
 // `out_pitch` (elements).  N % 128 == 0, K % 64 == 0.
+// Optional extras (sc_w != nullptr; bf16 output with N == 128 only), computed in the epilogue from the tile it holds:
+//   tok[m]                  = (sc_w[0,:]·y_m, sc_w[1,:]·y_m)  from the fp32 row y_m
+//   colsum[clip][slot][128] = sum of the rows of `clip` (rows m in [clip*seg_len, +seg_len)) inside output tile
+//                             (clip*seg_len)/128 + slot; a clip overlaps at most kColsumSlots tiles.
+constexpr int kColsumSlots = 3;
 int gemm_tc_bf16(cudaStream_t st, const void* X, const void* W, const float* bias, void* out, bool out_bf16, int64_t out_pitch,
-                 int M, int N, int K);
+                 int M, int N, int K, const float* sc_w = nullptr, float* tok = nullptr, float* colsum = nullptr, int seg_len = 0);
 int make_tmap_bf16_2d(void* tmap_out, const void* base, int64_t rows, int64_t cols, int box_rows, int box_cols);
 }  // namespace xf

@@ -1,0 +1,10 @@
+set -x
+timeout 900 python -m pytest tests/test_gpu_bf16.py -q -x 2>&1 | tail -3
+for st in 5 4 3; do
+XATTN_GEMM_STAGES=$st python bench.py --steps 30 --warmup 5 --no-cpu-baseline > gpurun_out/r7_bench_$st.json 2> gpurun_out/r7_bench.err; python - <<PY
+import json
+d=json.loads(open('gpurun_out/r7_bench_$st.json').read().strip().splitlines()[-1])
+print('stages=$st', d['value'], d['ms_per_step'], d['roofline']['whole_step']['bracketed_pass_ms_per_step'])
+print([(s['kernel'], round(s['us'],1)) for s in d['roofline']['stages']])
+PY
+done

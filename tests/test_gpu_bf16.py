@@ -58,7 +58,8 @@ def _ws_views(ws, B, T, Ta):
     E, EP = 128, 136
     spec = [("v0", torch.float32, (B, T, E)), ("a0", torch.bfloat16, (B * Ta, EP)), ("qt", torch.bfloat16, (B, 64, EP)),
             ("meanv", torch.float32, (B, E)), ("tqv", torch.float32, (B, 16)), ("tkv", torch.float32, (B, 16)),
-            ("u", torch.bfloat16, (B, 64, E)), ("tqa", torch.float32, (B, 160)), ("pc", torch.float32, (B, 4)),
+            ("u", torch.bfloat16, (B, 64, E)), ("tok", torch.float32, (B * Ta, 2)), ("acol", torch.float32, (B, 3, E)),
+            ("pc", torch.float32, (B, 4)),
             ("kt", torch.bfloat16, (B, 64, EP)), ("vt", torch.bfloat16, (B, 64, EP)), ("cv", torch.float32, (B, 64)),
             ("pooled", torch.float32, (B, 2 * E))]
     out, off = {}, 0
@@ -161,3 +162,40 @@ def test_bf16_full_batch_top1_and_tolerance(cuda_device):
     solid = margin > 2 * err
     assert agree[solid].float().mean().item() >= 0.999
     assert agree.float().mean().item() >= 0.98
+
+
+@pytest.mark.parametrize("mode,N,K", [(0, 160, 128), (1, 128, 160), (0, 64, 128), (1, 128, 64)])
+def test_umma_probe_m64_halves_and_mn_major(cuda_device, mode, N, K):
+    """tcgen05 features of the attention kernels, pinned in isolation: two M=64 products land in lanes 0-15 / 16-31 of each
+    TMEM sub-partition; mode 1 feeds B as an MN-major (rows = K) swizzled tile; 16x256b loads return mma C-fragment order."""
+    from multimodalemotionrecognition_b200 import _lib
+    lib = _lib.load()
+    g = torch.Generator().manual_seed(mode * 7 + N + K)
+    A = torch.randn(128, K, generator=g).bfloat16()
+    B = (torch.randn(2, N, K, generator=g) if mode == 0 else torch.randn(2, K, N, generator=g)).bfloat16()
+    Ad, Bd = A.to(cuda_device), B.to(cuda_device)
+    out32 = torch.full((128, N), float("nan"), device=cuda_device)
+    out16 = torch.full((2, 4, 32, 64), float("nan"), device=cuda_device)
+    _lib.check(lib.xattn_debug_umma_probe(Ad.data_ptr(), Bd.data_ptr(), out32.data_ptr(), out16.data_ptr(), N, K, mode,
+                                          torch.cuda.current_stream().cuda_stream))
+    torch.cuda.synchronize()
+    ref = []
+    for p in range(2):
+        a = A[64 * p:64 * p + 64].double()
+        b = B[p].double()
+        ref.append(a @ (b.T if mode == 0 else b))
+    got = out32.cpu().double().reshape(4, 2, 16, N)          # [sub-partition][half][lane in half][col]
+    for p in range(2):
+        want = ref[p].reshape(4, 16, N)                      # row m -> sub-partition m // 16, lane m % 16 (+16 for the upper half)
+        err = (got[:, p] - want).abs().max().item()
+        assert err < 1e-3 * max(1.0, want.abs().max().item()), (mode, p, err)
+    if N >= 128:
+        o = out16.cpu().double()                             # [half][warp][lane][4*i + r]
+        for p in range(2):
+            want = ref[p].reshape(4, 16, N)
+            for lane in range(32):
+                g_, t_ = lane >> 2, lane & 3
+                for i in range(16):
+                    for r in range(4):
+                        w = want[:, g_ + 8 * (r >> 1), 8 * i + 2 * t_ + (r & 1)]
+                        assert (o[p, :, lane, 4 * i + r] - w).abs().max().item() < 1e-3 * max(1.0, w.abs().max().item()), (p, lane, i, r)
