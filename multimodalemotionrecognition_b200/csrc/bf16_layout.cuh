@@ -72,7 +72,8 @@ struct Bf16Ctx {
 };
 int launch_video_pre(const Bf16Ctx& x);
 int launch_prior(const Bf16Ctx& x);
-int launch_v2a_attn(const Bf16Ctx& x);
+int launch_v2a_attn(const Bf16Ctx& x);   // mma.sync version (kept for A/B runs: XATTN_ATTN=legacy)
+int launch_v2a_tc(const Bf16Ctx& x);     // tcgen05 version
 int launch_video_update(const Bf16Ctx& x);
 int launch_a2v_attn(const Bf16Ctx& x);
 int launch_head_pooled(const Bf16Ctx& x, float* logits);

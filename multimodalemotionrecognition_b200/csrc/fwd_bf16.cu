@@ -1,5 +1,8 @@
 // bf16 tensor-core forward of the xattn fusion head (precision == XATTN_DTYPE_BF16): launch sequence + classifier head.
 // Stage map against reference src/models/fusion.py is in bf16_layout.cuh.
+#include <stdlib.h>
+#include <string.h>
+
 #include "bf16_layout.cuh"
 #include "gemm_tc.cuh"
 #include "kernels_bf16.cuh"
@@ -150,6 +153,16 @@ int launch_head_pooled(const Bf16Ctx& x, float* logits) {
   return XATTN_OK;
 }
 
+// XATTN_ATTN=legacy selects the mma.sync attention kernels (A/B timing and bisecting); the default is the tcgen05 pair.
+static bool attn_legacy() {
+  static int v = -1;
+  if (v < 0) {
+    const char* e = getenv("XATTN_ATTN");
+    v = (e != nullptr && strcmp(e, "legacy") == 0) ? 1 : 0;
+  }
+  return v == 1;
+}
+
 // One private non-blocking stream per device for the forked video branch.
 static int side_stream(cudaStream_t* out) {
   static cudaStream_t streams[64] = {};
@@ -213,7 +226,7 @@ int forward_bf16(const xattn_config& c, const float* params, const void* packed,
   }
   XF_TRY(rc);
   if (c.use_prior) { StageScope t(ST_PRIOR, st); XF_TRY(launch_prior(x)); }
-  { StageScope t(ST_V2A, st); XF_TRY(launch_v2a_attn(x)); }
+  { StageScope t(ST_V2A, st); XF_TRY(attn_legacy() ? launch_v2a_attn(x) : launch_v2a_tc(x)); }
   { StageScope t(ST_VIDEO_UPD, st); XF_TRY(launch_video_update(x)); }
   { StageScope t(ST_A2V, st); XF_TRY(launch_a2v_attn(x)); }
   { StageScope t(ST_HEAD, st); XF_TRY(launch_head_pooled(x, logits)); }

@@ -12,5 +12,6 @@ namespace xf {
 constexpr int kColsumSlots = 3;
 int gemm_tc_bf16(cudaStream_t st, const void* X, const void* W, const float* bias, void* out, bool out_bf16, int64_t out_pitch,
                  int M, int N, int K, const float* sc_w = nullptr, float* tok = nullptr, float* colsum = nullptr, int seg_len = 0);
-int make_tmap_bf16_2d(void* tmap_out, const void* base, int64_t rows, int64_t cols, int box_rows, int box_cols);
+// 2D bf16 tensor map with SWIZZLE_128B boxes: `cols` contiguous elements per row, rows `pitch` elements apart (0 = cols).
+int make_tmap_bf16_2d(void* tmap_out, const void* base, int64_t rows, int64_t cols, int box_rows, int box_cols, int64_t pitch = 0);
 }  // namespace xf

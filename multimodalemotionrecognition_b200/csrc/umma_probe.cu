@@ -5,6 +5,7 @@
 // Two independent products run in one CTA:  D_lo = A[0:64]·op(B0)  -> lanes 0-15 of each sub-partition,
 //                                           D_hi = A[64:128]·op(B1) -> lanes 16-31.
 // mode 0: B_i given as [N][K] (K contiguous, K-major operand); mode 1: B_i given as [K][N] (N contiguous, MN-major operand).
+// mode 2 / 3: as 0 / 1 with the A operands in TENSOR MEMORY (tcgen05.st of bf16x2-packed rows into the lanes of the matching D).
 // Exported through xattn_debug_umma_probe for tests/test_gpu_bf16.py; not on the product path.
 #include "common.cuh"
 #include "tc.cuh"
@@ -27,8 +28,8 @@ __global__ void __launch_bounds__(128, 1) umma_probe_kernel(const __nv_bfloat16*
   const int a_bytes = KA * 64 * 128;                  // one [64 rows] A operand: KA boxes of 64 x 128 B
   // B operand of product i: mode 0 -> KA boxes of [N rows x 128 B]; mode 1 -> N/64 boxes of [Kp rows x 128 B]
   const int Kp = (K + 15) / 16 * 16;
-  const int b_box = mode == 0 ? N * 128 : Kp * 128;
-  const int b_bytes = (mode == 0 ? KA : N / 64) * b_box;
+  const int b_box = (mode & 1) == 0 ? N * 128 : Kp * 128;
+  const int b_bytes = ((mode & 1) == 0 ? KA : N / 64) * b_box;
   uint8_t* sA[2] = {smem, smem + a_bytes};
   uint8_t* sB[2] = {smem + 2 * a_bytes, smem + 2 * a_bytes + ((b_bytes + 1023) & ~1023)};
   for (int i = tid; i < (2 * a_bytes + 2 * ((b_bytes + 1023) & ~1023)) / 4; i += 128) reinterpret_cast<uint32_t*>(smem)[i] = 0;
@@ -38,7 +39,7 @@ __global__ void __launch_bounds__(128, 1) umma_probe_kernel(const __nv_bfloat16*
       const int r = i / K, k = i % K;
       *reinterpret_cast<__nv_bfloat16*>(sA[p] + (k / 64) * 64 * 128 + tc::sw128_off(r, k % 64)) = A[(int64_t)(p * 64 + r) * K + k];
     }
-    if (mode == 0) {
+    if ((mode & 1) == 0) {
       for (int i = tid; i < N * K; i += 128) {
         const int n = i / K, k = i % K;
         *reinterpret_cast<__nv_bfloat16*>(sB[p] + (k / 64) * b_box + tc::sw128_off(n, k % 64)) = B[(int64_t)p * N * K + i];
@@ -54,12 +55,32 @@ __global__ void __launch_bounds__(128, 1) umma_probe_kernel(const __nv_bfloat16*
     tc::mbar_init(&bar, 1);
     tc::fence_barrier_init();
   }
-  if (warp == 0) tc::tmem_alloc(&tmem_slot, 256);
+  if (warp == 0) tc::tmem_alloc(&tmem_slot, 512);
   tc::fence_proxy_async();
   tc::tc_fence_before();
   __syncthreads();
   tc::tc_fence_after();
   const uint32_t tmem = tmem_slot;
+  const bool a_tmem = mode >= 2;
+  mode &= 1;
+  constexpr uint32_t kTmemA = 256;   // A rows, packed: columns [256, 256 + K/2)
+  if (a_tmem) {   // lane l of warp w holds row 16w + (l & 15) of product (l >> 4)
+    const int p = lane >> 4, r = 16 * warp + (lane & 15);
+    for (int k0 = 0; k0 < Kp; k0 += 32) {
+      uint32_t v[16];
+      for (int j = 0; j < 16; ++j) {
+        const int k = k0 + 2 * j;
+        const __nv_bfloat16 lo = k < K ? A[(int64_t)(p * 64 + r) * K + k] : __float2bfloat16(0.f);
+        const __nv_bfloat16 hi = k + 1 < K ? A[(int64_t)(p * 64 + r) * K + k + 1] : __float2bfloat16(0.f);
+        v[j] = (uint32_t)__bfloat16_as_ushort(lo) | ((uint32_t)__bfloat16_as_ushort(hi) << 16);
+      }
+      tc::tmem_st_32x32_x16(tmem + kTmemA + ((uint32_t)(32 * warp) << 16) + (uint32_t)(k0 / 2), v);
+    }
+    tc::tmem_st_wait();
+    tc::tc_fence_before();
+    __syncthreads();
+    tc::tc_fence_after();
+  }
   if (tid == 0) {
     const uint32_t idesc = tc::umma_idesc_bf16_ex(64, N, false, mode == 1);
     for (int p = 0; p < 2; ++p) {
@@ -69,7 +90,8 @@ __global__ void __launch_bounds__(128, 1) umma_probe_kernel(const __nv_bfloat16*
         uint64_t db;
         if (mode == 0) db = tc::umma_desc_sw128(tc::smem_u32(sB[p]) + (ks / 4) * b_box + (ks % 4) * 32, 16, 1024);
         else db = tc::umma_desc_sw128(tc::smem_u32(sB[p]) + ks * 16 * 128, (uint32_t)b_box, 1024);
-        tc::umma_bf16(d, da, db, idesc, ks != 0);
+        if (a_tmem) tc::umma_bf16_ts(d, tmem + kTmemA + ((uint32_t)(16 * p) << 16) + (uint32_t)(ks * 8), db, idesc, ks != 0);
+        else tc::umma_bf16(d, da, db, idesc, ks != 0);
       }
     }
     tc::umma_commit(&bar);
@@ -92,16 +114,17 @@ __global__ void __launch_bounds__(128, 1) umma_probe_kernel(const __nv_bfloat16*
   }
   tc::tc_fence_before();
   __syncthreads();
-  if (warp == 0) tc::tmem_dealloc(tmem, 256);
+  if (warp == 0) tc::tmem_dealloc(tmem, 512);
 }
 
 }  // namespace
 
 int umma_probe(cudaStream_t st, const void* A, const void* B, float* out32, float* out16, int N, int K, int mode) {
-  if (N % 8 != 0 || N < 8 || N > 256 || K < 16 || K % 16 != 0 || (mode == 1 && N % 64 != 0) || (mode == 0 && K % 64 != 0))
+  if (N % 8 != 0 || N < 8 || N > 256 || K < 16 || K % 16 != 0 || K > 256 || mode < 0 || mode > 3 ||
+      ((mode & 1) == 1 && N % 64 != 0) || ((mode & 1) == 0 && K % 64 != 0))
     XF_FAIL(XATTN_ERR_SHAPE, "umma probe: unsupported N=%d K=%d mode=%d", N, K, mode);
   const int KA = (K + 63) / 64, Kp = (K + 15) / 16 * 16;
-  const int b_bytes = mode == 0 ? KA * N * 128 : (N / 64) * Kp * 128;
+  const int b_bytes = (mode & 1) == 0 ? KA * N * 128 : (N / 64) * Kp * 128;
   const int smem = 2 * KA * 64 * 128 + 2 * ((b_bytes + 1023) & ~1023) + 1024;
   if (smem > kProbeMaxBytes) XF_FAIL(XATTN_ERR_SHAPE, "umma probe: operands need %d bytes of smem", smem);
   XF_CUDA(cudaFuncSetAttribute(umma_probe_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));

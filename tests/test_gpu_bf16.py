@@ -164,7 +164,8 @@ def test_bf16_full_batch_top1_and_tolerance(cuda_device):
     assert agree.float().mean().item() >= 0.98
 
 
-@pytest.mark.parametrize("mode,N,K", [(0, 160, 128), (1, 128, 160), (0, 64, 128), (1, 128, 64)])
+@pytest.mark.parametrize("mode,N,K", [(0, 160, 128), (1, 128, 160), (0, 64, 128), (1, 128, 64), (2, 160, 128), (3, 128, 160),
+                                      (3, 128, 64)])
 def test_umma_probe_m64_halves_and_mn_major(cuda_device, mode, N, K):
     """tcgen05 features of the attention kernels, pinned in isolation: two M=64 products land in lanes 0-15 / 16-31 of each
     TMEM sub-partition; mode 1 feeds B as an MN-major (rows = K) swizzled tile; 16x256b loads return mma C-fragment order."""
@@ -172,7 +173,8 @@ def test_umma_probe_m64_halves_and_mn_major(cuda_device, mode, N, K):
     lib = _lib.load()
     g = torch.Generator().manual_seed(mode * 7 + N + K)
     A = torch.randn(128, K, generator=g).bfloat16()
-    B = (torch.randn(2, N, K, generator=g) if mode == 0 else torch.randn(2, K, N, generator=g)).bfloat16()
+    ts, mode_b = mode >= 2, mode & 1          # modes 2/3: A operand in tensor memory
+    B = (torch.randn(2, N, K, generator=g) if mode_b == 0 else torch.randn(2, K, N, generator=g)).bfloat16()
     Ad, Bd = A.to(cuda_device), B.to(cuda_device)
     out32 = torch.full((128, N), float("nan"), device=cuda_device)
     out16 = torch.full((2, 4, 32, 64), float("nan"), device=cuda_device)
@@ -183,12 +185,12 @@ def test_umma_probe_m64_halves_and_mn_major(cuda_device, mode, N, K):
     for p in range(2):
         a = A[64 * p:64 * p + 64].double()
         b = B[p].double()
-        ref.append(a @ (b.T if mode == 0 else b))
+        ref.append(a @ (b.T if mode_b == 0 else b))
     got = out32.cpu().double().reshape(4, 2, 16, N)          # [sub-partition][half][lane in half][col]
     for p in range(2):
         want = ref[p].reshape(4, 16, N)                      # row m -> sub-partition m // 16, lane m % 16 (+16 for the upper half)
         err = (got[:, p] - want).abs().max().item()
-        assert err < 1e-3 * max(1.0, want.abs().max().item()), (mode, p, err)
+        assert err < 1e-3 * max(1.0, want.abs().max().item()), (mode, ts, p, err)
     if N >= 128:
         o = out16.cpu().double()                             # [half][warp][lane][4*i + r]
         for p in range(2):
