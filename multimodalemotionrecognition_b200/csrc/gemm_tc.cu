@@ -13,7 +13,7 @@
 //               exact global image (rows at the output pitch are contiguous) and leaves with ONE cp.async.bulk store,
 //               while the MMA warp already fills the other accumulator with the next tile.
 // EXTRAS (the a0 projection): the epilogue also emits, from data it already holds,
-//   tok[m] = (w_ak·y_m, w_aq·y_m)   the token parts of a_key_bias / a_query_bias (fusion.py:173-174), from the fp32 row
+//   tok[0][m], tok[1][m] = w_ak·y_m, w_aq·y_m   the token parts of a_key_bias / a_query_bias (fusion.py:173-174), from the fp32 row
 //   colsum[clip][slot][n]           column sums of the tile's rows that belong to `clip` (rows are clips of seg_len tokens);
 //                                   slot = tile - first tile of the clip, so a reader adds <= 3 partials in a fixed order
 //                                   (the temporal mean that feeds prior_net, fusion.py:180)
@@ -41,7 +41,7 @@ __host__ __device__ constexpr int gemm_smem_bytes(bool staged, int pitch) {
 
 struct GemmExtras {
   const float* sc_w;   // [2][128] fp32 score weights
-  float* tok;          // [M][2]
+  float* tok;          // [2][M]
   float* colsum;       // [M / seg_len][kColsumSlots][128]
   int seg_len;
 };
@@ -202,7 +202,10 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_tc_kernel(const __grid_c
       tc::tc_fence_before();
       __syncwarp();
       if (lane == 0) tc::mbar_arrive(&acc_empty[ab]);
-      if (EXTRAS && m < M) *reinterpret_cast<float2*>(ex.tok + (int64_t)m * 2) = make_float2(sc0, sc1);
+      if (EXTRAS && m < M) {   // two planes [2][M]: coalesced here and for the per-clip readers
+        ex.tok[m] = sc0;
+        ex.tok[(int64_t)M + m] = sc1;
+      }
       if (STAGED) {
         tc::fence_proxy_async();          // generic-proxy smem writes -> visible to the bulk (async proxy) store
         tc::named_bar_sync(1, 128);

@@ -6,7 +6,7 @@ namespace xf {
 // Y[M,N] = X[M,K]·W[N,K]^T + bias.  X, W: bf16, K contiguous, 16-byte aligned.  out: bf16 or fp32 with row pitch
 // `out_pitch` (elements).  N % 128 == 0, K % 64 == 0.
 // Optional extras (sc_w != nullptr; bf16 output with N == 128 only), computed in the epilogue from the tile it holds:
-//   tok[m]                  = (sc_w[0,:]·y_m, sc_w[1,:]·y_m)  from the fp32 row y_m
+//   tok[i][m] (two planes)  = sc_w[i,:]·y_m  from the fp32 row y_m
 //   colsum[clip][slot][128] = sum of the rows of `clip` (rows m in [clip*seg_len, +seg_len)) inside output tile
 //                             (clip*seg_len)/128 + slot; a clip overlaps at most kColsumSlots tiles.
 constexpr int kColsumSlots = 3;
