@@ -18,7 +18,7 @@ constexpr int kOpBytes = 64 * BEP * 2;     // 17,408  (Qt / Kt / Vt)
 struct V2AArgs {
   const __nv_bfloat16* a0;   // [B*Ta, BEP]
   const __nv_bfloat16* qt;   // [B,64,BEP]
-  const float *tqv, *tok, *pc;   // [B,16] w_vq·v0_i ; [2,B*Ta] w_ak·a0_j | w_aq·a0_j ; [B,4] prior parts of the bias heads
+  const float *tqv, *tok, *pc;   // [B,16] w_vq·v0_i ; [2,B,160] w_ak·a0_j | w_aq·a0_j ; [B,4] prior parts of the bias heads
   const float* bias_scale;
   __nv_bfloat16* u;          // [B,64,E]
   int B, Ta, T, use_prior;
@@ -51,7 +51,7 @@ __global__ void __launch_bounds__(128, 3) v2a_attn_kernel(V2AArgs a) {
     for (int i = tid; i < nz; i += blockDim.x) z[i] = make_uint4(0, 0, 0, 0);
     if (a.use_prior) {
       const float pq = a.pc[(int64_t)c * 4 + 0], pk = a.pc[(int64_t)c * 4 + 1];
-      for (int i = tid; i < Ta; i += blockDim.x) ka_s[i] = a.tok[(int64_t)c * Ta + i] + pk;
+      for (int i = tid; i < Ta; i += blockDim.x) ka_s[i] = a.tok[(int64_t)c * BTAP + i] + pk;
       if (tid < 16) qv_s[tid] = a.tqv[(int64_t)c * 16 + tid] + pq;
     }
   }
@@ -133,8 +133,8 @@ __global__ void __launch_bounds__(128, 3) v2a_attn_kernel(V2AArgs a) {
     }
   }
   // U leaves in A-FRAGMENT order: lane (g,t) of head h writes the 32 registers it would feed to mma.sync as the A operand
-  // of the next product (video_update reads them back with eight 16-byte loads): [clip][head][lane][ks][4] x bf16x2.
-  uint4* up = reinterpret_cast<uint4*>(a.u) + (((int64_t)c * BH + h) * 32 + lane) * 8;
+  // of the next product (video_update reads them back with eight 16-byte loads): [clip][head][ks][lane][4] x bf16x2 (a warp-wide 16-byte access is 512 contiguous bytes).
+  uint4* up = reinterpret_cast<uint4*>(a.u) + ((int64_t)c * BH + h) * 256 + lane;
 #pragma unroll
   for (int ks = 0; ks < 8; ++ks) {
     uint4 v;
@@ -142,13 +142,13 @@ __global__ void __launch_bounds__(128, 3) v2a_attn_kernel(V2AArgs a) {
     v.y = tc::pack_bf16(o[2 * ks][2] * inv1, o[2 * ks][3] * inv1);
     v.z = tc::pack_bf16(o[2 * ks + 1][0] * inv0, o[2 * ks + 1][1] * inv0);
     v.w = tc::pack_bf16(o[2 * ks + 1][2] * inv1, o[2 * ks + 1][3] * inv1);
-    up[ks] = v;
+    up[ks * 32] = v;
   }
 }
 
 struct A2VArgs {
   const __nv_bfloat16 *a0, *kt, *vt;   // [B*Ta,BEP], [B,64,BEP] x2
-  const float *tok, *tkv, *pc, *cv;    // [2,B*Ta], [B,16], [B,4], [B,64]
+  const float *tok, *tkv, *pc, *cv;    // [2,B,160], [B,16], [B,4], [B,64]
   const float *bo2, *gam, *bet, *bias_scale;
   float* pooled;                       // [B,2E] (second E = pooled_a)
   int B, Ta, T, use_prior;
@@ -187,7 +187,7 @@ __global__ void __launch_bounds__(160, 2) a2v_attn_kernel(A2VArgs a) {
     const int nz = (BTAP - Ta) * BEP * 2 / 16;
     for (int i = tid; i < nz; i += blockDim.x) z[i] = make_uint4(0, 0, 0, 0);
     const float pq = a.use_prior ? a.pc[(int64_t)c * 4 + 2] : 0.f, pk = a.use_prior ? a.pc[(int64_t)c * 4 + 3] : 0.f;
-    for (int i = tid; i < BTAP; i += blockDim.x) qa_s[i] = (a.use_prior && i < Ta) ? a.tok[((int64_t)a.B + c) * Ta + i] + pq : 0.f;
+    for (int i = tid; i < BTAP; i += blockDim.x) qa_s[i] = (a.use_prior && i < Ta) ? a.tok[((int64_t)a.B + c) * BTAP + i] + pq : 0.f;
     if (tid < 16) kv_s[tid] = a.use_prior ? a.tkv[(int64_t)c * 16 + tid] + pk : 0.f;
     if (tid < 64) cv_s[tid] = a.cv[(int64_t)c * 64 + tid];
     for (int i = tid; i < BE; i += blockDim.x) {

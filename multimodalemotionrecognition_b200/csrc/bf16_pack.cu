@@ -61,7 +61,7 @@ void compute_ws_bf16(const xattn_config& c, WsBf16& w) {
   w.tqv = take(B * 16 * 4);
   w.tkv = take(B * 16 * 4);
   w.u = take(B * 64 * E * 2);
-  w.tok = take(B * c.Ta * 2 * 4);
+  w.tok = take(B * BTAP * 2 * 4);
   w.acol = take(B * 3 * E * 4);
   w.pc = take(B * 4 * 4);
   w.kt = take(B * 64 * BEP * 2);

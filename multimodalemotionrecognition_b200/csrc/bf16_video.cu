@@ -204,11 +204,11 @@ __global__ void __launch_bounds__(kUpdWarps * 32, 1) video_update_kernel(VideoUp
     uint32_t af[8][4];   // first the A fragments of O (k-steps 2h, 2h+1 <- head h), later those of v1
 #pragma unroll
     for (int h = 0; h < BH; ++h) {
-      const uint4* up = reinterpret_cast<const uint4*>(a.u) + (((int64_t)c * BH + h) * 32 + lane) * 8;   // fragment order
+      const uint4* up = reinterpret_cast<const uint4*>(a.u) + ((int64_t)c * BH + h) * 256 + lane;   // fragment order, [ks][lane]
       uint32_t au[8][4];
 #pragma unroll
       for (int ks = 0; ks < 8; ++ks) {
-        const uint4 v = __ldg(up + ks);
+        const uint4 v = __ldg(up + ks * 32);   // a warp reads 512 contiguous bytes
         au[ks][0] = v.x; au[ks][1] = v.y; au[ks][2] = v.z; au[ks][3] = v.w;
       }
       float o4[4][4];

@@ -41,7 +41,7 @@ __host__ __device__ constexpr int gemm_smem_bytes(bool staged, int pitch) {
 
 struct GemmExtras {
   const float* sc_w;   // [2][128] fp32 score weights
-  float* tok;          // [2][M]
+  float* tok;          // [2][M / seg_len][kTokPitch]
   float* colsum;       // [M / seg_len][kColsumSlots][128]
   int seg_len;
 };
@@ -202,9 +202,10 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_tc_kernel(const __grid_c
       tc::tc_fence_before();
       __syncwarp();
       if (lane == 0) tc::mbar_arrive(&acc_empty[ab]);
-      if (EXTRAS && m < M) {   // two planes [2][M]: coalesced here and for the per-clip readers
-        ex.tok[m] = sc0;
-        ex.tok[(int64_t)M + m] = sc1;
+      if (EXTRAS && m < M) {   // two planes [2][clips][kTokPitch]: 16-byte aligned rows per clip for the attention kernels
+        const int clip = m / ex.seg_len, j = m - clip * ex.seg_len;
+        ex.tok[(int64_t)clip * kTokPitch + j] = sc0;
+        ex.tok[((int64_t)(M / ex.seg_len) + clip) * kTokPitch + j] = sc1;
       }
       if (STAGED) {
         tc::fence_proxy_async();          // generic-proxy smem writes -> visible to the bulk (async proxy) store
@@ -294,7 +295,7 @@ int gemm_tc_bf16(cudaStream_t st, const void* X, const void* W, const float* bia
   if (M <= 0) return XATTN_OK;
   const bool extras = sc_w != nullptr;
   if (extras && !(out_bf16 && N == BN && out_pitch <= kMaxStagePitch && seg_len > 0 && M % seg_len == 0 &&
-                  (seg_len + BM - 2) / BM + 1 <= kColsumSlots))
+                  (seg_len + BM - 2) / BM + 1 <= kColsumSlots && seg_len <= kTokPitch))
     XF_FAIL(XATTN_ERR_SHAPE, "projection GEMM extras need bf16 output, N == 128 and rows in clips of <= 256 tokens");
   GemmExtras ex{sc_w, tok, colsum, seg_len};
   if (N % BN != 0 || K % BK != 0)

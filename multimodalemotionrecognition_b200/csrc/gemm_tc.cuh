@@ -6,10 +6,11 @@ namespace xf {
 // Y[M,N] = X[M,K]·W[N,K]^T + bias.  X, W: bf16, K contiguous, 16-byte aligned.  out: bf16 or fp32 with row pitch
 // `out_pitch` (elements).  N % 128 == 0, K % 64 == 0.
 // Optional extras (sc_w != nullptr; bf16 output with N == 128 only), computed in the epilogue from the tile it holds:
-//   tok[i][m] (two planes)  = sc_w[i,:]·y_m  from the fp32 row y_m
+//   tok[i][clip][j] (two planes, kTokPitch floats per clip) = sc_w[i,:]·y_m for row m = clip*seg_len + j, from the fp32 row
 //   colsum[clip][slot][128] = sum of the rows of `clip` (rows m in [clip*seg_len, +seg_len)) inside output tile
 //                             (clip*seg_len)/128 + slot; a clip overlaps at most kColsumSlots tiles.
 constexpr int kColsumSlots = 3;
+constexpr int kTokPitch = 160;   // floats per clip in each tok plane
 int gemm_tc_bf16(cudaStream_t st, const void* X, const void* W, const float* bias, void* out, bool out_bf16, int64_t out_pitch,
                  int M, int N, int K, const float* sc_w = nullptr, float* tok = nullptr, float* colsum = nullptr, int seg_len = 0);
 // 2D bf16 tensor map with SWIZZLE_128B boxes: `cols` contiguous elements per row, rows `pitch` elements apart (0 = cols).

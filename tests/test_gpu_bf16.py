@@ -58,7 +58,7 @@ def _ws_views(ws, B, T, Ta):
     E, EP = 128, 136
     spec = [("v0", torch.float32, (B, T, E)), ("a0", torch.bfloat16, (B * Ta, EP)), ("qt", torch.bfloat16, (B, 64, EP)),
             ("meanv", torch.float32, (B, E)), ("tqv", torch.float32, (B, 16)), ("tkv", torch.float32, (B, 16)),
-            ("u", torch.bfloat16, (B, 64, E)), ("tok", torch.float32, (2, B * Ta)), ("acol", torch.float32, (B, 3, E)),
+            ("u", torch.bfloat16, (B, 64, E)), ("tok", torch.float32, (2, B, 160)), ("acol", torch.float32, (B, 3, E)),
             ("pc", torch.float32, (B, 4)),
             ("kt", torch.bfloat16, (B, 64, EP)), ("vt", torch.bfloat16, (B, 64, EP)), ("cv", torch.float32, (B, 64)),
             ("pooled", torch.float32, (B, 2 * E))]
@@ -86,9 +86,9 @@ def _stage_report(m, xvb, xab, head, prior, dev):
     rep["a0"] = np.abs(w["a0"][:, :128].reshape(B, Ta, 128) - taps["a"]).max()
     _, p1 = xattn_oracle.multihead_attention(sd, "v2a_attn.", taps["v"], taps["a"], 4, taps["v2a_bias"], return_probs=True)
     u_ref = np.einsum("bhls,bse->bhle", p1, taps["a"])                       # U_h = P_h · a0
-    # U is stored in mma A-fragment order [clip][head][lane][ks][reg] x (2 bf16): lane = 4g+t, reg r -> row g+8(r&1),
+    # U is stored in mma A-fragment order [clip][head][ks][lane][reg] x (2 bf16): lane = 4g+t, reg r -> row g+8(r&1),
     # cols 16ks + 2t + 8(r>>1) + {0,1}
-    f = w["u"].reshape(B, 4, 32, 8, 4, 2)
+    f = w["u"].reshape(B, 4, 8, 32, 4, 2).transpose(0, 1, 3, 2, 4, 5)
     u_got = np.zeros((B, 4, 16, 128), dtype=np.float32)
     for lane in range(32):
         g_, t_ = lane >> 2, lane & 3
