@@ -328,6 +328,325 @@ __global__ void __launch_bounds__(kV2AThreads, 1) v2a_tc_kernel(const __grid_con
   if (warp == 1) tc::tmem_dealloc(tmem, 512);
 }
 
+
+// ---------------------------------------------------------------------------------------------------------------------------
+// a2v_tc_kernel — audio queries the updated video (fusion.py:398), residual + LayerNorm (:399), temporal mean (:402).
+// Two clips per pipeline step, their audio tokens stacked as 320 rows (clip 1 starts at row 160) and cut into three row
+// tiles: rows [0,128) and [128,256) as M=128 products, rows [256,320) as an M=64 product.  160 = 5 x 32, so every warp's
+// 32 rows belong to one clip.
+//   S  = a0_rows[M,128] · [Kt_0 ; Kt_1]^T        N = 128: columns 0-63 are the (head, key) scores against clip 0's video,
+//                                                64-127 against clip 1's; a row reads the half of its own clip
+//   P  = per-head softmax over the 16 keys of (S + c_hi + tanh(qa_j + kv_i)·s)    one thread per token row   (fusion.py:176)
+//        written back over S as bf16x2, the other clip's half as zeros
+//   O  = P[M,128] · [Vt_0 ; Vt_1]                A = P from tensor memory, B = the two Vt tiles stacked along K (MN-major);
+//                                                the zero half of P selects the clip, out_proj is already folded into Vt
+//   y  = LayerNorm(a0 + O + bo2) without the affine, rows kept in registers; the 32 rows of a warp are summed with a
+//        shuffle butterfly (4 columns per lane come out) and leave as one partial per (clip, tile, warp); the head kernel
+//        adds a clip's partials in a fixed order and applies gamma/Ta, beta (mean_t LN(x) = gamma·mean xhat + beta).
+//   warp 0: TMA producer   warp 1: MMA issuer, polls for whichever of {next S, next O} is ready
+//   warps 2-5 / 6-9: two softmax+LayerNorm groups alternating row tiles, each with its own 256-column TMEM buffer
+constexpr int kA2VThreads = 64 + 256;
+constexpr int kA2VHalf = 2 * kA0Box;                         // a0 stage layout: [feature half][clip][160 rows][128 B]
+constexpr int kKvHalf = 2 * kBox;                            // Kt / Vt layout:  [feature half][clip][64 rows][128 B]
+constexpr int kKvTile = 2 * kKvHalf;                         // 32 KB: both clips
+constexpr int kA2VOffKt = 2 * kA0Stage;
+constexpr int kA2VOffVt = kA2VOffKt + kKvTile;
+constexpr int kA2VOffKc = kA2VOffVt + kKvTile;               // [2 clips][80] f32: kv_i (16) | c_hi (64)
+constexpr int kA2VOffBo = kA2VOffKc + 2 * 80 * 4;            // [128] f32
+constexpr int kA2VOffBar = kA2VOffBo + BE * 4;
+constexpr int kA2VSmem = kA2VOffBar + 16 * 8 + 8;
+static_assert(kA2VSmem <= 227 * 1024, "a2v_tc_kernel shared memory");
+constexpr int kPoolSlots = 8;                                // partials per clip: even clip 5 (tile 0 x4, tile 1 warp 0), odd clip 7
+
+struct A2VTcArgs {
+  const float *tok, *tkv, *pc, *cv;    // [2,B,160], [B,16], [B,4], [B,64]
+  const float *bo2, *bias_scale;
+  float* poolp;                        // [B][kPoolSlots][128] partial sums of xhat over a warp's rows
+  int B, Ta, T, use_prior;
+  unsigned long long* trace;
+};
+
+__global__ void __launch_bounds__(kA2VThreads, 1) a2v_tc_kernel(const __grid_constant__ CUtensorMap tmA0,
+                                                                 const __grid_constant__ CUtensorMap tmKt,
+                                                                 const __grid_constant__ CUtensorMap tmVt, A2VTcArgs a) {
+  extern __shared__ __align__(1024) uint8_t smem[];
+  uint8_t* a0s = smem;
+  uint8_t* kts = smem + kA2VOffKt;
+  uint8_t* vts = smem + kA2VOffVt;
+  float* kc_s = reinterpret_cast<float*>(smem + kA2VOffKc);
+  float* bo_s = reinterpret_cast<float*>(smem + kA2VOffBo);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + kA2VOffBar);
+  uint64_t *a0_full = bars, *a0_empty = bars + 2, *kt_full = bars + 4, *kt_empty = bars + 5, *vt_full = bars + 6,
+           *vt_empty = bars + 7, *s_full = bars + 8, *p_full = bars + 10, *o_full = bars + 12, *o_empty = bars + 14;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 16);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int Ta = a.Ta;
+  const int npairs = (a.B + 1) / 2;
+  const int n_local = (npairs - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;
+  const uint32_t n_tiles = 3u * (uint32_t)(n_local > 0 ? n_local : 0);
+
+  if (threadIdx.x == 0) {
+    if ((tc::smem_u32(smem) & 1023u) != 0) __trap();
+    tc::tma_prefetch_desc(&tmA0);
+    tc::tma_prefetch_desc(&tmKt);
+    tc::tma_prefetch_desc(&tmVt);
+    for (int i = 0; i < 2; ++i) {
+      tc::mbar_init(&a0_full[i], 1);
+      tc::mbar_init(&a0_empty[i], 384);   // released by the rows themselves, after their residual read (3 tiles x 128 threads)
+      tc::mbar_init(&s_full[i], 1);
+      tc::mbar_init(&p_full[i], 128);
+      tc::mbar_init(&o_full[i], 1);
+      tc::mbar_init(&o_empty[i], 128);
+    }
+    tc::mbar_init(kt_full, 1);
+    tc::mbar_init(kt_empty, 384);         // likewise: the key constants that travel with Kt are read during the softmax
+    tc::mbar_init(vt_full, 1);
+    tc::mbar_init(vt_empty, 1);
+    tc::fence_barrier_init();
+  }
+  if (threadIdx.x >= 64 && threadIdx.x < 64 + BE) bo_s[threadIdx.x - 64] = __ldg(a.bo2 + threadIdx.x - 64);
+  if (warp == 1) tc::tmem_alloc(tmem_slot, 512);
+  tc::tc_fence_before();
+  __syncthreads();
+  tc::tc_fence_after();
+  const uint32_t tmem = *tmem_slot;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      uint32_t it = 0;
+      for (int p = blockIdx.x; p < npairs; p += gridDim.x, ++it) {
+        const uint32_t s = it & 1u, ph = (it >> 1) & 1u;
+        const int c0 = 2 * p, c1 = min(2 * p + 1, a.B - 1);
+        // Kt (+ the per-clip key constants) — free once the three score products of the previous pair have retired
+        while (!tc::mbar_try_wait(kt_empty, (it & 1u) ^ 1u)) __nanosleep(64);
+        tc::mbar_expect_tx(kt_full, kKvTile + 2 * 80 * 4);
+        for (int i = 0; i < 2; ++i) {
+          const int c = i == 0 ? c0 : c1;
+          tc::tma_load_2d(kts + i * kBox, &tmKt, kt_full, 0, c * 64);
+          tc::tma_load_2d(kts + kKvHalf + i * kBox, &tmKt, kt_full, 64, c * 64);
+          tc::bulk_load_1d(kc_s + i * 80, a.tkv + (int64_t)c * 16, 64, kt_full);
+          tc::bulk_load_1d(kc_s + i * 80 + 16, a.cv + (int64_t)c * 64, 256, kt_full);
+        }
+        while (!tc::mbar_try_wait(&a0_empty[s], ph ^ 1u)) __nanosleep(64);
+        tc::mbar_expect_tx(&a0_full[s], kA0Stage);
+        for (int i = 0; i < 2; ++i) {
+          uint8_t* dst = a0s + s * kA0Stage + i * kA0Box;
+          const int row = (2 * p + i) * Ta;   // rows past the clip / the tensor never reach the result (masked rows, OOB = 0)
+          tc::tma_load_2d(dst, &tmA0, &a0_full[s], 0, row);
+          tc::tma_load_2d(dst + kA2VHalf, &tmA0, &a0_full[s], 64, row);
+        }
+        while (!tc::mbar_try_wait(vt_empty, (it & 1u) ^ 1u)) __nanosleep(64);
+        tc::mbar_expect_tx(vt_full, kKvTile);
+        for (int i = 0; i < 2; ++i) {
+          const int c = i == 0 ? c0 : c1;
+          tc::tma_load_2d(vts + i * kBox, &tmVt, vt_full, 0, c * 64);
+          tc::tma_load_2d(vts + kKvHalf + i * kBox, &tmVt, vt_full, 64, c * 64);
+        }
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      constexpr uint32_t idesc128 = tc::umma_idesc_bf16_ex(128, 128, false, false), idesc64 = tc::umma_idesc_bf16_ex(64, 128, false, false);
+      constexpr uint32_t idesc128o = tc::umma_idesc_bf16_ex(128, 128, false, true), idesc64o = tc::umma_idesc_bf16_ex(64, 128, false, true);
+      // tile n: pair n / 3, row tile n % 3, TMEM buffer n & 1
+      auto s_ready = [&](uint32_t n) {
+        const uint32_t it = n / 3, t = n % 3, b = n & 1u;
+        if (t == 0 && !(tc::mbar_try_wait(kt_full, it & 1u) && tc::mbar_try_wait(&a0_full[it & 1u], (it >> 1) & 1u))) return false;
+        return n < 2 || tc::mbar_try_wait(&o_empty[b], ((n - 2) >> 1) & 1u);   // the buffer's previous tile has been drained
+      };
+      auto issue_s = [&](uint32_t n) {
+        const uint32_t it = n / 3, t = n % 3, b = n & 1u, s = it & 1u;
+        tc::tc_fence_after();
+        const uint64_t da0 = tc::umma_desc_sw128(tc::smem_u32(a0s + s * kA0Stage) + t * 128 * 128, 16, 1024);
+        const uint64_t db0 = tc::umma_desc_sw128(tc::smem_u32(kts), 16, 1024);
+        const uint32_t d = tmem + b * 256;
+#pragma unroll
+        for (int ks = 0; ks < 8; ++ks) {
+          const uint64_t da = da0 + (uint64_t)(((ks >> 2) * kA2VHalf + (ks & 3) * 32) >> 4);
+          const uint64_t db = db0 + (uint64_t)(((ks >> 2) * kKvHalf + (ks & 3) * 32) >> 4);
+          tc::umma_bf16(d, da, db, t == 2 ? idesc64 : idesc128, ks != 0);
+        }
+        tc::umma_commit(&s_full[b]);
+      };
+      auto o_ready = [&](uint32_t n) {
+        const uint32_t it = n / 3, t = n % 3, b = n & 1u;
+        if (t == 0 && !tc::mbar_try_wait(vt_full, it & 1u)) return false;
+        return tc::mbar_try_wait(&p_full[b], (n >> 1) & 1u);
+      };
+      auto issue_o = [&](uint32_t n) {
+        const uint32_t t = n % 3, b = n & 1u;
+        tc::tc_fence_after();
+        const uint64_t db0 = tc::umma_desc_sw128(tc::smem_u32(vts), kKvHalf, 1024);   // MN-major: K = (clip, head, key) rows
+        const uint32_t d = tmem + b * 256 + 128, pa = tmem + b * 256;
+#pragma unroll
+        for (int ks = 0; ks < 8; ++ks)
+          tc::umma_bf16_ts(d, pa + (uint32_t)(ks * 8), db0 + (uint64_t)((ks * 16 * 128) >> 4), t == 2 ? idesc64o : idesc128o, ks != 0);
+        tc::umma_commit(&o_full[b]);
+        if (t == 2) tc::umma_commit(vt_empty);
+      };
+      uint32_t ns = 0, no = 0;   // next score product / next output product to issue (ns runs at most one tile ahead of no + 1)
+      while (no < n_tiles) {
+        bool progressed = false;
+        if (ns < n_tiles && ns <= no + 1 && s_ready(ns)) {
+          issue_s(ns++);
+          progressed = true;
+        }
+        if (no < ns && o_ready(no)) {
+          issue_o(no++);
+          progressed = true;
+        }
+        if (!progressed) __nanosleep(32);
+      }
+    }
+  } else {
+    // ---- softmax + LayerNorm warps: group g handles the tiles with n & 1 == g in TMEM buffer g ----
+    const int sp = warp & 3, grp = (warp - 2) >> 2;
+    const uint32_t tlane = (uint32_t)(32 * sp) << 16;
+    const uint32_t tbuf = tmem + grp * 256 + tlane;
+    const float bsc = a.use_prior ? __ldg(a.bias_scale) : 0.f;
+    const float bl = bsc * kL2E;
+    for (uint32_t n = grp; n < n_tiles; n += 2) {
+      const uint32_t it = n / 3, t = n % 3, s = it & 1u;
+      const int p = blockIdx.x + (int)it * (int)gridDim.x;
+      const bool m64 = t == 2;
+      const int R = 128 * (int)t + (m64 ? 16 * sp + (lane & 15) : 32 * sp + lane);   // row of the 320-row pair
+      const int ci = R >= BTAP ? 1 : 0, j = R - BTAP * ci;                            // warp-uniform clip, token index
+      const int c = 2 * p + ci;
+      const bool valid = j < Ta && c < a.B && !(m64 && lane >= 16);
+      float qa = 0.f;   // a_query token score + prior part (fusion.py:174)
+      if (a.use_prior && valid) qa = __ldg(a.tok + ((int64_t)a.B + c) * BTAP + j) + __ldg(a.pc + (int64_t)c * 4 + 2);
+      const float pk = (a.use_prior && c < a.B) ? __ldg(a.pc + (int64_t)c * 4 + 3) : 0.f;
+      tc::mbar_wait(&s_full[grp], (n >> 1) & 1u);
+      tc::mbar_wait(kt_full, it & 1u);        // already complete; acquires the TMA-written key constants
+      tc::tc_fence_after();
+      {
+        uint32_t r0[32], r1[32];              // the 4 heads x 16 keys of this row against its own clip
+        tc::tmem_ld_32x32(tbuf + (uint32_t)(64 * ci), r0);
+        tc::tmem_ld_32x32(tbuf + (uint32_t)(64 * ci + 32), r1);
+        const float* kc = kc_s + ci * 80;
+        float bia[16];   // the prior bias is the same for every head (fusion.py:351-354): once per key
+#pragma unroll
+        for (int i = 0; i < 16; ++i) {
+          bia[i] = a.use_prior ? tc::tanh_fast(qa + kc[i] + pk) * bl : 0.f;
+          if (i >= a.T) bia[i] = -INFINITY;   // padded video tokens never receive probability mass
+        }
+        tc::tmem_ld_wait();
+        uint32_t pk2[32];
+#pragma unroll
+        for (int hh = 0; hh < BH; ++hh) {
+          float x[16];
+          float m = -INFINITY;
+#pragma unroll
+          for (int i = 0; i < 16; ++i) {
+            const float sc = __uint_as_float(hh < 2 ? r0[16 * hh + i] : r1[16 * (hh - 2) + i]);
+            x[i] = fmaf(sc + kc[16 + 16 * hh + i], kL2E, bia[i]);
+            m = fmaxf(m, x[i]);
+          }
+          float l0 = 0.f, l1 = 0.f;
+#pragma unroll
+          for (int i = 0; i < 16; i += 2) {
+            x[i] = ex2_fast(x[i] - m);
+            x[i + 1] = ex2_fast(x[i + 1] - m);
+            l0 += x[i];
+            l1 += x[i + 1];
+          }
+          const float inv = __frcp_rn(l0 + l1);
+#pragma unroll
+          for (int i = 0; i < 16; i += 2) pk2[8 * hh + (i >> 1)] = tc::pack_bf16(x[i] * inv, x[i + 1] * inv);
+        }
+        uint32_t z[16];
+#pragma unroll
+        for (int i = 0; i < 16; ++i) z[i] = 0u;
+        uint32_t lo[16], hi[16];
+#pragma unroll
+        for (int i = 0; i < 16; ++i) {
+          lo[i] = pk2[i];
+          hi[i] = pk2[16 + i];
+        }
+        tc::tmem_st_32x32_x16(tbuf + (uint32_t)(32 * ci), lo);
+        tc::tmem_st_32x32_x16(tbuf + (uint32_t)(32 * ci + 16), hi);
+        tc::tmem_st_32x32_x16(tbuf + (uint32_t)(32 * (ci ^ 1)), z);
+        tc::tmem_st_32x32_x16(tbuf + (uint32_t)(32 * (ci ^ 1) + 16), z);
+        tc::tmem_st_wait();
+        tc::tc_fence_before();
+        tc::mbar_arrive(&p_full[grp]);
+        tc::mbar_arrive(kt_empty);             // done with Kt (S is complete) and with kc_s
+      }
+      // ---- a1 = LayerNorm(a0 + out + bo2) (fusion.py:399) accumulated into the temporal mean (:402) ----
+      float x[BE];
+      const uint8_t* arow = a0s + s * kA0Stage + R * 128;
+      tc::mbar_wait(&o_full[grp], (n >> 1) & 1u);
+      tc::tc_fence_after();
+      float sum0 = 0.f, sum1 = 0.f;
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        uint32_t r[32];
+        tc::tmem_ld_32x32(tbuf + 128u + (uint32_t)(32 * k), r);
+        uint4 res[4];
+#pragma unroll
+        for (int v = 0; v < 4; ++v)
+          res[v] = *reinterpret_cast<const uint4*>(arow + (k >> 1) * kA2VHalf + ((((4 * (k & 1) + v) ^ R) & 7) << 4));
+        tc::tmem_ld_wait();
+#pragma unroll
+        for (int v = 0; v < 4; ++v) {
+          const uint32_t w[4] = {res[v].x, res[v].y, res[v].z, res[v].w};
+#pragma unroll
+          for (int e = 0; e < 4; ++e) {
+            const int col = 32 * k + 8 * v + 2 * e;
+            const float2 bo = *reinterpret_cast<const float2*>(bo_s + col);
+            const float xa = __uint_as_float(r[8 * v + 2 * e]) + __uint_as_float(w[e] << 16) + bo.x;
+            const float xb = __uint_as_float(r[8 * v + 2 * e + 1]) + __uint_as_float(w[e] & 0xFFFF0000u) + bo.y;
+            x[col] = xa;
+            x[col + 1] = xb;
+            sum0 += xa;
+            sum1 += xb;
+          }
+        }
+      }
+      tc::tc_fence_before();
+      tc::mbar_arrive(&o_empty[grp]);          // O (and the P it was made from) is in registers: the buffer can be refilled
+      tc::mbar_arrive(&a0_empty[s]);           // and so is this row's residual
+      const float mu = (sum0 + sum1) * (1.f / BE);
+      float q0 = 0.f, q1 = 0.f;
+#pragma unroll
+      for (int i = 0; i < BE; i += 2) {        // two-pass variance (as torch LayerNorm): sum (x - mu)^2
+        x[i] -= mu;
+        x[i + 1] -= mu;
+        q0 = fmaf(x[i], x[i], q0);
+        q1 = fmaf(x[i + 1], x[i + 1], q1);
+      }
+      const float rs = rsqrtf((q0 + q1) * (1.f / BE) + 1e-5f);
+#pragma unroll
+      for (int i = 0; i < BE; ++i) x[i] = valid ? x[i] * rs : 0.f;   // padded / absent rows contribute nothing (select, not multiply)
+      // sum over the warp's 32 rows: butterfly, the live columns halve at every step; lane L ends with columns 32b + rev...
+#pragma unroll
+      for (int off = 16, cnt = BE / 2; off >= 1; off >>= 1, cnt >>= 1) {
+        const bool up = (lane & off) != 0;
+#pragma unroll
+        for (int i = 0; i < cnt; ++i) {
+          const float send = up ? x[i] : x[i + cnt];
+          const float keep = up ? x[i + cnt] : x[i];
+          x[i] = keep + __shfl_xor_sync(0xffffffffu, send, off);
+        }
+      }
+      // after the five steps lane L holds columns {cidx(L) + 0..3}: bit k of L chose the upper half at step k
+      {
+        int base = 0;
+#pragma unroll
+        for (int off = 16, cnt = BE / 2; off >= 1; off >>= 1, cnt >>= 1)
+          if (lane & off) base += cnt;
+        // slot of this (clip, tile, warp): even clip: tile 0 warps 0-3 -> 0-3, tile 1 warp 0 -> 4; odd clip: tile 1 warps 1-3 -> 0-2, tile 2 -> 3-6
+        const int slot = ci == 0 ? (t == 0 ? sp : 4) : (t == 1 ? sp - 1 : 3 + sp);
+        if (c < a.B) *reinterpret_cast<float4*>(a.poolp + ((int64_t)c * kPoolSlots + slot) * BE + base) = make_float4(x[0], x[1], x[2], x[3]);
+      }
+    }
+  }
+  tc::tc_fence_before();
+  __syncthreads();
+  if (warp == 1) tc::tmem_dealloc(tmem, 512);
+}
+
 }  // namespace
 
 int launch_v2a_tc(const Bf16Ctx& x) {
@@ -375,6 +694,38 @@ int launch_v2a_tc(const Bf16Ctx& x) {
       fprintf(stderr, "\n");
     }
   }
+  return XATTN_OK;
+}
+
+
+
+int launch_a2v_tc(const Bf16Ctx& x) {
+  const xattn_config& c = *x.cfg;
+  auto P = [&](int id) { return x.params + x.pl.off[id]; };
+  A2VTcArgs a;
+  a.tok = reinterpret_cast<const float*>(x.ws + x.w.tok);
+  a.tkv = reinterpret_cast<const float*>(x.ws + x.w.tkv);
+  a.pc = reinterpret_cast<const float*>(x.ws + x.w.pc);
+  a.cv = reinterpret_cast<const float*>(x.ws + x.w.cv);
+  a.bo2 = P(XP_A2V_OUT_B);
+  a.bias_scale = P(XP_BIAS_SCALE);
+  a.poolp = reinterpret_cast<float*>(x.ws + x.w.poolp);
+  a.B = c.B; a.Ta = c.Ta; a.T = c.T; a.use_prior = c.use_prior;
+  a.trace = nullptr;
+  alignas(64) CUtensorMap tmA0, tmKt, tmVt;
+  XF_TRY(make_tmap_bf16_2d(&tmA0, x.ws + x.w.a0, (int64_t)c.B * c.Ta, BE, BTAP, 64, BEP));
+  XF_TRY(make_tmap_bf16_2d(&tmKt, x.ws + x.w.kt, (int64_t)c.B * 64, BE, 64, 64, BEP));
+  XF_TRY(make_tmap_bf16_2d(&tmVt, x.ws + x.w.vt, (int64_t)c.B * 64, BE, 64, 64, BEP));
+  static bool configured = false;
+  if (!configured) {
+    XF_CUDA(cudaFuncSetAttribute(a2v_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kA2VSmem));
+    configured = true;
+  }
+  const int npairs = (c.B + 1) / 2;
+  const int grid = npairs < num_sms() ? npairs : num_sms();
+  a2v_tc_kernel<<<grid, kA2VThreads, kA2VSmem, x.st>>>(tmA0, tmKt, tmVt, a);
+  count_launch();
+  XF_LAUNCH_CHECK();
   return XATTN_OK;
 }
 

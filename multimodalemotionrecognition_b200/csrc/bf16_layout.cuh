@@ -53,6 +53,7 @@ struct WsBf16 {
   int64_t kt, vt;   // bf16 [B,64,BEP]
   int64_t cv;       // f32  [B,64]
   int64_t pooled;   // f32  [B,2E]
+  int64_t poolp;    // f32  [B,8,E]    per-warp partial sums of LayerNorm-ed audio rows (a2v_tc -> head)
   int64_t total;
 };
 void compute_ws_bf16(const xattn_config& c, WsBf16& w);
@@ -74,6 +75,7 @@ int launch_video_pre(const Bf16Ctx& x);
 int launch_prior(const Bf16Ctx& x);
 int launch_v2a_attn(const Bf16Ctx& x);   // mma.sync version (kept for A/B runs: XATTN_ATTN=legacy)
 int launch_v2a_tc(const Bf16Ctx& x);     // tcgen05 version
+int launch_a2v_tc(const Bf16Ctx& x);     // tcgen05 version: leaves pooled_a as partial sums in ws.poolp
 int launch_video_update(const Bf16Ctx& x);
 int launch_a2v_attn(const Bf16Ctx& x);
 int launch_head_pooled(const Bf16Ctx& x, float* logits);

@@ -68,6 +68,7 @@ void compute_ws_bf16(const xattn_config& c, WsBf16& w) {
   w.vt = take(B * 64 * BEP * 2);
   w.cv = take(B * 64 * 4);
   w.pooled = take(B * 2 * E * 4);
+  w.poolp = take(B * 8 * E * 4);
   w.total = off + 256;
 }
 

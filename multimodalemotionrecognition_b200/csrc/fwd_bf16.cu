@@ -15,7 +15,10 @@ namespace {
 constexpr int kHeadClips = 16;   // clips per CTA of the head kernel: each weight element is read once per 16 clips
 
 struct HeadPooledArgs {
-  const float* pooled;   // [B,2E] = [pooled_v ; pooled_a]
+  float* pooled;         // [B,2E] = [pooled_v ; pooled_a]
+  const float* poolp;    // [B,8,E] partial sums of the normalised audio rows (tcgen05 a2v) or nullptr (pooled_a already final)
+  const float *an_w, *an_b;   // a_norm affine, applied here when poolp is set: mean_t LN(x) = gamma * mean xhat + beta
+  int Ta;
   const __nv_bfloat16* w0b;   // [HW,2E] layer 0 weight, bf16
   const float *b0, *w1, *b1, *wc, *bc;
   float* logits;
@@ -45,7 +48,24 @@ __global__ void __launch_bounds__(256) head_pooled_kernel(HeadPooledArgs a) {
   for (int i = tid; i < kHeadClips * 2 * BE / 2; i += blockDim.x) {
     const int cc = i / BE, k = (i % BE) * 2;
     float2 x = make_float2(0.f, 0.f);
-    if (cc < nc) x = *reinterpret_cast<const float2*>(a.pooled + (int64_t)(c0 + cc) * 2 * BE + k);
+    if (cc < nc) {
+      const int64_t c = c0 + cc;
+      if (a.poolp != nullptr && k >= BE) {   // add the clip's partials in slot order (even clips own 5 slots, odd clips 7)
+        const int ns = (c & 1) ? 7 : 5;
+        const float* pp = a.poolp + c * 8 * BE + (k - BE);
+        for (int s2 = 0; s2 < ns; ++s2) {
+          const float2 v = *reinterpret_cast<const float2*>(pp + s2 * BE);
+          x.x += v.x;
+          x.y += v.y;
+        }
+        const float inv = 1.f / (float)a.Ta;
+        x.x = a.an_w[k - BE] * (x.x * inv) + a.an_b[k - BE];
+        x.y = a.an_w[k - BE + 1] * (x.y * inv) + a.an_b[k - BE + 1];
+        *reinterpret_cast<float2*>(a.pooled + c * 2 * BE + k) = x;
+      } else {
+        x = *reinterpret_cast<const float2*>(a.pooled + c * 2 * BE + k);
+      }
+    }
     const __nv_bfloat162 h = __floats2bfloat162_rn(x.x, x.y);
     *reinterpret_cast<__nv_bfloat162*>(&xhi[cc][k]) = h;
     *reinterpret_cast<__nv_bfloat162*>(&xlo[cc][k]) = __floats2bfloat162_rn(x.x - __low2float(h), x.y - __high2float(h));
@@ -137,11 +157,16 @@ __global__ void __launch_bounds__(256) head_pooled_kernel(HeadPooledArgs a) {
 
 }  // namespace
 
+static bool attn_legacy();
+
 int launch_head_pooled(const Bf16Ctx& x, float* logits) {
   const xattn_config& c = *x.cfg;
   auto P = [&](int id) { return x.params + x.pl.off[id]; };
   HeadPooledArgs a;
-  a.pooled = reinterpret_cast<const float*>(x.ws + x.w.pooled);
+  a.pooled = reinterpret_cast<float*>(x.ws + x.w.pooled);
+  a.poolp = attn_legacy() ? nullptr : reinterpret_cast<const float*>(x.ws + x.w.poolp);
+  a.an_w = P(XP_AN_W); a.an_b = P(XP_AN_B);
+  a.Ta = c.Ta;
   a.w0b = reinterpret_cast<const __nv_bfloat16*>(x.packed + x.pk.W0b);
   a.b0 = P(XP_HEAD0_B); a.w1 = P(XP_HEAD1_W); a.b1 = P(XP_HEAD1_B); a.wc = P(XP_CLS_W); a.bc = P(XP_CLS_B);
   a.logits = logits;
@@ -228,7 +253,7 @@ int forward_bf16(const xattn_config& c, const float* params, const void* packed,
   if (c.use_prior) { StageScope t(ST_PRIOR, st); XF_TRY(launch_prior(x)); }
   { StageScope t(ST_V2A, st); XF_TRY(attn_legacy() ? launch_v2a_attn(x) : launch_v2a_tc(x)); }
   { StageScope t(ST_VIDEO_UPD, st); XF_TRY(launch_video_update(x)); }
-  { StageScope t(ST_A2V, st); XF_TRY(launch_a2v_attn(x)); }
+  { StageScope t(ST_A2V, st); XF_TRY(attn_legacy() ? launch_a2v_attn(x) : launch_a2v_tc(x)); }
   { StageScope t(ST_HEAD, st); XF_TRY(launch_head_pooled(x, logits)); }
   return XATTN_OK;
 }

