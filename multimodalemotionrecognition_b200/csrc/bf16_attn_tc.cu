@@ -340,7 +340,7 @@ __global__ void __launch_bounds__(kV2AThreads, 1) v2a_tc_kernel(const __grid_con
 //        written back over S as bf16x2, the other clip's half as zeros
 //   O  = P[M,128] · [Vt_0 ; Vt_1]                A = P from tensor memory, B = the two Vt tiles stacked along K (MN-major);
 //                                                the zero half of P selects the clip, out_proj is already folded into Vt
-//   y  = LayerNorm(a0 + O + bo2) without the affine, rows kept in registers; the 32 rows of a warp are summed with a
+//   y  = LayerNorm(a0 + O) without the affine (out_proj's bias bo2 rides in Vt), rows kept in registers; the 32 rows of a warp are summed with a
 //        shuffle butterfly (4 columns per lane come out) and leave as one partial per (clip, tile, warp); the head kernel
 //        adds a clip's partials in a fixed order and applies gamma/Ta, beta (mean_t LN(x) = gamma·mean xhat + beta).
 //   warp 0: TMA producer   warp 1: MMA issuer, polls for whichever of {next S, next O} is ready
@@ -351,16 +351,15 @@ constexpr int kKvHalf = 2 * kBox;                            // Kt / Vt layout: 
 constexpr int kKvTile = 2 * kKvHalf;                         // 32 KB: both clips
 constexpr int kA2VOffKt = 2 * kA0Stage;
 constexpr int kA2VOffVt = kA2VOffKt + kKvTile;
-constexpr int kA2VOffKc = kA2VOffVt + kKvTile;               // [2 clips][80] f32: kv_i (16) | c_hi (64)
-constexpr int kA2VOffBo = kA2VOffKc + 2 * 80 * 4;            // [128] f32
-constexpr int kA2VOffBar = kA2VOffBo + BE * 4;
+constexpr int kA2VOffKc = kA2VOffVt + kKvTile;               // [2 stages][2 clips][80] f32: kv_i (16) | c_hi (64), travels with the a0 stage
+constexpr int kA2VOffBar = kA2VOffKc + 4 * 80 * 4;
 constexpr int kA2VSmem = kA2VOffBar + 16 * 8 + 8;
 static_assert(kA2VSmem <= 227 * 1024, "a2v_tc_kernel shared memory");
 constexpr int kPoolSlots = 8;                                // partials per clip: even clip 5 (tile 0 x4, tile 1 warp 0), odd clip 7
 
 struct A2VTcArgs {
   const float *tok, *tkv, *pc, *cv;    // [2,B,160], [B,16], [B,4], [B,64]
-  const float *bo2, *bias_scale;
+  const float* bias_scale;
   float* poolp;                        // [B][kPoolSlots][128] partial sums of xhat over a warp's rows
   int B, Ta, T, use_prior;
   unsigned long long* trace;
@@ -374,7 +373,6 @@ __global__ void __launch_bounds__(kA2VThreads, 1) a2v_tc_kernel(const __grid_con
   uint8_t* kts = smem + kA2VOffKt;
   uint8_t* vts = smem + kA2VOffVt;
   float* kc_s = reinterpret_cast<float*>(smem + kA2VOffKc);
-  float* bo_s = reinterpret_cast<float*>(smem + kA2VOffBo);
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + kA2VOffBar);
   uint64_t *a0_full = bars, *a0_empty = bars + 2, *kt_full = bars + 4, *kt_empty = bars + 5, *vt_full = bars + 6,
            *vt_empty = bars + 7, *s_full = bars + 8, *p_full = bars + 10, *o_full = bars + 12, *o_empty = bars + 14;
@@ -400,12 +398,11 @@ __global__ void __launch_bounds__(kA2VThreads, 1) a2v_tc_kernel(const __grid_con
       tc::mbar_init(&o_empty[i], 128);
     }
     tc::mbar_init(kt_full, 1);
-    tc::mbar_init(kt_empty, 384);         // likewise: the key constants that travel with Kt are read during the softmax
+    tc::mbar_init(kt_empty, 1);
     tc::mbar_init(vt_full, 1);
     tc::mbar_init(vt_empty, 1);
     tc::fence_barrier_init();
   }
-  if (threadIdx.x >= 64 && threadIdx.x < 64 + BE) bo_s[threadIdx.x - 64] = __ldg(a.bo2 + threadIdx.x - 64);
   if (warp == 1) tc::tmem_alloc(tmem_slot, 512);
   tc::tc_fence_before();
   __syncthreads();
@@ -418,23 +415,25 @@ __global__ void __launch_bounds__(kA2VThreads, 1) a2v_tc_kernel(const __grid_con
       for (int p = blockIdx.x; p < npairs; p += gridDim.x, ++it) {
         const uint32_t s = it & 1u, ph = (it >> 1) & 1u;
         const int c0 = 2 * p, c1 = min(2 * p + 1, a.B - 1);
-        // Kt (+ the per-clip key constants) — free once the three score products of the previous pair have retired
-        while (!tc::mbar_try_wait(kt_empty, (it & 1u) ^ 1u)) __nanosleep(64);
-        tc::mbar_expect_tx(kt_full, kKvTile + 2 * 80 * 4);
-        for (int i = 0; i < 2; ++i) {
-          const int c = i == 0 ? c0 : c1;
-          tc::tma_load_2d(kts + i * kBox, &tmKt, kt_full, 0, c * 64);
-          tc::tma_load_2d(kts + kKvHalf + i * kBox, &tmKt, kt_full, 64, c * 64);
-          tc::bulk_load_1d(kc_s + i * 80, a.tkv + (int64_t)c * 16, 64, kt_full);
-          tc::bulk_load_1d(kc_s + i * 80 + 16, a.cv + (int64_t)c * 64, 256, kt_full);
-        }
         while (!tc::mbar_try_wait(&a0_empty[s], ph ^ 1u)) __nanosleep(64);
-        tc::mbar_expect_tx(&a0_full[s], kA0Stage);
+        trace_mark(a.trace, 0, 3 * it);   // a0 stage free, loads issued
+        tc::mbar_expect_tx(&a0_full[s], kA0Stage + 2 * 80 * 4);
         for (int i = 0; i < 2; ++i) {
           uint8_t* dst = a0s + s * kA0Stage + i * kA0Box;
           const int row = (2 * p + i) * Ta;   // rows past the clip / the tensor never reach the result (masked rows, OOB = 0)
           tc::tma_load_2d(dst, &tmA0, &a0_full[s], 0, row);
           tc::tma_load_2d(dst + kA2VHalf, &tmA0, &a0_full[s], 64, row);
+          const int c = i == 0 ? c0 : c1;   // the clip's key-side constants live and die with its a0 tile
+          tc::bulk_load_1d(kc_s + (s * 2 + i) * 80, a.tkv + (int64_t)c * 16, 64, &a0_full[s]);
+          tc::bulk_load_1d(kc_s + (s * 2 + i) * 80 + 16, a.cv + (int64_t)c * 64, 256, &a0_full[s]);
+        }
+        // Kt (+ the per-clip key constants) — free once the three score products of the previous pair have retired
+        while (!tc::mbar_try_wait(kt_empty, (it & 1u) ^ 1u)) __nanosleep(64);
+        tc::mbar_expect_tx(kt_full, kKvTile);
+        for (int i = 0; i < 2; ++i) {
+          const int c = i == 0 ? c0 : c1;
+          tc::tma_load_2d(kts + i * kBox, &tmKt, kt_full, 0, c * 64);
+          tc::tma_load_2d(kts + kKvHalf + i * kBox, &tmKt, kt_full, 64, c * 64);
         }
         while (!tc::mbar_try_wait(vt_empty, (it & 1u) ^ 1u)) __nanosleep(64);
         tc::mbar_expect_tx(vt_full, kKvTile);
@@ -452,11 +451,12 @@ __global__ void __launch_bounds__(kA2VThreads, 1) a2v_tc_kernel(const __grid_con
       // tile n: pair n / 3, row tile n % 3, TMEM buffer n & 1
       auto s_ready = [&](uint32_t n) {
         const uint32_t it = n / 3, t = n % 3, b = n & 1u;
-        if (t == 0 && !(tc::mbar_try_wait(kt_full, it & 1u) && tc::mbar_try_wait(&a0_full[it & 1u], (it >> 1) & 1u))) return false;
-        return n < 2 || tc::mbar_try_wait(&o_empty[b], ((n - 2) >> 1) & 1u);   // the buffer's previous tile has been drained
+        if (t == 0 && !(tc::mbar_test_wait(kt_full, it & 1u) && tc::mbar_test_wait(&a0_full[it & 1u], (it >> 1) & 1u))) return false;
+        return n < 2 || tc::mbar_test_wait(&o_empty[b], ((n - 2) >> 1) & 1u);   // the buffer's previous tile has been drained
       };
       auto issue_s = [&](uint32_t n) {
         const uint32_t it = n / 3, t = n % 3, b = n & 1u, s = it & 1u;
+        trace_mark(a.trace, 1, n);   // S issued
         tc::tc_fence_after();
         const uint64_t da0 = tc::umma_desc_sw128(tc::smem_u32(a0s + s * kA0Stage) + t * 128 * 128, 16, 1024);
         const uint64_t db0 = tc::umma_desc_sw128(tc::smem_u32(kts), 16, 1024);
@@ -468,14 +468,16 @@ __global__ void __launch_bounds__(kA2VThreads, 1) a2v_tc_kernel(const __grid_con
           tc::umma_bf16(d, da, db, t == 2 ? idesc64 : idesc128, ks != 0);
         }
         tc::umma_commit(&s_full[b]);
+        if (t == 2) tc::umma_commit(kt_empty);   // last score product of the pair
       };
       auto o_ready = [&](uint32_t n) {
         const uint32_t it = n / 3, t = n % 3, b = n & 1u;
-        if (t == 0 && !tc::mbar_try_wait(vt_full, it & 1u)) return false;
-        return tc::mbar_try_wait(&p_full[b], (n >> 1) & 1u);
+        if (t == 0 && !tc::mbar_test_wait(vt_full, it & 1u)) return false;
+        return tc::mbar_test_wait(&p_full[b], (n >> 1) & 1u);
       };
       auto issue_o = [&](uint32_t n) {
         const uint32_t t = n % 3, b = n & 1u;
+        trace_mark(a.trace, 2, n);   // O issued
         tc::tc_fence_after();
         const uint64_t db0 = tc::umma_desc_sw128(tc::smem_u32(vts), kKvHalf, 1024);   // MN-major: K = (clip, head, key) rows
         const uint32_t d = tmem + b * 256 + 128, pa = tmem + b * 256;
@@ -496,7 +498,7 @@ __global__ void __launch_bounds__(kA2VThreads, 1) a2v_tc_kernel(const __grid_con
           issue_o(no++);
           progressed = true;
         }
-        if (!progressed) __nanosleep(32);
+        if (!progressed) __nanosleep(20);
       }
     }
   } else {
@@ -506,25 +508,43 @@ __global__ void __launch_bounds__(kA2VThreads, 1) a2v_tc_kernel(const __grid_con
     const uint32_t tbuf = tmem + grp * 256 + tlane;
     const float bsc = a.use_prior ? __ldg(a.bias_scale) : 0.f;
     const float bl = bsc * kL2E;
+    // row of tile n owned by this thread: R in the 320-row pair (clip 1 starts at 160), clip c, token j
+    auto row_of = [&](uint32_t n, int& R, int& ci, int& c, bool& valid) {
+      const uint32_t it = n / 3, t = n % 3;
+      const int p = blockIdx.x + (int)it * (int)gridDim.x;
+      R = 128 * (int)t + (t == 2 ? 16 * sp + (lane & 15) : 32 * sp + lane);
+      ci = R >= BTAP ? 1 : 0;                                                 // warp-uniform: 160 = 5 x 32
+      c = 2 * p + ci;
+      valid = n < n_tiles && R - BTAP * ci < Ta && c < a.B && !(t == 2 && lane >= 16);
+    };
+    // a_query token score + prior part (fusion.py:174) and the v_key prior part of the row's clip
+    auto row_consts = [&](uint32_t n, float& qa, float& pk) {
+      int R, ci, c;
+      bool valid;
+      row_of(n, R, ci, c, valid);
+      qa = pk = 0.f;
+      if (a.use_prior && valid) {
+        qa = __ldg(a.tok + ((int64_t)a.B + c) * BTAP + (R - BTAP * ci)) + __ldg(a.pc + (int64_t)c * 4 + 2);
+        pk = __ldg(a.pc + (int64_t)c * 4 + 3);
+      }
+    };
+    float qa_n, pk_n;
+    row_consts(grp, qa_n, pk_n);
     for (uint32_t n = grp; n < n_tiles; n += 2) {
       const uint32_t it = n / 3, t = n % 3, s = it & 1u;
-      const int p = blockIdx.x + (int)it * (int)gridDim.x;
-      const bool m64 = t == 2;
-      const int R = 128 * (int)t + (m64 ? 16 * sp + (lane & 15) : 32 * sp + lane);   // row of the 320-row pair
-      const int ci = R >= BTAP ? 1 : 0, j = R - BTAP * ci;                            // warp-uniform clip, token index
-      const int c = 2 * p + ci;
-      const bool valid = j < Ta && c < a.B && !(m64 && lane >= 16);
-      float qa = 0.f;   // a_query token score + prior part (fusion.py:174)
-      if (a.use_prior && valid) qa = __ldg(a.tok + ((int64_t)a.B + c) * BTAP + j) + __ldg(a.pc + (int64_t)c * 4 + 2);
-      const float pk = (a.use_prior && c < a.B) ? __ldg(a.pc + (int64_t)c * 4 + 3) : 0.f;
+      int R, ci, c;
+      bool valid;
+      row_of(n, R, ci, c, valid);
+      const float qa = qa_n, pk = pk_n;
       tc::mbar_wait(&s_full[grp], (n >> 1) & 1u);
-      tc::mbar_wait(kt_full, it & 1u);        // already complete; acquires the TMA-written key constants
+      tc::mbar_wait(&a0_full[s], (it >> 1) & 1u);   // already complete; acquires the TMA-written key constants
+      if (sp == 2 && lane == 0) trace_mark(a.trace, 3, n);   // worker: scores ready
       tc::tc_fence_after();
       {
         uint32_t r0[32], r1[32];              // the 4 heads x 16 keys of this row against its own clip
         tc::tmem_ld_32x32(tbuf + (uint32_t)(64 * ci), r0);
         tc::tmem_ld_32x32(tbuf + (uint32_t)(64 * ci + 32), r1);
-        const float* kc = kc_s + ci * 80;
+        const float* kc = kc_s + (s * 2 + ci) * 80;
         float bia[16];   // the prior bias is the same for every head (fusion.py:351-354): once per key
 #pragma unroll
         for (int i = 0; i < 16; ++i) {
@@ -571,42 +591,46 @@ __global__ void __launch_bounds__(kA2VThreads, 1) a2v_tc_kernel(const __grid_con
         tc::tmem_st_wait();
         tc::tc_fence_before();
         tc::mbar_arrive(&p_full[grp]);
-        tc::mbar_arrive(kt_empty);             // done with Kt (S is complete) and with kc_s
+        if (sp == 2 && lane == 0) trace_mark(a.trace, 4, n);   // worker: P written
       }
-      // ---- a1 = LayerNorm(a0 + out + bo2) (fusion.py:399) accumulated into the temporal mean (:402) ----
+      row_consts(n + 2, qa_n, pk_n);           // next tile's row constants: in flight during the LayerNorm below
+      // ---- a1 = LayerNorm(a0 + out [+ bo2, inside out]) (fusion.py:399) accumulated into the temporal mean (:402) ----
       float x[BE];
       const uint8_t* arow = a0s + s * kA0Stage + R * 128;
       tc::mbar_wait(&o_full[grp], (n >> 1) & 1u);
+      if (sp == 2 && lane == 0) trace_mark(a.trace, 5, n);   // worker: O ready
       tc::tc_fence_after();
-      float sum0 = 0.f, sum1 = 0.f;
-#pragma unroll
-      for (int k = 0; k < 4; ++k) {
-        uint32_t r[32];
-        tc::tmem_ld_32x32(tbuf + 128u + (uint32_t)(32 * k), r);
-        uint4 res[4];
-#pragma unroll
-        for (int v = 0; v < 4; ++v)
-          res[v] = *reinterpret_cast<const uint4*>(arow + (k >> 1) * kA2VHalf + ((((4 * (k & 1) + v) ^ R) & 7) << 4));
+      {
+        uint32_t (&xr)[BE] = reinterpret_cast<uint32_t (&)[BE]>(x);
+        uint32_t t0[32], t1[32], t2[32], t3[32];
+        tc::tmem_ld_32x32(tbuf + 128u, t0);
+        tc::tmem_ld_32x32(tbuf + 160u, t1);
+        tc::tmem_ld_32x32(tbuf + 192u, t2);
+        tc::tmem_ld_32x32(tbuf + 224u, t3);
         tc::tmem_ld_wait();
 #pragma unroll
-        for (int v = 0; v < 4; ++v) {
-          const uint32_t w[4] = {res[v].x, res[v].y, res[v].z, res[v].w};
+        for (int i = 0; i < 32; ++i) {
+          xr[i] = t0[i]; xr[32 + i] = t1[i]; xr[64 + i] = t2[i]; xr[96 + i] = t3[i];
+        }
+      }
+      float sum0 = 0.f, sum1 = 0.f;
 #pragma unroll
-          for (int e = 0; e < 4; ++e) {
-            const int col = 32 * k + 8 * v + 2 * e;
-            const float2 bo = *reinterpret_cast<const float2*>(bo_s + col);
-            const float xa = __uint_as_float(r[8 * v + 2 * e]) + __uint_as_float(w[e] << 16) + bo.x;
-            const float xb = __uint_as_float(r[8 * v + 2 * e + 1]) + __uint_as_float(w[e] & 0xFFFF0000u) + bo.y;
-            x[col] = xa;
-            x[col + 1] = xb;
-            sum0 += xa;
-            sum1 += xb;
-          }
+      for (int k = 0; k < 16; ++k) {   // + this row of a0 (the residual, 16-byte chunk k of the swizzled row)
+        const uint4 res = *reinterpret_cast<const uint4*>(arow + (k >> 3) * kA2VHalf + (((k ^ R) & 7) << 4));
+        const uint32_t w[4] = {res.x, res.y, res.z, res.w};
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+          const int col = 8 * k + 2 * e;
+          x[col] += __uint_as_float(w[e] << 16);               // (bo2 arrives inside O: folded into Vt by video_update)
+          x[col + 1] += __uint_as_float(w[e] & 0xFFFF0000u);
+          sum0 += x[col];
+          sum1 += x[col + 1];
         }
       }
       tc::tc_fence_before();
       tc::mbar_arrive(&o_empty[grp]);          // O (and the P it was made from) is in registers: the buffer can be refilled
       tc::mbar_arrive(&a0_empty[s]);           // and so is this row's residual
+      if (sp == 2 && lane == 0) trace_mark(a.trace, 6, n);   // worker: O + residual in registers
       const float mu = (sum0 + sum1) * (1.f / BE);
       float q0 = 0.f, q1 = 0.f;
 #pragma unroll
@@ -640,6 +664,7 @@ __global__ void __launch_bounds__(kA2VThreads, 1) a2v_tc_kernel(const __grid_con
         const int slot = ci == 0 ? (t == 0 ? sp : 4) : (t == 1 ? sp - 1 : 3 + sp);
         if (c < a.B) *reinterpret_cast<float4*>(a.poolp + ((int64_t)c * kPoolSlots + slot) * BE + base) = make_float4(x[0], x[1], x[2], x[3]);
       }
+      if (sp == 2 && lane == 0) trace_mark(a.trace, 7, n);   // worker: tile done
     }
   }
   tc::tc_fence_before();
@@ -668,8 +693,8 @@ int launch_v2a_tc(const Bf16Ctx& x) {
     a.trace = trace_buf;
   }
   alignas(64) CUtensorMap tmA0, tmQt;
-  XF_TRY(make_tmap_bf16_2d(&tmA0, x.ws + x.w.a0, (int64_t)c.B * c.Ta, BE, BTAP, 64, BEP));
-  XF_TRY(make_tmap_bf16_2d(&tmQt, x.ws + x.w.qt, (int64_t)c.B * 64, BE, 64, 64, BEP));
+  XF_TRY(make_tmap_bf16_2d(&tmA0, x.ws + x.w.a0, (int64_t)c.B * c.Ta, BE, BTAP, 64, BOP));
+  XF_TRY(make_tmap_bf16_2d(&tmQt, x.ws + x.w.qt, (int64_t)c.B * 64, BE, 64, 64, BOP));
   static bool configured = false;
   if (!configured) {
     XF_CUDA(cudaFuncSetAttribute(v2a_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kV2ASmem));
@@ -707,15 +732,21 @@ int launch_a2v_tc(const Bf16Ctx& x) {
   a.tkv = reinterpret_cast<const float*>(x.ws + x.w.tkv);
   a.pc = reinterpret_cast<const float*>(x.ws + x.w.pc);
   a.cv = reinterpret_cast<const float*>(x.ws + x.w.cv);
-  a.bo2 = P(XP_A2V_OUT_B);
   a.bias_scale = P(XP_BIAS_SCALE);
   a.poolp = reinterpret_cast<float*>(x.ws + x.w.poolp);
   a.B = c.B; a.Ta = c.Ta; a.T = c.T; a.use_prior = c.use_prior;
   a.trace = nullptr;
+  static unsigned long long* trace_buf = nullptr;
+  static const bool tracing = getenv("XATTN_TC_TRACE") != nullptr;
+  if (tracing) {
+    if (trace_buf == nullptr) XF_CUDA(cudaMalloc(&trace_buf, 8 * 64 * 8));
+    XF_CUDA(cudaMemsetAsync(trace_buf, 0, 8 * 64 * 8, x.st));
+    a.trace = trace_buf;
+  }
   alignas(64) CUtensorMap tmA0, tmKt, tmVt;
-  XF_TRY(make_tmap_bf16_2d(&tmA0, x.ws + x.w.a0, (int64_t)c.B * c.Ta, BE, BTAP, 64, BEP));
-  XF_TRY(make_tmap_bf16_2d(&tmKt, x.ws + x.w.kt, (int64_t)c.B * 64, BE, 64, 64, BEP));
-  XF_TRY(make_tmap_bf16_2d(&tmVt, x.ws + x.w.vt, (int64_t)c.B * 64, BE, 64, 64, BEP));
+  XF_TRY(make_tmap_bf16_2d(&tmA0, x.ws + x.w.a0, (int64_t)c.B * c.Ta, BE, BTAP, 64, BOP));
+  XF_TRY(make_tmap_bf16_2d(&tmKt, x.ws + x.w.kt, (int64_t)c.B * 64, BE, 64, 64, BOP));
+  XF_TRY(make_tmap_bf16_2d(&tmVt, x.ws + x.w.vt, (int64_t)c.B * 64, BE, 64, 64, BOP));
   static bool configured = false;
   if (!configured) {
     XF_CUDA(cudaFuncSetAttribute(a2v_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kA2VSmem));
@@ -726,6 +757,20 @@ int launch_a2v_tc(const Bf16Ctx& x) {
   a2v_tc_kernel<<<grid, kA2VThreads, kA2VSmem, x.st>>>(tmA0, tmKt, tmVt, a);
   count_launch();
   XF_LAUNCH_CHECK();
+  if (tracing) {   // debugging aid: timeline of CTA 0 by row tile, microseconds from its first load
+    static unsigned long long h[8 * 64];
+    XF_CUDA(cudaStreamSynchronize(x.st));
+    XF_CUDA(cudaMemcpy(h, trace_buf, sizeof(h), cudaMemcpyDeviceToHost));
+    const char* names[8] = {"load_issue", "s_issue", "o_issue", "w_s_ready", "w_p_done", "w_o_ready", "w_o_in_regs", "w_done"};
+    fprintf(stderr, "a2v_tc trace (us), B=%d\n%-8s", c.B, "tile");
+    for (int e = 0; e < 8; ++e) fprintf(stderr, "%12s", names[e]);
+    fprintf(stderr, "\n");
+    for (int n = 0; n < 24; ++n) {
+      fprintf(stderr, "%-8d", n);
+      for (int e = 0; e < 8; ++e) fprintf(stderr, "%12.2f", h[e * 64 + n] ? (double)(h[e * 64 + n] - h[0]) * 1e-3 : -1.0);
+      fprintf(stderr, "\n");
+    }
+  }
   return XATTN_OK;
 }
 

@@ -2,7 +2,7 @@
 //
 // Data flow per clip (reference src/models/fusion.py:372-411), B clips per launch:
 //   gemm_tc   v0  = video_emb · Wv^T + b                      [T,128]  fp32           :372
-//   gemm_tc   a0  = audio_emb · (W_in·W_seq)^T + b_fold         [Ta,128] bf16, row pitch 136       :378 + :386 folded
+//   gemm_tc   a0  = audio_emb · (W_in·W_seq)^T + b_fold         [Ta,128] bf16                      :378 + :386 folded
 //               + epilogue extras: token scores (w_ak·a0_j, w_aq·a0_j) and per-clip column sums of a0 (-> mean_t a0, :180)
 //   video_pre   Qt_h = (scale·(v0·Wq1^T + bq1))_h · Wk1_h       [64,128] bf16 — so that  Q_h·K_h^T = Qt_h · a0^T   (:394)
 //               + mean_t v0, w_vq·v0_i, w_vk·v0_i  (emotion prior inputs, :171-181)
@@ -23,7 +23,9 @@ namespace xf {
 constexpr int BE = 128;    // d_model the bf16 kernels are specialised for
 constexpr int BH = 4;      // heads
 constexpr int BDH = 32;    // head dim
-constexpr int BEP = 136;   // bf16 row pitch (elements) of every 128-wide smem/global operand: 272 B rows => conflict-free ldmatrix
+constexpr int BEP = 136;   // bf16 row pitch (elements) of the 128-wide WEIGHT tiles kept in smem: 272 B rows => conflict-free ldmatrix
+constexpr int BOP = 128;   // row pitch of the per-clip operands in HBM (a0, Qt, Kt, Vt): dense 256 B rows, so every 128 B
+                           // half-row a TMA box fetches is one aligned line
 constexpr int BTP = 16;    // video tokens padded to one m16 tile
 constexpr int BTAP = 160;  // audio tokens padded to ten m16 tiles
 
@@ -42,15 +44,15 @@ void compute_pack_bf16(const xattn_config& c, PackBf16& p);
 // ---- workspace, byte offsets -----------------------------------------------------------------------------------------
 struct WsBf16 {
   int64_t v0;       // f32  [B,T,E]
-  int64_t a0;       // bf16 [B*Ta, BEP]
-  int64_t qt;       // bf16 [B,64,BEP]
+  int64_t a0;       // bf16 [B*Ta, BOP]
+  int64_t qt;       // bf16 [B,64,BOP]
   int64_t meanv;    // f32  [B,E]
   int64_t tqv, tkv; // f32  [B,16]
   int64_t u;        // bf16 [B,64,E]
   int64_t tok;      // f32  [2,B,160]  w_ak·a0_j | w_aq·a0_j from the a0 GEMM epilogue
   int64_t acol;     // f32  [B,3,E]    column sums of a0 per clip and output tile (gemm_tc.cuh)
   int64_t pc;       // f32  [B,4]
-  int64_t kt, vt;   // bf16 [B,64,BEP]
+  int64_t kt, vt;   // bf16 [B,64,BOP]  (Vt rows carry + bo2/4: every head's probabilities sum to one)
   int64_t cv;       // f32  [B,64]
   int64_t pooled;   // f32  [B,2E]
   int64_t poolp;    // f32  [B,8,E]    per-warp partial sums of LayerNorm-ed audio rows (a2v_tc -> head)
@@ -73,11 +75,9 @@ struct Bf16Ctx {
 };
 int launch_video_pre(const Bf16Ctx& x);
 int launch_prior(const Bf16Ctx& x);
-int launch_v2a_attn(const Bf16Ctx& x);   // mma.sync version (kept for A/B runs: XATTN_ATTN=legacy)
-int launch_v2a_tc(const Bf16Ctx& x);     // tcgen05 version
-int launch_a2v_tc(const Bf16Ctx& x);     // tcgen05 version: leaves pooled_a as partial sums in ws.poolp
+int launch_v2a_tc(const Bf16Ctx& x);
+int launch_a2v_tc(const Bf16Ctx& x);     // leaves pooled_a as per-warp partial sums in ws.poolp (finalised by the head kernel)
 int launch_video_update(const Bf16Ctx& x);
-int launch_a2v_attn(const Bf16Ctx& x);
 int launch_head_pooled(const Bf16Ctx& x, float* logits);
 
 }  // namespace xf

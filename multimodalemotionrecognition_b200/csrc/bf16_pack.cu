@@ -55,8 +55,8 @@ void compute_ws_bf16(const xattn_config& c, WsBf16& w) {
     return o;
   };
   w.v0 = take(B * c.T * E * 4);
-  w.a0 = take(B * c.Ta * BEP * 2);
-  w.qt = take(B * 64 * BEP * 2);
+  w.a0 = take(B * c.Ta * BOP * 2);
+  w.qt = take(B * 64 * BOP * 2);
   w.meanv = take(B * E * 4);
   w.tqv = take(B * 16 * 4);
   w.tkv = take(B * 16 * 4);
@@ -64,8 +64,8 @@ void compute_ws_bf16(const xattn_config& c, WsBf16& w) {
   w.tok = take(B * BTAP * 2 * 4);
   w.acol = take(B * 3 * E * 4);
   w.pc = take(B * 4 * 4);
-  w.kt = take(B * 64 * BEP * 2);
-  w.vt = take(B * 64 * BEP * 2);
+  w.kt = take(B * 64 * BOP * 2);
+  w.vt = take(B * 64 * BOP * 2);
   w.cv = take(B * 64 * 4);
   w.pooled = take(B * 2 * E * 4);
   w.poolp = take(B * 8 * E * 4);

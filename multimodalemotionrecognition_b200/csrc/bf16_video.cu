@@ -115,7 +115,7 @@ __global__ void __launch_bounds__(256, 2) video_pre_kernel(VideoPreArgs a) {
       uint32_t aq[2][4];
       fr::c2a(acc[0], acc[1], aq[0]);
       fr::c2a(acc[2], acc[3], aq[1]);
-      __nv_bfloat16* q0 = a.qt + ((int64_t)c * 64 + h * 16 + g) * BEP + 2 * t;
+      __nv_bfloat16* q0 = a.qt + ((int64_t)c * 64 + h * 16 + g) * BOP + 2 * t;
 #pragma unroll
       for (int nt2 = 0; nt2 < 8; ++nt2) {
         float d0[4] = {0.f, 0.f, 0.f, 0.f}, d1[4] = {0.f, 0.f, 0.f, 0.f};
@@ -127,9 +127,9 @@ __global__ void __launch_bounds__(256, 2) video_pre_kernel(VideoPreArgs a) {
           tc::mma_bf16(d1, aq[kk], b[2], b[3]);
         }
         *reinterpret_cast<uint32_t*>(q0 + nt2 * 16) = tc::pack_bf16(d0[0], d0[1]);
-        *reinterpret_cast<uint32_t*>(q0 + nt2 * 16 + 8 * BEP) = tc::pack_bf16(d0[2], d0[3]);
+        *reinterpret_cast<uint32_t*>(q0 + nt2 * 16 + 8 * BOP) = tc::pack_bf16(d0[2], d0[3]);
         *reinterpret_cast<uint32_t*>(q0 + nt2 * 16 + 8) = tc::pack_bf16(d1[0], d1[1]);
-        *reinterpret_cast<uint32_t*>(q0 + nt2 * 16 + 8 + 8 * BEP) = tc::pack_bf16(d1[2], d1[3]);
+        *reinterpret_cast<uint32_t*>(q0 + nt2 * 16 + 8 + 8 * BOP) = tc::pack_bf16(d1[2], d1[3]);
       }
     }
   }
@@ -139,8 +139,8 @@ struct VideoUpdArgs {
   const __nv_bfloat16* u;    // [B,4,32,8,4] bf16x2: U_h = softmax(S_h) · a0 in mma A-fragment order (see v2a_attn_kernel)
   const float* v0;           // [B,T,E]
   const __nv_bfloat16* W[6]; // Wv1, Wo1, Wk2, Wv2, Wq2, Wo2
-  const float* vec[7];       // bv1, bo1, bk2, bv2, bq2, v_norm.weight, v_norm.bias
-  __nv_bfloat16 *kt, *vt;    // [B,64,BEP]
+  const float* vec[8];       // bv1, bo1, bk2, bv2, bq2, v_norm.weight, v_norm.bias, bo2
+  __nv_bfloat16 *kt, *vt;    // [B,64,BOP]
   float *cv, *pooled;        // [B,64], [B,2E] (first E = pooled_v)
   int B, T;
   float scale;
@@ -191,12 +191,12 @@ __global__ void __launch_bounds__(kUpdWarps * 32, 1) video_update_kernel(VideoUp
 #pragma unroll
   for (int i = 0; i < 6; ++i) fr::copy_g2s(sm + i * kWBytes, a.W[i], kWBytes, tid, blockDim.x);
   float* vecs = reinterpret_cast<float*>(sm + 6 * kWBytes);
-  for (int i = tid; i < 7 * BE; i += blockDim.x) vecs[i] = a.vec[i / BE][i % BE];
+  for (int i = tid; i < 8 * BE; i += blockDim.x) vecs[i] = a.vec[i / BE][i % BE];
   __syncthreads();
   const uint32_t wv1 = tc::smem_u32(sm), wo1 = wv1 + kWBytes, wk2 = wv1 + 2 * kWBytes, wv2 = wv1 + 3 * kWBytes,
                  wq2 = wv1 + 4 * kWBytes, wo2 = wv1 + 5 * kWBytes;
   const float *bv1 = vecs, *bo1 = vecs + BE, *bk2 = vecs + 2 * BE, *bv2 = vecs + 3 * BE, *bq2 = vecs + 4 * BE,
-              *gam = vecs + 5 * BE, *bet = vecs + 6 * BE;
+              *gam = vecs + 5 * BE, *bet = vecs + 6 * BE, *bo2 = vecs + 7 * BE;
   const int T = a.T;
   const float invT = 1.f / (float)T;
   for (int c = blockIdx.x * kUpdWarps + warp; c < a.B; c += gridDim.x * kUpdWarps) {
@@ -294,7 +294,7 @@ __global__ void __launch_bounds__(kUpdWarps * 32, 1) video_update_kernel(VideoUp
         a.cv[(int64_t)c * 64 + h * 16 + g] = c0 * a.scale;
         a.cv[(int64_t)c * 64 + h * 16 + g + 8] = c1 * a.scale;
       }
-      __nv_bfloat16* k0 = a.kt + ((int64_t)c * 64 + h * 16 + g) * BEP + 2 * t;
+      __nv_bfloat16* k0 = a.kt + ((int64_t)c * 64 + h * 16 + g) * BOP + 2 * t;
 #pragma unroll
       for (int nt2 = 0; nt2 < 8; ++nt2) {
         float d0[4] = {0.f, 0.f, 0.f, 0.f}, d1[4] = {0.f, 0.f, 0.f, 0.f};
@@ -306,9 +306,9 @@ __global__ void __launch_bounds__(kUpdWarps * 32, 1) video_update_kernel(VideoUp
           tc::mma_bf16(d1, aq[kk], b[2], b[3]);
         }
         *reinterpret_cast<uint32_t*>(k0 + nt2 * 16) = tc::pack_bf16(d0[0] * a.scale, d0[1] * a.scale);
-        *reinterpret_cast<uint32_t*>(k0 + nt2 * 16 + 8 * BEP) = tc::pack_bf16(d0[2] * a.scale, d0[3] * a.scale);
+        *reinterpret_cast<uint32_t*>(k0 + nt2 * 16 + 8 * BOP) = tc::pack_bf16(d0[2] * a.scale, d0[3] * a.scale);
         *reinterpret_cast<uint32_t*>(k0 + nt2 * 16 + 8) = tc::pack_bf16(d1[0] * a.scale, d1[1] * a.scale);
-        *reinterpret_cast<uint32_t*>(k0 + nt2 * 16 + 8 + 8 * BEP) = tc::pack_bf16(d1[2] * a.scale, d1[3] * a.scale);
+        *reinterpret_cast<uint32_t*>(k0 + nt2 * 16 + 8 + 8 * BOP) = tc::pack_bf16(d1[2] * a.scale, d1[3] * a.scale);
       }
     }
     // ---- values of a2v with out_proj folded in: V2_h = v1·Wv2_h^T + bv2_h ; Vt_h[i, e'] = sum_d V2_h[i,d] Wo2[e', 32h+d] ----
@@ -319,16 +319,18 @@ __global__ void __launch_bounds__(kUpdWarps * 32, 1) video_update_kernel(VideoUp
       uint32_t aq[2][4];
       fr::c2a(v4[0], v4[1], aq[0]);
       fr::c2a(v4[2], v4[3], aq[1]);
-      __nv_bfloat16* v0p = a.vt + ((int64_t)c * 64 + h * 16 + g) * BEP + 2 * t;
+      __nv_bfloat16* v0p = a.vt + ((int64_t)c * 64 + h * 16 + g) * BOP + 2 * t;
 #pragma unroll
       for (int nt = 0; nt < 16; ++nt) {
-        float d[4] = {0.f, 0.f, 0.f, 0.f};
+        // + bo2/4 on every head's rows: the 4 heads' probabilities each sum to one, so P·Vt arrives with out_proj's bias
+        const float bq0 = 0.25f * bo2[nt * 8 + 2 * t], bq1 = 0.25f * bo2[nt * 8 + 2 * t + 1];
+        float d[4] = {bq0, bq1, bq0, bq1};
         uint32_t b[4];
         fr::ldB_nk(wo2, nt, 0, lane, b, 32 * h);
         tc::mma_bf16(d, aq[0], b[0], b[1]);
         tc::mma_bf16(d, aq[1], b[2], b[3]);
         *reinterpret_cast<uint32_t*>(v0p + nt * 8) = tc::pack_bf16(d[0], d[1]);
-        *reinterpret_cast<uint32_t*>(v0p + nt * 8 + 8 * BEP) = tc::pack_bf16(d[2], d[3]);
+        *reinterpret_cast<uint32_t*>(v0p + nt * 8 + 8 * BOP) = tc::pack_bf16(d[2], d[3]);
       }
     }
   }
@@ -385,13 +387,14 @@ int launch_video_update(const Bf16Ctx& x) {
   a.vec[4] = P(XP_A2V_IN_B);            // bq2
   a.vec[5] = P(XP_VN_W);
   a.vec[6] = P(XP_VN_B);
+  a.vec[7] = P(XP_A2V_OUT_B);          // bo2
   a.kt = reinterpret_cast<__nv_bfloat16*>(x.ws + x.w.kt);
   a.vt = reinterpret_cast<__nv_bfloat16*>(x.ws + x.w.vt);
   a.cv = reinterpret_cast<float*>(x.ws + x.w.cv);
   a.pooled = reinterpret_cast<float*>(x.ws + x.w.pooled);
   a.B = c.B; a.T = c.T;
   a.scale = 1.0f / sqrtf((float)BDH);
-  const int smem = 6 * kWBytes + 7 * BE * 4;
+  const int smem = 6 * kWBytes + 8 * BE * 4;
   static bool configured = false;
   if (!configured) {
     XF_CUDA(cudaFuncSetAttribute(video_update_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));

@@ -157,14 +157,12 @@ __global__ void __launch_bounds__(256) head_pooled_kernel(HeadPooledArgs a) {
 
 }  // namespace
 
-static bool attn_legacy();
-
 int launch_head_pooled(const Bf16Ctx& x, float* logits) {
   const xattn_config& c = *x.cfg;
   auto P = [&](int id) { return x.params + x.pl.off[id]; };
   HeadPooledArgs a;
   a.pooled = reinterpret_cast<float*>(x.ws + x.w.pooled);
-  a.poolp = attn_legacy() ? nullptr : reinterpret_cast<const float*>(x.ws + x.w.poolp);
+  a.poolp = reinterpret_cast<const float*>(x.ws + x.w.poolp);
   a.an_w = P(XP_AN_W); a.an_b = P(XP_AN_B);
   a.Ta = c.Ta;
   a.w0b = reinterpret_cast<const __nv_bfloat16*>(x.packed + x.pk.W0b);
@@ -176,16 +174,6 @@ int launch_head_pooled(const Bf16Ctx& x, float* logits) {
   count_launch();
   XF_LAUNCH_CHECK();
   return XATTN_OK;
-}
-
-// XATTN_ATTN=legacy selects the mma.sync attention kernels (A/B timing and bisecting); the default is the tcgen05 pair.
-static bool attn_legacy() {
-  static int v = -1;
-  if (v < 0) {
-    const char* e = getenv("XATTN_ATTN");
-    v = (e != nullptr && strcmp(e, "legacy") == 0) ? 1 : 0;
-  }
-  return v == 1;
 }
 
 // One private non-blocking stream per device for the forked video branch.
@@ -240,7 +228,7 @@ int forward_bf16(const xattn_config& c, const float* params, const void* packed,
   if (rc == XATTN_OK) {
     StageScope t(ST_GEMM_A0, st);
     rc = gemm_tc_bf16(st, xa, x.packed + x.pk.Wfold, reinterpret_cast<const float*>(x.packed + x.pk.bfold), x.ws + x.w.a0, true,
-                      BEP, c.B * c.Ta, BE, c.Da, c.use_prior ? reinterpret_cast<const float*>(x.packed + x.pk.scw) : nullptr,
+                      BOP, c.B * c.Ta, BE, c.Da, c.use_prior ? reinterpret_cast<const float*>(x.packed + x.pk.scw) : nullptr,
                       reinterpret_cast<float*>(x.ws + x.w.tok), reinterpret_cast<float*>(x.ws + x.w.acol), c.Ta);
   }
   if (ev_fork != nullptr) {   // always rejoin, also on an error above, so the caller's stream stays ordered after the side work
@@ -251,9 +239,9 @@ int forward_bf16(const xattn_config& c, const float* params, const void* packed,
   }
   XF_TRY(rc);
   if (c.use_prior) { StageScope t(ST_PRIOR, st); XF_TRY(launch_prior(x)); }
-  { StageScope t(ST_V2A, st); XF_TRY(attn_legacy() ? launch_v2a_attn(x) : launch_v2a_tc(x)); }
+  { StageScope t(ST_V2A, st); XF_TRY(launch_v2a_tc(x)); }
   { StageScope t(ST_VIDEO_UPD, st); XF_TRY(launch_video_update(x)); }
-  { StageScope t(ST_A2V, st); XF_TRY(attn_legacy() ? launch_a2v_attn(x) : launch_a2v_tc(x)); }
+  { StageScope t(ST_A2V, st); XF_TRY(launch_a2v_tc(x)); }
   { StageScope t(ST_HEAD, st); XF_TRY(launch_head_pooled(x, logits)); }
   return XATTN_OK;
 }

@@ -32,11 +32,11 @@ constexpr int kStages = 5;
 constexpr int kAccs = 4;                               // TMEM accumulators (4 x 128 columns = all of TMEM): the MMA warp can run 3 tiles ahead of the epilogue
 constexpr int kStageBytes = (BM * BK + BN * BK) * 2;   // 32 KB
 constexpr int kGemmThreads = 192;
-constexpr int kMaxStagePitch = 160;                    // staged (bulk-store) epilogue supports pitches up to this
+constexpr int kStageBox = BM * 128;                      // one staged box: 128 rows x 64 bf16 (STAGED: N == 128, dense rows)
 constexpr int kBarBytes = 256;
 
 __host__ __device__ constexpr int gemm_smem_bytes(bool staged, int pitch) {
-  return kStages * kStageBytes + (staged ? BM * pitch * 2 : 0) + 3 * BN * 4 + kBarBytes + 1024;
+  return kStages * kStageBytes + (staged ? 2 * kStageBox : 0) + 3 * BN * 4 + kBarBytes + 1024;
 }
 
 struct GemmExtras {
@@ -46,17 +46,18 @@ struct GemmExtras {
   int seg_len;
 };
 
-// OUT_BF16: output dtype.  STAGED: N == 128 and bf16 -> smem image + one bulk store per tile.
+// OUT_BF16: output dtype.  STAGED: bf16, N == 128, dense output rows -> swizzled smem tile + TMA tensor stores.
 template <bool OUT_BF16, bool STAGED, bool EXTRAS>
 __global__ void __launch_bounds__(kGemmThreads, 1) gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA,
                                                                   const __grid_constant__ CUtensorMap tmB,
+                                                                  const __grid_constant__ CUtensorMap tmC,
                                                                   const float* __restrict__ bias, void* __restrict__ out,
                                                                   int64_t out_pitch, int M, int N, int K, GemmExtras ex) {
   static_assert(!EXTRAS || STAGED, "the extras read the staged tile");
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
-  uint8_t* stage_out = smem + kStages * kStageBytes;                                   // [128][pitch] bf16 (STAGED)
-  float* bias_s = reinterpret_cast<float*>(stage_out + (STAGED ? BM * (int)out_pitch * 2 : 0));
+  uint8_t* stage_out = smem + kStages * kStageBytes;                                   // 2 boxes [128 rows][64 bf16], swizzled (STAGED)
+  float* bias_s = reinterpret_cast<float*>(stage_out + (STAGED ? 2 * kStageBox : 0));
   float2* scw_s = reinterpret_cast<float2*>(bias_s + BN);   // [128] (w_ak[n], w_aq[n])
   uint64_t* full = reinterpret_cast<uint64_t*>(bias_s + 3 * BN);
   uint64_t* empty = full + kStages;
@@ -73,6 +74,7 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_tc_kernel(const __grid_c
   if (warp == 0 && lane == 0) {
     tc::tma_prefetch_desc(&tmA);
     tc::tma_prefetch_desc(&tmB);
+    if (STAGED) tc::tma_prefetch_desc(&tmC);
     for (int s = 0; s < kStages; ++s) {
       tc::mbar_init(&full[s], 1);
       tc::mbar_init(&empty[s], 1);
@@ -136,10 +138,6 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_tc_kernel(const __grid_c
     const int row = q * 32 + lane;
     const int et = threadIdx.x - 64;
     const bool leader = et == 0;
-    if (STAGED) {   // pad columns of the staged image are written as zeros
-      __nv_bfloat16* r = reinterpret_cast<__nv_bfloat16*>(stage_out) + (int64_t)row * out_pitch;
-      for (int cidx = BN; cidx < (int)out_pitch; ++cidx) r[cidx] = __float2bfloat16(0.f);
-    }
     if (EXTRAS) scw_s[et] = make_float2(__ldg(ex.sc_w + et), __ldg(ex.sc_w + BN + et));
     uint32_t lt = 0;
     int cur_n0 = -1;
@@ -172,8 +170,7 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_tc_kernel(const __grid_c
           }
         }
         if (OUT_BF16) {
-          __nv_bfloat16* o = STAGED ? reinterpret_cast<__nv_bfloat16*>(stage_out) + (int64_t)row * out_pitch + c
-                                    : reinterpret_cast<__nv_bfloat16*>(out) + (int64_t)m * out_pitch + n0 + c;
+          __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(out) + (int64_t)m * out_pitch + n0 + c;
           if (STAGED || m < M) {
 #pragma unroll
             for (int v = 0; v < 4; ++v) {
@@ -182,7 +179,12 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_tc_kernel(const __grid_c
               pk.y = tc::pack_bf16(__uint_as_float(r[8 * v + 2]) + bias_s[c + 8 * v + 2], __uint_as_float(r[8 * v + 3]) + bias_s[c + 8 * v + 3]);
               pk.z = tc::pack_bf16(__uint_as_float(r[8 * v + 4]) + bias_s[c + 8 * v + 4], __uint_as_float(r[8 * v + 5]) + bias_s[c + 8 * v + 5]);
               pk.w = tc::pack_bf16(__uint_as_float(r[8 * v + 6]) + bias_s[c + 8 * v + 6], __uint_as_float(r[8 * v + 7]) + bias_s[c + 8 * v + 7]);
-              *reinterpret_cast<uint4*>(o + 8 * v) = pk;
+              if (STAGED) {   // 16-byte chunk q of the row -> box q / 8, slot (q % 8) ^ (row % 8)
+                const int q8 = (c >> 3) + v;
+                *reinterpret_cast<uint4*>(stage_out + (q8 >> 3) * kStageBox + row * 128 + (((q8 ^ row) & 7) << 4)) = pk;
+              } else {
+                *reinterpret_cast<uint4*>(o + 8 * v) = pk;
+              }
             }
           }
         } else if (m < M) {
@@ -211,22 +213,28 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_tc_kernel(const __grid_c
         tc::fence_proxy_async();          // generic-proxy smem writes -> visible to the bulk (async proxy) store
         tc::named_bar_sync(1, 128);
         const int rows = min(BM, M - m0);
-        if (leader)
-          tc::bulk_store_1d(reinterpret_cast<__nv_bfloat16*>(out) + (int64_t)m0 * out_pitch, stage_out,
-                            (uint32_t)(rows * out_pitch * 2));
+        if (leader) {   // rows past M are clipped by the tensor map
+          tc::tma_store_2d(&tmC, stage_out, 0, m0);
+          tc::tma_store_2d(&tmC, stage_out + kStageBox, 64, m0);
+          tc::bulk_commit_group();
+        }
         if (EXTRAS) {   // thread `et` owns column et: sum it over the rows of each clip present in this tile
           const int L = ex.seg_len;
-          const __nv_bfloat16* colp = reinterpret_cast<const __nv_bfloat16*>(stage_out) + et;
+          const uint8_t* colp = stage_out + (et >> 6) * kStageBox + (et & 7) * 2;   // + rr*128 + swizzled chunk
+          const int chunk = (et & 63) >> 3;
+          auto at = [&](int rr) {
+            return __bfloat162float(*reinterpret_cast<const __nv_bfloat16*>(colp + rr * 128 + (((chunk ^ rr) & 7) << 4)));
+          };
           const int clip_last = (m0 + rows - 1) / L;
           for (int clip = m0 / L; clip <= clip_last; ++clip) {
             const int r0 = max(clip * L, m0) - m0, r1 = min((clip + 1) * L, m0 + rows) - m0;
             float s0 = 0.f, s1 = 0.f;
             int rr = r0;
             for (; rr + 1 < r1; rr += 2) {
-              s0 += __bfloat162float(colp[(int64_t)rr * out_pitch]);
-              s1 += __bfloat162float(colp[(int64_t)(rr + 1) * out_pitch]);
+              s0 += at(rr);
+              s1 += at(rr + 1);
             }
-            if (rr < r1) s0 += __bfloat162float(colp[(int64_t)rr * out_pitch]);
+            if (rr < r1) s0 += at(rr);
             const int slot = m0 / BM - (clip * L) / BM;
             ex.colsum[((int64_t)clip * kColsumSlots + slot) * BN + et] = s0 + s1;
           }
@@ -256,7 +264,8 @@ EncodeTiledFn encode_tiled_fn() {
 }
 
 template <bool OUT_BF16, bool STAGED, bool EXTRAS>
-int launch_gemm_tc(cudaStream_t st, const CUtensorMap& tmA, const CUtensorMap& tmB, const float* bias, void* out, int64_t pitch,
+int launch_gemm_tc(cudaStream_t st, const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmC, const float* bias,
+                   void* out, int64_t pitch,
                    int M, int N, int K, const GemmExtras& ex) {
   const int smem = gemm_smem_bytes(STAGED, (int)pitch);
   static int configured = 0;
@@ -266,7 +275,7 @@ int launch_gemm_tc(cudaStream_t st, const CUtensorMap& tmA, const CUtensorMap& t
   }
   const int tiles = ((M + BM - 1) / BM) * (N / BN);
   const int grid = tiles < num_sms() ? tiles : num_sms();
-  gemm_tc_kernel<OUT_BF16, STAGED, EXTRAS><<<grid, kGemmThreads, smem, st>>>(tmA, tmB, bias, out, pitch, M, N, K, ex);
+  gemm_tc_kernel<OUT_BF16, STAGED, EXTRAS><<<grid, kGemmThreads, smem, st>>>(tmA, tmB, tmC, bias, out, pitch, M, N, K, ex);
   count_launch();
   XF_LAUNCH_CHECK();
   return XATTN_OK;
@@ -294,22 +303,24 @@ int gemm_tc_bf16(cudaStream_t st, const void* X, const void* W, const float* bia
                  int M, int N, int K, const float* sc_w, float* tok, float* colsum, int seg_len) {
   if (M <= 0) return XATTN_OK;
   const bool extras = sc_w != nullptr;
-  if (extras && !(out_bf16 && N == BN && out_pitch <= kMaxStagePitch && seg_len > 0 && M % seg_len == 0 &&
+  const bool staged = out_bf16 && N == BN && out_pitch == BN;
+  if (extras && !(staged && seg_len > 0 && M % seg_len == 0 &&
                   (seg_len + BM - 2) / BM + 1 <= kColsumSlots && seg_len <= kTokPitch))
-    XF_FAIL(XATTN_ERR_SHAPE, "projection GEMM extras need bf16 output, N == 128 and rows in clips of <= 256 tokens");
+    XF_FAIL(XATTN_ERR_SHAPE, "projection GEMM extras need dense bf16 output with N == 128 and rows in clips of <= 160 tokens");
   GemmExtras ex{sc_w, tok, colsum, seg_len};
   if (N % BN != 0 || K % BK != 0)
     XF_FAIL(XATTN_ERR_SHAPE, "tcgen05 projection GEMM needs N %% 128 == 0 and K %% 64 == 0 (N=%d K=%d)", N, K);
   if (out_pitch < N || (out_bf16 && out_pitch % 8 != 0) || (!out_bf16 && out_pitch % 4 != 0))
     XF_FAIL(XATTN_ERR_SHAPE, "output pitch %lld must be >= N and keep rows 16-byte aligned", (long long)out_pitch);
-  alignas(64) CUtensorMap tmA, tmB;
+  alignas(64) CUtensorMap tmA, tmB, tmC;
   XF_TRY(make_tmap_bf16_2d(&tmA, X, M, K, BM, BK));
   XF_TRY(make_tmap_bf16_2d(&tmB, W, N, K, BN, BK));
-  if (extras) return launch_gemm_tc<true, true, true>(st, tmA, tmB, bias, out, out_pitch, M, N, K, ex);
-  if (out_bf16 && N == BN && out_pitch <= kMaxStagePitch)
-    return launch_gemm_tc<true, true, false>(st, tmA, tmB, bias, out, out_pitch, M, N, K, ex);
-  if (out_bf16) return launch_gemm_tc<true, false, false>(st, tmA, tmB, bias, out, out_pitch, M, N, K, ex);
-  return launch_gemm_tc<false, false, false>(st, tmA, tmB, bias, out, out_pitch, M, N, K, ex);
+  if (staged) XF_TRY(make_tmap_bf16_2d(&tmC, out, M, BN, BM, 64));
+  else tmC = tmA;
+  if (extras) return launch_gemm_tc<true, true, true>(st, tmA, tmB, tmC, bias, out, out_pitch, M, N, K, ex);
+  if (staged) return launch_gemm_tc<true, true, false>(st, tmA, tmB, tmC, bias, out, out_pitch, M, N, K, ex);
+  if (out_bf16) return launch_gemm_tc<true, false, false>(st, tmA, tmB, tmC, bias, out, out_pitch, M, N, K, ex);
+  return launch_gemm_tc<false, false, false>(st, tmA, tmB, tmC, bias, out, out_pitch, M, N, K, ex);
 }
 
 }  // namespace xf

@@ -5,4 +5,4 @@ d=json.loads(open('gpurun_out/r8_bench.json').read().strip().splitlines()[-1])
 print(d['value'], d['ms_per_step'], d['roofline']['whole_step']['bracketed_pass_ms_per_step'])
 print([(s['kernel'], round(s['us'],1)) for s in d['roofline']['stages']])
 PY
-XATTN_TC_TRACE=1 timeout -k 5 120 python scripts/prof_fwd.py 4096 1 2>&1 | tail -18
+bash scripts/gpu_trace.sh

@@ -55,7 +55,7 @@ def _al256(n):
 
 def _ws_views(ws, B, T, Ta):
     """Mirror of compute_ws_bf16 (csrc/bf16_pack.cu): typed views of the workspace intermediates."""
-    E, EP = 128, 136
+    E, EP = 128, 128
     spec = [("v0", torch.float32, (B, T, E)), ("a0", torch.bfloat16, (B * Ta, EP)), ("qt", torch.bfloat16, (B, 64, EP)),
             ("meanv", torch.float32, (B, E)), ("tqv", torch.float32, (B, 16)), ("tkv", torch.float32, (B, 16)),
             ("u", torch.bfloat16, (B, 64, E)), ("tok", torch.float32, (2, B, 160)), ("acol", torch.float32, (B, 3, E)),
