@@ -50,7 +50,7 @@ struct WsBf16 {
   int64_t tqv, tkv; // f32  [B,16]
   int64_t u;        // bf16 [B,64,E]
   int64_t tok;      // f32  [2,B,160]  w_ak·a0_j | w_aq·a0_j from the a0 GEMM epilogue
-  int64_t acol;     // f32  [B,3,E]    column sums of a0 per clip and output tile (gemm_tc.cuh)
+  int64_t acol;     // f32  [B,6,E]    column sums of a0 per clip and 32-row output group (gemm_tc.cuh)
   int64_t pc;       // f32  [B,4]
   int64_t kt, vt;   // bf16 [B,64,BOP]  (Vt rows carry + bo2/4: every head's probabilities sum to one)
   int64_t cv;       // f32  [B,64]

@@ -5,6 +5,7 @@
 //    a 136-element row pitch; * head layer 0 transposed for coalesced reads.
 #include "bf16_layout.cuh"
 #include "gemm_simt.cuh"
+#include "gemm_tc.cuh"
 #include "kernels_bf16.cuh"
 
 namespace xf {
@@ -62,7 +63,7 @@ void compute_ws_bf16(const xattn_config& c, WsBf16& w) {
   w.tkv = take(B * 16 * 4);
   w.u = take(B * 64 * E * 2);
   w.tok = take(B * BTAP * 2 * 4);
-  w.acol = take(B * 3 * E * 4);
+  w.acol = take(B * kColsumSlots * E * 4);
   w.pc = take(B * 4 * 4);
   w.kt = take(B * 64 * BOP * 2);
   w.vt = take(B * 64 * BOP * 2);

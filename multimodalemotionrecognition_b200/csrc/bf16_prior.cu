@@ -27,7 +27,8 @@ struct PriorArgs {
   int B, Ta, P, Hd;
 };
 
-__global__ void __launch_bounds__(128) prior_kernel(PriorArgs a) {
+constexpr int kPriorThreads = 256;
+__global__ void __launch_bounds__(kPriorThreads) prior_kernel(PriorArgs a) {
   __shared__ __align__(16) __nv_bfloat16 xhi[kPriorClips][kXP];
   __shared__ __align__(16) __nv_bfloat16 xlo[kPriorClips][kXP];
   __shared__ float hid[kPriorClips][128 + 1];
@@ -35,29 +36,40 @@ __global__ void __launch_bounds__(128) prior_kernel(PriorArgs a) {
   const int tid = threadIdx.x, c0 = blockIdx.x * kPriorClips;
   const int nc = min(kPriorClips, a.B - c0);
   const float invTa = 1.f / (float)a.Ta;
-  for (int i = tid; i < kPriorClips * 2 * BE; i += blockDim.x) {
-    const int cc = i / (2 * BE), k = i % (2 * BE);
-    float x = 0.f;
+  for (int i = tid; i < kPriorClips * 2 * BE / 4; i += kPriorThreads) {   // one float4 of the pooled input per step
+    const int cc = i / (2 * BE / 4), k = (i % (2 * BE / 4)) * 4;
+    float4 x = make_float4(0.f, 0.f, 0.f, 0.f);
     if (cc < nc) {
       const int64_t c = c0 + cc;
       if (k < BE) {
-        x = a.meanv[c * BE + k];
-      } else {   // add the partial sums of the output tiles the clip overlaps, first tile first
+        x = *reinterpret_cast<const float4*>(a.meanv + c * BE + k);
+      } else {   // add the partial sums of the 32-row output groups the clip overlaps, first group first
         const int64_t r0 = c * a.Ta;
-        const int nslot = (int)((r0 + a.Ta - 1) / 128 - r0 / 128) + 1;
-        for (int s = 0; s < nslot; ++s) x += a.acol[(c * kColsumSlots + s) * BE + (k - BE)];
-        x *= invTa;
+        const int nslot = (int)((r0 + a.Ta - 1) / 32 - r0 / 32) + 1;
+        float4 v[kColsumSlots];
+#pragma unroll
+        for (int s = 0; s < kColsumSlots; ++s)
+          v[s] = s < nslot ? *reinterpret_cast<const float4*>(a.acol + (c * kColsumSlots + s) * BE + (k - BE)) : make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+        for (int s = 0; s < kColsumSlots; ++s) {
+          x.x += v[s].x; x.y += v[s].y; x.z += v[s].z; x.w += v[s].w;
+        }
+        x.x *= invTa; x.y *= invTa; x.z *= invTa; x.w *= invTa;
       }
     }
-    const __nv_bfloat16 h = __float2bfloat16(x);
-    xhi[cc][k] = h;
-    xlo[cc][k] = __float2bfloat16(x - __bfloat162float(h));
+    const float xs[4] = {x.x, x.y, x.z, x.w};
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+      const __nv_bfloat16 h = __float2bfloat16(xs[e]);
+      xhi[cc][k + e] = h;
+      xlo[cc][k + e] = __float2bfloat16(xs[e] - __bfloat162float(h));
+    }
   }
   __syncthreads();
   {
     const int warp = tid >> 5, lane = tid & 31, g = lane >> 2, t = lane & 3;
     const int ntiles = (a.Hd + 7) / 8;
-    for (int nt = warp; nt < ntiles; nt += 4) {
+    for (int nt = warp; nt < ntiles; nt += kPriorThreads / 32) {
       const int n = nt * 8 + g;
       const __nv_bfloat16* wrow = a.pw0b + (int64_t)min(n, a.Hd - 1) * (2 * BE) + 2 * t;
       uint32_t b[2 * BE / 16][2];
@@ -93,12 +105,19 @@ __global__ void __launch_bounds__(128) prior_kernel(PriorArgs a) {
     }
   }
   __syncthreads();
-  for (int o = tid; o < kPriorClips * a.P; o += blockDim.x) {
+  for (int o = tid; o < kPriorClips * a.P; o += kPriorThreads) {
     const int cc = o / a.P, p = o % a.P;
     const float* w = a.pw3 + (int64_t)p * a.Hd;
-    float s = a.pb3[p];
-    for (int k = 0; k < a.Hd; ++k) s = fmaf(__ldg(w + k), hid[cc][k], s);
-    prior[cc][p] = s;
+    float s0 = a.pb3[p], s1 = 0.f, s2 = 0.f, s3 = 0.f;
+    int k = 0;
+    for (; k + 3 < a.Hd; k += 4) {
+      s0 = fmaf(__ldg(w + k), hid[cc][k], s0);
+      s1 = fmaf(__ldg(w + k + 1), hid[cc][k + 1], s1);
+      s2 = fmaf(__ldg(w + k + 2), hid[cc][k + 2], s2);
+      s3 = fmaf(__ldg(w + k + 3), hid[cc][k + 3], s3);
+    }
+    for (; k < a.Hd; ++k) s0 = fmaf(__ldg(w + k), hid[cc][k], s0);
+    prior[cc][p] = (s0 + s1) + (s2 + s3);
   }
   __syncthreads();
   if (tid < kPriorClips * 4) {
@@ -126,7 +145,7 @@ int launch_prior(const Bf16Ctx& x) {
   a.wh[2] = P(XP_AQ_W); a.bh[2] = P(XP_AQ_B); a.wh[3] = P(XP_VK_W); a.bh[3] = P(XP_VK_B);
   a.pc = reinterpret_cast<float*>(x.ws + x.w.pc);
   a.B = c.B; a.Ta = c.Ta; a.P = c.prior_dim; a.Hd = c.prior_hidden;
-  prior_kernel<<<(c.B + kPriorClips - 1) / kPriorClips, 128, 0, x.st>>>(a);
+  prior_kernel<<<(c.B + kPriorClips - 1) / kPriorClips, kPriorThreads, 0, x.st>>>(a);
   count_launch();
   XF_LAUNCH_CHECK();
   return XATTN_OK;

@@ -32,7 +32,8 @@ struct HeadPooledArgs {
 // that the eight rows a fragment load touches fall in different banks.
 constexpr int kXP = 2 * BE + 8;    // bf16 pitch of the split activations (528 B: row g -> bank 4g)
 constexpr int kHP = 256 + 4;       // fp32 pitch of hid / final-layer weights
-__global__ void __launch_bounds__(256) head_pooled_kernel(HeadPooledArgs a) {
+constexpr int kHeadThreads = 512;   // 16 warps: the n-tiles of layer 0 spread thin, the kernel is one latency chain per CTA
+__global__ void __launch_bounds__(kHeadThreads) head_pooled_kernel(HeadPooledArgs a) {
   // xhi/xlo (layer-0 operands) and wl (final linear, [C][K]) are live in different phases and share one region.
   __shared__ __align__(16) unsigned char region[2 * kHeadClips * kXP * 2 > 16 * kHP * 4 ? 2 * kHeadClips * kXP * 2 : 16 * kHP * 4];
   __shared__ __align__(16) float hid[kHeadClips][kHP];
@@ -53,10 +54,13 @@ __global__ void __launch_bounds__(256) head_pooled_kernel(HeadPooledArgs a) {
       if (a.poolp != nullptr && k >= BE) {   // add the clip's partials in slot order (even clips own 5 slots, odd clips 7)
         const int ns = (c & 1) ? 7 : 5;
         const float* pp = a.poolp + c * 8 * BE + (k - BE);
-        for (int s2 = 0; s2 < ns; ++s2) {
-          const float2 v = *reinterpret_cast<const float2*>(pp + s2 * BE);
-          x.x += v.x;
-          x.y += v.y;
+        float2 v[7];
+#pragma unroll
+        for (int s2 = 0; s2 < 7; ++s2) v[s2] = s2 < ns ? *reinterpret_cast<const float2*>(pp + s2 * BE) : make_float2(0.f, 0.f);
+#pragma unroll
+        for (int s2 = 0; s2 < 7; ++s2) {   // fixed order
+          x.x += v[s2].x;
+          x.y += v[s2].y;
         }
         const float inv = 1.f / (float)a.Ta;
         x.x = a.an_w[k - BE] * (x.x * inv) + a.an_b[k - BE];
@@ -70,16 +74,16 @@ __global__ void __launch_bounds__(256) head_pooled_kernel(HeadPooledArgs a) {
     *reinterpret_cast<__nv_bfloat162*>(&xhi[cc][k]) = h;
     *reinterpret_cast<__nv_bfloat162*>(&xlo[cc][k]) = __floats2bfloat162_rn(x.x - __low2float(h), x.y - __high2float(h));
   }
-  float4 wpre[4];   // final-layer weights, fetched now and parked in smem once layer 0 is done with the region (C*K <= 4096)
+  float4 wpre[2];   // final-layer weights, fetched now and parked in smem once layer 0 is done with the region (C*K <= 4096)
 #pragma unroll
-  for (int r = 0; r < 4; ++r) {
-    const int i = tid + r * 256;
+  for (int r = 0; r < 2; ++r) {
+    const int i = tid + r * kHeadThreads;
     wpre[r] = i < a.C * K / 4 ? __ldg(reinterpret_cast<const float4*>(wfin) + i) : make_float4(0.f, 0.f, 0.f, 0.f);
   }
   __syncthreads();
   {
     const int warp = tid >> 5, lane = tid & 31, g = lane >> 2, t = lane & 3;
-    const int ntw = a.HW / 64;   // n-tiles per warp (8 warps)
+    const int ntot = a.HW / 8;   // n-tiles of layer 0, dealt round-robin to the 16 warps
     // The weight fragments of a tile are fetched with volatile loads, all 32 in flight at once and one tile ahead of the
     // MMAs that use them; left to the compiler they trail their use by two steps and every step waits out an L2 round trip.
     auto fetch = [&](uint32_t (&b)[2 * BE / 16][2], int nt) {
@@ -91,10 +95,9 @@ __global__ void __launch_bounds__(256) head_pooled_kernel(HeadPooledArgs a) {
       }
     };
     uint32_t b[2 * BE / 16][2], bn[2 * BE / 16][2];
-    fetch(b, warp * ntw);
-    for (int n = 0; n < ntw; ++n) {
-      const int nt = warp * ntw + n;
-      if (n + 1 < ntw) fetch(bn, nt + 1);
+    if (warp < ntot) fetch(b, warp);
+    for (int nt = warp; nt < ntot; nt += kHeadThreads / 32) {
+      if (nt + kHeadThreads / 32 < ntot) fetch(bn, nt + kHeadThreads / 32);
       float d[4] = {0.f, 0.f, 0.f, 0.f}, e[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
       for (int ks = 0; ks < 2 * BE / 16; ++ks) {
@@ -113,7 +116,7 @@ __global__ void __launch_bounds__(256) head_pooled_kernel(HeadPooledArgs a) {
       hid[g][col + 1] = fmaxf(d[1] + e[1] + c1b, 0.f);
       hid[g + 8][col] = fmaxf(d[2] + e[2] + c0b, 0.f);
       hid[g + 8][col + 1] = fmaxf(d[3] + e[3] + c1b, 0.f);
-      if (n + 1 < ntw) {
+      if (nt + kHeadThreads / 32 < ntot) {
 #pragma unroll
         for (int ks = 0; ks < 2 * BE / 16; ++ks) { b[ks][0] = bn[ks][0]; b[ks][1] = bn[ks][1]; }
       }
@@ -121,8 +124,8 @@ __global__ void __launch_bounds__(256) head_pooled_kernel(HeadPooledArgs a) {
   }
   __syncthreads();
 #pragma unroll
-  for (int r = 0; r < 4; ++r) {
-    const int i = tid + r * 256;
+  for (int r = 0; r < 2; ++r) {
+    const int i = tid + r * kHeadThreads;
     if (i < a.C * K / 4) *reinterpret_cast<float4*>(&wl[(i * 4) / K][(i * 4) % K]) = wpre[r];
   }
   if (a.gated) {
@@ -170,7 +173,7 @@ int launch_head_pooled(const Bf16Ctx& x, float* logits) {
   a.logits = logits;
   a.B = c.B; a.C = c.C; a.gated = c.head_kind == XATTN_HEAD_GATED;
   a.HW = a.gated ? c.E : c.common_dim;
-  head_pooled_kernel<<<(c.B + kHeadClips - 1) / kHeadClips, 256, 0, x.st>>>(a);
+  head_pooled_kernel<<<(c.B + kHeadClips - 1) / kHeadClips, kHeadThreads, 0, x.st>>>(a);
   count_launch();
   XF_LAUNCH_CHECK();
   return XATTN_OK;

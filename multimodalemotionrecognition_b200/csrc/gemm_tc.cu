@@ -14,8 +14,8 @@
 //               while the MMA warp already fills the other accumulator with the next tile.
 // EXTRAS (the a0 projection): the epilogue also emits, from data it already holds,
 //   tok[0][m], tok[1][m] = w_ak·y_m, w_aq·y_m   the token parts of a_key_bias / a_query_bias (fusion.py:173-174), from the fp32 row
-//   colsum[clip][slot][n]           column sums of the tile's rows that belong to `clip` (rows are clips of seg_len tokens);
-//                                   slot = tile - first tile of the clip, so a reader adds <= 3 partials in a fixed order
+//   colsum[clip][slot][n]           column sums of a warp's 32 output rows that belong to `clip` (rows are clips of seg_len
+//                                   tokens); slot = 32-row group - first group of the clip: a reader adds <= 6 partials in order
 //                                   (the temporal mean that feeds prior_net, fusion.py:180)
 #include <cuda.h>
 
@@ -50,7 +50,6 @@ struct GemmExtras {
 template <bool OUT_BF16, bool STAGED, bool EXTRAS>
 __global__ void __launch_bounds__(kGemmThreads, 1) gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA,
                                                                   const __grid_constant__ CUtensorMap tmB,
-                                                                  const __grid_constant__ CUtensorMap tmC,
                                                                   const float* __restrict__ bias, void* __restrict__ out,
                                                                   int64_t out_pitch, int M, int N, int K, GemmExtras ex) {
   static_assert(!EXTRAS || STAGED, "the extras read the staged tile");
@@ -74,7 +73,6 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_tc_kernel(const __grid_c
   if (warp == 0 && lane == 0) {
     tc::tma_prefetch_desc(&tmA);
     tc::tma_prefetch_desc(&tmB);
-    if (STAGED) tc::tma_prefetch_desc(&tmC);
     for (int s = 0; s < kStages; ++s) {
       tc::mbar_init(&full[s], 1);
       tc::mbar_init(&empty[s], 1);
@@ -137,7 +135,6 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_tc_kernel(const __grid_c
     const int q = warp & 3;
     const int row = q * 32 + lane;
     const int et = threadIdx.x - 64;
-    const bool leader = et == 0;
     if (EXTRAS) scw_s[et] = make_float2(__ldg(ex.sc_w + et), __ldg(ex.sc_w + BN + et));
     uint32_t lt = 0;
     int cur_n0 = -1;
@@ -148,9 +145,9 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_tc_kernel(const __grid_c
         tc::named_bar_sync(2, 128);
         bias_s[et] = __ldg(bias + n0 + et);
         cur_n0 = n0;
+        tc::named_bar_sync(2, 128);   // (also publishes scw_s on the first pass)
       }
-      if (STAGED && leader) tc::bulk_store_wait_read();   // previous tile's image has left smem
-      tc::named_bar_sync(1, 128);
+      if (STAGED) __syncwarp();   // this warp's copy-out of the previous tile has finished reading its staged rows
       tc::mbar_wait(&acc_full[ab], aph);
       tc::tc_fence_after();
       const int m = m0 + row;
@@ -210,38 +207,37 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_tc_kernel(const __grid_c
         ex.tok[((int64_t)(M / ex.seg_len) + clip) * kTokPitch + j] = sc1;
       }
       if (STAGED) {
-        tc::fence_proxy_async();          // generic-proxy smem writes -> visible to the bulk (async proxy) store
-        tc::named_bar_sync(1, 128);
-        const int rows = min(BM, M - m0);
-        if (leader) {   // rows past M are clipped by the tensor map
-          tc::tma_store_2d(&tmC, stage_out, 0, m0);
-          tc::tma_store_2d(&tmC, stage_out + kStageBox, 64, m0);
-          tc::bulk_commit_group();
+        // Each warp owns 32 rows of the tile end to end: no CTA-level barrier, no asynchronous store to wait for.  The rows
+        // were staged swizzled (conflict-free 16-byte writes); they leave in global order, 512 contiguous bytes per access.
+        __syncwarp();
+        const int wrow0 = q * 32, mrow0 = m0 + wrow0;
+        uint4* gout = reinterpret_cast<uint4*>(reinterpret_cast<__nv_bfloat16*>(out) + (int64_t)mrow0 * BN);
+#pragma unroll 4
+        for (int i = 0; i < 16; ++i) {
+          const int lin = i * 32 + lane, rr = lin >> 4, q8 = lin & 15;   // row in the warp's block, 16-byte chunk of the row
+          if (mrow0 + rr < M)
+            gout[lin] = *reinterpret_cast<const uint4*>(stage_out + (q8 >> 3) * kStageBox + (wrow0 + rr) * 128 + (((q8 ^ rr) & 7) << 4));
         }
-        if (EXTRAS) {   // thread `et` owns column et: sum it over the rows of each clip present in this tile
+        if (EXTRAS) {   // lane owns columns 4*lane .. 4*lane+3: sum them over the warp's rows of each clip present
           const int L = ex.seg_len;
-          const uint8_t* colp = stage_out + (et >> 6) * kStageBox + (et & 7) * 2;   // + rr*128 + swizzled chunk
-          const int chunk = (et & 63) >> 3;
-          auto at = [&](int rr) {
-            return __bfloat162float(*reinterpret_cast<const __nv_bfloat16*>(colp + rr * 128 + (((chunk ^ rr) & 7) << 4)));
-          };
-          const int clip_last = (m0 + rows - 1) / L;
-          for (int clip = m0 / L; clip <= clip_last; ++clip) {
-            const int r0 = max(clip * L, m0) - m0, r1 = min((clip + 1) * L, m0 + rows) - m0;
-            float s0 = 0.f, s1 = 0.f;
-            int rr = r0;
-            for (; rr + 1 < r1; rr += 2) {
-              s0 += at(rr);
-              s1 += at(rr + 1);
+          const int cb = 4 * lane, chunk = (cb & 63) >> 3;
+          const uint8_t* colp = stage_out + (cb >> 6) * kStageBox + wrow0 * 128 + (cb & 7) * 2;
+          const int nrows = min(32, M - mrow0);
+          const int clip_last = (mrow0 + nrows - 1) / L;
+          for (int clip = mrow0 / L; clip <= clip_last; ++clip) {
+            const int r0 = max(clip * L, mrow0) - mrow0, r1 = min((clip + 1) * L, mrow0 + nrows) - mrow0;
+            float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
+            for (int rr = r0; rr < r1; ++rr) {
+              const uint2 v = *reinterpret_cast<const uint2*>(colp + rr * 128 + (((chunk ^ rr) & 7) << 4));
+              a0 += __uint_as_float(v.x << 16); a1 += __uint_as_float(v.x & 0xFFFF0000u);
+              a2 += __uint_as_float(v.y << 16); a3 += __uint_as_float(v.y & 0xFFFF0000u);
             }
-            if (rr < r1) s0 += at(rr);
-            const int slot = m0 / BM - (clip * L) / BM;
-            ex.colsum[((int64_t)clip * kColsumSlots + slot) * BN + et] = s0 + s1;
+            const int slot = mrow0 / 32 - (clip * L) / 32;   // 32-row group of the output relative to the clip's first group
+            *reinterpret_cast<float4*>(ex.colsum + ((int64_t)clip * kColsumSlots + slot) * BN + cb) = make_float4(a0, a1, a2, a3);
           }
         }
       }
     }
-    if (STAGED && leader) tc::bulk_store_wait_all();
   }
   tc::tc_fence_before();
   __syncthreads();
@@ -264,8 +260,7 @@ EncodeTiledFn encode_tiled_fn() {
 }
 
 template <bool OUT_BF16, bool STAGED, bool EXTRAS>
-int launch_gemm_tc(cudaStream_t st, const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmC, const float* bias,
-                   void* out, int64_t pitch,
+int launch_gemm_tc(cudaStream_t st, const CUtensorMap& tmA, const CUtensorMap& tmB, const float* bias, void* out, int64_t pitch,
                    int M, int N, int K, const GemmExtras& ex) {
   const int smem = gemm_smem_bytes(STAGED, (int)pitch);
   static int configured = 0;
@@ -275,7 +270,7 @@ int launch_gemm_tc(cudaStream_t st, const CUtensorMap& tmA, const CUtensorMap& t
   }
   const int tiles = ((M + BM - 1) / BM) * (N / BN);
   const int grid = tiles < num_sms() ? tiles : num_sms();
-  gemm_tc_kernel<OUT_BF16, STAGED, EXTRAS><<<grid, kGemmThreads, smem, st>>>(tmA, tmB, tmC, bias, out, pitch, M, N, K, ex);
+  gemm_tc_kernel<OUT_BF16, STAGED, EXTRAS><<<grid, kGemmThreads, smem, st>>>(tmA, tmB, bias, out, pitch, M, N, K, ex);
   count_launch();
   XF_LAUNCH_CHECK();
   return XATTN_OK;
@@ -305,22 +300,20 @@ int gemm_tc_bf16(cudaStream_t st, const void* X, const void* W, const float* bia
   const bool extras = sc_w != nullptr;
   const bool staged = out_bf16 && N == BN && out_pitch == BN;
   if (extras && !(staged && seg_len > 0 && M % seg_len == 0 &&
-                  (seg_len + BM - 2) / BM + 1 <= kColsumSlots && seg_len <= kTokPitch))
+                  (seg_len + 30) / 32 + 1 <= kColsumSlots && seg_len <= kTokPitch))
     XF_FAIL(XATTN_ERR_SHAPE, "projection GEMM extras need dense bf16 output with N == 128 and rows in clips of <= 160 tokens");
   GemmExtras ex{sc_w, tok, colsum, seg_len};
   if (N % BN != 0 || K % BK != 0)
     XF_FAIL(XATTN_ERR_SHAPE, "tcgen05 projection GEMM needs N %% 128 == 0 and K %% 64 == 0 (N=%d K=%d)", N, K);
   if (out_pitch < N || (out_bf16 && out_pitch % 8 != 0) || (!out_bf16 && out_pitch % 4 != 0))
     XF_FAIL(XATTN_ERR_SHAPE, "output pitch %lld must be >= N and keep rows 16-byte aligned", (long long)out_pitch);
-  alignas(64) CUtensorMap tmA, tmB, tmC;
+  alignas(64) CUtensorMap tmA, tmB;
   XF_TRY(make_tmap_bf16_2d(&tmA, X, M, K, BM, BK));
   XF_TRY(make_tmap_bf16_2d(&tmB, W, N, K, BN, BK));
-  if (staged) XF_TRY(make_tmap_bf16_2d(&tmC, out, M, BN, BM, 64));
-  else tmC = tmA;
-  if (extras) return launch_gemm_tc<true, true, true>(st, tmA, tmB, tmC, bias, out, out_pitch, M, N, K, ex);
-  if (staged) return launch_gemm_tc<true, true, false>(st, tmA, tmB, tmC, bias, out, out_pitch, M, N, K, ex);
-  if (out_bf16) return launch_gemm_tc<true, false, false>(st, tmA, tmB, tmC, bias, out, out_pitch, M, N, K, ex);
-  return launch_gemm_tc<false, false, false>(st, tmA, tmB, tmC, bias, out, out_pitch, M, N, K, ex);
+  if (extras) return launch_gemm_tc<true, true, true>(st, tmA, tmB, bias, out, out_pitch, M, N, K, ex);
+  if (staged) return launch_gemm_tc<true, true, false>(st, tmA, tmB, bias, out, out_pitch, M, N, K, ex);
+  if (out_bf16) return launch_gemm_tc<true, false, false>(st, tmA, tmB, bias, out, out_pitch, M, N, K, ex);
+  return launch_gemm_tc<false, false, false>(st, tmA, tmB, bias, out, out_pitch, M, N, K, ex);
 }
 
 }  // namespace xf

@@ -7,9 +7,9 @@ namespace xf {
 // `out_pitch` (elements).  N % 128 == 0, K % 64 == 0.
 // Optional extras (sc_w != nullptr; bf16 output with N == 128 only), computed in the epilogue from the tile it holds:
 //   tok[i][clip][j] (two planes, kTokPitch floats per clip) = sc_w[i,:]·y_m for row m = clip*seg_len + j, from the fp32 row
-//   colsum[clip][slot][128] = sum of the rows of `clip` (rows m in [clip*seg_len, +seg_len)) inside output tile
-//                             (clip*seg_len)/128 + slot; a clip overlaps at most kColsumSlots tiles.
-constexpr int kColsumSlots = 3;
+//   colsum[clip][slot][128] = sum of the rows of `clip` (rows m in [clip*seg_len, +seg_len)) inside the 32-row group
+//                             (clip*seg_len)/32 + slot of the output; a clip overlaps at most kColsumSlots groups.
+constexpr int kColsumSlots = 6;
 constexpr int kTokPitch = 160;   // floats per clip in each tok plane
 int gemm_tc_bf16(cudaStream_t st, const void* X, const void* W, const float* bias, void* out, bool out_bf16, int64_t out_pitch,
                  int M, int N, int K, const float* sc_w = nullptr, float* tok = nullptr, float* colsum = nullptr, int seg_len = 0);

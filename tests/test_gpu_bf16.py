@@ -58,7 +58,7 @@ def _ws_views(ws, B, T, Ta):
     E, EP = 128, 128
     spec = [("v0", torch.float32, (B, T, E)), ("a0", torch.bfloat16, (B * Ta, EP)), ("qt", torch.bfloat16, (B, 64, EP)),
             ("meanv", torch.float32, (B, E)), ("tqv", torch.float32, (B, 16)), ("tkv", torch.float32, (B, 16)),
-            ("u", torch.bfloat16, (B, 64, E)), ("tok", torch.float32, (2, B, 160)), ("acol", torch.float32, (B, 3, E)),
+            ("u", torch.bfloat16, (B, 64, E)), ("tok", torch.float32, (2, B, 160)), ("acol", torch.float32, (B, 6, E)),
             ("pc", torch.float32, (B, 4)),
             ("kt", torch.bfloat16, (B, 64, EP)), ("vt", torch.bfloat16, (B, 64, EP)), ("cv", torch.float32, (B, 64)),
             ("pooled", torch.float32, (B, 2 * E))]
