@@ -344,8 +344,11 @@ __global__ void __launch_bounds__(kV2AThreads, 1) v2a_tc_kernel(const __grid_con
 //        shuffle butterfly (4 columns per lane come out) and leave as one partial per (clip, tile, warp); the head kernel
 //        adds a clip's partials in a fixed order and applies gamma/Ta, beta (mean_t LN(x) = gamma·mean xhat + beta).
 //   warp 0: TMA producer   warp 1: MMA issuer, polls for whichever of {next S, next O} is ready
-//   warps 2-5 / 6-9: two softmax+LayerNorm groups alternating row tiles, each with its own 256-column TMEM buffer
-constexpr int kA2VThreads = 64 + 256;
+//   warps 2-9 / 10-17: two softmax+LayerNorm groups alternating row tiles, each with its own 256-column TMEM buffer.
+//   Inside a group, warps w and w+4 share a TMEM sub-partition (the same 32 rows) and split the work in halves: two of
+//   the four heads in the softmax, 64 of the 128 columns in the LayerNorm; the row statistics meet in the dead half of
+//   the score columns.
+constexpr int kA2VThreads = 64 + 512;
 constexpr int kA2VHalf = 2 * kA0Box;                         // a0 stage layout: [feature half][clip][160 rows][128 B]
 constexpr int kKvHalf = 2 * kBox;                            // Kt / Vt layout:  [feature half][clip][64 rows][128 B]
 constexpr int kKvTile = 2 * kKvHalf;                         // 32 KB: both clips
@@ -391,11 +394,11 @@ __global__ void __launch_bounds__(kA2VThreads, 1) a2v_tc_kernel(const __grid_con
     tc::tma_prefetch_desc(&tmVt);
     for (int i = 0; i < 2; ++i) {
       tc::mbar_init(&a0_full[i], 1);
-      tc::mbar_init(&a0_empty[i], 384);   // released by the rows themselves, after their residual read (3 tiles x 128 threads)
+      tc::mbar_init(&a0_empty[i], 768);   // released by the rows themselves, after their residual read (3 tiles x 256 threads)
       tc::mbar_init(&s_full[i], 1);
-      tc::mbar_init(&p_full[i], 128);
+      tc::mbar_init(&p_full[i], 256);
       tc::mbar_init(&o_full[i], 1);
-      tc::mbar_init(&o_empty[i], 128);
+      tc::mbar_init(&o_empty[i], 256);
     }
     tc::mbar_init(kt_full, 1);
     tc::mbar_init(kt_empty, 1);
@@ -503,11 +506,13 @@ __global__ void __launch_bounds__(kA2VThreads, 1) a2v_tc_kernel(const __grid_con
     }
   } else {
     // ---- softmax + LayerNorm warps: group g handles the tiles with n & 1 == g in TMEM buffer g ----
-    const int sp = warp & 3, grp = (warp - 2) >> 2;
+    const int ww = warp - 2, grp = ww >> 3, hf = (ww >> 2) & 1, sp = warp & 3;
     const uint32_t tlane = (uint32_t)(32 * sp) << 16;
     const uint32_t tbuf = tmem + grp * 256 + tlane;
+    const uint32_t pair_bar = 1 + grp * 4 + sp;      // named barrier of the two warps that share these 32 rows
     const float bsc = a.use_prior ? __ldg(a.bias_scale) : 0.f;
     const float bl = bsc * kL2E;
+    const bool tracer = hf == 0 && sp == 2 && lane == 0;
     // row of tile n owned by this thread: R in the 320-row pair (clip 1 starts at 160), clip c, token j
     auto row_of = [&](uint32_t n, int& R, int& ci, int& c, bool& valid) {
       const uint32_t it = n / 3, t = n % 3;
@@ -538,12 +543,11 @@ __global__ void __launch_bounds__(kA2VThreads, 1) a2v_tc_kernel(const __grid_con
       const float qa = qa_n, pk = pk_n;
       tc::mbar_wait(&s_full[grp], (n >> 1) & 1u);
       tc::mbar_wait(&a0_full[s], (it >> 1) & 1u);   // already complete; acquires the TMA-written key constants
-      if (sp == 2 && lane == 0) trace_mark(a.trace, 3, n);   // worker: scores ready
+      if (tracer) trace_mark(a.trace, 3, n);   // worker: scores ready
       tc::tc_fence_after();
       {
-        uint32_t r0[32], r1[32];              // the 4 heads x 16 keys of this row against its own clip
-        tc::tmem_ld_32x32(tbuf + (uint32_t)(64 * ci), r0);
-        tc::tmem_ld_32x32(tbuf + (uint32_t)(64 * ci + 32), r1);
+        uint32_t r0[32];                      // heads 2hf, 2hf+1 x 16 keys of this row against its own clip
+        tc::tmem_ld_32x32(tbuf + (uint32_t)(64 * ci + 32 * hf), r0);
         const float* kc = kc_s + (s * 2 + ci) * 80;
         float bia[16];   // the prior bias is the same for every head (fusion.py:351-354): once per key
 #pragma unroll
@@ -552,15 +556,14 @@ __global__ void __launch_bounds__(kA2VThreads, 1) a2v_tc_kernel(const __grid_con
           if (i >= a.T) bia[i] = -INFINITY;   // padded video tokens never receive probability mass
         }
         tc::tmem_ld_wait();
-        uint32_t pk2[32];
+        uint32_t pk2[16];
 #pragma unroll
-        for (int hh = 0; hh < BH; ++hh) {
+        for (int h2 = 0; h2 < 2; ++h2) {
           float x[16];
           float m = -INFINITY;
 #pragma unroll
           for (int i = 0; i < 16; ++i) {
-            const float sc = __uint_as_float(hh < 2 ? r0[16 * hh + i] : r1[16 * (hh - 2) + i]);
-            x[i] = fmaf(sc + kc[16 + 16 * hh + i], kL2E, bia[i]);
+            x[i] = fmaf(__uint_as_float(r0[16 * h2 + i]) + kc[16 + 32 * hf + 16 * h2 + i], kL2E, bia[i]);
             m = fmaxf(m, x[i]);
           }
           float l0 = 0.f, l1 = 0.f;
@@ -573,50 +576,42 @@ __global__ void __launch_bounds__(kA2VThreads, 1) a2v_tc_kernel(const __grid_con
           }
           const float inv = __frcp_rn(l0 + l1);
 #pragma unroll
-          for (int i = 0; i < 16; i += 2) pk2[8 * hh + (i >> 1)] = tc::pack_bf16(x[i] * inv, x[i + 1] * inv);
+          for (int i = 0; i < 16; i += 2) pk2[8 * h2 + (i >> 1)] = tc::pack_bf16(x[i] * inv, x[i + 1] * inv);
         }
         uint32_t z[16];
 #pragma unroll
         for (int i = 0; i < 16; ++i) z[i] = 0u;
-        uint32_t lo[16], hi[16];
-#pragma unroll
-        for (int i = 0; i < 16; ++i) {
-          lo[i] = pk2[i];
-          hi[i] = pk2[16 + i];
-        }
-        tc::tmem_st_32x32_x16(tbuf + (uint32_t)(32 * ci), lo);
-        tc::tmem_st_32x32_x16(tbuf + (uint32_t)(32 * ci + 16), hi);
-        tc::tmem_st_32x32_x16(tbuf + (uint32_t)(32 * (ci ^ 1)), z);
-        tc::tmem_st_32x32_x16(tbuf + (uint32_t)(32 * (ci ^ 1) + 16), z);
+        tc::tmem_st_32x32_x16(tbuf + (uint32_t)(32 * ci + 16 * hf), pk2);
+        tc::tmem_st_32x32_x16(tbuf + (uint32_t)(32 * (ci ^ 1) + 16 * hf), z);
         tc::tmem_st_wait();
         tc::tc_fence_before();
         tc::mbar_arrive(&p_full[grp]);
-        if (sp == 2 && lane == 0) trace_mark(a.trace, 4, n);   // worker: P written
+        if (tracer) trace_mark(a.trace, 4, n);   // worker: P written
       }
       row_consts(n + 2, qa_n, pk_n);           // next tile's row constants: in flight during the LayerNorm below
-      // ---- a1 = LayerNorm(a0 + out [+ bo2, inside out]) (fusion.py:399) accumulated into the temporal mean (:402) ----
-      float x[BE];
-      const uint8_t* arow = a0s + s * kA0Stage + R * 128;
+      // ---- a1 = LayerNorm(a0 + out [+ bo2, inside out]) (fusion.py:399) accumulated into the temporal mean (:402);
+      //      this thread: columns [64 hf, 64 hf + 64) of its row ----
+      constexpr int HC = BE / 2;
+      float x[HC];
+      const uint8_t* arow = a0s + s * kA0Stage + hf * kA2VHalf + R * 128;
       tc::mbar_wait(&o_full[grp], (n >> 1) & 1u);
-      if (sp == 2 && lane == 0) trace_mark(a.trace, 5, n);   // worker: O ready
+      if (tracer) trace_mark(a.trace, 5, n);   // worker: O ready
       tc::tc_fence_after();
       {
-        uint32_t (&xr)[BE] = reinterpret_cast<uint32_t (&)[BE]>(x);
-        uint32_t t0[32], t1[32], t2[32], t3[32];
-        tc::tmem_ld_32x32(tbuf + 128u, t0);
-        tc::tmem_ld_32x32(tbuf + 160u, t1);
-        tc::tmem_ld_32x32(tbuf + 192u, t2);
-        tc::tmem_ld_32x32(tbuf + 224u, t3);
+        uint32_t (&xr)[HC] = reinterpret_cast<uint32_t (&)[HC]>(x);
+        uint32_t t0[32], t1[32];
+        tc::tmem_ld_32x32(tbuf + 128u + (uint32_t)(64 * hf), t0);
+        tc::tmem_ld_32x32(tbuf + 160u + (uint32_t)(64 * hf), t1);
         tc::tmem_ld_wait();
 #pragma unroll
         for (int i = 0; i < 32; ++i) {
-          xr[i] = t0[i]; xr[32 + i] = t1[i]; xr[64 + i] = t2[i]; xr[96 + i] = t3[i];
+          xr[i] = t0[i]; xr[32 + i] = t1[i];
         }
       }
-      float sum0 = 0.f, sum1 = 0.f;
+      float sum0 = 0.f, sum1 = 0.f, sq0 = 0.f, sq1 = 0.f;
 #pragma unroll
-      for (int k = 0; k < 16; ++k) {   // + this row of a0 (the residual, 16-byte chunk k of the swizzled row)
-        const uint4 res = *reinterpret_cast<const uint4*>(arow + (k >> 3) * kA2VHalf + (((k ^ R) & 7) << 4));
+      for (int k = 0; k < 8; ++k) {   // + this row of a0 (the residual, 16-byte chunk k of the swizzled half row)
+        const uint4 res = *reinterpret_cast<const uint4*>(arow + (((k ^ R) & 7) << 4));
         const uint32_t w[4] = {res.x, res.y, res.z, res.w};
 #pragma unroll
         for (int e = 0; e < 4; ++e) {
@@ -625,27 +620,38 @@ __global__ void __launch_bounds__(kA2VThreads, 1) a2v_tc_kernel(const __grid_con
           x[col + 1] += __uint_as_float(w[e] & 0xFFFF0000u);
           sum0 += x[col];
           sum1 += x[col + 1];
+          sq0 = fmaf(x[col], x[col], sq0);
+          sq1 = fmaf(x[col + 1], x[col + 1], sq1);
         }
       }
-      tc::tc_fence_before();
-      tc::mbar_arrive(&o_empty[grp]);          // O (and the P it was made from) is in registers: the buffer can be refilled
-      tc::mbar_arrive(&a0_empty[s]);           // and so is this row's residual
-      if (sp == 2 && lane == 0) trace_mark(a.trace, 6, n);   // worker: O + residual in registers
-      const float mu = (sum0 + sum1) * (1.f / BE);
-      float q0 = 0.f, q1 = 0.f;
-#pragma unroll
-      for (int i = 0; i < BE; i += 2) {        // two-pass variance (as torch LayerNorm): sum (x - mu)^2
-        x[i] -= mu;
-        x[i + 1] -= mu;
-        q0 = fmaf(x[i], x[i], q0);
-        q1 = fmaf(x[i + 1], x[i + 1], q1);
+      // the two halves of the row meet: (sum, sum of squares) through the dead upper half of the score columns
+      float su = sum0 + sum1, sq = sq0 + sq1;
+      {
+        const uint32_t tx = tbuf + 64u;
+        tc::tmem_st_32x32_x1(tx + (uint32_t)(2 * hf), __float_as_uint(su));
+        tc::tmem_st_32x32_x1(tx + (uint32_t)(2 * hf + 1), __float_as_uint(sq));
+        tc::tmem_st_wait();
+        tc::tc_fence_before();
+        tc::named_bar_sync(pair_bar, 64);
+        tc::tc_fence_after();
+        const uint32_t psu = tc::tmem_ld_32x32_x1(tx + (uint32_t)(2 * (hf ^ 1)));
+        const uint32_t psq = tc::tmem_ld_32x32_x1(tx + (uint32_t)(2 * (hf ^ 1) + 1));
+        tc::tmem_ld_wait();
+        su += __uint_as_float(psu);
+        sq += __uint_as_float(psq);
       }
-      const float rs = rsqrtf((q0 + q1) * (1.f / BE) + 1e-5f);
+      tc::tc_fence_before();
+      tc::mbar_arrive(&o_empty[grp]);          // O, P and the exchange columns are done with: the buffer can be refilled
+      tc::mbar_arrive(&a0_empty[s]);           // and so is this row's residual
+      if (tracer) trace_mark(a.trace, 6, n);   // worker: O + residual in registers
+      const float mu = su * (1.f / BE);
+      const float rs = rsqrtf(fmaxf(sq * (1.f / BE) - mu * mu, 0.f) + 1e-5f);
+      const float nmr = -mu * rs;
 #pragma unroll
-      for (int i = 0; i < BE; ++i) x[i] = valid ? x[i] * rs : 0.f;   // padded / absent rows contribute nothing (select, not multiply)
-      // sum over the warp's 32 rows: butterfly, the live columns halve at every step; lane L ends with columns 32b + rev...
+      for (int i = 0; i < HC; ++i) x[i] = valid ? fmaf(x[i], rs, nmr) : 0.f;   // padded / absent rows contribute nothing (select)
+      // sum over the warp's 32 rows: butterfly, the live columns halve at every step
 #pragma unroll
-      for (int off = 16, cnt = BE / 2; off >= 1; off >>= 1, cnt >>= 1) {
+      for (int off = 16, cnt = HC / 2; off >= 1; off >>= 1, cnt >>= 1) {
         const bool up = (lane & off) != 0;
 #pragma unroll
         for (int i = 0; i < cnt; ++i) {
@@ -654,17 +660,18 @@ __global__ void __launch_bounds__(kA2VThreads, 1) a2v_tc_kernel(const __grid_con
           x[i] = keep + __shfl_xor_sync(0xffffffffu, send, off);
         }
       }
-      // after the five steps lane L holds columns {cidx(L) + 0..3}: bit k of L chose the upper half at step k
+      // after the five steps lane L holds two columns: bit k of L chose the upper half at step k
       {
         int base = 0;
 #pragma unroll
-        for (int off = 16, cnt = BE / 2; off >= 1; off >>= 1, cnt >>= 1)
+        for (int off = 16, cnt = HC / 2; off >= 1; off >>= 1, cnt >>= 1)
           if (lane & off) base += cnt;
         // slot of this (clip, tile, warp): even clip: tile 0 warps 0-3 -> 0-3, tile 1 warp 0 -> 4; odd clip: tile 1 warps 1-3 -> 0-2, tile 2 -> 3-6
         const int slot = ci == 0 ? (t == 0 ? sp : 4) : (t == 1 ? sp - 1 : 3 + sp);
-        if (c < a.B) *reinterpret_cast<float4*>(a.poolp + ((int64_t)c * kPoolSlots + slot) * BE + base) = make_float4(x[0], x[1], x[2], x[3]);
+        if (c < a.B)
+          *reinterpret_cast<float2*>(a.poolp + ((int64_t)c * kPoolSlots + slot) * BE + HC * hf + base) = make_float2(x[0], x[1]);
       }
-      if (sp == 2 && lane == 0) trace_mark(a.trace, 7, n);   // worker: tile done
+      if (tracer) trace_mark(a.trace, 7, n);   // worker: tile done
     }
   }
   tc::tc_fence_before();

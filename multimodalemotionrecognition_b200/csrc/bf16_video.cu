@@ -188,11 +188,19 @@ __device__ __forceinline__ void proj32(float (&acc)[4][4], const uint32_t (&af)[
 __global__ void __launch_bounds__(kUpdWarps * 32, 1) video_update_kernel(VideoUpdArgs a) {
   extern __shared__ __align__(16) uint8_t sm[];
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, g = lane >> 2, t = lane & 3;
+  // the six weight matrices arrive as bulk async copies (one thread issues, the copy engine streams 204 KB from L2)
+  __shared__ uint64_t wbar;
+  if (tid == 0) {
+    tc::mbar_init(&wbar, 1);
+    tc::fence_barrier_init();
+    tc::mbar_expect_tx(&wbar, 6 * kWBytes);
 #pragma unroll
-  for (int i = 0; i < 6; ++i) fr::copy_g2s(sm + i * kWBytes, a.W[i], kWBytes, tid, blockDim.x);
+    for (int i = 0; i < 6; ++i) tc::bulk_load_1d(sm + i * kWBytes, a.W[i], kWBytes, &wbar);
+  }
   float* vecs = reinterpret_cast<float*>(sm + 6 * kWBytes);
   for (int i = tid; i < 8 * BE; i += blockDim.x) vecs[i] = a.vec[i / BE][i % BE];
   __syncthreads();
+  tc::mbar_wait(&wbar, 0);
   const uint32_t wv1 = tc::smem_u32(sm), wo1 = wv1 + kWBytes, wk2 = wv1 + 2 * kWBytes, wv2 = wv1 + 3 * kWBytes,
                  wq2 = wv1 + 4 * kWBytes, wo2 = wv1 + 5 * kWBytes;
   const float *bv1 = vecs, *bo1 = vecs + BE, *bk2 = vecs + 2 * BE, *bv2 = vecs + 3 * BE, *bq2 = vecs + 4 * BE,
