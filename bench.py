@@ -47,20 +47,20 @@ def stage_model():
     qt = 4 * T * E_ * 2                        # one folded per-clip operand [H*T, E] bf16
     return {
         "gemm_v0": {"bytes": T * DV * 2 + T * E_ * 4, "flops": 2 * T * DV * E_},
-        "gemm_a0": {"bytes": TA * DA * 2 + TA * E_ * 2 + TA * 8, "flops": 2 * TA * DA * E_ + 4 * TA * E_},
+        "gemm_a0": {"bytes": TA * DA * 2 + TA * E_ * 2 + TA * 8 + 6 * E_ * 4, "flops": 2 * TA * DA * E_ + 4 * TA * E_},
         "video_pre": {"bytes": T * E_ * 4 + qt, "flops": 2 * tee},
         "prior": {"bytes": 4 * E_ * 4 + E_ * 4 + 16, "flops": 2 * (2 * E_ * 64 + 64 * 8)},
-        "v2a_attn": {"bytes": TA * E_ * 2 + 2 * qt, "flops": 2 * (2 * H_ * T * TA * E_)},
+        "v2a_attn": {"bytes": TA * E_ * 2 + 2 * qt + TA * 4, "flops": 2 * (2 * H_ * T * TA * E_)},
         "video_update": {"bytes": 3 * qt + T * E_ * 4 + E_ * 4, "flops": 7 * tee},
-        "a2v_attn": {"bytes": TA * E_ * 2 + 2 * qt + E_ * 4, "flops": 2 * (2 * TA * H_ * T * E_)},
-        "head": {"bytes": 2 * E_ * 4 + NCLS * 4, "flops": 2 * (2 * E_ * HW_ + HW_ * NCLS)},
+        "a2v_attn": {"bytes": TA * E_ * 2 + 2 * qt + TA * 4 + 6 * E_ * 4, "flops": 2 * (2 * TA * H_ * T * E_)},
+        "head": {"bytes": E_ * 4 + 6 * E_ * 4 + NCLS * 4, "flops": 2 * (2 * E_ * HW_ + HW_ * NCLS)},
     }
 
 
 # dram__bytes_read.sum + dram__bytes_write.sum per launch at B=4096 from the committed `ncu --set full` capture
-# (profiles/r01_ncu_full_bf16.csv); reported as roofline.traffic only when the bench runs that batch.
-NCU_TRAFFIC_B4096 = {"gemm_a0": 1.0856e9, "v2a_attn": 288.6e6, "a2v_attn": 317.6e6, "video_update": 218.4e6,
-                     "video_pre": 61.4e6, "head": 4.35e6}
+# (profiles/r01_ncu_full_bf16_v3.csv); reported as roofline.traffic only when the bench runs that batch.
+NCU_TRAFFIC_B4096 = {"gemm_v0": 73.0e6, "gemm_a0": 1095.1e6, "video_pre": 50.1e6, "v2a_attn": 269.1e6, "video_update": 198.1e6,
+                     "a2v_attn": 309.9e6}
 
 METRIC = "xattn fusion clips/sec at 1/2/4/8 B200; % of tensor/HBM roofline vs CPU ref"
 
