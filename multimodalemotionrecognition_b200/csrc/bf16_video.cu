@@ -4,6 +4,8 @@
 //   video_pre_kernel     v0 -> Qt (the per-clip 64x128 operand that replaces Q·K^T's audio-side K projection) + prior inputs
 //   video_update_kernel  U -> attention output -> out_proj -> v1 = LN(v0 + .) -> pooled_v, Kt, c, Vt
 // Reference: src/models/fusion.py:394-395 (v2a_attn, v_norm) and the K/V side of :398 (a2v_attn).
+#include <cstdlib>
+
 #include "bf16_layout.cuh"
 #include "frag.cuh"
 
@@ -352,8 +354,12 @@ static int video_grid(int B, int ctas_per_sm, int warps = 8) {
   return need < cap ? need : cap;
 }
 
+int launch_video_pre_tc(const Bf16Ctx& x);
+
 int launch_video_pre(const Bf16Ctx& x) {
   const xattn_config& c = *x.cfg;
+  static const bool legacy = getenv("XATTN_VIDEO_PRE_LEGACY") != nullptr;
+  if (!legacy) return launch_video_pre_tc(x);
   auto P = [&](int id) { return x.params + x.pl.off[id]; };
   VideoPreArgs a;
   a.v0 = reinterpret_cast<const float*>(x.ws + x.w.v0);
