@@ -10,7 +10,7 @@
 //                                            as an MN-major operand — a0 is loaded once, P never touches shared memory
 //   The two clips' accumulators share TMEM columns: clip 0 in lanes 0-15, clip 1 in lanes 16-31 of every sub-partition
 //   (the M=64 data-path layout), so a warp's 32 lanes are 32 independent softmax rows and no row statistic crosses lanes.
-//   U leaves in mma A-fragment order (16x256b TMEM loads return exactly that distribution) for video_update.
+//   U leaves row-major as [16·clip + i][128h + e] bf16, the A operand of the video_mix GEMM (gemm_tc.cuh).
 //   warp 0: TMA producer (a0 and Qt rings, one pair ahead)    warp 1: MMA issuer (S of pair i+1 right behind U of pair i)
 //   warps 2-9: softmax + epilogue.  Warps w and w+4 share a TMEM sub-partition (= head) and split the 160 key columns of
 //   every row in halves, so all eight warps work on the pair whose a0 tile is resident and the tile is released early.
@@ -47,7 +47,7 @@ static_assert(kV2ASmem <= 227 * 1024, "v2a_tc_kernel shared memory");
 struct V2ATcArgs {
   const float *tqv, *tok, *pc;   // [B,16] w_vq·v0_i ; [2,B,160] w_ak·a0_j | w_aq·a0_j ; [B,4]
   const float* bias_scale;
-  __nv_bfloat16* u;              // [B,4,8,32] x uint4: mma A-fragment order, [clip][head][ks][lane]
+  __nv_bfloat16* u;              // [16·B, 4·128]: row (clip, i), columns 128h + e
   int B, Ta, use_prior;
   unsigned long long* trace;     // XATTN_TC_TRACE=1: [8 events][64 pairs] globaltimer stamps of CTA 0 (pipeline debugging)
 };
@@ -215,7 +215,6 @@ __global__ void __launch_bounds__(kV2AThreads, 1) v2a_tc_kernel(const __grid_con
     const uint32_t tX = tmem + kTmemX + tlane;
     const float bsc = a.use_prior ? __ldg(a.bias_scale) : 0.f;
     const float bl = bsc * kL2E;
-    const int g = lane >> 2;
     const int j0 = 80 * half;
     // qk = qv_i + the prior parts of both bias heads: w_vq·v0_i + pc[v_query] + pc[a_key]   (fusion.py:171, :173)
     auto qk_fetch = [&](int p, float& t0, float& t1, float& t2) {
@@ -292,32 +291,33 @@ __global__ void __launch_bounds__(kV2AThreads, 1) v2a_tc_kernel(const __grid_con
       tc::mbar_arrive(p_full);
       if (threadIdx.x == 64) trace_mark(a.trace, 5, it);   // worker: P written
       qk_fetch(p + gridDim.x, q0, q1, q2);            // next pair's row constants: in flight during the U product
-      // ---- epilogue: this warp's head of clip `half`; U rows scaled by 1/l, bf16, mma A-fragment order ----
+      // ---- epilogue: this warp's head, both clips (lane = (clip, row)), columns [64·half, +64); rows scaled by 1/l, bf16,
+      //      row-major [16·clip + q][128h + e]: the A operand of the video_mix GEMM ----
       tc::mbar_wait(u_full, it & 1u);                 // (completes after every p_full arrival: the partner's sums are in place)
       if (threadIdx.x == 64) trace_mark(a.trace, 6, it);   // worker: U ready
       tc::tc_fence_after();
       {
-        uint32_t r[64];
-        tc::tmem_ld_16x256_x16(tmem + kTmemU + tlane + ((uint32_t)(16 * half) << 16), r);
+        uint32_t r0u[32], r1u[32];
+        tc::tmem_ld_32x32(tmem + kTmemU + tlane + (uint32_t)(64 * half), r0u);
+        tc::tmem_ld_32x32(tmem + kTmemU + tlane + (uint32_t)(64 * half + 32), r1u);
         const float lp = __uint_as_float(tc::tmem_ld_32x32_x1(tX + 2u + (uint32_t)(half ^ 1)));
         tc::tmem_ld_wait();
         tc::tc_fence_before();
         tc::mbar_arrive(u_empty);
-        const float lt = l + lp;                      // whole-row sum of this lane's row
-        const float inv0 = 1.f / __shfl_sync(0xffffffffu, lt, 16 * half + g);
-        const float inv1 = 1.f / __shfl_sync(0xffffffffu, lt, 16 * half + g + 8);
-        const int cc = 2 * p + half;
+        const float inv = 1.f / (l + lp);             // whole-row sum of this lane's row
+        const int cc = 2 * p + (lane >> 4);
         if (cc < a.B) {
-          uint4* up = reinterpret_cast<uint4*>(a.u) + ((int64_t)cc * BH + h) * 256 + lane;   // [ks][lane]: coalesced
+          // 128 bytes of this lane's row: four 32-byte stores, each a whole sector
+          __nv_bfloat16* up = a.u + ((int64_t)cc * 16 + (lane & 15)) * (4 * BE) + h * BE + 64 * half;
+          uint32_t w[32];
 #pragma unroll
-          for (int ks = 0; ks < 8; ++ks) {
-            uint4 v;
-            v.x = tc::pack_bf16(__uint_as_float(r[8 * ks + 0]) * inv0, __uint_as_float(r[8 * ks + 1]) * inv0);
-            v.y = tc::pack_bf16(__uint_as_float(r[8 * ks + 2]) * inv1, __uint_as_float(r[8 * ks + 3]) * inv1);
-            v.z = tc::pack_bf16(__uint_as_float(r[8 * ks + 4]) * inv0, __uint_as_float(r[8 * ks + 5]) * inv0);
-            v.w = tc::pack_bf16(__uint_as_float(r[8 * ks + 6]) * inv1, __uint_as_float(r[8 * ks + 7]) * inv1);
-            up[ks * 32] = v;
+          for (int v = 0; v < 16; ++v) {
+            w[v] = tc::pack_bf16(__uint_as_float(r0u[2 * v]) * inv, __uint_as_float(r0u[2 * v + 1]) * inv);
+            w[16 + v] = tc::pack_bf16(__uint_as_float(r1u[2 * v]) * inv, __uint_as_float(r1u[2 * v + 1]) * inv);
           }
+#pragma unroll
+          for (int v = 0; v < 4; ++v)
+            tc::stg256(up + 16 * v, w[8 * v], w[8 * v + 1], w[8 * v + 2], w[8 * v + 3], w[8 * v + 4], w[8 * v + 5], w[8 * v + 6], w[8 * v + 7]);
         }
       }
       if (threadIdx.x == 64) trace_mark(a.trace, 7, it);   // worker: U stored

@@ -43,7 +43,10 @@ void compute_pack_bf16(const xattn_config& c, PackBf16& p) {
   p.W0b = take(HW * 2 * E * 2);
   p.pW0 = take((int64_t)(c.use_prior ? c.prior_hidden : 0) * 2 * E * 2);
   p.scw = take(2 * E * 4);
-  p.scratch = take(E * c.Da * 4);
+  p.Gmix = take(E * 4 * E * 2); p.bmix = take(E * 4);
+  p.Fkv = take(8 * E * E * 2); p.bkv = take(8 * E * 4);
+  p.wcv = take((4 * E + 4) * 4);
+  p.scratch = take((E * c.Da > 8 * E * E ? E * c.Da : 8 * E * E) * 4);
   p.total = off;
 }
 
@@ -70,6 +73,7 @@ void compute_ws_bf16(const xattn_config& c, WsBf16& w) {
   w.cv = take(B * 64 * 4);
   w.pooled = take(B * 2 * E * 4);
   w.poolp = take(B * 8 * E * 4);
+  w.v1 = take(B * 16 * E * 2);
   w.total = off + 256;
 }
 
@@ -94,12 +98,21 @@ int workspace_bytes_bf16(const xattn_config& c, int64_t* bytes) {
 
 // dst[r, 0..cols) (pitch dpitch, bf16) = src[r, 0..cols) (pitch spitch, fp32); pad columns zeroed.
 __global__ void cvt_rows_bf16_kernel(const float* __restrict__ src, int64_t spitch, __nv_bfloat16* __restrict__ dst,
-                                     int64_t dpitch, int rows, int cols) {
+                                     int64_t dpitch, int rows, int cols, float scale) {
   const int64_t n = (int64_t)rows * dpitch;
   for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
     const int64_t r = i / dpitch, cidx = i - r * dpitch;
-    dst[i] = __float2bfloat16(cidx < cols ? src[r * spitch + cidx] : 0.f);
+    dst[i] = __float2bfloat16(cidx < cols ? scale * src[r * spitch + cidx] : 0.f);
   }
+}
+// out[n] = alpha · sum_{d<D} x[d]·M[d*rs + n*cs]  (+ beta·add[n])      — the bias / vector halves of the folded projections
+__global__ void fold_vec_kernel(const float* __restrict__ x, const float* __restrict__ Mx, int64_t rs, int64_t cs, int D, int N,
+                                float alpha, const float* __restrict__ add, float beta, float* __restrict__ out) {
+  const int n = blockIdx.x * blockDim.x + threadIdx.x;
+  if (n >= N) return;
+  float s = 0.f;
+  for (int d = 0; d < D; ++d) s = fmaf(x[d], Mx[d * rs + n * cs], s);
+  out[n] = alpha * s + (add != nullptr ? beta * add[n] : 0.f);
 }
 // out[e] = W_in[e,:]·b_seq + b_in[e]
 __global__ void fold_bias_kernel(const float* __restrict__ w_in, const float* __restrict__ b_seq, const float* __restrict__ b_in,
@@ -120,10 +133,15 @@ int pack_weights_bf16(const xattn_config& c, const float* params, void* packed_v
   auto P = [&](int id) { return params + pl.off[id]; };
   auto BF = [&](int64_t off) { return reinterpret_cast<__nv_bfloat16*>(packed + off); };
   const int E = c.E;
-  auto cvt = [&](const float* src, int64_t spitch, int64_t dst_off, int64_t dpitch, int rows, int cols) {
+  auto cvt = [&](const float* src, int64_t spitch, int64_t dst_off, int64_t dpitch, int rows, int cols, float scale = 1.f) {
     const int64_t n = (int64_t)rows * dpitch;
     const int blocks = (int)((n + 255) / 256 < 1024 ? (n + 255) / 256 : 1024);
-    cvt_rows_bf16_kernel<<<blocks, 256, 0, st>>>(src, spitch, BF(dst_off), dpitch, rows, cols);
+    cvt_rows_bf16_kernel<<<blocks, 256, 0, st>>>(src, spitch, BF(dst_off), dpitch, rows, cols, scale);
+    count_launch();
+  };
+  auto fvec = [&](const float* x, const float* Mx, int64_t rs, int64_t cs, int D, int N, float alpha, const float* add, float beta,
+                  float* out) {
+    fold_vec_kernel<<<(N + 127) / 128, 128, 0, st>>>(x, Mx, rs, cs, D, N, alpha, add, beta, out);
     count_launch();
   };
   cvt(P(XP_V_IN_W), c.Dv, pk.Wv, c.Dv, E, c.Dv);
@@ -143,6 +161,33 @@ int pack_weights_bf16(const xattn_config& c, const float* params, void* packed_v
   cvt(in2 + (int64_t)E * E, E, pk.Wk2, BEP, E, E);
   cvt(in2 + (int64_t)2 * E * E, E, pk.Wv2, BEP, E, E);
   cvt(P(XP_A2V_OUT_W), E, pk.Wo2, BEP, E, E);
+  {
+    // ---- the video-side update as two GEMMs: per-head folds in fp32, rounded to bf16 once (fusion.py:394-398) ----
+    const float scale = 1.0f / sqrtf((float)BDH);
+    const float *Wv1 = in1 + (int64_t)2 * E * E, *bv1 = P(XP_V2A_IN_B) + 2 * E, *Wo1 = P(XP_V2A_OUT_W), *bo1 = P(XP_V2A_OUT_B);
+    const float *Wq2 = in2, *bq2 = P(XP_A2V_IN_B), *Wk2 = in2 + (int64_t)E * E, *bk2 = bq2 + E, *Wv2 = in2 + (int64_t)2 * E * E,
+                *bv2 = bq2 + 2 * E, *Wo2 = P(XP_A2V_OUT_W), *bo2 = P(XP_A2V_OUT_B);
+    // G[n][128h + e] = sum_d Wo1[n][32h+d]·Wv1[32h+d][e]: O_h = U_h·Wv1_h^T + bv1_h (softmax rows sum to one), then out_proj
+    for (int h = 0; h < BH; ++h)
+      launch_gemm<float, float>(st, Wo1 + 32 * h, E, 1, Wv1 + (int64_t)32 * h * E, E, 1, scratch + h * E, 4 * E, E, E, BDH, nullptr, 0);
+    cvt(scratch, 4 * E, pk.Gmix, 4 * E, E, 4 * E);
+    fvec(bv1, Wo1, 1, E, E, E, 1.f, bo1, 1.f, reinterpret_cast<float*>(packed + pk.bmix));
+    // Fk_h[e'][k] = scale·sum_d Wq2[32h+d][e']·Wk2[32h+d][k]   (Kt_h = scale·K2_h·Wq2_h with K2_h = v1·Wk2_h^T + bk2_h)
+    // Fv_h[e'][k] =       sum_d Wo2[e'][32h+d]·Wv2[32h+d][k]   (Vt_h = V2_h·Wo2_h^T + bo2/4)
+    float* bkv = reinterpret_cast<float*>(packed + pk.bkv);
+    float* wcv = reinterpret_cast<float*>(packed + pk.wcv);
+    for (int h = 0; h < BH; ++h) {
+      const int64_t ho = (int64_t)32 * h * E;
+      launch_gemm<float, float>(st, Wq2 + ho, 1, E, Wk2 + ho, E, 1, scratch + (int64_t)h * E * E, E, E, E, BDH, nullptr, 0);
+      launch_gemm<float, float>(st, Wo2 + 32 * h, E, 1, Wv2 + ho, E, 1, scratch + (int64_t)(4 + h) * E * E, E, E, E, BDH, nullptr, 0);
+      fvec(bk2 + 32 * h, Wq2 + ho, E, 1, BDH, E, scale, nullptr, 0.f, bkv + h * E);
+      fvec(bv2 + 32 * h, Wo2 + 32 * h, 1, E, BDH, E, 1.f, bo2, 0.25f, bkv + (4 + h) * E);
+      fvec(bq2 + 32 * h, Wk2 + ho, E, 1, BDH, E, scale, nullptr, 0.f, wcv + h * E);            // wc_h[k]
+      fvec(bk2 + 32 * h, bq2 + 32 * h, 1, 0, BDH, 1, scale, nullptr, 0.f, wcv + 4 * E + h);    // cc_h
+    }
+    cvt(scratch, E, pk.Fkv, E, 4 * E, E, scale);
+    cvt(scratch + (int64_t)4 * E * E, E, pk.Fkv + (int64_t)4 * E * E * 2, E, 4 * E, E);
+  }
   const int HW = c.head_kind == XATTN_HEAD_GATED ? E : c.common_dim;
   cvt(P(XP_HEAD0_W), 2 * E, pk.W0b, 2 * E, HW, 2 * E);
   XF_CUDA(cudaMemsetAsync(packed + pk.scw, 0, 2 * E * 4, st));

@@ -254,7 +254,7 @@ __global__ void __launch_bounds__(kVThreads, 2) video_pre_tc_kernel(const __grid
 
 }  // namespace
 
-int launch_video_pre_tc(const Bf16Ctx& x) {
+int launch_video_pre(const Bf16Ctx& x) {
   const xattn_config& c = *x.cfg;
   auto P = [&](int id) { return x.params + x.pl.off[id]; };
   VideoPreTcArgs a;

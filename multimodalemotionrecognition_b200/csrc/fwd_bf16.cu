@@ -190,6 +190,18 @@ static int side_stream(cudaStream_t* out) {
   return XATTN_OK;
 }
 
+// fusion.py:394-398, video side: v1 = LN(v0 + out_proj(attn)) and the per-clip operands of a2v_attn, as two tensor-core GEMMs
+// over per-head folded weights (bf16_pack.cu).
+int launch_video_update(const Bf16Ctx& x) {
+  const xattn_config& c = *x.cfg;
+  auto P = [&](int id) { return x.params + x.pl.off[id]; };
+  auto F32 = [&](int64_t off) { return reinterpret_cast<const float*>(x.packed + off); };
+  XF_TRY(gemm_tc_video_mix(x.st, x.ws + x.w.u, x.packed + x.pk.Gmix, F32(x.pk.bmix), reinterpret_cast<const float*>(x.ws + x.w.v0),
+                           P(XP_VN_W), P(XP_VN_B), F32(x.pk.wcv), x.ws + x.w.v1, reinterpret_cast<float*>(x.ws + x.w.cv),
+                           reinterpret_cast<float*>(x.ws + x.w.pooled), c.B, c.T));
+  return gemm_tc_video_kv(x.st, x.ws + x.w.v1, x.packed + x.pk.Fkv, F32(x.pk.bkv), x.ws + x.w.kt, x.ws + x.w.vt, c.B);
+}
+
 int forward_bf16(const xattn_config& c, const float* params, const void* packed, const void* xv, const void* xa, float* logits,
                  void* ws, cudaStream_t st) {
   XF_TRY(bf16_supported(c));

@@ -17,6 +17,11 @@
 //   colsum[clip][slot][n]           column sums of a warp's 32 output rows that belong to `clip` (rows are clips of seg_len
 //                                   tokens); slot = 32-row group - first group of the clip: a reader adds <= 6 partials in order
 //                                   (the temporal mean that feeds prior_net, fusion.py:180)
+// Two further epilogues run the video-side update of the xattn head as plain GEMMs over folded weights (bf16_pack.cu):
+//   EPI_LNRES    v1 = LayerNorm(v0 + [U_0|U_1|U_2|U_3]·G^T + b)  (fusion.py:394-395 with the value and output projections
+//                folded per head), + the temporal mean of v1 (:401) and c_hi = v1_i·wc_h + cc_h; rows are clips of 16 slots
+//   EPI_HEADROWS Y[m, 128h' .. +128) lands in rows 16h + i of clip m/16 of one of two [clips][64][128] operands
+//                (Kt | Vt of a2v_attn: N = 1024, column block h' = 4·which + h)
 #include <cuda.h>
 
 #include "common.cuh"
@@ -28,15 +33,23 @@ namespace xf {
 namespace {
 
 constexpr int BM = 128, BN = 128, BK = 64;
-constexpr int kStages = 5;
+constexpr int kStagesDefault = 5;
 constexpr int kAccs = 4;                               // TMEM accumulators (4 x 128 columns = all of TMEM): the MMA warp can run 3 tiles ahead of the epilogue
 constexpr int kStageBytes = (BM * BK + BN * BK) * 2;   // 32 KB
-constexpr int kGemmThreads = 192;
+constexpr int gemm_threads(int epg) { return 64 + 128 * epg; }   // TMA warp, MMA warp, EPG groups of 4 epilogue warps
 constexpr int kStageBox = BM * 128;                      // one staged box: 128 rows x 64 bf16 (STAGED: N == 128, dense rows)
 constexpr int kBarBytes = 256;
+constexpr int kVecBytes = 6144;   // bias [<= 1024] f32 | 2 KB of per-mode vectors
 
-__host__ __device__ constexpr int gemm_smem_bytes(bool staged, int pitch) {
-  return kStages * kStageBytes + (staged ? 2 * kStageBox : 0) + 3 * BN * 4 + kBarBytes + 1024;
+enum { EPI_F32 = 0, EPI_BF16 = 1, EPI_STAGED = 2, EPI_EXTRAS = 3, EPI_LNRES = 4, EPI_HEADROWS = 5 };
+//   EPI_F32 / EPI_BF16: rows go straight to global.  EPI_STAGED: bf16, N == 128, dense rows: the tile is staged in smem and
+//   leaves in global order.  EPI_EXTRAS: EPI_STAGED + token scores + column sums.
+
+__host__ __device__ constexpr int gemm_stage_region(int epi) {
+  return (epi == EPI_STAGED || epi == EPI_EXTRAS) ? 2 * kStageBox : 0;
+}
+__host__ __device__ constexpr int gemm_smem_bytes(int epi, int stages) {
+  return stages * kStageBytes + gemm_stage_region(epi) + kVecBytes + kBarBytes + 1024;
 }
 
 struct GemmExtras {
@@ -44,21 +57,47 @@ struct GemmExtras {
   float* tok;          // [2][M / seg_len][kTokPitch]
   float* colsum;       // [M / seg_len][kColsumSlots][128]
   int seg_len;
+  // EPI_HEADROWS: column blocks 4..7 go to out2
+  void* out2;
+  // EPI_LNRES
+  const float* res;            // v0 [clips][T][128] fp32
+  const float *gamma, *beta;   // LayerNorm affine [128]
+  const float* wc;             // [4][128] + [4]: c_hi = y·wc_h + wc[512 + h]
+  float *cv, *pooled;          // [clips][64], [clips][256] (first 128 = temporal mean)
+  int T, clips;
 };
 
-// OUT_BF16: output dtype.  STAGED: bf16, N == 128, dense output rows -> swizzled smem tile + TMA tensor stores.
-template <bool OUT_BF16, bool STAGED, bool EXTRAS>
-__global__ void __launch_bounds__(kGemmThreads, 1) gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA,
+// One step of the transpose-reduce over lanes: x[0..N) (+)= the partner's other half; N values remain.
+template <int N, int O>
+__device__ __forceinline__ void lnres_fold(float (&x)[BN], int lane) {
+  const bool up = (lane & O) != 0;
+#pragma unroll
+  for (int k = 0; k < N; ++k) {
+    const float send = up ? x[k] : x[k + N];
+    const float keep = up ? x[k + N] : x[k];
+    x[k] = keep + __shfl_xor_sync(0xffffffffu, send, O);
+  }
+}
+
+// EPG groups of epilogue warps take the tiles of a CTA in turn (tile l of the CTA -> group l % EPG): for the short-K products the
+// epilogue, not the operand stream, is what a tile costs.
+template <int EPI, int kStages, int EPG>
+__global__ void __launch_bounds__(gemm_threads(EPG), 1) gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA,
                                                                   const __grid_constant__ CUtensorMap tmB,
                                                                   const float* __restrict__ bias, void* __restrict__ out,
                                                                   int64_t out_pitch, int M, int N, int K, GemmExtras ex) {
-  static_assert(!EXTRAS || STAGED, "the extras read the staged tile");
+  constexpr bool OUT_BF16 = EPI != EPI_F32 && EPI != EPI_LNRES;
+  constexpr bool STAGED = EPI == EPI_STAGED || EPI == EPI_EXTRAS;
+  constexpr bool EXTRAS = EPI == EPI_EXTRAS;
+  constexpr bool HEADROWS = EPI == EPI_HEADROWS;
+  constexpr bool LNRES = EPI == EPI_LNRES;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
-  uint8_t* stage_out = smem + kStages * kStageBytes;                                   // 2 boxes [128 rows][64 bf16], swizzled (STAGED)
-  float* bias_s = reinterpret_cast<float*>(stage_out + (STAGED ? 2 * kStageBox : 0));
-  float2* scw_s = reinterpret_cast<float2*>(bias_s + BN);   // [128] (w_ak[n], w_aq[n])
-  uint64_t* full = reinterpret_cast<uint64_t*>(bias_s + 3 * BN);
+  uint8_t* stage_out = smem + kStages * kStageBytes;   // STAGED: 2 boxes [128 rows][64 bf16], swizzled
+  float* bias_s = reinterpret_cast<float*>(stage_out + gemm_stage_region(EPI));   // [N] (HEADROWS) or the current 128-column slice
+  float2* scw_s = reinterpret_cast<float2*>(bias_s + 1024);   // EXTRAS: [128] (w_ak[n], w_aq[n])
+  float4* wc_s = reinterpret_cast<float4*>(bias_s + 1024);    // LNRES: [128] (wc_0[k], wc_1[k], wc_2[k], wc_3[k]); gamma, beta, cc behind the bias
+  uint64_t* full = reinterpret_cast<uint64_t*>(reinterpret_cast<uint8_t*>(bias_s) + kVecBytes);
   uint64_t* empty = full + kStages;
   uint64_t* acc_full = empty + kStages;        // [kAccs]
   uint64_t* acc_empty = acc_full + kAccs;      // [kAccs]
@@ -134,20 +173,129 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_tc_kernel(const __grid_c
     // ---- epilogue warps: warp w may only touch TMEM lanes [32*(w%4), +32) ----
     const int q = warp & 3;
     const int row = q * 32 + lane;
-    const int et = threadIdx.x - 64;
+    const int eg = (warp - 2) >> 2;            // epilogue group
+    const int et = (threadIdx.x - 64) & 127;   // thread within the group
     if (EXTRAS) scw_s[et] = make_float2(__ldg(ex.sc_w + et), __ldg(ex.sc_w + BN + et));
+    if (HEADROWS) {   // every column block's bias stays resident
+      for (int i = et; i < N; i += 128) bias_s[i] = __ldg(bias + i);   // (every group writes the same values)
+      tc::named_bar_sync(2 + eg, 128);
+    }
+    if (LNRES) {
+      bias_s[BN + et] = __ldg(ex.gamma + et);
+      bias_s[2 * BN + et] = __ldg(ex.beta + et);
+      if (et < 4) bias_s[3 * BN + et] = __ldg(ex.wc + 4 * BN + et);
+      wc_s[et] = make_float4(__ldg(ex.wc + et), __ldg(ex.wc + BN + et), __ldg(ex.wc + 2 * BN + et), __ldg(ex.wc + 3 * BN + et));
+    }
     uint32_t lt = 0;
     int cur_n0 = -1;
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++lt) {
       const int m0 = (tile / tiles_n) * BM, n0 = (tile % tiles_n) * BN;
       const uint32_t ab = lt % kAccs, aph = (lt / kAccs) & 1u;
-      if (n0 != cur_n0) {   // (re)load the bias slice; all epilogue threads pass the barrier below before reading it
+      if (EPG > 1 && (int)(lt % EPG) != eg) continue;
+      if (!HEADROWS && n0 != cur_n0) {   // (re)load the bias slice; all epilogue threads pass the barrier below before reading it
+        static_assert(EPG == 1 || HEADROWS, "the bias slice is shared by the groups");
         tc::named_bar_sync(2, 128);
         bias_s[et] = __ldg(bias + n0 + et);
         cur_n0 = n0;
-        tc::named_bar_sync(2, 128);   // (also publishes scw_s on the first pass)
+        tc::named_bar_sync(2, 128);   // (also publishes scw_s / the LayerNorm vectors on the first pass)
       }
+      const float* bs = bias_s + (HEADROWS ? n0 : 0);
       if (STAGED) __syncwarp();   // this warp's copy-out of the previous tile has finished reading its staged rows
+      if (LNRES) {
+        // ---- v1 = LayerNorm(v0 + acc + b): thread = row (clip, slot) = (m / 16, m % 16); v0 has T <= 16 rows per clip.
+        //      All global traffic is 32 bytes per lane (whole sectors), nothing is staged. ----
+        const int T = ex.T;
+        const int mm = m0 + row, clip = mm >> 4, slot = mm & 15;
+        const bool live = clip < ex.clips;
+        float x[BN];
+        {   // the residual row, in flight while the accumulator is still being produced
+          const float* rp = ex.res + ((int64_t)clip * T + slot) * BN;
+          if (live && slot < T) {
+#pragma unroll
+            for (int k = 0; k < BN; k += 8)
+              tc::ldg256f(rp + k, x[k], x[k + 1], x[k + 2], x[k + 3], x[k + 4], x[k + 5], x[k + 6], x[k + 7]);
+          } else {
+#pragma unroll
+            for (int k = 0; k < BN; ++k) x[k] = 0.f;
+          }
+        }
+        tc::mbar_wait(&acc_full[ab], aph);
+        tc::tc_fence_after();
+#pragma unroll
+        for (int c = 0; c < BN; c += 32) {
+          uint32_t r[32];
+          tc::tmem_ld_32x32(tmem_base + ab * BN + ((uint32_t)(q * 32) << 16) + (uint32_t)c, r);
+          tc::tmem_ld_wait();
+#pragma unroll
+          for (int i = 0; i < 32; ++i) x[c + i] += __uint_as_float(r[i]) + bs[c + i];
+        }
+        tc::tc_fence_before();
+        __syncwarp();
+        if (lane == 0) tc::mbar_arrive(&acc_empty[ab]);
+        float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
+#pragma unroll
+        for (int k = 0; k < BN; k += 4) { s0 += x[k]; s1 += x[k + 1]; s2 += x[k + 2]; s3 += x[k + 3]; }
+        const float mu = ((s0 + s1) + (s2 + s3)) * (1.f / BN);
+        s0 = s1 = s2 = s3 = 0.f;
+#pragma unroll
+        for (int k = 0; k < BN; k += 4) {
+          float d;
+          d = x[k] - mu; s0 = fmaf(d, d, s0);
+          d = x[k + 1] - mu; s1 = fmaf(d, d, s1);
+          d = x[k + 2] - mu; s2 = fmaf(d, d, s2);
+          d = x[k + 3] - mu; s3 = fmaf(d, d, s3);
+        }
+        const float rstd = rsqrtf(((s0 + s1) + (s2 + s3)) * (1.f / BN) + 1e-5f);
+        float cvh0 = bias_s[3 * BN + 0], cvh1 = bias_s[3 * BN + 1], cvh2 = bias_s[3 * BN + 2], cvh3 = bias_s[3 * BN + 3];
+        __nv_bfloat16* orow = reinterpret_cast<__nv_bfloat16*>(out) + (int64_t)mm * BN;
+        uint32_t x_hold[4] = {0u, 0u, 0u, 0u};
+#pragma unroll
+        for (int k8 = 0; k8 < BN; k8 += 8) {
+          uint32_t pk[4];
+#pragma unroll
+          for (int e = 0; e < 8; e += 4) {
+            const float4 gm = *reinterpret_cast<const float4*>(bias_s + BN + k8 + e);
+            const float4 bt = *reinterpret_cast<const float4*>(bias_s + 2 * BN + k8 + e);
+            const float y0 = (x[k8 + e + 0] - mu) * rstd * gm.x + bt.x;
+            const float y1 = (x[k8 + e + 1] - mu) * rstd * gm.y + bt.y;
+            const float y2 = (x[k8 + e + 2] - mu) * rstd * gm.z + bt.z;
+            const float y3 = (x[k8 + e + 3] - mu) * rstd * gm.w + bt.w;
+            const float4 w0 = wc_s[k8 + e + 0], w1 = wc_s[k8 + e + 1], w2 = wc_s[k8 + e + 2], w3 = wc_s[k8 + e + 3];
+            cvh0 = fmaf(y0, w0.x, fmaf(y1, w1.x, fmaf(y2, w2.x, fmaf(y3, w3.x, cvh0))));
+            cvh1 = fmaf(y0, w0.y, fmaf(y1, w1.y, fmaf(y2, w2.y, fmaf(y3, w3.y, cvh1))));
+            cvh2 = fmaf(y0, w0.z, fmaf(y1, w1.z, fmaf(y2, w2.z, fmaf(y3, w3.z, cvh2))));
+            cvh3 = fmaf(y0, w0.w, fmaf(y1, w1.w, fmaf(y2, w2.w, fmaf(y3, w3.w, cvh3))));
+            pk[e >> 1] = tc::pack_bf16(y0, y1);
+            pk[(e >> 1) + 1] = tc::pack_bf16(y2, y3);
+            // rows past T do not enter the temporal mean (fusion.py:401 averages the T real tokens)
+            x[k8 + e + 0] = slot < T ? y0 : 0.f; x[k8 + e + 1] = slot < T ? y1 : 0.f;
+            x[k8 + e + 2] = slot < T ? y2 : 0.f; x[k8 + e + 3] = slot < T ? y3 : 0.f;
+          }
+          // 16 bytes per 8 columns: two consecutive groups make one 32-byte store
+          if ((k8 & 8) == 0) {
+            x_hold[0] = pk[0]; x_hold[1] = pk[1]; x_hold[2] = pk[2]; x_hold[3] = pk[3];
+          } else if (live) {
+            tc::stg256(orow + k8 - 8, x_hold[0], x_hold[1], x_hold[2], x_hold[3], pk[0], pk[1], pk[2], pk[3]);
+          }
+        }
+        if (live) {
+          float* cvp = ex.cv + (int64_t)clip * 64 + slot;
+          cvp[0] = cvh0; cvp[16] = cvh1; cvp[32] = cvh2; cvp[48] = cvh3;
+        }
+        // temporal mean: the 16 rows of a clip are the 16 lanes of a half-warp.  Transpose-reduce: after the step with lane
+        // offset o a lane keeps the half of the columns whose index bit matches its lane bit, so lane l ends with the
+        // complete sums of columns 8·(l % 16) .. +8
+        lnres_fold<64, 8>(x, lane);
+        lnres_fold<32, 4>(x, lane);
+        lnres_fold<16, 2>(x, lane);
+        lnres_fold<8, 1>(x, lane);
+        if (live) {
+          const float invT = 1.f / (float)T;
+          tc::stg256f(ex.pooled + (int64_t)clip * 2 * BN + 8 * (lane & 15), x[0] * invT, x[1] * invT, x[2] * invT, x[3] * invT,
+                      x[4] * invT, x[5] * invT, x[6] * invT, x[7] * invT);
+        }
+        continue;
+      }
       tc::mbar_wait(&acc_full[ab], aph);
       tc::tc_fence_after();
       const int m = m0 + row;
@@ -160,40 +308,62 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_tc_kernel(const __grid_c
         if (EXTRAS) {
 #pragma unroll
           for (int i = 0; i < 32; ++i) {
-            const float y = __uint_as_float(r[i]) + bias_s[c + i];
+            const float y = __uint_as_float(r[i]) + bs[c + i];
             const float2 w = scw_s[c + i];
             sc0 = fmaf(y, w.x, sc0);
             sc1 = fmaf(y, w.y, sc1);
           }
         }
         if (OUT_BF16) {
-          __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(out) + (int64_t)m * out_pitch + n0 + c;
+          // direct rows: 32 columns = 64 bytes = two whole sectors per lane.  HEADROWS: column block n0/128 = 4·which + h sends
+          // row (clip, i) of the tile to row 16h + i of the clip's [64][128] operand (which: out | out2)
+          __nv_bfloat16* o;
+          if (HEADROWS) {
+            const int nt = n0 >> 7;
+            o = reinterpret_cast<__nv_bfloat16*>(nt < 4 ? out : ex.out2) + ((int64_t)(m >> 4) * 64 + 16 * (nt & 3) + (m & 15)) * BN + c;
+          } else {
+            o = reinterpret_cast<__nv_bfloat16*>(out) + (int64_t)m * out_pitch + n0 + c;
+          }
           if (STAGED || m < M) {
+            uint32_t pk[16];
 #pragma unroll
-            for (int v = 0; v < 4; ++v) {
-              uint4 pk;
-              pk.x = tc::pack_bf16(__uint_as_float(r[8 * v + 0]) + bias_s[c + 8 * v + 0], __uint_as_float(r[8 * v + 1]) + bias_s[c + 8 * v + 1]);
-              pk.y = tc::pack_bf16(__uint_as_float(r[8 * v + 2]) + bias_s[c + 8 * v + 2], __uint_as_float(r[8 * v + 3]) + bias_s[c + 8 * v + 3]);
-              pk.z = tc::pack_bf16(__uint_as_float(r[8 * v + 4]) + bias_s[c + 8 * v + 4], __uint_as_float(r[8 * v + 5]) + bias_s[c + 8 * v + 5]);
-              pk.w = tc::pack_bf16(__uint_as_float(r[8 * v + 6]) + bias_s[c + 8 * v + 6], __uint_as_float(r[8 * v + 7]) + bias_s[c + 8 * v + 7]);
-              if (STAGED) {   // 16-byte chunk q of the row -> box q / 8, slot (q % 8) ^ (row % 8)
+            for (int v = 0; v < 16; ++v)
+              pk[v] = tc::pack_bf16(__uint_as_float(r[2 * v]) + bs[c + 2 * v], __uint_as_float(r[2 * v + 1]) + bs[c + 2 * v + 1]);
+            if (STAGED) {   // 16-byte chunk q of the row -> box q / 8, slot (q % 8) ^ (row % 8)
+#pragma unroll
+              for (int v = 0; v < 4; ++v) {
                 const int q8 = (c >> 3) + v;
-                *reinterpret_cast<uint4*>(stage_out + (q8 >> 3) * kStageBox + row * 128 + (((q8 ^ row) & 7) << 4)) = pk;
-              } else {
-                *reinterpret_cast<uint4*>(o + 8 * v) = pk;
+                *reinterpret_cast<uint4*>(stage_out + (q8 >> 3) * kStageBox + row * 128 + (((q8 ^ row) & 7) << 4)) =
+                    make_uint4(pk[4 * v], pk[4 * v + 1], pk[4 * v + 2], pk[4 * v + 3]);
               }
+            } else if ((reinterpret_cast<uintptr_t>(o) & 31) == 0) {
+              tc::stg256(o, pk[0], pk[1], pk[2], pk[3], pk[4], pk[5], pk[6], pk[7]);
+              tc::stg256(o + 16, pk[8], pk[9], pk[10], pk[11], pk[12], pk[13], pk[14], pk[15]);
+            } else {
+#pragma unroll
+              for (int v = 0; v < 4; ++v)
+                *reinterpret_cast<uint4*>(o + 8 * v) = make_uint4(pk[4 * v], pk[4 * v + 1], pk[4 * v + 2], pk[4 * v + 3]);
             }
           }
         } else if (m < M) {
           float* o = reinterpret_cast<float*>(out) + (int64_t)m * out_pitch + n0 + c;
+          if ((reinterpret_cast<uintptr_t>(o) & 31) == 0) {
 #pragma unroll
-          for (int v = 0; v < 8; ++v) {
-            float4 f;
-            f.x = __uint_as_float(r[4 * v + 0]) + bias_s[c + 4 * v + 0];
-            f.y = __uint_as_float(r[4 * v + 1]) + bias_s[c + 4 * v + 1];
-            f.z = __uint_as_float(r[4 * v + 2]) + bias_s[c + 4 * v + 2];
-            f.w = __uint_as_float(r[4 * v + 3]) + bias_s[c + 4 * v + 3];
-            *reinterpret_cast<float4*>(o + 4 * v) = f;
+            for (int v = 0; v < 4; ++v)
+              tc::stg256f(o + 8 * v, __uint_as_float(r[8 * v + 0]) + bs[c + 8 * v + 0], __uint_as_float(r[8 * v + 1]) + bs[c + 8 * v + 1],
+                          __uint_as_float(r[8 * v + 2]) + bs[c + 8 * v + 2], __uint_as_float(r[8 * v + 3]) + bs[c + 8 * v + 3],
+                          __uint_as_float(r[8 * v + 4]) + bs[c + 8 * v + 4], __uint_as_float(r[8 * v + 5]) + bs[c + 8 * v + 5],
+                          __uint_as_float(r[8 * v + 6]) + bs[c + 8 * v + 6], __uint_as_float(r[8 * v + 7]) + bs[c + 8 * v + 7]);
+          } else {
+#pragma unroll
+            for (int v = 0; v < 8; ++v) {
+              float4 f;
+              f.x = __uint_as_float(r[4 * v + 0]) + bs[c + 4 * v + 0];
+              f.y = __uint_as_float(r[4 * v + 1]) + bs[c + 4 * v + 1];
+              f.z = __uint_as_float(r[4 * v + 2]) + bs[c + 4 * v + 2];
+              f.w = __uint_as_float(r[4 * v + 3]) + bs[c + 4 * v + 3];
+              *reinterpret_cast<float4*>(o + 4 * v) = f;
+            }
           }
         }
       }
@@ -211,12 +381,14 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_tc_kernel(const __grid_c
         // were staged swizzled (conflict-free 16-byte writes); they leave in global order, 512 contiguous bytes per access.
         __syncwarp();
         const int wrow0 = q * 32, mrow0 = m0 + wrow0;
-        uint4* gout = reinterpret_cast<uint4*>(reinterpret_cast<__nv_bfloat16*>(out) + (int64_t)mrow0 * BN);
+        {
+          uint4* gout = reinterpret_cast<uint4*>(reinterpret_cast<__nv_bfloat16*>(out) + (int64_t)mrow0 * BN);
 #pragma unroll 4
-        for (int i = 0; i < 16; ++i) {
-          const int lin = i * 32 + lane, rr = lin >> 4, q8 = lin & 15;   // row in the warp's block, 16-byte chunk of the row
-          if (mrow0 + rr < M)
-            gout[lin] = *reinterpret_cast<const uint4*>(stage_out + (q8 >> 3) * kStageBox + (wrow0 + rr) * 128 + (((q8 ^ rr) & 7) << 4));
+          for (int i = 0; i < 16; ++i) {
+            const int lin = i * 32 + lane, rr = lin >> 4, q8 = lin & 15;   // row in the warp's block, 16-byte chunk of the row
+            if (mrow0 + rr < M)
+              gout[lin] = *reinterpret_cast<const uint4*>(stage_out + (q8 >> 3) * kStageBox + (wrow0 + rr) * 128 + (((q8 ^ rr) & 7) << 4));
+          }
         }
         if (EXTRAS) {   // lane owns columns 4*lane .. 4*lane+3: sum them over the warp's rows of each clip present
           const int L = ex.seg_len;
@@ -259,18 +431,19 @@ EncodeTiledFn encode_tiled_fn() {
   return fn;
 }
 
-template <bool OUT_BF16, bool STAGED, bool EXTRAS>
+template <int EPI, int STAGES = kStagesDefault, int EPG = 1>
 int launch_gemm_tc(cudaStream_t st, const CUtensorMap& tmA, const CUtensorMap& tmB, const float* bias, void* out, int64_t pitch,
                    int M, int N, int K, const GemmExtras& ex) {
-  const int smem = gemm_smem_bytes(STAGED, (int)pitch);
-  static int configured = 0;
-  if (smem > configured) {
-    XF_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<OUT_BF16, STAGED, EXTRAS>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-    configured = smem;
+  constexpr int smem = gemm_smem_bytes(EPI, STAGES);
+  static_assert(smem <= 227 * 1024, "projection GEMM: shared memory");
+  static bool configured = false;
+  if (!configured) {
+    XF_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<EPI, STAGES, EPG>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    configured = true;
   }
   const int tiles = ((M + BM - 1) / BM) * (N / BN);
   const int grid = tiles < num_sms() ? tiles : num_sms();
-  gemm_tc_kernel<OUT_BF16, STAGED, EXTRAS><<<grid, kGemmThreads, smem, st>>>(tmA, tmB, bias, out, pitch, M, N, K, ex);
+  gemm_tc_kernel<EPI, STAGES, EPG><<<grid, gemm_threads(EPG), smem, st>>>(tmA, tmB, bias, out, pitch, M, N, K, ex);
   count_launch();
   XF_LAUNCH_CHECK();
   return XATTN_OK;
@@ -302,7 +475,8 @@ int gemm_tc_bf16(cudaStream_t st, const void* X, const void* W, const float* bia
   if (extras && !(staged && seg_len > 0 && M % seg_len == 0 &&
                   (seg_len + 30) / 32 + 1 <= kColsumSlots && seg_len <= kTokPitch))
     XF_FAIL(XATTN_ERR_SHAPE, "projection GEMM extras need dense bf16 output with N == 128 and rows in clips of <= 160 tokens");
-  GemmExtras ex{sc_w, tok, colsum, seg_len};
+  GemmExtras ex{};
+  ex.sc_w = sc_w; ex.tok = tok; ex.colsum = colsum; ex.seg_len = seg_len;
   if (N % BN != 0 || K % BK != 0)
     XF_FAIL(XATTN_ERR_SHAPE, "tcgen05 projection GEMM needs N %% 128 == 0 and K %% 64 == 0 (N=%d K=%d)", N, K);
   if (out_pitch < N || (out_bf16 && out_pitch % 8 != 0) || (!out_bf16 && out_pitch % 4 != 0))
@@ -310,10 +484,33 @@ int gemm_tc_bf16(cudaStream_t st, const void* X, const void* W, const float* bia
   alignas(64) CUtensorMap tmA, tmB;
   XF_TRY(make_tmap_bf16_2d(&tmA, X, M, K, BM, BK));
   XF_TRY(make_tmap_bf16_2d(&tmB, W, N, K, BN, BK));
-  if (extras) return launch_gemm_tc<true, true, true>(st, tmA, tmB, bias, out, out_pitch, M, N, K, ex);
-  if (staged) return launch_gemm_tc<true, true, false>(st, tmA, tmB, bias, out, out_pitch, M, N, K, ex);
-  if (out_bf16) return launch_gemm_tc<true, false, false>(st, tmA, tmB, bias, out, out_pitch, M, N, K, ex);
-  return launch_gemm_tc<false, false, false>(st, tmA, tmB, bias, out, out_pitch, M, N, K, ex);
+  if (extras) return launch_gemm_tc<EPI_EXTRAS>(st, tmA, tmB, bias, out, out_pitch, M, N, K, ex);
+  if (staged) return launch_gemm_tc<EPI_STAGED>(st, tmA, tmB, bias, out, out_pitch, M, N, K, ex);
+  if (out_bf16) return launch_gemm_tc<EPI_BF16>(st, tmA, tmB, bias, out, out_pitch, M, N, K, ex);
+  return launch_gemm_tc<EPI_F32>(st, tmA, tmB, bias, out, out_pitch, M, N, K, ex);
+}
+
+int gemm_tc_video_mix(cudaStream_t st, const void* U, const void* G, const float* bias, const float* v0, const float* gamma,
+                      const float* beta, const float* wc, void* v1, float* cv, float* pooled, int clips, int T) {
+  if (clips <= 0) return XATTN_OK;
+  const int M = clips * 16;
+  GemmExtras ex{};
+  ex.res = v0; ex.gamma = gamma; ex.beta = beta; ex.wc = wc; ex.cv = cv; ex.pooled = pooled; ex.T = T; ex.clips = clips;
+  alignas(64) CUtensorMap tmA, tmB;
+  XF_TRY(make_tmap_bf16_2d(&tmA, U, M, 4 * BN, BM, BK));
+  XF_TRY(make_tmap_bf16_2d(&tmB, G, BN, 4 * BN, BN, BK));
+  return launch_gemm_tc<EPI_LNRES, 6, 1>(st, tmA, tmB, bias, v1, BN, M, BN, 4 * BN, ex);
+}
+
+int gemm_tc_video_kv(cudaStream_t st, const void* v1, const void* F, const float* bias, void* kt, void* vt, int clips) {
+  if (clips <= 0) return XATTN_OK;
+  const int M = clips * 16;
+  GemmExtras ex{};
+  ex.out2 = vt;
+  alignas(64) CUtensorMap tmA, tmB;
+  XF_TRY(make_tmap_bf16_2d(&tmA, v1, M, BN, BM, BK));
+  XF_TRY(make_tmap_bf16_2d(&tmB, F, 8 * BN, BN, BN, BK));
+  return launch_gemm_tc<EPI_HEADROWS, 5, 2>(st, tmA, tmB, bias, kt, BN, M, 8 * BN, BN, ex);
 }
 
 }  // namespace xf

@@ -13,6 +13,13 @@ constexpr int kColsumSlots = 6;
 constexpr int kTokPitch = 160;   // floats per clip in each tok plane
 int gemm_tc_bf16(cudaStream_t st, const void* X, const void* W, const float* bias, void* out, bool out_bf16, int64_t out_pitch,
                  int M, int N, int K, const float* sc_w = nullptr, float* tok = nullptr, float* colsum = nullptr, int seg_len = 0);
+// Video-side update as two GEMMs over weights folded at pack time (bf16_pack.cu), rows = (clip, token slot), 16 slots per clip:
+//   video_mix: v1 = LayerNorm(v0 + U[16·clips, 512]·G[128, 512]^T + bias) as bf16 [16·clips, 128]  (fusion.py:394-395);
+//              pooled[clip][0..128) = mean over the T real slots (:401); cv[clip][16h + i] = v1_i·wc[h] + wc[512 + h]
+//   video_kv : [Kt | Vt][clip][16h + i][:] = v1[16·clip + i]·F[128·(4·which + h) .., 128]^T + bias   (F: [1024, 128])
+int gemm_tc_video_mix(cudaStream_t st, const void* U, const void* G, const float* bias, const float* v0, const float* gamma,
+                      const float* beta, const float* wc, void* v1, float* cv, float* pooled, int clips, int T);
+int gemm_tc_video_kv(cudaStream_t st, const void* v1, const void* F, const float* bias, void* kt, void* vt, int clips);
 // 2D bf16 tensor map with SWIZZLE_128B boxes: `cols` contiguous elements per row, rows `pitch` elements apart (0 = cols).
 int make_tmap_bf16_2d(void* tmap_out, const void* base, int64_t rows, int64_t cols, int box_rows, int box_cols, int64_t pitch = 0);
 }  // namespace xf

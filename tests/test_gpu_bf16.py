@@ -61,7 +61,7 @@ def _ws_views(ws, B, T, Ta):
             ("u", torch.bfloat16, (B, 64, E)), ("tok", torch.float32, (2, B, 160)), ("acol", torch.float32, (B, 6, E)),
             ("pc", torch.float32, (B, 4)),
             ("kt", torch.bfloat16, (B, 64, EP)), ("vt", torch.bfloat16, (B, 64, EP)), ("cv", torch.float32, (B, 64)),
-            ("pooled", torch.float32, (B, 2 * E))]
+            ("pooled", torch.float32, (B, 2 * E)), ("poolp", torch.float32, (B, 8, E)), ("v1", torch.bfloat16, (B * 16, E))]
     out, off = {}, 0
     for name, dt, shape in spec:
         n = int(np.prod(shape)) * (4 if dt == torch.float32 else 2)
@@ -86,17 +86,10 @@ def _stage_report(m, xvb, xab, head, prior, dev):
     rep["a0"] = np.abs(w["a0"][:, :128].reshape(B, Ta, 128) - taps["a"]).max()
     _, p1 = xattn_oracle.multihead_attention(sd, "v2a_attn.", taps["v"], taps["a"], 4, taps["v2a_bias"], return_probs=True)
     u_ref = np.einsum("bhls,bse->bhle", p1, taps["a"])                       # U_h = P_h · a0
-    # U is stored in mma A-fragment order [clip][head][ks][lane][reg] x (2 bf16): lane = 4g+t, reg r -> row g+8(r&1),
-    # cols 16ks + 2t + 8(r>>1) + {0,1}
-    f = w["u"].reshape(B, 4, 8, 32, 4, 2).transpose(0, 1, 3, 2, 4, 5)
-    u_got = np.zeros((B, 4, 16, 128), dtype=np.float32)
-    for lane in range(32):
-        g_, t_ = lane >> 2, lane & 3
-        for ks in range(8):
-            for r in range(4):
-                col = 16 * ks + 2 * t_ + 8 * (r >> 1)
-                u_got[:, :, g_ + 8 * (r & 1), col:col + 2] = f[:, :, lane, ks, r, :]
+    # U is stored row-major as [16*clip + i][128*h + e] (the A operand of the video_mix GEMM)
+    u_got = w["u"].reshape(B, 16, 4, 128).transpose(0, 2, 1, 3)
     rep["u"] = np.abs(u_got[:, :, :T] - u_ref).max()
+    rep["v1"] = np.abs(w["v1"].reshape(B, 16, 128)[:, :T] - taps["v_new"]).max()
     rep["pooled_v"] = np.abs(w["pooled"][:, :128] - taps["v_emb"]).max()
     rep["pooled_a"] = np.abs(w["pooled"][:, 128:] - taps["a_emb"]).max()
     rep["logits"] = np.abs(logits.cpu().numpy() - ref).max()
