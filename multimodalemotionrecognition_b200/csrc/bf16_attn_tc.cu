@@ -346,8 +346,8 @@ __global__ void __launch_bounds__(kV2AThreads, 1) v2a_tc_kernel(const __grid_con
 //   warp 0: TMA producer   warp 1: MMA issuer, polls for whichever of {next S, next O} is ready
 //   warps 2-9 / 10-17: two softmax+LayerNorm groups alternating row tiles, each with its own 256-column TMEM buffer.
 //   Inside a group, warps w and w+4 share a TMEM sub-partition (the same 32 rows) and split the work in halves: two of
-//   the four heads in the softmax, 64 of the 128 columns in the LayerNorm; the row statistics meet in the dead half of
-//   the score columns.
+//   the four heads in the softmax, 64 of the 128 columns in the LayerNorm; the row statistics meet in two output columns
+//   the thread has already loaded.
 constexpr int kA2VThreads = 64 + 512;
 constexpr int kA2VHalf = 2 * kA0Box;                         // a0 stage layout: [feature half][clip][160 rows][128 B]
 constexpr int kKvHalf = 2 * kBox;                            // Kt / Vt layout:  [feature half][clip][64 rows][128 B]
@@ -455,7 +455,7 @@ __global__ void __launch_bounds__(kA2VThreads, 1) a2v_tc_kernel(const __grid_con
       auto s_ready = [&](uint32_t n) {
         const uint32_t it = n / 3, t = n % 3, b = n & 1u;
         if (t == 0 && !(tc::mbar_test_wait(kt_full, it & 1u) && tc::mbar_test_wait(&a0_full[it & 1u], (it >> 1) & 1u))) return false;
-        return n < 2 || tc::mbar_test_wait(&o_empty[b], ((n - 2) >> 1) & 1u);   // the buffer's previous tile has been drained
+        return n < 2 || tc::mbar_test_wait(&o_full[b], ((n - 2) >> 1) & 1u);   // the buffer's previous P has been consumed
       };
       auto issue_s = [&](uint32_t n) {
         const uint32_t it = n / 3, t = n % 3, b = n & 1u, s = it & 1u;
@@ -476,6 +476,7 @@ __global__ void __launch_bounds__(kA2VThreads, 1) a2v_tc_kernel(const __grid_con
       auto o_ready = [&](uint32_t n) {
         const uint32_t it = n / 3, t = n % 3, b = n & 1u;
         if (t == 0 && !tc::mbar_test_wait(vt_full, it & 1u)) return false;
+        if (n >= 2 && !tc::mbar_test_wait(&o_empty[b], ((n - 2) >> 1) & 1u)) return false;   // the buffer's previous O is in registers
         return tc::mbar_test_wait(&p_full[b], (n >> 1) & 1u);
       };
       auto issue_o = [&](uint32_t n) {
@@ -484,21 +485,25 @@ __global__ void __launch_bounds__(kA2VThreads, 1) a2v_tc_kernel(const __grid_con
         tc::tc_fence_after();
         const uint64_t db0 = tc::umma_desc_sw128(tc::smem_u32(vts), kKvHalf, 1024);   // MN-major: K = (clip, head, key) rows
         const uint32_t d = tmem + b * 256 + 128, pa = tmem + b * 256;
+        // K order of P: step ks = 4·(head pair) + 2·clip + (head in pair), 16 keys each — so that a thread's probabilities
+        // and zeros land inside the score columns it read itself (see the softmax below); Vt rows are (clip, head, key)
 #pragma unroll
-        for (int ks = 0; ks < 8; ++ks)
-          tc::umma_bf16_ts(d, pa + (uint32_t)(ks * 8), db0 + (uint64_t)((ks * 16 * 128) >> 4), t == 2 ? idesc64o : idesc128o, ks != 0);
+        for (int ks = 0; ks < 8; ++ks) {
+          const int vrow = 64 * ((ks >> 1) & 1) + 32 * (ks >> 2) + 16 * (ks & 1);
+          tc::umma_bf16_ts(d, pa + (uint32_t)(ks * 8), db0 + (uint64_t)((vrow * 128) >> 4), t == 2 ? idesc64o : idesc128o, ks != 0);
+        }
         tc::umma_commit(&o_full[b]);
         if (t == 2) tc::umma_commit(vt_empty);
       };
-      uint32_t ns = 0, no = 0;   // next score product / next output product to issue (ns runs at most one tile ahead of no + 1)
+      uint32_t ns = 0, no = 0;   // next score product / next output product to issue
       while (no < n_tiles) {
         bool progressed = false;
-        if (ns < n_tiles && ns <= no + 1 && s_ready(ns)) {
-          issue_s(ns++);
-          progressed = true;
-        }
         if (no < ns && o_ready(no)) {
           issue_o(no++);
+          progressed = true;
+        }
+        if (ns < n_tiles && ns <= no + 2 && s_ready(ns)) {
+          issue_s(ns++);
           progressed = true;
         }
         if (!progressed) __nanosleep(20);
@@ -535,8 +540,11 @@ __global__ void __launch_bounds__(kA2VThreads, 1) a2v_tc_kernel(const __grid_con
     };
     float qa_n, pk_n;
     row_consts(grp, qa_n, pk_n);
-    for (uint32_t n = grp; n < n_tiles; n += 2) {
-      const uint32_t it = n / 3, t = n % 3, s = it & 1u;
+    // Per tile: phase A (scores -> probabilities) and phase B (output -> LayerNorm -> pooled partial).  The kernel is bound by
+    // instruction issue (67% of the issue slots), not by the tensor-core round trips: running B one group iteration late, behind
+    // A of the group's next tile, was measured and is slower (113 vs 107 us at B=4096).
+    auto phase_a = [&](uint32_t n) {
+      const uint32_t it = n / 3, s = it & 1u;
       int R, ci, c;
       bool valid;
       row_of(n, R, ci, c, valid);
@@ -581,16 +589,24 @@ __global__ void __launch_bounds__(kA2VThreads, 1) a2v_tc_kernel(const __grid_con
         uint32_t z[16];
 #pragma unroll
         for (int i = 0; i < 16; ++i) z[i] = 0u;
-        tc::tmem_st_32x32_x16(tbuf + (uint32_t)(32 * ci + 16 * hf), pk2);
-        tc::tmem_st_32x32_x16(tbuf + (uint32_t)(32 * (ci ^ 1) + 16 * hf), z);
+        // P columns [32 hf, +32) = (clip 0 | clip 1) x (2 heads x 16 keys as bf16x2): for a clip-0 row exactly the score columns
+        // this thread just read, for a clip-1 row clip-0 score columns nobody reads — the partner warp's scores stay intact
+        tc::tmem_st_32x32_x16(tbuf + (uint32_t)(32 * hf + 16 * ci), pk2);
+        tc::tmem_st_32x32_x16(tbuf + (uint32_t)(32 * hf + 16 * (ci ^ 1)), z);
         tc::tmem_st_wait();
         tc::tc_fence_before();
         tc::mbar_arrive(&p_full[grp]);
         if (tracer) trace_mark(a.trace, 4, n);   // worker: P written
       }
       row_consts(n + 2, qa_n, pk_n);           // next tile's row constants: in flight during the LayerNorm below
+    };
+    auto phase_b = [&](uint32_t n) {
       // ---- a1 = LayerNorm(a0 + out [+ bo2, inside out]) (fusion.py:399) accumulated into the temporal mean (:402);
       //      this thread: columns [64 hf, 64 hf + 64) of its row ----
+      const uint32_t it = n / 3, t = n % 3, s = it & 1u;
+      int R, ci, c;
+      bool valid;
+      row_of(n, R, ci, c, valid);
       constexpr int HC = BE / 2;
       float x[HC];
       const uint8_t* arow = a0s + s * kA0Stage + hf * kA2VHalf + R * 128;
@@ -624,24 +640,25 @@ __global__ void __launch_bounds__(kA2VThreads, 1) a2v_tc_kernel(const __grid_con
           sq1 = fmaf(x[col + 1], x[col + 1], sq1);
         }
       }
-      // the two halves of the row meet: (sum, sum of squares) through the dead upper half of the score columns
+      // the two halves of the row meet: (sum, sum of squares) through the first two of the output columns this thread has
+      // just loaded (its own half: the partner never reads them, and the buffer is not refilled before o_empty below)
       float su = sum0 + sum1, sq = sq0 + sq1;
       {
-        const uint32_t tx = tbuf + 64u;
-        tc::tmem_st_32x32_x1(tx + (uint32_t)(2 * hf), __float_as_uint(su));
-        tc::tmem_st_32x32_x1(tx + (uint32_t)(2 * hf + 1), __float_as_uint(sq));
+        const uint32_t tx = tbuf + 128u;
+        tc::tmem_st_32x32_x1(tx + (uint32_t)(64 * hf), __float_as_uint(su));
+        tc::tmem_st_32x32_x1(tx + (uint32_t)(64 * hf + 1), __float_as_uint(sq));
         tc::tmem_st_wait();
         tc::tc_fence_before();
         tc::named_bar_sync(pair_bar, 64);
         tc::tc_fence_after();
-        const uint32_t psu = tc::tmem_ld_32x32_x1(tx + (uint32_t)(2 * (hf ^ 1)));
-        const uint32_t psq = tc::tmem_ld_32x32_x1(tx + (uint32_t)(2 * (hf ^ 1) + 1));
+        const uint32_t psu = tc::tmem_ld_32x32_x1(tx + (uint32_t)(64 * (hf ^ 1)));
+        const uint32_t psq = tc::tmem_ld_32x32_x1(tx + (uint32_t)(64 * (hf ^ 1) + 1));
         tc::tmem_ld_wait();
         su += __uint_as_float(psu);
         sq += __uint_as_float(psq);
       }
       tc::tc_fence_before();
-      tc::mbar_arrive(&o_empty[grp]);          // O, P and the exchange columns are done with: the buffer can be refilled
+      tc::mbar_arrive(&o_empty[grp]);          // O and the exchange columns are done with: the next output product may land
       tc::mbar_arrive(&a0_empty[s]);           // and so is this row's residual
       if (tracer) trace_mark(a.trace, 6, n);   // worker: O + residual in registers
       const float mu = su * (1.f / BE);
@@ -672,6 +689,10 @@ __global__ void __launch_bounds__(kA2VThreads, 1) a2v_tc_kernel(const __grid_con
           *reinterpret_cast<float2*>(a.poolp + ((int64_t)c * kPoolSlots + slot) * BE + HC * hf + base) = make_float2(x[0], x[1]);
       }
       if (tracer) trace_mark(a.trace, 7, n);   // worker: tile done
+    };
+    for (uint32_t n = grp; n < n_tiles; n += 2) {
+      phase_a(n);
+      phase_b(n);
     }
   }
   tc::tc_fence_before();

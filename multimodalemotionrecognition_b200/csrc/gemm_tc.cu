@@ -24,6 +24,8 @@
 //                (Kt | Vt of a2v_attn: N = 1024, column block h' = 4·which + h)
 #include <cuda.h>
 
+#include <cstdlib>
+
 #include "common.cuh"
 #include "gemm_tc.cuh"
 #include "tc.cuh"
@@ -46,7 +48,10 @@ enum { EPI_F32 = 0, EPI_BF16 = 1, EPI_STAGED = 2, EPI_EXTRAS = 3, EPI_LNRES = 4,
 //   leaves in global order.  EPI_EXTRAS: EPI_STAGED + token scores + column sums.
 
 __host__ __device__ constexpr int gemm_stage_region(int epi) {
-  return (epi == EPI_STAGED || epi == EPI_EXTRAS) ? 2 * kStageBox : 0;
+  return (epi == EPI_STAGED || epi == EPI_EXTRAS) ? 2 * kStageBox   // one bf16 tile
+         : epi == EPI_HEADROWS                        ? 4 * kStageBox   // one bf16 tile per epilogue group
+         : epi == EPI_LNRES                           ? 8192            // statistics / c_hi exchange between the column halves
+                                                      : 0;
 }
 __host__ __device__ constexpr int gemm_smem_bytes(int epi, int stages) {
   return stages * kStageBytes + gemm_stage_region(epi) + kVecBytes + kBarBytes + 1024;
@@ -68,8 +73,8 @@ struct GemmExtras {
 };
 
 // One step of the transpose-reduce over lanes: x[0..N) (+)= the partner's other half; N values remain.
-template <int N, int O>
-__device__ __forceinline__ void lnres_fold(float (&x)[BN], int lane) {
+template <int N, int O, int LEN>
+__device__ __forceinline__ void lnres_fold(float (&x)[LEN], int lane) {
   const bool up = (lane & O) != 0;
 #pragma unroll
   for (int k = 0; k < N; ++k) {
@@ -84,10 +89,12 @@ __device__ __forceinline__ void lnres_fold(float (&x)[BN], int lane) {
 template <int EPI, int kStages, int EPG>
 __global__ void __launch_bounds__(gemm_threads(EPG), 1) gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA,
                                                                   const __grid_constant__ CUtensorMap tmB,
+                                                                  const __grid_constant__ CUtensorMap tmO,
+                                                                  const __grid_constant__ CUtensorMap tmO2,
                                                                   const float* __restrict__ bias, void* __restrict__ out,
                                                                   int64_t out_pitch, int M, int N, int K, GemmExtras ex) {
   constexpr bool OUT_BF16 = EPI != EPI_F32 && EPI != EPI_LNRES;
-  constexpr bool STAGED = EPI == EPI_STAGED || EPI == EPI_EXTRAS;
+  constexpr bool STAGED = EPI == EPI_STAGED || EPI == EPI_EXTRAS || EPI == EPI_HEADROWS;   // the tile is written to smem first
   constexpr bool EXTRAS = EPI == EPI_EXTRAS;
   constexpr bool HEADROWS = EPI == EPI_HEADROWS;
   constexpr bool LNRES = EPI == EPI_LNRES;
@@ -118,7 +125,7 @@ __global__ void __launch_bounds__(gemm_threads(EPG), 1) gemm_tc_kernel(const __g
     }
     for (int b = 0; b < kAccs; ++b) {
       tc::mbar_init(&acc_full[b], 1);
-      tc::mbar_init(&acc_empty[b], 4);   // one arrival per epilogue warp
+      tc::mbar_init(&acc_empty[b], LNRES ? 4 * EPG : 4);   // one arrival per epilogue warp that reads it
     }
     tc::fence_barrier_init();
   }
@@ -180,87 +187,96 @@ __global__ void __launch_bounds__(gemm_threads(EPG), 1) gemm_tc_kernel(const __g
       for (int i = et; i < N; i += 128) bias_s[i] = __ldg(bias + i);   // (every group writes the same values)
       tc::named_bar_sync(2 + eg, 128);
     }
-    if (LNRES) {
+    if (LNRES) {   // (both column halves write the same values; each waits for its own copy)
+      bias_s[et] = __ldg(bias + et);
       bias_s[BN + et] = __ldg(ex.gamma + et);
       bias_s[2 * BN + et] = __ldg(ex.beta + et);
       if (et < 4) bias_s[3 * BN + et] = __ldg(ex.wc + 4 * BN + et);
       wc_s[et] = make_float4(__ldg(ex.wc + et), __ldg(ex.wc + BN + et), __ldg(ex.wc + 2 * BN + et), __ldg(ex.wc + 3 * BN + et));
+      tc::named_bar_sync(2 + eg, 128);
     }
+    if (HEADROWS) stage_out += eg * 2 * kStageBox;
     uint32_t lt = 0;
     int cur_n0 = -1;
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++lt) {
       const int m0 = (tile / tiles_n) * BM, n0 = (tile % tiles_n) * BN;
       const uint32_t ab = lt % kAccs, aph = (lt / kAccs) & 1u;
-      if (EPG > 1 && (int)(lt % EPG) != eg) continue;
-      if (!HEADROWS && n0 != cur_n0) {   // (re)load the bias slice; all epilogue threads pass the barrier below before reading it
-        static_assert(EPG == 1 || HEADROWS, "the bias slice is shared by the groups");
+      if (!LNRES && EPG > 1 && (int)(lt % EPG) != eg) continue;   // (LNRES: the groups split the columns of every tile)
+      if (!HEADROWS && !LNRES && n0 != cur_n0) {   // (re)load the bias slice; all epilogue threads pass the barrier below before reading it
+        static_assert(EPG == 1 || HEADROWS || LNRES, "the bias slice is shared by the groups");
         tc::named_bar_sync(2, 128);
         bias_s[et] = __ldg(bias + n0 + et);
         cur_n0 = n0;
         tc::named_bar_sync(2, 128);   // (also publishes scw_s / the LayerNorm vectors on the first pass)
       }
       const float* bs = bias_s + (HEADROWS ? n0 : 0);
-      if (STAGED) __syncwarp();   // this warp's copy-out of the previous tile has finished reading its staged rows
+      if (STAGED && !HEADROWS) __syncwarp();   // this warp's copy-out of the previous tile has finished reading its staged rows
+      if (HEADROWS) {   // the group's previous tile has left the staging buffer
+        if (et == 0) tc::bulk_store_wait_read();
+        tc::named_bar_sync(2 + eg, 128);
+      }
       if (LNRES) {
-        // ---- v1 = LayerNorm(v0 + acc + b): thread = row (clip, slot) = (m / 16, m % 16); v0 has T <= 16 rows per clip.
-        //      All global traffic is 32 bytes per lane (whole sectors), nothing is staged. ----
+        // ---- v1 = LayerNorm(v0 + acc + b): a row (clip, slot) = (m / 16, m % 16) belongs to the two threads with this lane in
+        //      the warps of its TMEM sub-partition, group eg owning columns [64·eg, +64); v0 has T <= 16 rows per clip.
+        //      All global traffic is 32 bytes per lane (whole sectors); only the statistics and c_hi cross between the halves. ----
+        static_assert(!LNRES || EPG == 2, "LNRES: two column halves");
+        constexpr int HC = BN / 2;
         const int T = ex.T;
-        const int mm = m0 + row, clip = mm >> 4, slot = mm & 15;
+        const int mm = m0 + row, clip = mm >> 4, slot = mm & 15, c0 = HC * eg;
         const bool live = clip < ex.clips;
-        float x[BN];
-        {   // the residual row, in flight while the accumulator is still being produced
-          const float* rp = ex.res + ((int64_t)clip * T + slot) * BN;
+        float2* xs = reinterpret_cast<float2*>(stage_out) + (lt & 1u) * 2 * BM;          // [parity][half][row] (sum, sum of squares)
+        float4* xc = reinterpret_cast<float4*>(stage_out + 4096) + (lt & 1u) * BM;       // [parity][row] c_hi partials of half 1
+        float x[HC];
+        {   // the residual half row, in flight while the accumulator is still being produced
+          const float* rp = ex.res + ((int64_t)clip * T + slot) * BN + c0;
           if (live && slot < T) {
 #pragma unroll
-            for (int k = 0; k < BN; k += 8)
+            for (int k = 0; k < HC; k += 8)
               tc::ldg256f(rp + k, x[k], x[k + 1], x[k + 2], x[k + 3], x[k + 4], x[k + 5], x[k + 6], x[k + 7]);
           } else {
 #pragma unroll
-            for (int k = 0; k < BN; ++k) x[k] = 0.f;
+            for (int k = 0; k < HC; ++k) x[k] = 0.f;
           }
         }
         tc::mbar_wait(&acc_full[ab], aph);
         tc::tc_fence_after();
 #pragma unroll
-        for (int c = 0; c < BN; c += 32) {
+        for (int c = 0; c < HC; c += 32) {
           uint32_t r[32];
-          tc::tmem_ld_32x32(tmem_base + ab * BN + ((uint32_t)(q * 32) << 16) + (uint32_t)c, r);
+          tc::tmem_ld_32x32(tmem_base + ab * BN + ((uint32_t)(q * 32) << 16) + (uint32_t)(c0 + c), r);
           tc::tmem_ld_wait();
 #pragma unroll
-          for (int i = 0; i < 32; ++i) x[c + i] += __uint_as_float(r[i]) + bs[c + i];
+          for (int i = 0; i < 32; ++i) x[c + i] += __uint_as_float(r[i]) + bs[c0 + c + i];
         }
         tc::tc_fence_before();
         __syncwarp();
         if (lane == 0) tc::mbar_arrive(&acc_empty[ab]);
-        float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
+        float s0 = 0.f, s1 = 0.f, q0 = 0.f, q1 = 0.f;
 #pragma unroll
-        for (int k = 0; k < BN; k += 4) { s0 += x[k]; s1 += x[k + 1]; s2 += x[k + 2]; s3 += x[k + 3]; }
-        const float mu = ((s0 + s1) + (s2 + s3)) * (1.f / BN);
-        s0 = s1 = s2 = s3 = 0.f;
-#pragma unroll
-        for (int k = 0; k < BN; k += 4) {
-          float d;
-          d = x[k] - mu; s0 = fmaf(d, d, s0);
-          d = x[k + 1] - mu; s1 = fmaf(d, d, s1);
-          d = x[k + 2] - mu; s2 = fmaf(d, d, s2);
-          d = x[k + 3] - mu; s3 = fmaf(d, d, s3);
+        for (int k = 0; k < HC; k += 2) {
+          s0 += x[k]; s1 += x[k + 1];
+          q0 = fmaf(x[k], x[k], q0); q1 = fmaf(x[k + 1], x[k + 1], q1);
         }
-        const float rstd = rsqrtf(((s0 + s1) + (s2 + s3)) * (1.f / BN) + 1e-5f);
-        float cvh0 = bias_s[3 * BN + 0], cvh1 = bias_s[3 * BN + 1], cvh2 = bias_s[3 * BN + 2], cvh3 = bias_s[3 * BN + 3];
-        __nv_bfloat16* orow = reinterpret_cast<__nv_bfloat16*>(out) + (int64_t)mm * BN;
-        uint32_t x_hold[4] = {0u, 0u, 0u, 0u};
+        xs[eg * BM + row] = make_float2(s0 + s1, q0 + q1);
+        tc::named_bar_sync(4 + q, 64);   // the two warps of this sub-partition
+        const float2 oth = xs[(eg ^ 1) * BM + row];
+        const float mu = ((s0 + s1) + oth.x) * (1.f / BN);
+        const float rstd = rsqrtf(fmaxf(((q0 + q1) + oth.y) * (1.f / BN) - mu * mu, 0.f) + 1e-5f);
+        float cvh0 = 0.f, cvh1 = 0.f, cvh2 = 0.f, cvh3 = 0.f;
+        __nv_bfloat16* orow = reinterpret_cast<__nv_bfloat16*>(out) + (int64_t)mm * BN + c0;
 #pragma unroll
-        for (int k8 = 0; k8 < BN; k8 += 8) {
-          uint32_t pk[4];
+        for (int k16 = 0; k16 < HC; k16 += 16) {
+          uint32_t pk[8];
 #pragma unroll
-          for (int e = 0; e < 8; e += 4) {
-            const float4 gm = *reinterpret_cast<const float4*>(bias_s + BN + k8 + e);
-            const float4 bt = *reinterpret_cast<const float4*>(bias_s + 2 * BN + k8 + e);
-            const float y0 = (x[k8 + e + 0] - mu) * rstd * gm.x + bt.x;
-            const float y1 = (x[k8 + e + 1] - mu) * rstd * gm.y + bt.y;
-            const float y2 = (x[k8 + e + 2] - mu) * rstd * gm.z + bt.z;
-            const float y3 = (x[k8 + e + 3] - mu) * rstd * gm.w + bt.w;
-            const float4 w0 = wc_s[k8 + e + 0], w1 = wc_s[k8 + e + 1], w2 = wc_s[k8 + e + 2], w3 = wc_s[k8 + e + 3];
+          for (int e = 0; e < 16; e += 4) {
+            const int k = k16 + e;
+            const float4 gm = *reinterpret_cast<const float4*>(bias_s + BN + c0 + k);
+            const float4 bt = *reinterpret_cast<const float4*>(bias_s + 2 * BN + c0 + k);
+            const float y0 = (x[k + 0] - mu) * rstd * gm.x + bt.x;
+            const float y1 = (x[k + 1] - mu) * rstd * gm.y + bt.y;
+            const float y2 = (x[k + 2] - mu) * rstd * gm.z + bt.z;
+            const float y3 = (x[k + 3] - mu) * rstd * gm.w + bt.w;
+            const float4 w0 = wc_s[c0 + k + 0], w1 = wc_s[c0 + k + 1], w2 = wc_s[c0 + k + 2], w3 = wc_s[c0 + k + 3];
             cvh0 = fmaf(y0, w0.x, fmaf(y1, w1.x, fmaf(y2, w2.x, fmaf(y3, w3.x, cvh0))));
             cvh1 = fmaf(y0, w0.y, fmaf(y1, w1.y, fmaf(y2, w2.y, fmaf(y3, w3.y, cvh1))));
             cvh2 = fmaf(y0, w0.z, fmaf(y1, w1.z, fmaf(y2, w2.z, fmaf(y3, w3.z, cvh2))));
@@ -268,31 +284,30 @@ __global__ void __launch_bounds__(gemm_threads(EPG), 1) gemm_tc_kernel(const __g
             pk[e >> 1] = tc::pack_bf16(y0, y1);
             pk[(e >> 1) + 1] = tc::pack_bf16(y2, y3);
             // rows past T do not enter the temporal mean (fusion.py:401 averages the T real tokens)
-            x[k8 + e + 0] = slot < T ? y0 : 0.f; x[k8 + e + 1] = slot < T ? y1 : 0.f;
-            x[k8 + e + 2] = slot < T ? y2 : 0.f; x[k8 + e + 3] = slot < T ? y3 : 0.f;
+            x[k + 0] = slot < T ? y0 : 0.f; x[k + 1] = slot < T ? y1 : 0.f;
+            x[k + 2] = slot < T ? y2 : 0.f; x[k + 3] = slot < T ? y3 : 0.f;
           }
-          // 16 bytes per 8 columns: two consecutive groups make one 32-byte store
-          if ((k8 & 8) == 0) {
-            x_hold[0] = pk[0]; x_hold[1] = pk[1]; x_hold[2] = pk[2]; x_hold[3] = pk[3];
-          } else if (live) {
-            tc::stg256(orow + k8 - 8, x_hold[0], x_hold[1], x_hold[2], x_hold[3], pk[0], pk[1], pk[2], pk[3]);
-          }
+          if (live) tc::stg256(orow + k16, pk[0], pk[1], pk[2], pk[3], pk[4], pk[5], pk[6], pk[7]);
         }
-        if (live) {
+        if (eg == 1) xc[row] = make_float4(cvh0, cvh1, cvh2, cvh3);
+        tc::named_bar_sync(4 + q, 64);
+        if (eg == 0 && live) {
+          const float4 o = xc[row];
           float* cvp = ex.cv + (int64_t)clip * 64 + slot;
-          cvp[0] = cvh0; cvp[16] = cvh1; cvp[32] = cvh2; cvp[48] = cvh3;
+          cvp[0] = cvh0 + o.x + bias_s[3 * BN + 0]; cvp[16] = cvh1 + o.y + bias_s[3 * BN + 1];
+          cvp[32] = cvh2 + o.z + bias_s[3 * BN + 2]; cvp[48] = cvh3 + o.w + bias_s[3 * BN + 3];
         }
         // temporal mean: the 16 rows of a clip are the 16 lanes of a half-warp.  Transpose-reduce: after the step with lane
         // offset o a lane keeps the half of the columns whose index bit matches its lane bit, so lane l ends with the
-        // complete sums of columns 8·(l % 16) .. +8
-        lnres_fold<64, 8>(x, lane);
-        lnres_fold<32, 4>(x, lane);
-        lnres_fold<16, 2>(x, lane);
-        lnres_fold<8, 1>(x, lane);
+        // complete sums of columns 64·eg + 4·(l % 16) .. +4
+        lnres_fold<32, 8>(x, lane);
+        lnres_fold<16, 4>(x, lane);
+        lnres_fold<8, 2>(x, lane);
+        lnres_fold<4, 1>(x, lane);
         if (live) {
           const float invT = 1.f / (float)T;
-          tc::stg256f(ex.pooled + (int64_t)clip * 2 * BN + 8 * (lane & 15), x[0] * invT, x[1] * invT, x[2] * invT, x[3] * invT,
-                      x[4] * invT, x[5] * invT, x[6] * invT, x[7] * invT);
+          *reinterpret_cast<float4*>(ex.pooled + (int64_t)clip * 2 * BN + c0 + 4 * (lane & 15)) =
+              make_float4(x[0] * invT, x[1] * invT, x[2] * invT, x[3] * invT);
         }
         continue;
       }
@@ -315,15 +330,8 @@ __global__ void __launch_bounds__(gemm_threads(EPG), 1) gemm_tc_kernel(const __g
           }
         }
         if (OUT_BF16) {
-          // direct rows: 32 columns = 64 bytes = two whole sectors per lane.  HEADROWS: column block n0/128 = 4·which + h sends
-          // row (clip, i) of the tile to row 16h + i of the clip's [64][128] operand (which: out | out2)
-          __nv_bfloat16* o;
-          if (HEADROWS) {
-            const int nt = n0 >> 7;
-            o = reinterpret_cast<__nv_bfloat16*>(nt < 4 ? out : ex.out2) + ((int64_t)(m >> 4) * 64 + 16 * (nt & 3) + (m & 15)) * BN + c;
-          } else {
-            o = reinterpret_cast<__nv_bfloat16*>(out) + (int64_t)m * out_pitch + n0 + c;
-          }
+          // direct rows: 32 columns = 64 bytes = two whole sectors per lane
+          __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(out) + (int64_t)m * out_pitch + n0 + c;
           if (STAGED || m < M) {
             uint32_t pk[16];
 #pragma unroll
@@ -376,7 +384,19 @@ __global__ void __launch_bounds__(gemm_threads(EPG), 1) gemm_tc_kernel(const __g
         ex.tok[(int64_t)clip * kTokPitch + j] = sc0;
         ex.tok[((int64_t)(M / ex.seg_len) + clip) * kTokPitch + j] = sc1;
       }
-      if (STAGED) {
+      if (HEADROWS) {
+        // column block n0/128 = 4·which + h: rows (clip, i) of the tile are rows 16h + i of 8 consecutive clips of the [clips][64][128]
+        // operand `which` (out | out2) — one 3D box per 64-column half, written by the copy engine as whole lines
+        tc::fence_proxy_async();
+        tc::named_bar_sync(2 + eg, 128);
+        if (et == 0) {
+          const int nt = n0 >> 7;
+          const void* tm = nt < 4 ? reinterpret_cast<const void*>(&tmO) : reinterpret_cast<const void*>(&tmO2);
+          tc::tma_store_3d(tm, stage_out, 0, 16 * (nt & 3), m0 >> 4);
+          tc::tma_store_3d(tm, stage_out + kStageBox, 64, 16 * (nt & 3), m0 >> 4);
+          tc::bulk_commit_group();
+        }
+      } else if (STAGED) {
         // Each warp owns 32 rows of the tile end to end: no CTA-level barrier, no asynchronous store to wait for.  The rows
         // were staged swizzled (conflict-free 16-byte writes); they leave in global order, 512 contiguous bytes per access.
         __syncwarp();
@@ -411,6 +431,7 @@ __global__ void __launch_bounds__(gemm_threads(EPG), 1) gemm_tc_kernel(const __g
       }
     }
   }
+  if (HEADROWS && warp >= 2 && ((threadIdx.x - 64) & 127) == 0) tc::bulk_store_wait_all();
   tc::tc_fence_before();
   __syncthreads();
   if (warp == 1) tc::tmem_dealloc(tmem_base, kAccs * BN);
@@ -433,7 +454,9 @@ EncodeTiledFn encode_tiled_fn() {
 
 template <int EPI, int STAGES = kStagesDefault, int EPG = 1>
 int launch_gemm_tc(cudaStream_t st, const CUtensorMap& tmA, const CUtensorMap& tmB, const float* bias, void* out, int64_t pitch,
-                   int M, int N, int K, const GemmExtras& ex) {
+                   int M, int N, int K, const GemmExtras& ex, const CUtensorMap* tmO = nullptr, const CUtensorMap* tmO2 = nullptr) {
+  if (tmO == nullptr) tmO = &tmA;   // (only EPI_HEADROWS stores through tensor maps)
+  if (tmO2 == nullptr) tmO2 = &tmA;
   constexpr int smem = gemm_smem_bytes(EPI, STAGES);
   static_assert(smem <= 227 * 1024, "projection GEMM: shared memory");
   static bool configured = false;
@@ -443,7 +466,7 @@ int launch_gemm_tc(cudaStream_t st, const CUtensorMap& tmA, const CUtensorMap& t
   }
   const int tiles = ((M + BM - 1) / BM) * (N / BN);
   const int grid = tiles < num_sms() ? tiles : num_sms();
-  gemm_tc_kernel<EPI, STAGES, EPG><<<grid, gemm_threads(EPG), smem, st>>>(tmA, tmB, bias, out, pitch, M, N, K, ex);
+  gemm_tc_kernel<EPI, STAGES, EPG><<<grid, gemm_threads(EPG), smem, st>>>(tmA, tmB, *tmO, *tmO2, bias, out, pitch, M, N, K, ex);
   count_launch();
   XF_LAUNCH_CHECK();
   return XATTN_OK;
@@ -464,6 +487,21 @@ int make_tmap_bf16_2d(void* tmap_out, const void* base, int64_t rows, int64_t co
                   CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) XF_FAIL(XATTN_ERR_CUDA, "cuTensorMapEncodeTiled failed with CUresult %d (rows=%lld cols=%lld)", (int)r,
                                  (long long)rows, (long long)cols);
+  return XATTN_OK;
+}
+
+// dense [d2][d1][d0] bf16 tensor (d0 contiguous), boxes b2 x b1 x b0 with the 128-byte swizzle
+int make_tmap_bf16_3d(void* tmap_out, const void* base, int64_t d0, int64_t d1, int64_t d2, int b0, int b1, int b2) {
+  EncodeTiledFn fn = encode_tiled_fn();
+  if (fn == nullptr) XF_FAIL(XATTN_ERR_CUDA, "cuTensorMapEncodeTiled is not available from the driver");
+  cuuint64_t gdim[3] = {(cuuint64_t)d0, (cuuint64_t)d1, (cuuint64_t)d2};
+  cuuint64_t gstride[2] = {(cuuint64_t)d0 * 2, (cuuint64_t)d0 * d1 * 2};
+  cuuint32_t box[3] = {(cuuint32_t)b0, (cuuint32_t)b1, (cuuint32_t)b2};
+  cuuint32_t estr[3] = {1, 1, 1};
+  CUresult r = fn(reinterpret_cast<CUtensorMap*>(tmap_out), CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<void*>(base), gdim,
+                  gstride, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                  CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) XF_FAIL(XATTN_ERR_CUDA, "cuTensorMapEncodeTiled (3D) failed with CUresult %d", (int)r);
   return XATTN_OK;
 }
 
@@ -499,7 +537,7 @@ int gemm_tc_video_mix(cudaStream_t st, const void* U, const void* G, const float
   alignas(64) CUtensorMap tmA, tmB;
   XF_TRY(make_tmap_bf16_2d(&tmA, U, M, 4 * BN, BM, BK));
   XF_TRY(make_tmap_bf16_2d(&tmB, G, BN, 4 * BN, BN, BK));
-  return launch_gemm_tc<EPI_LNRES, 6, 1>(st, tmA, tmB, bias, v1, BN, M, BN, 4 * BN, ex);
+  return launch_gemm_tc<EPI_LNRES, 6, 2>(st, tmA, tmB, bias, v1, BN, M, BN, 4 * BN, ex);
 }
 
 int gemm_tc_video_kv(cudaStream_t st, const void* v1, const void* F, const float* bias, void* kt, void* vt, int clips) {
@@ -510,7 +548,10 @@ int gemm_tc_video_kv(cudaStream_t st, const void* v1, const void* F, const float
   alignas(64) CUtensorMap tmA, tmB;
   XF_TRY(make_tmap_bf16_2d(&tmA, v1, M, BN, BM, BK));
   XF_TRY(make_tmap_bf16_2d(&tmB, F, 8 * BN, BN, BN, BK));
-  return launch_gemm_tc<EPI_HEADROWS, 5, 2>(st, tmA, tmB, bias, kt, BN, M, 8 * BN, BN, ex);
+  alignas(64) CUtensorMap tmK, tmV;   // [clips][64][128], boxes of 8 clips x 16 rows x 64 columns
+  XF_TRY(make_tmap_bf16_3d(&tmK, kt, BN, 64, clips, 64, 16, 8));
+  XF_TRY(make_tmap_bf16_3d(&tmV, vt, BN, 64, clips, 64, 16, 8));
+  return launch_gemm_tc<EPI_HEADROWS, 4, 2>(st, tmA, tmB, bias, kt, BN, M, 8 * BN, BN, ex, &tmK, &tmV);
 }
 
 }  // namespace xf

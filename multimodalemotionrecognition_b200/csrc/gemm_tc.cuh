@@ -22,4 +22,5 @@ int gemm_tc_video_mix(cudaStream_t st, const void* U, const void* G, const float
 int gemm_tc_video_kv(cudaStream_t st, const void* v1, const void* F, const float* bias, void* kt, void* vt, int clips);
 // 2D bf16 tensor map with SWIZZLE_128B boxes: `cols` contiguous elements per row, rows `pitch` elements apart (0 = cols).
 int make_tmap_bf16_2d(void* tmap_out, const void* base, int64_t rows, int64_t cols, int box_rows, int box_cols, int64_t pitch = 0);
+int make_tmap_bf16_3d(void* tmap_out, const void* base, int64_t d0, int64_t d1, int64_t d2, int b0, int b1, int b2);
 }  // namespace xf

@@ -7,11 +7,17 @@ rep, kre, obj = sys.argv[1:4]
 main = sys.argv[4] if len(sys.argv) > 4 else os.path.basename(obj).replace(".o", ".cu")
 src = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv", "--kernel-name", f"regex:{kre}"], capture_output=True, text=True).stdout
 rows = list(csv.reader(io.StringIO(src)))
+# several launches / template instances may match: keep the first block whose full name matches NCU_LINES_NAME (default: first)
+starts = [i for i, r in enumerate(rows) if r and r[0] == "Kernel Name"] + [len(rows)]
+want = os.environ.get("NCU_LINES_NAME", "")
+pick = next((k for k in range(len(starts) - 1) if want in rows[starts[k]][1]), 0)
+rows = rows[starts[pick]:starts[pick + 1]]
 kname = rows[0][1]
 hdr = rows[1]; idx = {h: i for i, h in enumerate(hdr)}
 si, ii, so = idx["# Samples"], idx["Instructions Executed"], idx["Source"]
 ins = [(int(r[si] or 0), int(r[ii] or 0), r[so]) for r in rows[2:] if len(r) > si]
-base = re.sub(r"\(.*", "", kname).split("::")[-1]
+base = re.sub(r"[<(].*", "", kname).split("::")[-1]
+mangled = os.environ.get("NCU_LINES_MANGLED", "")   # e.g. ILi4ELi6ELi1E to pick one template instance
 with tempfile.TemporaryDirectory() as d:
     subprocess.run(["cuobjdump", "-xelf", "all", os.path.abspath(obj)], cwd=d, capture_output=True)
     cub = [os.path.join(d, f) for f in os.listdir(d) if f.endswith(".cubin")][0]
@@ -19,7 +25,7 @@ with tempfile.TemporaryDirectory() as d:
 lines, cur_file, cur_line, main_line, active = [], "?", 0, 0, False
 for l in dis.splitlines():
     if l.startswith(".text."):
-        active = base in l
+        active = base in l and mangled in l
         continue
     if not active:
         continue
