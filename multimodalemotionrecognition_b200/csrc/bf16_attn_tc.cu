@@ -557,34 +557,65 @@ __global__ void __launch_bounds__(kA2VThreads, 1) a2v_tc_kernel(const __grid_con
         uint32_t r0[32];                      // heads 2hf, 2hf+1 x 16 keys of this row against its own clip
         tc::tmem_ld_32x32(tbuf + (uint32_t)(64 * ci + 32 * hf), r0);
         const float* kc = kc_s + (s * 2 + ci) * 80;
-        float bia[16];   // the prior bias is the same for every head (fusion.py:351-354): once per key
+        // (element-wise math on fp32 pairs: FADD2 / FMUL2 / FFMA2 halve the issue slots of this issue-bound kernel)
+        uint64_t bia2[8];   // the prior bias is the same for every head (fusion.py:351-354): once per key
+        {
+          const uint64_t qp2 = tc::f2_pack(qa + pk, qa + pk), bl2 = tc::f2_pack(bl, bl);
 #pragma unroll
-        for (int i = 0; i < 16; ++i) {
-          bia[i] = a.use_prior ? tc::tanh_fast(qa + kc[i] + pk) * bl : 0.f;
-          if (i >= a.T) bia[i] = -INFINITY;   // padded video tokens never receive probability mass
+          for (int i = 0; i < 8; ++i) {
+            bia2[i] = 0ull;
+            if (a.use_prior) {
+              const float2 k2 = *reinterpret_cast<const float2*>(kc + 2 * i);
+              float t0_, t1_;
+              tc::f2_unpack(tc::f2_add(qp2, tc::f2_pack(k2.x, k2.y)), t0_, t1_);
+              bia2[i] = tc::f2_mul(tc::f2_pack(tc::tanh_fast(t0_), tc::tanh_fast(t1_)), bl2);
+            }
+          }
+          if (a.T < 16) {   // padded video tokens never receive probability mass
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+              float b0_, b1_;
+              tc::f2_unpack(bia2[i], b0_, b1_);
+              if (2 * i >= a.T) b0_ = -INFINITY;
+              if (2 * i + 1 >= a.T) b1_ = -INFINITY;
+              bia2[i] = tc::f2_pack(b0_, b1_);
+            }
+          }
         }
         tc::tmem_ld_wait();
         uint32_t pk2[16];
+        const uint64_t l2e2 = tc::f2_pack(kL2E, kL2E);
 #pragma unroll
         for (int h2 = 0; h2 < 2; ++h2) {
-          float x[16];
+          uint64_t xq[8];
           float m = -INFINITY;
 #pragma unroll
-          for (int i = 0; i < 16; ++i) {
-            x[i] = fmaf(__uint_as_float(r0[16 * h2 + i]) + kc[16 + 32 * hf + 16 * h2 + i], kL2E, bia[i]);
-            m = fmaxf(m, x[i]);
+          for (int i = 0; i < 8; ++i) {
+            const float2 c2 = *reinterpret_cast<const float2*>(kc + 16 + 32 * hf + 16 * h2 + 2 * i);
+            xq[i] = tc::f2_fma(tc::f2_add(tc::f2_pack_u(r0[16 * h2 + 2 * i], r0[16 * h2 + 2 * i + 1]), tc::f2_pack(c2.x, c2.y)), l2e2, bia2[i]);
+            float x0_, x1_;
+            tc::f2_unpack(xq[i], x0_, x1_);
+            m = fmaxf(m, fmaxf(x0_, x1_));
           }
-          float l0 = 0.f, l1 = 0.f;
+          const uint64_t nm2 = tc::f2_pack(-m, -m);
+          uint64_t l2 = 0ull;
 #pragma unroll
-          for (int i = 0; i < 16; i += 2) {
-            x[i] = ex2_fast(x[i] - m);
-            x[i + 1] = ex2_fast(x[i + 1] - m);
-            l0 += x[i];
-            l1 += x[i + 1];
+          for (int i = 0; i < 8; ++i) {
+            float x0_, x1_;
+            tc::f2_unpack(tc::f2_add(xq[i], nm2), x0_, x1_);
+            xq[i] = tc::f2_pack(ex2_fast(x0_), ex2_fast(x1_));
+            l2 = tc::f2_add(l2, xq[i]);
           }
+          float l0, l1;
+          tc::f2_unpack(l2, l0, l1);
           const float inv = __frcp_rn(l0 + l1);
+          const uint64_t inv2 = tc::f2_pack(inv, inv);
 #pragma unroll
-          for (int i = 0; i < 16; i += 2) pk2[8 * h2 + (i >> 1)] = tc::pack_bf16(x[i] * inv, x[i + 1] * inv);
+          for (int i = 0; i < 8; ++i) {
+            float x0_, x1_;
+            tc::f2_unpack(tc::f2_mul(xq[i], inv2), x0_, x1_);
+            pk2[8 * h2 + i] = tc::pack_bf16(x0_, x1_);
+          }
         }
         uint32_t z[16];
 #pragma unroll
@@ -607,42 +638,46 @@ __global__ void __launch_bounds__(kA2VThreads, 1) a2v_tc_kernel(const __grid_con
       int R, ci, c;
       bool valid;
       row_of(n, R, ci, c, valid);
-      constexpr int HC = BE / 2;
-      float x[HC];
+      constexpr int HC = BE / 2, HP = HC / 2;
+      uint64_t xp[HP];   // the half row as fp32 pairs: this phase is bound by instruction issue, so its element-wise math is packed (FADD2 / FFMA2)
       const uint8_t* arow = a0s + s * kA0Stage + hf * kA2VHalf + R * 128;
       tc::mbar_wait(&o_full[grp], (n >> 1) & 1u);
       if (tracer) trace_mark(a.trace, 5, n);   // worker: O ready
       tc::tc_fence_after();
       {
-        uint32_t (&xr)[HC] = reinterpret_cast<uint32_t (&)[HC]>(x);
         uint32_t t0[32], t1[32];
         tc::tmem_ld_32x32(tbuf + 128u + (uint32_t)(64 * hf), t0);
         tc::tmem_ld_32x32(tbuf + 160u + (uint32_t)(64 * hf), t1);
         tc::tmem_ld_wait();
 #pragma unroll
-        for (int i = 0; i < 32; ++i) {
-          xr[i] = t0[i]; xr[32 + i] = t1[i];
+        for (int i = 0; i < 16; ++i) {
+          xp[i] = tc::f2_pack_u(t0[2 * i], t0[2 * i + 1]);
+          xp[16 + i] = tc::f2_pack_u(t1[2 * i], t1[2 * i + 1]);
         }
       }
-      float sum0 = 0.f, sum1 = 0.f, sq0 = 0.f, sq1 = 0.f;
+      uint64_t sum2 = 0ull, sq2 = 0ull;
 #pragma unroll
       for (int k = 0; k < 8; ++k) {   // + this row of a0 (the residual, 16-byte chunk k of the swizzled half row)
         const uint4 res = *reinterpret_cast<const uint4*>(arow + (((k ^ R) & 7) << 4));
         const uint32_t w[4] = {res.x, res.y, res.z, res.w};
 #pragma unroll
         for (int e = 0; e < 4; ++e) {
-          const int col = 8 * k + 2 * e;
-          x[col] += __uint_as_float(w[e] << 16);               // (bo2 arrives inside O: folded into Vt by video_update)
-          x[col + 1] += __uint_as_float(w[e] & 0xFFFF0000u);
-          sum0 += x[col];
-          sum1 += x[col + 1];
-          sq0 = fmaf(x[col], x[col], sq0);
-          sq1 = fmaf(x[col + 1], x[col + 1], sq1);
+          const int j = 4 * k + e;   // (bo2 arrives inside O: folded into Vt by video_update)
+          xp[j] = tc::f2_add(xp[j], tc::f2_pack_u(w[e] << 16, w[e] & 0xFFFF0000u));
+          sum2 = tc::f2_add(sum2, xp[j]);
+          sq2 = tc::f2_fma(xp[j], xp[j], sq2);
         }
       }
       // the two halves of the row meet: (sum, sum of squares) through the first two of the output columns this thread has
       // just loaded (its own half: the partner never reads them, and the buffer is not refilled before o_empty below)
-      float su = sum0 + sum1, sq = sq0 + sq1;
+      float su, sq;
+      {
+        float a0_, a1_;
+        tc::f2_unpack(sum2, a0_, a1_);
+        su = a0_ + a1_;
+        tc::f2_unpack(sq2, a0_, a1_);
+        sq = a0_ + a1_;
+      }
       {
         const uint32_t tx = tbuf + 128u;
         tc::tmem_st_32x32_x1(tx + (uint32_t)(64 * hf), __float_as_uint(su));
@@ -662,19 +697,23 @@ __global__ void __launch_bounds__(kA2VThreads, 1) a2v_tc_kernel(const __grid_con
       tc::mbar_arrive(&a0_empty[s]);           // and so is this row's residual
       if (tracer) trace_mark(a.trace, 6, n);   // worker: O + residual in registers
       const float mu = su * (1.f / BE);
-      const float rs = rsqrtf(fmaxf(sq * (1.f / BE) - mu * mu, 0.f) + 1e-5f);
+      // padded / absent rows contribute nothing: scale and shift of zero (their x is finite: real or zero-filled a0 rows, and
+      // the unused lanes of the M=64 tile hold the previous tile's finite values)
+      const float rs = valid ? rsqrtf(fmaxf(sq * (1.f / BE) - mu * mu, 0.f) + 1e-5f) : 0.f;
       const float nmr = -mu * rs;
+      const uint64_t rs2 = tc::f2_pack(rs, rs), nmr2 = tc::f2_pack(nmr, nmr);
 #pragma unroll
-      for (int i = 0; i < HC; ++i) x[i] = valid ? fmaf(x[i], rs, nmr) : 0.f;   // padded / absent rows contribute nothing (select)
-      // sum over the warp's 32 rows: butterfly, the live columns halve at every step
+      for (int i = 0; i < HP; ++i) xp[i] = tc::f2_fma(xp[i], rs2, nmr2);
+      // sum over the warp's 32 rows: butterfly, the live columns halve at every step (pairs stay pairs down to the last step)
 #pragma unroll
-      for (int off = 16, cnt = HC / 2; off >= 1; off >>= 1, cnt >>= 1) {
+      for (int off = 16, cnt = HP / 2; off >= 1; off >>= 1, cnt >>= 1) {
         const bool up = (lane & off) != 0;
 #pragma unroll
         for (int i = 0; i < cnt; ++i) {
-          const float send = up ? x[i] : x[i + cnt];
-          const float keep = up ? x[i + cnt] : x[i];
-          x[i] = keep + __shfl_xor_sync(0xffffffffu, send, off);
+          float s0_, s1_;
+          tc::f2_unpack(up ? xp[i] : xp[i + cnt], s0_, s1_);
+          const uint64_t keep = up ? xp[i + cnt] : xp[i];
+          xp[i] = tc::f2_add(keep, tc::f2_pack(__shfl_xor_sync(0xffffffffu, s0_, off), __shfl_xor_sync(0xffffffffu, s1_, off)));
         }
       }
       // after the five steps lane L holds two columns: bit k of L chose the upper half at step k
@@ -685,8 +724,10 @@ __global__ void __launch_bounds__(kA2VThreads, 1) a2v_tc_kernel(const __grid_con
           if (lane & off) base += cnt;
         // slot of this (clip, tile, warp): even clip: tile 0 warps 0-3 -> 0-3, tile 1 warp 0 -> 4; odd clip: tile 1 warps 1-3 -> 0-2, tile 2 -> 3-6
         const int slot = ci == 0 ? (t == 0 ? sp : 4) : (t == 1 ? sp - 1 : 3 + sp);
+        float x0_, x1_;
+        tc::f2_unpack(xp[0], x0_, x1_);
         if (c < a.B)
-          *reinterpret_cast<float2*>(a.poolp + ((int64_t)c * kPoolSlots + slot) * BE + HC * hf + base) = make_float2(x[0], x[1]);
+          *reinterpret_cast<float2*>(a.poolp + ((int64_t)c * kPoolSlots + slot) * BE + HC * hf + base) = make_float2(x0_, x1_);
       }
       if (tracer) trace_mark(a.trace, 7, n);   // worker: tile done
     };

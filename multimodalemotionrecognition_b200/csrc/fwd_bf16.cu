@@ -33,7 +33,7 @@ struct HeadPooledArgs {
 constexpr int kXP = 2 * BE + 8;    // bf16 pitch of the split activations (528 B: row g -> bank 4g)
 constexpr int kHP = 256 + 4;       // fp32 pitch of hid / final-layer weights
 constexpr int kHeadThreads = 512;   // 16 warps: the n-tiles of layer 0 spread thin, the kernel is one latency chain per CTA
-__global__ void __launch_bounds__(kHeadThreads) head_pooled_kernel(HeadPooledArgs a) {
+__global__ void __launch_bounds__(kHeadThreads, 2) head_pooled_kernel(HeadPooledArgs a) {
   // xhi/xlo (layer-0 operands) and wl (final linear, [C][K]) are live in different phases and share one region.
   __shared__ __align__(16) unsigned char region[2 * kHeadClips * kXP * 2 > 16 * kHP * 4 ? 2 * kHeadClips * kXP * 2 : 16 * kHP * 4];
   __shared__ __align__(16) float hid[kHeadClips][kHP];
