@@ -97,13 +97,14 @@ __device__ __forceinline__ void v2a_strip(const uint32_t (&r)[N], uint32_t (&pk)
 }
 
 __global__ void __launch_bounds__(kV2AThreads, 1) v2a_tc_kernel(const __grid_constant__ CUtensorMap tmA0,
-                                                                 const __grid_constant__ CUtensorMap tmQt, V2ATcArgs a) {
+                                                                 const __grid_constant__ CUtensorMap tmQt,
+                                                                 const __grid_constant__ CUtensorMap tmU, V2ATcArgs a) {
   extern __shared__ __align__(1024) uint8_t smem[];
   uint8_t* a0s = smem;                              // [2 stages][2 clips][2 boxes]
   uint8_t* qts = smem + 2 * kA0Stage;               // [2 stages][2 clips][2 boxes]
   float* ka_s = reinterpret_cast<float*>(smem + kV2AOffKa);
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + kV2AOffBar);
-  uint64_t *a0_full = bars, *a0_empty = bars + 2, *qt_full = bars + 4, *qt_empty = bars + 6, *s_full = bars + 8,
+  uint64_t *a0_full = bars, *a0_empty = bars + 2, *qt_full = bars + 4, *u_staged = bars + 6, *s_full = bars + 8,
            *p_full = bars + 9, *u_full = bars + 10, *u_empty = bars + 11;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 12);
 
@@ -116,11 +117,12 @@ __global__ void __launch_bounds__(kV2AThreads, 1) v2a_tc_kernel(const __grid_con
     if ((tc::smem_u32(smem) & 1023u) != 0) __trap();   // the swizzled TMA boxes need a 1024-byte aligned base
     tc::tma_prefetch_desc(&tmA0);
     tc::tma_prefetch_desc(&tmQt);
+    tc::tma_prefetch_desc(&tmU);
     for (int i = 0; i < 2; ++i) {
       tc::mbar_init(&a0_full[i], 1);
       tc::mbar_init(&a0_empty[i], 1);
       tc::mbar_init(&qt_full[i], 1);
-      tc::mbar_init(&qt_empty[i], 1);
+      tc::mbar_init(&u_staged[i], 256);   // the pair's U rows are staged in its (dead) Qt stage
     }
     tc::mbar_init(s_full, 1);
     tc::mbar_init(p_full, 256);
@@ -136,10 +138,12 @@ __global__ void __launch_bounds__(kV2AThreads, 1) v2a_tc_kernel(const __grid_con
 
   if (warp == 0) {
     if (lane == 0) {
-      uint32_t it = 0;
-      for (int p = blockIdx.x; p < npairs; p += gridDim.x, ++it) {
-        const uint32_t s = it & 1u, ph = (it >> 1) & 1u;
-        while (!tc::mbar_try_wait(&qt_empty[s], ph ^ 1u)) __nanosleep(64);   // not latency critical: leave the issue slots to the softmax warps
+      // Producer: keeps the a0 ring full, and owns the Qt stages end to end — pair i's Qt stage is dead once its scores exist,
+      // the softmax warps stage the pair's U rows in it, this thread sends them out with the copy engine (whole lines) and, when
+      // the engine has read them, refills the stage with the Qt of pair i + 2.
+      auto load_qt = [&](uint32_t it) {
+        const uint32_t s = it & 1u;
+        const int p = blockIdx.x + (int)it * (int)gridDim.x;
         tc::mbar_expect_tx(&qt_full[s], kQtStage);
         for (int i = 0; i < 2; ++i) {
           uint8_t* dst = qts + s * kQtStage + i * kQtClip;
@@ -147,7 +151,10 @@ __global__ void __launch_bounds__(kV2AThreads, 1) v2a_tc_kernel(const __grid_con
           tc::tma_load_2d(dst, &tmQt, &qt_full[s], 0, row);
           tc::tma_load_2d(dst + kBox, &tmQt, &qt_full[s], 64, row);
         }
-        while (!tc::mbar_try_wait(&a0_empty[s], ph ^ 1u)) __nanosleep(64);
+      };
+      auto load_a0 = [&](uint32_t it) {
+        const uint32_t s = it & 1u;
+        const int p = blockIdx.x + (int)it * (int)gridDim.x;
         trace_mark(a.trace, 0, it);   // a0 stage free, loads issued
         tc::mbar_expect_tx(&a0_full[s], kA0Stage + (a.use_prior ? 2 * BTAP * 4 : 0));
         for (int i = 0; i < 2; ++i) {
@@ -158,7 +165,33 @@ __global__ void __launch_bounds__(kV2AThreads, 1) v2a_tc_kernel(const __grid_con
           if (a.use_prior)   // the clip's key-side token scores ride along
             tc::bulk_load_1d(ka_s + (s * 2 + i) * kKaPitch, a.tok + (int64_t)min(2 * p + i, a.B - 1) * BTAP, BTAP * 4, &a0_full[s]);
         }
+      };
+      const uint32_t nl = (uint32_t)(n_local > 0 ? n_local : 0);
+      uint32_t na = 0, nst = 0;   // next pair whose a0 is to be loaded / whose U is to be stored
+      for (; na < 2 && na < nl; ++na) {
+        load_qt(na);
+        load_a0(na);
       }
+      while (nst < nl) {
+        bool progressed = false;
+        if (na < nl && tc::mbar_test_wait(&a0_empty[na & 1u], ((na >> 1) & 1u) ^ 1u)) {
+          load_a0(na++);
+          progressed = true;
+        }
+        if (tc::mbar_test_wait(&u_staged[nst & 1u], (nst >> 1) & 1u)) {
+          const uint32_t s = nst & 1u;
+          const int p = blockIdx.x + (int)nst * (int)gridDim.x;
+#pragma unroll
+          for (int g8 = 0; g8 < 8; ++g8) tc::tma_store_2d(&tmU, qts + s * kQtStage + g8 * 4096, 64 * g8, 32 * p);
+          tc::bulk_commit_group();
+          tc::bulk_store_wait_read();
+          if (nst + 2 < nl) load_qt(nst + 2);
+          ++nst;
+          progressed = true;
+        }
+        if (!progressed) __nanosleep(64);   // not latency critical: leave the issue slots to the softmax warps
+      }
+      tc::bulk_store_wait_all();
     }
   } else if (warp == 1) {
     if (lane == 0) {
@@ -183,7 +216,6 @@ __global__ void __launch_bounds__(kV2AThreads, 1) v2a_tc_kernel(const __grid_con
           }
         }
         tc::umma_commit(s_full);
-        tc::umma_commit(&qt_empty[s]);
       };
       if (n_local > 0) issue_s(0);
       for (uint32_t it = 0; it < (uint32_t)n_local; ++it) {
@@ -305,19 +337,30 @@ __global__ void __launch_bounds__(kV2AThreads, 1) v2a_tc_kernel(const __grid_con
         tc::tc_fence_before();
         tc::mbar_arrive(u_empty);
         const float inv = 1.f / (l + lp);             // whole-row sum of this lane's row
-        const int cc = 2 * p + (lane >> 4);
-        if (cc < a.B) {
-          // 128 bytes of this lane's row: four 32-byte stores, each a whole sector
-          __nv_bfloat16* up = a.u + ((int64_t)cc * 16 + (lane & 15)) * (4 * BE) + h * BE + 64 * half;
-          uint32_t w[32];
+        // 128 bytes of this lane's row -> the pair's Qt stage, as box (2h + half) of eight [32 rows][64 columns] swizzled boxes
+        // (rows of clips past the batch are clipped by the tensor map)
+        {
+          uint8_t* stg = qts + s * kQtStage + (2 * h + half) * 4096 + lane * 128;
 #pragma unroll
-          for (int v = 0; v < 16; ++v) {
-            w[v] = tc::pack_bf16(__uint_as_float(r0u[2 * v]) * inv, __uint_as_float(r0u[2 * v + 1]) * inv);
-            w[16 + v] = tc::pack_bf16(__uint_as_float(r1u[2 * v]) * inv, __uint_as_float(r1u[2 * v + 1]) * inv);
+          for (int v = 0; v < 4; ++v) {
+            uint4 w;
+            w.x = tc::pack_bf16(__uint_as_float(r0u[8 * v + 0]) * inv, __uint_as_float(r0u[8 * v + 1]) * inv);
+            w.y = tc::pack_bf16(__uint_as_float(r0u[8 * v + 2]) * inv, __uint_as_float(r0u[8 * v + 3]) * inv);
+            w.z = tc::pack_bf16(__uint_as_float(r0u[8 * v + 4]) * inv, __uint_as_float(r0u[8 * v + 5]) * inv);
+            w.w = tc::pack_bf16(__uint_as_float(r0u[8 * v + 6]) * inv, __uint_as_float(r0u[8 * v + 7]) * inv);
+            *reinterpret_cast<uint4*>(stg + (((v ^ lane) & 7) << 4)) = w;
           }
 #pragma unroll
-          for (int v = 0; v < 4; ++v)
-            tc::stg256(up + 16 * v, w[8 * v], w[8 * v + 1], w[8 * v + 2], w[8 * v + 3], w[8 * v + 4], w[8 * v + 5], w[8 * v + 6], w[8 * v + 7]);
+          for (int v = 0; v < 4; ++v) {
+            uint4 w;
+            w.x = tc::pack_bf16(__uint_as_float(r1u[8 * v + 0]) * inv, __uint_as_float(r1u[8 * v + 1]) * inv);
+            w.y = tc::pack_bf16(__uint_as_float(r1u[8 * v + 2]) * inv, __uint_as_float(r1u[8 * v + 3]) * inv);
+            w.z = tc::pack_bf16(__uint_as_float(r1u[8 * v + 4]) * inv, __uint_as_float(r1u[8 * v + 5]) * inv);
+            w.w = tc::pack_bf16(__uint_as_float(r1u[8 * v + 6]) * inv, __uint_as_float(r1u[8 * v + 7]) * inv);
+            *reinterpret_cast<uint4*>(stg + ((((4 + v) ^ lane) & 7) << 4)) = w;
+          }
+          tc::fence_proxy_async();
+          tc::mbar_arrive(&u_staged[s]);
         }
       }
       if (threadIdx.x == 64) trace_mark(a.trace, 7, it);   // worker: U stored
@@ -761,9 +804,10 @@ int launch_v2a_tc(const Bf16Ctx& x) {
     XF_CUDA(cudaMemsetAsync(trace_buf, 0, 8 * 64 * 8, x.st));
     a.trace = trace_buf;
   }
-  alignas(64) CUtensorMap tmA0, tmQt;
+  alignas(64) CUtensorMap tmA0, tmQt, tmU;
   XF_TRY(make_tmap_bf16_2d(&tmA0, x.ws + x.w.a0, (int64_t)c.B * c.Ta, BE, BTAP, 64, BOP));
   XF_TRY(make_tmap_bf16_2d(&tmQt, x.ws + x.w.qt, (int64_t)c.B * 64, BE, 64, 64, BOP));
+  XF_TRY(make_tmap_bf16_2d(&tmU, x.ws + x.w.u, (int64_t)c.B * 16, 4 * BE, 32, 64));
   static bool configured = false;
   if (!configured) {
     XF_CUDA(cudaFuncSetAttribute(v2a_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kV2ASmem));
@@ -771,7 +815,7 @@ int launch_v2a_tc(const Bf16Ctx& x) {
   }
   const int npairs = (c.B + 1) / 2;
   const int grid = npairs < num_sms() ? npairs : num_sms();
-  v2a_tc_kernel<<<grid, kV2AThreads, kV2ASmem, x.st>>>(tmA0, tmQt, a);
+  v2a_tc_kernel<<<grid, kV2AThreads, kV2ASmem, x.st>>>(tmA0, tmQt, tmU, a);
   count_launch();
   XF_LAUNCH_CHECK();
   if (tracing) {   // debugging aid: timeline of CTA 0, microseconds from its first load
