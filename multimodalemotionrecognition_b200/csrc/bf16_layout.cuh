@@ -35,8 +35,9 @@ constexpr int BTAP = 160;  // audio tokens padded to ten m16 tiles
 struct PackBf16 {
   int64_t Wv, Wfold, bfold;                          // bf16 [E,Dv], bf16 [E,Da], f32 [E]
   int64_t Wq1, Wk1, Wv1, Wo1, Wk2, Wv2, Wq2, Wo2;    // bf16 [E,BEP] each (torch [out,in] layout, padded pitch)
-  int64_t W0b;                                       // bf16 [HW,2E]: head layer 0 (xattn_mlp.0 / xattn_gate.0) weight
-  int64_t pW0;                                       // bf16 [Hd,2E]: prior_net.0.weight (0 bytes without the prior)
+  int64_t W0b;                                       // bf16 [HW,2E] in mma B-fragment order (bf16_pack.cu: frag_pack_kernel): head layer 0
+                                                     // (xattn_mlp.0 / xattn_gate.0) weight
+  int64_t pW0;                                       // same order, [ceil8(Hd),2E]: prior_net.0.weight (0 bytes without the prior)
   int64_t scw;                                       // f32 [2,E]: a_key_bias / a_query_bias weights, token part (first E entries)
   // video-side update folded into two GEMMs (gemm_tc.cuh: video_mix, video_kv)
   int64_t Gmix, bmix;                                // bf16 [E,4E]: G[n][128h+e] = sum_d Wo1[n][32h+d]·Wv1[32h+d][e]; f32 [E]: Wo1·bv1 + bo1

@@ -41,7 +41,7 @@ void compute_pack_bf16(const xattn_config& c, PackBf16& p) {
   p.Wq1 = take(E * BEP * 2); p.Wk1 = take(E * BEP * 2); p.Wv1 = take(E * BEP * 2); p.Wo1 = take(E * BEP * 2);
   p.Wk2 = take(E * BEP * 2); p.Wv2 = take(E * BEP * 2); p.Wq2 = take(E * BEP * 2); p.Wo2 = take(E * BEP * 2);
   p.W0b = take(HW * 2 * E * 2);
-  p.pW0 = take((int64_t)(c.use_prior ? c.prior_hidden : 0) * 2 * E * 2);
+  p.pW0 = take((int64_t)(c.use_prior ? (c.prior_hidden + 7) / 8 * 8 : 0) * 2 * E * 2);
   p.scw = take(2 * E * 4);
   p.Gmix = take(E * 4 * E * 2); p.bmix = take(E * 4);
   p.Fkv = take(8 * E * E * 2); p.bkv = take(8 * E * 4);
@@ -113,6 +113,22 @@ __global__ void fold_vec_kernel(const float* __restrict__ x, const float* __rest
   float s = 0.f;
   for (int d = 0; d < D; ++d) s = fmaf(x[d], Mx[d * rs + n * cs], s);
   out[n] = alpha * s + (add != nullptr ? beta * add[n] : 0.f);
+}
+// W[N,K] (fp32, row pitch K) -> bf16 in mma.m16n8k16 B-fragment order: for n-tile nt (8 rows), k-step pair kp (32 columns) and
+// lane (g = lane / 4, t = lane % 4) the four registers {b0, b1 of k-step 2kp, b0, b1 of k-step 2kp+1} are one uint4 at
+// [(nt * K/32 + kp) * 32 + lane]: a warp's fetch is 512 contiguous bytes instead of 8 rows x 16 bytes.  Rows past N repeat N-1.
+__global__ void frag_pack_kernel(const float* __restrict__ W, int N, int K, uint4* __restrict__ out) {
+  const int ntiles = (N + 7) / 8, kps = K / 32;
+  const int total = ntiles * kps * 32;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
+    const int lane = i & 31, kp = (i >> 5) % kps, nt = (i >> 5) / kps, g = lane >> 2, t = lane & 3;
+    const float* w = W + (int64_t)min(nt * 8 + g, N - 1) * K + kp * 32 + 2 * t;
+    auto pk = [&](int k) {
+      const __nv_bfloat162 h = __floats2bfloat162_rn(w[k], w[k + 1]);
+      return *reinterpret_cast<const uint32_t*>(&h);
+    };
+    out[i] = make_uint4(pk(0), pk(8), pk(16), pk(24));
+  }
 }
 // out[e] = W_in[e,:]·b_seq + b_in[e]
 __global__ void fold_bias_kernel(const float* __restrict__ w_in, const float* __restrict__ b_seq, const float* __restrict__ b_in,
@@ -189,10 +205,12 @@ int pack_weights_bf16(const xattn_config& c, const float* params, void* packed_v
     cvt(scratch + (int64_t)4 * E * E, E, pk.Fkv + (int64_t)4 * E * E * 2, E, 4 * E, E);
   }
   const int HW = c.head_kind == XATTN_HEAD_GATED ? E : c.common_dim;
-  cvt(P(XP_HEAD0_W), 2 * E, pk.W0b, 2 * E, HW, 2 * E);
+  frag_pack_kernel<<<32, 256, 0, st>>>(P(XP_HEAD0_W), HW, 2 * E, reinterpret_cast<uint4*>(packed + pk.W0b));
+  count_launch();
   XF_CUDA(cudaMemsetAsync(packed + pk.scw, 0, 2 * E * 4, st));
   if (c.use_prior) {
-    cvt(P(XP_PRIOR0_W), 2 * E, pk.pW0, 2 * E, c.prior_hidden, 2 * E);
+    frag_pack_kernel<<<32, 256, 0, st>>>(P(XP_PRIOR0_W), c.prior_hidden, 2 * E, reinterpret_cast<uint4*>(packed + pk.pW0));
+    count_launch();
     XF_CUDA(cudaMemcpyAsync(packed + pk.scw, P(XP_AK_W), E * 4, cudaMemcpyDeviceToDevice, st));           // a_key_bias.weight[:E]
     XF_CUDA(cudaMemcpyAsync(packed + pk.scw + E * 4, P(XP_AQ_W), E * 4, cudaMemcpyDeviceToDevice, st));   // a_query_bias.weight[:E]
   }

@@ -18,6 +18,7 @@
 // warps 0-3: rows (TMEM sub-partition = warp), warp 4: barrier init / TMEM alloc / weight TMA / MMA issue.
 // Two CTAs per SM (108 KB, 256 TMEM columns each) cover each other's serial chain.
 #include <cuda.h>
+#include <stdlib.h>
 
 #include "bf16_layout.cuh"
 #include "gemm_tc.cuh"

@@ -12,14 +12,15 @@ namespace xf {
 
 namespace {
 
-constexpr int kHeadClips = 16;   // clips per CTA of the head kernel: each weight element is read once per 16 clips
+constexpr int kHeadClips = 32;   // clips per CTA of the head kernel (two m16 tiles): 128 CTAs at B = 4096 — every CTA reads the whole
+                                 // layer-0 weight from L2, and with more, smaller CTAs those identical reads queue up on the same lines
 
 struct HeadPooledArgs {
   float* pooled;         // [B,2E] = [pooled_v ; pooled_a]
   const float* poolp;    // [B,8,E] partial sums of the normalised audio rows (tcgen05 a2v) or nullptr (pooled_a already final)
   const float *an_w, *an_b;   // a_norm affine, applied here when poolp is set: mean_t LN(x) = gamma * mean xhat + beta
   int Ta;
-  const __nv_bfloat16* w0b;   // [HW,2E] layer 0 weight, bf16
+  const __nv_bfloat16* w0b;   // [HW,2E] layer 0 weight, bf16 in mma B-fragment order (frag_pack_kernel)
   const float *b0, *w1, *b1, *wc, *bc;
   float* logits;
   int B, HW, C, gated;
@@ -27,16 +28,21 @@ struct HeadPooledArgs {
 
 // concat head: Linear(2E->HW), ReLU, (Dropout eval), Linear(HW->C)                       (fusion.py:405-407)
 // gated head : g = sigmoid(Linear(E->1)(ReLU(Linear(2E->E)))), fused = g*v + (1-g)*a, Linear(E->C)   (:408-411)
-// Layer 0 runs on bf16 mma.sync with M = the 16 clips of the CTA.  The fp32 activations are split once into a hi + lo bf16
+// Layer 0 runs on bf16 mma.sync with M = the clips of the CTA (m16 tiles).  The fp32 activations are split once into a hi + lo bf16
 // pair (two MMAs per step) so only the weights are rounded, as everywhere else on this path.  Row pitches are chosen so
 // that the eight rows a fragment load touches fall in different banks.
 constexpr int kXP = 2 * BE + 8;    // bf16 pitch of the split activations (528 B: row g -> bank 4g)
 constexpr int kHP = 256 + 4;       // fp32 pitch of hid / final-layer weights
 constexpr int kHeadThreads = 512;   // 16 warps: the n-tiles of layer 0 spread thin, the kernel is one latency chain per CTA
-__global__ void __launch_bounds__(kHeadThreads, 2) head_pooled_kernel(HeadPooledArgs a) {
-  // xhi/xlo (layer-0 operands) and wl (final linear, [C][K]) are live in different phases and share one region.
-  __shared__ __align__(16) unsigned char region[2 * kHeadClips * kXP * 2 > 16 * kHP * 4 ? 2 * kHeadClips * kXP * 2 : 16 * kHP * 4];
-  __shared__ __align__(16) float hid[kHeadClips][kHP];
+constexpr int kHeadRegion = 2 * kHeadClips * kXP * 2 > 16 * kHP * 4 ? 2 * kHeadClips * kXP * 2 : 16 * kHP * 4;
+constexpr int kHeadSmem = kHeadClips * 8 * BE * 4 + kHeadRegion + kHeadClips * kHP * 4;
+__global__ void __launch_bounds__(kHeadThreads, 1) head_pooled_kernel(HeadPooledArgs a) {
+  // dynamic smem: [pstage: the clip block's partial sums][region][hid].  xhi/xlo (layer-0 operands) and wl (final linear, [C][K])
+  // are live in different phases and share `region`.
+  extern __shared__ __align__(16) unsigned char hsm[];
+  float* pstage = reinterpret_cast<float*>(hsm);   // [kHeadClips][8][BE] (only with poolp)
+  unsigned char* region = hsm + kHeadClips * 8 * BE * 4;
+  auto hid = reinterpret_cast<float(*)[kHP]>(region + kHeadRegion);
   auto xhi = reinterpret_cast<__nv_bfloat16(*)[kXP]>(region);
   auto xlo = reinterpret_cast<__nv_bfloat16(*)[kXP]>(region + kHeadClips * kXP * 2);
   auto wl = reinterpret_cast<float(*)[kHP]>(region);
@@ -46,33 +52,31 @@ __global__ void __launch_bounds__(kHeadThreads, 2) head_pooled_kernel(HeadPooled
   const float* wfin = a.gated ? a.wc : a.w1;
   const float* bfin = a.gated ? a.bc : a.b1;
   const int K = a.gated ? BE : a.HW;
-  for (int i = tid; i < kHeadClips * 2 * BE / 2; i += blockDim.x) {
-    const int cc = i / BE, k = (i % BE) * 2;
-    float2 x = make_float2(0.f, 0.f);
-    if (cc < nc) {
-      const int64_t c = c0 + cc;
-      if (a.poolp != nullptr && k >= BE) {   // add the clip's partials in slot order (even clips own 5 slots, odd clips 7)
-        const int ns = (c & 1) ? 7 : 5;
-        const float* pp = a.poolp + c * 8 * BE + (k - BE);
-        float2 v[7];
+  // The clip block's partial sums (16 clips x 8 slots x 128 floats, contiguous) arrive as ONE bulk async copy: one memory round
+  // trip instead of one per loop iteration of dependent loads.
+  __shared__ uint64_t pbar;
+  if (a.poolp != nullptr && tid == 0) {
+    tc::mbar_init(&pbar, 1);
+    tc::fence_barrier_init();
+    tc::mbar_expect_tx(&pbar, (uint32_t)(nc * 8 * BE * 4));
+    tc::bulk_load_1d(pstage, a.poolp + (int64_t)c0 * 8 * BE, (uint32_t)(nc * 8 * BE * 4), &pbar);
+  }
+  // The weight fragments of a layer-0 tile (fragment order: 8 x 512 contiguous bytes per warp) are fetched one tile ahead of the
+  // MMAs that use them; the first tile's right here, so their L2 round trip hides behind the activation loads.
+  const int warp = tid >> 5, lane = tid & 31;
+  const int ntot = a.HW / 8;   // n-tiles of layer 0, dealt round-robin to the 16 warps
+  auto fetch = [&](uint4 (&bw)[2 * BE / 32], int nt) {
+    const uint4* wf = reinterpret_cast<const uint4*>(a.w0b) + ((int64_t)nt * (2 * BE / 32)) * 32 + lane;
 #pragma unroll
-        for (int s2 = 0; s2 < 7; ++s2) v[s2] = s2 < ns ? *reinterpret_cast<const float2*>(pp + s2 * BE) : make_float2(0.f, 0.f);
+    for (int kp = 0; kp < 2 * BE / 32; ++kp) bw[kp] = __ldg(wf + kp * 32);
+  };
+  uint4 b[2 * BE / 32];
+  if (warp < ntot) fetch(b, warp);
+  float2 xv[kHeadClips * BE / 2 / kHeadThreads];   // pooled_v, in flight meanwhile
 #pragma unroll
-        for (int s2 = 0; s2 < 7; ++s2) {   // fixed order
-          x.x += v[s2].x;
-          x.y += v[s2].y;
-        }
-        const float inv = 1.f / (float)a.Ta;
-        x.x = a.an_w[k - BE] * (x.x * inv) + a.an_b[k - BE];
-        x.y = a.an_w[k - BE + 1] * (x.y * inv) + a.an_b[k - BE + 1];
-        *reinterpret_cast<float2*>(a.pooled + c * 2 * BE + k) = x;
-      } else {
-        x = *reinterpret_cast<const float2*>(a.pooled + c * 2 * BE + k);
-      }
-    }
-    const __nv_bfloat162 h = __floats2bfloat162_rn(x.x, x.y);
-    *reinterpret_cast<__nv_bfloat162*>(&xhi[cc][k]) = h;
-    *reinterpret_cast<__nv_bfloat162*>(&xlo[cc][k]) = __floats2bfloat162_rn(x.x - __low2float(h), x.y - __high2float(h));
+  for (int r = 0; r < kHeadClips * BE / 2 / kHeadThreads; ++r) {
+    const int i = tid + r * kHeadThreads, cc = i / (BE / 2), k = (i % (BE / 2)) * 2;
+    xv[r] = cc < nc ? *reinterpret_cast<const float2*>(a.pooled + (int64_t)(c0 + cc) * 2 * BE + k) : make_float2(0.f, 0.f);
   }
   float4 wpre[2];   // final-layer weights, fetched now and parked in smem once layer 0 is done with the region (C*K <= 4096)
 #pragma unroll
@@ -80,45 +84,83 @@ __global__ void __launch_bounds__(kHeadThreads, 2) head_pooled_kernel(HeadPooled
     const int i = tid + r * kHeadThreads;
     wpre[r] = i < a.C * K / 4 ? __ldg(reinterpret_cast<const float4*>(wfin) + i) : make_float4(0.f, 0.f, 0.f, 0.f);
   }
+  auto put = [&](int cc, int k, float2 x) {
+    const __nv_bfloat162 h = __floats2bfloat162_rn(x.x, x.y);
+    *reinterpret_cast<__nv_bfloat162*>(&xhi[cc][k]) = h;
+    *reinterpret_cast<__nv_bfloat162*>(&xlo[cc][k]) = __floats2bfloat162_rn(x.x - __low2float(h), x.y - __high2float(h));
+  };
+#pragma unroll
+  for (int r = 0; r < kHeadClips * BE / 2 / kHeadThreads; ++r) {
+    const int i = tid + r * kHeadThreads;
+    put(i / (BE / 2), (i % (BE / 2)) * 2, xv[r]);
+  }
+  if (a.poolp != nullptr) {
+    __syncthreads();   // the barrier is initialised
+    tc::mbar_wait(&pbar, 0);
+  }
+  for (int i = tid; i < kHeadClips * BE / 2; i += kHeadThreads) {
+    const int cc = i / (BE / 2), k = (i % (BE / 2)) * 2;
+    float2 x = make_float2(0.f, 0.f);
+    if (cc < nc) {
+      const int64_t c = c0 + cc;
+      if (a.poolp != nullptr) {   // add the clip's partials in slot order (even clips own 5 slots, odd clips 7)
+        const int ns = (c & 1) ? 7 : 5;
+        const float* pp = pstage + cc * 8 * BE + k;
+#pragma unroll
+        for (int s2 = 0; s2 < 7; ++s2) {   // fixed order
+          if (s2 < ns) {
+            const float2 v = *reinterpret_cast<const float2*>(pp + s2 * BE);
+            x.x += v.x;
+            x.y += v.y;
+          }
+        }
+        const float inv = 1.f / (float)a.Ta;
+        x.x = a.an_w[k] * (x.x * inv) + a.an_b[k];
+        x.y = a.an_w[k + 1] * (x.y * inv) + a.an_b[k + 1];
+        *reinterpret_cast<float2*>(a.pooled + c * 2 * BE + BE + k) = x;
+      } else {
+        x = *reinterpret_cast<const float2*>(a.pooled + c * 2 * BE + BE + k);
+      }
+    }
+    put(cc, BE + k, x);
+  }
   __syncthreads();
   {
-    const int warp = tid >> 5, lane = tid & 31, g = lane >> 2, t = lane & 3;
-    const int ntot = a.HW / 8;   // n-tiles of layer 0, dealt round-robin to the 16 warps
-    // The weight fragments of a tile are fetched with volatile loads, all 32 in flight at once and one tile ahead of the
-    // MMAs that use them; left to the compiler they trail their use by two steps and every step waits out an L2 round trip.
-    auto fetch = [&](uint32_t (&b)[2 * BE / 16][2], int nt) {
-      const __nv_bfloat16* wrow = a.w0b + (int64_t)(nt * 8 + g) * (2 * BE) + 2 * t;
-#pragma unroll
-      for (int ks = 0; ks < 2 * BE / 16; ++ks) {
-        asm volatile("ld.global.nc.b32 %0, [%1];" : "=r"(b[ks][0]) : "l"(wrow + ks * 16));
-        asm volatile("ld.global.nc.b32 %0, [%1];" : "=r"(b[ks][1]) : "l"(wrow + ks * 16 + 8));
-      }
-    };
-    uint32_t b[2 * BE / 16][2], bn[2 * BE / 16][2];
-    if (warp < ntot) fetch(b, warp);
+    const int g = lane >> 2, t = lane & 3;
+    uint4 bn[2 * BE / 32];
+    const uint32_t ahi = tc::smem_u32(&xhi[(lane & 7) + 8 * ((lane >> 3) & 1)][8 * (lane >> 4)]);
+    const uint32_t alo = tc::smem_u32(&xlo[(lane & 7) + 8 * ((lane >> 3) & 1)][8 * (lane >> 4)]);
     for (int nt = warp; nt < ntot; nt += kHeadThreads / 32) {
       if (nt + kHeadThreads / 32 < ntot) fetch(bn, nt + kHeadThreads / 32);
-      float d[4] = {0.f, 0.f, 0.f, 0.f}, e[4] = {0.f, 0.f, 0.f, 0.f};
+      float d[kHeadClips / 16][4], e[kHeadClips / 16][4];
+#pragma unroll
+      for (int mt = 0; mt < kHeadClips / 16; ++mt)
+#pragma unroll
+        for (int r = 0; r < 4; ++r) d[mt][r] = e[mt][r] = 0.f;
 #pragma unroll
       for (int ks = 0; ks < 2 * BE / 16; ++ks) {
-        const int col = ks * 16 + 2 * t;
-        uint32_t hi[4], lo[4];
-        hi[0] = *reinterpret_cast<const uint32_t*>(&xhi[g][col]);      hi[1] = *reinterpret_cast<const uint32_t*>(&xhi[g + 8][col]);
-        hi[2] = *reinterpret_cast<const uint32_t*>(&xhi[g][col + 8]);  hi[3] = *reinterpret_cast<const uint32_t*>(&xhi[g + 8][col + 8]);
-        lo[0] = *reinterpret_cast<const uint32_t*>(&xlo[g][col]);      lo[1] = *reinterpret_cast<const uint32_t*>(&xlo[g + 8][col]);
-        lo[2] = *reinterpret_cast<const uint32_t*>(&xlo[g][col + 8]);  lo[3] = *reinterpret_cast<const uint32_t*>(&xlo[g + 8][col + 8]);
-        tc::mma_bf16(d, hi, b[ks][0], b[ks][1]);
-        tc::mma_bf16(e, lo, b[ks][0], b[ks][1]);
+        const uint32_t b0 = (ks & 1) ? b[ks >> 1].z : b[ks >> 1].x, b1 = (ks & 1) ? b[ks >> 1].w : b[ks >> 1].y;
+#pragma unroll
+        for (int mt = 0; mt < kHeadClips / 16; ++mt) {
+          uint32_t hi[4], lo[4];
+          tc::ldsm_x4(ahi + mt * 16 * kXP * 2 + ks * 32, hi[0], hi[1], hi[2], hi[3]);
+          tc::ldsm_x4(alo + mt * 16 * kXP * 2 + ks * 32, lo[0], lo[1], lo[2], lo[3]);
+          tc::mma_bf16(d[mt], hi, b0, b1);
+          tc::mma_bf16(e[mt], lo, b0, b1);
+        }
       }
       const int col = nt * 8 + 2 * t;
       const float c0b = a.b0[col], c1b = a.b0[col + 1];
-      hid[g][col] = fmaxf(d[0] + e[0] + c0b, 0.f);
-      hid[g][col + 1] = fmaxf(d[1] + e[1] + c1b, 0.f);
-      hid[g + 8][col] = fmaxf(d[2] + e[2] + c0b, 0.f);
-      hid[g + 8][col + 1] = fmaxf(d[3] + e[3] + c1b, 0.f);
+#pragma unroll
+      for (int mt = 0; mt < kHeadClips / 16; ++mt) {
+        hid[16 * mt + g][col] = fmaxf(d[mt][0] + e[mt][0] + c0b, 0.f);
+        hid[16 * mt + g][col + 1] = fmaxf(d[mt][1] + e[mt][1] + c1b, 0.f);
+        hid[16 * mt + g + 8][col] = fmaxf(d[mt][2] + e[mt][2] + c0b, 0.f);
+        hid[16 * mt + g + 8][col + 1] = fmaxf(d[mt][3] + e[mt][3] + c1b, 0.f);
+      }
       if (nt + kHeadThreads / 32 < ntot) {
 #pragma unroll
-        for (int ks = 0; ks < 2 * BE / 16; ++ks) { b[ks][0] = bn[ks][0]; b[ks][1] = bn[ks][1]; }
+        for (int kp = 0; kp < 2 * BE / 32; ++kp) b[kp] = bn[kp];
       }
     }
   }
@@ -173,7 +215,12 @@ int launch_head_pooled(const Bf16Ctx& x, float* logits) {
   a.logits = logits;
   a.B = c.B; a.C = c.C; a.gated = c.head_kind == XATTN_HEAD_GATED;
   a.HW = a.gated ? c.E : c.common_dim;
-  head_pooled_kernel<<<(c.B + kHeadClips - 1) / kHeadClips, kHeadThreads, 0, x.st>>>(a);
+  static bool configured = false;
+  if (!configured) {
+    XF_CUDA(cudaFuncSetAttribute(head_pooled_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kHeadSmem));
+    configured = true;
+  }
+  head_pooled_kernel<<<(c.B + kHeadClips - 1) / kHeadClips, kHeadThreads, kHeadSmem, x.st>>>(a);
   count_launch();
   XF_LAUNCH_CHECK();
   return XATTN_OK;
