@@ -58,9 +58,9 @@ def stage_model():
 
 
 # dram__bytes_read.sum + dram__bytes_write.sum per launch at B=4096 from the committed `ncu --set full` capture
-# (profiles/r01_ncu_full_bf16_v3.csv); reported as roofline.traffic only when the bench runs that batch.
-NCU_TRAFFIC_B4096 = {"gemm_v0": 73.0e6, "gemm_a0": 1095.1e6, "video_pre": 50.1e6, "v2a_attn": 269.1e6, "video_update": 198.1e6,
-                     "a2v_attn": 309.9e6}
+# (profiles/r01_ncu_full_bf16_v4.csv); reported as roofline.traffic only when the bench runs that batch.
+NCU_TRAFFIC_B4096 = {"gemm_v0": 71.3e6, "gemm_a0": 1094.4e6, "video_pre": 52.1e6, "prior": 14.7e6, "v2a_attn": 270.3e6,
+                     "a2v_attn": 306.1e6, "head": 19.0e6}
 
 METRIC = "xattn fusion clips/sec at 1/2/4/8 B200; % of tensor/HBM roofline vs CPU ref"
 
