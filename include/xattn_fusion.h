@@ -26,7 +26,7 @@
 extern "C" {
 #endif
 
-#define XATTN_ABI_VERSION 6
+#define XATTN_ABI_VERSION 7
 
 #if defined(__GNUC__)
 #define XATTN_API __attribute__((visibility("default")))
@@ -179,6 +179,8 @@ typedef struct flat_head_config {
   int32_t C;
   int32_t gated;            /* 0: mode="concat" (fusion.py:243-248), 1: mode="gated" (:252-259)         */
   int32_t io_dtype;
+  int32_t precision;        /* XATTN_DTYPE_F32: fp32 SIMT arithmetic; XATTN_DTYPE_BF16: temporal mean -> bf16, every Linear
+                               of width >= 128 on the tcgen05 projection GEMM (bf16 embeddings, dims %% 64 / %% 128) */
 } flat_head_config;
 
 typedef enum flat_param_id {

@@ -12,7 +12,7 @@ from pathlib import Path
 
 LIB_NAME = "libxattn_fusion.so"
 LIB_PATH = Path(__file__).resolve().parent / LIB_NAME
-ABI_VERSION = 6
+ABI_VERSION = 7
 
 # xattn_status
 OK, ERR_SHAPE, ERR_DTYPE, ERR_ALIGN, ERR_ARCH, ERR_CUDA, ERR_WORKSPACE, ERR_NULL = range(8)
@@ -66,7 +66,8 @@ class XAttnConfig(C.Structure):
 
 
 class FlatHeadConfig(C.Structure):
-    _fields_ = [(n, C.c_int32) for n in ("B", "T", "Ta", "Dv", "Da", "align_dim", "common_dim", "C", "gated", "io_dtype")]
+    _fields_ = [(n, C.c_int32) for n in ("B", "T", "Ta", "Dv", "Da", "align_dim", "common_dim", "C", "gated", "io_dtype",
+                                                 "precision")]
 
 
 _EXPORTS = {

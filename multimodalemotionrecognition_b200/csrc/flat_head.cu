@@ -4,6 +4,7 @@
 // [B,Ta,Da] embeddings the xattn head reads — an HBM-bound streaming reduction with 128-bit loads.
 // Eval-mode forward (ModalityDropout and Dropout are identity; the alignment loss is a training-only output).
 #include "gemm_simt.cuh"
+#include "gemm_tc.cuh"
 
 namespace xf {
 
@@ -37,11 +38,18 @@ static int flat_validate(const flat_head_config* c) {
   if (c->B < 0 || c->T <= 0 || c->Ta <= 0 || c->Dv <= 0 || c->Da <= 0 || c->common_dim <= 0 || c->C <= 0 || c->align_dim < 0)
     XF_FAIL(XATTN_ERR_SHAPE, "bad flat head dimensions");
   if (c->io_dtype != XATTN_DTYPE_F32 && c->io_dtype != XATTN_DTYPE_BF16) XF_FAIL(XATTN_ERR_DTYPE, "unknown io_dtype %d", c->io_dtype);
+  if (c->precision != XATTN_DTYPE_F32 && c->precision != XATTN_DTYPE_BF16) XF_FAIL(XATTN_ERR_DTYPE, "unknown precision %d", c->precision);
+  if (c->precision == XATTN_DTYPE_BF16) {   // tcgen05 projection GEMMs: bf16 embeddings, K %% 64 == 0, N %% 128 == 0
+    const int in_a = c->align_dim > 0 ? c->align_dim : c->Da, in_v = c->align_dim > 0 ? c->align_dim : c->Dv;
+    if (c->io_dtype != XATTN_DTYPE_BF16 || c->Da % 64 || c->Dv % 64 || c->align_dim % 128 || c->common_dim % 128 || in_a % 64 || in_v % 64)
+      XF_FAIL(XATTN_ERR_SHAPE, "flat heads, precision = BF16: bf16 embeddings with Da, Dv %% 64 == 0 and align_dim, common_dim %% 128 == 0 only");
+  }
   return XATTN_OK;
 }
 
 struct FlatWs {
-  int64_t a_pool, v_pool, a_al, v_al, cat, hid, z, total;
+  int64_t a_pool, v_pool, a_al, v_al, cat, hid, z, total;   // offsets in floats
+  int64_t wbf;                                               // precision = BF16: bf16 copy of the parameter buffer
 };
 static void flat_ws(const flat_head_config& c, FlatWs& w) {
   const int64_t B = c.B, A = c.align_dim > 0 ? c.align_dim : 1, Cm = c.common_dim;
@@ -49,13 +57,22 @@ static void flat_ws(const flat_head_config& c, FlatWs& w) {
   auto take = [&](int64_t n) { int64_t o = off; off += al4(n); return o; };
   w.a_pool = take(B * c.Da); w.v_pool = take(B * c.Dv); w.a_al = take(B * A); w.v_al = take(B * A);
   w.cat = take(B * 2 * Cm); w.hid = take(B * Cm); w.z = take(B);
+  w.wbf = off;
+  if (c.precision == XATTN_DTYPE_BF16) {   // (the activation slots above are reused as bf16: half of each is spare)
+    FlatLayout pl;
+    flat_layout(c, pl);
+    take((pl.total + 1) / 2);
+  }
   w.total = off;
 }
 
+__device__ __forceinline__ void store_out(float* p, float v) { *p = v; }
+__device__ __forceinline__ void store_out(__nv_bfloat16* p, float v) { *p = __float2bfloat16_rn(v); }
+
 // Temporal mean over [B,L,D] -> [B,D]; each thread owns VEC consecutive channels (one 128-bit load per row),
 // a CTA covers one clip's channel slab; rows unrolled x4 for memory-level parallelism.
-template <typename TIO>
-__global__ void __launch_bounds__(128) temporal_mean_kernel(const TIO* __restrict__ x, float* __restrict__ out, int L, int D) {
+template <typename TIO, typename TOUT>
+__global__ void __launch_bounds__(128) temporal_mean_kernel(const TIO* __restrict__ x, TOUT* __restrict__ out, int L, int D) {
   constexpr int VEC = 16 / sizeof(TIO);
   const int b = blockIdx.y;
   const int c0 = (blockIdx.x * blockDim.x + threadIdx.x) * VEC;
@@ -88,15 +105,15 @@ __global__ void __launch_bounds__(128) temporal_mean_kernel(const TIO* __restric
       for (int i = 0; i < VEC && c0 + i < D; ++i) acc[i] += to_f32(base[(int64_t)l * D + i]);
   }
   const float inv = 1.f / (float)L;
-  for (int i = 0; i < VEC && c0 + i < D; ++i) out[(int64_t)b * D + c0 + i] = acc[i] * inv;
+  for (int i = 0; i < VEC && c0 + i < D; ++i) store_out(out + (int64_t)b * D + c0 + i, acc[i] * inv);
 }
 
-template <typename TIO>
-static void launch_mean(cudaStream_t st, const TIO* x, float* out, int B, int L, int D) {
+template <typename TIO, typename TOUT>
+static void launch_mean(cudaStream_t st, const TIO* x, TOUT* out, int B, int L, int D) {
   constexpr int VEC = 16 / sizeof(TIO);
   const int threads_needed = (D + VEC - 1) / VEC;
   dim3 grid((threads_needed + 127) / 128, B);
-  temporal_mean_kernel<TIO><<<grid, 128, 0, st>>>(x, out, L, D);
+  temporal_mean_kernel<TIO, TOUT><<<grid, 128, 0, st>>>(x, out, L, D);
   count_launch();
 }
 
@@ -127,8 +144,8 @@ static int flat_forward_impl(const flat_head_config& c, const float* params, con
   flat_ws(c, w);
   auto P = [&](int id) { return params + pl.off[id]; };
   const int B = c.B, Cm = c.common_dim, A = c.align_dim;
-  launch_mean<TIO>(st, xa, ws + w.a_pool, B, c.Ta, c.Da);
-  launch_mean<TIO>(st, xv, ws + w.v_pool, B, c.T, c.Dv);
+  launch_mean<TIO, float>(st, xa, ws + w.a_pool, B, c.Ta, c.Da);
+  launch_mean<TIO, float>(st, xv, ws + w.v_pool, B, c.T, c.Dv);
   const float* a_in = ws + w.a_pool;
   const float* v_in = ws + w.v_pool;
   int in_a = c.Da, in_v = c.Dv;
@@ -148,6 +165,89 @@ static int flat_forward_impl(const flat_head_config& c, const float* params, con
     flat_gate_cls_kernel<<<B, 256, sizeof(float) * Cm, st>>>(ws + w.cat, ws + w.z, P(FP_CLS_W), P(FP_CLS_B), logits, Cm, c.C);
     count_launch();
   }
+  XF_LAUNCH_CHECK();
+  return XATTN_OK;
+}
+
+// ---- precision = BF16: the same op sequence with every Linear of width >= 128 on the tcgen05 projection GEMM (gemm_tc.cu) ----
+__global__ void __launch_bounds__(256) cvt_f32_bf16_kernel(const float* __restrict__ x, __nv_bfloat16* __restrict__ y, int64_t n) {
+  const int64_t i = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) * 4;
+  if (i + 4 <= n) {
+    const float4 v = *reinterpret_cast<const float4*>(x + i);
+    __nv_bfloat162 lo = __floats2bfloat162_rn(v.x, v.y), hi = __floats2bfloat162_rn(v.z, v.w);
+    *reinterpret_cast<uint2*>(y + i) = make_uint2(*reinterpret_cast<uint32_t*>(&lo), *reinterpret_cast<uint32_t*>(&hi));
+  } else {
+    for (int64_t k = i; k < n; ++k) y[k] = __float2bfloat16_rn(x[k]);
+  }
+}
+
+// Last layer(s), one warp per clip (fusion.py:427-435): concat: logits = W1·hid + b1.  gated: z = w1·hid + b1, g = sigmoid(z),
+// fused = g·a + (1-g)·v with [a | v] = cat (bf16), logits = Wc·fused + bc.
+__global__ void __launch_bounds__(256) flat_out_kernel(const float* __restrict__ hid, const __nv_bfloat16* __restrict__ cat,
+                                                       const float* __restrict__ w1, const float* __restrict__ b1,
+                                                       const float* __restrict__ wc, const float* __restrict__ bc,
+                                                       float* __restrict__ logits, int B, int Cm, int C, int gated) {
+  const int lane = threadIdx.x & 31;
+  const int b = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (b >= B) return;
+  const float* h = hid + (int64_t)b * Cm;
+  if (!gated) {
+    for (int c = 0; c < C; ++c) {
+      float s = 0.f;
+      for (int k = lane; k < Cm; k += 32) s = fmaf(__ldg(w1 + (int64_t)c * Cm + k), h[k], s);
+      s = warp_sum(s);
+      if (lane == 0) logits[(int64_t)b * C + c] = s + __ldg(b1 + c);
+    }
+    return;
+  }
+  float z = 0.f;
+  for (int k = lane; k < Cm; k += 32) z = fmaf(__ldg(w1 + k), h[k], z);
+  z = warp_sum(z) + __ldg(b1);
+  const float g = 1.f / (1.f + expf(-z));
+  const __nv_bfloat16* cr = cat + (int64_t)b * 2 * Cm;
+  for (int c = 0; c < C; ++c) {
+    float s = 0.f;
+    for (int k = lane; k < Cm; k += 32) {
+      const float f = g * __bfloat162float(cr[k]) + (1.f - g) * __bfloat162float(cr[Cm + k]);
+      s = fmaf(__ldg(wc + (int64_t)c * Cm + k), f, s);
+    }
+    s = warp_sum(s);
+    if (lane == 0) logits[(int64_t)b * C + c] = s + __ldg(bc + c);
+  }
+}
+
+static int flat_forward_tc(const flat_head_config& c, const float* params, const __nv_bfloat16* xv, const __nv_bfloat16* xa, float* logits,
+                           float* ws, cudaStream_t st) {
+  FlatLayout pl;
+  flat_layout(c, pl);
+  FlatWs w;
+  flat_ws(c, w);
+  auto P = [&](int id) { return params + pl.off[id]; };
+  __nv_bfloat16* wbf = reinterpret_cast<__nv_bfloat16*>(ws + w.wbf);
+  auto PB = [&](int id) { return wbf + pl.off[id]; };
+  auto BF = [&](int64_t off) { return reinterpret_cast<__nv_bfloat16*>(ws + off); };
+  const int B = c.B, Cm = c.common_dim, A = c.align_dim;
+  for (int id : {FP_ALIGN_A_W, FP_ALIGN_V_W, FP_AUDIO_W, FP_VIDEO_W, FP_H0_W})
+    if (pl.off[id] % 8 != 0) XF_FAIL(XATTN_ERR_ALIGN, "flat heads, precision = BF16: weight %d is not 16-byte aligned in the bf16 copy", id);
+  cvt_f32_bf16_kernel<<<(unsigned)((pl.total / 4 + 255) / 256 + 1), 256, 0, st>>>(params, wbf, pl.total);
+  count_launch();
+  launch_mean<__nv_bfloat16, __nv_bfloat16>(st, xa, BF(w.a_pool), B, c.Ta, c.Da);
+  launch_mean<__nv_bfloat16, __nv_bfloat16>(st, xv, BF(w.v_pool), B, c.T, c.Dv);
+  const __nv_bfloat16* a_in = BF(w.a_pool);
+  const __nv_bfloat16* v_in = BF(w.v_pool);
+  int in_a = c.Da, in_v = c.Dv;
+  if (A > 0) {  // ClipStyleAlignment projections, fusion.py:138-139
+    XF_TRY(gemm_tc_bf16(st, a_in, PB(FP_ALIGN_A_W), P(FP_ALIGN_A_B), BF(w.a_al), true, A, B, A, c.Da));
+    XF_TRY(gemm_tc_bf16(st, v_in, PB(FP_ALIGN_V_W), P(FP_ALIGN_V_B), BF(w.v_al), true, A, B, A, c.Dv));
+    a_in = BF(w.a_al); v_in = BF(w.v_al); in_a = in_v = A;
+  }
+  // audio_proj / video_proj written side by side: cat = [a | v] (fusion.py:421-425)
+  XF_TRY(gemm_tc_bf16(st, a_in, PB(FP_AUDIO_W), P(FP_AUDIO_B), BF(w.cat), true, 2 * Cm, B, Cm, in_a));
+  XF_TRY(gemm_tc_bf16(st, v_in, PB(FP_VIDEO_W), P(FP_VIDEO_B), BF(w.cat) + Cm, true, 2 * Cm, B, Cm, in_v));
+  XF_TRY(gemm_tc_bf16(st, BF(w.cat), PB(FP_H0_W), P(FP_H0_B), ws + w.hid, false, Cm, B, Cm, 2 * Cm, nullptr, nullptr, nullptr, 0, true));
+  flat_out_kernel<<<(B + 7) / 8, 256, 0, st>>>(ws + w.hid, BF(w.cat), P(FP_H1_W), P(FP_H1_B), P(FP_CLS_W), P(FP_CLS_B), logits, B, Cm,
+                                              c.C, c.gated);
+  count_launch();
   XF_LAUNCH_CHECK();
   return XATTN_OK;
 }
@@ -190,6 +290,8 @@ extern "C" XATTN_API int flat_head_forward(const flat_head_config* cfg, const fl
     XF_FAIL(XATTN_ERR_WORKSPACE, "workspace too small: %lld < %lld bytes", (long long)workspace_bytes, (long long)(w.total * 4));
   if (cfg->B == 0) return XATTN_OK;
   cudaStream_t st = (cudaStream_t)stream;
+  if (cfg->precision == XATTN_DTYPE_BF16)
+    return flat_forward_tc(*cfg, params, (const __nv_bfloat16*)video_emb, (const __nv_bfloat16*)audio_emb, logits, (float*)workspace, st);
   if (cfg->io_dtype == XATTN_DTYPE_BF16)
     return flat_forward_impl<__nv_bfloat16>(*cfg, params, (const __nv_bfloat16*)video_emb, (const __nv_bfloat16*)audio_emb, logits,
                                             (float*)workspace, st);

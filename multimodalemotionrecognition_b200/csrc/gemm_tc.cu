@@ -70,6 +70,7 @@ struct GemmExtras {
   const float* wc;             // [4][128] + [4]: c_hi = y·wc_h + wc[512 + h]
   float *cv, *pooled;          // [clips][64], [clips][256] (first 128 = temporal mean)
   int T, clips;
+  int relu;                    // EPI_F32 / EPI_BF16: y = max(y, 0) after the bias
 };
 
 // One step of the transpose-reduce over lanes: x[0..N) (+)= the partner's other half; N values remain.
@@ -206,6 +207,7 @@ __global__ void __launch_bounds__(gemm_threads(EPG), 1) gemm_tc_kernel(const __g
         static_assert(EPG == 1 || HEADROWS || LNRES, "the bias slice is shared by the groups");
         tc::named_bar_sync(2, 128);
         bias_s[et] = __ldg(bias + n0 + et);
+        if (EPI == EPI_F32 || EPI == EPI_BF16) bias_s[1024 + et] = 0.f;
         cur_n0 = n0;
         tc::named_bar_sync(2, 128);   // (also publishes scw_s / the LayerNorm vectors on the first pass)
       }
@@ -329,6 +331,15 @@ __global__ void __launch_bounds__(gemm_threads(EPG), 1) gemm_tc_kernel(const __g
             sc1 = fmaf(y, w.y, sc1);
           }
         }
+        if (EPI == EPI_F32 || EPI == EPI_BF16) {   // bias (+ ReLU) in place; the stores below then add nothing
+#pragma unroll
+          for (int i = 0; i < 32; ++i) {
+            float y = __uint_as_float(r[i]) + bs[c + i];
+            if (ex.relu) y = fmaxf(y, 0.f);
+            r[i] = __float_as_uint(y);
+          }
+        }
+        const float* bq = (EPI == EPI_F32 || EPI == EPI_BF16) ? bias_s + 1024 : bs;   // (zeros: the bias is already in)
         if (OUT_BF16) {
           // direct rows: 32 columns = 64 bytes = two whole sectors per lane
           __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(out) + (int64_t)m * out_pitch + n0 + c;
@@ -336,7 +347,7 @@ __global__ void __launch_bounds__(gemm_threads(EPG), 1) gemm_tc_kernel(const __g
             uint32_t pk[16];
 #pragma unroll
             for (int v = 0; v < 16; ++v)
-              pk[v] = tc::pack_bf16(__uint_as_float(r[2 * v]) + bs[c + 2 * v], __uint_as_float(r[2 * v + 1]) + bs[c + 2 * v + 1]);
+              pk[v] = tc::pack_bf16(__uint_as_float(r[2 * v]) + bq[c + 2 * v], __uint_as_float(r[2 * v + 1]) + bq[c + 2 * v + 1]);
             if (STAGED) {   // 16-byte chunk q of the row -> box q / 8, slot (q % 8) ^ (row % 8)
 #pragma unroll
               for (int v = 0; v < 4; ++v) {
@@ -358,18 +369,18 @@ __global__ void __launch_bounds__(gemm_threads(EPG), 1) gemm_tc_kernel(const __g
           if ((reinterpret_cast<uintptr_t>(o) & 31) == 0) {
 #pragma unroll
             for (int v = 0; v < 4; ++v)
-              tc::stg256f(o + 8 * v, __uint_as_float(r[8 * v + 0]) + bs[c + 8 * v + 0], __uint_as_float(r[8 * v + 1]) + bs[c + 8 * v + 1],
-                          __uint_as_float(r[8 * v + 2]) + bs[c + 8 * v + 2], __uint_as_float(r[8 * v + 3]) + bs[c + 8 * v + 3],
-                          __uint_as_float(r[8 * v + 4]) + bs[c + 8 * v + 4], __uint_as_float(r[8 * v + 5]) + bs[c + 8 * v + 5],
-                          __uint_as_float(r[8 * v + 6]) + bs[c + 8 * v + 6], __uint_as_float(r[8 * v + 7]) + bs[c + 8 * v + 7]);
+              tc::stg256f(o + 8 * v, __uint_as_float(r[8 * v + 0]) + bq[c + 8 * v + 0], __uint_as_float(r[8 * v + 1]) + bq[c + 8 * v + 1],
+                          __uint_as_float(r[8 * v + 2]) + bq[c + 8 * v + 2], __uint_as_float(r[8 * v + 3]) + bq[c + 8 * v + 3],
+                          __uint_as_float(r[8 * v + 4]) + bq[c + 8 * v + 4], __uint_as_float(r[8 * v + 5]) + bq[c + 8 * v + 5],
+                          __uint_as_float(r[8 * v + 6]) + bq[c + 8 * v + 6], __uint_as_float(r[8 * v + 7]) + bq[c + 8 * v + 7]);
           } else {
 #pragma unroll
             for (int v = 0; v < 8; ++v) {
               float4 f;
-              f.x = __uint_as_float(r[4 * v + 0]) + bs[c + 4 * v + 0];
-              f.y = __uint_as_float(r[4 * v + 1]) + bs[c + 4 * v + 1];
-              f.z = __uint_as_float(r[4 * v + 2]) + bs[c + 4 * v + 2];
-              f.w = __uint_as_float(r[4 * v + 3]) + bs[c + 4 * v + 3];
+              f.x = __uint_as_float(r[4 * v + 0]) + bq[c + 4 * v + 0];
+              f.y = __uint_as_float(r[4 * v + 1]) + bq[c + 4 * v + 1];
+              f.z = __uint_as_float(r[4 * v + 2]) + bq[c + 4 * v + 2];
+              f.w = __uint_as_float(r[4 * v + 3]) + bq[c + 4 * v + 3];
               *reinterpret_cast<float4*>(o + 4 * v) = f;
             }
           }
@@ -506,15 +517,16 @@ int make_tmap_bf16_3d(void* tmap_out, const void* base, int64_t d0, int64_t d1, 
 }
 
 int gemm_tc_bf16(cudaStream_t st, const void* X, const void* W, const float* bias, void* out, bool out_bf16, int64_t out_pitch,
-                 int M, int N, int K, const float* sc_w, float* tok, float* colsum, int seg_len) {
+                 int M, int N, int K, const float* sc_w, float* tok, float* colsum, int seg_len, bool relu) {
   if (M <= 0) return XATTN_OK;
   const bool extras = sc_w != nullptr;
-  const bool staged = out_bf16 && N == BN && out_pitch == BN;
-  if (extras && !(staged && seg_len > 0 && M % seg_len == 0 &&
+  const bool staged0 = out_bf16 && N == BN && out_pitch == BN;
+  if (extras && !(staged0 && !relu && seg_len > 0 && M % seg_len == 0 &&
                   (seg_len + 30) / 32 + 1 <= kColsumSlots && seg_len <= kTokPitch))
     XF_FAIL(XATTN_ERR_SHAPE, "projection GEMM extras need dense bf16 output with N == 128 and rows in clips of <= 160 tokens");
   GemmExtras ex{};
-  ex.sc_w = sc_w; ex.tok = tok; ex.colsum = colsum; ex.seg_len = seg_len;
+  ex.sc_w = sc_w; ex.tok = tok; ex.colsum = colsum; ex.seg_len = seg_len; ex.relu = relu ? 1 : 0;
+  const bool staged = !relu && staged0;
   if (N % BN != 0 || K % BK != 0)
     XF_FAIL(XATTN_ERR_SHAPE, "tcgen05 projection GEMM needs N %% 128 == 0 and K %% 64 == 0 (N=%d K=%d)", N, K);
   if (out_pitch < N || (out_bf16 && out_pitch % 8 != 0) || (!out_bf16 && out_pitch % 4 != 0))

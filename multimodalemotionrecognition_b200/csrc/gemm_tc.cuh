@@ -4,7 +4,7 @@
 
 namespace xf {
 // Y[M,N] = X[M,K]·W[N,K]^T + bias.  X, W: bf16, K contiguous, 16-byte aligned.  out: bf16 or fp32 with row pitch
-// `out_pitch` (elements).  N % 128 == 0, K % 64 == 0.
+// `out_pitch` (elements).  N % 128 == 0, K % 64 == 0.  relu: Y = max(Y, 0) (plain epilogues only).
 // Optional extras (sc_w != nullptr; bf16 output with N == 128 only), computed in the epilogue from the tile it holds:
 //   tok[i][clip][j] (two planes, kTokPitch floats per clip) = sc_w[i,:]·y_m for row m = clip*seg_len + j, from the fp32 row
 //   colsum[clip][slot][128] = sum of the rows of `clip` (rows m in [clip*seg_len, +seg_len)) inside the 32-row group
@@ -12,7 +12,8 @@ namespace xf {
 constexpr int kColsumSlots = 6;
 constexpr int kTokPitch = 160;   // floats per clip in each tok plane
 int gemm_tc_bf16(cudaStream_t st, const void* X, const void* W, const float* bias, void* out, bool out_bf16, int64_t out_pitch,
-                 int M, int N, int K, const float* sc_w = nullptr, float* tok = nullptr, float* colsum = nullptr, int seg_len = 0);
+                 int M, int N, int K, const float* sc_w = nullptr, float* tok = nullptr, float* colsum = nullptr, int seg_len = 0,
+                 bool relu = false);
 // Video-side update as two GEMMs over weights folded at pack time (bf16_pack.cu), rows = (clip, token slot), 16 slots per clip:
 //   video_mix: v1 = LayerNorm(v0 + U[16·clips, 512]·G[128, 512]^T + bias) as bf16 [16·clips, 128]  (fusion.py:394-395);
 //              pooled[clip][0..128) = mean over the T real slots (:401); cv[clip][16h + i] = v1_i·wc[h] + wc[512 + h]

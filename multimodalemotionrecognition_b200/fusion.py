@@ -445,7 +445,11 @@ class FlatHeadKernelsMixin:
     """``mode in {"concat","gated"}`` heads (``fusion.py:226-260``, ``:413-435``) on the CUDA extension (eval forward)."""
 
     def _build_flat(self, *, audio_dim: int, video_dim: int, num_classes: int, common_dim: int, mode: str,
-                    fusion_align_mode: str, fusion_align_dim: int, fusion_align_temperature: float) -> None:
+                    fusion_align_mode: str, fusion_align_dim: int, fusion_align_temperature: float,
+                    precision: str = "auto") -> None:
+        if precision not in ("auto", "fp32", "bf16"):
+            raise ValueError(f"precision must be auto|fp32|bf16, got {precision}")
+        self._flat_precision = precision
         self._flat_audio_dim, self._flat_video_dim = audio_dim, video_dim
         self._flat_common, self._flat_classes = common_dim, num_classes
         fusion_audio_dim, fusion_video_dim = audio_dim, video_dim
@@ -477,7 +481,26 @@ class FlatHeadKernelsMixin:
         cfg.B, cfg.T, cfg.Ta, cfg.Dv, cfg.Da = B, T, Ta, self._flat_video_dim, self._flat_audio_dim
         cfg.align_dim, cfg.common_dim, cfg.C = self._flat_align, self._flat_common, self._flat_classes
         cfg.gated, cfg.io_dtype = int(self._flat_gated), io_dtype
+        cfg.precision = self._flat_pick_precision(io_dtype)
         return cfg
+
+    def _flat_tc_supported(self) -> bool:
+        """Dimensions the tcgen05 projection GEMM takes (K % 64 == 0, N % 128 == 0)."""
+        a, cm = self._flat_align, self._flat_common
+        in_a = a if a > 0 else self._flat_audio_dim
+        in_v = a if a > 0 else self._flat_video_dim
+        return (self._flat_audio_dim % 64 == 0 and self._flat_video_dim % 64 == 0 and a % 128 == 0 and cm % 128 == 0
+                and in_a % 64 == 0 and in_v % 64 == 0)
+
+    def _flat_pick_precision(self, io_dtype: int) -> int:
+        """``auto``: bf16 embeddings at supported dimensions run the tensor-core path (bf16 operands, fp32 accumulate);
+        everything else the fp32 kernels.  ``bf16`` forces the tensor-core path (the library raises if it cannot)."""
+        mode = getattr(self, "_flat_precision", "auto")
+        if mode == "fp32":
+            return _lib.DTYPE_F32
+        if mode == "bf16":
+            return _lib.DTYPE_BF16
+        return _lib.DTYPE_BF16 if io_dtype == _lib.DTYPE_BF16 and self._flat_tc_supported() else _lib.DTYPE_F32
 
     def _flat_params(self, dev) -> torch.Tensor:
         own = dict(self.named_parameters(recurse=True))
@@ -534,14 +557,14 @@ class FlatFusionHead(FlatHeadKernelsMixin, nn.Module):
 
     def __init__(self, num_classes: int = 8, video_dim: int = 512, audio_dim: int = 768, common_dim: int = 256,
                  mode: str = "concat", fusion_align_mode: str = "clip", fusion_align_dim: int = 256,
-                 fusion_align_temperature: float = 0.07) -> None:
+                 fusion_align_temperature: float = 0.07, precision: str = "auto") -> None:
         super().__init__()
         if mode not in ("concat", "gated"):
             raise ValueError(f"Unknown fusion mode: {mode}")
         self.mode = mode
         self._build_flat(audio_dim=audio_dim, video_dim=video_dim, num_classes=num_classes, common_dim=common_dim, mode=mode,
                          fusion_align_mode=fusion_align_mode, fusion_align_dim=fusion_align_dim,
-                         fusion_align_temperature=fusion_align_temperature)
+                         fusion_align_temperature=fusion_align_temperature, precision=precision)
 
     def forward(self, video_emb: torch.Tensor, audio_emb: torch.Tensor) -> torch.Tensor:
         return self.flat_forward_sequences(video_emb, audio_emb)
@@ -577,7 +600,8 @@ class FusionModel(XAttnKernelsMixin, FlatHeadKernelsMixin, nn.Module):
         if mode in {"concat", "gated"}:
             self._build_flat(audio_dim=audio_model.embedding_dim, video_dim=video_model.embedding_dim, num_classes=num_classes,
                              common_dim=common_dim, mode=mode, fusion_align_mode=fusion_align_mode,
-                             fusion_align_dim=fusion_align_dim, fusion_align_temperature=fusion_align_temperature)
+                             fusion_align_dim=fusion_align_dim, fusion_align_temperature=fusion_align_temperature,
+                             precision=precision)
         if mode in _XATTN_MODES:
             self._build_xattn(v_dim=getattr(video_model, "embedding_dim", 512),
                               audio_sequence_dim=getattr(audio_model, "sequence_dim", d_model), num_classes=num_classes,

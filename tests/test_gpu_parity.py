@@ -5,6 +5,7 @@ import pytest
 import torch
 
 from helpers import config1_inputs, digest, fusion_state_np, load_npz, make_head, tiny_head
+from multimodalemotionrecognition_b200 import _lib
 from oracle import torch_port, xattn_oracle
 
 pytestmark = pytest.mark.gpu
@@ -320,8 +321,17 @@ def test_flat_heads_match_reference(cuda_device, mode):
     # bf16 sequence inputs with the fused temporal mean vs the oracle on the same rounded inputs
     xa = torch.randn(9, 149, 768, generator=g).bfloat16()
     xv = torch.randn(9, 16, 512, generator=g).bfloat16()
+    mm._flat_precision = "fp32"
     with torch.no_grad():
         out = mm(xv.to(cuda_device), xa.to(cuda_device)).cpu().numpy()
     sd = {k: v.cpu().numpy() for k, v in mm.state_dict().items()}
     ref = xattn_oracle.flat_head_forward(sd, xa.float().numpy().mean(1), xv.float().numpy().mean(1), mode=mode)
     assert np.abs(out - ref).max() <= FP32_TOL
+    # the same on the tensor-core path (precision="auto" picks it for bf16 embeddings): bf16 operands, fp32 accumulate
+    mm._flat_precision = "auto"
+    n0 = _lib.launch_count()
+    with torch.no_grad():
+        out_tc = mm(xv.to(cuda_device), xa.to(cuda_device)).cpu().numpy()
+    assert _lib.launch_count() - n0 == 9     # cvt + 2 means + 5 tcgen05 GEMMs + output kernel
+    assert np.abs(out_tc - ref).max() <= BF16_TOL
+    assert np.abs(out_tc - ref).max() > 0    # (a different code path really ran)
