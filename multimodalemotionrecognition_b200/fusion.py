@@ -105,6 +105,39 @@ class _XAttnFunction(torch.autograd.Function):
         return (None, None, None, *grads)
 
 
+class GraphedForward:
+    """One CUDA graph of the bf16 forward at a fixed batch size ("CUDA-graph per batch size").
+
+    Below a few hundred clips a forward is bound by the host issuing its 9 launches, not by the device.  The graph is
+    captured once over static device buffers (``video``, ``audio`` -> ``logits`` / ``probs``); a call is then one
+    ``cudaGraphLaunch``.  Fill ``video`` / ``audio`` (e.g. ``copy_(host, non_blocking=True)``), call the object, read
+    ``logits`` — all on the current stream.  The graph holds the packed-weight pointers: it is only valid while ``key``
+    matches the head's ``_xattn_packed_key`` (``XAttnKernelsMixin.graphed_forward`` re-captures when parameters change).
+    """
+
+    def __init__(self, head: "XAttnKernelsMixin", B: int, T: int, Ta: int, dtype: torch.dtype, device: torch.device) -> None:
+        self.B, self.key = B, None
+        with torch.cuda.device(device), torch.no_grad():
+            self.video = torch.zeros((B, T, head.v_dim), dtype=dtype, device=device)
+            self.audio = torch.zeros((B, Ta, head.audio_sequence_dim), dtype=dtype, device=device)
+            self.logits = torch.empty((B, head.num_classes), dtype=torch.float32, device=device)
+            side = torch.cuda.Stream(device)
+            side.wait_stream(torch.cuda.current_stream(device))
+            with torch.cuda.stream(side):     # warm-up outside the capture: packs weights, sets kernel attributes
+                for _ in range(2):
+                    head._launch_forward(self.video, self.audio, save=False, training=False, out=self.logits)
+            torch.cuda.current_stream(device).wait_stream(side)
+            self.key = head._xattn_packed_key
+            self.graph = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(self.graph):
+                head._launch_forward(self.video, self.audio, save=False, training=False, out=self.logits)
+                self.probs = torch.softmax(self.logits, dim=1)
+
+    def __call__(self) -> torch.Tensor:
+        self.graph.replay()
+        return self.logits
+
+
 class XAttnKernelsMixin:
     """Builds the xattn parameters under the reference's names and runs them through the C ABI."""
 
@@ -171,11 +204,27 @@ class XAttnKernelsMixin:
 
     # ---- config / parameter plumbing ------------------------------------------------------------------------------
     def _xattn_named_params(self) -> list[Optional[nn.Parameter]]:
-        own = dict(self.named_parameters(recurse=True))
-        out = []
-        for name in _lib.xattn_param_names(self.xattn_head):
-            out.append(own.get(name))
-        return out
+        """The Parameters in flat-buffer order.  Resolved once and re-validated per call by identity against the owning
+        module's ``_parameters`` dict (cheap), so replacing a Parameter object is still noticed."""
+        cache = getattr(self, "_xattn_param_cache", None)
+        if cache is not None:
+            for owner, key, p in cache:
+                if owner is not None and owner._parameters.get(key) is not p:
+                    cache = None
+                    break
+        if cache is None:
+            cache = []
+            for name in _lib.xattn_param_names(self.xattn_head):
+                owner, _, key = name.rpartition(".")
+                try:
+                    mod = self.get_submodule(owner) if owner else self
+                except AttributeError:
+                    mod = None
+                p = mod._parameters.get(key) if mod is not None else None
+                cache.append((mod if p is not None else None, key, p))
+            self._xattn_param_cache = cache
+            self._xattn_layout = None
+        return [p for _, _, p in cache]
 
     def _make_cfg(self, B: int, T: int, Ta: int, io_dtype: int, precision: int, training: bool, save: bool) -> _lib.XAttnConfig:
         cfg = _lib.XAttnConfig()
@@ -198,8 +247,11 @@ class XAttnKernelsMixin:
         params = self._xattn_named_params()
         ref = next(p for p in params if p is not None)
         dev = ref.device
-        cfg = self._make_cfg(0, 1, 1, _lib.DTYPE_F32, _lib.DTYPE_F32, False, False)
-        offs, sizes, total = _lib.xattn_param_layout(cfg)
+        layout = getattr(self, "_xattn_layout", None)
+        if layout is None:   # depends on the module's dimensions only
+            layout = _lib.xattn_param_layout(self._make_cfg(0, 1, 1, _lib.DTYPE_F32, _lib.DTYPE_F32, False, False))
+            self._xattn_layout = layout
+        offs, sizes, total = layout
         flat = self._xattn_flat
         ok = flat is not None and flat.device == dev and flat.numel() == total
         if ok:
@@ -330,9 +382,33 @@ class XAttnKernelsMixin:
                                                   _ptr(grads), _ptr(ws), ws.numel(), _stream_ptr(dev)))
         return grads
 
+    def graphed_forward(self, B: int, T: int = 16, Ta: int = 149, dtype: torch.dtype = torch.bfloat16,
+                        device: Optional[torch.device] = None) -> GraphedForward:
+        """The cached ``GraphedForward`` for this batch size (captured on first use, re-captured when the parameters or the
+        packed weights changed).  Inference only; shapes must be ones the bf16 tensor-core path takes."""
+        if device is None:
+            device = next(p for p in self._xattn_named_params() if p is not None).device
+        if self._pick_precision(_lib.DTYPE_BF16 if dtype == torch.bfloat16 else _lib.DTYPE_F32, False, T, Ta) != _lib.DTYPE_BF16:
+            raise ValueError("graphed_forward covers the bf16 tensor-core inference path only")
+        cache = self.__dict__.setdefault("_xattn_graphs", {})
+        k = (B, T, Ta, dtype, device)
+        g = cache.get(k)
+        if g is not None:   # still the same weights?  (cheap: data_ptr + versions, as _packed_weights keys them)
+            flat = self.flat_parameters()
+            params = self._xattn_named_params()
+            key = (flat.data_ptr(), self._xattn_epoch, tuple(0 if p is None else p._version for p in params))
+            if key != g.key:
+                g = None
+        if g is None:
+            if len(cache) >= 16:
+                cache.pop(next(iter(cache)))
+            g = GraphedForward(self, B, T, Ta, dtype, device)
+            cache[k] = g
+        return g
+
     @torch.no_grad()
     def predict_host(self, video_host: torch.Tensor, audio_host: torch.Tensor, chunk: int = 1024,
-                     probs: bool = False) -> torch.Tensor:
+                     probs: bool = False, graph_max: int = 256) -> torch.Tensor:
         """Batch path with HOST buffers, mirroring ``TorchModelRunner.predict_probs`` (``optimized_runtime.py:99-108``:
         ``.to(device)`` -> model -> ``softmax`` -> ``.cpu()``) and the worker's ``torch.stack(...).to(device)``
         (``inference_worker.py:131-134``).  The host batch (pinned memory for full PCIe rate) is cut into ``chunk``-clip
@@ -349,17 +425,30 @@ class XAttnKernelsMixin:
             raise RuntimeError("the B200 xattn fusion head has no CPU path: move the module to an sm_100 device")
         B, T_, Dv = video_host.shape
         Ta_, Da = audio_host.shape[1], audio_host.shape[2]
+        out_buf = getattr(self, "_host_out", None)
+        if out_buf is None or out_buf.shape[0] < B or out_buf.shape[1] != self.num_classes:
+            out_buf = torch.empty((max(B, 1), self.num_classes), dtype=torch.float32).pin_memory()
+            self._host_out = out_buf
+        if 0 < B <= min(graph_max, chunk) and video_host.dtype == torch.bfloat16 and self.precision != "fp32" \
+                and self._bf16_supported(T_, Ta_):
+            # worker-sized batches (inference_worker.py:33-34) are launch-bound: H2D, one graph launch, D2H
+            with torch.cuda.device(dev):
+                g = self.graphed_forward(B, T_, Ta_, video_host.dtype, dev)
+                g.video.copy_(video_host, non_blocking=True)
+                g.audio.copy_(audio_host, non_blocking=True)
+                g()
+                host = out_buf[:B]
+                host.copy_(g.probs if probs else g.logits, non_blocking=True)
+                torch.cuda.current_stream(dev).synchronize()
+            return host
         key = (dev, chunk, T_, Dv, Ta_, Da, video_host.dtype)
         pipe = getattr(self, "_host_pipe", None)
         if pipe is None or pipe["key"] != key:
             pipe = {"key": key, "stream": torch.cuda.Stream(dev),
                     "v": [torch.empty((chunk, T_, Dv), dtype=video_host.dtype, device=dev) for _ in range(2)],
                     "a": [torch.empty((chunk, Ta_, Da), dtype=audio_host.dtype, device=dev) for _ in range(2)],
-                    "ready": [torch.cuda.Event() for _ in range(2)], "done": [torch.cuda.Event() for _ in range(2)],
-                    "out": None}
+                    "ready": [torch.cuda.Event() for _ in range(2)], "done": [torch.cuda.Event() for _ in range(2)]}
             self._host_pipe = pipe
-        if pipe["out"] is None or pipe["out"].shape[0] < B:
-            pipe["out"] = torch.empty((max(B, 1), self.num_classes), dtype=torch.float32).pin_memory()
         with torch.cuda.device(dev):
             cur = torch.cuda.current_stream(dev)
             side = pipe["stream"]
@@ -380,7 +469,7 @@ class XAttnKernelsMixin:
                 pipe["done"][slot].record(cur)
             if probs:
                 logits = torch.softmax(logits, dim=1)
-            host = pipe["out"][:B]
+            host = out_buf[:B]
             host.copy_(logits, non_blocking=True)
             cur.synchronize()
         return host

@@ -198,3 +198,33 @@ def test_umma_probe_m64_halves_and_mn_major(cuda_device, mode, N, K):
                     for r in range(4):
                         w = want[:, g_ + 8 * (r >> 1), 8 * i + 2 * t_ + (r & 1)]
                         assert (o[p, :, lane, 4 * i + r] - w).abs().max().item() < 1e-3 * max(1.0, w.abs().max().item()), (p, lane, i, r)
+
+
+@pytest.mark.parametrize("B", [1, 8, 37])
+def test_graphed_forward_and_small_batch_host_path(cuda_device, B):
+    """SURVEY 8f rank 2 (worker batch path, optimized_runtime.py:99-108): one CUDA graph per batch size.  The graph replays the
+    same deterministic kernels, so its logits are bit-identical to the eager launch; predict_host routes worker-sized
+    batches through it; an in-place parameter update re-captures (the graph holds the packed-weight pointers)."""
+    m = make_head("concat", True, seed=0, precision="bf16").to(cuda_device).eval()
+    g = torch.Generator().manual_seed(5)
+    xv = torch.randn(B, 16, 512, generator=g).bfloat16()
+    xa = torch.randn(B, 149, 768, generator=g).bfloat16()
+    with torch.no_grad():
+        eager = m(xv.to(cuda_device), xa.to(cuda_device))
+        gf = m.graphed_forward(B)
+        gf.video.copy_(xv)
+        gf.audio.copy_(xa)
+        assert torch.equal(gf(), eager)
+        assert m.graphed_forward(B) is gf                      # cached
+        host = m.predict_host(xv.pin_memory(), xa.pin_memory())
+        assert torch.equal(host, eager.cpu())
+        probs = m.predict_host(xv.pin_memory(), xa.pin_memory(), probs=True)
+        assert torch.allclose(probs, torch.softmax(eager, dim=1).cpu(), atol=1e-6)
+        big = m.predict_host(xv.pin_memory(), xa.pin_memory(), graph_max=0)   # the chunked pipeline gives the same answer
+        assert torch.equal(big, eager.cpu())
+        m.v_norm.weight.mul_(1.5)                              # parameters changed in place: stale graph must not be replayed
+        eager2 = m(xv.to(cuda_device), xa.to(cuda_device))
+        assert not torch.equal(eager2, eager)
+        host2 = m.predict_host(xv.pin_memory(), xa.pin_memory())
+        assert torch.equal(host2, eager2.cpu())
+        assert m.graphed_forward(B) is not gf
