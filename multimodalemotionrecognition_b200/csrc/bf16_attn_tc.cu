@@ -135,6 +135,8 @@ __global__ void __launch_bounds__(kV2AThreads, 1) v2a_tc_kernel(const __grid_con
   __syncthreads();
   tc::tc_fence_after();
   const uint32_t tmem = *tmem_slot;
+  tc::pdl_wait();     // everything above overlapped the previous kernel's tail; its results are visible from here on
+  tc::pdl_launch();
 
   if (warp == 0) {
     if (lane == 0) {
@@ -454,6 +456,8 @@ __global__ void __launch_bounds__(kA2VThreads, 1) a2v_tc_kernel(const __grid_con
   __syncthreads();
   tc::tc_fence_after();
   const uint32_t tmem = *tmem_slot;
+  tc::pdl_wait();     // everything above overlapped the previous kernel's tail; its results are visible from here on
+  tc::pdl_launch();
 
   if (warp == 0) {
     if (lane == 0) {
@@ -815,7 +819,7 @@ int launch_v2a_tc(const Bf16Ctx& x) {
   }
   const int npairs = (c.B + 1) / 2;
   const int grid = npairs < num_sms() ? npairs : num_sms();
-  v2a_tc_kernel<<<grid, kV2AThreads, kV2ASmem, x.st>>>(tmA0, tmQt, tmU, a);
+  XF_CUDA(launch_chain(v2a_tc_kernel, dim3(grid), dim3(kV2AThreads), kV2ASmem, x.st, tmA0, tmQt, tmU, a));
   count_launch();
   XF_LAUNCH_CHECK();
   if (tracing) {   // debugging aid: timeline of CTA 0, microseconds from its first load
@@ -867,7 +871,7 @@ int launch_a2v_tc(const Bf16Ctx& x) {
   }
   const int npairs = (c.B + 1) / 2;
   const int grid = npairs < num_sms() ? npairs : num_sms();
-  a2v_tc_kernel<<<grid, kA2VThreads, kA2VSmem, x.st>>>(tmA0, tmKt, tmVt, a);
+  XF_CUDA(launch_chain(a2v_tc_kernel, dim3(grid), dim3(kA2VThreads), kA2VSmem, x.st, tmA0, tmKt, tmVt, a));
   count_launch();
   XF_LAUNCH_CHECK();
   if (tracing) {   // debugging aid: timeline of CTA 0 by row tile, microseconds from its first load

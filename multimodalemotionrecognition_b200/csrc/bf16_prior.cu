@@ -51,6 +51,8 @@ __global__ void __launch_bounds__(kPriorThreads) prior_kernel(PriorArgs a) {
   };
   uint4 bq[2 * BE / 32];
   if (wid < (a.Hd + 7) / 8) fetchw(bq, wid);
+  tc::pdl_wait();     // (weights above are static; everything below reads what the previous kernels wrote)
+  tc::pdl_launch();
   // the clip block's column sums (16 clips x 6 slots x 128 floats, contiguous) arrive as one bulk async copy
   __shared__ uint64_t abar;
   if (tid == 0) {
@@ -189,7 +191,7 @@ int launch_prior(const Bf16Ctx& x) {
     XF_CUDA(cudaFuncSetAttribute(prior_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, dyn));
     configured = true;
   }
-  prior_kernel<<<(c.B + kPriorClips - 1) / kPriorClips, kPriorThreads, dyn, x.st>>>(a);
+  XF_CUDA(launch_chain(prior_kernel, dim3((c.B + kPriorClips - 1) / kPriorClips), dim3(kPriorThreads), dyn, x.st, a));
   count_launch();
   XF_LAUNCH_CHECK();
   return XATTN_OK;

@@ -1,3 +1,4 @@
+#include <stdlib.h>
 // Host-side plumbing: error text, config validation, parameter + workspace layouts.
 #include "common.cuh"
 
@@ -12,6 +13,10 @@ static thread_local char g_err[512] = "";
 unsigned long long g_launch_count = 0;
 
 bool g_stage_timing = false;
+bool pdl_enabled() {
+  static const bool off = getenv("XATTN_NO_PDL") != nullptr;
+  return !off && !g_stage_timing;
+}
 static std::vector<cudaEvent_t> g_stage_ev[ST_COUNT][2];
 static const char* const kStageNames[ST_COUNT] = {"gemm_v0", "gemm_a0", "video_pre", "prior", "v2a_attn", "video_update", "a2v_attn", "head"};
 

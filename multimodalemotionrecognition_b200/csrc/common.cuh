@@ -54,6 +54,20 @@ inline void count_launch(int n = 1) { g_launch_count += (unsigned long long)n; }
 // Optional per-stage CUDA-event timing of the bf16 forward (xattn_stage_timing): bench.py's live per-kernel durations.
 enum { ST_GEMM_V0 = 0, ST_GEMM_A0, ST_VIDEO_PRE, ST_PRIOR, ST_V2A, ST_VIDEO_UPD, ST_A2V, ST_HEAD, ST_COUNT };
 extern bool g_stage_timing;
+// Kernels of the bf16 forward chain are launched with programmatic stream serialisation (each one starts with
+// griddepcontrol.wait, tc.cuh) unless XATTN_NO_PDL is set or per-kernel timing brackets are on.
+bool pdl_enabled();
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_chain(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, Args&&... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = pdl_enabled() ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+}
 void stage_mark(int stage, int end, cudaStream_t st);   // records an event on st (no-op unless timing is on)
 struct StageScope {
   int s;

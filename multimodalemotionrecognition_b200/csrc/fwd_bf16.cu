@@ -55,6 +55,8 @@ __global__ void __launch_bounds__(kHeadThreads, 1) head_pooled_kernel(HeadPooled
   // The clip block's partial sums (16 clips x 8 slots x 128 floats, contiguous) arrive as ONE bulk async copy: one memory round
   // trip instead of one per loop iteration of dependent loads.
   __shared__ uint64_t pbar;
+  tc::pdl_wait();
+  tc::pdl_launch();
   if (a.poolp != nullptr && tid == 0) {
     tc::mbar_init(&pbar, 1);
     tc::fence_barrier_init();
@@ -220,7 +222,7 @@ int launch_head_pooled(const Bf16Ctx& x, float* logits) {
     XF_CUDA(cudaFuncSetAttribute(head_pooled_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kHeadSmem));
     configured = true;
   }
-  head_pooled_kernel<<<(c.B + kHeadClips - 1) / kHeadClips, kHeadThreads, kHeadSmem, x.st>>>(a);
+  XF_CUDA(launch_chain(head_pooled_kernel, dim3((c.B + kHeadClips - 1) / kHeadClips), dim3(kHeadThreads), kHeadSmem, x.st, a));
   count_launch();
   XF_LAUNCH_CHECK();
   return XATTN_OK;

@@ -135,6 +135,8 @@ __global__ void __launch_bounds__(gemm_threads(EPG), 1) gemm_tc_kernel(const __g
   __syncthreads();
   tc::tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  tc::pdl_wait();     // no-op unless launched as part of the forward chain (launch_gemm_tc, chain = true)
+  tc::pdl_launch();
 
   if (warp == 0) {
     if (lane == 0) {
@@ -465,7 +467,8 @@ EncodeTiledFn encode_tiled_fn() {
 
 template <int EPI, int STAGES = kStagesDefault, int EPG = 1>
 int launch_gemm_tc(cudaStream_t st, const CUtensorMap& tmA, const CUtensorMap& tmB, const float* bias, void* out, int64_t pitch,
-                   int M, int N, int K, const GemmExtras& ex, const CUtensorMap* tmO = nullptr, const CUtensorMap* tmO2 = nullptr) {
+                   int M, int N, int K, const GemmExtras& ex, const CUtensorMap* tmO = nullptr, const CUtensorMap* tmO2 = nullptr,
+                   bool chain = false) {
   if (tmO == nullptr) tmO = &tmA;   // (only EPI_HEADROWS stores through tensor maps)
   if (tmO2 == nullptr) tmO2 = &tmA;
   constexpr int smem = gemm_smem_bytes(EPI, STAGES);
@@ -477,7 +480,11 @@ int launch_gemm_tc(cudaStream_t st, const CUtensorMap& tmA, const CUtensorMap& t
   }
   const int tiles = ((M + BM - 1) / BM) * (N / BN);
   const int grid = tiles < num_sms() ? tiles : num_sms();
-  gemm_tc_kernel<EPI, STAGES, EPG><<<grid, gemm_threads(EPG), smem, st>>>(tmA, tmB, *tmO, *tmO2, bias, out, pitch, M, N, K, ex);
+  if (chain)
+    XF_CUDA(launch_chain(gemm_tc_kernel<EPI, STAGES, EPG>, dim3(grid), dim3(gemm_threads(EPG)), smem, st, tmA, tmB, *tmO, *tmO2, bias, out,
+                         pitch, M, N, K, ex));
+  else
+    gemm_tc_kernel<EPI, STAGES, EPG><<<grid, gemm_threads(EPG), smem, st>>>(tmA, tmB, *tmO, *tmO2, bias, out, pitch, M, N, K, ex);
   count_launch();
   XF_LAUNCH_CHECK();
   return XATTN_OK;
@@ -549,7 +556,7 @@ int gemm_tc_video_mix(cudaStream_t st, const void* U, const void* G, const float
   alignas(64) CUtensorMap tmA, tmB;
   XF_TRY(make_tmap_bf16_2d(&tmA, U, M, 4 * BN, BM, BK));
   XF_TRY(make_tmap_bf16_2d(&tmB, G, BN, 4 * BN, BN, BK));
-  return launch_gemm_tc<EPI_LNRES, 6, 2>(st, tmA, tmB, bias, v1, BN, M, BN, 4 * BN, ex);
+  return launch_gemm_tc<EPI_LNRES, 6, 2>(st, tmA, tmB, bias, v1, BN, M, BN, 4 * BN, ex, nullptr, nullptr, true);
 }
 
 int gemm_tc_video_kv(cudaStream_t st, const void* v1, const void* F, const float* bias, void* kt, void* vt, int clips) {
@@ -563,7 +570,7 @@ int gemm_tc_video_kv(cudaStream_t st, const void* v1, const void* F, const float
   alignas(64) CUtensorMap tmK, tmV;   // [clips][64][128], boxes of 8 clips x 16 rows x 64 columns
   XF_TRY(make_tmap_bf16_3d(&tmK, kt, BN, 64, clips, 64, 16, 8));
   XF_TRY(make_tmap_bf16_3d(&tmV, vt, BN, 64, clips, 64, 16, 8));
-  return launch_gemm_tc<EPI_HEADROWS, 4, 2>(st, tmA, tmB, bias, kt, BN, M, 8 * BN, BN, ex, &tmK, &tmV);
+  return launch_gemm_tc<EPI_HEADROWS, 4, 2>(st, tmA, tmB, bias, kt, BN, M, 8 * BN, BN, ex, &tmK, &tmV, true);
 }
 
 }  // namespace xf

@@ -61,6 +61,12 @@ __device__ __forceinline__ void tma_load_2d(void* smem_dst, const void* tmap, ui
       "l"(tmap), "r"(smem_u32(bar)), "r"(c0), "r"(c1)
       : "memory");
 }
+// Programmatic dependent launch (sm_90+): `pdl_wait` blocks until every grid this one depends on has completed and its memory
+// is visible (a no-op for a normally launched grid); `pdl_launch` lets the next grid in the stream be scheduled as soon as
+// every CTA of this one has issued it — that grid runs its prologue in the shadow of our tail and blocks in its own pdl_wait.
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_launch() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
 __device__ __forceinline__ void tma_prefetch_desc(const void* tmap) {
   asm volatile("prefetch.tensormap [%0];" ::"l"(tmap) : "memory");
 }
