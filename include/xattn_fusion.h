@@ -26,7 +26,7 @@
 extern "C" {
 #endif
 
-#define XATTN_ABI_VERSION 7
+#define XATTN_ABI_VERSION 8
 
 #if defined(__GNUC__)
 #define XATTN_API __attribute__((visibility("default")))
@@ -47,6 +47,9 @@ typedef enum xattn_status {
 
 enum { XATTN_HEAD_CONCAT = 0, XATTN_HEAD_GATED = 1 };
 enum { XATTN_DTYPE_F32 = 0, XATTN_DTYPE_BF16 = 1 };
+/* xattn_config.precision only: the fp32 kernel family (forward, backward, training) with every Linear whose dimensions allow it
+ * on the tensor cores — tcgen05 kind::tf32 straight from the fp32 tensors (kind::f16 for bf16 embeddings), fp32 accumulation. */
+enum { XATTN_PREC_TF32 = 2 };
 
 /* Problem description.  Field meaning follows FusionModel.__init__ (fusion.py:188-213). */
 typedef struct xattn_config {
@@ -65,7 +68,8 @@ typedef struct xattn_config {
   int32_t use_prior;    /* xattn_use_emotion_prior                                   */
   int32_t io_dtype;     /* dtype of video_emb / audio_emb: XATTN_DTYPE_*             */
   int32_t precision;    /* XATTN_DTYPE_F32: fp32 SIMT kernels (parity + training path)
-                           XATTN_DTYPE_BF16: tcgen05 bf16 kernels, fp32 accumulate   */
+                           XATTN_DTYPE_BF16: tcgen05 bf16 kernels, fp32 accumulate
+                           XATTN_PREC_TF32: fp32 family, Linears on tcgen05 tf32     */
   int32_t training;     /* 1: dropouts active (Philox) and activations saved for
                            xattn_backward; 0: eval                                   */
   int32_t save_for_backward; /* 1: keep activations in the workspace even in eval mode
@@ -208,6 +212,12 @@ XATTN_API int flat_head_workspace_bytes(const flat_head_config* cfg, int64_t* by
  * fusion.py:413-435 (+ :137-139).  Eval mode (ModalityDropout / Dropout identity). */
 XATTN_API int flat_head_forward(const flat_head_config* cfg, const float* params, const void* video_emb, const void* audio_emb,
                       float* logits, void* workspace, int64_t workspace_bytes, void* stream);
+
+/* One tensor-core GEMM of the training path in isolation (tests): form 0: C[M,N] = A[M,K]·W[N,K]^T + bias; form 1: C[M,N] =
+ * A[M,K]·W[K,N]; form 2: C[N1=K... see gemm_tc.cuh] C[N,K] += A[M,N]^T·B[M,K] with fp32 operands; form 3: the same with bf16
+ * operands.  C is fp32. */
+XATTN_API int xattn_debug_gemm_tf32(int32_t form, const void* A, const void* B, const float* bias, float* C, int32_t M, int32_t N,
+                                    int32_t K, int32_t relu, int32_t accumulate, void* stream);
 
 /* ---- diagnostics ---------------------------------------------------------------------------------- */
 /* Kernel launches issued by this library since process start (bench.py's gpu_launches evidence). */

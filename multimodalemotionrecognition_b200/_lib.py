@@ -12,12 +12,13 @@ from pathlib import Path
 
 LIB_NAME = "libxattn_fusion.so"
 LIB_PATH = Path(__file__).resolve().parent / LIB_NAME
-ABI_VERSION = 7
+ABI_VERSION = 8
 
 # xattn_status
 OK, ERR_SHAPE, ERR_DTYPE, ERR_ALIGN, ERR_ARCH, ERR_CUDA, ERR_WORKSPACE, ERR_NULL = range(8)
 HEAD_CONCAT, HEAD_GATED = 0, 1
 DTYPE_F32, DTYPE_BF16 = 0, 1
+PREC_TF32 = 2   # xattn_config.precision only: fp32 kernel family with the Linears on tcgen05 tf32 (gemm_tf32.cu)
 
 # xattn_param_id -> reference state_dict key (None: resolved per head kind)
 XP_NAMES = [
@@ -95,6 +96,8 @@ _EXPORTS = {
     "flat_head_workspace_bytes": (C.c_int, [C.POINTER(FlatHeadConfig), C.POINTER(C.c_int64)]),
     "xattn_debug_gemm_tc": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_int64, C.c_int32, C.c_int32,
                                       C.c_int32, C.c_void_p]),
+    "xattn_debug_gemm_tf32": (C.c_int, [C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_int32,
+                                        C.c_int32, C.c_int32, C.c_void_p]),
     "xattn_debug_umma_probe": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_int32,
                                          C.c_void_p]),
     "flat_head_forward": (C.c_int, [C.POINTER(FlatHeadConfig), C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,

@@ -93,7 +93,7 @@ extern "C" XATTN_API int xattn_backward(const xattn_config* cfg, const float* pa
   if (!params || !video_emb || !audio_emb || !dlogits || !grads || !workspace) XF_FAIL(XATTN_ERR_NULL, "NULL pointer argument");
   if (misaligned(params) || misaligned(video_emb) || misaligned(audio_emb) || misaligned(workspace) || misaligned(grads))
     XF_FAIL(XATTN_ERR_ALIGN, "pointers must be 16-byte aligned");
-  if (cfg->precision != XATTN_DTYPE_F32) XF_FAIL(XATTN_ERR_DTYPE, "xattn_backward runs with precision=f32");
+  if (cfg->precision == XATTN_DTYPE_BF16) XF_FAIL(XATTN_ERR_DTYPE, "xattn_backward runs with precision=f32 or tf32");
   if (!cfg->training && !cfg->save_for_backward)
     XF_FAIL(XATTN_ERR_WORKSPACE, "forward was not run with training or save_for_backward set: no saved activations");
   XF_TRY(check_device_sm100());
@@ -133,6 +133,17 @@ extern "C" XATTN_API int xattn_debug_gemm_tc(const void* X, const void* W, const
   if (misaligned(X) || misaligned(W) || misaligned(Y)) XF_FAIL(XATTN_ERR_ALIGN, "pointers must be 16-byte aligned");
   XF_TRY(check_device_sm100());
   return gemm_tc_bf16((cudaStream_t)stream, X, W, bias, Y, out_bf16 != 0, out_pitch, M, N, K);
+}
+
+extern "C" XATTN_API int xattn_debug_gemm_tf32(int32_t form, const void* A, const void* B, const float* bias, float* C, int32_t M, int32_t N,
+                                               int32_t K, int32_t relu, int32_t accumulate, void* stream) {
+  if (!A || !B || !C) XF_FAIL(XATTN_ERR_NULL, "NULL pointer argument");
+  XF_TRY(check_device_sm100());
+  cudaStream_t st = (cudaStream_t)stream;
+  if (form == 0 || form == 1)
+    return gemm_tf32_rows(st, (const float*)A, K, (const float*)B, form == 1, bias, C, N, M, N, K, relu != 0, accumulate != 0);
+  if (form == 2 || form == 3) return gemm_cols(st, A, N, B, K, form == 3, C, K, M, N, K);
+  XF_FAIL(XATTN_ERR_SHAPE, "xattn_debug_gemm_tf32: unknown form %d", form);
 }
 
 extern "C" XATTN_API int xattn_debug_umma_probe(const void* A, const void* B, float* out32, float* out16, int32_t N, int32_t K,

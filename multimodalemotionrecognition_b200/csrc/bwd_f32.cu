@@ -451,9 +451,23 @@ static int backward_f32_impl(const xattn_config& c, const float* params, const T
   linear_bwd_dw<float>(st, ws + w.d_a0, E, ws + w.aseq, E, G(XP_A_IN_W), B * Ta, E, E);
   launch_colsum(st, ws + w.d_a0, E, B * Ta, E, G(XP_A_IN_B));
   linear_bwd_dx(st, ws + w.d_a0, E, P(XP_A_IN_W), ws + w.d_aseq, B * Ta, E, E, false);
-  linear_bwd_dw<TIO>(st, ws + w.d_aseq, E, xa, c.Da, G(XP_SEQ_W), B * Ta, E, c.Da);
+  const bool tc16 = g_tc_gemm && std::is_same<TIO, __nv_bfloat16>::value && gemm_cols_ok(B * Ta, E, c.Da, E, c.Da, true) &&
+                    gemm_cols_ok(B * T, E, c.Dv, E, c.Dv, true);
+  if (tc16) {   // bf16 embeddings: the gradient is rounded to bf16 (into d_o2, dead by now) and both operands go through kind::f16
+    __nv_bfloat16* dyb = reinterpret_cast<__nv_bfloat16*>(ws + w.d_o2);
+    cvt_f32_to_bf16(st, ws + w.d_aseq, dyb, (int64_t)B * Ta * E);
+    XF_TRY(gemm_cols(st, dyb, E, xa, c.Da, true, G(XP_SEQ_W), c.Da, B * Ta, E, c.Da));
+  } else {
+    linear_bwd_dw<TIO>(st, ws + w.d_aseq, E, xa, c.Da, G(XP_SEQ_W), B * Ta, E, c.Da);
+  }
   launch_colsum(st, ws + w.d_aseq, E, B * Ta, E, G(XP_SEQ_B));
-  linear_bwd_dw<TIO>(st, ws + w.d_v0, E, xv, c.Dv, G(XP_V_IN_W), B * T, E, c.Dv);
+  if (tc16) {
+    __nv_bfloat16* dyb = reinterpret_cast<__nv_bfloat16*>(ws + w.d_o1);
+    cvt_f32_to_bf16(st, ws + w.d_v0, dyb, (int64_t)B * T * E);
+    XF_TRY(gemm_cols(st, dyb, E, xv, c.Dv, true, G(XP_V_IN_W), c.Dv, B * T, E, c.Dv));
+  } else {
+    linear_bwd_dw<TIO>(st, ws + w.d_v0, E, xv, c.Dv, G(XP_V_IN_W), B * T, E, c.Dv);
+  }
   launch_colsum(st, ws + w.d_v0, E, B * T, E, G(XP_V_IN_B));
   XF_LAUNCH_CHECK();
   return XATTN_OK;
@@ -461,9 +475,15 @@ static int backward_f32_impl(const xattn_config& c, const float* params, const T
 
 int backward_f32(const xattn_config& c, const float* params, const void* xv, const void* xa, const float* dlogits, float* grads,
                  void* ws, cudaStream_t st) {
+  g_tc_gemm = c.precision == XATTN_PREC_TF32;
+  g_tc_status = XATTN_OK;
+  int rc;
   if (c.io_dtype == XATTN_DTYPE_BF16)
-    return backward_f32_impl<__nv_bfloat16>(c, params, (const __nv_bfloat16*)xv, (const __nv_bfloat16*)xa, dlogits, grads, (float*)ws, st);
-  return backward_f32_impl<float>(c, params, (const float*)xv, (const float*)xa, dlogits, grads, (float*)ws, st);
+    rc = backward_f32_impl<__nv_bfloat16>(c, params, (const __nv_bfloat16*)xv, (const __nv_bfloat16*)xa, dlogits, grads, (float*)ws, st);
+  else
+    rc = backward_f32_impl<float>(c, params, (const float*)xv, (const float*)xa, dlogits, grads, (float*)ws, st);
+  g_tc_gemm = false;
+  return rc != XATTN_OK ? rc : g_tc_status;
 }
 
 }  // namespace xf

@@ -13,6 +13,8 @@ static thread_local char g_err[512] = "";
 unsigned long long g_launch_count = 0;
 
 bool g_stage_timing = false;
+thread_local bool g_tc_gemm = false;
+thread_local int g_tc_status = 0;
 bool pdl_enabled() {
   static const bool off = getenv("XATTN_NO_PDL") != nullptr;
   return !off && !g_stage_timing;
@@ -65,6 +67,31 @@ void set_error(const char* fmt, ...) {
 }
 const char* last_error() { return g_err; }
 
+namespace {
+__global__ void __launch_bounds__(256) cvt_bf16_kernel(const float* __restrict__ x, __nv_bfloat16* __restrict__ y, int64_t n) {
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x * 8;
+  for (int64_t i = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) * 8; i < n; i += stride) {
+    if (i + 8 <= n) {
+      const float4 a = *reinterpret_cast<const float4*>(x + i), b = *reinterpret_cast<const float4*>(x + i + 4);
+      __nv_bfloat162 p0 = __floats2bfloat162_rn(a.x, a.y), p1 = __floats2bfloat162_rn(a.z, a.w), p2 = __floats2bfloat162_rn(b.x, b.y),
+                     p3 = __floats2bfloat162_rn(b.z, b.w);
+      *reinterpret_cast<uint4*>(y + i) = make_uint4(*reinterpret_cast<uint32_t*>(&p0), *reinterpret_cast<uint32_t*>(&p1),
+                                                    *reinterpret_cast<uint32_t*>(&p2), *reinterpret_cast<uint32_t*>(&p3));
+    } else {
+      for (int64_t k = i; k < n; ++k) y[k] = __float2bfloat16_rn(x[k]);
+    }
+  }
+}
+}  // namespace
+
+void cvt_f32_to_bf16(cudaStream_t st, const float* x, void* y, int64_t n) {
+  if (n <= 0) return;
+  int64_t blocks = (n / 8 + 255) / 256 + 1;
+  if (blocks > 148 * 16) blocks = 148 * 16;
+  cvt_bf16_kernel<<<(unsigned)blocks, 256, 0, st>>>(x, reinterpret_cast<__nv_bfloat16*>(y), n);
+  count_launch();
+}
+
 int check_device_sm100() {
   int dev = 0;
   XF_CUDA(cudaGetDevice(&dev));
@@ -103,7 +130,7 @@ int validate_config(const xattn_config* c) {
   if (c->use_prior && (c->prior_dim <= 0 || c->prior_hidden <= 0))
     XF_FAIL(XATTN_ERR_SHAPE, "emotion prior needs positive prior_dim / prior_hidden");
   if (c->io_dtype != XATTN_DTYPE_F32 && c->io_dtype != XATTN_DTYPE_BF16) XF_FAIL(XATTN_ERR_DTYPE, "unknown io_dtype %d", c->io_dtype);
-  if (c->precision != XATTN_DTYPE_F32 && c->precision != XATTN_DTYPE_BF16)
+  if (c->precision != XATTN_DTYPE_F32 && c->precision != XATTN_DTYPE_BF16 && c->precision != XATTN_PREC_TF32)
     XF_FAIL(XATTN_ERR_DTYPE, "unknown precision %d", c->precision);
   if ((int64_t)c->B * c->Ta * c->Da >= ((int64_t)1 << 40)) XF_FAIL(XATTN_ERR_SHAPE, "input too large");
   return XATTN_OK;
@@ -171,6 +198,9 @@ void compute_ws_f32(const xattn_config& c, WsF32& w) {
     w.d_qv = take(B * T); w.d_ka = take(B * Ta); w.d_qa = take(B * Ta); w.d_kvs = take(B * T);
     w.d_prior = take(B * P); w.d_phid = take(B * Hd);
   }
+  // precision = TF32 with bf16 embeddings: bf16 copies of the two first-layer weights (forward), and of d_aseq / d_v0 for the
+  // first-layer weight gradients (backward; those live in d_o2 / d_o1, dead by then)
+  w.wbf = take((E * (int64_t)c.Da + E * (int64_t)c.Dv + 1) / 2 + 8);
   w.total = off;
 }
 

@@ -54,6 +54,11 @@ inline void count_launch(int n = 1) { g_launch_count += (unsigned long long)n; }
 // Optional per-stage CUDA-event timing of the bf16 forward (xattn_stage_timing): bench.py's live per-kernel durations.
 enum { ST_GEMM_V0 = 0, ST_GEMM_A0, ST_VIDEO_PRE, ST_PRIOR, ST_V2A, ST_VIDEO_UPD, ST_A2V, ST_HEAD, ST_COUNT };
 extern bool g_stage_timing;
+// precision = XATTN_PREC_TF32: the Linear helpers of gemm_simt.cuh route to the tensor-core GEMMs (gemm_tf32.cu) while this is
+// set (by forward_f32 / backward_f32 for the duration of one call); a failed launch is remembered in g_tc_status.
+void cvt_f32_to_bf16(cudaStream_t st, const float* x, void* y_bf16, int64_t n);   // n % 4 == 0 or any n; 16-byte aligned
+extern thread_local bool g_tc_gemm;
+extern thread_local int g_tc_status;
 // Kernels of the bf16 forward chain are launched with programmatic stream serialisation (each one starts with
 // griddepcontrol.wait, tc.cuh) unless XATTN_NO_PDL is set or per-kernel timing brackets are on.
 bool pdl_enabled();
@@ -100,6 +105,7 @@ struct WsF32 {
   // backward scratch (only laid out when training / save_for_backward)
   int64_t d_pooled, d_hh, d_z, d_fused, d_a0, d_br2, d_o2, d_q2, d_kv2, d_v1, d_v0, d_br1, d_o1, d_q1, d_kv1, d_aseq;
   int64_t d_qv, d_ka, d_qa, d_kvs, d_prior, d_phid;
+  int64_t wbf;    // bf16 scratch of the TF32 precision (see compute_ws_f32)
   int64_t total;  // floats
 };
 void compute_ws_f32(const xattn_config& c, WsF32& w);

@@ -307,8 +307,18 @@ static int forward_f32_impl(const xattn_config& c, const float* params, const TI
               p_prior = train ? c.p_prior : 0.f;
 
   // projections (fusion.py:372, :378, :386)
-  linear_fwd<TIO>(st, xv, P(XP_V_IN_W), P(XP_V_IN_B), ws + w.v0, B * T, E, c.Dv);
-  linear_fwd<TIO>(st, xa, P(XP_SEQ_W), P(XP_SEQ_B), ws + w.aseq, B * Ta, E, c.Da);
+  if (g_tc_gemm && std::is_same<TIO, __nv_bfloat16>::value && E % 128 == 0 && c.Dv % 64 == 0 && c.Da % 64 == 0) {
+    // bf16 embeddings: kind::f16 products against bf16-rounded copies of the two weights (gemm_tc.cu), fp32 out
+    __nv_bfloat16* wv = reinterpret_cast<__nv_bfloat16*>(ws + w.wbf);
+    __nv_bfloat16* wa = wv + (int64_t)E * c.Dv;
+    cvt_f32_to_bf16(st, P(XP_V_IN_W), wv, (int64_t)E * c.Dv);
+    cvt_f32_to_bf16(st, P(XP_SEQ_W), wa, (int64_t)E * c.Da);
+    XF_TRY(gemm_tc_bf16(st, xv, wv, P(XP_V_IN_B), ws + w.v0, false, E, B * T, E, c.Dv));
+    XF_TRY(gemm_tc_bf16(st, xa, wa, P(XP_SEQ_B), ws + w.aseq, false, E, B * Ta, E, c.Da));
+  } else {
+    linear_fwd<TIO>(st, xv, P(XP_V_IN_W), P(XP_V_IN_B), ws + w.v0, B * T, E, c.Dv);
+    linear_fwd<TIO>(st, xa, P(XP_SEQ_W), P(XP_SEQ_B), ws + w.aseq, B * Ta, E, c.Da);
+  }
   linear_fwd<float>(st, ws + w.aseq, P(XP_A_IN_W), P(XP_A_IN_B), ws + w.a0, B * Ta, E, E);
   XF_LAUNCH_CHECK();
 
@@ -394,9 +404,15 @@ static int forward_f32_impl(const xattn_config& c, const float* params, const TI
 
 int forward_f32(const xattn_config& c, const float* params, const void* xv, const void* xa, float* logits, void* ws,
                 cudaStream_t st) {
+  g_tc_gemm = c.precision == XATTN_PREC_TF32;   // the Linear helpers route to the tensor-core GEMMs for this call
+  g_tc_status = XATTN_OK;
+  int rc;
   if (c.io_dtype == XATTN_DTYPE_BF16)
-    return forward_f32_impl<__nv_bfloat16>(c, params, (const __nv_bfloat16*)xv, (const __nv_bfloat16*)xa, logits, (float*)ws, st);
-  return forward_f32_impl<float>(c, params, (const float*)xv, (const float*)xa, logits, (float*)ws, st);
+    rc = forward_f32_impl<__nv_bfloat16>(c, params, (const __nv_bfloat16*)xv, (const __nv_bfloat16*)xa, logits, (float*)ws, st);
+  else
+    rc = forward_f32_impl<float>(c, params, (const float*)xv, (const float*)xa, logits, (float*)ws, st);
+  g_tc_gemm = false;
+  return rc != XATTN_OK ? rc : g_tc_status;
 }
 
 }  // namespace xf

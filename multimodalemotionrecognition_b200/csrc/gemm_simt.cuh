@@ -5,7 +5,10 @@
 // fp32 accumulate, FFMA only — this path exists for the 1e-4 fp32 parity gate; the bf16 tcgen05 kernels
 // in fwd_bf16.cu are the performance path.
 #pragma once
+#include <type_traits>
+
 #include "common.cuh"
+#include "gemm_tc.cuh"
 
 namespace xf {
 
@@ -106,17 +109,32 @@ inline void launch_gemm(cudaStream_t st, const TA* A, int64_t am, int64_t ak, co
 template <typename TX>
 inline void linear_fwd(cudaStream_t st, const TX* X, const float* W, const float* b, float* Y, int M, int N, int K,
                        bool relu = false) {
+  if (std::is_same<TX, float>::value && g_tc_gemm && gemm_tf32_rows_ok(M, N, K, K, N)) {
+    const int rc = gemm_tf32_rows(st, reinterpret_cast<const float*>(X), K, W, false, b, Y, N, M, N, K, relu, false);
+    if (rc != XATTN_OK) g_tc_status = rc;
+    return;
+  }
   launch_gemm<TX, float>(st, X, K, 1, W, 1, K, Y, N, M, N, K, b, relu ? GEMM_RELU : 0);
 }
 // dX[M,K] (+)= dY[M,N] · W[N,K]
 inline void linear_bwd_dx(cudaStream_t st, const float* dY, int64_t ldy, const float* W, float* dX, int M, int N, int K,
                           bool accumulate) {
+  if (g_tc_gemm && gemm_tf32_rows_ok(M, K, N, ldy, K)) {   // reduction over N, K output columns, W[N,K] read as [reduction, out]
+    const int rc = gemm_tf32_rows(st, dY, ldy, W, true, nullptr, dX, K, M, K, N, false, accumulate);
+    if (rc != XATTN_OK) g_tc_status = rc;
+    return;
+  }
   launch_gemm<float, float>(st, dY, ldy, 1, W, K, 1, dX, K, M, K, N, nullptr, accumulate ? GEMM_ACCUM : 0);
 }
 // dW[N,K] += dY[M,N]^T · X[M,K]   (dW must be zeroed or hold a partial sum; long reduction over M is split)
 template <typename TX>
 inline void linear_bwd_dw(cudaStream_t st, const float* dY, int64_t ldy, const TX* X, int64_t ldx, float* dW, int M, int N,
                           int K) {
+  if (std::is_same<TX, float>::value && g_tc_gemm && gemm_cols_ok(M, N, K, ldy, ldx, false)) {
+    const int rc = gemm_cols(st, dY, ldy, X, ldx, false, dW, K, M, N, K);
+    if (rc != XATTN_OK) g_tc_status = rc;
+    return;
+  }
   int splits = M / 1024;
   if (splits < 1) splits = 1;
   if (splits > 512) splits = 512;

@@ -24,4 +24,15 @@ int gemm_tc_video_kv(cudaStream_t st, const void* v1, const void* F, const float
 // 2D bf16 tensor map with SWIZZLE_128B boxes: `cols` contiguous elements per row, rows `pitch` elements apart (0 = cols).
 int make_tmap_bf16_2d(void* tmap_out, const void* base, int64_t rows, int64_t cols, int box_rows, int box_cols, int64_t pitch = 0);
 int make_tmap_bf16_3d(void* tmap_out, const void* base, int64_t d0, int64_t d1, int64_t d2, int b0, int b1, int b2);
+
+// ---- tensor-core GEMMs of the training path (gemm_tf32.cu), precision = XATTN_PREC_TF32 ----
+// C[M,N] (+)= A[M,K]·W^T (+bias)(ReLU) with W given as [N,K] (w_is_kn = false) or as [K,N] (true: dX = dY·W, no transposed copy);
+// fp32 tensors, tf32 products, fp32 accumulation.  N % 128 == 0, K % 32 == 0.
+bool gemm_tf32_rows_ok(int M, int N, int K, int64_t lda, int64_t ldc);
+int gemm_tf32_rows(cudaStream_t st, const float* A, int64_t lda, const float* W, bool w_is_kn, const float* bias, float* C, int64_t ldc,
+                   int M, int N, int K, bool relu, bool accumulate);
+// C[N1,N2] += A[M,N1]^T·B[M,N2] (dW = dY^T·X), A and B both fp32 (tf32 products) or both bf16; N1, N2 % 128 == 0.
+bool gemm_cols_ok(int M, int N1, int N2, int64_t lda, int64_t ldb, bool bf16);
+int gemm_cols(cudaStream_t st, const void* A, int64_t lda, const void* B, int64_t ldb, bool bf16, float* C, int64_t ldc, int M, int N1,
+              int N2);
 }  // namespace xf

@@ -148,8 +148,8 @@ class XAttnKernelsMixin:
                      prior_hidden: int, prior_dropout: float, precision: str = "auto") -> None:
         if xattn_head not in ("concat", "gated"):
             raise ValueError(f"Unknown xattn head: {xattn_head}")
-        if precision not in ("auto", "fp32", "bf16"):
-            raise ValueError(f"precision must be auto|fp32|bf16, got {precision}")
+        if precision not in ("auto", "fp32", "bf16", "tf32"):
+            raise ValueError(f"precision must be auto|fp32|bf16|tf32, got {precision}")
         self.v_dim = v_dim
         self.audio_sequence_dim = audio_sequence_dim
         self.a_dim = d_model
@@ -331,8 +331,12 @@ class XAttnKernelsMixin:
 
     def _pick_precision(self, io_dtype: int, need_grad: bool, T: int = 16, Ta: int = 149) -> int:
         """fp32 SIMT kernels for training / gradient parity and for shapes outside the bf16 specialisation; the bf16
-        tcgen05 + mma.sync path for bf16 embeddings at inference (``precision="bf16"`` forces it and raises on
-        unsupported shapes).  Both are CUDA paths of this library — there is no eager fallback."""
+        tcgen05 path for bf16 embeddings at inference (``precision="bf16"`` forces it and raises on unsupported shapes);
+        ``precision="tf32"``: the fp32 kernel family with every Linear on the tensor cores (tcgen05 kind::tf32 / kind::f16,
+        fp32 accumulate) — the fast Stage-1 training step, gradients within ~1e-2 relative of the fp32 ones.
+        All are CUDA paths of this library — there is no eager fallback."""
+        if self.precision == "tf32":
+            return _lib.PREC_TF32
         if need_grad or self.precision == "fp32":
             return _lib.DTYPE_F32
         if self.precision == "bf16":
@@ -429,7 +433,7 @@ class XAttnKernelsMixin:
         if out_buf is None or out_buf.shape[0] < B or out_buf.shape[1] != self.num_classes:
             out_buf = torch.empty((max(B, 1), self.num_classes), dtype=torch.float32).pin_memory()
             self._host_out = out_buf
-        if 0 < B <= min(graph_max, chunk) and video_host.dtype == torch.bfloat16 and self.precision != "fp32" \
+        if 0 < B <= min(graph_max, chunk) and video_host.dtype == torch.bfloat16 and self.precision in ("auto", "bf16") \
                 and self._bf16_supported(T_, Ta_):
             # worker-sized batches (inference_worker.py:33-34) are launch-bound: H2D, one graph launch, D2H
             with torch.cuda.device(dev):

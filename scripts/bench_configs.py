@@ -118,20 +118,22 @@ def run_sweep():
 
 
 def run_train():
-    torch.manual_seed(0)
     B = 1024
-    head = XAttnFusionHead(num_classes=NCLS, audio_n_mels=DA, xattn_use_emotion_prior=True).to(dev).train()
-    tr = Stage1Trainer(head, lr=1e-3, weight_decay=1e-4)
     sets = make_inputs(B, 2, 1 + rank)
-    n0 = _lib.launch_count()
-    ms = timed(lambda i: tr.step(*sets[i % 2], training=True), 20, 5)
-    launches = (_lib.launch_count() - n0) // 25
-    # the same step without the collective, to show what the all-reduce costs
-    ms_local = timed(lambda i: (tr.forward_backward(*sets[i % 2], training=True), tr.optimizer_step()), 20, 3)
-    emit({"config": "configs[3] Stage-1 training step", "batch_per_gpu": B, "n_gpus": world, "ms_per_step": ms,
-          "clips_per_s": B * world / (ms * 1e-3), "ms_per_step_without_allreduce": ms_local, "kernel_launches_per_step": launches,
-          "step": "forward(train, dropouts 0.1/0.1/0.2/0.1) + CE + backward + NCCL all-reduce of the 398,581-float bucket + Adam",
-          "dtype": "f32 kernels, bf16 embeddings", "tflops": 150_416_000 * B / (ms * 1e-3) / 1e12})
+    for prec in ("fp32", "tf32"):
+        torch.manual_seed(0)
+        head = XAttnFusionHead(num_classes=NCLS, audio_n_mels=DA, xattn_use_emotion_prior=True, precision=prec).to(dev).train()
+        tr = Stage1Trainer(head, lr=1e-3, weight_decay=1e-4)
+        n0 = _lib.launch_count()
+        ms = timed(lambda i: tr.step(*sets[i % 2], training=True), 20, 5)
+        launches = (_lib.launch_count() - n0) // 25
+        # the same step without the collective, to show what the all-reduce costs
+        ms_local = timed(lambda i: (tr.forward_backward(*sets[i % 2], training=True), tr.optimizer_step()), 20, 3)
+        emit({"config": "configs[3] Stage-1 training step", "precision": prec, "batch_per_gpu": B, "n_gpus": world, "ms_per_step": ms,
+              "clips_per_s": B * world / (ms * 1e-3), "ms_per_step_without_allreduce": ms_local, "kernel_launches_per_step": launches,
+              "step": "forward(train, dropouts 0.1/0.1/0.2/0.1) + CE + backward + NCCL all-reduce of the 398,581-float bucket + Adam",
+              "dtype": "fp32 SIMT kernels" if prec == "fp32" else "fp32 tensors, Linears on tcgen05 (tf32 products; bf16 first layer), fp32 accumulate",
+              "tflops": 150_416_000 * B / (ms * 1e-3) / 1e12})
 
 
 def run_flat():

@@ -10,7 +10,8 @@ B = int(sys.argv[1]) if len(sys.argv) > 1 else 1024
 n = int(sys.argv[2]) if len(sys.argv) > 2 else 3
 dev = torch.device("cuda:0")
 torch.manual_seed(0)
-head = XAttnFusionHead(num_classes=8, audio_n_mels=768, xattn_use_emotion_prior=True).to(dev).train()
+prec = sys.argv[3] if len(sys.argv) > 3 else "fp32"
+head = XAttnFusionHead(num_classes=8, audio_n_mels=768, xattn_use_emotion_prior=True, precision=prec).to(dev).train()
 tr = Stage1Trainer(head, lr=1e-3, weight_decay=1e-4)
 g = torch.Generator(device=dev).manual_seed(1)
 xv = torch.randn(B, 16, 512, device=dev, generator=g).bfloat16()

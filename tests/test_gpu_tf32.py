@@ -1,0 +1,118 @@
+"""GPU tests (``-m gpu``) of the tensor-core training path (precision="tf32"): the three tcgen05 GEMM forms of
+csrc/gemm_tf32.cu in isolation against float64 products, then the whole Stage-1 forward + backward against the fp32 SIMT
+path (which is itself pinned to the reference's gradients in test_gpu_parity.py).  tf32 keeps 10 mantissa bits of every
+operand, bf16 7: the gates below are relative to the largest entry of the exact result."""
+import numpy as np
+import pytest
+import torch
+
+from helpers import make_head
+
+pytestmark = pytest.mark.gpu
+
+
+def _gemm(form, A, B, bias, C, M, N, K, relu=False, accumulate=False):
+    from multimodalemotionrecognition_b200 import _lib
+    from multimodalemotionrecognition_b200.fusion import _ptr, _stream_ptr
+
+    _lib.check(_lib.load().xattn_debug_gemm_tf32(form, _ptr(A), _ptr(B), _ptr(bias), _ptr(C), M, N, K, int(relu), int(accumulate),
+                                                 _stream_ptr(A.device)))
+    torch.cuda.synchronize()
+
+
+def _trunc_tf32(x):
+    return (x.contiguous().view(torch.int32) & ~0x1FFF).view(torch.float32)
+
+
+@pytest.mark.parametrize("M,N,K,relu,acc", [(300, 128, 128, False, False), (1000, 256, 768, True, False), (4097, 128, 512, False, True),
+                                            (128, 384, 32, False, False)])
+def test_tf32_linear_forward_form(cuda_device, M, N, K, relu, acc):
+    g = torch.Generator().manual_seed(M + N + K)
+    A = torch.randn(M, K, generator=g).to(cuda_device)
+    W = torch.randn(N, K, generator=g).to(cuda_device)
+    bias = torch.randn(N, generator=g).to(cuda_device)
+    C0 = torch.randn(M, N, generator=g).to(cuda_device)
+    C = C0.clone()
+    _gemm(0, A, W, bias, C, M, N, K, relu, acc)
+    ref = A.double() @ W.double().T + bias.double()
+    if relu:
+        ref = ref.clamp_min(0)
+    if acc:
+        ref = ref + C0.double()
+    scale = ref.abs().max().item()
+    err = (C.double() - ref).abs().max().item()
+    assert err <= 4e-3 * scale, (err, scale)
+    tight = _trunc_tf32(A).double() @ _trunc_tf32(W).double().T + bias.double()
+    print("vs truncated operands:", ((C.double() - (tight.clamp_min(0) if relu else tight) - (C0.double() if acc else 0)).abs().max().item()) / scale)
+
+
+@pytest.mark.parametrize("M,Nred,Kout,acc", [(500, 128, 128, False), (2049, 256, 128, True), (64, 128, 256, False)])
+def test_tf32_input_gradient_form(cuda_device, M, Nred, Kout, acc):
+    """dX[M,Kout] (+)= dY[M,Nred] · W[Nred,Kout] with W read in place as an MN-major operand."""
+    g = torch.Generator().manual_seed(M + Nred)
+    dY = torch.randn(M, Nred, generator=g).to(cuda_device)
+    W = torch.randn(Nred, Kout, generator=g).to(cuda_device)
+    C0 = torch.randn(M, Kout, generator=g).to(cuda_device)
+    C = C0.clone()
+    _gemm(1, dY, W, None, C, M, Kout, Nred, False, acc)
+    ref = dY.double() @ W.double() + (C0.double() if acc else 0)
+    scale = ref.abs().max().item()
+    assert (C.double() - ref).abs().max().item() <= 4e-3 * scale
+
+
+@pytest.mark.parametrize("M,N,K,bf16", [(5000, 128, 768, False), (77, 256, 128, False), (152576, 128, 128, False),
+                                        (5000, 128, 768, True), (33, 128, 512, True)])
+def test_weight_gradient_form(cuda_device, M, N, K, bf16):
+    """dW[N,K] += dY[M,N]^T · X[M,K]: both operands MN-major (the reduction runs down the rows), split over M."""
+    g = torch.Generator().manual_seed(M + K)
+    dY = torch.randn(M, N, generator=g).to(cuda_device)
+    X = torch.randn(M, K, generator=g).to(cuda_device)
+    if bf16:
+        dY, X = dY.bfloat16(), X.bfloat16()
+    C0 = torch.randn(N, K, generator=g).to(cuda_device)
+    C = C0.clone()
+    _gemm(3 if bf16 else 2, dY, X, None, C, M, N, K)
+    ref = dY.double().T @ X.double() + C0.double()
+    scale = ref.abs().max().item()
+    err = (C.double() - ref).abs().max().item()
+    assert err <= (1e-4 if bf16 else 4e-3) * scale, (err, scale)   # bf16 operands are exact here: only the summation order differs
+
+
+@pytest.mark.parametrize("io", ["bf16", "fp32"])
+def test_tf32_stage1_step_close_to_fp32(cuda_device, io):
+    """Forward + CE + backward of BASELINE configs[3] (B reduced to 96 clips), dropouts off: the tensor-core path against the
+    fp32 SIMT path on the same inputs.  Logits within 1e-2 (the bf16 gate of north_star), loss within 2e-3.  Gradients: tf32
+    keeps 10 mantissa bits and the tensor core truncates, so every Linear output carries ~5e-4 relative error; ~20 chained
+    layers (forward + backward, through LayerNorm and softmax) and the ReLU units that flip at 96 clips bring the far end of
+    the chain to a few percent of the gradient's largest entry (measured 1e-3 .. 9e-2) — what torch's allow_tf32 does to the
+    reference.  Gate: every parameter gradient within 15 % of its largest entry AND cosine similarity >= 0.99."""
+    from multimodalemotionrecognition_b200.training import Stage1Trainer
+
+    g = torch.Generator().manual_seed(3)
+    B = 96
+    xv = torch.randn(B, 16, 512, generator=g)
+    xa = torch.randn(B, 149, 768, generator=g)
+    labels = torch.randint(0, 8, (B,), generator=g)
+    if io == "bf16":
+        xv, xa = xv.bfloat16(), xa.bfloat16()
+    res = {}
+    for prec in ("fp32", "tf32"):
+        m = make_head("concat", True, seed=0, precision=prec).to(cuda_device).train()
+        tr = Stage1Trainer(m)
+        loss = tr.forward_backward(xv.to(cuda_device), xa.to(cuda_device), labels.to(cuda_device), training=False)
+        res[prec] = (float(loss), tr._logits.detach().cpu().clone(), {k: p.grad.detach().cpu().clone() for k, p in m.named_parameters()
+                                                                      if p.grad is not None})
+    l0, z0, g0 = res["fp32"]
+    l1, z1, g1 = res["tf32"]
+    assert abs(l0 - l1) <= 2e-3, (l0, l1)
+    assert (z0 - z1).abs().max().item() <= 1e-2
+    assert set(g0) == set(g1)
+    worst = 0.0
+    for k in g0:
+        scale = g0[k].abs().max().item()
+        rel = (g0[k] - g1[k]).abs().max().item() / max(scale, 1e-12)
+        worst = max(worst, rel)
+        assert rel <= 0.15, (k, rel, scale)
+        cos = torch.nn.functional.cosine_similarity(g0[k].flatten().double(), g1[k].flatten().double(), dim=0).item()
+        assert cos >= 0.99, (k, cos)
+    print(f"tf32 vs fp32 ({io} embeddings): loss {l1:.6f} vs {l0:.6f}, worst relative gradient error {worst:.2e}")
