@@ -135,7 +135,7 @@ inline void linear_bwd_dw(cudaStream_t st, const float* dY, int64_t ldy, const T
     if (rc != XATTN_OK) g_tc_status = rc;
     return;
   }
-  int splits = M / 1024;
+  int splits = M / 128;   // (short reductions too: one CTA walking 1024 rows alone is a 180 us kernel)
   if (splits < 1) splits = 1;
   if (splits > 512) splits = 512;
   if (splits == 1) {

@@ -180,11 +180,16 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_tf32_rows_kernel(const __gri
       const int m = m0 + q * 32 + lane;
 #pragma unroll 1
       for (int c = 0; c < TN; c += 32) {
+        float* o = C + (int64_t)m * ldc + n0 + c;
+        float4 old[8];
+        if (accumulate && m < M) {   // the previous values: eight independent loads in flight while the accumulator strip arrives
+#pragma unroll
+          for (int v = 0; v < 8; ++v) old[v] = __ldcs(reinterpret_cast<const float4*>(o + 4 * v));
+        }
         uint32_t r[32];
         tc::tmem_ld_32x32(tmem_base + ab * TN + ((uint32_t)(q * 32) << 16) + (uint32_t)c, r);
         tc::tmem_ld_wait();
         if (m < M) {
-          float* o = C + (int64_t)m * ldc + n0 + c;
 #pragma unroll
           for (int v = 0; v < 8; ++v) {
             float4 f;
@@ -193,10 +198,7 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_tf32_rows_kernel(const __gri
             f.z = __uint_as_float(r[4 * v + 2]) + bias_s[c + 4 * v + 2];
             f.w = __uint_as_float(r[4 * v + 3]) + bias_s[c + 4 * v + 3];
             if (relu) { f.x = fmaxf(f.x, 0.f); f.y = fmaxf(f.y, 0.f); f.z = fmaxf(f.z, 0.f); f.w = fmaxf(f.w, 0.f); }
-            if (accumulate) {
-              const float4 old = *reinterpret_cast<const float4*>(o + 4 * v);
-              f.x += old.x; f.y += old.y; f.z += old.z; f.w += old.w;
-            }
+            if (accumulate) { f.x += old[v].x; f.y += old[v].y; f.z += old[v].z; f.w += old[v].w; }
             *reinterpret_cast<float4*>(o + 4 * v) = f;
           }
         }
