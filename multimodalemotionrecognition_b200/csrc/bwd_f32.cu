@@ -3,6 +3,7 @@
 // Hand-derived reverse of fwd_f32.cu; activations come from the forward's workspace, dropout masks are
 // regenerated from the same Philox counters.
 #include "gemm_simt.cuh"
+#include "smem_tile.cuh"
 #include "kernels_f32.cuh"
 
 namespace xf {
@@ -238,8 +239,176 @@ __global__ void __launch_bounds__(256) attn_bwd_kernel(AttnBwdArgs a) {
   }
 }
 
+
+// The same for dh == 32 with register-tiled products (smem_tile.cuh).  [L][SP] matrices (SP = S rounded up to 4) come first in
+// shared memory so their rows stay 16-byte aligned.
+__global__ void __launch_bounds__(256) attn_bwd32_kernel(AttnBwdArgs a) {
+  extern __shared__ __align__(16) float sm[];
+  const int b = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nw = blockDim.x >> 5;
+  const int L = a.L, S = a.S, E = a.E, H = a.H, SP = (S + 3) & ~3;
+  constexpr int dh = 32, dp = 33;
+  float* Ps = sm;                  // [L][SP]  P
+  float* Pds = Ps + L * SP;        // [L][SP]  dropout(P)
+  float* dSs = Pds + L * SP;       // [L][SP]  dP, then dS
+  float* dBs = dSs + L * SP;       // [L][SP]  sum over heads of dS
+  float* Qs = dBs + L * SP;        // [L][dp]  (scaled q)
+  float* Ks = Qs + L * dp;         // [S][dp]
+  float* Vs = Ks + S * dp;         // [S][dp]
+  float* dOs = Vs + S * dp;        // [L][dp]
+  __shared__ float red[32];
+  const float* q = a.q + (int64_t)b * L * E;
+  const float* kv = a.kv + (int64_t)b * S * 2 * E;
+  const float* dO = a.dO + (int64_t)b * L * E;
+  const bool lanes_on_s = S >= L;
+  const int AR = lanes_on_s ? L : S, BR = lanes_on_s ? S : L;
+  const float* Am = lanes_on_s ? dOs : Vs;
+  const float* Bm = lanes_on_s ? Vs : dOs;
+  const int tiles_a = (AR + 1) / 2, ntile = tiles_a * ((BR + 159) / 160);
+  for (int i = tid; i < L * SP; i += blockDim.x) {
+    dBs[i] = 0.f;
+    Pds[i] = 0.f;   // (padding columns stay zero: the dQ product reads them)
+    dSs[i] = 0.f;
+  }
+  for (int h = 0; h < H; ++h) {
+    for (int i = tid; i < L * dh; i += blockDim.x) {
+      const int l = i >> 5, d = i & 31;
+      Qs[l * dp + d] = q[(int64_t)l * E + h * dh + d] * a.scale;
+      dOs[l * dp + d] = dO[(int64_t)l * E + h * dh + d];
+    }
+    for (int i = tid; i < S * dh; i += blockDim.x) {
+      const int s = i >> 5, d = i & 31;
+      Ks[s * dp + d] = kv[(int64_t)s * 2 * E + h * dh + d];
+      Vs[s * dp + d] = kv[(int64_t)s * 2 * E + E + h * dh + d];
+    }
+    __syncthreads();
+    const int64_t hbase = ((int64_t)b * H + h) * L * S;
+    for (int t = warp; t < ntile; t += nw) {   // dPd = dO · V^T
+      const int a0 = (t % tiles_a) * 2, b0 = (t / tiles_a) * 160;
+      float acc[2][5];
+      tile_nt<2, 5>(Am, a0, AR, dp, Bm, b0, BR, dp, dh, lane, acc);
+#pragma unroll
+      for (int i = 0; i < 2; ++i)
+#pragma unroll
+        for (int j = 0; j < 5; ++j) {
+          const int ar = a0 + i, br = b0 + lane + 32 * j;
+          if (ar < AR && br < BR) {
+            const int l = lanes_on_s ? ar : br, s2 = lanes_on_s ? br : ar;
+            const int64_t pi = hbase + (int64_t)l * S + s2;
+            const float p = a.P[pi];
+            const float f = a.p_drop > 0.f ? drop_factor(a.p_drop, a.seed, a.offset, a.rng_stream, (uint64_t)pi) : 1.f;
+            Ps[l * SP + s2] = p;
+            Pds[l * SP + s2] = p * f;
+            dSs[l * SP + s2] = acc[i][j] * f;   // dP until the row dot is known
+          }
+        }
+    }
+    __syncthreads();
+    for (int l = warp; l < L; l += nw) {   // dS = P ⊙ (dP - rowsum(dP ⊙ P))
+      float rowdot = 0.f;
+      for (int s2 = lane; s2 < S; s2 += 32) rowdot = fmaf(dSs[l * SP + s2], Ps[l * SP + s2], rowdot);
+      rowdot = warp_sum(rowdot);
+      for (int s2 = lane; s2 < S; s2 += 32) {
+        const float ds = Ps[l * SP + s2] * (dSs[l * SP + s2] - rowdot);
+        dSs[l * SP + s2] = ds;
+        dBs[l * SP + s2] += ds;
+      }
+    }
+    __syncthreads();
+    // dV = Pd^T dO, dK = dS^T (scale·Q): [S, dh], lane = column
+    if (S > 32) {
+      for (int t = warp; t < (S + 3) / 4; t += nw) {
+        float dv[4], dk[4];
+        tile_am<4>(Pds, 4 * t, SP, dOs, dp, L, lane, dv);
+        tile_am<4>(dSs, 4 * t, SP, Qs, dp, L, lane, dk);
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+          if (4 * t + i < S) {
+            a.dkv[((int64_t)b * S + 4 * t + i) * 2 * E + h * dh + lane] = dk[i];
+            a.dkv[((int64_t)b * S + 4 * t + i) * 2 * E + E + h * dh + lane] = dv[i];
+          }
+      }
+    } else {
+      for (int t = warp; t < (S + 1) / 2; t += nw) {
+        float dv[2], dk[2];
+        tile_am<2>(Pds, 2 * t, SP, dOs, dp, L, lane, dv);
+        tile_am<2>(dSs, 2 * t, SP, Qs, dp, L, lane, dk);
+#pragma unroll
+        for (int i = 0; i < 2; ++i)
+          if (2 * t + i < S) {
+            a.dkv[((int64_t)b * S + 2 * t + i) * 2 * E + h * dh + lane] = dk[i];
+            a.dkv[((int64_t)b * S + 2 * t + i) * 2 * E + E + h * dh + lane] = dv[i];
+          }
+      }
+    }
+    // dQ = scale · dS K: [L, dh]
+    if (L > 32) {
+      for (int t = warp; t < (L + 3) / 4; t += nw) {
+        float dq[4];
+        tile_ak<4>(dSs, 4 * t, L, SP, Ks, dp, S, lane, dq);
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+          if (4 * t + i < L) a.dq[((int64_t)b * L + 4 * t + i) * E + h * dh + lane] = dq[i] * a.scale;
+      }
+    } else {
+      for (int t = warp; t < (L + 1) / 2; t += nw) {
+        float dq[2];
+        tile_ak<2>(dSs, 2 * t, L, SP, Ks, dp, S, lane, dq);
+#pragma unroll
+        for (int i = 0; i < 2; ++i)
+          if (2 * t + i < L) a.dq[((int64_t)b * L + 2 * t + i) * E + h * dh + lane] = dq[i] * a.scale;
+      }
+    }
+    __syncthreads();
+  }
+  if (a.qs == nullptr) return;
+  const float* qs = a.qs + (int64_t)b * L;
+  const float* ks = a.ks + (int64_t)b * S;
+  const float bscale = a.bias_scale[0];
+  float dscale = 0.f;
+  for (int i = tid; i < L * S; i += blockDim.x) {
+    const int l = i / S, s2 = i - l * S;
+    const float t = tanhf(qs[l] + ks[s2]);
+    const float db = dBs[l * SP + s2];
+    dscale = fmaf(db, t, dscale);
+    dBs[l * SP + s2] = db * bscale * (1.f - t * t);
+  }
+  dscale = warp_sum(dscale);
+  if (lane == 0) red[warp] = dscale;
+  __syncthreads();
+  if (tid == 0) {
+    float s2 = 0.f;
+    for (int i = 0; i < nw; ++i) s2 += red[i];
+    atomicAdd(a.dbias_scale, s2);
+  }
+  for (int l = warp; l < L; l += nw) {
+    float s2 = 0.f;
+    for (int j = lane; j < S; j += 32) s2 += dBs[l * SP + j];
+    s2 = warp_sum(s2);
+    if (lane == 0) a.dqs[(int64_t)b * L + l] = s2;
+  }
+  for (int j = tid; j < S; j += blockDim.x) {
+    float s2 = 0.f;
+    for (int l = 0; l < L; ++l) s2 += dBs[l * SP + j];
+    a.dks[(int64_t)b * S + j] = s2;
+  }
+}
+
 static int launch_attn_bwd(cudaStream_t st, const AttnBwdArgs& a, int B) {
   const int dh = a.E / a.H;
+  if (dh == 32) {
+    const int SP = (a.S + 3) & ~3;
+    const size_t smem32 = sizeof(float) * (4 * (size_t)a.L * SP + (size_t)(2 * a.L + 2 * a.S) * 33);
+    if (smem32 > 200 * 1024) XF_FAIL(XATTN_ERR_SHAPE, "attention backward tile needs %zu B of shared memory (> 200 KiB)", smem32);
+    static size_t configured32 = 0;
+    if (smem32 > 48 * 1024 && smem32 > configured32) {
+      XF_CUDA(cudaFuncSetAttribute(attn_bwd32_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem32));
+      configured32 = smem32;
+    }
+    attn_bwd32_kernel<<<B, 256, smem32, st>>>(a);
+    count_launch();
+    XF_LAUNCH_CHECK();
+    return XATTN_OK;
+  }
   const size_t smem = sizeof(float) * ((size_t)(2 * a.L + 2 * a.S) * (dh + 1) + 3 * (size_t)a.L * a.S);
   if (smem > 200 * 1024) XF_FAIL(XATTN_ERR_SHAPE, "attention backward tile needs %zu B of shared memory (> 200 KiB)", smem);
   static size_t configured = 0;

@@ -5,6 +5,7 @@
 //   (temporal.py:108-109) | head :405-411.
 // Every intermediate the backward needs is kept in the caller's workspace (layout: compute_ws_f32).
 #include "gemm_simt.cuh"
+#include "smem_tile.cuh"
 #include "kernels_f32.cuh"
 
 namespace xf {
@@ -161,6 +162,103 @@ __global__ void __launch_bounds__(256) attn_fwd_kernel(AttnArgs a) {
   }
 }
 
+
+// The same for dh == 32 (one lane per head column) with register-tiled products (smem_tile.cuh): scores of the whole head go to
+// shared memory as [L][SP] (SP = S rounded up to 4, padding zeroed), one warp normalises a row, then O = Pd·V.
+__global__ void __launch_bounds__(256) attn_fwd32_kernel(AttnArgs a) {
+  extern __shared__ __align__(16) float sm[];
+  const int b = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nw = blockDim.x >> 5;
+  const int L = a.L, S = a.S, E = a.E, H = a.H, SP = (S + 3) & ~3;
+  constexpr int dh = 32, dp = 33;
+  float* Sc = sm;                 // [L][SP]
+  float* Qs = Sc + L * SP;        // [L][dp]
+  float* Ks = Qs + L * dp;        // [S][dp]
+  float* Vs = Ks + S * dp;        // [S][dp]
+  const float* q = a.q + (int64_t)b * L * E;
+  const float* kv = a.kv + (int64_t)b * S * 2 * E;
+  const float bscale = a.bias_scale ? a.bias_scale[0] : 0.f;
+  const float* qs = a.qs ? a.qs + (int64_t)b * L : nullptr;
+  const float* ks = a.ks ? a.ks + (int64_t)b * S : nullptr;
+  const bool lanes_on_s = S >= L;   // the longer side runs along the lanes
+  const int AR = lanes_on_s ? L : S, BR = lanes_on_s ? S : L;
+  const float* Am = lanes_on_s ? Qs : Ks;
+  const float* Bm = lanes_on_s ? Ks : Qs;
+  const int tiles_a = (AR + 1) / 2, ntile = tiles_a * ((BR + 159) / 160);
+  for (int h = 0; h < H; ++h) {
+    for (int i = tid; i < L * dh; i += blockDim.x) {
+      const int l = i >> 5, d = i & 31;
+      Qs[l * dp + d] = q[(int64_t)l * E + h * dh + d] * a.scale;   // q scaled before the product, as torch does
+    }
+    for (int i = tid; i < S * dh; i += blockDim.x) {
+      const int s = i >> 5, d = i & 31;
+      Ks[s * dp + d] = kv[(int64_t)s * 2 * E + h * dh + d];
+      Vs[s * dp + d] = kv[(int64_t)s * 2 * E + E + h * dh + d];
+    }
+    __syncthreads();
+    for (int t = warp; t < ntile; t += nw) {
+      const int a0 = (t % tiles_a) * 2, b0 = (t / tiles_a) * 160;
+      float acc[2][5];
+      tile_nt<2, 5>(Am, a0, AR, dp, Bm, b0, BR, dp, dh, lane, acc);
+#pragma unroll
+      for (int i = 0; i < 2; ++i)
+#pragma unroll
+        for (int j = 0; j < 5; ++j) {
+          const int ar = a0 + i, br = b0 + lane + 32 * j;
+          if (ar < AR && br < BR) {
+            const int l = lanes_on_s ? ar : br, s2 = lanes_on_s ? br : ar;
+            float v = acc[i][j];
+            if (qs) v += tanhf(qs[l] + ks[s2]) * bscale;
+            Sc[l * SP + s2] = v;
+          }
+        }
+    }
+    __syncthreads();
+    for (int l = warp; l < L; l += nw) {
+      float* pr = Sc + l * SP;
+      float mx = -INFINITY;
+      for (int s2 = lane; s2 < S; s2 += 32) mx = fmaxf(mx, pr[s2]);
+      mx = warp_max(mx);
+      float sum = 0.f;
+      for (int s2 = lane; s2 < S; s2 += 32) {
+        const float e = expf(pr[s2] - mx);
+        pr[s2] = e;
+        sum += e;
+      }
+      sum = warp_sum(sum);
+      const float inv = 1.f / sum;
+      const int64_t prow_idx = (((int64_t)b * H + h) * L + l) * S;
+      for (int s2 = lane; s2 < SP; s2 += 32) {
+        float p = 0.f;
+        if (s2 < S) {
+          p = pr[s2] * inv;
+          if (a.P) a.P[prow_idx + s2] = p;
+          if (a.p_drop > 0.f) p *= drop_factor(a.p_drop, a.seed, a.offset, a.rng_stream, (uint64_t)(prow_idx + s2));
+        }
+        pr[s2] = p;   // (padding columns: zero, the product below reads them)
+      }
+    }
+    __syncthreads();
+    if (L > 32) {
+      for (int t = warp; t < (L + 3) / 4; t += nw) {
+        float o[4];
+        tile_ak<4>(Sc, 4 * t, L, SP, Vs, dp, S, lane, o);
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+          if (4 * t + i < L) a.O[((int64_t)b * L + 4 * t + i) * E + h * dh + lane] = o[i];
+      }
+    } else {
+      for (int t = warp; t < (L + 1) / 2; t += nw) {
+        float o[2];
+        tile_ak<2>(Sc, 2 * t, L, SP, Vs, dp, S, lane, o);
+#pragma unroll
+        for (int i = 0; i < 2; ++i)
+          if (2 * t + i < L) a.O[((int64_t)b * L + 2 * t + i) * E + h * dh + lane] = o[i];
+      }
+    }
+    __syncthreads();
+  }
+}
+
 // ---------------------------------------------------------------------------------------------------------
 // s = x + drop_path(y) ; out = LayerNorm(s) (fusion.py:395 / :399).  One warp per token row.  `y` is
 // overwritten with s (the backward needs it) and mean / rstd are saved.
@@ -279,6 +377,19 @@ __global__ void __launch_bounds__(256) pool_head_fwd_kernel(HeadArgs a) {
 size_t attn_smem_bytes(int L, int S, int dh, int nwarps) { return sizeof(float) * ((size_t)(L + 2 * S) * (dh + 1) + (size_t)nwarps * S); }
 
 int launch_attn_fwd(cudaStream_t st, const AttnArgs& a, int B) {
+  if (a.E / a.H == 32) {   // one lane per head column: the register-tiled kernel
+    const size_t smem = sizeof(float) * ((size_t)a.L * ((a.S + 3) & ~3) + (size_t)(a.L + 2 * a.S) * 33);
+    if (smem > 200 * 1024) XF_FAIL(XATTN_ERR_SHAPE, "attention tile needs %zu B of shared memory (> 200 KiB)", smem);
+    static size_t configured32 = 0;
+    if (smem > 48 * 1024 && smem > configured32) {
+      XF_CUDA(cudaFuncSetAttribute(attn_fwd32_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      configured32 = smem;
+    }
+    attn_fwd32_kernel<<<B, 256, smem, st>>>(a);
+    count_launch();
+    XF_LAUNCH_CHECK();
+    return XATTN_OK;
+  }
   const size_t smem = attn_smem_bytes(a.L, a.S, a.E / a.H, 8);
   if (smem > 200 * 1024) XF_FAIL(XATTN_ERR_SHAPE, "attention tile needs %zu B of shared memory (> 200 KiB)", smem);
   static size_t configured = 0;

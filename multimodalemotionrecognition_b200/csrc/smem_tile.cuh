@@ -1,0 +1,87 @@
+// Register-tiled products over operands that sit in shared memory — the per-clip, per-head matrix products of the fp32
+// attention kernels (fwd_f32.cu / bwd_f32.cu) when the head width is one warp (dh == 32).  The plain loops they replace spent
+// two shared-memory loads on every FMA; here a warp shares TM broadcast rows and every lane reuses them.
+#pragma once
+#include "common.cuh"
+
+namespace xf {
+
+// acc[i][j] = sum_k A[(a0+i)*pa + k] * B[(b0 + lane + 32j)*pb + k],  k < K.  Rows past the operands are clamped (the caller drops
+// those results).  pa, pb odd (dh + 1): the lane-strided rows of B fall in distinct banks, the rows of A are broadcasts.
+template <int TM, int TN>
+__device__ __forceinline__ void tile_nt(const float* __restrict__ A, int a0, int a_rows, int pa, const float* __restrict__ B, int b0,
+                                        int b_rows, int pb, int K, int lane, float (&acc)[TM][TN]) {
+  const float* ap[TM];
+  const float* bp[TN];
+#pragma unroll
+  for (int i = 0; i < TM; ++i) ap[i] = A + min(a0 + i, a_rows - 1) * pa;
+#pragma unroll
+  for (int j = 0; j < TN; ++j) bp[j] = B + min(b0 + lane + 32 * j, b_rows - 1) * pb;
+#pragma unroll
+  for (int i = 0; i < TM; ++i)
+#pragma unroll
+    for (int j = 0; j < TN; ++j) acc[i][j] = 0.f;
+#pragma unroll 4
+  for (int k = 0; k < K; ++k) {
+    float a[TM], b[TN];
+#pragma unroll
+    for (int i = 0; i < TM; ++i) a[i] = ap[i][k];
+#pragma unroll
+    for (int j = 0; j < TN; ++j) b[j] = bp[j][k];
+#pragma unroll
+    for (int i = 0; i < TM; ++i)
+#pragma unroll
+      for (int j = 0; j < TN; ++j) acc[i][j] = fmaf(a[i], b[j], acc[i][j]);
+  }
+}
+
+// acc[i] = sum_k A[(r0+i)*pa + k] * B[k*pb + lane],  k < K.  pa % 4 == 0 and A 16-byte aligned: four k at a time come in as one
+// broadcast float4 per row; entries A[r][k >= K] up to the next multiple of 4 must be readable (they are multiplied by clamped B
+// rows and must be ZERO).  Rows past `rows` are clamped.
+template <int TM>
+__device__ __forceinline__ void tile_ak(const float* __restrict__ A, int r0, int rows, int pa, const float* __restrict__ B, int pb, int K,
+                                        int lane, float (&acc)[TM]) {
+  const float4* ap[TM];
+#pragma unroll
+  for (int i = 0; i < TM; ++i) {
+    ap[i] = reinterpret_cast<const float4*>(A + min(r0 + i, rows - 1) * pa);
+    acc[i] = 0.f;
+  }
+  const float* bp = B + lane;
+  const int K4 = (K + 3) >> 2;
+#pragma unroll 2
+  for (int k4 = 0; k4 < K4; ++k4) {
+    const int k = 4 * k4;
+    const float b0 = bp[min(k, K - 1) * pb], b1 = bp[min(k + 1, K - 1) * pb], b2 = bp[min(k + 2, K - 1) * pb], b3 = bp[min(k + 3, K - 1) * pb];
+#pragma unroll
+    for (int i = 0; i < TM; ++i) {
+      const float4 a = ap[i][k4];
+      acc[i] = fmaf(a.x, b0, fmaf(a.y, b1, fmaf(a.z, b2, fmaf(a.w, b3, acc[i]))));
+    }
+  }
+}
+
+// acc[i] = sum_k A[k*pa + m0 + i] * B[k*pb + lane],  k < K, TM in {2, 4}.  pa % 4 == 0, m0 % TM == 0: the TM consecutive columns of a
+// row of A come in as one broadcast vector load (columns past the operand are padding the caller ignores).
+template <int TM>
+__device__ __forceinline__ void tile_am(const float* __restrict__ A, int m0, int pa, const float* __restrict__ B, int pb, int K, int lane,
+                                        float (&acc)[TM]) {
+  static_assert(TM == 2 || TM == 4, "tile_am: TM is 2 or 4");
+#pragma unroll
+  for (int i = 0; i < TM; ++i) acc[i] = 0.f;
+  const float* ap = A + m0;
+  const float* bp = B + lane;
+#pragma unroll 4
+  for (int k = 0; k < K; ++k) {
+    const float b = bp[k * pb];
+    if (TM == 4) {
+      const float4 a = *reinterpret_cast<const float4*>(ap + k * pa);
+      acc[0] = fmaf(a.x, b, acc[0]); acc[1] = fmaf(a.y, b, acc[1]); acc[2] = fmaf(a.z, b, acc[2]); acc[3] = fmaf(a.w, b, acc[3]);
+    } else {
+      const float2 a = *reinterpret_cast<const float2*>(ap + k * pa);
+      acc[0] = fmaf(a.x, b, acc[0]); acc[1] = fmaf(a.y, b, acc[1]);
+    }
+  }
+}
+
+}  // namespace xf
