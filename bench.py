@@ -374,7 +374,7 @@ def run_b200_arm(args) -> None:
         line = {
             "metric": METRIC, "value": value, "unit": "clips/s", "n_gpus": world, "steps": args.steps,
             "warmup": max(args.warmup, 3), "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak",
-            "vs_baseline": None, "dtype": "bf16" if args.precision == "bf16" else "f32", "data": "synthetic",
+            "vs_baseline": None, "dtype": {"bf16": "bf16", "fp32": "f32", "tf32": "tf32"}[args.precision], "data": "synthetic",
             "config": workload_config(args), "clocks": clocks, "gpu_launches": int(launches),
             "roofline": roofline, "e2e": e2e, "cpu_baseline": cpu,
         }
@@ -391,13 +391,16 @@ def main() -> None:
     ap.add_argument("--impl", choices=["b200", "reference"], default="b200")
     ap.add_argument("--workload", choices=["forward", "train"], default="forward")
     ap.add_argument("--batch", type=int, default=None, help="clips per GPU (default 4096 forward, 1024 train)")
-    ap.add_argument("--precision", choices=["bf16", "fp32"], default="bf16")
+    ap.add_argument("--precision", choices=["bf16", "fp32", "tf32"], default=None,
+                    help="forward: bf16 (default) | fp32; train: tf32 (default: fp32 tensors, Linears on tcgen05) | fp32 (SIMT parity path)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
     if args.batch is None:
         args.batch = 1024 if args.workload == "train" else 4096
-    if args.workload == "train":
-        args.precision = "fp32"
+    if args.precision is None:
+        args.precision = "tf32" if args.workload == "train" else "bf16"
+    if args.workload == "train" and args.precision == "bf16":
+        raise SystemExit("the bf16 tcgen05 path is inference-only; train with --precision tf32 or fp32")
     if args.impl == "reference":
         run_reference_arm(args)
     else:

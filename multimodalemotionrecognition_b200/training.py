@@ -104,6 +104,10 @@ def gather_logits(local_logits: torch.Tensor, total: int, group=None) -> torch.T
     if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size(group) == 1:
         return local_logits
     world = dist.get_world_size(group)
+    if total % world == 0:   # equal shards: one collective straight into the result, no padding / slicing kernels
+        out = torch.empty((total, local_logits.shape[1]), dtype=local_logits.dtype, device=local_logits.device)
+        dist.all_gather_into_tensor(out, local_logits.contiguous(), group=group)
+        return out
     per = (total + world - 1) // world
     pad = torch.zeros((per, local_logits.shape[1]), dtype=local_logits.dtype, device=local_logits.device)
     pad[: local_logits.shape[0]] = local_logits

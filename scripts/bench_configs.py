@@ -151,7 +151,7 @@ def run_flat():
               "sequence_inputs": {"ms_per_step": ms_seq, "clips_per_s": B * world / (ms_seq * 1e-3), "input_gbs_per_gpu": gbs,
                                   "note": "temporal mean fused in; HBM-bound (245,248 B/clip)"},
               "pooled_inputs": {"ms_per_step": ms_pool, "clips_per_s": B * world / (ms_pool * 1e-3), "note": "latency-bound"},
-              "dtype": "bf16 embeddings, f32 arithmetic"})
+              "dtype": "bf16 embeddings and operands (tcgen05 kind::f16), fp32 accumulate"})
 
 
 if __name__ == "__main__":
