@@ -91,12 +91,77 @@ class Stage1Trainer:
                                                    self.weight_decay, self.step_count, int(self.decoupled), _stream_ptr(dev)))
         head.mark_parameters_updated()
 
+    def step_cached(self, cache: "FrozenEmbeddingCache", indices: torch.Tensor, video: torch.Tensor, audio: torch.Tensor,
+                    labels: torch.Tensor, training: bool = True) -> torch.Tensor:
+        """One Stage-1 step of a ``FusionModel`` from raw loader tensors: the frozen backbones run only for samples the
+        cache has not seen (``FrozenEmbeddingCache``), the head steps on the cached bf16 embeddings."""
+        video_emb, audio_emb = cache.fetch_or_compute(self.head, indices, video, audio)
+        return self.step(video_emb, audio_emb, labels, training=training)
+
     def step(self, video_emb: torch.Tensor, audio_emb: torch.Tensor, labels: torch.Tensor, training: bool = True) -> torch.Tensor:
         """One full Stage-1 step; returns this rank's mean loss as a 0-dim CUDA tensor (no host sync)."""
         loss = self.forward_backward(video_emb, audio_emb, labels, training=training)
         self.allreduce_gradients()
         self.optimizer_step()
         return loss
+
+
+class FrozenEmbeddingCache:
+    """Backbone outputs of a Stage-1 dataset, resident in HBM in the dtype the tensor-core kernels read.
+
+    Stage 1 freezes both encoders (``train.py:808-812``) but the reference still runs ResNet18 and WavLM on every sample
+    of every epoch (``train.py:211`` -> ``fusion.py:368-377``); with the head at ~0.1 µs per clip that is where the
+    Stage-1 wall-clock goes.  The cache keeps each sample's ``[T,Dv]`` / ``[Ta,Da]`` embeddings as bf16 rows keyed by
+    dataset index (245,248 B per clip at the reference dimensions: ~700 k clips fit in 180 GB), computes a sample's
+    embeddings the first time its index shows up and serves later epochs from HBM, emitting bf16 directly — no fp32
+    round trip between backbone and head.  Only valid when a sample's input tensors are the same every epoch (no
+    augmentation; the loader's 4th item, ``train.py:200``, identifies the sample)."""
+
+    def __init__(self, num_samples: int, T: int, Ta: int, Dv: int = 512, Da: int = 768, device="cuda",
+                 dtype: torch.dtype = torch.bfloat16) -> None:
+        self.video = torch.empty((num_samples, T, Dv), dtype=dtype, device=device)
+        self.audio = torch.empty((num_samples, Ta, Da), dtype=dtype, device=device)
+        self.valid = torch.zeros(num_samples, dtype=torch.bool, device=device)
+        self.hits = 0
+        self.misses = 0
+
+    def nbytes(self) -> int:
+        return self.video.numel() * self.video.element_size() + self.audio.numel() * self.audio.element_size()
+
+    def missing(self, indices: torch.Tensor) -> torch.Tensor:
+        """Boolean mask over ``indices``: True where the sample has not been embedded yet."""
+        return ~self.valid[indices.to(self.valid.device)]
+
+    def put(self, indices: torch.Tensor, video_emb: torch.Tensor, audio_emb: torch.Tensor) -> None:
+        idx = indices.to(self.valid.device)
+        self.video[idx] = video_emb.to(device=self.video.device, dtype=self.video.dtype)
+        self.audio[idx] = audio_emb.to(device=self.audio.device, dtype=self.audio.dtype)
+        self.valid[idx] = True
+
+    def get(self, indices: torch.Tensor) -> tuple[torch.Tensor, torch.Tensor]:
+        idx = indices.to(self.valid.device)
+        return self.video.index_select(0, idx), self.audio.index_select(0, idx)
+
+    @staticmethod
+    @torch.no_grad()
+    def embed(model, video: torch.Tensor, audio: torch.Tensor) -> tuple[torch.Tensor, torch.Tensor]:
+        """The frozen part of ``FusionModel.forward`` (``fusion.py:368-370``, ``:377``)."""
+        b, t, c, h, w = video.shape
+        v_feat = model.video_model.backbone(video.view(b * t, c, h, w)).view(b, t, -1)
+        a_seq = model.audio_model.encode_sequence(audio)
+        return v_feat, a_seq
+
+    def fetch_or_compute(self, model, indices: torch.Tensor, video: torch.Tensor, audio: torch.Tensor):
+        """Embeddings of the batch; the backbones run only on the samples whose index is new."""
+        miss = self.missing(indices)
+        n_miss = int(miss.sum())
+        if n_miss:
+            sel = miss.to(video.device)
+            v_feat, a_seq = self.embed(model, video[sel], audio[sel])
+            self.put(indices.to(self.valid.device)[miss], v_feat, a_seq)
+        self.misses += n_miss
+        self.hits += int(indices.numel()) - n_miss
+        return self.get(indices)
 
 
 def gather_logits(local_logits: torch.Tensor, total: int, group=None) -> torch.Tensor:

@@ -64,3 +64,50 @@ def test_shard_range_partitions():
             for (a, b), (c, d) in zip(spans, spans[1:]):
                 assert b == c and b - a >= d - c >= 0
             assert max(b - a for a, b in spans) - min(b - a for a, b in spans) <= 1
+
+
+def test_frozen_embedding_cache_runs_backbones_once_per_sample():
+    """Stage-1 embeddings are computed the first time a dataset index shows up and served from the cache
+    (bf16) afterwards; host-side logic, CPU tensors."""
+    import torch
+    from torch import nn
+
+    from multimodalemotionrecognition_b200.training import FrozenEmbeddingCache
+
+    calls = {"video": 0, "audio": 0}
+
+    class Video(nn.Module):
+        embedding_dim = 12
+
+        def __init__(self):
+            super().__init__()
+
+            class Backbone(nn.Module):
+                def forward(self, x):
+                    calls["video"] += x.shape[0]
+                    return x.flatten(1)[:, :12]
+            self.backbone = Backbone()
+
+    class Audio(nn.Module):
+        def encode_sequence(self, a):
+            calls["audio"] += a.shape[0]
+            return a.view(a.shape[0], 5, 10)
+
+    class Model:
+        video_model, audio_model = Video(), Audio()
+
+    cache = FrozenEmbeddingCache(num_samples=9, T=3, Ta=5, Dv=12, Da=10, device="cpu")
+    assert cache.nbytes() == 9 * (3 * 12 + 5 * 10) * 2
+    g = torch.Generator().manual_seed(0)
+    data_v = torch.randn(9, 3, 3, 2, 2, generator=g)
+    data_a = torch.randn(9, 50, generator=g)
+    idx = torch.tensor([4, 1, 7])
+    v, a = cache.fetch_or_compute(Model, idx, data_v[idx], data_a[idx])
+    assert v.dtype == torch.bfloat16 and v.shape == (3, 3, 12) and a.shape == (3, 5, 10)
+    assert calls == {"video": 9, "audio": 3} and (cache.hits, cache.misses) == (0, 3)
+    assert torch.equal(v, data_v[idx].reshape(9, -1)[:, :12].view(3, 3, 12).bfloat16())
+    idx2 = torch.tensor([1, 2, 4])
+    v2, a2 = cache.fetch_or_compute(Model, idx2, data_v[idx2], data_a[idx2])
+    assert calls == {"video": 12, "audio": 4} and (cache.hits, cache.misses) == (2, 4)   # only sample 2 was new
+    assert torch.equal(a2[0], a[1]) and torch.equal(v2[2], v[0])
+    assert cache.missing(torch.arange(9)).tolist() == [True, False, False, True, False, True, True, False, True]
