@@ -26,7 +26,7 @@
 extern "C" {
 #endif
 
-#define XATTN_ABI_VERSION 8
+#define XATTN_ABI_VERSION 9
 
 #if defined(__GNUC__)
 #define XATTN_API __attribute__((visibility("default")))
@@ -184,7 +184,8 @@ typedef struct flat_head_config {
   int32_t gated;            /* 0: mode="concat" (fusion.py:243-248), 1: mode="gated" (:252-259)         */
   int32_t io_dtype;
   int32_t precision;        /* XATTN_DTYPE_F32: fp32 SIMT arithmetic; XATTN_DTYPE_BF16: temporal mean -> bf16, every Linear
-                               of width >= 128 on the tcgen05 projection GEMM (bf16 embeddings, dims %% 64 / %% 128) */
+                               of width >= 128 on the tcgen05 projection GEMM (bf16 embeddings, dims %% 64 / %% 128);
+                               XATTN_PREC_TF32: fp32 arithmetic with the Linears on tcgen05 tf32 where dims allow  */
 } flat_head_config;
 
 typedef enum flat_param_id {
@@ -212,6 +213,15 @@ XATTN_API int flat_head_workspace_bytes(const flat_head_config* cfg, int64_t* by
  * fusion.py:413-435 (+ :137-139).  Eval mode (ModalityDropout / Dropout identity). */
 XATTN_API int flat_head_forward(const flat_head_config* cfg, const float* params, const void* video_emb, const void* audio_emb,
                       float* logits, void* workspace, int64_t workspace_bytes, void* stream);
+
+/* The ClipStyleAlignment loss of the flat heads (fusion.py:141-149; what FusionModel.pop_alignment_loss() returns, train.py:221-222):
+ * 0.5·(CE(s·â v̂ᵀ, arange(B)) + CE(s·v̂ âᵀ, arange(B))) with â, v̂ the L2-normalised alignment projections of the temporally
+ * pooled embeddings and s = min(exp(*logit_scale), 100).  A B x B cross-sample term: under batch sharding gather the batch first.
+ * `logit_scale`: device pointer to semantic_alignment.logit_scale; `loss`: device scalar.  precision != F32 runs the three
+ * contractions on tcgen05 (tf32 products). */
+XATTN_API int flat_head_alignment_workspace_bytes(const flat_head_config* cfg, int64_t* bytes);
+XATTN_API int flat_head_alignment_loss(const flat_head_config* cfg, const float* params, const float* logit_scale, const void* video_emb,
+                                       const void* audio_emb, float* loss, void* workspace, int64_t workspace_bytes, void* stream);
 
 /* One tensor-core GEMM of the training path in isolation (tests): form 0: C[M,N] = A[M,K]·W[N,K]^T + bias; form 1: C[M,N] =
  * A[M,K]·W[K,N]; form 2: C[N1=K... see gemm_tc.cuh] C[N,K] += A[M,N]^T·B[M,K] with fp32 operands; form 3: the same with bf16

@@ -12,7 +12,7 @@ from pathlib import Path
 
 LIB_NAME = "libxattn_fusion.so"
 LIB_PATH = Path(__file__).resolve().parent / LIB_NAME
-ABI_VERSION = 8
+ABI_VERSION = 9
 
 # xattn_status
 OK, ERR_SHAPE, ERR_DTYPE, ERR_ALIGN, ERR_ARCH, ERR_CUDA, ERR_WORKSPACE, ERR_NULL = range(8)
@@ -94,6 +94,9 @@ _EXPORTS = {
     "flat_head_param_layout": (C.c_int, [C.POINTER(FlatHeadConfig), C.POINTER(C.c_int64), C.POINTER(C.c_int64),
                                          C.POINTER(C.c_int64)]),
     "flat_head_workspace_bytes": (C.c_int, [C.POINTER(FlatHeadConfig), C.POINTER(C.c_int64)]),
+    "flat_head_alignment_workspace_bytes": (C.c_int, [C.POINTER(FlatHeadConfig), C.POINTER(C.c_int64)]),
+    "flat_head_alignment_loss": (C.c_int, [C.POINTER(FlatHeadConfig), C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
+                                           C.c_void_p, C.c_int64, C.c_void_p]),
     "xattn_debug_gemm_tc": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_int64, C.c_int32, C.c_int32,
                                       C.c_int32, C.c_void_p]),
     "xattn_debug_gemm_tf32": (C.c_int, [C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_int32,

@@ -38,7 +38,8 @@ static int flat_validate(const flat_head_config* c) {
   if (c->B < 0 || c->T <= 0 || c->Ta <= 0 || c->Dv <= 0 || c->Da <= 0 || c->common_dim <= 0 || c->C <= 0 || c->align_dim < 0)
     XF_FAIL(XATTN_ERR_SHAPE, "bad flat head dimensions");
   if (c->io_dtype != XATTN_DTYPE_F32 && c->io_dtype != XATTN_DTYPE_BF16) XF_FAIL(XATTN_ERR_DTYPE, "unknown io_dtype %d", c->io_dtype);
-  if (c->precision != XATTN_DTYPE_F32 && c->precision != XATTN_DTYPE_BF16) XF_FAIL(XATTN_ERR_DTYPE, "unknown precision %d", c->precision);
+  if (c->precision != XATTN_DTYPE_F32 && c->precision != XATTN_DTYPE_BF16 && c->precision != XATTN_PREC_TF32)
+    XF_FAIL(XATTN_ERR_DTYPE, "unknown precision %d", c->precision);
   if (c->precision == XATTN_DTYPE_BF16) {   // tcgen05 projection GEMMs: bf16 embeddings, K %% 64 == 0, N %% 128 == 0
     const int in_a = c->align_dim > 0 ? c->align_dim : c->Da, in_v = c->align_dim > 0 ? c->align_dim : c->Dv;
     if (c->io_dtype != XATTN_DTYPE_BF16 || c->Da % 64 || c->Dv % 64 || c->align_dim % 128 || c->common_dim % 128 || in_a % 64 || in_v % 64)
@@ -146,6 +147,8 @@ static int flat_forward_impl(const flat_head_config& c, const float* params, con
   const int B = c.B, Cm = c.common_dim, A = c.align_dim;
   launch_mean<TIO, float>(st, xa, ws + w.a_pool, B, c.Ta, c.Da);
   launch_mean<TIO, float>(st, xv, ws + w.v_pool, B, c.T, c.Dv);
+  g_tc_gemm = c.precision == XATTN_PREC_TF32;   // (linear_fwd: tcgen05 tf32 where the dimensions allow; launch_gemm stays SIMT)
+  g_tc_status = XATTN_OK;
   const float* a_in = ws + w.a_pool;
   const float* v_in = ws + w.v_pool;
   int in_a = c.Da, in_v = c.Dv;
@@ -165,8 +168,9 @@ static int flat_forward_impl(const flat_head_config& c, const float* params, con
     flat_gate_cls_kernel<<<B, 256, sizeof(float) * Cm, st>>>(ws + w.cat, ws + w.z, P(FP_CLS_W), P(FP_CLS_B), logits, Cm, c.C);
     count_launch();
   }
+  g_tc_gemm = false;
   XF_LAUNCH_CHECK();
-  return XATTN_OK;
+  return g_tc_status;
 }
 
 // ---- precision = BF16: the same op sequence with every Linear of width >= 128 on the tcgen05 projection GEMM (gemm_tc.cu) ----
@@ -252,6 +256,91 @@ static int flat_forward_tc(const flat_head_config& c, const float* params, const
   return XATTN_OK;
 }
 
+// ---- ClipStyleAlignment loss (fusion.py:141-149): 0.5·(CE(s·â v̂ᵀ, arange) + CE(s·v̂ âᵀ, arange)), s = min(exp(logit_scale), 100) ----
+struct AlignWs {
+  int64_t a_pool, v_pool, a_al, v_al, L, terms, total;   // floats
+};
+static void align_ws(const flat_head_config& c, AlignWs& w) {
+  const int64_t B = c.B, A = c.align_dim > 0 ? c.align_dim : 1;
+  int64_t off = 0;
+  auto take = [&](int64_t n) { int64_t o = off; off += al4(n); return o; };
+  w.a_pool = take(B * c.Da); w.v_pool = take(B * c.Dv); w.a_al = take(B * A); w.v_al = take(B * A);
+  w.L = take(B * B); w.terms = take(2 * B);
+  w.total = off;
+}
+
+// x_r /= max(||x_r||, 1e-12)   (F.normalize, fusion.py:141-142); one warp per row
+__global__ void __launch_bounds__(256) l2norm_rows_kernel(float* __restrict__ x, int rows, int D) {
+  const int r = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+  if (r >= rows) return;
+  float* p = x + (int64_t)r * D;
+  float s = 0.f;
+  for (int k = lane; k < D; k += 32) s = fmaf(p[k], p[k], s);
+  s = warp_sum(s);
+  const float inv = 1.f / fmaxf(sqrtf(s), 1e-12f);
+  for (int k = lane; k < D; k += 32) p[k] *= inv;
+}
+
+// out[i] = logsumexp_j(s·L[i,j]) - s·L[i,i]: the cross-entropy term of row i against target i; one warp per row, two passes
+__global__ void __launch_bounds__(256) clip_row_terms_kernel(const float* __restrict__ L, int B, const float* __restrict__ logit_scale,
+                                                             float* __restrict__ out) {
+  const int i = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+  if (i >= B) return;
+  const float s = fminf(expf(__ldg(logit_scale)), 100.f);
+  const float* row = L + (int64_t)i * B;
+  float mx = -INFINITY;
+  for (int j = lane; j < B; j += 32) mx = fmaxf(mx, row[j]);
+  mx = warp_max(mx);
+  float sum = 0.f;
+  for (int j = lane; j < B; j += 32) sum += expf(s * (row[j] - mx));
+  sum = warp_sum(sum);
+  if (lane == 0) out[i] = s * mx + logf(sum) - s * row[i];
+}
+
+// loss = 0.5·(mean(terms[0:B]) + mean(terms[B:2B])), summed in a fixed order by one CTA
+__global__ void __launch_bounds__(256) clip_loss_final_kernel(const float* __restrict__ terms, int B, float* __restrict__ loss) {
+  __shared__ float red[256];
+  float s = 0.f;
+  for (int i = threadIdx.x; i < 2 * B; i += 256) s += terms[i];
+  red[threadIdx.x] = s;
+  __syncthreads();
+  for (int o = 128; o > 0; o >>= 1) {
+    if ((int)threadIdx.x < o) red[threadIdx.x] += red[threadIdx.x + o];
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) loss[0] = 0.5f * red[0] / (float)B;
+}
+
+template <typename TIO>
+static int alignment_loss_impl(const flat_head_config& c, const float* params, const float* logit_scale, const TIO* xv, const TIO* xa,
+                               float* loss, float* ws, cudaStream_t st) {
+  FlatLayout pl;
+  flat_layout(c, pl);
+  AlignWs w;
+  align_ws(c, w);
+  auto P = [&](int id) { return params + pl.off[id]; };
+  const int B = c.B, A = c.align_dim;
+  launch_mean<TIO, float>(st, xa, ws + w.a_pool, B, c.Ta, c.Da);
+  launch_mean<TIO, float>(st, xv, ws + w.v_pool, B, c.T, c.Dv);
+  g_tc_gemm = c.precision != XATTN_DTYPE_F32;   // tensor-core Linears (tf32 products) where the dimensions allow
+  g_tc_status = XATTN_OK;
+  linear_fwd<float>(st, ws + w.a_pool, P(FP_ALIGN_A_W), P(FP_ALIGN_A_B), ws + w.a_al, B, A, c.Da);
+  linear_fwd<float>(st, ws + w.v_pool, P(FP_ALIGN_V_W), P(FP_ALIGN_V_B), ws + w.v_al, B, A, c.Dv);
+  l2norm_rows_kernel<<<(B + 7) / 8, 256, 0, st>>>(ws + w.a_al, B, A);
+  l2norm_rows_kernel<<<(B + 7) / 8, 256, 0, st>>>(ws + w.v_al, B, A);
+  count_launch(2);
+  // the B x B cosine matrix once per direction (the second product is the transpose: rows stay contiguous for the row-wise pass)
+  linear_fwd<float>(st, ws + w.a_al, ws + w.v_al, nullptr, ws + w.L, B, B, A);
+  clip_row_terms_kernel<<<(B + 7) / 8, 256, 0, st>>>(ws + w.L, B, logit_scale, ws + w.terms);
+  linear_fwd<float>(st, ws + w.v_al, ws + w.a_al, nullptr, ws + w.L, B, B, A);
+  clip_row_terms_kernel<<<(B + 7) / 8, 256, 0, st>>>(ws + w.L, B, logit_scale, ws + w.terms + B);
+  clip_loss_final_kernel<<<1, 256, 0, st>>>(ws + w.terms, B, loss);
+  count_launch(3);
+  g_tc_gemm = false;
+  XF_LAUNCH_CHECK();
+  return g_tc_status;
+}
+
 }  // namespace xf
 
 using namespace xf;
@@ -296,4 +385,34 @@ extern "C" XATTN_API int flat_head_forward(const flat_head_config* cfg, const fl
     return flat_forward_impl<__nv_bfloat16>(*cfg, params, (const __nv_bfloat16*)video_emb, (const __nv_bfloat16*)audio_emb, logits,
                                             (float*)workspace, st);
   return flat_forward_impl<float>(*cfg, params, (const float*)video_emb, (const float*)audio_emb, logits, (float*)workspace, st);
+}
+
+extern "C" XATTN_API int flat_head_alignment_workspace_bytes(const flat_head_config* cfg, int64_t* bytes) {
+  XF_TRY(flat_validate(cfg));
+  if (!bytes) XF_FAIL(XATTN_ERR_NULL, "bytes is NULL");
+  AlignWs w;
+  align_ws(*cfg, w);
+  *bytes = w.total * (int64_t)sizeof(float);
+  return XATTN_OK;
+}
+
+extern "C" XATTN_API int flat_head_alignment_loss(const flat_head_config* cfg, const float* params, const float* logit_scale,
+                                                  const void* video_emb, const void* audio_emb, float* loss, void* workspace,
+                                                  int64_t workspace_bytes, void* stream) {
+  XF_TRY(flat_validate(cfg));
+  if (!params || !logit_scale || !video_emb || !audio_emb || !loss || !workspace) XF_FAIL(XATTN_ERR_NULL, "NULL pointer argument");
+  if (cfg->align_dim <= 0) XF_FAIL(XATTN_ERR_SHAPE, "the alignment loss needs align_dim > 0 (fusion_align_mode=\"clip\")");
+  if (cfg->B <= 0) XF_FAIL(XATTN_ERR_SHAPE, "the alignment loss needs at least one clip");
+  if (((uintptr_t)video_emb | (uintptr_t)audio_emb | (uintptr_t)params | (uintptr_t)workspace) & 15)
+    XF_FAIL(XATTN_ERR_ALIGN, "pointers must be 16-byte aligned");
+  XF_TRY(check_device_sm100());
+  AlignWs w;
+  align_ws(*cfg, w);
+  if (workspace_bytes < w.total * (int64_t)sizeof(float))
+    XF_FAIL(XATTN_ERR_WORKSPACE, "workspace too small: %lld < %lld bytes", (long long)workspace_bytes, (long long)(w.total * 4));
+  cudaStream_t st = (cudaStream_t)stream;
+  if (cfg->io_dtype == XATTN_DTYPE_BF16)
+    return alignment_loss_impl<__nv_bfloat16>(*cfg, params, logit_scale, (const __nv_bfloat16*)video_emb, (const __nv_bfloat16*)audio_emb, loss,
+                                              (float*)workspace, st);
+  return alignment_loss_impl<float>(*cfg, params, logit_scale, (const float*)video_emb, (const float*)audio_emb, loss, (float*)workspace, st);
 }

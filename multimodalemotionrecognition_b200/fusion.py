@@ -524,7 +524,7 @@ class XAttnFusionHead(XAttnKernelsMixin, nn.Module):
 
 class ClipStyleAlignment(nn.Module):
     """Parameter container for the CLIP-style alignment (``fusion.py:127-135``); the projections run in the flat-head
-    kernels, the contrastive loss (training only, B x B) in ``FlatHeadKernelsMixin.alignment_loss_from``."""
+    kernels, the contrastive loss (B x B) in ``FlatHeadKernelsMixin.flat_alignment_loss``."""
 
     def __init__(self, audio_dim: int, video_dim: int, align_dim: int, init_temperature: float = 0.07) -> None:
         super().__init__()
@@ -640,6 +640,38 @@ class FlatHeadKernelsMixin:
                                                      _ptr(ws), ws.numel(), _stream_ptr(dev)))
         return logits
 
+    @torch.no_grad()
+    def flat_alignment_loss(self, video_emb: torch.Tensor, audio_emb: torch.Tensor) -> torch.Tensor:
+        """The CLIP-style alignment loss of ``ClipStyleAlignment.forward`` (``fusion.py:141-149``) for a batch of sequence
+        ``[B,T,Dv]`` / ``[B,Ta,Da]`` (or pooled ``[B,1,D]``) embeddings: a 0-dim CUDA tensor, no host sync.  It is a B x B
+        cross-sample term — under batch sharding gather the embeddings first.  Forward value only (the flat
+        heads are inference-only here)."""
+        if self.semantic_alignment is None:
+            raise ValueError("the alignment loss needs fusion_align_mode=\"clip\"")
+        if video_emb.ndim != 3 or audio_emb.ndim != 3 or video_emb.shape[0] != audio_emb.shape[0] or video_emb.shape[0] == 0:
+            raise ValueError("expected non-empty video_emb [B,T,Dv] and audio_emb [B,Ta,Da] with the same B")
+        if not (video_emb.is_cuda and audio_emb.is_cuda):
+            raise RuntimeError("the B200 flat fusion heads have no CPU path: inputs must be CUDA tensors")
+        if video_emb.dtype != audio_emb.dtype:
+            raise ValueError("video_emb / audio_emb must share dtype")
+        video_emb, audio_emb = video_emb.contiguous(), audio_emb.contiguous()
+        dev = video_emb.device
+        with torch.cuda.device(dev):
+            cfg = self._flat_cfg(video_emb.shape[0], video_emb.shape[1], audio_emb.shape[1], _io_dtype(video_emb))
+            if self._flat_precision == "auto":   # tensor cores (tf32 products) whenever the three contractions fit them
+                cfg.precision = _lib.PREC_TF32 if self._flat_tc_supported() else _lib.DTYPE_F32
+            elif self._flat_precision != "fp32":
+                cfg.precision = _lib.PREC_TF32
+            flat = self._flat_params(dev)
+            n = C.c_int64()
+            _lib.check(_lib.load().flat_head_alignment_workspace_bytes(C.byref(cfg), C.byref(n)))
+            ws = torch.empty(n.value, dtype=torch.uint8, device=dev)
+            loss = torch.empty((), dtype=torch.float32, device=dev)
+            scale = self.semantic_alignment.logit_scale.detach().to(device=dev, dtype=torch.float32).contiguous()
+            _lib.check(_lib.load().flat_head_alignment_loss(C.byref(cfg), _ptr(flat), _ptr(scale), _ptr(video_emb), _ptr(audio_emb),
+                                                            _ptr(loss), _ptr(ws), ws.numel(), _stream_ptr(dev)))
+        return loss
+
     def flat_forward_pooled(self, audio_pooled: torch.Tensor, video_pooled: torch.Tensor) -> torch.Tensor:
         """logits from already pooled [B,Da] / [B,Dv] embeddings (what ``audio_model.encode`` returns)."""
         return self.flat_forward_sequences(video_pooled.unsqueeze(1), audio_pooled.unsqueeze(1))
@@ -661,6 +693,9 @@ class FlatFusionHead(FlatHeadKernelsMixin, nn.Module):
 
     def forward(self, video_emb: torch.Tensor, audio_emb: torch.Tensor) -> torch.Tensor:
         return self.flat_forward_sequences(video_emb, audio_emb)
+
+    def alignment_loss(self, video_emb: torch.Tensor, audio_emb: torch.Tensor) -> torch.Tensor:
+        return self.flat_alignment_loss(video_emb, audio_emb)
 
 
 class FusionModel(XAttnKernelsMixin, FlatHeadKernelsMixin, nn.Module):
@@ -706,12 +741,19 @@ class FusionModel(XAttnKernelsMixin, FlatHeadKernelsMixin, nn.Module):
                               precision=precision)
 
     def pop_alignment_loss(self):
+        """``fusion.py:346-349``.  The reference computes the loss inside every concat/gated forward; here the B x B term is
+        evaluated only when it is asked for, from the embeddings the last forward kept."""
         loss = self.alignment_loss
+        pending = self.__dict__.pop("_align_pending", None)
+        if loss is None and pending is not None and self.semantic_alignment is not None:
+            a_emb, v_emb = pending
+            loss = self.flat_alignment_loss(v_emb.unsqueeze(1), a_emb.unsqueeze(1))
         self.alignment_loss = None
         return loss
 
     def forward(self, video: torch.Tensor, audio: torch.Tensor):
         self.alignment_loss = None
+        self.__dict__.pop("_align_pending", None)
         if self.mode == "late":  # fusion.py:358-363 — backbone-only, no fusion math
             a_probs = torch.softmax(self.audio_model(audio), dim=1)
             v_probs = torch.softmax(self.video_model(video), dim=1)
@@ -729,5 +771,7 @@ class FusionModel(XAttnKernelsMixin, FlatHeadKernelsMixin, nn.Module):
                 raise RuntimeError("the B200 flat concat/gated heads are inference-only (eval forward, BASELINE config 5)")
             a_emb = self.audio_model.encode(audio)                                                   # fusion.py:414-415
             v_emb = self.video_model.encode(video)
+            if self.semantic_alignment is not None:
+                self._align_pending = (a_emb, v_emb)                                                 # fusion.py:417-418, evaluated lazily
             return self.flat_forward_pooled(a_emb, v_emb)
         raise ValueError(f"Unknown fusion mode: {self.mode}")

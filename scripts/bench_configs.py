@@ -146,11 +146,15 @@ def run_flat():
         with torch.no_grad():
             ms_seq = timed(lambda i: head(sets[i % 2][0], sets[i % 2][1]), 30, 5)
             ms_pool = timed(lambda i: head.flat_forward_pooled(*pooled[i % 2]), 100, 10)
+            ms_align = timed(lambda i: head.alignment_loss(sets[i % 2][0], sets[i % 2][1]), 20, 3)
         gbs = B * (T * DV + TA * DA) * 2 / (ms_seq * 1e-3) / 1e9
         emit({"config": "configs[4] flat heads with CLIP-style alignment projection", "mode": mode, "B": B, "n_gpus": world,
               "sequence_inputs": {"ms_per_step": ms_seq, "clips_per_s": B * world / (ms_seq * 1e-3), "input_gbs_per_gpu": gbs,
                                   "note": "temporal mean fused in; HBM-bound (245,248 B/clip)"},
               "pooled_inputs": {"ms_per_step": ms_pool, "clips_per_s": B * world / (ms_pool * 1e-3), "note": "latency-bound"},
+              "alignment_loss": {"ms_per_call": ms_align, "note": "B x B CLIP-style loss (training-only output, reported separately): "
+                                 "temporal means + 2 alignment projections + 2 B x B cosine products on tcgen05 (tf32) + row passes; "
+                                 f"{2 * 2 * B * B * 256 / (ms_align * 1e-3) / 1e12:.1f} TFLOP/s on the B x B products alone"},
               "dtype": "bf16 embeddings and operands (tcgen05 kind::f16), fp32 accumulate"})
 
 

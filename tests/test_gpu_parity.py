@@ -335,3 +335,55 @@ def test_flat_heads_match_reference(cuda_device, mode):
     assert _lib.launch_count() - n0 == 9     # cvt + 2 means + 5 tcgen05 GEMMs + output kernel
     assert np.abs(out_tc - ref).max() <= BF16_TOL
     assert np.abs(out_tc - ref).max() > 0    # (a different code path really ran)
+
+
+@pytest.mark.parametrize("mode", ["concat", "gated"])
+def test_flat_alignment_loss_matches_reference(cuda_device, mode):
+    """ClipStyleAlignment loss (fusion.py:141-149), SURVEY 8a row a14: the tiny golden case against the reference's own value
+    (fp32 kernels), then config-5 dimensions against the oracle on fp32 SIMT and on the tensor cores (tf32 products), and the
+    drop-in FusionModel.pop_alignment_loss() (train.py:221-222)."""
+    from multimodalemotionrecognition_b200 import FlatFusionHead, FusionModel
+
+    blob = load_npz(f"flat_tiny_{mode}.npz")
+    m = FlatFusionHead(num_classes=8, video_dim=12, audio_dim=10, common_dim=16, mode=mode, fusion_align_mode="clip",
+                       fusion_align_dim=256)
+    m.load_state_dict({k[2:]: torch.from_numpy(v) for k, v in blob.items() if k.startswith("w:")}, strict=True)
+    m = m.to(cuda_device).eval()
+    loss = m.alignment_loss(torch.from_numpy(blob["xv"]).to(cuda_device), torch.from_numpy(blob["xa"]).to(cuda_device))
+    assert loss.shape == () and abs(float(loss) - float(blob["align_loss"])) < 1e-5
+    torch.manual_seed(0)
+    mm = FlatFusionHead(num_classes=8, video_dim=512, audio_dim=768, common_dim=256, mode=mode).to(cuda_device).eval()
+    with torch.no_grad():
+        mm.semantic_alignment.logit_scale.fill_(2.0)
+    g = torch.Generator().manual_seed(4)
+    B = 256
+    xa = torch.randn(B, 5, 768, generator=g)
+    xv = torch.randn(B, 3, 512, generator=g)
+    sd = {k: v.cpu().numpy() for k, v in mm.state_dict().items()}
+    _, ref = xattn_oracle.flat_head_forward(sd, xa.numpy().mean(1), xv.numpy().mean(1), mode=mode, return_align_loss=True)
+    mm._flat_precision = "fp32"
+    l32 = float(mm.alignment_loss(xv.to(cuda_device), xa.to(cuda_device)))
+    assert abs(l32 - ref) < 1e-4, (l32, ref)
+    mm._flat_precision = "auto"
+    n0 = _lib.launch_count()
+    ltc = float(mm.alignment_loss(xv.to(cuda_device), xa.to(cuda_device)))
+    assert _lib.launch_count() - n0 == 11     # 2 means, 4 tcgen05 GEMMs, 2 normalisations, 2 row passes, final sum
+    assert abs(ltc - ref) < 1e-2, (ltc, ref)
+    # drop-in: the loss of the last concat/gated forward, evaluated when popped
+    class Enc(torch.nn.Module):
+        def __init__(self, dim):
+            super().__init__()
+            self.embedding_dim = dim
+
+        def encode(self, x):
+            return x
+    torch.manual_seed(0)
+    fm = FusionModel(Enc(768), Enc(512), 8, mode=mode, fusion_align_mode="clip", precision="fp32").to(cuda_device).eval()
+    with torch.no_grad():
+        fm.semantic_alignment.logit_scale.fill_(2.0)
+        fm(xv.mean(1).to(cuda_device), xa.mean(1).to(cuda_device))
+    sdf = {k: v.cpu().numpy() for k, v in fm.state_dict().items()}
+    _, reff = xattn_oracle.flat_head_forward(sdf, xa.numpy().mean(1), xv.numpy().mean(1), mode=mode, return_align_loss=True)
+    popped = fm.pop_alignment_loss()
+    assert popped is not None and abs(float(popped) - reff) < 1e-4
+    assert fm.pop_alignment_loss() is None
