@@ -26,7 +26,7 @@
 extern "C" {
 #endif
 
-#define XATTN_ABI_VERSION 9
+#define XATTN_ABI_VERSION 10
 
 #if defined(__GNUC__)
 #define XATTN_API __attribute__((visibility("default")))
@@ -46,6 +46,7 @@ typedef enum xattn_status {
 } xattn_status;
 
 enum { XATTN_HEAD_CONCAT = 0, XATTN_HEAD_GATED = 1 };
+enum { XATTN_POOL_MEAN = 0, XATTN_POOL_ATTN = 1 };
 enum { XATTN_DTYPE_F32 = 0, XATTN_DTYPE_BF16 = 1 };
 /* xattn_config.precision only: the fp32 kernel family (forward, backward, training) with every Linear whose dimensions allow it
  * on the tensor cores — tcgen05 kind::tf32 straight from the fp32 tensors (kind::f16 for bf16 embeddings), fp32 accumulation. */
@@ -74,6 +75,9 @@ typedef struct xattn_config {
                            xattn_backward; 0: eval                                   */
   int32_t save_for_backward; /* 1: keep activations in the workspace even in eval mode
                                 (gradient parity in eval mode)            */
+  int32_t pool_mode;    /* XATTN_POOL_MEAN (temporal.py:108-109) | XATTN_POOL_ATTN (TemporalAttentionPooling,
+                           temporal.py:9-26: LN -> Linear -> GELU -> Linear -> softmax over time -> weighted sum;
+                           fp32 family, forward only)                                 */
   float p_attn;         /* attention dropout            (fusion.py:277,280)          */
   float p_path;         /* stochastic depth             (fusion.py:282-283)          */
   float p_head;         /* head Dropout(0.2)            (fusion.py:315,322)          */
@@ -123,6 +127,19 @@ typedef enum xattn_param_id {
   XP_VK_W,         /* emotion_prior_bias.v_key_bias.weight   [1,E+P] */
   XP_VK_B,         /* emotion_prior_bias.v_key_bias.bias     [1]     */
   XP_BIAS_SCALE,   /* emotion_prior_bias.bias_scale          []      */
+  /* temporal_pooling="attn" (size 0 for "mean"): {v,a}_temporal_pool.pool.score.{0,1,4}.{weight,bias} (temporal.py:15-21) */
+  XP_VPOOL_LN_W,   /* v_temporal_pool.pool.score.0.weight [E]       */
+  XP_VPOOL_LN_B,   /* v_temporal_pool.pool.score.0.bias   [E]       */
+  XP_VPOOL_W1,     /* v_temporal_pool.pool.score.1.weight [E/2,E]   */
+  XP_VPOOL_B1,     /* v_temporal_pool.pool.score.1.bias   [E/2]     */
+  XP_VPOOL_W2,     /* v_temporal_pool.pool.score.4.weight [1,E/2]   */
+  XP_VPOOL_B2,     /* v_temporal_pool.pool.score.4.bias   [1]       */
+  XP_APOOL_LN_W,   /* a_temporal_pool.pool.score.* as above          */
+  XP_APOOL_LN_B,
+  XP_APOOL_W1,
+  XP_APOOL_B1,
+  XP_APOOL_W2,
+  XP_APOOL_B2,
   XP_COUNT
 } xattn_param_id;
 

@@ -12,12 +12,13 @@ from pathlib import Path
 
 LIB_NAME = "libxattn_fusion.so"
 LIB_PATH = Path(__file__).resolve().parent / LIB_NAME
-ABI_VERSION = 9
+ABI_VERSION = 10
 
 # xattn_status
 OK, ERR_SHAPE, ERR_DTYPE, ERR_ALIGN, ERR_ARCH, ERR_CUDA, ERR_WORKSPACE, ERR_NULL = range(8)
 HEAD_CONCAT, HEAD_GATED = 0, 1
 DTYPE_F32, DTYPE_BF16 = 0, 1
+POOL_MEAN, POOL_ATTN = 0, 1
 PREC_TF32 = 2   # xattn_config.precision only: fp32 kernel family with the Linears on tcgen05 tf32 (gemm_tf32.cu)
 
 # xattn_param_id -> reference state_dict key (None: resolved per head kind)
@@ -35,6 +36,11 @@ XP_NAMES = [
     "emotion_prior_bias.a_query_bias.weight", "emotion_prior_bias.a_query_bias.bias",
     "emotion_prior_bias.v_key_bias.weight", "emotion_prior_bias.v_key_bias.bias",
     "emotion_prior_bias.bias_scale",
+    # temporal_pooling="attn" (temporal.py:15-21); absent (size 0) for "mean"
+    "v_temporal_pool.pool.score.0.weight", "v_temporal_pool.pool.score.0.bias", "v_temporal_pool.pool.score.1.weight",
+    "v_temporal_pool.pool.score.1.bias", "v_temporal_pool.pool.score.4.weight", "v_temporal_pool.pool.score.4.bias",
+    "a_temporal_pool.pool.score.0.weight", "a_temporal_pool.pool.score.0.bias", "a_temporal_pool.pool.score.1.weight",
+    "a_temporal_pool.pool.score.1.bias", "a_temporal_pool.pool.score.4.weight", "a_temporal_pool.pool.score.4.bias",
 ]
 XP_COUNT = len(XP_NAMES)
 
@@ -61,7 +67,7 @@ def flat_param_names(gated: bool) -> list[str]:
 class XAttnConfig(C.Structure):
     _fields_ = [(n, C.c_int32) for n in (
         "B", "T", "Ta", "Dv", "Da", "E", "H", "prior_dim", "prior_hidden", "common_dim", "C", "head_kind",
-        "use_prior", "io_dtype", "precision", "training", "save_for_backward")] + [
+        "use_prior", "io_dtype", "precision", "training", "save_for_backward", "pool_mode")] + [
         ("p_attn", C.c_float), ("p_path", C.c_float), ("p_head", C.c_float), ("p_prior", C.c_float),
         ("seed", C.c_uint64), ("offset", C.c_uint64)]
 

@@ -371,6 +371,92 @@ __global__ void __launch_bounds__(256) pool_head_fwd_kernel(HeadArgs a) {
   }
 }
 
+
+// ---------------------------------------------------------------------------------------------------------
+// TemporalAttentionPooling (temporal.py:9-26): score_l = w2·GELU(W1·LN(x_l) + b1) + b2, attn = softmax_l(score),
+// out = sum_l attn_l · x_l (the UN-normalised tokens).  One CTA per clip; W1 is staged transposed in shared memory
+// ([e][j], so lane j walks a column without bank conflicts), one warp per token row.  Eval mode (Dropout identity).
+// ---------------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) attn_pool_kernel(const float* __restrict__ x, const float* __restrict__ ln_w,
+                                                        const float* __restrict__ ln_b, const float* __restrict__ w1,
+                                                        const float* __restrict__ b1, const float* __restrict__ w2,
+                                                        const float* __restrict__ b2, float* __restrict__ out, int L, int E) {
+  extern __shared__ float sm[];
+  const int b = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nw = blockDim.x >> 5;
+  const int H2 = E / 2 > 0 ? E / 2 : 1;
+  float* w1t = sm;                 // [E][H2]
+  float* yrow = w1t + E * H2;      // [nw][E]
+  float* score = yrow + nw * E;    // [L]
+  __shared__ float s_stat[2];
+  for (int i = tid; i < E * H2; i += blockDim.x) {
+    const int j = i / E, e = i - j * E;
+    w1t[e * H2 + j] = w1[i];
+  }
+  __syncthreads();
+  const float* xb = x + (int64_t)b * L * E;
+  float* y = yrow + warp * E;
+  for (int l = warp; l < L; l += nw) {
+    const float* xr = xb + (int64_t)l * E;
+    float sum = 0.f;
+    for (int e = lane; e < E; e += 32) sum += xr[e];
+    const float mu = warp_sum(sum) / (float)E;
+    float var = 0.f;
+    for (int e = lane; e < E; e += 32) {
+      const float d = xr[e] - mu;
+      var = fmaf(d, d, var);
+    }
+    const float rstd = rsqrtf(warp_sum(var) / (float)E + 1e-5f);
+    for (int e = lane; e < E; e += 32) y[e] = (xr[e] - mu) * rstd * ln_w[e] + ln_b[e];
+    __syncwarp();
+    float sc = 0.f;
+    for (int j = lane; j < H2; j += 32) {
+      float h = b1[j];
+      for (int e = 0; e < E; ++e) h = fmaf(w1t[e * H2 + j], y[e], h);
+      const float g = 0.5f * h * (1.f + erff(h * 0.70710678118654752f));   // nn.GELU() (exact)
+      sc = fmaf(w2[j], g, sc);
+    }
+    sc = warp_sum(sc);
+    if (lane == 0) score[l] = sc + b2[0];
+    __syncwarp();
+  }
+  __syncthreads();
+  if (warp == 0) {   // softmax over time
+    float mx = -INFINITY;
+    for (int l = lane; l < L; l += 32) mx = fmaxf(mx, score[l]);
+    mx = warp_max(mx);
+    float sum = 0.f;
+    for (int l = lane; l < L; l += 32) {
+      const float e = expf(score[l] - mx);
+      score[l] = e;
+      sum += e;
+    }
+    sum = warp_sum(sum);
+    if (lane == 0) s_stat[0] = 1.f / sum;
+  }
+  __syncthreads();
+  const float inv = s_stat[0];
+  for (int e = tid; e < E; e += blockDim.x) {
+    float acc = 0.f;
+    for (int l = 0; l < L; ++l) acc = fmaf(score[l], xb[(int64_t)l * E + e], acc);
+    out[(int64_t)b * E + e] = acc * inv;
+  }
+}
+
+static int launch_attn_pool(cudaStream_t st, const float* x, const float* const* p, float* out, int B, int L, int E) {
+  const int H2 = E / 2 > 0 ? E / 2 : 1;
+  const size_t smem = sizeof(float) * ((size_t)E * H2 + 8 * (size_t)E + (size_t)L);
+  if (smem > 200 * 1024) XF_FAIL(XATTN_ERR_SHAPE, "attention pooling needs %zu B of shared memory (> 200 KiB)", smem);
+  static size_t configured = 0;
+  if (smem > 48 * 1024 && smem > configured) {
+    XF_CUDA(cudaFuncSetAttribute(attn_pool_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    configured = smem;
+  }
+  attn_pool_kernel<<<B, 256, smem, st>>>(x, p[0], p[1], p[2], p[3], p[4], p[5], out, L, E);
+  count_launch();
+  XF_LAUNCH_CHECK();
+  return XATTN_OK;
+}
+
 // ---------------------------------------------------------------------------------------------------------
 // launch helpers shared with bwd_f32.cu
 // ---------------------------------------------------------------------------------------------------------
@@ -498,11 +584,20 @@ static int forward_f32_impl(const xattn_config& c, const float* params, const TI
   {
     HeadArgs ha;
     ha.v1 = ws + w.v1; ha.a1 = ws + w.a1;
+    int hT = T, hTa = Ta;
+    if (c.pool_mode == XATTN_POOL_ATTN) {   // learned pooling first; the head kernel then sees one (already pooled) token per clip
+      const float* pv[6] = {P(XP_VPOOL_LN_W), P(XP_VPOOL_LN_B), P(XP_VPOOL_W1), P(XP_VPOOL_B1), P(XP_VPOOL_W2), P(XP_VPOOL_B2)};
+      const float* pa[6] = {P(XP_APOOL_LN_W), P(XP_APOOL_LN_B), P(XP_APOOL_W1), P(XP_APOOL_B1), P(XP_APOOL_W2), P(XP_APOOL_B2)};
+      XF_TRY(launch_attn_pool(st, ws + w.v1, pv, ws + w.poolv, B, T, E));
+      XF_TRY(launch_attn_pool(st, ws + w.a1, pa, ws + w.poola, B, Ta, E));
+      ha.v1 = ws + w.poolv; ha.a1 = ws + w.poola;
+      hT = hTa = 1;
+    }
     ha.w0 = P(XP_HEAD0_W); ha.b0 = P(XP_HEAD0_B); ha.w1 = P(XP_HEAD1_W); ha.b1 = P(XP_HEAD1_B);
     ha.wc = P(XP_CLS_W); ha.bc = P(XP_CLS_B);
     ha.pooled = ws + w.pooled; ha.hhid = ws + w.hhid; ha.gate = ws + w.gate; ha.fusedg = ws + w.fusedg;
     ha.logits = logits;
-    ha.T = T; ha.Ta = Ta; ha.E = E; ha.C = c.C; ha.gated = c.head_kind == XATTN_HEAD_GATED;
+    ha.T = hT; ha.Ta = hTa; ha.E = E; ha.C = c.C; ha.gated = c.head_kind == XATTN_HEAD_GATED;
     ha.HW = ha.gated ? E : c.common_dim;
     ha.p_drop = p_head; ha.seed = c.seed; ha.offset = c.offset;
     const size_t smem = sizeof(float) * (3 * E + ha.HW);

@@ -56,16 +56,36 @@ class StochasticDepth(nn.Module):
         raise RuntimeError("StochasticDepth is fused into the CUDA residual+LayerNorm kernel")
 
 
-class TemporalPooler(nn.Module):
-    """Mean pooling only (``temporal.py:91-92, 108-109``); carries no parameters.  ``attn`` / ``transformer`` modes are
-    SURVEY 8(f) rank 3 and raise."""
+class TemporalAttentionPooling(nn.Module):
+    """Parameter container of the learned pooling (``temporal.py:9-26``): LayerNorm -> Linear(dim, dim/2) -> GELU -> Dropout ->
+    Linear(dim/2, 1); the arithmetic runs in ``attn_pool_kernel``."""
 
-    def __init__(self, dim: int, mode: str = "mean", **_unused) -> None:
+    def __init__(self, dim: int, dropout: float = 0.1) -> None:
         super().__init__()
-        if mode != "mean":
-            raise ValueError(f"Unsupported temporal pooling mode for the B200 xattn path: {mode} (only 'mean')")
+        hidden_dim = max(1, dim // 2)
+        self.score = nn.Sequential(nn.LayerNorm(dim), nn.Linear(dim, hidden_dim), nn.GELU(), nn.Dropout(dropout),
+                                   nn.Linear(hidden_dim, 1))
+
+    def forward(self, x: torch.Tensor) -> torch.Tensor:  # pragma: no cover - not on the kernel path
+        raise RuntimeError("TemporalAttentionPooling runs inside the CUDA forward (attn_pool_kernel)")
+
+
+class TemporalPooler(nn.Module):
+    """``mean`` (``temporal.py:91-92, 108-109``; no parameters) and ``attn`` (``temporal.py:93-94``: the learned pooling, fp32
+    kernel family, forward only).  ``transformer`` (a full encoder layer in front of the pooling, ``temporal.py:46-75``) is the
+    rest of SURVEY 8(f) rank 3 and raises."""
+
+    def __init__(self, dim: int, mode: str = "mean", dropout: float = 0.1, **_unused) -> None:
+        super().__init__()
+        if mode == "mean":
+            self.pool = None
+        elif mode == "attn":
+            self.pool = TemporalAttentionPooling(dim=dim, dropout=dropout)
+        elif mode == "transformer":
+            raise ValueError("Unsupported temporal pooling mode for the B200 xattn path: transformer (built: 'mean', 'attn')")
+        else:
+            raise ValueError(f"Unsupported temporal pooling mode: {mode}")
         self.mode = mode
-        self.pool = None
 
 
 class EmotionPriorBiasAdapter(nn.Module):
@@ -145,7 +165,7 @@ class XAttnKernelsMixin:
     def _build_xattn(self, *, v_dim: int, audio_sequence_dim: int, num_classes: int, common_dim: int, xattn_head: str,
                      d_model: int, num_heads: int, audio_n_mels: int, xattn_attn_dropout: float,
                      xattn_stochastic_depth: float, temporal_pooling: str, use_emotion_prior: bool, prior_dim: int,
-                     prior_hidden: int, prior_dropout: float, precision: str = "auto") -> None:
+                     prior_hidden: int, prior_dropout: float, precision: str = "auto", temporal_dropout: float = 0.1) -> None:
         if xattn_head not in ("concat", "gated"):
             raise ValueError(f"Unknown xattn head: {xattn_head}")
         if precision not in ("auto", "fp32", "bf16", "tf32"):
@@ -173,8 +193,9 @@ class XAttnKernelsMixin:
             self.emotion_prior_bias = EmotionPriorBiasAdapter(d_model, prior_dim, prior_hidden, prior_dropout)
         else:
             self.emotion_prior_bias = None
-        self.v_temporal_pool = TemporalPooler(dim=d_model, mode=temporal_pooling)
-        self.a_temporal_pool = TemporalPooler(dim=d_model, mode=temporal_pooling)
+        self.v_temporal_pool = TemporalPooler(dim=d_model, mode=temporal_pooling, dropout=temporal_dropout)
+        self.a_temporal_pool = TemporalPooler(dim=d_model, mode=temporal_pooling, dropout=temporal_dropout)
+        self._temporal_pooling = temporal_pooling
         self.xattn_head = xattn_head
         if xattn_head == "concat":
             self.xattn_mlp = nn.Sequential(
@@ -236,6 +257,7 @@ class XAttnKernelsMixin:
         cfg.use_prior = 1 if self.emotion_prior_bias is not None else 0
         cfg.io_dtype, cfg.precision = io_dtype, precision
         cfg.training, cfg.save_for_backward = int(training), int(save)
+        cfg.pool_mode = _lib.POOL_ATTN if getattr(self, "_temporal_pooling", "mean") == "attn" else _lib.POOL_MEAN
         cfg.p_attn, cfg.p_path = self.xattn_attn_dropout, self.xattn_stochastic_depth
         cfg.p_head, cfg.p_prior = self.xattn_head_dropout, self.xattn_prior_dropout
         cfg.seed = torch.initial_seed() & 0xFFFFFFFFFFFFFFFF
@@ -325,6 +347,8 @@ class XAttnKernelsMixin:
     def _bf16_supported(self, T: int, Ta: int) -> bool:
         """Shapes the bf16 tensor-core kernels are specialised for (csrc/bf16_pack.cu: bf16_supported)."""
         hw = self.d_model if self.xattn_head == "gated" else self.common_dim
+        if getattr(self, "_temporal_pooling", "mean") != "mean":   # the learned pooling lives in the fp32 kernel family
+            return False
         return (self.d_model == 128 and self.num_heads == 4 and T <= 16 and Ta <= 160 and self.v_dim % 64 == 0
                 and self.audio_sequence_dim % 64 == 0 and hw <= 256 and hw % 64 == 0 and self.num_classes <= 16
                 and self._prior_hidden <= 128 and self._prior_dim <= 32)
@@ -353,6 +377,9 @@ class XAttnKernelsMixin:
         B, T, _ = video_emb.shape
         Ta = audio_emb.shape[1]
         io = _io_dtype(video_emb)
+        if (save or training) and getattr(self, "_temporal_pooling", "mean") != "mean":
+            raise ValueError("temporal_pooling='attn' is forward-only on the B200 path (no backward kernels yet): call it "
+                             "in eval mode under torch.no_grad()")
         precision = self._pick_precision(io, save or training, T, Ta)
         if precision == _lib.DTYPE_BF16 and io != _lib.DTYPE_BF16:   # precision="bf16" forced on fp32 embeddings
             video_emb, audio_emb, io = video_emb.bfloat16(), audio_emb.bfloat16(), _lib.DTYPE_BF16
@@ -500,7 +527,7 @@ class XAttnFusionHead(XAttnKernelsMixin, nn.Module):
 
     def __init__(self, num_classes: int = 8, video_dim: int = 512, audio_dim: int = 768, common_dim: int = 256,
                  xattn_head: str = "concat", d_model: int = 128, num_heads: int = 4, audio_n_mels: int = 64,
-                 xattn_attn_dropout: float = 0.1, xattn_stochastic_depth: float = 0.1, temporal_pooling: str = "mean",
+                 xattn_attn_dropout: float = 0.1, xattn_stochastic_depth: float = 0.1, temporal_pooling: str = "mean", temporal_dropout: float = 0.1,
                  xattn_use_emotion_prior: bool = False, xattn_emotion_prior_dim: int = 8,
                  xattn_emotion_prior_hidden_dim: int = 64, xattn_emotion_prior_dropout: float = 0.1,
                  precision: str = "auto") -> None:
@@ -511,7 +538,7 @@ class XAttnFusionHead(XAttnKernelsMixin, nn.Module):
                           xattn_attn_dropout=xattn_attn_dropout, xattn_stochastic_depth=xattn_stochastic_depth,
                           temporal_pooling=temporal_pooling, use_emotion_prior=xattn_use_emotion_prior,
                           prior_dim=xattn_emotion_prior_dim, prior_hidden=xattn_emotion_prior_hidden_dim,
-                          prior_dropout=xattn_emotion_prior_dropout, precision=precision)
+                          prior_dropout=xattn_emotion_prior_dropout, precision=precision, temporal_dropout=temporal_dropout)
 
     def forward(self, video_emb: torch.Tensor, audio_emb: torch.Tensor) -> torch.Tensor:
         return self.xattn_forward_embeddings(video_emb, audio_emb)
@@ -738,7 +765,7 @@ class FusionModel(XAttnKernelsMixin, FlatHeadKernelsMixin, nn.Module):
                               xattn_stochastic_depth=xattn_stochastic_depth, temporal_pooling=temporal_pooling,
                               use_emotion_prior=xattn_use_emotion_prior, prior_dim=xattn_emotion_prior_dim,
                               prior_hidden=xattn_emotion_prior_hidden_dim, prior_dropout=xattn_emotion_prior_dropout,
-                              precision=precision)
+                              precision=precision, temporal_dropout=temporal_dropout)
 
     def pop_alignment_loss(self):
         """``fusion.py:346-349``.  The reference computes the loss inside every concat/gated forward; here the B x B term is

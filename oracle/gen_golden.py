@@ -54,8 +54,9 @@ class StubAudio(nn.Module):
 
 
 def build_ref(FusionModel, *, dv, da, d_model, heads, head, prior, common=256, prior_dim=8, prior_hidden=64, classes=8,
-              mode="xattn", align="none"):
+              mode="xattn", align="none", pooling="mean"):
     return FusionModel(StubAudio(da), StubVideo(dv), classes, mode=mode, common_dim=common, xattn_head=head, d_model=d_model,
+                       temporal_pooling=pooling,
                        num_heads=heads, audio_n_mels=da, xattn_use_emotion_prior=prior, xattn_emotion_prior_dim=prior_dim,
                        xattn_emotion_prior_hidden_dim=prior_hidden, fusion_align_mode=align, fusion_align_dim=256)
 
@@ -92,6 +93,35 @@ def run_case(model, xv, xa, labels, lr=1e-3, wd=1e-4):
     return logits, loss.detach(), grads, after
 
 
+def gen_attnpool(FusionModel) -> None:
+    """temporal_pooling="attn" (temporal.py:9-26), eval forward: a tiny case stored in full and the
+    BASELINE config-1 dimensions with seed-0 weights (digest of the weights, full logits)."""
+    blob = {}
+    torch.manual_seed(12)
+    m = build_ref(FusionModel, dv=16, da=8, d_model=8, heads=2, head="concat", prior=True, common=16, prior_dim=4, prior_hidden=8,
+                  pooling="attn").eval()
+    g = torch.Generator().manual_seed(13)
+    xv = torch.randn(3, 4, 16, generator=g)
+    xa = torch.randn(3, 12, 8, generator=g)
+    with torch.no_grad():
+        logits = m(xv[..., None, None], xa)
+    blob.update({"tiny:xv": xv.numpy(), "tiny:xa": xa.numpy(), "tiny:logits": logits.numpy()})
+    blob.update({"tiny:w:" + k: v.numpy() for k, v in fusion_state(m).items()})
+    g = torch.Generator().manual_seed(1)
+    xv = torch.randn(8, 16, 512, generator=g)
+    xa = torch.randn(8, 149, 768, generator=g)
+    for head in ("concat", "gated"):
+        torch.manual_seed(0)
+        m = build_ref(FusionModel, dv=512, da=768, d_model=128, heads=4, head=head, prior=True, pooling="attn").eval()
+        with torch.no_grad():
+            logits = m(xv[..., None, None], xa)
+        sd = fusion_state(m)
+        blob[f"{head}:logits"] = logits.numpy()
+        blob[f"{head}:keys"] = np.array(sorted(sd))
+        blob[f"{head}:pool_digest"] = digest(torch.cat([v.flatten() for k, v in sorted(sd.items()) if "temporal_pool" in k]))
+    np.savez_compressed(OUT / "xattn_attnpool.npz", **blob)
+
+
 def main() -> None:
     sys.path.insert(0, REF)
     sys.dont_write_bytecode = True
@@ -99,6 +129,9 @@ def main() -> None:
 
     OUT.mkdir(parents=True, exist_ok=True)
     torch.set_num_threads(1)
+    gen_attnpool(FusionModel)
+    if "--only-attnpool" in sys.argv:
+        return
 
     # ---- tiny case: everything stored in full (d_model=8, heads=2 as the reference's own shape tests) -------------
     for head in ("concat", "gated"):

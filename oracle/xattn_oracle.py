@@ -114,6 +114,18 @@ def multihead_attention(sd: Dict[str, Array], prefix: str, q_in: Array, kv_in: A
     return out
 
 
+def temporal_attention_pool(sd: Dict[str, Array], prefix: str, x: Array) -> Array:
+    """TemporalAttentionPooling, reference temporal.py:9-26 (eval mode): ``score`` = LayerNorm -> Linear -> GELU (exact, erf) ->
+    Dropout -> Linear; attn = softmax over time; out = sum_t attn_t * x_t (the un-normalised tokens).  x [B,L,D] -> [B,D]."""
+    y = layer_norm(x, sd[prefix + "score.0.weight"], sd[prefix + "score.0.bias"])           # temporal.py:16
+    h = linear(y, sd[prefix + "score.1.weight"], sd[prefix + "score.1.bias"])               # :17
+    erf = np.vectorize(math.erf, otypes=[np.float64])
+    g = 0.5 * h * (1.0 + erf(h / math.sqrt(2.0)))                                           # :18 nn.GELU()
+    logits = linear(g, sd[prefix + "score.4.weight"], sd[prefix + "score.4.bias"])[..., 0]  # :20, :24
+    attn = softmax(logits, axis=1)[..., None]                                               # :25
+    return (x * attn).sum(axis=1)                                                           # :26
+
+
 def xattn_forward(sd: Dict[str, Array], video_emb: Array, audio_emb: Array, *, num_heads: int = 4,
                   head: str = "concat", use_prior: Optional[bool] = None, taps: Optional[dict] = None) -> Array:
     """Forward of the xattn fusion head, reference fusion.py:372-411, eval mode.
@@ -139,8 +151,12 @@ def xattn_forward(sd: Dict[str, Array], video_emb: Array, audio_emb: Array, *, n
     v_new = layer_norm(v + v2, sd["v_norm.weight"], sd["v_norm.bias"])           # :395
     a2 = multihead_attention(sd, "a2v_attn.", a, v_new, num_heads, a2v_bias)     # :398 (uses UPDATED v)
     a_new = layer_norm(a + a2, sd["a_norm.weight"], sd["a_norm.bias"])           # :399
-    v_emb = v_new.mean(axis=1)                                                  # temporal.py:108-109
-    a_emb = a_new.mean(axis=1)
+    if "v_temporal_pool.pool.score.0.weight" in sd:                             # temporal_pooling="attn", temporal.py:93-94
+        v_emb = temporal_attention_pool(sd, "v_temporal_pool.pool.", v_new)
+        a_emb = temporal_attention_pool(sd, "a_temporal_pool.pool.", a_new)
+    else:
+        v_emb = v_new.mean(axis=1)                                              # temporal.py:108-109
+        a_emb = a_new.mean(axis=1)
     fused = np.concatenate([v_emb, a_emb], axis=-1)
     if head == "concat":                                                        # :405-407
         hid = np.maximum(linear(fused, sd["xattn_mlp.0.weight"], sd["xattn_mlp.0.bias"]), 0.0)

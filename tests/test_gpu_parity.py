@@ -387,3 +387,36 @@ def test_flat_alignment_loss_matches_reference(cuda_device, mode):
     popped = fm.pop_alignment_loss()
     assert popped is not None and abs(float(popped) - reff) < 1e-4
     assert fm.pop_alignment_loss() is None
+
+
+def test_attention_pooling_matches_reference(cuda_device):
+    """temporal_pooling="attn" (TemporalAttentionPooling, temporal.py:9-26) in the fp32 kernel family: the tiny
+    golden case and the BASELINE config-1 dimensions against the reference's logits (1e-4); bf16 embeddings route to the same
+    kernels (the bf16 tensor-core path pools by mean only); training raises (forward only)."""
+    from multimodalemotionrecognition_b200 import XAttnFusionHead
+
+    blob = load_npz("xattn_attnpool.npz")
+    sd = {k[len("tiny:w:"):]: torch.from_numpy(v) for k, v in blob.items() if k.startswith("tiny:w:")}
+    m = XAttnFusionHead(num_classes=8, video_dim=16, audio_dim=8, common_dim=16, d_model=8, num_heads=2, audio_n_mels=8,
+                        xattn_use_emotion_prior=True, xattn_emotion_prior_dim=4, xattn_emotion_prior_hidden_dim=8,
+                        temporal_pooling="attn")
+    m.load_state_dict(sd, strict=True)
+    m = m.to(cuda_device).eval()
+    with torch.no_grad():
+        out = m(torch.from_numpy(blob["tiny:xv"]).to(cuda_device), torch.from_numpy(blob["tiny:xa"]).to(cuda_device))
+    assert np.abs(out.cpu().numpy() - blob["tiny:logits"]).max() <= 1e-5
+    g = torch.Generator().manual_seed(1)
+    xv = torch.randn(8, 16, 512, generator=g)
+    xa = torch.randn(8, 149, 768, generator=g)
+    for head in ("concat", "gated"):
+        mm = make_head(head, True, seed=0, temporal_pooling="attn").to(cuda_device).eval()
+        with torch.no_grad():
+            out = mm(xv.to(cuda_device), xa.to(cuda_device))
+            outb = mm(xv.bfloat16().to(cuda_device), xa.bfloat16().to(cuda_device))
+        assert np.abs(out.cpu().numpy() - blob[f"{head}:logits"]).max() <= FP32_TOL
+        sdn = {k: v.cpu().numpy() for k, v in mm.state_dict().items()}
+        refb = xattn_oracle.xattn_forward(sdn, xv.bfloat16().float().numpy(), xa.bfloat16().float().numpy(), num_heads=4, head=head)
+        assert np.abs(outb.cpu().numpy() - refb).max() <= FP32_TOL
+    mm.train()
+    with pytest.raises(ValueError):
+        mm(xv.to(cuda_device), xa.to(cuda_device))
