@@ -26,7 +26,7 @@
 extern "C" {
 #endif
 
-#define XATTN_ABI_VERSION 10
+#define XATTN_ABI_VERSION 11
 
 #if defined(__GNUC__)
 #define XATTN_API __attribute__((visibility("default")))
@@ -230,6 +230,13 @@ XATTN_API int flat_head_workspace_bytes(const flat_head_config* cfg, int64_t* by
  * fusion.py:413-435 (+ :137-139).  Eval mode (ModalityDropout / Dropout identity). */
 XATTN_API int flat_head_forward(const flat_head_config* cfg, const float* params, const void* video_emb, const void* audio_emb,
                       float* logits, void* workspace, int64_t workspace_bytes, void* stream);
+
+/* Mel front end (fusion.py:379-384: audio_time_conv = Conv1d(n_mels -> a_dim, kernel 3, padding 1) over time, then permute to
+ * [B, Ta, a_dim]) for audio encoders without encode_sequence().  mel [B, n_mels, Ta] -> unfolded [B, Ta, 3*n_mels] (same
+ * dtype), unfolded[b,t,c*3+k] = mel[b,c,t+k-1] (0 outside [0,Ta)).  The convolution then IS the audio_seq_proj Linear of the
+ * head: call xattn_forward / xattn_backward with cfg.Da = 3*n_mels and the XP_SEQ_W / XP_SEQ_B slots holding
+ * audio_time_conv.weight (viewed [a_dim, n_mels*3], its own memory order) / audio_time_conv.bias. */
+XATTN_API int xattn_mel_unfold(const void* mel, void* unfolded, int32_t io_dtype, int32_t B, int32_t n_mels, int32_t Ta, void* stream);
 
 /* The ClipStyleAlignment loss of the flat heads (fusion.py:141-149; what FusionModel.pop_alignment_loss() returns, train.py:221-222):
  * 0.5·(CE(s·â v̂ᵀ, arange(B)) + CE(s·v̂ âᵀ, arange(B))) with â, v̂ the L2-normalised alignment projections of the temporally

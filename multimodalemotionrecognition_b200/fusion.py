@@ -139,7 +139,7 @@ class GraphedForward:
         self.B, self.key = B, None
         with torch.cuda.device(device), torch.no_grad():
             self.video = torch.zeros((B, T, head.v_dim), dtype=dtype, device=device)
-            self.audio = torch.zeros((B, Ta, head.audio_sequence_dim), dtype=dtype, device=device)
+            self.audio = torch.zeros((B, Ta, head._kernel_audio_dim), dtype=dtype, device=device)
             self.logits = torch.empty((B, head.num_classes), dtype=torch.float32, device=device)
             side = torch.cuda.Stream(device)
             side.wait_stream(torch.cuda.current_stream(device))
@@ -165,13 +165,22 @@ class XAttnKernelsMixin:
     def _build_xattn(self, *, v_dim: int, audio_sequence_dim: int, num_classes: int, common_dim: int, xattn_head: str,
                      d_model: int, num_heads: int, audio_n_mels: int, xattn_attn_dropout: float,
                      xattn_stochastic_depth: float, temporal_pooling: str, use_emotion_prior: bool, prior_dim: int,
-                     prior_hidden: int, prior_dropout: float, precision: str = "auto", temporal_dropout: float = 0.1) -> None:
+                     prior_hidden: int, prior_dropout: float, precision: str = "auto", temporal_dropout: float = 0.1,
+                     audio_frontend: str = "seq") -> None:
         if xattn_head not in ("concat", "gated"):
             raise ValueError(f"Unknown xattn head: {xattn_head}")
         if precision not in ("auto", "fp32", "bf16", "tf32"):
             raise ValueError(f"precision must be auto|fp32|bf16|tf32, got {precision}")
+        if audio_frontend not in ("seq", "mel"):
+            raise ValueError(f"audio_frontend must be seq|mel, got {audio_frontend}")
         self.v_dim = v_dim
         self.audio_sequence_dim = audio_sequence_dim
+        # "seq": audio_seq_proj over encoder states (fusion.py:374-378).  "mel": audio_time_conv over a mel spectrogram
+        # (:379-384) — run as the same Linear over time-unfolded rows (csrc/mel_frontend.cu), so the kernels see
+        # Da = 3*n_mels and the audio_seq_proj slots of the flat buffer hold audio_time_conv.{weight,bias}.
+        self.audio_frontend = audio_frontend
+        self.audio_n_mels = audio_n_mels
+        self._kernel_audio_dim = 3 * audio_n_mels if audio_frontend == "mel" else audio_sequence_dim
         self.a_dim = d_model
         self.d_model = d_model
         self.num_heads = num_heads
@@ -180,7 +189,7 @@ class XAttnKernelsMixin:
         self.precision = precision
         self.v_in_proj = nn.Linear(self.v_dim, d_model)
         self.a_in_proj = nn.Linear(self.a_dim, d_model)
-        # kept for state_dict parity; unused on the WavLM path (fusion.py:273, :379-384)
+        # both front ends exist in every checkpoint (fusion.py:273-274); the one not selected is never touched
         self.audio_time_conv = nn.Conv1d(in_channels=audio_n_mels, out_channels=self.a_dim, kernel_size=3, padding=1)
         self.audio_seq_proj = nn.Linear(self.audio_sequence_dim, self.a_dim)
         self.v2a_attn = nn.MultiheadAttention(embed_dim=d_model, num_heads=num_heads, dropout=xattn_attn_dropout, batch_first=True)
@@ -224,6 +233,12 @@ class XAttnKernelsMixin:
         self._rng_offset = 0
 
     # ---- config / parameter plumbing ------------------------------------------------------------------------------
+    def _xattn_param_names(self) -> list[str]:
+        names = _lib.xattn_param_names(self.xattn_head)
+        if getattr(self, "audio_frontend", "seq") == "mel":
+            names = [n.replace("audio_seq_proj.", "audio_time_conv.") for n in names]
+        return names
+
     def _xattn_named_params(self) -> list[Optional[nn.Parameter]]:
         """The Parameters in flat-buffer order.  Resolved once and re-validated per call by identity against the owning
         module's ``_parameters`` dict (cheap), so replacing a Parameter object is still noticed."""
@@ -235,7 +250,7 @@ class XAttnKernelsMixin:
                     break
         if cache is None:
             cache = []
-            for name in _lib.xattn_param_names(self.xattn_head):
+            for name in self._xattn_param_names():
                 owner, _, key = name.rpartition(".")
                 try:
                     mod = self.get_submodule(owner) if owner else self
@@ -249,7 +264,7 @@ class XAttnKernelsMixin:
 
     def _make_cfg(self, B: int, T: int, Ta: int, io_dtype: int, precision: int, training: bool, save: bool) -> _lib.XAttnConfig:
         cfg = _lib.XAttnConfig()
-        cfg.B, cfg.T, cfg.Ta, cfg.Dv, cfg.Da = B, T, Ta, self.v_dim, self.audio_sequence_dim
+        cfg.B, cfg.T, cfg.Ta, cfg.Dv, cfg.Da = B, T, Ta, self.v_dim, self._kernel_audio_dim
         cfg.E, cfg.H = self.d_model, self.num_heads
         cfg.prior_dim, cfg.prior_hidden = self._prior_dim, self._prior_hidden
         cfg.common_dim, cfg.C = self.common_dim, self.num_classes
@@ -287,7 +302,7 @@ class XAttnKernelsMixin:
         if not ok:
             flat = torch.zeros(total, dtype=torch.float32, device=dev)
             with torch.no_grad():
-                for p, off, n, name in zip(params, offs, sizes, _lib.xattn_param_names(self.xattn_head)):
+                for p, off, n, name in zip(params, offs, sizes, self._xattn_param_names()):
                     if n == 0:
                         continue
                     if p is None or p.numel() != n:
@@ -332,13 +347,13 @@ class XAttnKernelsMixin:
     def _check_inputs(self, video_emb: torch.Tensor, audio_emb: torch.Tensor) -> None:
         if video_emb.ndim != 3 or audio_emb.ndim != 3:
             raise ValueError(
-                f"xattn head expects video_emb [B,T,{self.v_dim}] and audio_emb [B,Ta,{self.audio_sequence_dim}], got "
+                f"xattn head expects video_emb [B,T,{self.v_dim}] and audio_emb [B,Ta,{self._kernel_audio_dim}], got "
                 f"shapes {tuple(video_emb.shape)} and {tuple(audio_emb.shape)}")
         if video_emb.shape[0] != audio_emb.shape[0]:
             raise ValueError("video_emb and audio_emb disagree on the batch size")
-        if video_emb.shape[2] != self.v_dim or audio_emb.shape[2] != self.audio_sequence_dim:
+        if video_emb.shape[2] != self.v_dim or audio_emb.shape[2] != self._kernel_audio_dim:
             raise ValueError(
-                f"embedding dims ({video_emb.shape[2]}, {audio_emb.shape[2]}) != ({self.v_dim}, {self.audio_sequence_dim})")
+                f"embedding dims ({video_emb.shape[2]}, {audio_emb.shape[2]}) != ({self.v_dim}, {self._kernel_audio_dim})")
         if not (video_emb.is_cuda and audio_emb.is_cuda):
             raise RuntimeError("the B200 xattn fusion head has no CPU path: inputs must be CUDA tensors on an sm_100 device")
         if video_emb.dtype != audio_emb.dtype:
@@ -350,7 +365,7 @@ class XAttnKernelsMixin:
         if getattr(self, "_temporal_pooling", "mean") != "mean":   # the learned pooling lives in the fp32 kernel family
             return False
         return (self.d_model == 128 and self.num_heads == 4 and T <= 16 and Ta <= 160 and self.v_dim % 64 == 0
-                and self.audio_sequence_dim % 64 == 0 and hw <= 256 and hw % 64 == 0 and self.num_classes <= 16
+                and self._kernel_audio_dim % 64 == 0 and hw <= 256 and hw % 64 == 0 and self.num_classes <= 16
                 and self._prior_hidden <= 128 and self._prior_dim <= 32)
 
     def _pick_precision(self, io_dtype: int, need_grad: bool, T: int = 16, Ta: int = 149) -> int:
@@ -505,6 +520,31 @@ class XAttnKernelsMixin:
             cur.synchronize()
         return host
 
+    def mel_unfold(self, mel: torch.Tensor) -> torch.Tensor:
+        """mel [B, 1, n_mels, Ta] or [B, n_mels, Ta] -> time-unfolded rows [B, Ta, 3*n_mels] (csrc/mel_frontend.cu), the
+        operand that turns ``audio_time_conv`` (fusion.py:381-384) into the head's first audio Linear."""
+        if mel.ndim == 4 and mel.shape[1] == 1:
+            mel = mel[:, 0]                                                                         # fusion.py:382 (squeeze(1))
+        if mel.ndim != 3 or mel.shape[1] != self.audio_n_mels:
+            raise ValueError(f"expected mel [B,1,{self.audio_n_mels},Ta] or [B,{self.audio_n_mels},Ta], got {tuple(mel.shape)}")
+        if not mel.is_cuda:
+            raise RuntimeError("the B200 xattn fusion head has no CPU path: inputs must be CUDA tensors on an sm_100 device")
+        if mel.dtype not in (torch.float32, torch.bfloat16):
+            mel = mel.float()
+        mel = mel.contiguous()
+        B, n_mels, Ta = mel.shape
+        out = torch.empty((B, Ta, 3 * n_mels), dtype=mel.dtype, device=mel.device)
+        with torch.cuda.device(mel.device):
+            _lib.check(_lib.load().xattn_mel_unfold(_ptr(mel), _ptr(out), _lib.DTYPE_BF16 if mel.dtype == torch.bfloat16 else _lib.DTYPE_F32,
+                                                    B, n_mels, Ta, _stream_ptr(mel.device)))
+        return out
+
+    def xattn_forward_mel(self, video_emb: torch.Tensor, mel: torch.Tensor) -> torch.Tensor:
+        """logits from video embeddings and a mel spectrogram (``audio_frontend="mel"``, fusion.py:379-411)."""
+        if self.audio_frontend != "mel":
+            raise ValueError('xattn_forward_mel needs a head built with audio_frontend="mel"')
+        return self.xattn_forward_embeddings(video_emb, self.mel_unfold(mel))
+
     def xattn_forward_embeddings(self, video_emb: torch.Tensor, audio_emb: torch.Tensor) -> torch.Tensor:
         """logits from backbone embeddings; differentiable w.r.t. the fusion parameters (not the embeddings)."""
         params = self._xattn_named_params()
@@ -530,7 +570,7 @@ class XAttnFusionHead(XAttnKernelsMixin, nn.Module):
                  xattn_attn_dropout: float = 0.1, xattn_stochastic_depth: float = 0.1, temporal_pooling: str = "mean", temporal_dropout: float = 0.1,
                  xattn_use_emotion_prior: bool = False, xattn_emotion_prior_dim: int = 8,
                  xattn_emotion_prior_hidden_dim: int = 64, xattn_emotion_prior_dropout: float = 0.1,
-                 precision: str = "auto") -> None:
+                 precision: str = "auto", audio_frontend: str = "seq") -> None:
         super().__init__()
         self.mode = "xattn"
         self._build_xattn(v_dim=video_dim, audio_sequence_dim=audio_dim, num_classes=num_classes, common_dim=common_dim,
@@ -538,9 +578,14 @@ class XAttnFusionHead(XAttnKernelsMixin, nn.Module):
                           xattn_attn_dropout=xattn_attn_dropout, xattn_stochastic_depth=xattn_stochastic_depth,
                           temporal_pooling=temporal_pooling, use_emotion_prior=xattn_use_emotion_prior,
                           prior_dim=xattn_emotion_prior_dim, prior_hidden=xattn_emotion_prior_hidden_dim,
-                          prior_dropout=xattn_emotion_prior_dropout, precision=precision, temporal_dropout=temporal_dropout)
+                          prior_dropout=xattn_emotion_prior_dropout, precision=precision, temporal_dropout=temporal_dropout,
+                          audio_frontend=audio_frontend)
 
     def forward(self, video_emb: torch.Tensor, audio_emb: torch.Tensor) -> torch.Tensor:
+        """``audio_emb``: encoder states [B,Ta,audio_dim] (``audio_frontend="seq"``) or a mel spectrogram
+        [B,1,n_mels,Ta] / [B,n_mels,Ta] (``"mel"``)."""
+        if self.audio_frontend == "mel":
+            return self.xattn_forward_mel(video_emb, audio_emb)
         return self.xattn_forward_embeddings(video_emb, audio_emb)
 
     @torch.no_grad()
@@ -765,7 +810,8 @@ class FusionModel(XAttnKernelsMixin, FlatHeadKernelsMixin, nn.Module):
                               xattn_stochastic_depth=xattn_stochastic_depth, temporal_pooling=temporal_pooling,
                               use_emotion_prior=xattn_use_emotion_prior, prior_dim=xattn_emotion_prior_dim,
                               prior_hidden=xattn_emotion_prior_hidden_dim, prior_dropout=xattn_emotion_prior_dropout,
-                              precision=precision, temporal_dropout=temporal_dropout)
+                              precision=precision, temporal_dropout=temporal_dropout,
+                              audio_frontend="seq" if hasattr(audio_model, "encode_sequence") else "mel")
 
     def pop_alignment_loss(self):
         """``fusion.py:346-349``.  The reference computes the loss inside every concat/gated forward; here the B x B term is
@@ -788,9 +834,8 @@ class FusionModel(XAttnKernelsMixin, FlatHeadKernelsMixin, nn.Module):
         if self.mode in _XATTN_MODES:
             b, t, c, h, w = video.shape
             v_feat = self.video_model.backbone(video.view(b * t, c, h, w)).view(b, t, self.v_dim)   # fusion.py:368-370
-            if not hasattr(self.audio_model, "encode_sequence"):
-                raise ValueError("the B200 xattn path needs audio_model.encode_sequence (WavLM path, fusion.py:374-378); "
-                                 "the mel/audio_time_conv fallback (:379-384) is not built")
+            if self.audio_frontend == "mel":                                                         # fusion.py:379-384
+                return self.xattn_forward_mel(v_feat, audio)
             a_seq = self.audio_model.encode_sequence(audio)                                          # fusion.py:377
             return self.xattn_forward_embeddings(v_feat, a_seq)
         if self.mode in {"concat", "gated"}:

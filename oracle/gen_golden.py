@@ -122,6 +122,52 @@ def gen_attnpool(FusionModel) -> None:
     np.savez_compressed(OUT / "xattn_attnpool.npz", **blob)
 
 
+class StubAudioMel(nn.Module):
+    """An encoder without encode_sequence(): the reference takes the mel fallback (fusion.py:379-384)."""
+
+    def __init__(self, dim: int) -> None:
+        super().__init__()
+        self.embedding_dim = dim
+
+
+def gen_mel(FusionModel) -> None:
+    """Mel front end (audio_time_conv, fusion.py:379-384): eval forward, CE, backward and one Adam step.
+    A tiny case stored in full; n_mels=64 / Ta=149 / d_model=128 with seed-0 weights stored as logits + gradient digests."""
+    blob = {}
+    torch.manual_seed(21)
+    m = FusionModel(StubAudioMel(8), StubVideo(16), 8, mode="xattn", common_dim=16, xattn_head="concat", d_model=8, num_heads=2,
+                    audio_n_mels=5, xattn_use_emotion_prior=True, xattn_emotion_prior_dim=4, xattn_emotion_prior_hidden_dim=8)
+    g = torch.Generator().manual_seed(22)
+    xv = torch.randn(3, 4, 16, generator=g)
+    mel = torch.randn(3, 1, 5, 37, generator=g)
+    labels = torch.randint(0, 8, (3,), generator=g)
+    before = fusion_state(m)
+    logits, loss, grads, after = run_case(m, xv, mel, labels)
+    blob.update({"tiny:xv": xv.numpy(), "tiny:mel": mel.numpy(), "tiny:labels": labels.numpy(), "tiny:logits": logits.numpy(),
+                 "tiny:loss": loss.numpy()})
+    blob.update({"tiny:w:" + k: v.numpy() for k, v in before.items()})
+    blob.update({"tiny:g:" + k: v.numpy() for k, v in grads.items()})
+    blob.update({"tiny:after:" + k: v.numpy() for k, v in after.items()})
+    g = torch.Generator().manual_seed(1)
+    xv = torch.randn(8, 16, 512, generator=g)
+    mel = torch.randn(8, 1, 64, 149, generator=g)
+    labels = torch.randint(0, 8, (8,), generator=g)
+    for head in ("concat", "gated"):
+        torch.manual_seed(0)
+        m = FusionModel(StubAudioMel(128), StubVideo(512), 8, mode="xattn", xattn_head=head, d_model=128, num_heads=4,
+                        audio_n_mels=64, xattn_use_emotion_prior=True)
+        logits, loss, grads, after = run_case(m, xv, mel, labels)
+        blob[f"{head}:logits"] = logits.numpy()
+        blob[f"{head}:loss"] = loss.numpy()
+        blob[f"{head}:keys"] = np.array(sorted(fusion_state(m)))
+        blob[f"{head}:g:audio_time_conv.weight"] = grads["audio_time_conv.weight"].numpy()
+        blob[f"{head}:g:audio_time_conv.bias"] = grads["audio_time_conv.bias"].numpy()
+        for k, v in grads.items():
+            blob[f"{head}:gd:{k}"] = digest(v)
+        assert "audio_seq_proj.weight" not in grads
+    np.savez_compressed(OUT / "xattn_mel.npz", **blob)
+
+
 def main() -> None:
     sys.path.insert(0, REF)
     sys.dont_write_bytecode = True
@@ -129,9 +175,13 @@ def main() -> None:
 
     OUT.mkdir(parents=True, exist_ok=True)
     torch.set_num_threads(1)
+    if "--only-mel" in sys.argv:
+        gen_mel(FusionModel)
+        return
     gen_attnpool(FusionModel)
     if "--only-attnpool" in sys.argv:
         return
+    gen_mel(FusionModel)
 
     # ---- tiny case: everything stored in full (d_model=8, heads=2 as the reference's own shape tests) -------------
     for head in ("concat", "gated"):

@@ -126,8 +126,26 @@ def temporal_attention_pool(sd: Dict[str, Array], prefix: str, x: Array) -> Arra
     return (x * attn).sum(axis=1)                                                           # :26
 
 
+def audio_time_conv(sd: Dict[str, Array], mel: Array) -> Array:
+    """Mel front end, reference fusion.py:379-384: Conv1d(n_mels -> a_dim, kernel_size=3, padding=1) over time, then
+    permute to [B, Ta, a_dim].  ``mel`` [B,1,n_mels,Ta] or [B,n_mels,Ta].  Restated as the convolution sum itself
+    (cross-correlation, zero padding), NOT as the unfold + Linear the CUDA path uses."""
+    x = _f64(mel)
+    if x.ndim == 4:
+        x = x[:, 0]                                                                          # :382 squeeze(1)
+    w = _f64(sd["audio_time_conv.weight"])                                                   # [a_dim, n_mels, 3]
+    bsz, _, ta = x.shape
+    xp = np.pad(x, ((0, 0), (0, 0), (1, 1)))                                                 # padding=1
+    out = np.zeros((bsz, w.shape[0], ta))
+    for k in range(3):                                                                       # out[b,o,t] += w[o,c,k] x[b,c,t+k-1]
+        out += np.einsum("oc,bct->bot", w[:, :, k], xp[:, :, k:k + ta])
+    out += _f64(sd["audio_time_conv.bias"])[None, :, None]                                   # :383
+    return out.transpose(0, 2, 1)                                                            # :384
+
+
 def xattn_forward(sd: Dict[str, Array], video_emb: Array, audio_emb: Array, *, num_heads: int = 4,
-                  head: str = "concat", use_prior: Optional[bool] = None, taps: Optional[dict] = None) -> Array:
+                  head: str = "concat", use_prior: Optional[bool] = None, taps: Optional[dict] = None,
+                  audio_frontend: str = "seq") -> Array:
     """Forward of the xattn fusion head, reference fusion.py:372-411, eval mode.
 
     ``sd`` maps reference state_dict keys (head only) to arrays.  ``video_emb`` [B,T,Dv],
@@ -136,12 +154,15 @@ def xattn_forward(sd: Dict[str, Array], video_emb: Array, audio_emb: Array, *, n
     """
     xv = _f64(video_emb)
     xa = _f64(audio_emb)
-    if xv.ndim != 3 or xa.ndim != 3:
+    if audio_frontend == "mel":
+        a_seq = audio_time_conv(sd, xa)                                           # :379-384
+    elif xv.ndim != 3 or xa.ndim != 3:
         raise ValueError("expected video_emb [B,T,Dv] and audio_emb [B,Ta,Da]")
     if use_prior is None:
         use_prior = any(k.startswith("emotion_prior_bias.") for k in sd)
     v = linear(xv, sd["v_in_proj.weight"], sd["v_in_proj.bias"])                 # :372
-    a_seq = linear(xa, sd["audio_seq_proj.weight"], sd["audio_seq_proj.bias"])   # :378
+    if audio_frontend != "mel":
+        a_seq = linear(xa, sd["audio_seq_proj.weight"], sd["audio_seq_proj.bias"])   # :378
     a = linear(a_seq, sd["a_in_proj.weight"], sd["a_in_proj.bias"])              # :386
     v2a_bias = a2v_bias = None
     prior = None

@@ -420,3 +420,97 @@ def test_attention_pooling_matches_reference(cuda_device):
     mm.train()
     with pytest.raises(ValueError):
         mm(xv.to(cuda_device), xa.to(cuda_device))
+
+
+def test_mel_front_end_matches_reference(cuda_device):
+    """audio_time_conv (fusion.py:379-384) as unfold (csrc/mel_frontend.cu) + the head's first audio Linear:
+    the unfold is exact; tiny case logits / loss / every gradient / post-Adam parameters against the reference; n_mels=64,
+    Ta=149, d_model=128 through FusionModel.forward(video, mel) in fp32, tf32 and bf16, gradients in fp32."""
+    from multimodalemotionrecognition_b200 import FusionModel, XAttnFusionHead
+    from multimodalemotionrecognition_b200.training import Stage1Trainer
+
+    blob = load_npz("xattn_mel.npz")
+    sd = {k[len("tiny:w:"):]: torch.from_numpy(v) for k, v in blob.items() if k.startswith("tiny:w:")}
+    m = XAttnFusionHead(num_classes=8, video_dim=16, audio_dim=8, common_dim=16, d_model=8, num_heads=2, audio_n_mels=5,
+                        xattn_use_emotion_prior=True, xattn_emotion_prior_dim=4, xattn_emotion_prior_hidden_dim=8,
+                        audio_frontend="mel")
+    m.load_state_dict(sd, strict=True)
+    m = m.to(cuda_device).eval()
+    xv = torch.from_numpy(blob["tiny:xv"]).to(cuda_device)
+    mel = torch.from_numpy(blob["tiny:mel"]).to(cuda_device)
+    labels = torch.from_numpy(blob["tiny:labels"]).to(cuda_device)
+    unf = m.mel_unfold(mel)
+    pad = torch.nn.functional.pad(mel[:, 0], (1, 1))
+    want = torch.stack([pad[:, :, k:k + mel.shape[3]] for k in range(3)], dim=-1).permute(0, 2, 1, 3).reshape(3, mel.shape[3], 15)
+    assert torch.equal(unf, want)
+    assert torch.equal(m.mel_unfold(mel.bfloat16()), want.bfloat16())
+    out = m(xv, mel)
+    assert np.abs(out.detach().cpu().numpy() - blob["tiny:logits"]).max() <= 1e-5
+    loss = torch.nn.functional.cross_entropy(out, labels)
+    assert abs(float(loss) - float(blob["tiny:loss"])) < 1e-5
+    loss.backward()
+    named = dict(m.named_parameters())
+    n = 0
+    for k, v in blob.items():
+        if k.startswith("tiny:g:"):
+            g = named[k[len("tiny:g:"):]].grad
+            assert g is not None, k
+            np.testing.assert_allclose(g.cpu().numpy(), v, atol=2e-6, rtol=1e-4, err_msg=k)
+            n += 1
+    assert n >= 20 and "tiny:g:audio_time_conv.weight" in blob
+    assert named["audio_seq_proj.weight"].grad is None
+    # one Stage-1 step (CE + backward + Adam lr 1e-3 wd 1e-4) against the reference's post-step parameters
+    m2 = XAttnFusionHead(num_classes=8, video_dim=16, audio_dim=8, common_dim=16, d_model=8, num_heads=2, audio_n_mels=5,
+                         xattn_use_emotion_prior=True, xattn_emotion_prior_dim=4, xattn_emotion_prior_hidden_dim=8,
+                         audio_frontend="mel")
+    m2.load_state_dict(sd, strict=True)
+    m2 = m2.to(cuda_device)
+    tr = Stage1Trainer(m2, lr=1e-3, weight_decay=1e-4)
+    tr.step(xv, m2.mel_unfold(mel), labels, training=False)
+    sd2 = m2.state_dict()
+    for k, v in blob.items():
+        name = k[len("tiny:after:"):]
+        if k.startswith("tiny:after:") and ("tiny:g:" + name) in blob:
+            got, gr, w0 = sd2[name].cpu().numpy(), blob["tiny:g:" + name], blob["tiny:w:" + name]
+            solid = np.abs(gr) > 1e-5     # ~0 gradients (attention key bias): Adam's first step is the sign of rounding noise
+            np.testing.assert_allclose(got[solid], v[solid], atol=3e-6, rtol=0, err_msg=k)
+            assert np.all(np.abs(got - w0) <= 1e-3 * 1.001 + 1e-7), k
+    np.testing.assert_array_equal(sd2["audio_seq_proj.weight"].cpu().numpy(), blob["tiny:w:audio_seq_proj.weight"])
+
+    class StubVideo(torch.nn.Module):
+        embedding_dim = 512
+
+        def __init__(self):
+            super().__init__()
+            self.backbone = torch.nn.Identity()
+
+    class StubAudioMel(torch.nn.Module):
+        embedding_dim = 128
+
+    g = torch.Generator().manual_seed(1)
+    xv = torch.randn(8, 16, 512, generator=g).to(cuda_device)
+    mel = torch.randn(8, 1, 64, 149, generator=g).to(cuda_device)
+    labels = torch.randint(0, 8, (8,), generator=g).to(cuda_device)
+    for head in ("concat", "gated"):
+        torch.manual_seed(0)
+        fm = FusionModel(StubAudioMel(), StubVideo(), 8, mode="xattn", xattn_head=head, d_model=128, num_heads=4, audio_n_mels=64,
+                         xattn_use_emotion_prior=True).to(cuda_device).eval()
+        out = fm(xv[..., None, None], mel)
+        assert np.abs(out.detach().cpu().numpy() - blob[f"{head}:logits"]).max() <= FP32_TOL
+        loss = torch.nn.functional.cross_entropy(out, labels)
+        assert abs(float(loss) - float(blob[f"{head}:loss"])) < 1e-5
+        loss.backward()
+        for name in ("audio_time_conv.weight", "audio_time_conv.bias"):
+            np.testing.assert_allclose(dict(fm.named_parameters())[name].grad.cpu().numpy(), blob[f"{head}:g:{name}"],
+                                       atol=2e-6, rtol=1e-4, err_msg=name)
+        for k, v in blob.items():
+            if k.startswith(f"{head}:gd:"):
+                gr = dict(fm.named_parameters())[k[len(head) + 4:]].grad
+                np.testing.assert_allclose(digest(gr), v, atol=5e-5, rtol=1e-4, err_msg=k)
+        with torch.no_grad():
+            fm.precision = "tf32"
+            assert np.abs(fm(xv[..., None, None], mel).cpu().numpy() - blob[f"{head}:logits"]).max() <= BF16_TOL
+            fm.precision = "bf16"
+            outb = fm(xv.bfloat16()[..., None, None], mel.bfloat16())
+            assert np.abs(outb.cpu().numpy() - blob[f"{head}:logits"]).max() <= 2 * BF16_TOL
+            fm.precision = "auto"
