@@ -270,16 +270,9 @@ __global__ void __launch_bounds__(256) attn_bwd32_kernel(AttnBwdArgs a) {
     dSs[i] = 0.f;
   }
   for (int h = 0; h < H; ++h) {
-    for (int i = tid; i < L * dh; i += blockDim.x) {
-      const int l = i >> 5, d = i & 31;
-      Qs[l * dp + d] = q[(int64_t)l * E + h * dh + d] * a.scale;
-      dOs[l * dp + d] = dO[(int64_t)l * E + h * dh + d];
-    }
-    for (int i = tid; i < S * dh; i += blockDim.x) {
-      const int s = i >> 5, d = i & 31;
-      Ks[s * dp + d] = kv[(int64_t)s * 2 * E + h * dh + d];
-      Vs[s * dp + d] = kv[(int64_t)s * 2 * E + E + h * dh + d];
-    }
+    stage_rows32(Qs, q + h * dh, L, E, a.scale, tid, blockDim.x);
+    stage_rows32(dOs, dO + h * dh, L, E, 1.f, tid, blockDim.x);
+    stage_rows32x2(Ks, Vs, kv + h * dh, E, S, 2 * E, tid, blockDim.x);
     __syncthreads();
     const int64_t hbase = ((int64_t)b * H + h) * L * S;
     for (int t = warp; t < ntile; t += nw) {   // dPd = dO · V^T

@@ -155,6 +155,18 @@ __device__ __forceinline__ float drop_factor(float p, uint64_t seed, uint64_t of
   if (p >= 1.f) return 0.f;
   return rng_uniform(seed, offset, stream, idx) < p ? 0.f : 1.f / (1.f - p);
 }
+// Factors of the four elements idx0 .. idx0+3 (idx0 % 4 == 0) from ONE Philox evaluation — the same values drop_factor gives
+// element by element (rng_uniform maps idx to counter idx >> 2, word idx & 3).
+__device__ __forceinline__ void drop_factor4(float p, uint64_t seed, uint64_t offset, uint32_t stream, uint64_t idx0, float (&f)[4]) {
+  if (p <= 0.f) { f[0] = f[1] = f[2] = f[3] = 1.f; return; }
+  if (p >= 1.f) { f[0] = f[1] = f[2] = f[3] = 0.f; return; }
+  const uint4 r = philox4x32(seed, (offset << 8) | stream, idx0 >> 2);
+  const float keep = 1.f / (1.f - p), sc = 1.0f / 16777216.0f;
+  f[0] = (float)(r.x >> 8) * sc < p ? 0.f : keep;
+  f[1] = (float)(r.y >> 8) * sc < p ? 0.f : keep;
+  f[2] = (float)(r.z >> 8) * sc < p ? 0.f : keep;
+  f[3] = (float)(r.w >> 8) * sc < p ? 0.f : keep;
+}
 enum : uint32_t { RS_ATTN1 = 1, RS_ATTN2 = 2, RS_PATH1 = 3, RS_PATH2 = 4, RS_HEAD = 5, RS_PRIOR = 6 };
 
 }  // namespace xf

@@ -184,16 +184,11 @@ __global__ void __launch_bounds__(256) attn_fwd32_kernel(AttnArgs a) {
   const float* Am = lanes_on_s ? Qs : Ks;
   const float* Bm = lanes_on_s ? Ks : Qs;
   const int tiles_a = (AR + 1) / 2, ntile = tiles_a * ((BR + 159) / 160);
+  const bool short_rows = (S & 3) == 0 && S <= 32;
+  const bool p_vec = (reinterpret_cast<uintptr_t>(a.P) & 15) == 0;
   for (int h = 0; h < H; ++h) {
-    for (int i = tid; i < L * dh; i += blockDim.x) {
-      const int l = i >> 5, d = i & 31;
-      Qs[l * dp + d] = q[(int64_t)l * E + h * dh + d] * a.scale;   // q scaled before the product, as torch does
-    }
-    for (int i = tid; i < S * dh; i += blockDim.x) {
-      const int s = i >> 5, d = i & 31;
-      Ks[s * dp + d] = kv[(int64_t)s * 2 * E + h * dh + d];
-      Vs[s * dp + d] = kv[(int64_t)s * 2 * E + E + h * dh + d];
-    }
+    stage_rows32(Qs, q + h * dh, L, E, a.scale, tid, blockDim.x);   // q scaled before the product, as torch does
+    stage_rows32x2(Ks, Vs, kv + h * dh, E, S, 2 * E, tid, blockDim.x);
     __syncthreads();
     for (int t = warp; t < ntile; t += nw) {
       const int a0 = (t % tiles_a) * 2, b0 = (t / tiles_a) * 160;
@@ -213,6 +208,37 @@ __global__ void __launch_bounds__(256) attn_fwd32_kernel(AttnArgs a) {
         }
     }
     __syncthreads();
+    if (short_rows) {
+      // rows of <= 32 scores (a2v: 16): lpr lanes per row with four scores each, 32/lpr rows per warp, one Philox evaluation
+      // per lane (a row's first element index is a multiple of 4) — a warp per row left half the lanes idle and spent one
+      // Philox evaluation and ten shuffles on every 16 scores.
+      const int lpr = S <= 16 ? 4 : 8, rpw = 32 / lpr, sub = lane / lpr, sl = lane - sub * lpr;
+      const bool act = 4 * sl < S;
+      for (int l0 = warp * rpw; l0 < L; l0 += nw * rpw) {
+        const int l = min(l0 + sub, L - 1);
+        const bool ok = act && l0 + sub < L;
+        float4* pr4 = reinterpret_cast<float4*>(Sc + l * SP) + sl;
+        float4 x = act ? *pr4 : make_float4(-INFINITY, -INFINITY, -INFINITY, -INFINITY);
+        float mx = fmaxf(fmaxf(x.x, x.y), fmaxf(x.z, x.w));
+        for (int o = lpr >> 1; o > 0; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+        x.x = expf(x.x - mx); x.y = expf(x.y - mx); x.z = expf(x.z - mx); x.w = expf(x.w - mx);
+        float sum = (x.x + x.y) + (x.z + x.w);
+        for (int o = lpr >> 1; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
+        const float inv = 1.f / sum;
+        x.x *= inv; x.y *= inv; x.z *= inv; x.w *= inv;
+        const int64_t idx0 = (((int64_t)b * H + h) * L + l) * S + 4 * sl;
+        if (ok && a.P) {
+          if (p_vec) *reinterpret_cast<float4*>(a.P + idx0) = x;
+          else { a.P[idx0] = x.x; a.P[idx0 + 1] = x.y; a.P[idx0 + 2] = x.z; a.P[idx0 + 3] = x.w; }
+        }
+        if (a.p_drop > 0.f) {
+          float f[4];
+          drop_factor4(a.p_drop, a.seed, a.offset, a.rng_stream, (uint64_t)idx0, f);
+          x.x *= f[0]; x.y *= f[1]; x.z *= f[2]; x.w *= f[3];
+        }
+        if (ok) *pr4 = x;
+      }
+    } else
     for (int l = warp; l < L; l += nw) {
       float* pr = Sc + l * SP;
       float mx = -INFINITY;

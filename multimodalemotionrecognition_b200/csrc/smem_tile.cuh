@@ -6,6 +6,57 @@
 
 namespace xf {
 
+// Stage `rows` rows of 32 floats (one head's slice; global row stride gs floats, 16-byte aligned) into dst[rows][33], times scale.
+// float4 loads, four in flight per thread before the first store: the scalar load->store loop this replaces held 40 % of the
+// attention kernels' stall samples on its long-scoreboard waits.  Eight lanes cover one row; with the odd pitch the four
+// scalar stores of a quarter-warp's rows fall in distinct banks.
+__device__ __forceinline__ void stage_rows32(float* __restrict__ dst, const float* __restrict__ src, int rows, int64_t gs, float scale,
+                                             int tid, int nthreads) {
+  const int n4 = rows * 8;
+  for (int base = 0; base < n4; base += 4 * nthreads) {
+    float4 v[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int i = base + tid + j * nthreads;
+      if (i < n4) v[j] = __ldg(reinterpret_cast<const float4*>(src + (int64_t)(i >> 3) * gs + (i & 7) * 4));
+    }
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int i = base + tid + j * nthreads;
+      if (i < n4) {
+        float* d = dst + (i >> 3) * 33 + (i & 7) * 4;
+        d[0] = v[j].x * scale; d[1] = v[j].y * scale; d[2] = v[j].z * scale; d[3] = v[j].w * scale;
+      }
+    }
+  }
+}
+// The same for two slices of one row at once (K and V of a head: src and src + second), so both sets of loads are in flight together.
+__device__ __forceinline__ void stage_rows32x2(float* __restrict__ dst0, float* __restrict__ dst1, const float* __restrict__ src,
+                                               int64_t second, int rows, int64_t gs, int tid, int nthreads) {
+  const int n4 = rows * 8;
+  for (int base = 0; base < n4; base += 2 * nthreads) {
+    float4 v[2], w[2];
+#pragma unroll
+    for (int j = 0; j < 2; ++j) {
+      const int i = base + tid + j * nthreads;
+      if (i < n4) {
+        const float* g = src + (int64_t)(i >> 3) * gs + (i & 7) * 4;
+        v[j] = __ldg(reinterpret_cast<const float4*>(g));
+        w[j] = __ldg(reinterpret_cast<const float4*>(g + second));
+      }
+    }
+#pragma unroll
+    for (int j = 0; j < 2; ++j) {
+      const int i = base + tid + j * nthreads;
+      if (i < n4) {
+        const int o = (i >> 3) * 33 + (i & 7) * 4;
+        dst0[o] = v[j].x; dst0[o + 1] = v[j].y; dst0[o + 2] = v[j].z; dst0[o + 3] = v[j].w;
+        dst1[o] = w[j].x; dst1[o + 1] = w[j].y; dst1[o + 2] = w[j].z; dst1[o + 3] = w[j].w;
+      }
+    }
+  }
+}
+
 // acc[i][j] = sum_k A[(a0+i)*pa + k] * B[(b0 + lane + 32j)*pb + k],  k < K.  Rows past the operands are clamped (the caller drops
 // those results).  pa, pb odd (dh + 1): the lane-strided rows of B fall in distinct banks, the rows of A are broadcasts.
 template <int TM, int TN>
