@@ -24,8 +24,44 @@ __global__ void colsum_kernel(const float* __restrict__ dY, int64_t ldy, int M, 
   for (; r < r1; ++r) s0 += dY[(int64_t)r * ldy + n];
   atomicAdd(db + n, (s0 + s1) + (s2 + s3));
 }
+// The same with float4 lanes (N % 4 == 0, N <= 1024, rows 16-byte aligned): N/4 threads cover a row, the CTA's 256/(N/4) row
+// groups stride over the block's rows with eight 16-byte loads in flight each, partial sums meet in shared memory and one
+// thread per column group issues the atomics.  The scalar kernel kept 4 bytes per load in flight and reached a quarter of HBM.
+__global__ void __launch_bounds__(256) colsum4_kernel(const float* __restrict__ dY, int64_t ldy, int M, int N, float* __restrict__ db,
+                                                      int rows_per_block) {
+  __shared__ float4 red[256];
+  const int tid = threadIdx.x, nc4 = N >> 2, nry = 256 / nc4, cx = tid % nc4, ry = tid / nc4;
+  const int r0 = blockIdx.x * rows_per_block, r1 = min(M, r0 + rows_per_block);
+  float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
+  if (ry < nry) {
+#pragma unroll 8
+    for (int r = r0 + ry; r < r1; r += nry) {
+      const float4 u = __ldg(reinterpret_cast<const float4*>(dY + (int64_t)r * ldy) + cx);
+      s.x += u.x; s.y += u.y; s.z += u.z; s.w += u.w;
+    }
+  }
+  red[tid] = s;
+  __syncthreads();
+  if (ry == 0) {
+    for (int k = 1; k < nry; ++k) {
+      const float4 u = red[cx + k * nc4];
+      s.x += u.x; s.y += u.y; s.z += u.z; s.w += u.w;
+    }
+    atomicAdd(db + 4 * cx, s.x);
+    atomicAdd(db + 4 * cx + 1, s.y);
+    atomicAdd(db + 4 * cx + 2, s.z);
+    atomicAdd(db + 4 * cx + 3, s.w);
+  }
+}
 void launch_colsum(cudaStream_t st, const float* dY, int64_t ldy, int M, int N, float* db) {
   if (M <= 0 || N <= 0) return;
+  if ((N & 3) == 0 && N <= 1024 && (ldy & 3) == 0 && (reinterpret_cast<uintptr_t>(dY) & 15) == 0) {
+    int rpb = (M + 4 * num_sms() - 1) / (4 * num_sms());
+    if (rpb < 64) rpb = 64;
+    colsum4_kernel<<<(M + rpb - 1) / rpb, 256, 0, st>>>(dY, ldy, M, N, db, rpb);
+    count_launch();
+    return;
+  }
   const int rpb = 256;
   dim3 grid((N + 127) / 128, (M + rpb - 1) / rpb);
   colsum_kernel<<<grid, 128, 0, st>>>(dY, ldy, M, N, db, rpb);
@@ -131,6 +167,84 @@ __global__ void __launch_bounds__(256) ln_bwd_kernel(const float* __restrict__ d
       atomicAdd(dbeta + e, ab[k]);
     }
   }
+}
+
+// E == 128: a lane owns four adjacent columns, so one float4 load per operand covers the row and dy / x stay in registers
+// between the two passes; a warp works on two rows at a time (all their loads in flight before the first reduction); the
+// dgamma / dbeta partials of the CTA's warps meet in shared memory before the atomics (one per column and CTA).
+__global__ void __launch_bounds__(256) ln_bwd128_kernel(const float* __restrict__ dy_full, const float* __restrict__ dy_pool,
+                                                        int64_t pool_ld, float inv_L, const float* __restrict__ s,
+                                                        const float* __restrict__ mean, const float* __restrict__ rstd,
+                                                        const float* __restrict__ gamma, const float* __restrict__ dpf,
+                                                        float* __restrict__ dx_out, float* __restrict__ dbranch,
+                                                        float* __restrict__ dgamma, float* __restrict__ dbeta, int rows, int L) {
+  constexpr int E = 128;
+  __shared__ float red[8][2 * E];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const float4 g4 = __ldg(reinterpret_cast<const float4*>(gamma) + lane);
+  float4 ag = make_float4(0.f, 0.f, 0.f, 0.f), ab = ag;
+  const int stride = gridDim.x * 8 * 2;
+  for (int row0 = (blockIdx.x * 8 + warp) * 2; row0 < rows; row0 += stride) {
+    float4 dy[2], xh[2];
+    float mu[2], rs[2], f[2];
+    bool ok[2];
+#pragma unroll
+    for (int i = 0; i < 2; ++i) {
+      const int row = row0 + i;
+      ok[i] = row < rows;
+      const int rr = ok[i] ? row : rows - 1, b = rr / L;
+      dy[i] = dy_full ? __ldg(reinterpret_cast<const float4*>(dy_full + (int64_t)rr * E) + lane) : make_float4(0.f, 0.f, 0.f, 0.f);
+      if (dy_pool) {
+        const float4 p = __ldg(reinterpret_cast<const float4*>(dy_pool + (int64_t)b * pool_ld) + lane);
+        dy[i].x = fmaf(p.x, inv_L, dy[i].x); dy[i].y = fmaf(p.y, inv_L, dy[i].y);
+        dy[i].z = fmaf(p.z, inv_L, dy[i].z); dy[i].w = fmaf(p.w, inv_L, dy[i].w);
+      }
+      xh[i] = __ldg(reinterpret_cast<const float4*>(s + (int64_t)rr * E) + lane);
+      mu[i] = mean[rr]; rs[i] = rstd[rr];
+      f[i] = dpf ? dpf[b] : 1.f;
+    }
+#pragma unroll
+    for (int i = 0; i < 2; ++i) {
+      xh[i].x = (xh[i].x - mu[i]) * rs[i]; xh[i].y = (xh[i].y - mu[i]) * rs[i];
+      xh[i].z = (xh[i].z - mu[i]) * rs[i]; xh[i].w = (xh[i].w - mu[i]) * rs[i];
+      const float4 dg = make_float4(dy[i].x * g4.x, dy[i].y * g4.y, dy[i].z * g4.z, dy[i].w * g4.w);
+      float s1 = (dg.x + dg.y) + (dg.z + dg.w);
+      float s2 = fmaf(dg.x, xh[i].x, fmaf(dg.y, xh[i].y, fmaf(dg.z, xh[i].z, dg.w * xh[i].w)));
+      s1 = warp_sum(s1) * (1.f / (float)E);
+      s2 = warp_sum(s2) * (1.f / (float)E);
+      if (ok[i]) {
+        float4 dx;
+        dx.x = rs[i] * (dg.x - s1 - xh[i].x * s2); dx.y = rs[i] * (dg.y - s1 - xh[i].y * s2);
+        dx.z = rs[i] * (dg.z - s1 - xh[i].z * s2); dx.w = rs[i] * (dg.w - s1 - xh[i].w * s2);
+        const int64_t o = (int64_t)(row0 + i) * E;
+        reinterpret_cast<float4*>(dx_out + o)[lane] = dx;
+        reinterpret_cast<float4*>(dbranch + o)[lane] = make_float4(dx.x * f[i], dx.y * f[i], dx.z * f[i], dx.w * f[i]);
+        ag.x = fmaf(dy[i].x, xh[i].x, ag.x); ag.y = fmaf(dy[i].y, xh[i].y, ag.y);
+        ag.z = fmaf(dy[i].z, xh[i].z, ag.z); ag.w = fmaf(dy[i].w, xh[i].w, ag.w);
+        ab.x += dy[i].x; ab.y += dy[i].y; ab.z += dy[i].z; ab.w += dy[i].w;
+      }
+    }
+  }
+  float* r = red[warp];
+  r[4 * lane] = ag.x; r[4 * lane + 1] = ag.y; r[4 * lane + 2] = ag.z; r[4 * lane + 3] = ag.w;
+  r[E + 4 * lane] = ab.x; r[E + 4 * lane + 1] = ab.y; r[E + 4 * lane + 2] = ab.z; r[E + 4 * lane + 3] = ab.w;
+  __syncthreads();
+  {
+    const int c = threadIdx.x;   // 256 threads: columns 0..127 of dgamma, then of dbeta
+    float t = 0.f;
+#pragma unroll
+    for (int w = 0; w < 8; ++w) t += red[w][c];
+    atomicAdd((c < E ? dgamma : dbeta - E) + c, t);
+  }
+}
+static void launch_ln_bwd(cudaStream_t st, int grid, const float* dy_full, const float* dy_pool, int64_t pool_ld, float inv_L, const float* s,
+                          const float* mean, const float* rstd, const float* gamma, const float* dpf, float* dx_out, float* dbranch,
+                          float* dgamma, float* dbeta, int rows, int L, int E) {
+  if (E == 128 && (pool_ld & 3) == 0)
+    ln_bwd128_kernel<<<grid, 256, 0, st>>>(dy_full, dy_pool, pool_ld, inv_L, s, mean, rstd, gamma, dpf, dx_out, dbranch, dgamma, dbeta, rows, L);
+  else
+    ln_bwd_kernel<<<grid, 256, 0, st>>>(dy_full, dy_pool, pool_ld, inv_L, s, mean, rstd, gamma, dpf, dx_out, dbranch, dgamma, dbeta, rows, L, E);
+  count_launch();
 }
 
 // ---- attention backward ---------------------------------------------------------------------------------------
@@ -425,6 +539,7 @@ struct PriorBwdArgs {
   float* g_bh[4];
   int T, Ta, E, P, Hd;
   float inv_keep;
+  int vec;   // float4 token loop (E % 4 == 0, dpool 16-byte aligned in shared memory is not needed: scalar smem accesses)
 };
 __global__ void __launch_bounds__(256) prior_bwd_kernel(PriorBwdArgs a) {
   extern __shared__ float sm[];
@@ -471,6 +586,59 @@ __global__ void __launch_bounds__(256) prior_bwd_kernel(PriorBwdArgs a) {
   const float* a0 = a.a0 + (int64_t)b * Ta * E;
   float* dv0 = a.d_v0 + (int64_t)b * T * E;
   float* da0 = a.d_a0 + (int64_t)b * Ta * E;
+  if (a.vec) {
+    // token gradients + the token part of the score-head weights: warps stride over the tokens, a lane owns four columns
+    // (float4 loads / read-modify-writes, independent across tokens); the four weight-gradient rows of the CTA's warps
+    // meet in shared memory, then one atomic per column.  (The scalar loop below walks the tokens with E threads.)
+    float* sd = dpool + 2 * E;          // [2T + 2Ta] score gradients of this clip
+    float* gred = sd + 2 * (T + Ta);    // [nw][4][E]
+    for (int i = tid; i < T; i += blockDim.x) { sd[i] = dsc[0][i]; sd[T + i] = dsc[3][i]; }
+    for (int j = tid; j < Ta; j += blockDim.x) { sd[2 * T + j] = dsc[1][j]; sd[2 * T + Ta + j] = dsc[2][j]; }
+    __syncthreads();
+    const float inv_T = 1.f / (float)T, inv_Ta = 1.f / (float)Ta;
+    for (int c4 = lane; c4 < (E >> 2); c4 += 32) {
+      const int e = 4 * c4;
+      float wq[4], wk[4], g0[4] = {0.f, 0.f, 0.f, 0.f}, g1[4] = {0.f, 0.f, 0.f, 0.f}, g2[4] = {0.f, 0.f, 0.f, 0.f}, g3[4] = {0.f, 0.f, 0.f, 0.f}, pm[4];
+#pragma unroll
+      for (int k = 0; k < 4; ++k) { wq[k] = a.wh[0][e + k]; wk[k] = a.wh[3][e + k]; pm[k] = dpool[e + k] * inv_T; }
+#pragma unroll 4
+      for (int i = warp; i < T; i += nw) {
+        const float dq = sd[i], dk = sd[T + i];
+        const float4 x = __ldg(reinterpret_cast<const float4*>(v0 + (int64_t)i * E) + c4);
+        float4* dp = reinterpret_cast<float4*>(dv0 + (int64_t)i * E) + c4;
+        float4 d = *dp;
+        d.x += dq * wq[0] + dk * wk[0] + pm[0]; d.y += dq * wq[1] + dk * wk[1] + pm[1];
+        d.z += dq * wq[2] + dk * wk[2] + pm[2]; d.w += dq * wq[3] + dk * wk[3] + pm[3];
+        *dp = d;
+        g0[0] = fmaf(dq, x.x, g0[0]); g0[1] = fmaf(dq, x.y, g0[1]); g0[2] = fmaf(dq, x.z, g0[2]); g0[3] = fmaf(dq, x.w, g0[3]);
+        g3[0] = fmaf(dk, x.x, g3[0]); g3[1] = fmaf(dk, x.y, g3[1]); g3[2] = fmaf(dk, x.z, g3[2]); g3[3] = fmaf(dk, x.w, g3[3]);
+      }
+#pragma unroll
+      for (int k = 0; k < 4; ++k) { wk[k] = a.wh[1][e + k]; wq[k] = a.wh[2][e + k]; pm[k] = dpool[E + e + k] * inv_Ta; }
+#pragma unroll 4
+      for (int j = warp; j < Ta; j += nw) {
+        const float dk = sd[2 * T + j], dq = sd[2 * T + Ta + j];
+        const float4 x = __ldg(reinterpret_cast<const float4*>(a0 + (int64_t)j * E) + c4);
+        float4* dp = reinterpret_cast<float4*>(da0 + (int64_t)j * E) + c4;
+        float4 d = *dp;
+        d.x += dk * wk[0] + dq * wq[0] + pm[0]; d.y += dk * wk[1] + dq * wq[1] + pm[1];
+        d.z += dk * wk[2] + dq * wq[2] + pm[2]; d.w += dk * wk[3] + dq * wq[3] + pm[3];
+        *dp = d;
+        g1[0] = fmaf(dk, x.x, g1[0]); g1[1] = fmaf(dk, x.y, g1[1]); g1[2] = fmaf(dk, x.z, g1[2]); g1[3] = fmaf(dk, x.w, g1[3]);
+        g2[0] = fmaf(dq, x.x, g2[0]); g2[1] = fmaf(dq, x.y, g2[1]); g2[2] = fmaf(dq, x.z, g2[2]); g2[3] = fmaf(dq, x.w, g2[3]);
+      }
+      float* gr = gred + (int64_t)warp * 4 * E + e;
+#pragma unroll
+      for (int k = 0; k < 4; ++k) { gr[k] = g0[k]; gr[E + k] = g1[k]; gr[2 * E + k] = g2[k]; gr[3 * E + k] = g3[k]; }
+    }
+    __syncthreads();
+    for (int idx = tid; idx < 4 * E; idx += blockDim.x) {
+      float t = 0.f;
+      for (int w2 = 0; w2 < nw; ++w2) t += gred[(int64_t)w2 * 4 * E + idx];
+      atomicAdd(a.g_wh[idx / E] + (idx % E), t);
+    }
+    return;
+  }
   // token gradients + the token part of the score-head weights (block-local reduction, then one atomic per e)
   for (int e = tid; e < E; e += blockDim.x) {
     const float w_vq = a.wh[0][e], w_ak = a.wh[1][e], w_aq = a.wh[2][e], w_vk = a.wh[3][e];
@@ -541,9 +709,8 @@ static int backward_f32_impl(const xattn_config& c, const float* params, const T
 
   const int ln_grid = 4 * num_sms();
   // ---- a_norm backward (fusion.py:399) + mean pool (temporal.py:108-109) ----
-  ln_bwd_kernel<<<ln_grid, 256, 0, st>>>(nullptr, ws + w.d_pooled + E, 2 * E, 1.f / (float)Ta, ws + w.s2, ws + w.mean2, ws + w.rstd2,
-                                         P(XP_AN_W), ws + w.dp2, ws + w.d_a0, ws + w.d_br2, G(XP_AN_W), G(XP_AN_B), B * Ta, Ta, E);
-  count_launch();
+  launch_ln_bwd(st, ln_grid, nullptr, ws + w.d_pooled + E, 2 * E, 1.f / (float)Ta, ws + w.s2, ws + w.mean2, ws + w.rstd2, P(XP_AN_W),
+                ws + w.dp2, ws + w.d_a0, ws + w.d_br2, G(XP_AN_W), G(XP_AN_B), B * Ta, Ta, E);
   // a2v out_proj
   linear_bwd_dw<float>(st, ws + w.d_br2, E, ws + w.o2, E, G(XP_A2V_OUT_W), B * Ta, E, E);
   launch_colsum(st, ws + w.d_br2, E, B * Ta, E, G(XP_A2V_OUT_B));
@@ -569,9 +736,8 @@ static int backward_f32_impl(const xattn_config& c, const float* params, const T
   linear_bwd_dx(st, ws + w.d_kv2, 2 * E, P(XP_A2V_IN_W) + (int64_t)E * E, ws + w.d_v1, B * T, 2 * E, E, false);
   XF_LAUNCH_CHECK();
   // ---- v_norm backward (fusion.py:395) ----
-  ln_bwd_kernel<<<ln_grid, 256, 0, st>>>(ws + w.d_v1, ws + w.d_pooled, 2 * E, 1.f / (float)T, ws + w.s1, ws + w.mean1, ws + w.rstd1,
-                                         P(XP_VN_W), ws + w.dp1, ws + w.d_v0, ws + w.d_br1, G(XP_VN_W), G(XP_VN_B), B * T, T, E);
-  count_launch();
+  launch_ln_bwd(st, ln_grid, ws + w.d_v1, ws + w.d_pooled, 2 * E, 1.f / (float)T, ws + w.s1, ws + w.mean1, ws + w.rstd1, P(XP_VN_W),
+                ws + w.dp1, ws + w.d_v0, ws + w.d_br1, G(XP_VN_W), G(XP_VN_B), B * T, T, E);
   linear_bwd_dw<float>(st, ws + w.d_br1, E, ws + w.o1, E, G(XP_V2A_OUT_W), B * T, E, E);
   launch_colsum(st, ws + w.d_br1, E, B * T, E, G(XP_V2A_OUT_B));
   linear_bwd_dx(st, ws + w.d_br1, E, P(XP_V2A_OUT_W), ws + w.d_o1, B * T, E, E, false);
@@ -606,7 +772,10 @@ static int backward_f32_impl(const xattn_config& c, const float* params, const T
     pa.d_qv = ws + w.d_qv; pa.d_ka = ws + w.d_ka; pa.d_qa = ws + w.d_qa; pa.d_kvs = ws + w.d_kvs;
     pa.d_v0 = ws + w.d_v0; pa.d_a0 = ws + w.d_a0; pa.d_prior = ws + w.d_prior; pa.d_phid = ws + w.d_phid;
     pa.T = T; pa.Ta = Ta; pa.E = E; pa.P = c.prior_dim; pa.Hd = c.prior_hidden; pa.inv_keep = 1.f / (1.f - p_prior);
-    const size_t smem = sizeof(float) * (4 + c.prior_dim + c.prior_hidden + 2 * E);
+    size_t smem = sizeof(float) * (4 + c.prior_dim + c.prior_hidden + 2 * E);
+    const size_t smem_vec = smem + sizeof(float) * (2 * (T + Ta) + 8 * 4 * E);
+    pa.vec = (E % 4 == 0 && smem_vec <= 48 * 1024) ? 1 : 0;
+    if (pa.vec) smem = smem_vec;
     prior_bwd_kernel<<<B, 256, smem, st>>>(pa);
     count_launch();
     linear_bwd_dw<float>(st, ws + w.d_prior, c.prior_dim, ws + w.phid, c.prior_hidden, G(XP_PRIOR3_W), B, c.prior_dim, c.prior_hidden);

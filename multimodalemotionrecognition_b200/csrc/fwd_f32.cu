@@ -25,17 +25,11 @@ __global__ void __launch_bounds__(256) prior_fwd_kernel(PriorArgs a) {
   float* hid = pooled + 2 * E;   // [Hd]
   float* prior = hid + Hd;       // [P]
   float* pc = prior + P;         // [4] prior contribution + bias of the four score heads
+  float* scratch = pc + 4;       // [nw][E]
   const float* v0 = a.v0 + (int64_t)b * T * E;
   const float* a0 = a.a0 + (int64_t)b * Ta * E;
-  for (int e = tid; e < E; e += blockDim.x) {
-    float s = 0.f;
-    for (int t = 0; t < T; ++t) s += v0[(int64_t)t * E + e];
-    pooled[e] = s / (float)T;
-    float s2 = 0.f;
-    for (int t = 0; t < Ta; ++t) s2 += a0[(int64_t)t * E + e];
-    pooled[E + e] = s2 / (float)Ta;
-  }
-  __syncthreads();
+  clip_mean(v0, T, E, pooled, scratch, tid, blockDim.x);
+  clip_mean(a0, Ta, E, pooled + E, scratch, tid, blockDim.x);
   for (int e = tid; e < 2 * E; e += blockDim.x) a.pooled0[(int64_t)b * 2 * E + e] = pooled[e];
   for (int h = warp; h < Hd; h += nw) {
     const float* w = a.w0 + (int64_t)h * 2 * E;
@@ -333,18 +327,12 @@ __global__ void __launch_bounds__(256) pool_head_fwd_kernel(HeadArgs a) {
   float* pooled = sm;            // [2E]
   float* hid = pooled + 2 * E;   // [HW]
   float* fused = hid + HW;       // [E] (gated)
+  float* scratch = fused + E;    // [nw][E]
   __shared__ float s_gate;
   const float* v1 = a.v1 + (int64_t)b * T * E;
   const float* a1 = a.a1 + (int64_t)b * Ta * E;
-  for (int e = tid; e < E; e += blockDim.x) {
-    float s = 0.f;
-    for (int t = 0; t < T; ++t) s += v1[(int64_t)t * E + e];
-    pooled[e] = s / (float)T;
-    float s2 = 0.f;
-    for (int t = 0; t < Ta; ++t) s2 += a1[(int64_t)t * E + e];
-    pooled[E + e] = s2 / (float)Ta;
-  }
-  __syncthreads();
+  clip_mean(v1, T, E, pooled, scratch, tid, blockDim.x);
+  clip_mean(a1, Ta, E, pooled + E, scratch, tid, blockDim.x);
   if (a.pooled)
     for (int e = tid; e < 2 * E; e += blockDim.x) a.pooled[(int64_t)b * 2 * E + e] = pooled[e];
   for (int h = warp; h < HW; h += nw) {
@@ -555,7 +543,7 @@ static int forward_f32_impl(const xattn_config& c, const float* params, const TI
     pa.qv = ws + w.qv; pa.ka = ws + w.ka; pa.qa = ws + w.qa; pa.kvs = ws + w.kvs;
     pa.T = T; pa.Ta = Ta; pa.E = E; pa.P = c.prior_dim; pa.Hd = c.prior_hidden;
     pa.p_drop = p_prior; pa.seed = c.seed; pa.offset = c.offset;
-    const size_t smem = sizeof(float) * (2 * E + c.prior_hidden + c.prior_dim + 4);
+    const size_t smem = sizeof(float) * (2 * E + c.prior_hidden + c.prior_dim + 4 + 8 * E);
     prior_fwd_kernel<<<B, 256, smem, st>>>(pa);
     count_launch();
     XF_LAUNCH_CHECK();
@@ -626,7 +614,7 @@ static int forward_f32_impl(const xattn_config& c, const float* params, const TI
     ha.T = hT; ha.Ta = hTa; ha.E = E; ha.C = c.C; ha.gated = c.head_kind == XATTN_HEAD_GATED;
     ha.HW = ha.gated ? E : c.common_dim;
     ha.p_drop = p_head; ha.seed = c.seed; ha.offset = c.offset;
-    const size_t smem = sizeof(float) * (3 * E + ha.HW);
+    const size_t smem = sizeof(float) * (3 * E + ha.HW + 8 * E);
     pool_head_fwd_kernel<<<B, 256, smem, st>>>(ha);
     count_launch();
     XF_LAUNCH_CHECK();

@@ -6,6 +6,41 @@
 
 namespace xf {
 
+// out[e] = mean over the L rows of x[L][E] (global, rows 16-byte aligned when E % 4 == 0), for every thread of the CTA; out and
+// scratch ((nthreads/32)·E floats) in shared memory.  Warps stride over the rows, a lane owns four columns (float4 loads, eight
+// in flight), partial sums meet in scratch.  The loop it replaces walked the rows with E of the CTA's threads, one scalar
+// load per row.  Ends with __syncthreads().
+__device__ __forceinline__ void clip_mean(const float* __restrict__ x, int L, int E, float* __restrict__ out, float* __restrict__ scratch,
+                                          int tid, int nthreads) {
+  const int lane = tid & 31, warp = tid >> 5, nw = nthreads >> 5;
+  if ((E & 3) != 0) {
+    for (int e = tid; e < E; e += nthreads) {
+      float s = 0.f;
+      for (int t = 0; t < L; ++t) s += x[(int64_t)t * E + e];
+      out[e] = s / (float)L;
+    }
+    __syncthreads();
+    return;
+  }
+  for (int c4 = lane; c4 < (E >> 2); c4 += 32) {
+    float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll 8
+    for (int t = warp; t < L; t += nw) {
+      const float4 u = __ldg(reinterpret_cast<const float4*>(x + (int64_t)t * E) + c4);
+      s.x += u.x; s.y += u.y; s.z += u.z; s.w += u.w;
+    }
+    float* d = scratch + warp * E + 4 * c4;
+    d[0] = s.x; d[1] = s.y; d[2] = s.z; d[3] = s.w;
+  }
+  __syncthreads();
+  for (int e = tid; e < E; e += nthreads) {
+    float s = 0.f;
+    for (int w = 0; w < nw; ++w) s += scratch[w * E + e];
+    out[e] = s / (float)L;
+  }
+  __syncthreads();
+}
+
 // Stage `rows` rows of 32 floats (one head's slice; global row stride gs floats, 16-byte aligned) into dst[rows][33], times scale.
 // float4 loads, four in flight per thread before the first store: the scalar load->store loop this replaces held 40 % of the
 // attention kernels' stall samples on its long-scoreboard waits.  Eight lanes cover one row; with the odd pitch the four
