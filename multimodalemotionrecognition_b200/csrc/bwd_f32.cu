@@ -177,12 +177,13 @@ __global__ void __launch_bounds__(256) ln_bwd128_kernel(const float* __restrict_
                                                         const float* __restrict__ mean, const float* __restrict__ rstd,
                                                         const float* __restrict__ gamma, const float* __restrict__ dpf,
                                                         float* __restrict__ dx_out, float* __restrict__ dbranch,
-                                                        float* __restrict__ dgamma, float* __restrict__ dbeta, int rows, int L) {
+                                                        float* __restrict__ dgamma, float* __restrict__ dbeta, float* __restrict__ dbranch_bias,
+                                                        int rows, int L) {
   constexpr int E = 128;
-  __shared__ float red[8][2 * E];
+  __shared__ float red[8][3 * E];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const float4 g4 = __ldg(reinterpret_cast<const float4*>(gamma) + lane);
-  float4 ag = make_float4(0.f, 0.f, 0.f, 0.f), ab = ag;
+  float4 ag = make_float4(0.f, 0.f, 0.f, 0.f), ab = ag, abr = ag;   // dgamma, dbeta, column sums of dbranch
   const int stride = gridDim.x * 8 * 2;
   for (int row0 = (blockIdx.x * 8 + warp) * 2; row0 < rows; row0 += stride) {
     float4 dy[2], xh[2];
@@ -222,29 +223,35 @@ __global__ void __launch_bounds__(256) ln_bwd128_kernel(const float* __restrict_
         ag.x = fmaf(dy[i].x, xh[i].x, ag.x); ag.y = fmaf(dy[i].y, xh[i].y, ag.y);
         ag.z = fmaf(dy[i].z, xh[i].z, ag.z); ag.w = fmaf(dy[i].w, xh[i].w, ag.w);
         ab.x += dy[i].x; ab.y += dy[i].y; ab.z += dy[i].z; ab.w += dy[i].w;
+        abr.x = fmaf(dx.x, f[i], abr.x); abr.y = fmaf(dx.y, f[i], abr.y); abr.z = fmaf(dx.z, f[i], abr.z); abr.w = fmaf(dx.w, f[i], abr.w);
       }
     }
   }
   float* r = red[warp];
   r[4 * lane] = ag.x; r[4 * lane + 1] = ag.y; r[4 * lane + 2] = ag.z; r[4 * lane + 3] = ag.w;
   r[E + 4 * lane] = ab.x; r[E + 4 * lane + 1] = ab.y; r[E + 4 * lane + 2] = ab.z; r[E + 4 * lane + 3] = ab.w;
+  r[2 * E + 4 * lane] = abr.x; r[2 * E + 4 * lane + 1] = abr.y; r[2 * E + 4 * lane + 2] = abr.z; r[2 * E + 4 * lane + 3] = abr.w;
   __syncthreads();
-  {
-    const int c = threadIdx.x;   // 256 threads: columns 0..127 of dgamma, then of dbeta
+  for (int c = threadIdx.x; c < (dbranch_bias ? 3 * E : 2 * E); c += 256) {   // columns of dgamma | dbeta | dbranch_bias
     float t = 0.f;
 #pragma unroll
     for (int w = 0; w < 8; ++w) t += red[w][c];
-    atomicAdd((c < E ? dgamma : dbeta - E) + c, t);
+    atomicAdd(c < E ? dgamma + c : c < 2 * E ? dbeta + (c - E) : dbranch_bias + (c - 2 * E), t);
   }
 }
-static void launch_ln_bwd(cudaStream_t st, int grid, const float* dy_full, const float* dy_pool, int64_t pool_ld, float inv_L, const float* s,
+// dbranch_bias (optional): += column sums of dbranch (the bias gradient of the Linear that produced the branch).  Returns
+// whether the kernel accumulated it; if not the caller runs the column-sum pass.
+static bool launch_ln_bwd(cudaStream_t st, int grid, const float* dy_full, const float* dy_pool, int64_t pool_ld, float inv_L, const float* s,
                           const float* mean, const float* rstd, const float* gamma, const float* dpf, float* dx_out, float* dbranch,
-                          float* dgamma, float* dbeta, int rows, int L, int E) {
-  if (E == 128 && (pool_ld & 3) == 0)
-    ln_bwd128_kernel<<<grid, 256, 0, st>>>(dy_full, dy_pool, pool_ld, inv_L, s, mean, rstd, gamma, dpf, dx_out, dbranch, dgamma, dbeta, rows, L);
+                          float* dgamma, float* dbeta, float* dbranch_bias, int rows, int L, int E) {
+  const bool fast = E == 128 && (pool_ld & 3) == 0;
+  if (fast)
+    ln_bwd128_kernel<<<grid, 256, 0, st>>>(dy_full, dy_pool, pool_ld, inv_L, s, mean, rstd, gamma, dpf, dx_out, dbranch, dgamma, dbeta,
+                                           dbranch_bias, rows, L);
   else
     ln_bwd_kernel<<<grid, 256, 0, st>>>(dy_full, dy_pool, pool_ld, inv_L, s, mean, rstd, gamma, dpf, dx_out, dbranch, dgamma, dbeta, rows, L, E);
   count_launch();
+  return fast;
 }
 
 // ---- attention backward ---------------------------------------------------------------------------------------
@@ -358,6 +365,7 @@ __global__ void __launch_bounds__(256) attn_bwd_kernel(AttnBwdArgs a) {
 // shared memory so their rows stay 16-byte aligned.
 __global__ void __launch_bounds__(256) attn_bwd32_kernel(AttnBwdArgs a) {
   extern __shared__ __align__(16) float sm[];
+  __shared__ float bred[8][96];   // per-warp column sums of dq | dk | dv of the current head
   const int b = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nw = blockDim.x >> 5;
   const int L = a.L, S = a.S, E = a.E, H = a.H, SP = (S + 3) & ~3;
   constexpr int dh = 32, dp = 33;
@@ -421,7 +429,9 @@ __global__ void __launch_bounds__(256) attn_bwd32_kernel(AttnBwdArgs a) {
       }
     }
     __syncthreads();
-    // dV = Pd^T dO, dK = dS^T (scale·Q): [S, dh], lane = column
+    // dV = Pd^T dO, dK = dS^T (scale·Q): [S, dh], lane = column.  bq / bk / bv: this warp's column sums of the rows it
+    // produced (the in_proj bias gradients, a.dbq / a.dbkv) — the separate column-sum passes over dq / dkv re-read them from HBM.
+    float bq = 0.f, bk = 0.f, bv = 0.f;
     if (S > 32) {
       for (int t = warp; t < (S + 3) / 4; t += nw) {
         float dv[4], dk[4];
@@ -432,6 +442,8 @@ __global__ void __launch_bounds__(256) attn_bwd32_kernel(AttnBwdArgs a) {
           if (4 * t + i < S) {
             a.dkv[((int64_t)b * S + 4 * t + i) * 2 * E + h * dh + lane] = dk[i];
             a.dkv[((int64_t)b * S + 4 * t + i) * 2 * E + E + h * dh + lane] = dv[i];
+            bk += dk[i];
+            bv += dv[i];
           }
       }
     } else {
@@ -444,6 +456,8 @@ __global__ void __launch_bounds__(256) attn_bwd32_kernel(AttnBwdArgs a) {
           if (2 * t + i < S) {
             a.dkv[((int64_t)b * S + 2 * t + i) * 2 * E + h * dh + lane] = dk[i];
             a.dkv[((int64_t)b * S + 2 * t + i) * 2 * E + E + h * dh + lane] = dv[i];
+            bk += dk[i];
+            bv += dv[i];
           }
       }
     }
@@ -454,7 +468,10 @@ __global__ void __launch_bounds__(256) attn_bwd32_kernel(AttnBwdArgs a) {
         tile_ak<4>(dSs, 4 * t, L, SP, Ks, dp, S, lane, dq);
 #pragma unroll
         for (int i = 0; i < 4; ++i)
-          if (4 * t + i < L) a.dq[((int64_t)b * L + 4 * t + i) * E + h * dh + lane] = dq[i] * a.scale;
+          if (4 * t + i < L) {
+            a.dq[((int64_t)b * L + 4 * t + i) * E + h * dh + lane] = dq[i] * a.scale;
+            bq += dq[i] * a.scale;
+          }
       }
     } else {
       for (int t = warp; t < (L + 1) / 2; t += nw) {
@@ -462,10 +479,24 @@ __global__ void __launch_bounds__(256) attn_bwd32_kernel(AttnBwdArgs a) {
         tile_ak<2>(dSs, 2 * t, L, SP, Ks, dp, S, lane, dq);
 #pragma unroll
         for (int i = 0; i < 2; ++i)
-          if (2 * t + i < L) a.dq[((int64_t)b * L + 2 * t + i) * E + h * dh + lane] = dq[i] * a.scale;
+          if (2 * t + i < L) {
+            a.dq[((int64_t)b * L + 2 * t + i) * E + h * dh + lane] = dq[i] * a.scale;
+            bq += dq[i] * a.scale;
+          }
       }
     }
+    if (a.dbq) {
+      bred[warp][lane] = bq;
+      bred[warp][32 + lane] = bk;
+      bred[warp][64 + lane] = bv;
+    }
     __syncthreads();
+    if (a.dbq && tid < 96) {   // (bred is rewritten only after the next head's staging barrier)
+      float t = 0.f;
+      for (int w2 = 0; w2 < nw; ++w2) t += bred[w2][tid];
+      const int which = tid >> 5, c = h * dh + (tid & 31);
+      atomicAdd(which == 0 ? a.dbq + c : a.dbkv + (which - 1) * E + c, t);
+    }
   }
   if (a.qs == nullptr) return;
   const float* qs = a.qs + (int64_t)b * L;
@@ -500,8 +531,10 @@ __global__ void __launch_bounds__(256) attn_bwd32_kernel(AttnBwdArgs a) {
   }
 }
 
-static int launch_attn_bwd(cudaStream_t st, const AttnBwdArgs& a, int B) {
+// *bias_fused: the kernel accumulated a.dbq / a.dbkv itself (else the caller runs the column sums over dq / dkv)
+static int launch_attn_bwd(cudaStream_t st, const AttnBwdArgs& a, int B, bool* bias_fused) {
   const int dh = a.E / a.H;
+  *bias_fused = dh == 32 && a.dbq != nullptr;
   if (dh == 32) {
     const int SP = (a.S + 3) & ~3;
     const size_t smem32 = sizeof(float) * (4 * (size_t)a.L * SP + (size_t)(2 * a.L + 2 * a.S) * 33);
@@ -708,12 +741,13 @@ static int backward_f32_impl(const xattn_config& c, const float* params, const T
   XF_LAUNCH_CHECK();
 
   const int ln_grid = 4 * num_sms();
+  bool bias_fused = false;
   // ---- a_norm backward (fusion.py:399) + mean pool (temporal.py:108-109) ----
-  launch_ln_bwd(st, ln_grid, nullptr, ws + w.d_pooled + E, 2 * E, 1.f / (float)Ta, ws + w.s2, ws + w.mean2, ws + w.rstd2, P(XP_AN_W),
-                ws + w.dp2, ws + w.d_a0, ws + w.d_br2, G(XP_AN_W), G(XP_AN_B), B * Ta, Ta, E);
+  bool ob_fused = launch_ln_bwd(st, ln_grid, nullptr, ws + w.d_pooled + E, 2 * E, 1.f / (float)Ta, ws + w.s2, ws + w.mean2, ws + w.rstd2,
+                                P(XP_AN_W), ws + w.dp2, ws + w.d_a0, ws + w.d_br2, G(XP_AN_W), G(XP_AN_B), G(XP_A2V_OUT_B), B * Ta, Ta, E);
   // a2v out_proj
   linear_bwd_dw<float>(st, ws + w.d_br2, E, ws + w.o2, E, G(XP_A2V_OUT_W), B * Ta, E, E);
-  launch_colsum(st, ws + w.d_br2, E, B * Ta, E, G(XP_A2V_OUT_B));
+  if (!ob_fused) launch_colsum(st, ws + w.d_br2, E, B * Ta, E, G(XP_A2V_OUT_B));
   linear_bwd_dx(st, ws + w.d_br2, E, P(XP_A2V_OUT_W), ws + w.d_o2, B * Ta, E, E, false);
   XF_LAUNCH_CHECK();
   {
@@ -725,21 +759,22 @@ static int backward_f32_impl(const xattn_config& c, const float* params, const T
     aa.dbias_scale = c.use_prior ? G(XP_BIAS_SCALE) : nullptr;
     aa.L = Ta; aa.S = T; aa.E = E; aa.H = H; aa.scale = scale; aa.p_drop = p_attn; aa.seed = c.seed; aa.offset = c.offset;
     aa.rng_stream = RS_ATTN2;
-    XF_TRY(launch_attn_bwd(st, aa, B));
+    aa.dbq = G(XP_A2V_IN_B); aa.dbkv = G(XP_A2V_IN_B) + E;
+    XF_TRY(launch_attn_bwd(st, aa, B, &bias_fused));
   }
   // a2v in_proj: q from a0, k|v from v1
   linear_bwd_dw<float>(st, ws + w.d_q2, E, ws + w.a0, E, G(XP_A2V_IN_W), B * Ta, E, E);
-  launch_colsum(st, ws + w.d_q2, E, B * Ta, E, G(XP_A2V_IN_B));
+  if (!bias_fused) launch_colsum(st, ws + w.d_q2, E, B * Ta, E, G(XP_A2V_IN_B));
   linear_bwd_dx(st, ws + w.d_q2, E, P(XP_A2V_IN_W), ws + w.d_a0, B * Ta, E, E, true);
   linear_bwd_dw<float>(st, ws + w.d_kv2, 2 * E, ws + w.v1, E, G(XP_A2V_IN_W) + (int64_t)E * E, B * T, 2 * E, E);
-  launch_colsum(st, ws + w.d_kv2, 2 * E, B * T, 2 * E, G(XP_A2V_IN_B) + E);
+  if (!bias_fused) launch_colsum(st, ws + w.d_kv2, 2 * E, B * T, 2 * E, G(XP_A2V_IN_B) + E);
   linear_bwd_dx(st, ws + w.d_kv2, 2 * E, P(XP_A2V_IN_W) + (int64_t)E * E, ws + w.d_v1, B * T, 2 * E, E, false);
   XF_LAUNCH_CHECK();
   // ---- v_norm backward (fusion.py:395) ----
-  launch_ln_bwd(st, ln_grid, ws + w.d_v1, ws + w.d_pooled, 2 * E, 1.f / (float)T, ws + w.s1, ws + w.mean1, ws + w.rstd1, P(XP_VN_W),
-                ws + w.dp1, ws + w.d_v0, ws + w.d_br1, G(XP_VN_W), G(XP_VN_B), B * T, T, E);
+  ob_fused = launch_ln_bwd(st, ln_grid, ws + w.d_v1, ws + w.d_pooled, 2 * E, 1.f / (float)T, ws + w.s1, ws + w.mean1, ws + w.rstd1,
+                           P(XP_VN_W), ws + w.dp1, ws + w.d_v0, ws + w.d_br1, G(XP_VN_W), G(XP_VN_B), G(XP_V2A_OUT_B), B * T, T, E);
   linear_bwd_dw<float>(st, ws + w.d_br1, E, ws + w.o1, E, G(XP_V2A_OUT_W), B * T, E, E);
-  launch_colsum(st, ws + w.d_br1, E, B * T, E, G(XP_V2A_OUT_B));
+  if (!ob_fused) launch_colsum(st, ws + w.d_br1, E, B * T, E, G(XP_V2A_OUT_B));
   linear_bwd_dx(st, ws + w.d_br1, E, P(XP_V2A_OUT_W), ws + w.d_o1, B * T, E, E, false);
   XF_LAUNCH_CHECK();
   {
@@ -751,13 +786,14 @@ static int backward_f32_impl(const xattn_config& c, const float* params, const T
     aa.dbias_scale = c.use_prior ? G(XP_BIAS_SCALE) : nullptr;
     aa.L = T; aa.S = Ta; aa.E = E; aa.H = H; aa.scale = scale; aa.p_drop = p_attn; aa.seed = c.seed; aa.offset = c.offset;
     aa.rng_stream = RS_ATTN1;
-    XF_TRY(launch_attn_bwd(st, aa, B));
+    aa.dbq = G(XP_V2A_IN_B); aa.dbkv = G(XP_V2A_IN_B) + E;
+    XF_TRY(launch_attn_bwd(st, aa, B, &bias_fused));
   }
   linear_bwd_dw<float>(st, ws + w.d_q1, E, ws + w.v0, E, G(XP_V2A_IN_W), B * T, E, E);
-  launch_colsum(st, ws + w.d_q1, E, B * T, E, G(XP_V2A_IN_B));
+  if (!bias_fused) launch_colsum(st, ws + w.d_q1, E, B * T, E, G(XP_V2A_IN_B));
   linear_bwd_dx(st, ws + w.d_q1, E, P(XP_V2A_IN_W), ws + w.d_v0, B * T, E, E, true);
   linear_bwd_dw<float>(st, ws + w.d_kv1, 2 * E, ws + w.a0, E, G(XP_V2A_IN_W) + (int64_t)E * E, B * Ta, 2 * E, E);
-  launch_colsum(st, ws + w.d_kv1, 2 * E, B * Ta, 2 * E, G(XP_V2A_IN_B) + E);
+  if (!bias_fused) launch_colsum(st, ws + w.d_kv1, 2 * E, B * Ta, 2 * E, G(XP_V2A_IN_B) + E);
   linear_bwd_dx(st, ws + w.d_kv1, 2 * E, P(XP_V2A_IN_W) + (int64_t)E * E, ws + w.d_a0, B * Ta, 2 * E, E, true);
   XF_LAUNCH_CHECK();
 

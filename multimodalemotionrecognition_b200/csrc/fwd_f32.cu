@@ -331,11 +331,25 @@ __global__ void __launch_bounds__(256) pool_head_fwd_kernel(HeadArgs a) {
   __shared__ float s_gate;
   const float* v1 = a.v1 + (int64_t)b * T * E;
   const float* a1 = a.a1 + (int64_t)b * Ta * E;
-  clip_mean(v1, T, E, pooled, scratch, tid, blockDim.x);
-  clip_mean(a1, Ta, E, pooled + E, scratch, tid, blockDim.x);
-  if (a.pooled)
-    for (int e = tid; e < 2 * E; e += blockDim.x) a.pooled[(int64_t)b * 2 * E + e] = pooled[e];
-  for (int h = warp; h < HW; h += nw) {
+  // stage 0: everything in this launch.  Large batches run it as three launches instead — stage 1: the means only (-> a.pooled);
+  // the hidden Linear + ReLU as a GEMM over the batch (tensor cores under PREC_TF32; per clip it re-read W0 from L2 and spent
+  // five shuffles per output); stage 2: dropout on a.hhid (holding relu(pre-activation)) and everything after it.
+  if (a.stage == 2) {
+    for (int e = tid; e < 2 * E; e += blockDim.x) pooled[e] = a.pooled[(int64_t)b * 2 * E + e];
+    for (int h = tid; h < HW; h += blockDim.x) {
+      float r = a.hhid[(int64_t)b * HW + h];
+      r *= drop_factor(a.p_drop, a.seed, a.offset, RS_HEAD, (uint64_t)b * HW + h);
+      hid[h] = r;
+      a.hhid[(int64_t)b * HW + h] = r;
+    }
+  } else {
+    clip_mean(v1, T, E, pooled, scratch, tid, blockDim.x);
+    clip_mean(a1, Ta, E, pooled + E, scratch, tid, blockDim.x);
+    if (a.pooled)
+      for (int e = tid; e < 2 * E; e += blockDim.x) a.pooled[(int64_t)b * 2 * E + e] = pooled[e];
+    if (a.stage == 1) return;
+  }
+  for (int h = warp; a.stage == 0 && h < HW; h += nw) {
     const float* w = a.w0 + (int64_t)h * 2 * E;
     float s = 0.f;
     for (int k = lane; k < 2 * E; k += 32) s = fmaf(w[k], pooled[k], s);
@@ -615,7 +629,13 @@ static int forward_f32_impl(const xattn_config& c, const float* params, const TI
     ha.HW = ha.gated ? E : c.common_dim;
     ha.p_drop = p_head; ha.seed = c.seed; ha.offset = c.offset;
     const size_t smem = sizeof(float) * (3 * E + ha.HW + 8 * E);
+    // always the three-launch form (a clip's logits must not depend on the batch it arrives in — shards are compared bit for bit)
+    ha.stage = 1;
     pool_head_fwd_kernel<<<B, 256, smem, st>>>(ha);
+    linear_fwd<float>(st, ws + w.pooled, ha.w0, ha.b0, ws + w.hhid, B, ha.HW, 2 * E, true);
+    ha.stage = 2;
+    pool_head_fwd_kernel<<<B, 256, smem, st>>>(ha);
+    count_launch();
     count_launch();
     XF_LAUNCH_CHECK();
   }

@@ -38,6 +38,8 @@ struct AttnBwdArgs {
   float* dqs;            // [B,L]  (nullptr without prior)
   float* dks;            // [B,S]
   float* dbias_scale;    // scalar, atomically accumulated
+  float* dbq = nullptr;  // [E]  += column sums of dq  (in_proj bias gradient; attn_bwd32_kernel only, see launch_attn_bwd)
+  float* dbkv = nullptr; // [2E] += column sums of dkv
   int L, S, E, H;
   float scale, p_drop;
   uint64_t seed, offset;
@@ -50,6 +52,7 @@ struct HeadArgs {
   float *pooled, *hhid, *gate, *fusedg; // saved: [B,2E], [B,HW], [B], [B,E]
   float* logits;
   int T, Ta, E, HW, C, gated;
+  int stage = 0;                        // pool_head_fwd_kernel: 0 = whole head, 1 = temporal means only, 2 = from a.pooled / a.hhid
   float p_drop;
   uint64_t seed, offset;
 };
