@@ -363,7 +363,7 @@ __global__ void __launch_bounds__(256) attn_bwd_kernel(AttnBwdArgs a) {
 
 // The same for dh == 32 with register-tiled products (smem_tile.cuh).  [L][SP] matrices (SP = S rounded up to 4) come first in
 // shared memory so their rows stay 16-byte aligned.
-__global__ void __launch_bounds__(256) attn_bwd32_kernel(AttnBwdArgs a) {
+__global__ void __launch_bounds__(256, 2) attn_bwd32_kernel(AttnBwdArgs a) {
   extern __shared__ __align__(16) float sm[];
   __shared__ float bred[8][96];   // per-warp column sums of dq | dk | dv of the current head
   const int b = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nw = blockDim.x >> 5;
@@ -391,12 +391,23 @@ __global__ void __launch_bounds__(256) attn_bwd32_kernel(AttnBwdArgs a) {
     Pds[i] = 0.f;   // (padding columns stay zero: the dQ product reads them)
     dSs[i] = 0.f;
   }
+  const bool p_vec = (S & 3) == 0 && (reinterpret_cast<uintptr_t>(a.P) & 15) == 0;   // SP == S: Ps has the layout of P itself
   for (int h = 0; h < H; ++h) {
     stage_rows32(Qs, q + h * dh, L, E, a.scale, tid, blockDim.x);
     stage_rows32(dOs, dO + h * dh, L, E, 1.f, tid, blockDim.x);
     stage_rows32x2(Ks, Vs, kv + h * dh, E, S, 2 * E, tid, blockDim.x);
-    __syncthreads();
     const int64_t hbase = ((int64_t)b * H + h) * L * S;
+    // P of this head -> Ps with coalesced loads (in the a2v direction the tile epilogue below would read it with a 64-byte stride)
+    if (p_vec) {
+      const float4* src = reinterpret_cast<const float4*>(a.P + hbase);
+      float4* dst = reinterpret_cast<float4*>(Ps);
+#pragma unroll 4
+      for (int i = tid; i < (L * S) >> 2; i += blockDim.x) dst[i] = __ldg(src + i);
+    } else {
+      for (int l = warp; l < L; l += nw)
+        for (int s2 = lane; s2 < S; s2 += 32) Ps[l * SP + s2] = a.P[hbase + (int64_t)l * S + s2];
+    }
+    __syncthreads();
     for (int t = warp; t < ntile; t += nw) {   // dPd = dO · V^T
       const int a0 = (t % tiles_a) * 2, b0 = (t / tiles_a) * 160;
       float acc[2][5];
@@ -409,15 +420,35 @@ __global__ void __launch_bounds__(256) attn_bwd32_kernel(AttnBwdArgs a) {
           if (ar < AR && br < BR) {
             const int l = lanes_on_s ? ar : br, s2 = lanes_on_s ? br : ar;
             const int64_t pi = hbase + (int64_t)l * S + s2;
-            const float p = a.P[pi];
+            const float p = Ps[l * SP + s2];
             const float f = a.p_drop > 0.f ? drop_factor(a.p_drop, a.seed, a.offset, a.rng_stream, (uint64_t)pi) : 1.f;
-            Ps[l * SP + s2] = p;
             Pds[l * SP + s2] = p * f;
             dSs[l * SP + s2] = acc[i][j] * f;   // dP until the row dot is known
           }
         }
     }
     __syncthreads();
+    if (p_vec && S <= 32) {   // short rows (a2v: 16 scores): lpr lanes per row with four scores each, 32/lpr rows per warp
+      const int lpr = S <= 16 ? 4 : 8, rpw = 32 / lpr, sub = lane / lpr, sl = lane - sub * lpr;
+      const bool act = 4 * sl < S;
+      for (int l0 = warp * rpw; l0 < L; l0 += nw * rpw) {
+        const int l = min(l0 + sub, L - 1);
+        const bool ok = act && l0 + sub < L;
+        const int o = l * SP + 4 * sl;
+        const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
+        const float4 pv = act ? *reinterpret_cast<const float4*>(Ps + o) : z;
+        float4 dv = act ? *reinterpret_cast<const float4*>(dSs + o) : z;
+        float rowdot = fmaf(dv.x, pv.x, fmaf(dv.y, pv.y, fmaf(dv.z, pv.z, dv.w * pv.w)));
+        for (int w2 = lpr >> 1; w2 > 0; w2 >>= 1) rowdot += __shfl_xor_sync(0xffffffffu, rowdot, w2);
+        if (ok) {
+          dv.x = pv.x * (dv.x - rowdot); dv.y = pv.y * (dv.y - rowdot); dv.z = pv.z * (dv.z - rowdot); dv.w = pv.w * (dv.w - rowdot);
+          *reinterpret_cast<float4*>(dSs + o) = dv;
+          float4 db = *reinterpret_cast<float4*>(dBs + o);
+          db.x += dv.x; db.y += dv.y; db.z += dv.z; db.w += dv.w;
+          *reinterpret_cast<float4*>(dBs + o) = db;
+        }
+      }
+    } else
     for (int l = warp; l < L; l += nw) {   // dS = P ⊙ (dP - rowsum(dP ⊙ P))
       float rowdot = 0.f;
       for (int s2 = lane; s2 < S; s2 += 32) rowdot = fmaf(dSs[l * SP + s2], Ps[l * SP + s2], rowdot);

@@ -159,7 +159,7 @@ __global__ void __launch_bounds__(256) attn_fwd_kernel(AttnArgs a) {
 
 // The same for dh == 32 (one lane per head column) with register-tiled products (smem_tile.cuh): scores of the whole head go to
 // shared memory as [L][SP] (SP = S rounded up to 4, padding zeroed), one warp normalises a row, then O = Pd·V.
-__global__ void __launch_bounds__(256) attn_fwd32_kernel(AttnArgs a) {
+__global__ void __launch_bounds__(256, 4) attn_fwd32_kernel(AttnArgs a) {
   extern __shared__ __align__(16) float sm[];
   const int b = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nw = blockDim.x >> 5;
   const int L = a.L, S = a.S, E = a.E, H = a.H, SP = (S + 3) & ~3;
