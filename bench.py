@@ -219,6 +219,7 @@ def run_b200_arm(args) -> None:
     import torch.distributed as dist
 
     from multimodalemotionrecognition_b200 import XAttnFusionHead, _lib
+    from multimodalemotionrecognition_b200.hostmem import bind_to_device_numa_node
     from multimodalemotionrecognition_b200.training import Stage1Trainer
 
     rank = int(os.environ.get("RANK", "0"))
@@ -230,6 +231,8 @@ def run_b200_arm(args) -> None:
         args.gpus = world
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
+    # one rank per GPU: keep the rank (and the pinned e2e buffers it allocates) on the GPU's own socket
+    numa_node = bind_to_device_numa_node(local) if world > 1 else None
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
     peaks = load_peaks()
@@ -360,7 +363,8 @@ def run_b200_arm(args) -> None:
             dist.all_reduce(dt, op=dist.ReduceOp.MAX)
         e2e = {"value": B * world * e2e_steps / float(dt.item()), "unit": "clips/s",
                "h2d_bytes_per_step": (hv.numel() + ha.numel()) * 2 * world, "d2h_bytes_per_step": out.numel() * 4 * world,
-               "steps": e2e_steps, "api": "XAttnFusionHead.predict_host (pinned host in, host logits out)"}
+               "steps": e2e_steps, "api": "XAttnFusionHead.predict_host (pinned host in, host logits out)",
+               "numa_node_rank0": numa_node}
 
     # ---- CPU baseline (rank 0, N=1 only) ----------------------------------------------------------------------------
     cpu = None
