@@ -111,3 +111,30 @@ def test_frozen_embedding_cache_runs_backbones_once_per_sample():
     assert calls == {"video": 12, "audio": 4} and (cache.hits, cache.misses) == (2, 4)   # only sample 2 was new
     assert torch.equal(a2[0], a[1]) and torch.equal(v2[2], v[0])
     assert cache.missing(torch.arange(9)).tolist() == [True, False, False, True, False, True, True, False, True]
+
+
+def test_hostmem_numa_binding_against_a_fake_sysfs(tmp_path, monkeypatch):
+    """hostmem: cpulist parsing, GPU -> NUMA node lookup and the affinity call, against a fabricated sysfs tree."""
+    import os
+
+    from multimodalemotionrecognition_b200 import hostmem
+
+    assert hostmem._parse_cpulist("0-3,8,10-11\n") == {0, 1, 2, 3, 8, 10, 11}
+    assert hostmem._parse_cpulist("") == set()
+    monkeypatch.setattr(hostmem, "pci_address", lambda device: "0000:1b:00.0")
+    dev = tmp_path / "bus" / "pci" / "devices" / "0000:1b:00.0"
+    dev.mkdir(parents=True)
+    (dev / "numa_node").write_text("-1\n")
+    assert hostmem.numa_node_of(0, str(tmp_path)) is None            # virtualised box: nothing to bind to
+    assert hostmem.bind_to_device_numa_node(0, str(tmp_path)) is None
+    (dev / "numa_node").write_text("1\n")
+    node = tmp_path / "devices" / "system" / "node" / "node1"
+    node.mkdir(parents=True)
+    mine = sorted(os.sched_getaffinity(0))
+    (node / "cpulist").write_text(f"{mine[0]}\n")
+    calls = []
+    monkeypatch.setattr(os, "sched_setaffinity", lambda pid, cpus: calls.append((pid, set(cpus))))
+    assert hostmem.bind_to_device_numa_node(0, str(tmp_path)) == 1
+    assert calls == [(0, {mine[0]})]
+    (node / "cpulist").write_text("100000\n")                         # no CPU of that node is ours: leave the process alone
+    assert hostmem.bind_to_device_numa_node(0, str(tmp_path)) is None
