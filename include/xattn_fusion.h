@@ -26,7 +26,7 @@
 extern "C" {
 #endif
 
-#define XATTN_ABI_VERSION 11
+#define XATTN_ABI_VERSION 12
 
 #if defined(__GNUC__)
 #define XATTN_API __attribute__((visibility("default")))
@@ -230,6 +230,11 @@ XATTN_API int flat_head_workspace_bytes(const flat_head_config* cfg, int64_t* by
  * fusion.py:413-435 (+ :137-139).  Eval mode (ModalityDropout / Dropout identity). */
 XATTN_API int flat_head_forward(const flat_head_config* cfg, const float* params, const void* video_emb, const void* audio_emb,
                       float* logits, void* workspace, int64_t workspace_bytes, void* stream);
+
+/* Serving epilogue (optimized_runtime.py:99-108 softmax(dim=1); inference_worker.py:136-143 row.argmax() and the probability at
+ * it) in one launch: probs[B,C] = softmax(logits) (may alias logits; NULL to skip), top1[B] = first maximal class, top1_prob[B]
+ * = its probability (either may be NULL). */
+XATTN_API int xattn_softmax_top1(const float* logits, int32_t B, int32_t C, float* probs, int32_t* top1, float* top1_prob, void* stream);
 
 /* Mel front end (fusion.py:379-384: audio_time_conv = Conv1d(n_mels -> a_dim, kernel 3, padding 1) over time, then permute to
  * [B, Ta, a_dim]) for audio encoders without encode_sequence().  mel [B, n_mels, Ta] -> unfolded [B, Ta, 3*n_mels] (same

@@ -125,6 +125,26 @@ class _XAttnFunction(torch.autograd.Function):
         return (None, None, None, *grads)
 
 
+def softmax_top1(logits: torch.Tensor, probs: Optional[torch.Tensor] = None, top1: Optional[torch.Tensor] = None,
+                 top1_prob: Optional[torch.Tensor] = None):
+    """``softmax(dim=1)`` (optimized_runtime.py:107), the row argmax and the probability at it (inference_worker.py:137-142)
+    in one launch (``xattn_softmax_top1``).  ``logits`` [B,C] fp32 CUDA; outputs are allocated unless given (``probs`` may be
+    ``logits`` itself).  Returns ``(probs, top1 int32 [B], top1_prob [B])``."""
+    if not logits.is_cuda or logits.dtype != torch.float32 or logits.ndim != 2 or not logits.is_contiguous():
+        raise ValueError("softmax_top1 expects a contiguous fp32 CUDA tensor [B,C]")
+    B, C_ = logits.shape
+    if probs is None:
+        probs = torch.empty_like(logits)
+    if top1 is None:
+        top1 = torch.empty((B,), dtype=torch.int32, device=logits.device)
+    if top1_prob is None:
+        top1_prob = torch.empty((B,), dtype=torch.float32, device=logits.device)
+    with torch.cuda.device(logits.device):
+        _lib.check(_lib.load().xattn_softmax_top1(_ptr(logits), B, C_, _ptr(probs), _ptr(top1), _ptr(top1_prob),
+                                                  _stream_ptr(logits.device)))
+    return probs, top1, top1_prob
+
+
 class GraphedForward:
     """One CUDA graph of the bf16 forward at a fixed batch size ("CUDA-graph per batch size").
 
@@ -151,7 +171,10 @@ class GraphedForward:
             self.graph = torch.cuda.CUDAGraph()
             with torch.cuda.graph(self.graph):
                 head._launch_forward(self.video, self.audio, save=False, training=False, out=self.logits)
-                self.probs = torch.softmax(self.logits, dim=1)
+                self.probs = torch.empty_like(self.logits)
+                self.top1 = torch.empty((B,), dtype=torch.int32, device=device)
+                self.top1_prob = torch.empty((B,), dtype=torch.float32, device=device)
+                softmax_top1(self.logits, self.probs, self.top1, self.top1_prob)
 
     def __call__(self) -> torch.Tensor:
         self.graph.replay()
@@ -454,12 +477,15 @@ class XAttnKernelsMixin:
 
     @torch.no_grad()
     def predict_host(self, video_host: torch.Tensor, audio_host: torch.Tensor, chunk: int = 1024,
-                     probs: bool = False, graph_max: int = 256) -> torch.Tensor:
+                     probs: bool = False, graph_max: int = 256, top1: bool = False):
         """Batch path with HOST buffers, mirroring ``TorchModelRunner.predict_probs`` (``optimized_runtime.py:99-108``:
         ``.to(device)`` -> model -> ``softmax`` -> ``.cpu()``) and the worker's ``torch.stack(...).to(device)``
         (``inference_worker.py:131-134``).  The host batch (pinned memory for full PCIe rate) is cut into ``chunk``-clip
         pieces that are copied on a side stream into two device staging slots while the previous piece is computed;
-        returns host logits (or probabilities) ``[B,C]`` after synchronising on the final device->host copy."""
+        returns host logits (or probabilities) ``[B,C]`` after synchronising on the final device->host copy.
+        ``top1=True`` returns ``(probs [B,C], top1 int32 [B], top1_prob [B])`` on the host — the three things the worker
+        puts into its result (``inference_worker.py:136-143``), computed on the device in the same launch as the softmax."""
+        probs = probs or top1
         if video_host.is_cuda or audio_host.is_cuda:
             raise ValueError("predict_host takes host tensors; call forward() for device tensors")
         if video_host.ndim != 3 or audio_host.ndim != 3 or video_host.shape[0] != audio_host.shape[0]:
@@ -475,6 +501,10 @@ class XAttnKernelsMixin:
         if out_buf is None or out_buf.shape[0] < B or out_buf.shape[1] != self.num_classes:
             out_buf = torch.empty((max(B, 1), self.num_classes), dtype=torch.float32).pin_memory()
             self._host_out = out_buf
+        t1_buf = getattr(self, "_host_top1", None)
+        if top1 and (t1_buf is None or t1_buf[0].shape[0] < B):
+            t1_buf = (torch.empty((max(B, 1),), dtype=torch.int32).pin_memory(), torch.empty((max(B, 1),), dtype=torch.float32).pin_memory())
+            self._host_top1 = t1_buf
         if 0 < B <= min(graph_max, chunk) and video_host.dtype == torch.bfloat16 and self.precision in ("auto", "bf16") \
                 and self._bf16_supported(T_, Ta_):
             # worker-sized batches (inference_worker.py:33-34) are launch-bound: H2D, one graph launch, D2H
@@ -485,8 +515,11 @@ class XAttnKernelsMixin:
                 g()
                 host = out_buf[:B]
                 host.copy_(g.probs if probs else g.logits, non_blocking=True)
+                if top1:
+                    t1_buf[0][:B].copy_(g.top1, non_blocking=True)
+                    t1_buf[1][:B].copy_(g.top1_prob, non_blocking=True)
                 torch.cuda.current_stream(dev).synchronize()
-            return host
+            return (host, t1_buf[0][:B], t1_buf[1][:B]) if top1 else host
         key = (dev, chunk, T_, Dv, Ta_, Da, video_host.dtype)
         pipe = getattr(self, "_host_pipe", None)
         if pipe is None or pipe["key"] != key:
@@ -514,11 +547,14 @@ class XAttnKernelsMixin:
                                      out=logits[s:e])
                 pipe["done"][slot].record(cur)
             if probs:
-                logits = torch.softmax(logits, dim=1)
+                _, t1, t1p = softmax_top1(logits, logits)
             host = out_buf[:B]
             host.copy_(logits, non_blocking=True)
+            if top1:
+                t1_buf[0][:B].copy_(t1, non_blocking=True)
+                t1_buf[1][:B].copy_(t1p, non_blocking=True)
             cur.synchronize()
-        return host
+        return (host, t1_buf[0][:B], t1_buf[1][:B]) if top1 else host
 
     def mel_unfold(self, mel: torch.Tensor) -> torch.Tensor:
         """mel [B, 1, n_mels, Ta] or [B, n_mels, Ta] -> time-unfolded rows [B, Ta, 3*n_mels] (csrc/mel_frontend.cu), the
@@ -591,7 +627,7 @@ class XAttnFusionHead(XAttnKernelsMixin, nn.Module):
     @torch.no_grad()
     def predict_probs(self, video_emb: torch.Tensor, audio_emb: torch.Tensor) -> torch.Tensor:
         """Batch-path helper mirroring ``TorchModelRunner.predict_probs`` (``optimized_runtime.py:99-108``)."""
-        return torch.softmax(self.forward(video_emb, audio_emb), dim=1)
+        return softmax_top1(self.forward(video_emb, audio_emb).contiguous())[0]
 
 
 class ClipStyleAlignment(nn.Module):

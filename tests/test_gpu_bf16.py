@@ -228,3 +228,34 @@ def test_graphed_forward_and_small_batch_host_path(cuda_device, B):
         host2 = m.predict_host(xv.pin_memory(), xa.pin_memory())
         assert torch.equal(host2, eager2.cpu())
         assert m.graphed_forward(B) is not gf
+
+
+def test_softmax_top1_epilogue_and_predict_host_top1(cuda_device):
+    """Serving epilogue: xattn_softmax_top1 against torch.softmax / argmax (first maximum on ties), and
+    predict_host(top1=True) — probabilities, top-1 class and its probability on the host — on the CUDA-graph path (B=32) and
+    the chunked path (B=600), as inference_worker.py:136-143 derives them from predict_probs."""
+    from multimodalemotionrecognition_b200 import softmax_top1
+
+    g = torch.Generator(device=cuda_device).manual_seed(5)
+    x = torch.randn(1000, 8, device=cuda_device, generator=g) * 4
+    x[3] = 1.5                      # all equal: first index wins, as torch.argmax
+    x[4, 2] = x[4, 6] = 9.0
+    probs, top1, top1p = softmax_top1(x)
+    ref = torch.softmax(x, dim=1)
+    assert (probs - ref).abs().max() < 1e-6
+    assert torch.equal(top1.long(), ref.argmax(1)) and int(top1[3]) == 0 and int(top1[4]) == 2
+    assert (top1p - ref.max(1).values).abs().max() < 1e-6
+    y = x.clone()
+    softmax_top1(y, y)              # in place
+    assert torch.equal(y, probs)
+    m = make_head("concat", True, seed=0, precision="bf16").to(cuda_device).eval()
+    for B in (32, 600):
+        xv = torch.randn(B, 16, 512, generator=torch.Generator().manual_seed(B)).bfloat16().pin_memory()
+        xa = torch.randn(B, 149, 768, generator=torch.Generator().manual_seed(B + 1)).bfloat16().pin_memory()
+        logits = m.predict_host(xv, xa).clone()
+        p, t1, t1p = m.predict_host(xv, xa, top1=True)
+        assert not p.is_cuda and t1.dtype == torch.int32 and p.shape == (B, 8)
+        refp = torch.softmax(logits, dim=1)
+        assert (p - refp).abs().max() < 1e-6
+        assert torch.equal(t1.long(), refp.argmax(1))
+        assert (t1p - refp.max(1).values).abs().max() < 1e-6
