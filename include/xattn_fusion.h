@@ -26,7 +26,7 @@
 extern "C" {
 #endif
 
-#define XATTN_ABI_VERSION 12
+#define XATTN_ABI_VERSION 13
 
 #if defined(__GNUC__)
 #define XATTN_API __attribute__((visibility("default")))
@@ -76,12 +76,13 @@ typedef struct xattn_config {
   int32_t save_for_backward; /* 1: keep activations in the workspace even in eval mode
                                 (gradient parity in eval mode)            */
   int32_t pool_mode;    /* XATTN_POOL_MEAN (temporal.py:108-109) | XATTN_POOL_ATTN (TemporalAttentionPooling,
-                           temporal.py:9-26: LN -> Linear -> GELU -> Linear -> softmax over time -> weighted sum;
-                           fp32 family, forward only)                                 */
+                           temporal.py:9-26: LN -> Linear -> GELU -> Dropout -> Linear -> softmax over time -> weighted
+                           sum; fp32 / tf32 family, forward and backward)             */
   float p_attn;         /* attention dropout            (fusion.py:277,280)          */
   float p_path;         /* stochastic depth             (fusion.py:282-283)          */
   float p_head;         /* head Dropout(0.2)            (fusion.py:315,322)          */
   float p_prior;        /* prior_net Dropout            (fusion.py:161)              */
+  float p_pool;         /* Dropout inside the attention pooler's score MLP (temporal.py:19; temporal_dropout) */
   uint64_t seed;        /* Philox seed for the dropouts                               */
   uint64_t offset;      /* Philox offset (advance per step)                           */
 } xattn_config;

@@ -12,7 +12,7 @@ from pathlib import Path
 
 LIB_NAME = "libxattn_fusion.so"
 LIB_PATH = Path(__file__).resolve().parent / LIB_NAME
-ABI_VERSION = 12
+ABI_VERSION = 13
 
 # xattn_status
 OK, ERR_SHAPE, ERR_DTYPE, ERR_ALIGN, ERR_ARCH, ERR_CUDA, ERR_WORKSPACE, ERR_NULL = range(8)
@@ -68,7 +68,7 @@ class XAttnConfig(C.Structure):
     _fields_ = [(n, C.c_int32) for n in (
         "B", "T", "Ta", "Dv", "Da", "E", "H", "prior_dim", "prior_hidden", "common_dim", "C", "head_kind",
         "use_prior", "io_dtype", "precision", "training", "save_for_backward", "pool_mode")] + [
-        ("p_attn", C.c_float), ("p_path", C.c_float), ("p_head", C.c_float), ("p_prior", C.c_float),
+        ("p_attn", C.c_float), ("p_path", C.c_float), ("p_head", C.c_float), ("p_prior", C.c_float), ("p_pool", C.c_float),
         ("seed", C.c_uint64), ("offset", C.c_uint64)]
 
 

@@ -727,6 +727,208 @@ __global__ void __launch_bounds__(256) prior_bwd_kernel(PriorBwdArgs a) {
   }
 }
 
+// ---- TemporalAttentionPooling backward (temporal.py:9-26) ---------------------------------------------------------
+// out = Σ_l a_l x_l, a = softmax_l(s), s_l = w2·(GELU(h_l) ⊙ m_l) + b2, h_l = W1 y_l + b1, y_l = LN(x_l)·γ + β.  Nothing but x was
+// saved: a first pass over the clip's tokens recomputes the scores and d_a_l = <d_out, x_l>, the softmax backward gives d_s, a
+// second pass recomputes y_l, h_l and pushes d_s_l through the score MLP and the LayerNorm:
+//   d_x_l = a_l·d_out + LN'(W1ᵀ d_h_l ⊙ γ),  d_h_l = d_s_l·w2 ⊙ m_l ⊙ GELU'(h_l).
+// dγ, dβ, dw2, db2 are accumulated here (registers -> shared memory -> one atomic per CTA and entry); y_l and d_h_l are written out
+// ([B·L,E], [B·L,H2]) so that dW1 = d_hᵀ·y and db1 = colsum(d_h) run as the batch GEMM / column sum of the Linear helpers.
+// One CTA per clip, one warp per token; W1 sits in shared memory twice ([e][j] for h, [j][e] for W1ᵀ d_h — both conflict-free).
+struct AttnPoolBwdArgs {
+  const float *x, *ln_w, *ln_b, *w1, *b1, *w2, *b2;
+  const float* d_out;      // [B, ld_out] gradient of the pooled vector
+  int64_t ld_out;
+  float* d_x;              // [B,L,E]
+  int accumulate;          // d_x += (else =)
+  float *y_out, *dh_out;   // [B·L,E], [B·L,H2]
+  float *g_ln_w, *g_ln_b, *g_w2, *g_b2;
+  int L, E;
+  float p_drop;
+  uint64_t seed, offset;
+  uint32_t rng_stream;
+};
+__global__ void __launch_bounds__(256) attn_pool_bwd_kernel(AttnPoolBwdArgs a) {
+  extern __shared__ float sm[];
+  const int b = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nw = blockDim.x >> 5;
+  const int L = a.L, E = a.E, H2 = E / 2 > 0 ? E / 2 : 1;
+  float* w1t = sm;                    // [E][H2]
+  float* w1s = w1t + E * H2;          // [H2][E]
+  float* yrow = w1s + E * H2;         // [nw][E]   y_l, then d_x̂_l
+  float* xh = yrow + nw * E;          // [nw][E]   x̂_l
+  float* dhrow = xh + nw * E;         // [nw][H2]
+  float* score = dhrow + nw * H2;     // [L]  s_l, then a_l
+  float* da = score + L;              // [L]  <d_out, x_l>, then d_s_l
+  float* red = da + L;                // [nw][2E + H2 + 1] partial dγ | dβ | dw2 | db2
+  __shared__ float s_stat[2];
+  for (int i = tid; i < E * H2; i += blockDim.x) {
+    const int j = i / E, e = i - j * E;
+    const float w = a.w1[i];
+    w1t[e * H2 + j] = w;
+    w1s[i] = w;
+  }
+  __syncthreads();
+  const float* xb = a.x + (int64_t)b * L * E;
+  const float* dout = a.d_out + (int64_t)b * a.ld_out;
+  float* y = yrow + warp * E;
+  float* xhat = xh + warp * E;
+  float* dh = dhrow + warp * H2;
+  // recompute of one token row into y / xhat (returns rstd); h_j for j = lane + 32k is then produced by the caller's loop
+  auto ln_row = [&](int l) -> float {
+    const float* xr = xb + (int64_t)l * E;
+    float sum = 0.f;
+    for (int e = lane; e < E; e += 32) sum += xr[e];
+    const float mu = warp_sum(sum) / (float)E;
+    float var = 0.f;
+    for (int e = lane; e < E; e += 32) {
+      const float d = xr[e] - mu;
+      var = fmaf(d, d, var);
+    }
+    const float rstd = rsqrtf(warp_sum(var) / (float)E + 1e-5f);
+    for (int e = lane; e < E; e += 32) {
+      const float xn = (xr[e] - mu) * rstd;
+      xhat[e] = xn;
+      y[e] = xn * a.ln_w[e] + a.ln_b[e];
+    }
+    __syncwarp();
+    return rstd;
+  };
+  for (int l = warp; l < L; l += nw) {   // pass 1: scores and d_a
+    ln_row(l);
+    float sc = 0.f;
+    for (int j = lane; j < H2; j += 32) {
+      float h = a.b1[j];
+      for (int e = 0; e < E; ++e) h = fmaf(w1t[e * H2 + j], y[e], h);
+      float g = 0.5f * h * (1.f + erff(h * 0.70710678118654752f));
+      if (a.p_drop > 0.f) g *= drop_factor(a.p_drop, a.seed, a.offset, a.rng_stream, ((uint64_t)b * L + l) * H2 + j);
+      sc = fmaf(a.w2[j], g, sc);
+    }
+    float d = 0.f;
+    for (int e = lane; e < E; e += 32) d = fmaf(dout[e], xb[(int64_t)l * E + e], d);
+    sc = warp_sum(sc);
+    d = warp_sum(d);
+    if (lane == 0) {
+      score[l] = sc + a.b2[0];
+      da[l] = d;
+    }
+    __syncwarp();
+  }
+  __syncthreads();
+  if (warp == 0) {   // softmax over time and its backward: d_s_l = a_l (d_a_l - Σ_m a_m d_a_m)
+    float mx = -INFINITY;
+    for (int l = lane; l < L; l += 32) mx = fmaxf(mx, score[l]);
+    mx = warp_max(mx);
+    float sum = 0.f;
+    for (int l = lane; l < L; l += 32) {
+      const float e = expf(score[l] - mx);
+      score[l] = e;
+      sum += e;
+    }
+    const float inv = 1.f / warp_sum(sum);
+    float dot = 0.f;
+    for (int l = lane; l < L; l += 32) {
+      const float p = score[l] * inv;
+      score[l] = p;
+      dot = fmaf(p, da[l], dot);
+    }
+    dot = warp_sum(dot);
+    for (int l = lane; l < L; l += 32) da[l] = score[l] * (da[l] - dot);
+  }
+  __syncthreads();
+  constexpr int MAXK = 16;   // E <= 512, H2 <= 256
+  float gg[MAXK], gb[MAXK], gw2[MAXK / 2];
+#pragma unroll
+  for (int k = 0; k < MAXK; ++k) gg[k] = gb[k] = 0.f;
+#pragma unroll
+  for (int k = 0; k < MAXK / 2; ++k) gw2[k] = 0.f;
+  float gb2 = 0.f;
+  for (int l = warp; l < L; l += nw) {   // pass 2
+    const float rstd = ln_row(l);
+    const float ds = da[l], al = score[l];
+    const int64_t row = (int64_t)b * L + l;
+#pragma unroll
+    for (int k = 0; k < MAXK / 2; ++k) {
+      const int j = lane + 32 * k;
+      if (j < H2) {
+        float h = a.b1[j];
+        for (int e = 0; e < E; ++e) h = fmaf(w1t[e * H2 + j], y[e], h);
+        const float cdf = 0.5f * (1.f + erff(h * 0.70710678118654752f));
+        const float pdf = 0.3989422804014327f * expf(-0.5f * h * h);
+        const float m = a.p_drop > 0.f ? drop_factor(a.p_drop, a.seed, a.offset, a.rng_stream, (uint64_t)row * H2 + j) : 1.f;
+        gw2[k] = fmaf(ds, h * cdf * m, gw2[k]);
+        const float d_h = ds * a.w2[j] * m * (cdf + h * pdf);
+        dh[j] = d_h;
+        a.dh_out[row * H2 + j] = d_h;
+      }
+    }
+    if (lane == 0) gb2 += ds;
+    __syncwarp();
+    float m1 = 0.f, m2 = 0.f;
+#pragma unroll
+    for (int k = 0; k < MAXK; ++k) {
+      const int e = lane + 32 * k;
+      if (e < E) {
+        float dy = 0.f;
+        for (int j = 0; j < H2; ++j) dy = fmaf(w1s[j * E + e], dh[j], dy);
+        a.y_out[row * E + e] = y[e];
+        gg[k] = fmaf(dy, xhat[e], gg[k]);
+        gb[k] += dy;
+        const float dxn = dy * a.ln_w[e];
+        m1 += dxn;
+        m2 = fmaf(dxn, xhat[e], m2);
+        y[e] = dxn;   // (each lane re-reads only its own entries below)
+      }
+    }
+    m1 = warp_sum(m1) / (float)E;
+    m2 = warp_sum(m2) / (float)E;
+#pragma unroll
+    for (int k = 0; k < MAXK; ++k) {
+      const int e = lane + 32 * k;
+      if (e < E) {
+        const float dx = fmaf(al, dout[e], rstd * (y[e] - m1 - xhat[e] * m2));
+        float* p = a.d_x + row * E + e;
+        *p = a.accumulate ? *p + dx : dx;
+      }
+    }
+    __syncwarp();
+  }
+  const int RW = 2 * E + H2 + 1;
+  float* r = red + warp * RW;
+#pragma unroll
+  for (int k = 0; k < MAXK; ++k) {
+    const int e = lane + 32 * k;
+    if (e < E) { r[e] = gg[k]; r[E + e] = gb[k]; }
+  }
+#pragma unroll
+  for (int k = 0; k < MAXK / 2; ++k) {
+    const int j = lane + 32 * k;
+    if (j < H2) r[2 * E + j] = gw2[k];
+  }
+  if (lane == 0) r[2 * E + H2] = gb2;
+  __syncthreads();
+  for (int i = tid; i < RW; i += blockDim.x) {
+    float t = 0.f;
+    for (int w = 0; w < nw; ++w) t += red[w * RW + i];
+    float* dst = i < E ? a.g_ln_w + i : i < 2 * E ? a.g_ln_b + (i - E) : i < 2 * E + H2 ? a.g_w2 + (i - 2 * E) : a.g_b2;
+    atomicAdd(dst, t);
+  }
+}
+static int launch_attn_pool_bwd(cudaStream_t st, const AttnPoolBwdArgs& a, int B) {
+  const int E = a.E, H2 = E / 2 > 0 ? E / 2 : 1, nw = 8;
+  if (E > 512) XF_FAIL(XATTN_ERR_SHAPE, "attention pooling backward supports d_model <= 512 (got %d)", E);
+  const size_t smem = sizeof(float) * (2 * (size_t)E * H2 + 2 * (size_t)nw * E + (size_t)nw * H2 + 2 * (size_t)a.L + (size_t)nw * (2 * E + H2 + 1));
+  if (smem > 200 * 1024) XF_FAIL(XATTN_ERR_SHAPE, "attention pooling backward needs %zu B of shared memory (> 200 KiB)", smem);
+  static size_t configured = 0;
+  if (smem > 48 * 1024 && smem > configured) {
+    XF_CUDA(cudaFuncSetAttribute(attn_pool_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    configured = smem;
+  }
+  attn_pool_bwd_kernel<<<B, 256, smem, st>>>(a);
+  count_launch();
+  XF_LAUNCH_CHECK();
+  return XATTN_OK;
+}
+
 // ---- orchestration ------------------------------------------------------------------------------------------------
 template <typename TIO>
 static int backward_f32_impl(const xattn_config& c, const float* params, const TIO* xv, const TIO* xa, const float* dlogits,
@@ -773,8 +975,29 @@ static int backward_f32_impl(const xattn_config& c, const float* params, const T
 
   const int ln_grid = 4 * num_sms();
   bool bias_fused = false;
+  const bool attn_pool = c.pool_mode == XATTN_POOL_ATTN;
+  const int H2 = E / 2 > 0 ? E / 2 : 1;
+  const float p_pool = train ? c.p_pool : 0.f;
+  // learned pooling (temporal.py:9-26): token gradients from attn_pool_bwd_kernel instead of d_pooled/L; its W1 / b1 gradients as
+  // a batch GEMM / column sum over the y and d_h rows it wrote into two buffers that are still free at that point
+  auto pool_bwd = [&](const float* x, const float* d_out, float* d_x, bool accumulate, float* y_buf, float* dh_buf, int L, int first_id,
+                      uint32_t stream) -> int {
+    AttnPoolBwdArgs pa;
+    pa.x = x; pa.ln_w = P(first_id); pa.ln_b = P(first_id + 1); pa.w1 = P(first_id + 2); pa.b1 = P(first_id + 3);
+    pa.w2 = P(first_id + 4); pa.b2 = P(first_id + 5);
+    pa.d_out = d_out; pa.ld_out = 2 * E; pa.d_x = d_x; pa.accumulate = accumulate ? 1 : 0; pa.y_out = y_buf; pa.dh_out = dh_buf;
+    pa.g_ln_w = G(first_id); pa.g_ln_b = G(first_id + 1); pa.g_w2 = G(first_id + 4); pa.g_b2 = G(first_id + 5);
+    pa.L = L; pa.E = E; pa.p_drop = p_pool; pa.seed = c.seed; pa.offset = c.offset; pa.rng_stream = stream;
+    XF_TRY(launch_attn_pool_bwd(st, pa, B));
+    linear_bwd_dw<float>(st, dh_buf, H2, y_buf, E, G(first_id + 2), B * L, H2, E);
+    launch_colsum(st, dh_buf, H2, B * L, H2, G(first_id + 3));
+    return XATTN_OK;
+  };
+  static_assert(XP_APOOL_B2 - XP_APOOL_LN_W == 5 && XP_VPOOL_B2 - XP_VPOOL_LN_W == 5, "pooler parameter ids are consecutive");
+  if (attn_pool) XF_TRY(pool_bwd(ws + w.a1, ws + w.d_pooled + E, ws + w.d_q2, false, ws + w.d_br2, ws + w.d_o2, Ta, XP_APOOL_LN_W, RS_POOLA));   // (d_q2 is free until the a2v attention backward)
   // ---- a_norm backward (fusion.py:399) + mean pool (temporal.py:108-109) ----
-  bool ob_fused = launch_ln_bwd(st, ln_grid, nullptr, ws + w.d_pooled + E, 2 * E, 1.f / (float)Ta, ws + w.s2, ws + w.mean2, ws + w.rstd2,
+  bool ob_fused = launch_ln_bwd(st, ln_grid, attn_pool ? ws + w.d_q2 : nullptr, attn_pool ? nullptr : ws + w.d_pooled + E, 2 * E,
+                                1.f / (float)Ta, ws + w.s2, ws + w.mean2, ws + w.rstd2,
                                 P(XP_AN_W), ws + w.dp2, ws + w.d_a0, ws + w.d_br2, G(XP_AN_W), G(XP_AN_B), G(XP_A2V_OUT_B), B * Ta, Ta, E);
   // a2v out_proj
   linear_bwd_dw<float>(st, ws + w.d_br2, E, ws + w.o2, E, G(XP_A2V_OUT_W), B * Ta, E, E);
@@ -801,8 +1024,9 @@ static int backward_f32_impl(const xattn_config& c, const float* params, const T
   if (!bias_fused) launch_colsum(st, ws + w.d_kv2, 2 * E, B * T, 2 * E, G(XP_A2V_IN_B) + E);
   linear_bwd_dx(st, ws + w.d_kv2, 2 * E, P(XP_A2V_IN_W) + (int64_t)E * E, ws + w.d_v1, B * T, 2 * E, E, false);
   XF_LAUNCH_CHECK();
+  if (attn_pool) XF_TRY(pool_bwd(ws + w.v1, ws + w.d_pooled, ws + w.d_v1, true, ws + w.d_br1, ws + w.d_o1, T, XP_VPOOL_LN_W, RS_POOLV));
   // ---- v_norm backward (fusion.py:395) ----
-  ob_fused = launch_ln_bwd(st, ln_grid, ws + w.d_v1, ws + w.d_pooled, 2 * E, 1.f / (float)T, ws + w.s1, ws + w.mean1, ws + w.rstd1,
+  ob_fused = launch_ln_bwd(st, ln_grid, ws + w.d_v1, attn_pool ? nullptr : ws + w.d_pooled, 2 * E, 1.f / (float)T, ws + w.s1, ws + w.mean1, ws + w.rstd1,
                            P(XP_VN_W), ws + w.dp1, ws + w.d_v0, ws + w.d_br1, G(XP_VN_W), G(XP_VN_B), G(XP_V2A_OUT_B), B * T, T, E);
   linear_bwd_dw<float>(st, ws + w.d_br1, E, ws + w.o1, E, G(XP_V2A_OUT_W), B * T, E, E);
   if (!ob_fused) launch_colsum(st, ws + w.d_br1, E, B * T, E, G(XP_V2A_OUT_B));

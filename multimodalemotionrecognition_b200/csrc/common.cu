@@ -133,8 +133,6 @@ int validate_config(const xattn_config* c) {
   if (c->pool_mode != XATTN_POOL_MEAN && c->pool_mode != XATTN_POOL_ATTN) XF_FAIL(XATTN_ERR_SHAPE, "unknown pool_mode %d", c->pool_mode);
   if (c->pool_mode != XATTN_POOL_MEAN && c->precision == XATTN_DTYPE_BF16)
     XF_FAIL(XATTN_ERR_SHAPE, "temporal_pooling=attn runs in the fp32 kernel family (precision f32 / tf32)");
-  if (c->pool_mode != XATTN_POOL_MEAN && (c->training || c->save_for_backward))
-    XF_FAIL(XATTN_ERR_SHAPE, "temporal_pooling=attn is forward-only (no backward kernels yet)");
   if (c->precision != XATTN_DTYPE_F32 && c->precision != XATTN_DTYPE_BF16 && c->precision != XATTN_PREC_TF32)
     XF_FAIL(XATTN_ERR_DTYPE, "unknown precision %d", c->precision);
   if ((int64_t)c->B * c->Ta * c->Da >= ((int64_t)1 << 40)) XF_FAIL(XATTN_ERR_SHAPE, "input too large");

@@ -167,6 +167,6 @@ __device__ __forceinline__ void drop_factor4(float p, uint64_t seed, uint64_t of
   f[2] = (float)(r.z >> 8) * sc < p ? 0.f : keep;
   f[3] = (float)(r.w >> 8) * sc < p ? 0.f : keep;
 }
-enum : uint32_t { RS_ATTN1 = 1, RS_ATTN2 = 2, RS_PATH1 = 3, RS_PATH2 = 4, RS_HEAD = 5, RS_PRIOR = 6 };
+enum : uint32_t { RS_ATTN1 = 1, RS_ATTN2 = 2, RS_PATH1 = 3, RS_PATH2 = 4, RS_HEAD = 5, RS_PRIOR = 6, RS_POOLV = 7, RS_POOLA = 8 };
 
 }  // namespace xf

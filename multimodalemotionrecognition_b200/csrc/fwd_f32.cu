@@ -403,12 +403,14 @@ __global__ void __launch_bounds__(256) pool_head_fwd_kernel(HeadArgs a) {
 // ---------------------------------------------------------------------------------------------------------
 // TemporalAttentionPooling (temporal.py:9-26): score_l = w2·GELU(W1·LN(x_l) + b1) + b2, attn = softmax_l(score),
 // out = sum_l attn_l · x_l (the UN-normalised tokens).  One CTA per clip; W1 is staged transposed in shared memory
-// ([e][j], so lane j walks a column without bank conflicts), one warp per token row.  Eval mode (Dropout identity).
+// ([e][j], so lane j walks a column without bank conflicts), one warp per token row.  The Dropout of the score MLP
+// (temporal.py:19) multiplies GELU's output by a Philox mask indexed (clip, token, hidden unit); attn_pool_bwd_kernel regenerates it.
 // ---------------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256) attn_pool_kernel(const float* __restrict__ x, const float* __restrict__ ln_w,
                                                         const float* __restrict__ ln_b, const float* __restrict__ w1,
                                                         const float* __restrict__ b1, const float* __restrict__ w2,
-                                                        const float* __restrict__ b2, float* __restrict__ out, int L, int E) {
+                                                        const float* __restrict__ b2, float* __restrict__ out, int L, int E,
+                                                        float p_drop, uint64_t seed, uint64_t offset, uint32_t rng_stream) {
   extern __shared__ float sm[];
   const int b = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nw = blockDim.x >> 5;
   const int H2 = E / 2 > 0 ? E / 2 : 1;
@@ -440,7 +442,8 @@ __global__ void __launch_bounds__(256) attn_pool_kernel(const float* __restrict_
     for (int j = lane; j < H2; j += 32) {
       float h = b1[j];
       for (int e = 0; e < E; ++e) h = fmaf(w1t[e * H2 + j], y[e], h);
-      const float g = 0.5f * h * (1.f + erff(h * 0.70710678118654752f));   // nn.GELU() (exact)
+      float g = 0.5f * h * (1.f + erff(h * 0.70710678118654752f));   // nn.GELU() (exact)
+      if (p_drop > 0.f) g *= drop_factor(p_drop, seed, offset, rng_stream, ((uint64_t)b * L + l) * H2 + j);
       sc = fmaf(w2[j], g, sc);
     }
     sc = warp_sum(sc);
@@ -470,7 +473,8 @@ __global__ void __launch_bounds__(256) attn_pool_kernel(const float* __restrict_
   }
 }
 
-static int launch_attn_pool(cudaStream_t st, const float* x, const float* const* p, float* out, int B, int L, int E) {
+static int launch_attn_pool(cudaStream_t st, const float* x, const float* const* p, float* out, int B, int L, int E, float p_drop,
+                            uint64_t seed, uint64_t offset, uint32_t rng_stream) {
   const int H2 = E / 2 > 0 ? E / 2 : 1;
   const size_t smem = sizeof(float) * ((size_t)E * H2 + 8 * (size_t)E + (size_t)L);
   if (smem > 200 * 1024) XF_FAIL(XATTN_ERR_SHAPE, "attention pooling needs %zu B of shared memory (> 200 KiB)", smem);
@@ -479,7 +483,7 @@ static int launch_attn_pool(cudaStream_t st, const float* x, const float* const*
     XF_CUDA(cudaFuncSetAttribute(attn_pool_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     configured = smem;
   }
-  attn_pool_kernel<<<B, 256, smem, st>>>(x, p[0], p[1], p[2], p[3], p[4], p[5], out, L, E);
+  attn_pool_kernel<<<B, 256, smem, st>>>(x, p[0], p[1], p[2], p[3], p[4], p[5], out, L, E, p_drop, seed, offset, rng_stream);
   count_launch();
   XF_LAUNCH_CHECK();
   return XATTN_OK;
@@ -616,8 +620,9 @@ static int forward_f32_impl(const xattn_config& c, const float* params, const TI
     if (c.pool_mode == XATTN_POOL_ATTN) {   // learned pooling first; the head kernel then sees one (already pooled) token per clip
       const float* pv[6] = {P(XP_VPOOL_LN_W), P(XP_VPOOL_LN_B), P(XP_VPOOL_W1), P(XP_VPOOL_B1), P(XP_VPOOL_W2), P(XP_VPOOL_B2)};
       const float* pa[6] = {P(XP_APOOL_LN_W), P(XP_APOOL_LN_B), P(XP_APOOL_W1), P(XP_APOOL_B1), P(XP_APOOL_W2), P(XP_APOOL_B2)};
-      XF_TRY(launch_attn_pool(st, ws + w.v1, pv, ws + w.poolv, B, T, E));
-      XF_TRY(launch_attn_pool(st, ws + w.a1, pa, ws + w.poola, B, Ta, E));
+      const float p_pool = train ? c.p_pool : 0.f;
+      XF_TRY(launch_attn_pool(st, ws + w.v1, pv, ws + w.poolv, B, T, E, p_pool, c.seed, c.offset, RS_POOLV));
+      XF_TRY(launch_attn_pool(st, ws + w.a1, pa, ws + w.poola, B, Ta, E, p_pool, c.seed, c.offset, RS_POOLA));
       ha.v1 = ws + w.poolv; ha.a1 = ws + w.poola;
       hT = hTa = 1;
     }

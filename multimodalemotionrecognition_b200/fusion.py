@@ -244,6 +244,7 @@ class XAttnKernelsMixin:
         self.xattn_stochastic_depth = float(max(0.0, min(1.0, xattn_stochastic_depth)))
         self.xattn_head_dropout = 0.2
         self.xattn_prior_dropout = float(prior_dropout)
+        self.xattn_pool_dropout = float(temporal_dropout)   # Dropout inside TemporalAttentionPooling.score (temporal.py:19)
         self._prior_dim = int(prior_dim) if use_emotion_prior else 0
         self._prior_hidden = int(prior_hidden) if use_emotion_prior else 0
         # kernel-side state
@@ -298,6 +299,7 @@ class XAttnKernelsMixin:
         cfg.pool_mode = _lib.POOL_ATTN if getattr(self, "_temporal_pooling", "mean") == "attn" else _lib.POOL_MEAN
         cfg.p_attn, cfg.p_path = self.xattn_attn_dropout, self.xattn_stochastic_depth
         cfg.p_head, cfg.p_prior = self.xattn_head_dropout, self.xattn_prior_dropout
+        cfg.p_pool = self.xattn_pool_dropout
         cfg.seed = torch.initial_seed() & 0xFFFFFFFFFFFFFFFF
         cfg.offset = self._rng_offset
         return cfg
@@ -415,9 +417,6 @@ class XAttnKernelsMixin:
         B, T, _ = video_emb.shape
         Ta = audio_emb.shape[1]
         io = _io_dtype(video_emb)
-        if (save or training) and getattr(self, "_temporal_pooling", "mean") != "mean":
-            raise ValueError("temporal_pooling='attn' is forward-only on the B200 path (no backward kernels yet): call it "
-                             "in eval mode under torch.no_grad()")
         precision = self._pick_precision(io, save or training, T, Ta)
         if precision == _lib.DTYPE_BF16 and io != _lib.DTYPE_BF16:   # precision="bf16" forced on fp32 embeddings
             video_emb, audio_emb, io = video_emb.bfloat16(), audio_emb.bfloat16(), _lib.DTYPE_BF16

@@ -107,6 +107,11 @@ def gen_attnpool(FusionModel) -> None:
         logits = m(xv[..., None, None], xa)
     blob.update({"tiny:xv": xv.numpy(), "tiny:xa": xa.numpy(), "tiny:logits": logits.numpy()})
     blob.update({"tiny:w:" + k: v.numpy() for k, v in fusion_state(m).items()})
+    labels = torch.randint(0, 8, (3,), generator=g)
+    loss = nn.functional.cross_entropy(m(xv[..., None, None], xa), labels)   # eval mode: dropouts identity, autograd on
+    loss.backward()
+    blob.update({"tiny:labels": labels.numpy(), "tiny:loss": loss.detach().numpy()})
+    blob.update({"tiny:g:" + k: v.numpy() for k, v in grads_of(m).items()})
     g = torch.Generator().manual_seed(1)
     xv = torch.randn(8, 16, 512, generator=g)
     xa = torch.randn(8, 149, 768, generator=g)
@@ -116,6 +121,15 @@ def gen_attnpool(FusionModel) -> None:
         with torch.no_grad():
             logits = m(xv[..., None, None], xa)
         sd = fusion_state(m)
+        labels = torch.randint(0, 8, (8,), generator=torch.Generator().manual_seed(2))
+        loss = nn.functional.cross_entropy(m(xv[..., None, None], xa), labels)
+        loss.backward()
+        blob[f"{head}:labels"] = labels.numpy()
+        blob[f"{head}:loss"] = loss.detach().numpy()
+        for k, v in grads_of(m).items():
+            blob[f"{head}:gd:{k}"] = digest(v)
+            if "temporal_pool" in k:
+                blob[f"{head}:g:{k}"] = v.numpy()
         blob[f"{head}:logits"] = logits.numpy()
         blob[f"{head}:keys"] = np.array(sorted(sd))
         blob[f"{head}:pool_digest"] = digest(torch.cat([v.flatten() for k, v in sorted(sd.items()) if "temporal_pool" in k]))

@@ -392,7 +392,7 @@ def test_flat_alignment_loss_matches_reference(cuda_device, mode):
 def test_attention_pooling_matches_reference(cuda_device):
     """temporal_pooling="attn" (TemporalAttentionPooling, temporal.py:9-26) in the fp32 kernel family: the tiny
     golden case and the BASELINE config-1 dimensions against the reference's logits (1e-4); bf16 embeddings route to the same
-    kernels (the bf16 tensor-core path pools by mean only); training raises (forward only)."""
+    kernels (the bf16 tensor-core path pools by mean only)."""
     from multimodalemotionrecognition_b200 import XAttnFusionHead
 
     blob = load_npz("xattn_attnpool.npz")
@@ -417,9 +417,67 @@ def test_attention_pooling_matches_reference(cuda_device):
         sdn = {k: v.cpu().numpy() for k, v in mm.state_dict().items()}
         refb = xattn_oracle.xattn_forward(sdn, xv.bfloat16().float().numpy(), xa.bfloat16().float().numpy(), num_heads=4, head=head)
         assert np.abs(outb.cpu().numpy() - refb).max() <= FP32_TOL
-    mm.train()
-    with pytest.raises(ValueError):
-        mm(xv.to(cuda_device), xa.to(cuda_device))
+
+
+def test_attention_pooling_backward_matches_reference(cuda_device):
+    """Backward through TemporalAttentionPooling (attn_pool_bwd_kernel): every gradient of the tiny case against the reference's
+    autograd (eval mode, dropouts identity); at the BASELINE config-1 dimensions the pooler's own gradients element-wise and all
+    others by digest, in fp32 and (cosine) tf32; training mode is deterministic for a given Philox offset and differs from eval."""
+    from multimodalemotionrecognition_b200 import XAttnFusionHead
+
+    blob = load_npz("xattn_attnpool.npz")
+    sd = {k[len("tiny:w:"):]: torch.from_numpy(v) for k, v in blob.items() if k.startswith("tiny:w:")}
+    m = XAttnFusionHead(num_classes=8, video_dim=16, audio_dim=8, common_dim=16, d_model=8, num_heads=2, audio_n_mels=8,
+                        xattn_use_emotion_prior=True, xattn_emotion_prior_dim=4, xattn_emotion_prior_hidden_dim=8,
+                        temporal_pooling="attn")
+    m.load_state_dict(sd, strict=True)
+    m = m.to(cuda_device).eval()
+    out = m(torch.from_numpy(blob["tiny:xv"]).to(cuda_device), torch.from_numpy(blob["tiny:xa"]).to(cuda_device))
+    loss = torch.nn.functional.cross_entropy(out, torch.from_numpy(blob["tiny:labels"]).to(cuda_device))
+    assert abs(float(loss.detach()) - float(blob["tiny:loss"])) < 1e-5
+    loss.backward()
+    named = dict(m.named_parameters())
+    n = 0
+    for k, v in blob.items():
+        if k.startswith("tiny:g:"):
+            g = named[k[len("tiny:g:"):]].grad
+            assert g is not None, k
+            np.testing.assert_allclose(g.cpu().numpy(), v, atol=2e-6, rtol=1e-4, err_msg=k)
+            n += 1
+    assert n >= 30 and "tiny:g:v_temporal_pool.pool.score.1.weight" in blob
+    g = torch.Generator().manual_seed(1)
+    xv = torch.randn(8, 16, 512, generator=g).to(cuda_device)
+    xa = torch.randn(8, 149, 768, generator=g).to(cuda_device)
+    for head in ("concat", "gated"):
+        labels = torch.from_numpy(blob[f"{head}:labels"]).to(cuda_device)
+        ref_pool = {}
+        for prec in ("fp32", "tf32"):
+            mm = make_head(head, True, seed=0, temporal_pooling="attn", precision=prec).to(cuda_device).eval()
+            loss = torch.nn.functional.cross_entropy(mm(xv, xa), labels)
+            loss.backward()
+            named = dict(mm.named_parameters())
+            if prec == "fp32":
+                assert abs(float(loss.detach()) - float(blob[f"{head}:loss"])) < 1e-5
+                for k, v in blob.items():
+                    if k.startswith(f"{head}:g:"):
+                        np.testing.assert_allclose(named[k[len(head) + 3:]].grad.cpu().numpy(), v, atol=2e-6, rtol=2e-4, err_msg=k)
+                    elif k.startswith(f"{head}:gd:"):
+                        np.testing.assert_allclose(digest(named[k[len(head) + 4:]].grad), v, atol=5e-5, rtol=2e-4, err_msg=k)
+            else:
+                for k, v in blob.items():
+                    if k.startswith(f"{head}:g:"):
+                        got = named[k[len(head) + 3:]].grad.flatten().double().cpu()
+                        want = torch.from_numpy(v).flatten().double()
+                        if want.numel() > 1:
+                            assert float(torch.dot(got, want) / (got.norm() * want.norm() + 1e-30)) >= 0.99, k
+    mm = make_head("concat", True, seed=0, temporal_pooling="attn").to(cuda_device).train()
+    mm._rng_offset = 7
+    a = mm(xv, xa).detach().clone()
+    mm._rng_offset = 7
+    b = mm(xv, xa).detach().clone()
+    assert torch.equal(a, b) and torch.isfinite(a).all()
+    mm.eval()
+    assert not torch.equal(a, mm(xv, xa).detach())
 
 
 def test_mel_front_end_matches_reference(cuda_device):
