@@ -26,7 +26,7 @@
 extern "C" {
 #endif
 
-#define XATTN_ABI_VERSION 13
+#define XATTN_ABI_VERSION 14
 
 #if defined(__GNUC__)
 #define XATTN_API __attribute__((visibility("default")))
@@ -46,7 +46,7 @@ typedef enum xattn_status {
 } xattn_status;
 
 enum { XATTN_HEAD_CONCAT = 0, XATTN_HEAD_GATED = 1 };
-enum { XATTN_POOL_MEAN = 0, XATTN_POOL_ATTN = 1 };
+enum { XATTN_POOL_MEAN = 0, XATTN_POOL_ATTN = 1, XATTN_POOL_TRANSFORMER = 2 };
 enum { XATTN_DTYPE_F32 = 0, XATTN_DTYPE_BF16 = 1 };
 /* xattn_config.precision only: the fp32 kernel family (forward, backward, training) with every Linear whose dimensions allow it
  * on the tensor cores — tcgen05 kind::tf32 straight from the fp32 tensors (kind::f16 for bf16 embeddings), fp32 accumulation. */
@@ -77,7 +77,10 @@ typedef struct xattn_config {
                                 (gradient parity in eval mode)            */
   int32_t pool_mode;    /* XATTN_POOL_MEAN (temporal.py:108-109) | XATTN_POOL_ATTN (TemporalAttentionPooling,
                            temporal.py:9-26: LN -> Linear -> GELU -> Dropout -> Linear -> softmax over time -> weighted
-                           sum; fp32 / tf32 family, forward and backward)             */
+                           sum; fp32 / tf32 family, forward and backward)
+                           XATTN_POOL_TRANSFORMER (TemporalTransformerPooling, temporal.py:46-75: sinusoidal positions, one
+                           pre-norm TransformerEncoderLayer (GELU, FFN = 4·E), then the attention pooling; forward only) */
+  int32_t pool_heads;   /* temporal_num_heads: heads of the pooler's self-attention (XATTN_POOL_TRANSFORMER) */
   float p_attn;         /* attention dropout            (fusion.py:277,280)          */
   float p_path;         /* stochastic depth             (fusion.py:282-283)          */
   float p_head;         /* head Dropout(0.2)            (fusion.py:315,322)          */
@@ -141,6 +144,22 @@ typedef enum xattn_param_id {
   XP_APOOL_B1,
   XP_APOOL_W2,
   XP_APOOL_B2,
+  /* XATTN_POOL_TRANSFORMER: {v,a}_temporal_pool.pool.encoder.layers.0.* (one layer); the XP_?POOL_* ids above then hold
+   * {v,a}_temporal_pool.pool.pool.score.* */
+  XP_VTX_IN_W,     /* self_attn.in_proj_weight [3E,E] */
+  XP_VTX_IN_B,     /* self_attn.in_proj_bias   [3E]   */
+  XP_VTX_OUT_W,    /* self_attn.out_proj.weight [E,E] */
+  XP_VTX_OUT_B,    /* self_attn.out_proj.bias   [E]   */
+  XP_VTX_FF1_W,    /* linear1.weight [F,E], F = max(2E, 4E) */
+  XP_VTX_FF1_B,    /* linear1.bias   [F]   */
+  XP_VTX_FF2_W,    /* linear2.weight [E,F] */
+  XP_VTX_FF2_B,    /* linear2.bias   [E]   */
+  XP_VTX_N1_W,     /* norm1.weight [E] */
+  XP_VTX_N1_B,
+  XP_VTX_N2_W,     /* norm2.weight [E] */
+  XP_VTX_N2_B,
+  XP_ATX_IN_W, XP_ATX_IN_B, XP_ATX_OUT_W, XP_ATX_OUT_B, XP_ATX_FF1_W, XP_ATX_FF1_B, XP_ATX_FF2_W, XP_ATX_FF2_B,
+  XP_ATX_N1_W, XP_ATX_N1_B, XP_ATX_N2_W, XP_ATX_N2_B,
   XP_COUNT
 } xattn_param_id;
 

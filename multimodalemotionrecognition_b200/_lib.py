@@ -12,13 +12,13 @@ from pathlib import Path
 
 LIB_NAME = "libxattn_fusion.so"
 LIB_PATH = Path(__file__).resolve().parent / LIB_NAME
-ABI_VERSION = 13
+ABI_VERSION = 14
 
 # xattn_status
 OK, ERR_SHAPE, ERR_DTYPE, ERR_ALIGN, ERR_ARCH, ERR_CUDA, ERR_WORKSPACE, ERR_NULL = range(8)
 HEAD_CONCAT, HEAD_GATED = 0, 1
 DTYPE_F32, DTYPE_BF16 = 0, 1
-POOL_MEAN, POOL_ATTN = 0, 1
+POOL_MEAN, POOL_ATTN, POOL_TRANSFORMER = 0, 1, 2
 PREC_TF32 = 2   # xattn_config.precision only: fp32 kernel family with the Linears on tcgen05 tf32 (gemm_tf32.cu)
 
 # xattn_param_id -> reference state_dict key (None: resolved per head kind)
@@ -41,7 +41,10 @@ XP_NAMES = [
     "v_temporal_pool.pool.score.1.bias", "v_temporal_pool.pool.score.4.weight", "v_temporal_pool.pool.score.4.bias",
     "a_temporal_pool.pool.score.0.weight", "a_temporal_pool.pool.score.0.bias", "a_temporal_pool.pool.score.1.weight",
     "a_temporal_pool.pool.score.1.bias", "a_temporal_pool.pool.score.4.weight", "a_temporal_pool.pool.score.4.bias",
-]
+] + [f"{side}_temporal_pool.pool.encoder.layers.0.{n}" for side in ("v", "a") for n in (
+    # temporal_pooling="transformer" (temporal.py:46-75), one encoder layer; the score ids above then name ...pool.pool.score.*
+    "self_attn.in_proj_weight", "self_attn.in_proj_bias", "self_attn.out_proj.weight", "self_attn.out_proj.bias",
+    "linear1.weight", "linear1.bias", "linear2.weight", "linear2.bias", "norm1.weight", "norm1.bias", "norm2.weight", "norm2.bias")]
 XP_COUNT = len(XP_NAMES)
 
 FP_NAMES = [
@@ -67,7 +70,7 @@ def flat_param_names(gated: bool) -> list[str]:
 class XAttnConfig(C.Structure):
     _fields_ = [(n, C.c_int32) for n in (
         "B", "T", "Ta", "Dv", "Da", "E", "H", "prior_dim", "prior_hidden", "common_dim", "C", "head_kind",
-        "use_prior", "io_dtype", "precision", "training", "save_for_backward", "pool_mode")] + [
+        "use_prior", "io_dtype", "precision", "training", "save_for_backward", "pool_mode", "pool_heads")] + [
         ("p_attn", C.c_float), ("p_path", C.c_float), ("p_head", C.c_float), ("p_prior", C.c_float), ("p_pool", C.c_float),
         ("seed", C.c_uint64), ("offset", C.c_uint64)]
 

@@ -130,7 +130,12 @@ int validate_config(const xattn_config* c) {
   if (c->use_prior && (c->prior_dim <= 0 || c->prior_hidden <= 0))
     XF_FAIL(XATTN_ERR_SHAPE, "emotion prior needs positive prior_dim / prior_hidden");
   if (c->io_dtype != XATTN_DTYPE_F32 && c->io_dtype != XATTN_DTYPE_BF16) XF_FAIL(XATTN_ERR_DTYPE, "unknown io_dtype %d", c->io_dtype);
-  if (c->pool_mode != XATTN_POOL_MEAN && c->pool_mode != XATTN_POOL_ATTN) XF_FAIL(XATTN_ERR_SHAPE, "unknown pool_mode %d", c->pool_mode);
+  if (c->pool_mode != XATTN_POOL_MEAN && c->pool_mode != XATTN_POOL_ATTN && c->pool_mode != XATTN_POOL_TRANSFORMER)
+    XF_FAIL(XATTN_ERR_SHAPE, "unknown pool_mode %d", c->pool_mode);
+  if (c->pool_mode == XATTN_POOL_TRANSFORMER) {
+    if (c->training || c->save_for_backward) XF_FAIL(XATTN_ERR_SHAPE, "temporal_pooling=transformer is forward-only (no backward kernels)");
+    if (c->pool_heads <= 0 || c->E % c->pool_heads != 0) XF_FAIL(XATTN_ERR_SHAPE, "pool_heads=%d must divide E=%d", c->pool_heads, c->E);
+  }
   if (c->pool_mode != XATTN_POOL_MEAN && c->precision == XATTN_DTYPE_BF16)
     XF_FAIL(XATTN_ERR_SHAPE, "temporal_pooling=attn runs in the fp32 kernel family (precision f32 / tf32)");
   if (c->precision != XATTN_DTYPE_F32 && c->precision != XATTN_DTYPE_BF16 && c->precision != XATTN_PREC_TF32)
@@ -162,7 +167,15 @@ void compute_param_layout(const xattn_config& c, ParamLayout& L) {
     sz[XP_VQ_B] = sz[XP_AK_B] = sz[XP_AQ_B] = sz[XP_VK_B] = 1;
     sz[XP_BIAS_SCALE] = 1;
   }
-  if (c.pool_mode == XATTN_POOL_ATTN) {
+  if (c.pool_mode == XATTN_POOL_TRANSFORMER) {
+    const int64_t F = 4 * E;   // max(2E, int(4.0·E)), temporal.py:58
+    for (int base : {(int)XP_VTX_IN_W, (int)XP_ATX_IN_W}) {
+      sz[base + 0] = 3 * E * E; sz[base + 1] = 3 * E; sz[base + 2] = E * E; sz[base + 3] = E;
+      sz[base + 4] = F * E; sz[base + 5] = F; sz[base + 6] = E * F; sz[base + 7] = E;
+      sz[base + 8] = sz[base + 9] = sz[base + 10] = sz[base + 11] = E;
+    }
+  }
+  if (c.pool_mode == XATTN_POOL_ATTN || c.pool_mode == XATTN_POOL_TRANSFORMER) {
     const int64_t H2 = E / 2 > 0 ? E / 2 : 1;
     for (int base : {(int)XP_VPOOL_LN_W, (int)XP_APOOL_LN_W}) {
       sz[base + 0] = E; sz[base + 1] = E; sz[base + 2] = H2 * E; sz[base + 3] = H2; sz[base + 4] = H2; sz[base + 5] = 1;
@@ -210,8 +223,12 @@ void compute_ws_f32(const xattn_config& c, WsF32& w) {
   // precision = TF32 with bf16 embeddings: bf16 copies of the two first-layer weights (forward), and of d_aseq / d_v0 for the
   // first-layer weight gradients (backward; those live in d_o2 / d_o1, dead by then)
   w.wbf = take((E * (int64_t)c.Da + E * (int64_t)c.Dv + 1) / 2 + 8);
-  w.poolv = take(c.pool_mode == XATTN_POOL_ATTN ? B * E : 0);
-  w.poola = take(c.pool_mode == XATTN_POOL_ATTN ? B * E : 0);
+  w.poolv = take(c.pool_mode != XATTN_POOL_MEAN ? B * E : 0);
+  w.poola = take(c.pool_mode != XATTN_POOL_MEAN ? B * E : 0);
+  {
+    const int64_t M = c.pool_mode == XATTN_POOL_TRANSFORMER ? B * (T > Ta ? T : Ta) : 0;   // rows of the longer side
+    w.tx_x = take(M * E); w.tx_h = take(M * E); w.tx_q = take(M * E); w.tx_kv = take(M * 2 * E); w.tx_f = take(M * 4 * E);
+  }
   w.total = off;
 }
 

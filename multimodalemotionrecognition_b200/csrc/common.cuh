@@ -106,7 +106,8 @@ struct WsF32 {
   int64_t d_pooled, d_hh, d_z, d_fused, d_a0, d_br2, d_o2, d_q2, d_kv2, d_v1, d_v0, d_br1, d_o1, d_q1, d_kv1, d_aseq;
   int64_t d_qv, d_ka, d_qa, d_kvs, d_prior, d_phid;
   int64_t wbf;    // bf16 scratch of the TF32 precision (see compute_ws_f32)
-  int64_t poolv, poola;   // pool_mode = ATTN: pooled tokens [B,E] each
+  int64_t poolv, poola;   // pool_mode != MEAN: pooled tokens [B,E] each
+  int64_t tx_x, tx_h, tx_q, tx_kv, tx_f;   // pool_mode = TRANSFORMER: encoder-layer activations of one side at a time
   int64_t total;  // floats
 };
 void compute_ws_f32(const xattn_config& c, WsF32& w);

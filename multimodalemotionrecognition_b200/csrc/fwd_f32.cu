@@ -490,6 +490,52 @@ static int launch_attn_pool(cudaStream_t st, const float* x, const float* const*
 }
 
 // ---------------------------------------------------------------------------------------------------------
+// TemporalTransformerPooling (temporal.py:46-75): x + sinusoidal positions -> one pre-norm nn.TransformerEncoderLayer
+// (x += SA(LN1(x)); x += W2·GELU(W1·LN2(x))) -> TemporalAttentionPooling.  The Linears go through linear_fwd (tensor cores
+// under PREC_TF32), the self-attention through the attention kernels of the fusion block (no bias, no dropout: eval); what is
+// left are the row-wise pieces below.  Forward only.
+// ---------------------------------------------------------------------------------------------------------
+// out[row, e] = x[row, e] + pe[row % L, e],  pe[l, 2i] = sin(l·w_i), pe[l, 2i+1] = cos(l·w_i), w_i = exp(2i·(-ln 10000 / E))  (temporal.py:33-38)
+__global__ void posenc_add_kernel(const float* __restrict__ x, float* __restrict__ out, int64_t n, int L, int E) {
+  const float c = -9.210340371976184f / (float)(E > 1 ? E : 1);
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    const int e = (int)(i % E), l = (int)((i / E) % L);
+    const float w = expf((float)(e & ~1) * c), arg = (float)l * w;
+    out[i] = x[i] + ((e & 1) ? cosf(arg) : sinf(arg));
+  }
+}
+// y = LayerNorm(x)·gamma + beta, one warp per row
+__global__ void __launch_bounds__(256) ln_rows_kernel(const float* __restrict__ x, const float* __restrict__ gamma,
+                                                      const float* __restrict__ beta, float* __restrict__ y, int rows, int E) {
+  const int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+  if (row >= rows) return;
+  const float* xr = x + (int64_t)row * E;
+  float sum = 0.f;
+  for (int e = lane; e < E; e += 32) sum += xr[e];
+  const float mu = warp_sum(sum) / (float)E;
+  float var = 0.f;
+  for (int e = lane; e < E; e += 32) {
+    const float d = xr[e] - mu;
+    var = fmaf(d, d, var);
+  }
+  const float rstd = rsqrtf(warp_sum(var) / (float)E + 1e-5f);
+  for (int e = lane; e < E; e += 32) y[(int64_t)row * E + e] = (xr[e] - mu) * rstd * gamma[e] + beta[e];
+}
+__global__ void gelu_kernel(float* __restrict__ x, int64_t n) {   // nn.GELU() (exact), in place
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    const float h = x[i];
+    x[i] = 0.5f * h * (1.f + erff(h * 0.70710678118654752f));
+  }
+}
+__global__ void add_inplace_kernel(float* __restrict__ x, const float* __restrict__ y, int64_t n) {
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) x[i] += y[i];
+}
+static inline int ew_grid(int64_t n) {
+  const int64_t g = (n + 255) / 256, cap = (int64_t)num_sms() * 16;
+  return (int)(g < cap ? (g > 0 ? g : 1) : cap);
+}
+
+// ---------------------------------------------------------------------------------------------------------
 // launch helpers shared with bwd_f32.cu
 // ---------------------------------------------------------------------------------------------------------
 size_t attn_smem_bytes(int L, int S, int dh, int nwarps) { return sizeof(float) * ((size_t)(L + 2 * S) * (dh + 1) + (size_t)nwarps * S); }
@@ -617,6 +663,41 @@ static int forward_f32_impl(const xattn_config& c, const float* params, const TI
     HeadArgs ha;
     ha.v1 = ws + w.v1; ha.a1 = ws + w.a1;
     int hT = T, hTa = Ta;
+    if (c.pool_mode == XATTN_POOL_TRANSFORMER) {   // encoder layer over each side's tokens, then the learned pooling
+      const int F = 4 * E, PH = c.pool_heads;
+      const float* pv[6] = {P(XP_VPOOL_LN_W), P(XP_VPOOL_LN_B), P(XP_VPOOL_W1), P(XP_VPOOL_B1), P(XP_VPOOL_W2), P(XP_VPOOL_B2)};
+      const float* pa[6] = {P(XP_APOOL_LN_W), P(XP_APOOL_LN_B), P(XP_APOOL_W1), P(XP_APOOL_B1), P(XP_APOOL_W2), P(XP_APOOL_B2)};
+      float *tx = ws + w.tx_x, *th = ws + w.tx_h, *tq = ws + w.tx_q, *tkv = ws + w.tx_kv, *tf = ws + w.tx_f;
+      for (int side = 0; side < 2; ++side) {
+        const int L = side == 0 ? T : Ta, base = side == 0 ? (int)XP_VTX_IN_W : (int)XP_ATX_IN_W;
+        const float* x = side == 0 ? ws + w.v1 : ws + w.a1;
+        const int M = B * L;
+        const int64_t n = (int64_t)M * E;
+        posenc_add_kernel<<<ew_grid(n), 256, 0, st>>>(x, tx, n, L, E);                                          // temporal.py:72
+        ln_rows_kernel<<<(M + 7) / 8, 256, 0, st>>>(tx, P(base + 8), P(base + 9), th, M, E);                    // norm1 (norm_first)
+        count_launch(2);
+        linear_fwd<float>(st, th, P(base + 0), P(base + 1), tq, M, E, E);
+        linear_fwd<float>(st, th, P(base + 0) + (int64_t)E * E, P(base + 1) + E, tkv, M, 2 * E, E);
+        AttnArgs aa;
+        aa.q = tq; aa.kv = tkv; aa.qs = nullptr; aa.ks = nullptr; aa.bias_scale = nullptr; aa.P = nullptr; aa.O = th;
+        aa.L = L; aa.S = L; aa.E = E; aa.H = PH; aa.scale = 1.0f / sqrtf((float)(E / PH)); aa.p_drop = 0.f; aa.seed = c.seed;
+        aa.offset = c.offset; aa.rng_stream = 0;
+        XF_TRY(launch_attn_fwd(st, aa, B));
+        linear_fwd<float>(st, th, P(base + 2), P(base + 3), tq, M, E, E);                                       // out_proj
+        add_inplace_kernel<<<ew_grid(n), 256, 0, st>>>(tx, tq, n);                                              // x += SA(LN1(x))
+        ln_rows_kernel<<<(M + 7) / 8, 256, 0, st>>>(tx, P(base + 10), P(base + 11), th, M, E);                  // norm2
+        count_launch(2);
+        linear_fwd<float>(st, th, P(base + 4), P(base + 5), tf, M, F, E);
+        gelu_kernel<<<ew_grid((int64_t)M * F), 256, 0, st>>>(tf, (int64_t)M * F);
+        linear_fwd<float>(st, tf, P(base + 6), P(base + 7), tq, M, E, F);
+        add_inplace_kernel<<<ew_grid(n), 256, 0, st>>>(tx, tq, n);                                              // x += FF(LN2(x))
+        count_launch(2);
+        XF_LAUNCH_CHECK();
+        XF_TRY(launch_attn_pool(st, tx, side == 0 ? pv : pa, side == 0 ? ws + w.poolv : ws + w.poola, B, L, E, 0.f, c.seed, c.offset, 0));
+      }
+      ha.v1 = ws + w.poolv; ha.a1 = ws + w.poola;
+      hT = hTa = 1;
+    }
     if (c.pool_mode == XATTN_POOL_ATTN) {   // learned pooling first; the head kernel then sees one (already pooled) token per clip
       const float* pv[6] = {P(XP_VPOOL_LN_W), P(XP_VPOOL_LN_B), P(XP_VPOOL_W1), P(XP_VPOOL_B1), P(XP_VPOOL_W2), P(XP_VPOOL_B2)};
       const float* pa[6] = {P(XP_APOOL_LN_W), P(XP_APOOL_LN_B), P(XP_APOOL_W1), P(XP_APOOL_B1), P(XP_APOOL_W2), P(XP_APOOL_B2)};

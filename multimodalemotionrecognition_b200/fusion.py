@@ -70,19 +70,40 @@ class TemporalAttentionPooling(nn.Module):
         raise RuntimeError("TemporalAttentionPooling runs inside the CUDA forward (attn_pool_kernel)")
 
 
-class TemporalPooler(nn.Module):
-    """``mean`` (``temporal.py:91-92, 108-109``; no parameters) and ``attn`` (``temporal.py:93-94``: the learned pooling, fp32
-    kernel family, forward only).  ``transformer`` (a full encoder layer in front of the pooling, ``temporal.py:46-75``) is the
-    rest of SURVEY 8(f) rank 3 and raises."""
+class TemporalTransformerPooling(nn.Module):
+    """Parameter container of ``temporal.py:46-75``: sinusoidal positions (no parameters; the reference's ``pe`` buffer is
+    non-persistent), ``nn.TransformerEncoder`` of pre-norm GELU layers, then ``TemporalAttentionPooling``.  Built from the same
+    torch modules as the reference so keys, shapes and same-seed initialisation are identical.  The B200 kernels run ONE layer."""
 
-    def __init__(self, dim: int, mode: str = "mean", dropout: float = 0.1, **_unused) -> None:
+    def __init__(self, dim: int, num_heads: int = 4, num_layers: int = 1, dropout: float = 0.1, mlp_ratio: float = 4.0) -> None:
+        super().__init__()
+        if num_layers != 1:
+            raise ValueError(f"the B200 transformer pooler runs one encoder layer (temporal_num_layers=1), got {num_layers}")
+        if max(dim * 2, int(dim * mlp_ratio)) != 4 * dim:
+            raise ValueError("the B200 transformer pooler is built for mlp_ratio=4")
+        layer = nn.TransformerEncoderLayer(d_model=dim, nhead=num_heads, dim_feedforward=4 * dim, dropout=dropout, activation="gelu",
+                                           batch_first=True, norm_first=True)
+        self.encoder = nn.TransformerEncoder(layer, num_layers=num_layers)
+        self.pool = TemporalAttentionPooling(dim=dim, dropout=dropout)
+        self.num_heads = num_heads
+
+    def forward(self, x: torch.Tensor) -> torch.Tensor:  # pragma: no cover - not on the kernel path
+        raise RuntimeError("TemporalTransformerPooling runs inside the CUDA forward")
+
+
+class TemporalPooler(nn.Module):
+    """``mean`` (``temporal.py:91-92, 108-109``; no parameters), ``attn`` (``temporal.py:93-94``: the learned pooling, forward
+    and backward in the fp32 / tf32 kernel family) and ``transformer`` (``temporal.py:95-102``: one encoder layer in front of
+    the learned pooling; forward only)."""
+
+    def __init__(self, dim: int, mode: str = "mean", dropout: float = 0.1, num_heads: int = 4, num_layers: int = 1, **_unused) -> None:
         super().__init__()
         if mode == "mean":
             self.pool = None
         elif mode == "attn":
             self.pool = TemporalAttentionPooling(dim=dim, dropout=dropout)
         elif mode == "transformer":
-            raise ValueError("Unsupported temporal pooling mode for the B200 xattn path: transformer (built: 'mean', 'attn')")
+            self.pool = TemporalTransformerPooling(dim=dim, num_heads=num_heads, num_layers=num_layers, dropout=dropout)
         else:
             raise ValueError(f"Unsupported temporal pooling mode: {mode}")
         self.mode = mode
@@ -189,7 +210,7 @@ class XAttnKernelsMixin:
                      d_model: int, num_heads: int, audio_n_mels: int, xattn_attn_dropout: float,
                      xattn_stochastic_depth: float, temporal_pooling: str, use_emotion_prior: bool, prior_dim: int,
                      prior_hidden: int, prior_dropout: float, precision: str = "auto", temporal_dropout: float = 0.1,
-                     audio_frontend: str = "seq") -> None:
+                     audio_frontend: str = "seq", temporal_num_heads: int = 4, temporal_num_layers: int = 1) -> None:
         if xattn_head not in ("concat", "gated"):
             raise ValueError(f"Unknown xattn head: {xattn_head}")
         if precision not in ("auto", "fp32", "bf16", "tf32"):
@@ -225,9 +246,12 @@ class XAttnKernelsMixin:
             self.emotion_prior_bias = EmotionPriorBiasAdapter(d_model, prior_dim, prior_hidden, prior_dropout)
         else:
             self.emotion_prior_bias = None
-        self.v_temporal_pool = TemporalPooler(dim=d_model, mode=temporal_pooling, dropout=temporal_dropout)
-        self.a_temporal_pool = TemporalPooler(dim=d_model, mode=temporal_pooling, dropout=temporal_dropout)
+        self.v_temporal_pool = TemporalPooler(dim=d_model, mode=temporal_pooling, dropout=temporal_dropout,
+                                              num_heads=temporal_num_heads, num_layers=temporal_num_layers)
+        self.a_temporal_pool = TemporalPooler(dim=d_model, mode=temporal_pooling, dropout=temporal_dropout,
+                                              num_heads=temporal_num_heads, num_layers=temporal_num_layers)
         self._temporal_pooling = temporal_pooling
+        self._temporal_num_heads = int(temporal_num_heads)
         self.xattn_head = xattn_head
         if xattn_head == "concat":
             self.xattn_mlp = nn.Sequential(
@@ -261,6 +285,8 @@ class XAttnKernelsMixin:
         names = _lib.xattn_param_names(self.xattn_head)
         if getattr(self, "audio_frontend", "seq") == "mel":
             names = [n.replace("audio_seq_proj.", "audio_time_conv.") for n in names]
+        if getattr(self, "_temporal_pooling", "mean") == "transformer":   # the score MLP sits one module deeper (temporal.py:70)
+            names = [n.replace("_temporal_pool.pool.score.", "_temporal_pool.pool.pool.score.") for n in names]
         return names
 
     def _xattn_named_params(self) -> list[Optional[nn.Parameter]]:
@@ -296,7 +322,9 @@ class XAttnKernelsMixin:
         cfg.use_prior = 1 if self.emotion_prior_bias is not None else 0
         cfg.io_dtype, cfg.precision = io_dtype, precision
         cfg.training, cfg.save_for_backward = int(training), int(save)
-        cfg.pool_mode = _lib.POOL_ATTN if getattr(self, "_temporal_pooling", "mean") == "attn" else _lib.POOL_MEAN
+        cfg.pool_mode = {"mean": _lib.POOL_MEAN, "attn": _lib.POOL_ATTN, "transformer": _lib.POOL_TRANSFORMER}[
+            getattr(self, "_temporal_pooling", "mean")]
+        cfg.pool_heads = getattr(self, "_temporal_num_heads", 4)
         cfg.p_attn, cfg.p_path = self.xattn_attn_dropout, self.xattn_stochastic_depth
         cfg.p_head, cfg.p_prior = self.xattn_head_dropout, self.xattn_prior_dropout
         cfg.p_pool = self.xattn_pool_dropout
@@ -417,6 +445,9 @@ class XAttnKernelsMixin:
         B, T, _ = video_emb.shape
         Ta = audio_emb.shape[1]
         io = _io_dtype(video_emb)
+        if (save or training) and getattr(self, "_temporal_pooling", "mean") == "transformer":
+            raise ValueError("temporal_pooling='transformer' is forward-only on the B200 path (no backward kernels): call it in "
+                             "eval mode under torch.no_grad()")
         precision = self._pick_precision(io, save or training, T, Ta)
         if precision == _lib.DTYPE_BF16 and io != _lib.DTYPE_BF16:   # precision="bf16" forced on fp32 embeddings
             video_emb, audio_emb, io = video_emb.bfloat16(), audio_emb.bfloat16(), _lib.DTYPE_BF16
@@ -605,7 +636,8 @@ class XAttnFusionHead(XAttnKernelsMixin, nn.Module):
                  xattn_attn_dropout: float = 0.1, xattn_stochastic_depth: float = 0.1, temporal_pooling: str = "mean", temporal_dropout: float = 0.1,
                  xattn_use_emotion_prior: bool = False, xattn_emotion_prior_dim: int = 8,
                  xattn_emotion_prior_hidden_dim: int = 64, xattn_emotion_prior_dropout: float = 0.1,
-                 precision: str = "auto", audio_frontend: str = "seq") -> None:
+                 precision: str = "auto", audio_frontend: str = "seq", temporal_num_heads: int = 4,
+                 temporal_num_layers: int = 1) -> None:
         super().__init__()
         self.mode = "xattn"
         self._build_xattn(v_dim=video_dim, audio_sequence_dim=audio_dim, num_classes=num_classes, common_dim=common_dim,
@@ -614,7 +646,8 @@ class XAttnFusionHead(XAttnKernelsMixin, nn.Module):
                           temporal_pooling=temporal_pooling, use_emotion_prior=xattn_use_emotion_prior,
                           prior_dim=xattn_emotion_prior_dim, prior_hidden=xattn_emotion_prior_hidden_dim,
                           prior_dropout=xattn_emotion_prior_dropout, precision=precision, temporal_dropout=temporal_dropout,
-                          audio_frontend=audio_frontend)
+                          audio_frontend=audio_frontend, temporal_num_heads=temporal_num_heads,
+                          temporal_num_layers=temporal_num_layers)
 
     def forward(self, video_emb: torch.Tensor, audio_emb: torch.Tensor) -> torch.Tensor:
         """``audio_emb``: encoder states [B,Ta,audio_dim] (``audio_frontend="seq"``) or a mel spectrogram
@@ -846,7 +879,8 @@ class FusionModel(XAttnKernelsMixin, FlatHeadKernelsMixin, nn.Module):
                               use_emotion_prior=xattn_use_emotion_prior, prior_dim=xattn_emotion_prior_dim,
                               prior_hidden=xattn_emotion_prior_hidden_dim, prior_dropout=xattn_emotion_prior_dropout,
                               precision=precision, temporal_dropout=temporal_dropout,
-                              audio_frontend="seq" if hasattr(audio_model, "encode_sequence") else "mel")
+                              audio_frontend="seq" if hasattr(audio_model, "encode_sequence") else "mel",
+                              temporal_num_heads=temporal_num_heads, temporal_num_layers=temporal_num_layers)
 
     def pop_alignment_loss(self):
         """``fusion.py:346-349``.  The reference computes the loss inside every concat/gated forward; here the B x B term is

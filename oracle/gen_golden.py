@@ -136,6 +136,36 @@ def gen_attnpool(FusionModel) -> None:
     np.savez_compressed(OUT / "xattn_attnpool.npz", **blob)
 
 
+def gen_txpool(FusionModel) -> None:
+    """temporal_pooling="transformer" (temporal.py:46-75), eval forward: a tiny case stored in full (2 pooler
+    heads) and the BASELINE config-1 dimensions with seed-0 weights (keys, digest of the pooler weights, full logits)."""
+    blob = {}
+    torch.manual_seed(31)
+    m = FusionModel(StubAudio(8), StubVideo(16), 8, mode="xattn", common_dim=16, xattn_head="concat", d_model=8, num_heads=2,
+                    audio_n_mels=8, temporal_pooling="transformer", temporal_num_heads=2, xattn_use_emotion_prior=True,
+                    xattn_emotion_prior_dim=4, xattn_emotion_prior_hidden_dim=8).eval()
+    g = torch.Generator().manual_seed(32)
+    xv = torch.randn(3, 4, 16, generator=g)
+    xa = torch.randn(3, 12, 8, generator=g)
+    with torch.no_grad():
+        logits = m(xv[..., None, None], xa)
+    blob.update({"tiny:xv": xv.numpy(), "tiny:xa": xa.numpy(), "tiny:logits": logits.numpy()})
+    blob.update({"tiny:w:" + k: v.numpy() for k, v in fusion_state(m).items()})
+    g = torch.Generator().manual_seed(1)
+    xv = torch.randn(8, 16, 512, generator=g)
+    xa = torch.randn(8, 149, 768, generator=g)
+    for head in ("concat", "gated"):
+        torch.manual_seed(0)
+        m = build_ref(FusionModel, dv=512, da=768, d_model=128, heads=4, head=head, prior=True, pooling="transformer").eval()
+        with torch.no_grad():
+            logits = m(xv[..., None, None], xa)
+        sd = fusion_state(m)
+        blob[f"{head}:logits"] = logits.numpy()
+        blob[f"{head}:keys"] = np.array(sorted(sd))
+        blob[f"{head}:pool_digest"] = digest(torch.cat([v.flatten() for k, v in sorted(sd.items()) if "temporal_pool" in k]))
+    np.savez_compressed(OUT / "xattn_txpool.npz", **blob)
+
+
 class StubAudioMel(nn.Module):
     """An encoder without encode_sequence(): the reference takes the mel fallback (fusion.py:379-384)."""
 
@@ -189,6 +219,9 @@ def main() -> None:
 
     OUT.mkdir(parents=True, exist_ok=True)
     torch.set_num_threads(1)
+    if "--only-txpool" in sys.argv:
+        gen_txpool(FusionModel)
+        return
     if "--only-mel" in sys.argv:
         gen_mel(FusionModel)
         return
@@ -196,6 +229,7 @@ def main() -> None:
     if "--only-attnpool" in sys.argv:
         return
     gen_mel(FusionModel)
+    gen_txpool(FusionModel)
 
     # ---- tiny case: everything stored in full (d_model=8, heads=2 as the reference's own shape tests) -------------
     for head in ("concat", "gated"):

@@ -126,6 +126,33 @@ def temporal_attention_pool(sd: Dict[str, Array], prefix: str, x: Array) -> Arra
     return (x * attn).sum(axis=1)                                                           # :26
 
 
+def sinusoidal_positions(length: int, dim: int) -> Array:
+    """temporal.py:31-39 (fp32 buffer in the reference; float64 here)."""
+    pos = np.arange(length, dtype=np.float64)[:, None]
+    div = np.exp(np.arange(0, dim, 2, dtype=np.float64) * (-np.log(10000.0) / max(1, dim)))
+    pe = np.zeros((length, dim))
+    pe[:, 0::2] = np.sin(pos * div)
+    if dim > 1:
+        pe[:, 1::2] = np.cos(pos * div[: pe[:, 1::2].shape[1]])
+    return pe
+
+
+def temporal_transformer_pool(sd: Dict[str, Array], prefix: str, x: Array, num_heads: int) -> Array:
+    """TemporalTransformerPooling, temporal.py:46-75, eval mode, one pre-norm GELU nn.TransformerEncoderLayer
+    (norm_first: x = x + SA(LN1(x)); x = x + W2·GELU(W1·LN2(x))), then the attention pooling (``prefix + "pool."``)."""
+    x = _f64(x) + sinusoidal_positions(x.shape[1], x.shape[2])[None]                          # :72
+    lp = prefix + "encoder.layers.0."
+    if (prefix + "encoder.layers.1.norm1.weight") in sd:
+        raise ValueError("oracle restates one encoder layer")
+    h = layer_norm(x, sd[lp + "norm1.weight"], sd[lp + "norm1.bias"])
+    x = x + multihead_attention(sd, lp + "self_attn.", h, h, num_heads, None)
+    h = layer_norm(x, sd[lp + "norm2.weight"], sd[lp + "norm2.bias"])
+    f = linear(h, sd[lp + "linear1.weight"], sd[lp + "linear1.bias"])
+    f = 0.5 * f * (1.0 + np.vectorize(math.erf, otypes=[np.float64])(f / math.sqrt(2.0)))                                             # activation="gelu" (exact)
+    x = x + linear(f, sd[lp + "linear2.weight"], sd[lp + "linear2.bias"])                    # :73
+    return temporal_attention_pool(sd, prefix + "pool.", x)                                  # :74
+
+
 def audio_time_conv(sd: Dict[str, Array], mel: Array) -> Array:
     """Mel front end, reference fusion.py:379-384: Conv1d(n_mels -> a_dim, kernel_size=3, padding=1) over time, then
     permute to [B, Ta, a_dim].  ``mel`` [B,1,n_mels,Ta] or [B,n_mels,Ta].  Restated as the convolution sum itself
@@ -145,7 +172,7 @@ def audio_time_conv(sd: Dict[str, Array], mel: Array) -> Array:
 
 def xattn_forward(sd: Dict[str, Array], video_emb: Array, audio_emb: Array, *, num_heads: int = 4,
                   head: str = "concat", use_prior: Optional[bool] = None, taps: Optional[dict] = None,
-                  audio_frontend: str = "seq") -> Array:
+                  audio_frontend: str = "seq", temporal_num_heads: int = 4) -> Array:
     """Forward of the xattn fusion head, reference fusion.py:372-411, eval mode.
 
     ``sd`` maps reference state_dict keys (head only) to arrays.  ``video_emb`` [B,T,Dv],
@@ -172,7 +199,10 @@ def xattn_forward(sd: Dict[str, Array], video_emb: Array, audio_emb: Array, *, n
     v_new = layer_norm(v + v2, sd["v_norm.weight"], sd["v_norm.bias"])           # :395
     a2 = multihead_attention(sd, "a2v_attn.", a, v_new, num_heads, a2v_bias)     # :398 (uses UPDATED v)
     a_new = layer_norm(a + a2, sd["a_norm.weight"], sd["a_norm.bias"])           # :399
-    if "v_temporal_pool.pool.score.0.weight" in sd:                             # temporal_pooling="attn", temporal.py:93-94
+    if "v_temporal_pool.pool.encoder.layers.0.norm1.weight" in sd:              # temporal_pooling="transformer", temporal.py:95-102
+        v_emb = temporal_transformer_pool(sd, "v_temporal_pool.pool.", v_new, temporal_num_heads)
+        a_emb = temporal_transformer_pool(sd, "a_temporal_pool.pool.", a_new, temporal_num_heads)
+    elif "v_temporal_pool.pool.score.0.weight" in sd:                           # temporal_pooling="attn", temporal.py:93-94
         v_emb = temporal_attention_pool(sd, "v_temporal_pool.pool.", v_new)
         a_emb = temporal_attention_pool(sd, "a_temporal_pool.pool.", a_new)
     else:

@@ -95,7 +95,9 @@ def test_unsupported_reference_options_raise_cleanly():
     from multimodalemotionrecognition_b200 import XAttnFusionHead
 
     with pytest.raises(ValueError, match="temporal pooling"):
-        XAttnFusionHead(temporal_pooling="transformer")
+        XAttnFusionHead(temporal_pooling="nope")                      # the reference's own message (temporal.py:104)
+    with pytest.raises(ValueError, match="one encoder layer"):
+        XAttnFusionHead(temporal_pooling="transformer", temporal_num_layers=2)
     with pytest.raises(ValueError):
         XAttnFusionHead(xattn_head="nope")
 

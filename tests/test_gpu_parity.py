@@ -572,3 +572,42 @@ def test_mel_front_end_matches_reference(cuda_device):
             outb = fm(xv.bfloat16()[..., None, None], mel.bfloat16())
             assert np.abs(outb.cpu().numpy() - blob[f"{head}:logits"]).max() <= 2 * BF16_TOL
             fm.precision = "auto"
+
+
+def test_transformer_pooling_matches_reference(cuda_device):
+    """temporal_pooling="transformer" (TemporalTransformerPooling, temporal.py:46-75), forward: the tiny case
+    (generic attention kernel, 2 pooler heads) and the BASELINE config-1 dimensions against the reference's logits in fp32 (1e-4),
+    tf32 and with bf16 embeddings; gradients raise (forward only)."""
+    import warnings
+
+    from multimodalemotionrecognition_b200 import XAttnFusionHead
+
+    warnings.simplefilter("ignore")
+    blob = load_npz("xattn_txpool.npz")
+    sd = {k[len("tiny:w:"):]: torch.from_numpy(v) for k, v in blob.items() if k.startswith("tiny:w:")}
+    m = XAttnFusionHead(num_classes=8, video_dim=16, audio_dim=8, common_dim=16, d_model=8, num_heads=2, audio_n_mels=8,
+                        xattn_use_emotion_prior=True, xattn_emotion_prior_dim=4, xattn_emotion_prior_hidden_dim=8,
+                        temporal_pooling="transformer", temporal_num_heads=2)
+    m.load_state_dict(sd, strict=True)
+    m = m.to(cuda_device).eval()
+    with torch.no_grad():
+        out = m(torch.from_numpy(blob["tiny:xv"]).to(cuda_device), torch.from_numpy(blob["tiny:xa"]).to(cuda_device))
+    assert np.abs(out.cpu().numpy() - blob["tiny:logits"]).max() <= 1e-5
+    g = torch.Generator().manual_seed(1)
+    xv = torch.randn(8, 16, 512, generator=g)
+    xa = torch.randn(8, 149, 768, generator=g)
+    for head in ("concat", "gated"):
+        mm = make_head(head, True, seed=0, temporal_pooling="transformer").to(cuda_device).eval()
+        with torch.no_grad():
+            out = mm(xv.to(cuda_device), xa.to(cuda_device))
+            outb = mm(xv.bfloat16().to(cuda_device), xa.bfloat16().to(cuda_device))
+            mm.precision = "tf32"
+            outt = mm(xv.to(cuda_device), xa.to(cuda_device))
+            mm.precision = "auto"
+        assert np.abs(out.cpu().numpy() - blob[f"{head}:logits"]).max() <= FP32_TOL
+        assert np.abs(outt.cpu().numpy() - blob[f"{head}:logits"]).max() <= BF16_TOL
+        sdn = {k: v.cpu().numpy() for k, v in mm.state_dict().items()}
+        refb = xattn_oracle.xattn_forward(sdn, xv.bfloat16().float().numpy(), xa.bfloat16().float().numpy(), num_heads=4, head=head)
+        assert np.abs(outb.cpu().numpy() - refb).max() <= FP32_TOL
+    with pytest.raises(ValueError):
+        mm(xv.to(cuda_device), xa.to(cuda_device))     # autograd on: no backward kernels for this pooler
