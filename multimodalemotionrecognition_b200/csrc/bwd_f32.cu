@@ -68,6 +68,16 @@ void launch_colsum(cudaStream_t st, const float* dY, int64_t ldy, int M, int N, 
   count_launch();
 }
 
+// gb_out[k] += Σ_n gb_in[n]·W[n,k]: the bias gradient of a Linear that feeds another Linear y = x·Wᵀ (+ b) directly, from the
+// bias gradient of that one (column sums commute with the product).
+__global__ void bias_chain_kernel(const float* __restrict__ gb_in, const float* __restrict__ W, float* __restrict__ gb_out, int N, int K) {
+  const int k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k >= K) return;
+  float s = 0.f;
+  for (int n = 0; n < N; ++n) s = fmaf(gb_in[n], W[(int64_t)n * K + k], s);
+  gb_out[k] += s;
+}
+
 // ---- head: gradient w.r.t. the hidden pre-activation (and the gated blend) ---------------------------------
 // concat: d_hh = (dlogits·W1) ⊙ relu'/dropout mask.
 // gated : dfused given; dg = <dfused, v̄-ā>; dz = dg·g(1-g); d_pooled = [g·dfused, (1-g)·dfused]; d_hh = dz·w3 ⊙ mask.
@@ -604,6 +614,7 @@ struct PriorBwdArgs {
   int T, Ta, E, P, Hd;
   float inv_keep;
   int vec;   // float4 token loop (E % 4 == 0, dpool 16-byte aligned in shared memory is not needed: scalar smem accesses)
+  float *g_bv, *g_ba;   // vec path: += column sums of the final d_v0 / d_a0 (the v_in_proj / a_in_proj bias gradients)
 };
 __global__ void __launch_bounds__(256) prior_bwd_kernel(PriorBwdArgs a) {
   extern __shared__ float sm[];
@@ -655,7 +666,7 @@ __global__ void __launch_bounds__(256) prior_bwd_kernel(PriorBwdArgs a) {
     // (float4 loads / read-modify-writes, independent across tokens); the four weight-gradient rows of the CTA's warps
     // meet in shared memory, then one atomic per column.  (The scalar loop below walks the tokens with E threads.)
     float* sd = dpool + 2 * E;          // [2T + 2Ta] score gradients of this clip
-    float* gred = sd + 2 * (T + Ta);    // [nw][4][E]
+    float* gred = sd + 2 * (T + Ta);    // [nw][6][E]: the four score-head rows, then the column sums of d_v0 and d_a0
     for (int i = tid; i < T; i += blockDim.x) { sd[i] = dsc[0][i]; sd[T + i] = dsc[3][i]; }
     for (int j = tid; j < Ta; j += blockDim.x) { sd[2 * T + j] = dsc[1][j]; sd[2 * T + Ta + j] = dsc[2][j]; }
     __syncthreads();
@@ -663,6 +674,7 @@ __global__ void __launch_bounds__(256) prior_bwd_kernel(PriorBwdArgs a) {
     for (int c4 = lane; c4 < (E >> 2); c4 += 32) {
       const int e = 4 * c4;
       float wq[4], wk[4], g0[4] = {0.f, 0.f, 0.f, 0.f}, g1[4] = {0.f, 0.f, 0.f, 0.f}, g2[4] = {0.f, 0.f, 0.f, 0.f}, g3[4] = {0.f, 0.f, 0.f, 0.f}, pm[4];
+      float4 sv = make_float4(0.f, 0.f, 0.f, 0.f), sa = sv;   // column sums of the finished token gradients
 #pragma unroll
       for (int k = 0; k < 4; ++k) { wq[k] = a.wh[0][e + k]; wk[k] = a.wh[3][e + k]; pm[k] = dpool[e + k] * inv_T; }
 #pragma unroll 4
@@ -674,6 +686,7 @@ __global__ void __launch_bounds__(256) prior_bwd_kernel(PriorBwdArgs a) {
         d.x += dq * wq[0] + dk * wk[0] + pm[0]; d.y += dq * wq[1] + dk * wk[1] + pm[1];
         d.z += dq * wq[2] + dk * wk[2] + pm[2]; d.w += dq * wq[3] + dk * wk[3] + pm[3];
         *dp = d;
+        sv.x += d.x; sv.y += d.y; sv.z += d.z; sv.w += d.w;
         g0[0] = fmaf(dq, x.x, g0[0]); g0[1] = fmaf(dq, x.y, g0[1]); g0[2] = fmaf(dq, x.z, g0[2]); g0[3] = fmaf(dq, x.w, g0[3]);
         g3[0] = fmaf(dk, x.x, g3[0]); g3[1] = fmaf(dk, x.y, g3[1]); g3[2] = fmaf(dk, x.z, g3[2]); g3[3] = fmaf(dk, x.w, g3[3]);
       }
@@ -688,18 +701,22 @@ __global__ void __launch_bounds__(256) prior_bwd_kernel(PriorBwdArgs a) {
         d.x += dk * wk[0] + dq * wq[0] + pm[0]; d.y += dk * wk[1] + dq * wq[1] + pm[1];
         d.z += dk * wk[2] + dq * wq[2] + pm[2]; d.w += dk * wk[3] + dq * wq[3] + pm[3];
         *dp = d;
+        sa.x += d.x; sa.y += d.y; sa.z += d.z; sa.w += d.w;
         g1[0] = fmaf(dk, x.x, g1[0]); g1[1] = fmaf(dk, x.y, g1[1]); g1[2] = fmaf(dk, x.z, g1[2]); g1[3] = fmaf(dk, x.w, g1[3]);
         g2[0] = fmaf(dq, x.x, g2[0]); g2[1] = fmaf(dq, x.y, g2[1]); g2[2] = fmaf(dq, x.z, g2[2]); g2[3] = fmaf(dq, x.w, g2[3]);
       }
-      float* gr = gred + (int64_t)warp * 4 * E + e;
+      float* gr = gred + (int64_t)warp * 6 * E + e;
 #pragma unroll
       for (int k = 0; k < 4; ++k) { gr[k] = g0[k]; gr[E + k] = g1[k]; gr[2 * E + k] = g2[k]; gr[3 * E + k] = g3[k]; }
+      gr[4 * E] = sv.x; gr[4 * E + 1] = sv.y; gr[4 * E + 2] = sv.z; gr[4 * E + 3] = sv.w;
+      gr[5 * E] = sa.x; gr[5 * E + 1] = sa.y; gr[5 * E + 2] = sa.z; gr[5 * E + 3] = sa.w;
     }
     __syncthreads();
-    for (int idx = tid; idx < 4 * E; idx += blockDim.x) {
+    for (int idx = tid; idx < 6 * E; idx += blockDim.x) {
       float t = 0.f;
-      for (int w2 = 0; w2 < nw; ++w2) t += gred[(int64_t)w2 * 4 * E + idx];
-      atomicAdd(a.g_wh[idx / E] + (idx % E), t);
+      for (int w2 = 0; w2 < nw; ++w2) t += gred[(int64_t)w2 * 6 * E + idx];
+      const int which = idx / E, e = idx - which * E;
+      atomicAdd(which < 4 ? a.g_wh[which] + e : which == 4 ? a.g_bv + e : a.g_ba + e, t);
     }
     return;
   }
@@ -1052,6 +1069,7 @@ static int backward_f32_impl(const xattn_config& c, const float* params, const T
   linear_bwd_dx(st, ws + w.d_kv1, 2 * E, P(XP_V2A_IN_W) + (int64_t)E * E, ws + w.d_a0, B * Ta, 2 * E, E, true);
   XF_LAUNCH_CHECK();
 
+  bool tok_bias_fused = false;
   // ---- emotion prior (fusion.py:170-184) ----
   if (c.use_prior) {
     PriorBwdArgs pa;
@@ -1064,8 +1082,10 @@ static int backward_f32_impl(const xattn_config& c, const float* params, const T
     pa.d_v0 = ws + w.d_v0; pa.d_a0 = ws + w.d_a0; pa.d_prior = ws + w.d_prior; pa.d_phid = ws + w.d_phid;
     pa.T = T; pa.Ta = Ta; pa.E = E; pa.P = c.prior_dim; pa.Hd = c.prior_hidden; pa.inv_keep = 1.f / (1.f - p_prior);
     size_t smem = sizeof(float) * (4 + c.prior_dim + c.prior_hidden + 2 * E);
-    const size_t smem_vec = smem + sizeof(float) * (2 * (T + Ta) + 8 * 4 * E);
+    const size_t smem_vec = smem + sizeof(float) * (2 * (T + Ta) + 8 * 6 * E);
     pa.vec = (E % 4 == 0 && smem_vec <= 48 * 1024) ? 1 : 0;
+    pa.g_bv = G(XP_V_IN_B); pa.g_ba = G(XP_A_IN_B);
+    tok_bias_fused = pa.vec != 0;   // d_v0 / d_a0 are final in that kernel: it leaves their column sums in the two bias gradients
     if (pa.vec) smem = smem_vec;
     prior_bwd_kernel<<<B, 256, smem, st>>>(pa);
     count_launch();
@@ -1078,7 +1098,7 @@ static int backward_f32_impl(const xattn_config& c, const float* params, const T
 
   // ---- input projections (fusion.py:386, :378, :372); the inputs are frozen embeddings: no dX ----
   linear_bwd_dw<float>(st, ws + w.d_a0, E, ws + w.aseq, E, G(XP_A_IN_W), B * Ta, E, E);
-  launch_colsum(st, ws + w.d_a0, E, B * Ta, E, G(XP_A_IN_B));
+  if (!tok_bias_fused) launch_colsum(st, ws + w.d_a0, E, B * Ta, E, G(XP_A_IN_B));
   linear_bwd_dx(st, ws + w.d_a0, E, P(XP_A_IN_W), ws + w.d_aseq, B * Ta, E, E, false);
   const bool tc16 = g_tc_gemm && std::is_same<TIO, __nv_bfloat16>::value && gemm_cols_ok(B * Ta, E, c.Da, E, c.Da, true) &&
                     gemm_cols_ok(B * T, E, c.Dv, E, c.Dv, true);
@@ -1089,7 +1109,10 @@ static int backward_f32_impl(const xattn_config& c, const float* params, const T
   } else {
     linear_bwd_dw<TIO>(st, ws + w.d_aseq, E, xa, c.Da, G(XP_SEQ_W), B * Ta, E, c.Da);
   }
-  launch_colsum(st, ws + w.d_aseq, E, B * Ta, E, G(XP_SEQ_B));
+  // colsum(d_aseq) = colsum(d_a0)·W_ain: the audio_seq_proj bias gradient follows from the a_in_proj one by a 128 x 128 product
+  // instead of another pass over the [B·Ta, E] gradient
+  bias_chain_kernel<<<(E + 127) / 128, 128, 0, st>>>(G(XP_A_IN_B), P(XP_A_IN_W), G(XP_SEQ_B), E, E);
+  count_launch();
   if (tc16) {
     __nv_bfloat16* dyb = reinterpret_cast<__nv_bfloat16*>(ws + w.d_o1);
     cvt_f32_to_bf16(st, ws + w.d_v0, dyb, (int64_t)B * T * E);
@@ -1097,7 +1120,7 @@ static int backward_f32_impl(const xattn_config& c, const float* params, const T
   } else {
     linear_bwd_dw<TIO>(st, ws + w.d_v0, E, xv, c.Dv, G(XP_V_IN_W), B * T, E, c.Dv);
   }
-  launch_colsum(st, ws + w.d_v0, E, B * T, E, G(XP_V_IN_B));
+  if (!tok_bias_fused) launch_colsum(st, ws + w.d_v0, E, B * T, E, G(XP_V_IN_B));
   XF_LAUNCH_CHECK();
   return XATTN_OK;
 }

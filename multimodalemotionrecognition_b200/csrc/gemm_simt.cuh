@@ -136,6 +136,7 @@ inline void linear_bwd_dw(cudaStream_t st, const float* dY, int64_t ldy, const T
     return;
   }
   int splits = M / 128;   // (short reductions too: one CTA walking 1024 rows alone is a 180 us kernel)
+  if (M <= 4096) splits = M / 32;   // batch-sized reductions (head / prior weights): each 16-row step is a dependent global round trip
   if (splits < 1) splits = 1;
   if (splits > 512) splits = 512;
   if (splits == 1) {
