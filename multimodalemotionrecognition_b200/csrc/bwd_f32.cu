@@ -70,12 +70,15 @@ void launch_colsum(cudaStream_t st, const float* dY, int64_t ldy, int M, int N, 
 
 // gb_out[k] += Σ_n gb_in[n]·W[n,k]: the bias gradient of a Linear that feeds another Linear y = x·Wᵀ (+ b) directly, from the
 // bias gradient of that one (column sums commute with the product).
+// grid (column blocks, 16-row slices of n): coalesced rows of W, partial sums meet in gb_out atomically.
 __global__ void bias_chain_kernel(const float* __restrict__ gb_in, const float* __restrict__ W, float* __restrict__ gb_out, int N, int K) {
   const int k = blockIdx.x * blockDim.x + threadIdx.x;
   if (k >= K) return;
+  const int n0 = blockIdx.y * 16, n1 = min(N, n0 + 16);
   float s = 0.f;
-  for (int n = 0; n < N; ++n) s = fmaf(gb_in[n], W[(int64_t)n * K + k], s);
-  gb_out[k] += s;
+#pragma unroll 4
+  for (int n = n0; n < n1; ++n) s = fmaf(gb_in[n], W[(int64_t)n * K + k], s);
+  atomicAdd(gb_out + k, s);
 }
 
 // ---- head: gradient w.r.t. the hidden pre-activation (and the gated blend) ---------------------------------
@@ -1111,7 +1114,7 @@ static int backward_f32_impl(const xattn_config& c, const float* params, const T
   }
   // colsum(d_aseq) = colsum(d_a0)·W_ain: the audio_seq_proj bias gradient follows from the a_in_proj one by a 128 x 128 product
   // instead of another pass over the [B·Ta, E] gradient
-  bias_chain_kernel<<<(E + 127) / 128, 128, 0, st>>>(G(XP_A_IN_B), P(XP_A_IN_W), G(XP_SEQ_B), E, E);
+  bias_chain_kernel<<<dim3((E + 127) / 128, (E + 15) / 16), 128, 0, st>>>(G(XP_A_IN_B), P(XP_A_IN_W), G(XP_SEQ_B), E, E);
   count_launch();
   if (tc16) {
     __nv_bfloat16* dyb = reinterpret_cast<__nv_bfloat16*>(ws + w.d_o1);
