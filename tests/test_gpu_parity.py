@@ -611,3 +611,33 @@ def test_transformer_pooling_matches_reference(cuda_device):
         assert np.abs(outb.cpu().numpy() - refb).max() <= FP32_TOL
     with pytest.raises(ValueError):
         mm(xv.to(cuda_device), xa.to(cuda_device))     # autograd on: no backward kernels for this pooler
+
+
+def test_mel_unfold_and_serving_epilogue_edge_cases(cuda_device):
+    """Ragged / empty inputs of the two small boundary kernels: mel_unfold at Ta = 1, 31, 33, 149 and n_mels = 1, 5, 64 (exact against
+    pad + stack), an empty batch; softmax_top1 on an empty batch and a single class; predict_host(top1=True) on an empty batch."""
+    from multimodalemotionrecognition_b200 import XAttnFusionHead, softmax_top1
+
+    g = torch.Generator().manual_seed(3)
+    for n_mels, Ta, B in [(1, 1, 2), (5, 31, 3), (5, 33, 1), (64, 149, 4), (64, 1, 1)]:
+        m = XAttnFusionHead(num_classes=8, video_dim=16, audio_dim=8, common_dim=16, d_model=8, num_heads=2, audio_n_mels=n_mels,
+                            audio_frontend="mel").to(cuda_device).eval()
+        mel = torch.randn(B, 1, n_mels, Ta, generator=g).to(cuda_device)
+        pad = torch.nn.functional.pad(mel[:, 0], (1, 1))
+        want = torch.stack([pad[:, :, k:k + Ta] for k in range(3)], dim=-1).permute(0, 2, 1, 3).reshape(B, Ta, 3 * n_mels)
+        assert torch.equal(m.mel_unfold(mel), want), (n_mels, Ta)
+        assert torch.equal(m.mel_unfold(mel[:, 0].bfloat16()), want.bfloat16())
+        with torch.no_grad():
+            assert m(torch.randn(B, 4, 16, generator=g).to(cuda_device), mel).shape == (B, 8)
+    assert m.mel_unfold(mel[:0]).shape == (0, 1, 192)
+    with pytest.raises(ValueError):
+        m.mel_unfold(torch.zeros(2, 63, 5, device=cuda_device))
+    p, t1, t1p = softmax_top1(torch.empty(0, 8, device=cuda_device))
+    assert p.shape == (0, 8) and t1.shape == (0,) and t1p.shape == (0,)
+    p, t1, t1p = softmax_top1(torch.tensor([[3.0], [-2.0]], device=cuda_device))
+    assert torch.equal(p, torch.ones(2, 1, device=cuda_device)) and t1.tolist() == [0, 0] and t1p.tolist() == [1.0, 1.0]
+    with pytest.raises(ValueError):
+        softmax_top1(torch.zeros(4, 8))
+    head = make_head("concat", True, seed=0).to(cuda_device).eval()
+    p, t1, t1p = head.predict_host(torch.empty(0, 16, 512, dtype=torch.bfloat16), torch.empty(0, 149, 768, dtype=torch.bfloat16), top1=True)
+    assert p.shape == (0, 8) and t1.shape == (0,) and t1p.shape == (0,)
