@@ -29,7 +29,9 @@ constexpr int kStage = 2 * kOpBytes;              // 32 KB
 constexpr int kStages = 6;
 constexpr int kAccs = 2;
 constexpr int kThreads = 64 + 128;
-constexpr int kSmem = kStages * kStage + 1024 /*bias*/ + 256 /*barriers*/ + 1024 /*alignment*/;
+constexpr int kEpiPitch = 36;                     // floats per staged row: 16-byte aligned, quarter-warp float4 accesses conflict-free
+constexpr int kEpiBytes = 4 * 32 * kEpiPitch * 4; // one 32 x 32 transpose buffer per epilogue warp
+constexpr int kSmem = kStages * kStage + 1024 /*bias*/ + 256 /*barriers*/ + kEpiBytes + 1024 /*alignment*/;
 constexpr int kRedRows = 32;                      // reduction rows per stage of the MN-major operands
 
 // Instruction descriptors: D = f32 (bits 4-5 = 1); A/B format at bits 7-9 / 10-12: bf16 = 1, tf32 = 2; bit 15 / 16 = A / B is
@@ -113,6 +115,7 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_tf32_rows_kernel(const __gri
   uint8_t* smem = align1k(smem_raw);
   float* bias_s = reinterpret_cast<float*>(smem + kStages * kStage);
   Bars* bars = reinterpret_cast<Bars*>(smem + kStages * kStage + 1024);
+  float* epi_s = reinterpret_cast<float*>(smem + kStages * kStage + 1024 + 256);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int KB = K / 32, tiles_n = N / TN, tiles_m = (M + TM - 1) / TM, num_tiles = tiles_m * tiles_n;
   const uint32_t tmem_base = prologue(bars, warp, lane, &tmA, &tmB);
@@ -177,31 +180,45 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_tf32_rows_kernel(const __gri
       }
       tc::mbar_wait(&bars->acc_full[ab], (lt / kAccs) & 1u);
       tc::tc_fence_after();
-      const int m = m0 + q * 32 + lane;
+      // TMEM hands a lane one ROW of the tile (32 columns at a time).  Storing that directly makes every store instruction touch 32
+      // different 128-byte lines with 16 bytes each; the strip goes through a per-warp shared-memory transpose instead, so that a
+      // store instruction writes four complete lines (rows rr = 4i + lane/8, float4 column lane%8) — and the `accumulate` loads
+      // are coalesced the same way.
+      float* buf = epi_s + q * (32 * kEpiPitch);
+      const int rsub = lane >> 3, c4 = lane & 7;
 #pragma unroll 1
       for (int c = 0; c < TN; c += 32) {
-        float* o = C + (int64_t)m * ldc + n0 + c;
+        float* o = C + (int64_t)(m0 + q * 32 + rsub) * ldc + n0 + c + 4 * c4;   // row rsub of the strip; + 4·i rows per step
         float4 old[8];
-        if (accumulate && m < M) {   // the previous values: eight independent loads in flight while the accumulator strip arrives
+        if (accumulate) {   // the previous values: eight independent loads in flight while the accumulator strip arrives
 #pragma unroll
-          for (int v = 0; v < 8; ++v) old[v] = __ldcs(reinterpret_cast<const float4*>(o + 4 * v));
+          for (int i = 0; i < 8; ++i)
+            if (m0 + q * 32 + 4 * i + rsub < M) old[i] = __ldcs(reinterpret_cast<const float4*>(o + (int64_t)(4 * i) * ldc));
         }
         uint32_t r[32];
         tc::tmem_ld_32x32(tmem_base + ab * TN + ((uint32_t)(q * 32) << 16) + (uint32_t)c, r);
         tc::tmem_ld_wait();
-        if (m < M) {
 #pragma unroll
-          for (int v = 0; v < 8; ++v) {
-            float4 f;
-            f.x = __uint_as_float(r[4 * v + 0]) + bias_s[c + 4 * v + 0];
-            f.y = __uint_as_float(r[4 * v + 1]) + bias_s[c + 4 * v + 1];
-            f.z = __uint_as_float(r[4 * v + 2]) + bias_s[c + 4 * v + 2];
-            f.w = __uint_as_float(r[4 * v + 3]) + bias_s[c + 4 * v + 3];
-            if (relu) { f.x = fmaxf(f.x, 0.f); f.y = fmaxf(f.y, 0.f); f.z = fmaxf(f.z, 0.f); f.w = fmaxf(f.w, 0.f); }
-            if (accumulate) { f.x += old[v].x; f.y += old[v].y; f.z += old[v].z; f.w += old[v].w; }
-            *reinterpret_cast<float4*>(o + 4 * v) = f;
+        for (int v = 0; v < 8; ++v) {
+          float4 f;
+          f.x = __uint_as_float(r[4 * v + 0]) + bias_s[c + 4 * v + 0];
+          f.y = __uint_as_float(r[4 * v + 1]) + bias_s[c + 4 * v + 1];
+          f.z = __uint_as_float(r[4 * v + 2]) + bias_s[c + 4 * v + 2];
+          f.w = __uint_as_float(r[4 * v + 3]) + bias_s[c + 4 * v + 3];
+          if (relu) { f.x = fmaxf(f.x, 0.f); f.y = fmaxf(f.y, 0.f); f.z = fmaxf(f.z, 0.f); f.w = fmaxf(f.w, 0.f); }
+          *reinterpret_cast<float4*>(buf + lane * kEpiPitch + 4 * v) = f;
+        }
+        __syncwarp();
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          const int rr = 4 * i + rsub;
+          if (m0 + q * 32 + rr < M) {
+            float4 f = *reinterpret_cast<const float4*>(buf + rr * kEpiPitch + 4 * c4);
+            if (accumulate) { f.x += old[i].x; f.y += old[i].y; f.z += old[i].z; f.w += old[i].w; }
+            *reinterpret_cast<float4*>(o + (int64_t)(4 * i) * ldc) = f;
           }
         }
+        __syncwarp();
       }
       tc::tc_fence_before();
       __syncwarp();
