@@ -680,33 +680,57 @@ __global__ void __launch_bounds__(256) prior_bwd_kernel(PriorBwdArgs a) {
       float4 sv = make_float4(0.f, 0.f, 0.f, 0.f), sa = sv;   // column sums of the finished token gradients
 #pragma unroll
       for (int k = 0; k < 4; ++k) { wq[k] = a.wh[0][e + k]; wk[k] = a.wh[3][e + k]; pm[k] = dpool[e + k] * inv_T; }
-#pragma unroll 4
-      for (int i = warp; i < T; i += nw) {
-        const float dq = sd[i], dk = sd[T + i];
-        const float4 x = __ldg(reinterpret_cast<const float4*>(v0 + (int64_t)i * E) + c4);
-        float4* dp = reinterpret_cast<float4*>(dv0 + (int64_t)i * E) + c4;
-        float4 d = *dp;
-        d.x += dq * wq[0] + dk * wk[0] + pm[0]; d.y += dq * wq[1] + dk * wk[1] + pm[1];
-        d.z += dq * wq[2] + dk * wk[2] + pm[2]; d.w += dq * wq[3] + dk * wk[3] + pm[3];
-        *dp = d;
-        sv.x += d.x; sv.y += d.y; sv.z += d.z; sv.w += d.w;
-        g0[0] = fmaf(dq, x.x, g0[0]); g0[1] = fmaf(dq, x.y, g0[1]); g0[2] = fmaf(dq, x.z, g0[2]); g0[3] = fmaf(dq, x.w, g0[3]);
-        g3[0] = fmaf(dk, x.x, g3[0]); g3[1] = fmaf(dk, x.y, g3[1]); g3[2] = fmaf(dk, x.z, g3[2]); g3[3] = fmaf(dk, x.w, g3[3]);
+      // (four tokens per step with all eight loads issued before the first store: the gradient pointers may alias the token
+      // pointers as far as the compiler knows, so it will not move a later load above an earlier store by itself)
+      for (int i0 = warp; i0 < T; i0 += 4 * nw) {
+        float4 x[4], d[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+          const int i = i0 + u * nw;
+          if (i < T) {
+            x[u] = __ldg(reinterpret_cast<const float4*>(v0 + (int64_t)i * E) + c4);
+            d[u] = *(reinterpret_cast<const float4*>(dv0 + (int64_t)i * E) + c4);
+          }
+        }
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+          const int i = i0 + u * nw;
+          if (i < T) {
+            const float dq = sd[i], dk = sd[T + i];
+            d[u].x += dq * wq[0] + dk * wk[0] + pm[0]; d[u].y += dq * wq[1] + dk * wk[1] + pm[1];
+            d[u].z += dq * wq[2] + dk * wk[2] + pm[2]; d[u].w += dq * wq[3] + dk * wk[3] + pm[3];
+            *(reinterpret_cast<float4*>(dv0 + (int64_t)i * E) + c4) = d[u];
+            sv.x += d[u].x; sv.y += d[u].y; sv.z += d[u].z; sv.w += d[u].w;
+            g0[0] = fmaf(dq, x[u].x, g0[0]); g0[1] = fmaf(dq, x[u].y, g0[1]); g0[2] = fmaf(dq, x[u].z, g0[2]); g0[3] = fmaf(dq, x[u].w, g0[3]);
+            g3[0] = fmaf(dk, x[u].x, g3[0]); g3[1] = fmaf(dk, x[u].y, g3[1]); g3[2] = fmaf(dk, x[u].z, g3[2]); g3[3] = fmaf(dk, x[u].w, g3[3]);
+          }
+        }
       }
 #pragma unroll
       for (int k = 0; k < 4; ++k) { wk[k] = a.wh[1][e + k]; wq[k] = a.wh[2][e + k]; pm[k] = dpool[E + e + k] * inv_Ta; }
-#pragma unroll 4
-      for (int j = warp; j < Ta; j += nw) {
-        const float dk = sd[2 * T + j], dq = sd[2 * T + Ta + j];
-        const float4 x = __ldg(reinterpret_cast<const float4*>(a0 + (int64_t)j * E) + c4);
-        float4* dp = reinterpret_cast<float4*>(da0 + (int64_t)j * E) + c4;
-        float4 d = *dp;
-        d.x += dk * wk[0] + dq * wq[0] + pm[0]; d.y += dk * wk[1] + dq * wq[1] + pm[1];
-        d.z += dk * wk[2] + dq * wq[2] + pm[2]; d.w += dk * wk[3] + dq * wq[3] + pm[3];
-        *dp = d;
-        sa.x += d.x; sa.y += d.y; sa.z += d.z; sa.w += d.w;
-        g1[0] = fmaf(dk, x.x, g1[0]); g1[1] = fmaf(dk, x.y, g1[1]); g1[2] = fmaf(dk, x.z, g1[2]); g1[3] = fmaf(dk, x.w, g1[3]);
-        g2[0] = fmaf(dq, x.x, g2[0]); g2[1] = fmaf(dq, x.y, g2[1]); g2[2] = fmaf(dq, x.z, g2[2]); g2[3] = fmaf(dq, x.w, g2[3]);
+      for (int j0 = warp; j0 < Ta; j0 += 4 * nw) {
+        float4 x[4], d[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+          const int j = j0 + u * nw;
+          if (j < Ta) {
+            x[u] = __ldg(reinterpret_cast<const float4*>(a0 + (int64_t)j * E) + c4);
+            d[u] = *(reinterpret_cast<const float4*>(da0 + (int64_t)j * E) + c4);
+          }
+        }
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+          const int j = j0 + u * nw;
+          if (j < Ta) {
+            const float dk = sd[2 * T + j], dq = sd[2 * T + Ta + j];
+            d[u].x += dk * wk[0] + dq * wq[0] + pm[0]; d[u].y += dk * wk[1] + dq * wq[1] + pm[1];
+            d[u].z += dk * wk[2] + dq * wq[2] + pm[2]; d[u].w += dk * wk[3] + dq * wq[3] + pm[3];
+            *(reinterpret_cast<float4*>(da0 + (int64_t)j * E) + c4) = d[u];
+            sa.x += d[u].x; sa.y += d[u].y; sa.z += d[u].z; sa.w += d[u].w;
+            g1[0] = fmaf(dk, x[u].x, g1[0]); g1[1] = fmaf(dk, x[u].y, g1[1]); g1[2] = fmaf(dk, x[u].z, g1[2]); g1[3] = fmaf(dk, x[u].w, g1[3]);
+            g2[0] = fmaf(dq, x[u].x, g2[0]); g2[1] = fmaf(dq, x[u].y, g2[1]); g2[2] = fmaf(dq, x[u].z, g2[2]); g2[3] = fmaf(dq, x[u].w, g2[3]);
+          }
+        }
       }
       float* gr = gred + (int64_t)warp * 6 * E + e;
 #pragma unroll
