@@ -26,7 +26,7 @@
 extern "C" {
 #endif
 
-#define XATTN_ABI_VERSION 14
+#define XATTN_ABI_VERSION 15
 
 #if defined(__GNUC__)
 #define XATTN_API __attribute__((visibility("default")))
@@ -191,6 +191,20 @@ XATTN_API int xattn_pack_weights(const xattn_config* cfg, const float* params, v
  * `packed` may be NULL when precision == F32. */
 XATTN_API int xattn_forward(const xattn_config* cfg, const float* params, const void* packed, const void* video_emb,
                   const void* audio_emb, float* logits, void* workspace, int64_t workspace_bytes, void* stream);
+
+/* xattn_forward for callers that may not allocate (code under CUDA graph capture, tight serving loops, harnesses that forbid
+ * cudaMalloc).  NO COUNTERPART IN THE REFERENCE.  Same kernels and results as
+ * xattn_forward (eval mode only), but the scratch workspace is a static __device__ array inside the library of
+ * XATTN_NOALLOC_MAX_WORKSPACE_BYTES (held by every GPU that loads the library until the process exits), so the call itself
+ * performs no cudaMalloc / cudaFree, creates no stream or event, and runs every kernel on `stream`.  A config whose
+ * xattn_workspace_bytes exceeds the maximum is refused with XATTN_ERR_WORKSPACE (bf16 path at T=16, Ta=149: B <= 66;
+ * fp32 path: B <= 8).  All calls on a device share the one array: it keeps the last call's contents (nothing needs to start
+ * at zero — every region is written before it is read) and calls that OVERLAP on the GPU (different streams or threads) RACE;
+ * calls ordered by one stream are safe. */
+#define XATTN_NOALLOC_MAX_WORKSPACE_BYTES (8 * 1024 * 1024)
+XATTN_API int64_t xattn_noalloc_max_workspace_bytes(void);
+XATTN_API int xattn_forward_noalloc(const xattn_config* cfg, const float* params, const void* packed, const void* video_emb,
+                                    const void* audio_emb, float* logits, void* stream);
 
 /* Backward of the same head for the Stage-1 step (frozen backbones => no input gradients).
  * `workspace` must be the buffer a preceding xattn_forward (same cfg, training or

@@ -12,7 +12,7 @@ from pathlib import Path
 
 LIB_NAME = "libxattn_fusion.so"
 LIB_PATH = Path(__file__).resolve().parent / LIB_NAME
-ABI_VERSION = 14
+ABI_VERSION = 15
 
 # xattn_status
 OK, ERR_SHAPE, ERR_DTYPE, ERR_ALIGN, ERR_ARCH, ERR_CUDA, ERR_WORKSPACE, ERR_NULL = range(8)
@@ -94,6 +94,9 @@ _EXPORTS = {
     "xattn_pack_weights": (C.c_int, [C.POINTER(XAttnConfig), C.c_void_p, C.c_void_p, C.c_void_p]),
     "xattn_forward": (C.c_int, [C.POINTER(XAttnConfig), C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
                                 C.c_void_p, C.c_int64, C.c_void_p]),
+    "xattn_noalloc_max_workspace_bytes": (C.c_int64, []),
+    "xattn_forward_noalloc": (C.c_int, [C.POINTER(XAttnConfig), C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
+                                        C.c_void_p]),
     "xattn_backward": (C.c_int, [C.POINTER(XAttnConfig), C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
                                  C.c_void_p, C.c_int64, C.c_void_p]),
     "xattn_ce_loss_fwd_bwd": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_float, C.c_float, C.c_void_p,

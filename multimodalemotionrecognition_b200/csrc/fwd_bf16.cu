@@ -252,7 +252,7 @@ int launch_video_update(const Bf16Ctx& x) {
 }
 
 int forward_bf16(const xattn_config& c, const float* params, const void* packed, const void* xv, const void* xa, float* logits,
-                 void* ws, cudaStream_t st) {
+                 void* ws, cudaStream_t st, bool fork) {
   XF_TRY(bf16_supported(c));
   Bf16Ctx x;
   x.cfg = &c;
@@ -269,7 +269,8 @@ int forward_bf16(const xattn_config& c, const float* params, const void* packed,
   // everything stays on the caller's stream so the brackets measure one kernel each.
   cudaStream_t side = st;
   cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
-  if (!g_stage_timing) {
+  static const bool no_fork_env = getenv("XATTN_NO_FORK") != nullptr;
+  if (fork && !no_fork_env && !g_stage_timing) {
     XF_TRY(side_stream(&side));
     XF_CUDA(cudaEventCreateWithFlags(&ev_fork, cudaEventDisableTiming));
     XF_CUDA(cudaEventCreateWithFlags(&ev_join, cudaEventDisableTiming));
