@@ -91,8 +91,8 @@ typedef struct xattn_config {
 } xattn_config;
 
 /* Parameter ids: order of the flat parameter / gradient buffer.  Names are the reference's
- * state_dict keys.  audio_time_conv.* is deliberately absent: it is unused on the
- * WavLM path and receives no gradient (fusion.py:273, :379-384). */
+ * state_dict keys.  audio_time_conv.* has no id of its own: on the WavLM path it is unused and receives no
+ * gradient (fusion.py:273, :379-384); with the mel front end (xattn_mel_unfold) it is bound to the XP_SEQ_W / XP_SEQ_B slots. */
 typedef enum xattn_param_id {
   XP_V_IN_W = 0,   /* v_in_proj.weight            [E,Dv]   */
   XP_V_IN_B,       /* v_in_proj.bias              [E]      */
@@ -286,12 +286,6 @@ XATTN_API int flat_head_alignment_workspace_bytes(const flat_head_config* cfg, i
 XATTN_API int flat_head_alignment_loss(const flat_head_config* cfg, const float* params, const float* logit_scale, const void* video_emb,
                                        const void* audio_emb, float* loss, void* workspace, int64_t workspace_bytes, void* stream);
 
-/* One tensor-core GEMM of the training path in isolation (tests): form 0: C[M,N] = A[M,K]·W[N,K]^T + bias; form 1: C[M,N] =
- * A[M,K]·W[K,N]; form 2: C[N1=K... see gemm_tc.cuh] C[N,K] += A[M,N]^T·B[M,K] with fp32 operands; form 3: the same with bf16
- * operands.  C is fp32. */
-XATTN_API int xattn_debug_gemm_tf32(int32_t form, const void* A, const void* B, const float* bias, float* C, int32_t M, int32_t N,
-                                    int32_t K, int32_t relu, int32_t accumulate, void* stream);
-
 /* ---- diagnostics ---------------------------------------------------------------------------------- */
 /* Kernel launches issued by this library since process start (bench.py's gpu_launches evidence). */
 XATTN_API unsigned long long xattn_launch_count(void);
@@ -302,20 +296,6 @@ XATTN_API unsigned long long xattn_launch_count(void);
 XATTN_API int xattn_stage_timing(int32_t enable);
 XATTN_API int xattn_stage_timing_read(double* ms_total, int64_t* launches, int32_t cap);
 XATTN_API const char* xattn_stage_name(int32_t i);
-/* The tcgen05/TMA projection GEMM on its own: Y[M,N] = X[M,K]·W[N,K]^T + bias (X, W bf16; Y bf16 or fp32 with row
- * pitch out_pitch in elements; N % 128 == 0, K % 64 == 0).  This is the kernel behind v_in_proj (fusion.py:372) and
- * a_in_proj∘audio_seq_proj (:378, :386) in xattn_forward(precision = BF16); exported so tests can pin it in isolation. */
-XATTN_API int xattn_debug_gemm_tc(const void* X, const void* W, const float* bias, void* Y, int32_t out_bf16, int64_t out_pitch,
-                        int32_t M, int32_t N, int32_t K, void* stream);
-
-/* Hardware probe of the tcgen05 features the attention kernels use (M = 64 accumulators in both halves of a TMEM
- * sub-partition, MN-major B operand, hand-swizzled operand tiles, 16x256b TMEM loads): two products in one CTA,
- * D_lo = A[0:64]·op(B[0]), D_hi = A[64:128]·op(B[1]); A [128,K] bf16; mode 0: B [2,N,K] (K-major), mode 1: B [2,K,N]
- * (MN-major).  out32 [128,N] = raw TMEM lanes x columns (32x32b loads), out16 [2,4,32,64] = raw 16x256b.x16 registers
- * (N >= 128).  Test-only; not on the product path. */
-XATTN_API int xattn_debug_umma_probe(const void* A, const void* B, float* out32, float* out16, int32_t N, int32_t K,
-                           int32_t mode, void* stream);
-
 #ifdef __cplusplus
 }
 #endif

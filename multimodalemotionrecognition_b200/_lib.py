@@ -12,6 +12,7 @@ from pathlib import Path
 
 LIB_NAME = "libxattn_fusion.so"
 LIB_PATH = Path(__file__).resolve().parent / LIB_NAME
+DEBUG_LIB_PATH = Path(__file__).resolve().parent / "libxattn_fusion_debug.so"
 ABI_VERSION = 15
 
 # xattn_status
@@ -109,18 +110,22 @@ _EXPORTS = {
     "flat_head_alignment_workspace_bytes": (C.c_int, [C.POINTER(FlatHeadConfig), C.POINTER(C.c_int64)]),
     "flat_head_alignment_loss": (C.c_int, [C.POINTER(FlatHeadConfig), C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
                                            C.c_void_p, C.c_int64, C.c_void_p]),
-    "xattn_debug_gemm_tc": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_int64, C.c_int32, C.c_int32,
-                                      C.c_int32, C.c_void_p]),
     "xattn_softmax_top1": (C.c_int, [C.c_void_p, C.c_int32, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     "xattn_mel_unfold": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_void_p]),
+    "flat_head_forward": (C.c_int, [C.POINTER(FlatHeadConfig), C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
+                                    C.c_int64, C.c_void_p]),
+}
+# test-only entry points of libxattn_fusion_debug.so (include/xattn_fusion_debug.h); the product library does not export them
+_DEBUG_EXPORTS = {
+    "xattn_debug_gemm_tc": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_int64, C.c_int32, C.c_int32,
+                                      C.c_int32, C.c_void_p]),
     "xattn_debug_gemm_tf32": (C.c_int, [C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_int32,
                                         C.c_int32, C.c_int32, C.c_void_p]),
     "xattn_debug_umma_probe": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_int32,
                                          C.c_void_p]),
-    "flat_head_forward": (C.c_int, [C.POINTER(FlatHeadConfig), C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
-                                    C.c_int64, C.c_void_p]),
 }
 EXPORTED_SYMBOLS = tuple(_EXPORTS)
+DEBUG_SYMBOLS = tuple(_DEBUG_EXPORTS)
 
 _lib = None
 
@@ -144,6 +149,33 @@ def load() -> C.CDLL:
         raise RuntimeError(f"{path}: ABI version {lib.xattn_abi_version()} != expected {ABI_VERSION}; rebuild")
     _lib = lib
     return lib
+
+
+_dbg = None
+
+
+def load_debug() -> C.CDLL:
+    """The test library: the product objects plus the ``xattn_debug_*`` entry points (tests only; a second, self-contained
+    library with its own error text — read it with ``debug_check``)."""
+    global _dbg
+    if _dbg is not None:
+        return _dbg
+    if not DEBUG_LIB_PATH.exists():
+        raise RuntimeError(f"{DEBUG_LIB_PATH} not found: run `python __graft_entry__.py build`")
+    lib = C.CDLL(str(DEBUG_LIB_PATH))
+    for name, (res, args) in {**_EXPORTS, **_DEBUG_EXPORTS}.items():
+        fn = getattr(lib, name)
+        fn.restype = res
+        fn.argtypes = args
+    _dbg = lib
+    return lib
+
+
+def debug_check(status: int) -> None:
+    if status != OK:
+        msg = load_debug().xattn_last_error().decode("utf-8", "replace")
+        raise (ValueError if status in (ERR_SHAPE, ERR_DTYPE, ERR_ALIGN, ERR_NULL) else RuntimeError)(
+            f"xattn_fusion_debug: {msg} (status {status})")
 
 
 def last_error() -> str:

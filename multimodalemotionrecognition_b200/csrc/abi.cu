@@ -10,9 +10,6 @@ int adam_step(float* p, const float* g, float* m, float* v, int64_t n, float lr,
               int step, int decoupled, cudaStream_t st);
 }  // namespace xf
 
-namespace xf {
-int umma_probe(cudaStream_t st, const void* A, const void* B, float* out32, float* out16, int N, int K, int mode);
-}
 using namespace xf;
 
 static inline bool misaligned(const void* p) { return ((uintptr_t)p & 15) != 0; }
@@ -125,30 +122,4 @@ extern "C" XATTN_API int xattn_adam_step(float* params, const float* grads, floa
     XF_FAIL(XATTN_ERR_ALIGN, "pointers must be 16-byte aligned");
   XF_TRY(check_device_sm100());
   return adam_step(params, grads, exp_avg, exp_avg_sq, n, lr, beta1, beta2, eps, weight_decay, step, decoupled, (cudaStream_t)stream);
-}
-
-extern "C" XATTN_API int xattn_debug_gemm_tc(const void* X, const void* W, const float* bias, void* Y, int32_t out_bf16, int64_t out_pitch,
-                                   int32_t M, int32_t N, int32_t K, void* stream) {
-  if (!X || !W || !bias || !Y) XF_FAIL(XATTN_ERR_NULL, "NULL pointer argument");
-  if (misaligned(X) || misaligned(W) || misaligned(Y)) XF_FAIL(XATTN_ERR_ALIGN, "pointers must be 16-byte aligned");
-  XF_TRY(check_device_sm100());
-  return gemm_tc_bf16((cudaStream_t)stream, X, W, bias, Y, out_bf16 != 0, out_pitch, M, N, K);
-}
-
-extern "C" XATTN_API int xattn_debug_gemm_tf32(int32_t form, const void* A, const void* B, const float* bias, float* C, int32_t M, int32_t N,
-                                               int32_t K, int32_t relu, int32_t accumulate, void* stream) {
-  if (!A || !B || !C) XF_FAIL(XATTN_ERR_NULL, "NULL pointer argument");
-  XF_TRY(check_device_sm100());
-  cudaStream_t st = (cudaStream_t)stream;
-  if (form == 0 || form == 1)
-    return gemm_tf32_rows(st, (const float*)A, K, (const float*)B, form == 1, bias, C, N, M, N, K, relu != 0, accumulate != 0);
-  if (form == 2 || form == 3) return gemm_cols(st, A, N, B, K, form == 3, C, K, M, N, K);
-  XF_FAIL(XATTN_ERR_SHAPE, "xattn_debug_gemm_tf32: unknown form %d", form);
-}
-
-extern "C" XATTN_API int xattn_debug_umma_probe(const void* A, const void* B, float* out32, float* out16, int32_t N, int32_t K,
-                                                int32_t mode, void* stream) {
-  XF_TRY(check_device_sm100());
-  if (!A || !B || !out32 || !out16) XF_FAIL(XATTN_ERR_NULL, "xattn_debug_umma_probe: null pointer");
-  return umma_probe(reinterpret_cast<cudaStream_t>(stream), A, B, out32, out16, N, K, mode);
 }

@@ -113,6 +113,11 @@ int num_sms() {
     cudaGetDevice(&dev);
     cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
     if (n <= 0) n = 148;
+    // experiments: cap the grid of every persistent kernel (SM partitioning between concurrent streams)
+    if (const char* e = getenv("XATTN_MAX_CTAS")) {
+      const int cap = atoi(e);
+      if (cap > 0 && cap < n) n = cap;
+    }
   }
   return n;
 }

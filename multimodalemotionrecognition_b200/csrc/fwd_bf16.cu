@@ -3,6 +3,8 @@
 #include <stdlib.h>
 #include <string.h>
 
+#include <mutex>
+
 #include "bf16_layout.cuh"
 #include "gemm_tc.cuh"
 #include "kernels_bf16.cuh"
@@ -228,14 +230,27 @@ int launch_head_pooled(const Bf16Ctx& x, float* logits) {
   return XATTN_OK;
 }
 
-// One private non-blocking stream per device for the forked video branch.
-static int side_stream(cudaStream_t* out) {
-  static cudaStream_t streams[64] = {};
+// Per-device resources of the forked video branch: one private non-blocking stream and the fork / join events, created once
+// (under a lock: two threads may call into the same device for the first time together) and reused by every forward.
+// Re-recording an event that an earlier forward's cudaStreamWaitEvent already consumed is safe: a wait captures the event's
+// state at the time it is enqueued.
+struct ForkRes {
+  cudaStream_t side = nullptr;
+  cudaEvent_t fork = nullptr, join = nullptr;
+  std::mutex enqueue;   // held while one forward enqueues its fork .. join: the events are shared by every caller of the device
+};
+static int fork_resources(ForkRes** out) {
+  static ForkRes res[64];
+  static std::mutex mu;
   int dev = 0;
   XF_CUDA(cudaGetDevice(&dev));
   if (dev < 0 || dev >= 64) XF_FAIL(XATTN_ERR_CUDA, "device index %d out of range", dev);
-  if (streams[dev] == nullptr) XF_CUDA(cudaStreamCreateWithFlags(&streams[dev], cudaStreamNonBlocking));
-  *out = streams[dev];
+  std::lock_guard<std::mutex> lock(mu);
+  ForkRes& r = res[dev];
+  if (r.side == nullptr) XF_CUDA(cudaStreamCreateWithFlags(&r.side, cudaStreamNonBlocking));
+  if (r.fork == nullptr) XF_CUDA(cudaEventCreateWithFlags(&r.fork, cudaEventDisableTiming));
+  if (r.join == nullptr) XF_CUDA(cudaEventCreateWithFlags(&r.join, cudaEventDisableTiming));
+  *out = &r;
   return XATTN_OK;
 }
 
@@ -268,14 +283,15 @@ int forward_bf16(const xattn_config& c, const float* params, const void* packed,
   // branch is forked onto a private stream and joined before the first kernel that needs both.  With per-kernel timing on
   // everything stays on the caller's stream so the brackets measure one kernel each.
   cudaStream_t side = st;
-  cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
+  ForkRes* fr = nullptr;
+  std::unique_lock<std::mutex> enqueue_lock;
   static const bool no_fork_env = getenv("XATTN_NO_FORK") != nullptr;
   if (fork && !no_fork_env && !g_stage_timing) {
-    XF_TRY(side_stream(&side));
-    XF_CUDA(cudaEventCreateWithFlags(&ev_fork, cudaEventDisableTiming));
-    XF_CUDA(cudaEventCreateWithFlags(&ev_join, cudaEventDisableTiming));
-    XF_CUDA(cudaEventRecord(ev_fork, st));
-    XF_CUDA(cudaStreamWaitEvent(side, ev_fork, 0));
+    XF_TRY(fork_resources(&fr));
+    enqueue_lock = std::unique_lock<std::mutex>(fr->enqueue);
+    side = fr->side;
+    XF_CUDA(cudaEventRecord(fr->fork, st));
+    XF_CUDA(cudaStreamWaitEvent(side, fr->fork, 0));
   }
   int rc = XATTN_OK;
   {
@@ -296,11 +312,10 @@ int forward_bf16(const xattn_config& c, const float* params, const void* packed,
                       BOP, c.B * c.Ta, BE, c.Da, c.use_prior ? reinterpret_cast<const float*>(x.packed + x.pk.scw) : nullptr,
                       reinterpret_cast<float*>(x.ws + x.w.tok), reinterpret_cast<float*>(x.ws + x.w.acol), c.Ta);
   }
-  if (ev_fork != nullptr) {   // always rejoin, also on an error above, so the caller's stream stays ordered after the side work
-    cudaEventRecord(ev_join, side);
-    cudaStreamWaitEvent(st, ev_join, 0);
-    cudaEventDestroy(ev_fork);
-    cudaEventDestroy(ev_join);
+  if (fr != nullptr) {   // always rejoin, also on an error above, so the caller's stream stays ordered after the side work
+    cudaEventRecord(fr->join, side);
+    cudaStreamWaitEvent(st, fr->join, 0);
+    enqueue_lock.unlock();
   }
   XF_TRY(rc);
   if (c.use_prior) { StageScope t(ST_PRIOR, st); XF_TRY(launch_prior(x)); }

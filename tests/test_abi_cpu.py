@@ -14,8 +14,8 @@ from helpers import load_npz, make_head, sha
 ROOT = Path(__file__).resolve().parents[1]
 
 
-def _declared_symbols():
-    text = (ROOT / "include" / "xattn_fusion.h").read_text()
+def _declared_symbols(header="xattn_fusion.h"):
+    text = (ROOT / "include" / header).read_text()
     return sorted(set(re.findall(r"XATTN_API\s+[\w\s\*]+?\b((?:xattn|flat_head)_\w+)\s*\(", text)))
 
 
@@ -29,6 +29,19 @@ def test_library_exports_every_declared_symbol():
         assert hasattr(lib, name), f"{name} declared in include/xattn_fusion.h but not exported"
         assert name in _lib.EXPORTED_SYMBOLS, f"{name} has no ctypes prototype"
     assert lib.xattn_abi_version() == _lib.ABI_VERSION
+
+
+def test_debug_entry_points_live_in_the_test_library_only():
+    from multimodalemotionrecognition_b200 import _lib
+
+    lib, dbg = _lib.load(), _lib.load_debug()
+    declared = _declared_symbols("xattn_fusion_debug.h")
+    assert sorted(declared) == sorted(_lib.DEBUG_SYMBOLS), declared
+    for name in declared:
+        assert hasattr(dbg, name), f"{name} declared in include/xattn_fusion_debug.h but not exported by the test library"
+        assert not hasattr(lib, name), f"{name} is test scaffolding and must not ship in the product library"
+    for name in _declared_symbols():   # the test library is the product plus the debug entry points
+        assert hasattr(dbg, name), name
 
 
 def test_param_layout_matches_state_dict_shapes():

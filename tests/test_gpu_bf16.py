@@ -21,7 +21,7 @@ def _gemm_tc(x, w, bias, out_bf16, pitch=None):
     N = w.shape[0]
     pitch = N if pitch is None else pitch
     out = torch.zeros((M, pitch), dtype=torch.bfloat16 if out_bf16 else torch.float32, device=x.device)
-    _lib.check(_lib.load().xattn_debug_gemm_tc(_ptr(x), _ptr(w), _ptr(bias), _ptr(out), int(out_bf16), pitch, M, N, K,
+    _lib.debug_check(_lib.load_debug().xattn_debug_gemm_tc(_ptr(x), _ptr(w), _ptr(bias), _ptr(out), int(out_bf16), pitch, M, N, K,
                                                _stream_ptr(x.device)))
     torch.cuda.synchronize()
     return out
@@ -167,7 +167,7 @@ def test_umma_probe_m64_halves_and_mn_major(cuda_device, mode, N, K):
     """tcgen05 features of the attention kernels, pinned in isolation: two M=64 products land in lanes 0-15 / 16-31 of each
     TMEM sub-partition; mode 1 feeds B as an MN-major (rows = K) swizzled tile; 16x256b loads return mma C-fragment order."""
     from multimodalemotionrecognition_b200 import _lib
-    lib = _lib.load()
+    lib = _lib.load_debug()
     g = torch.Generator().manual_seed(mode * 7 + N + K)
     A = torch.randn(128, K, generator=g).bfloat16()
     ts, mode_b = mode >= 2, mode & 1          # modes 2/3: A operand in tensor memory
@@ -175,7 +175,7 @@ def test_umma_probe_m64_halves_and_mn_major(cuda_device, mode, N, K):
     Ad, Bd = A.to(cuda_device), B.to(cuda_device)
     out32 = torch.full((128, N), float("nan"), device=cuda_device)
     out16 = torch.full((2, 4, 32, 64), float("nan"), device=cuda_device)
-    _lib.check(lib.xattn_debug_umma_probe(Ad.data_ptr(), Bd.data_ptr(), out32.data_ptr(), out16.data_ptr(), N, K, mode,
+    _lib.debug_check(lib.xattn_debug_umma_probe(Ad.data_ptr(), Bd.data_ptr(), out32.data_ptr(), out16.data_ptr(), N, K, mode,
                                           torch.cuda.current_stream().cuda_stream))
     torch.cuda.synchronize()
     ref = []

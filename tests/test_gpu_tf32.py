@@ -15,7 +15,7 @@ def _gemm(form, A, B, bias, C, M, N, K, relu=False, accumulate=False):
     from multimodalemotionrecognition_b200 import _lib
     from multimodalemotionrecognition_b200.fusion import _ptr, _stream_ptr
 
-    _lib.check(_lib.load().xattn_debug_gemm_tf32(form, _ptr(A), _ptr(B), _ptr(bias), _ptr(C), M, N, K, int(relu), int(accumulate),
+    _lib.debug_check(_lib.load_debug().xattn_debug_gemm_tf32(form, _ptr(A), _ptr(B), _ptr(bias), _ptr(C), M, N, K, int(relu), int(accumulate),
                                                  _stream_ptr(A.device)))
     torch.cuda.synchronize()
 
