@@ -26,7 +26,7 @@
 extern "C" {
 #endif
 
-#define XATTN_ABI_VERSION 15
+#define XATTN_ABI_VERSION 16
 
 #if defined(__GNUC__)
 #define XATTN_API __attribute__((visibility("default")))
@@ -212,6 +212,17 @@ XATTN_API int xattn_forward_noalloc(const xattn_config* cfg, const float* params
  * Replaces: loss.backward() over the fusion parameters at train.py:227. */
 XATTN_API int xattn_backward(const xattn_config* cfg, const float* params, const void* video_emb, const void* audio_emb,
                    const float* dlogits, float* grads, void* workspace, int64_t workspace_bytes, void* stream);
+
+/* xattn_backward with two options.
+ *  - tail_stream (a cudaStream_t, may be NULL): the library makes it wait for the point of `stream` where every gradient except
+ *    the input projections' — the flat buffer from *tail_offset_floats (= the offset of XP_V2A_IN_W) to its end — is final, so a
+ *    data-parallel caller can all-reduce that part on tail_stream while the input-projection backward is still running
+ *    ("launch it on a side stream as soon as the last backward kernel writes the bucket").
+ *  - d_video_emb [B,T,Dv] / d_audio_emb [B,Ta,Da] (fp32, may be NULL): gradients w.r.t. the embeddings, for Stage 2 of the
+ *    reference where backbone layers are trainable (train.py:815-830; loss.backward() at :227 then reaches v_feat / a_seq). */
+XATTN_API int xattn_backward_ex(const xattn_config* cfg, const float* params, const void* video_emb, const void* audio_emb,
+                      const float* dlogits, float* grads, void* workspace, int64_t workspace_bytes, void* stream,
+                      void* tail_stream, int64_t* tail_offset_floats, float* d_video_emb, float* d_audio_emb);
 
 /* ---- loss / optimizer ------------------------------------------------------------------------ */
 /* Mean-reduced cross entropy with label smoothing + its gradient w.r.t. logits.

@@ -32,6 +32,12 @@ XATTN_API int xattn_debug_gemm_tc(const void* X, const void* W, const float* bia
 XATTN_API int xattn_debug_umma_probe(const void* A, const void* B, float* out32, float* out16, int32_t N, int32_t K,
                            int32_t mode, void* stream);
 
+/* The dropout factors (0 or 1/keep) the training kernels draw for Philox stream `rng_stream` (1 attention v2a, 2 attention a2v,
+ * 3 / 4 stochastic depth video / audio, 5 head, 6 prior_net, 7 / 8 attention pooler video / audio) and element indices
+ * [idx0, idx0 + n); seed / offset as in xattn_config.  out: n floats. */
+XATTN_API int xattn_debug_dropout_factors(float p, uint64_t seed, uint64_t offset, uint32_t rng_stream, uint64_t idx0, int64_t n,
+                                          float* out, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -13,7 +13,7 @@ from pathlib import Path
 LIB_NAME = "libxattn_fusion.so"
 LIB_PATH = Path(__file__).resolve().parent / LIB_NAME
 DEBUG_LIB_PATH = Path(__file__).resolve().parent / "libxattn_fusion_debug.so"
-ABI_VERSION = 15
+ABI_VERSION = 16
 
 # xattn_status
 OK, ERR_SHAPE, ERR_DTYPE, ERR_ALIGN, ERR_ARCH, ERR_CUDA, ERR_WORKSPACE, ERR_NULL = range(8)
@@ -100,6 +100,8 @@ _EXPORTS = {
                                         C.c_void_p]),
     "xattn_backward": (C.c_int, [C.POINTER(XAttnConfig), C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
                                  C.c_void_p, C.c_int64, C.c_void_p]),
+    "xattn_backward_ex": (C.c_int, [C.POINTER(XAttnConfig), C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
+                                    C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.POINTER(C.c_int64), C.c_void_p, C.c_void_p]),
     "xattn_ce_loss_fwd_bwd": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_float, C.c_float, C.c_void_p,
                                         C.c_void_p, C.c_void_p]),
     "xattn_adam_step": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_float, C.c_float,
@@ -117,6 +119,8 @@ _EXPORTS = {
 }
 # test-only entry points of libxattn_fusion_debug.so (include/xattn_fusion_debug.h); the product library does not export them
 _DEBUG_EXPORTS = {
+    "xattn_debug_dropout_factors": (C.c_int, [C.c_float, C.c_uint64, C.c_uint64, C.c_uint32, C.c_uint64, C.c_int64, C.c_void_p,
+                                              C.c_void_p]),
     "xattn_debug_gemm_tc": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_int64, C.c_int32, C.c_int32,
                                       C.c_int32, C.c_void_p]),
     "xattn_debug_gemm_tf32": (C.c_int, [C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_int32,

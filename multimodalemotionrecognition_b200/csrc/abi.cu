@@ -107,6 +107,47 @@ extern "C" XATTN_API int xattn_backward(const xattn_config* cfg, const float* pa
   return backward_f32(*cfg, params, video_emb, audio_emb, dlogits, grads, workspace, (cudaStream_t)stream);
 }
 
+extern "C" XATTN_API int xattn_backward_ex(const xattn_config* cfg, const float* params, const void* video_emb, const void* audio_emb,
+                                           const float* dlogits, float* grads, void* workspace, int64_t workspace_bytes, void* stream,
+                                           void* tail_stream, int64_t* tail_offset_floats, float* d_video_emb, float* d_audio_emb) {
+  XF_TRY(validate_config(cfg));
+  if (tail_offset_floats) {
+    ParamLayout L;
+    compute_param_layout(*cfg, L);
+    *tail_offset_floats = L.off[XP_V2A_IN_W];
+  }
+  if (!params || !video_emb || !audio_emb || !dlogits || !grads || !workspace) XF_FAIL(XATTN_ERR_NULL, "NULL pointer argument");
+  if (misaligned(params) || misaligned(video_emb) || misaligned(audio_emb) || misaligned(workspace) || misaligned(grads) ||
+      misaligned(d_video_emb) || misaligned(d_audio_emb))
+    XF_FAIL(XATTN_ERR_ALIGN, "pointers must be 16-byte aligned");
+  if (cfg->precision == XATTN_DTYPE_BF16) XF_FAIL(XATTN_ERR_DTYPE, "xattn_backward runs with precision=f32 or tf32");
+  if (!cfg->training && !cfg->save_for_backward)
+    XF_FAIL(XATTN_ERR_WORKSPACE, "forward was not run with training or save_for_backward set: no saved activations");
+  XF_TRY(check_device_sm100());
+  int64_t need = 0;
+  XF_TRY(xattn_workspace_bytes(cfg, &need));
+  if (workspace_bytes < need)
+    XF_FAIL(XATTN_ERR_WORKSPACE, "workspace too small: %lld < %lld bytes", (long long)workspace_bytes, (long long)need);
+  cudaStream_t st = (cudaStream_t)stream;
+  if (cfg->B == 0) {
+    ParamLayout L;
+    compute_param_layout(*cfg, L);
+    XF_CUDA(cudaMemsetAsync(grads, 0, sizeof(float) * L.total, st));
+    if (tail_stream) {
+      cudaEvent_t ev = nullptr;
+      XF_TRY(device_event(0, &ev));
+      XF_CUDA(cudaEventRecord(ev, st));
+      XF_CUDA(cudaStreamWaitEvent((cudaStream_t)tail_stream, ev, 0));
+    }
+    return XATTN_OK;
+  }
+  BackwardOptions opt;
+  opt.tail_stream = (cudaStream_t)tail_stream;
+  opt.d_video = d_video_emb;
+  opt.d_audio = d_audio_emb;
+  return backward_f32(*cfg, params, video_emb, audio_emb, dlogits, grads, workspace, st, opt);
+}
+
 extern "C" XATTN_API int xattn_ce_loss_fwd_bwd(const float* logits, const int64_t* labels, int32_t B, int32_t C, float label_smoothing,
                                      float grad_scale, float* loss_out, float* dlogits, void* stream) {
   if (!logits || !labels || !loss_out) XF_FAIL(XATTN_ERR_NULL, "NULL pointer argument");

@@ -974,9 +974,13 @@ static int launch_attn_pool_bwd(cudaStream_t st, const AttnPoolBwdArgs& a, int B
 }
 
 // ---- orchestration ------------------------------------------------------------------------------------------------
+// `opt.tail_stream`: made to wait for the point of `st` where every gradient EXCEPT the input projections' (the flat buffer
+// from XP_V2A_IN_W on) is final, so the caller can all-reduce that part while the input-projection backward still runs.
+// `opt.d_video` / `opt.d_audio`: gradients w.r.t. the embeddings (Stage 2 of the reference unfreezes backbone layers,
+// train.py:815-830): dX = dY·W through v_in_proj / audio_seq_proj, fp32 [B,T,Dv] / [B,Ta,Da].
 template <typename TIO>
 static int backward_f32_impl(const xattn_config& c, const float* params, const TIO* xv, const TIO* xa, const float* dlogits,
-                             float* grads, float* ws, cudaStream_t st) {
+                             float* grads, float* ws, cudaStream_t st, const BackwardOptions& opt) {
   ParamLayout pl;
   compute_param_layout(c, pl);
   WsF32 w;
@@ -1123,7 +1127,13 @@ static int backward_f32_impl(const xattn_config& c, const float* params, const T
     XF_LAUNCH_CHECK();
   }
 
-  // ---- input projections (fusion.py:386, :378, :372); the inputs are frozen embeddings: no dX ----
+  if (opt.tail_stream != nullptr) {   // everything but the input projections' gradients is final from here on
+    cudaEvent_t ev = nullptr;
+    XF_TRY(device_event(0, &ev));
+    XF_CUDA(cudaEventRecord(ev, st));
+    XF_CUDA(cudaStreamWaitEvent(opt.tail_stream, ev, 0));
+  }
+  // ---- input projections (fusion.py:386, :378, :372); dX only on request (Stage 1 freezes the backbones) ----
   linear_bwd_dw<float>(st, ws + w.d_a0, E, ws + w.aseq, E, G(XP_A_IN_W), B * Ta, E, E);
   if (!tok_bias_fused) launch_colsum(st, ws + w.d_a0, E, B * Ta, E, G(XP_A_IN_B));
   linear_bwd_dx(st, ws + w.d_a0, E, P(XP_A_IN_W), ws + w.d_aseq, B * Ta, E, E, false);
@@ -1148,19 +1158,21 @@ static int backward_f32_impl(const xattn_config& c, const float* params, const T
     linear_bwd_dw<TIO>(st, ws + w.d_v0, E, xv, c.Dv, G(XP_V_IN_W), B * T, E, c.Dv);
   }
   if (!tok_bias_fused) launch_colsum(st, ws + w.d_v0, E, B * T, E, G(XP_V_IN_B));
+  if (opt.d_audio != nullptr) linear_bwd_dx(st, ws + w.d_aseq, E, P(XP_SEQ_W), opt.d_audio, B * Ta, E, c.Da, false);
+  if (opt.d_video != nullptr) linear_bwd_dx(st, ws + w.d_v0, E, P(XP_V_IN_W), opt.d_video, B * T, E, c.Dv, false);
   XF_LAUNCH_CHECK();
   return XATTN_OK;
 }
 
 int backward_f32(const xattn_config& c, const float* params, const void* xv, const void* xa, const float* dlogits, float* grads,
-                 void* ws, cudaStream_t st) {
+                 void* ws, cudaStream_t st, const BackwardOptions& opt) {
   g_tc_gemm = c.precision == XATTN_PREC_TF32;
   g_tc_status = XATTN_OK;
   int rc;
   if (c.io_dtype == XATTN_DTYPE_BF16)
-    rc = backward_f32_impl<__nv_bfloat16>(c, params, (const __nv_bfloat16*)xv, (const __nv_bfloat16*)xa, dlogits, grads, (float*)ws, st);
+    rc = backward_f32_impl<__nv_bfloat16>(c, params, (const __nv_bfloat16*)xv, (const __nv_bfloat16*)xa, dlogits, grads, (float*)ws, st, opt);
   else
-    rc = backward_f32_impl<float>(c, params, (const float*)xv, (const float*)xa, dlogits, grads, (float*)ws, st);
+    rc = backward_f32_impl<float>(c, params, (const float*)xv, (const float*)xa, dlogits, grads, (float*)ws, st, opt);
   g_tc_gemm = false;
   return rc != XATTN_OK ? rc : g_tc_status;
 }

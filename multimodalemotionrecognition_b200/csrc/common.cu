@@ -5,6 +5,7 @@
 #include <stdarg.h>
 #include <string.h>
 
+#include <mutex>
 #include <vector>
 
 namespace xf {
@@ -120,6 +121,18 @@ int num_sms() {
     }
   }
   return n;
+}
+
+int device_event(int slot, cudaEvent_t* out) {
+  static cudaEvent_t ev[64][4] = {};
+  static std::mutex mu;
+  int dev = 0;
+  XF_CUDA(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= 64 || slot < 0 || slot >= 4) XF_FAIL(XATTN_ERR_CUDA, "device_event: device %d / slot %d out of range", dev, slot);
+  std::lock_guard<std::mutex> lock(mu);
+  if (ev[dev][slot] == nullptr) XF_CUDA(cudaEventCreateWithFlags(&ev[dev][slot], cudaEventDisableTiming));
+  *out = ev[dev][slot];
+  return XATTN_OK;
 }
 
 int validate_config(const xattn_config* c) {

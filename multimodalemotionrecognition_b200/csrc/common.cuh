@@ -46,6 +46,9 @@ const char* last_error();
 int check_device_sm100();           // XATTN_ERR_ARCH unless the current device is sm_100
 int validate_config(const xattn_config* cfg);
 int num_sms();
+// A cached, timing-disabled event of the current device (slot < 4), created once under a lock; for cross-stream edges the
+// library inserts itself (record on one stream, cudaStreamWaitEvent on another: the wait captures the record made before it).
+int device_event(int slot, cudaEvent_t* out);
 
 // Count of kernels this library launched since process start (bench.py's gpu_launches claim).
 extern unsigned long long g_launch_count;

@@ -37,3 +37,23 @@ extern "C" XATTN_API int xattn_debug_umma_probe(const void* A, const void* B, fl
   if (!A || !B || !out32 || !out16) XF_FAIL(XATTN_ERR_NULL, "xattn_debug_umma_probe: null pointer");
   return umma_probe(reinterpret_cast<cudaStream_t>(stream), A, B, out32, out16, N, K, mode);
 }
+
+// The dropout factors (0 or 1/keep) every kernel of the training path draws: drop_factor(p, seed, offset, stream, idx) for idx in
+// [idx0, idx0 + n).  tests/test_gpu_rng.py reconstructs each dropout site of the reference from them (fusion.py:18-26, :161,
+// :277/:280, :315; temporal.py:19) and checks keep-rate and 1/keep scaling.
+namespace {
+__global__ void dropout_factors_kernel(float p, uint64_t seed, uint64_t offset, uint32_t rng_stream, uint64_t idx0, int64_t n,
+                                       float* __restrict__ out) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) out[i] = xf::drop_factor(p, seed, offset, rng_stream, idx0 + (uint64_t)i);
+}
+}  // namespace
+extern "C" XATTN_API int xattn_debug_dropout_factors(float p, uint64_t seed, uint64_t offset, uint32_t rng_stream, uint64_t idx0,
+                                                     int64_t n, float* out, void* stream) {
+  if (!out) XF_FAIL(XATTN_ERR_NULL, "NULL pointer argument");
+  XF_TRY(check_device_sm100());
+  if (n <= 0) return XATTN_OK;
+  dropout_factors_kernel<<<(unsigned)((n + 255) / 256), 256, 0, (cudaStream_t)stream>>>(p, seed, offset, rng_stream, idx0, n, out);
+  XF_LAUNCH_CHECK();
+  return XATTN_OK;
+}

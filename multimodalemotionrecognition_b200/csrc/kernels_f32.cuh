@@ -62,7 +62,12 @@ int launch_attn_fwd(cudaStream_t st, const AttnArgs& a, int B);
 
 int forward_f32(const xattn_config& c, const float* params, const void* xv, const void* xa, float* logits, void* ws,
                 cudaStream_t st);
+struct BackwardOptions {
+  cudaStream_t tail_stream = nullptr;   // see backward_f32_impl
+  float* d_video = nullptr;             // [B,T,Dv] fp32 or nullptr
+  float* d_audio = nullptr;             // [B,Ta,Da] fp32 or nullptr
+};
 int backward_f32(const xattn_config& c, const float* params, const void* xv, const void* xa, const float* dlogits,
-                 float* grads, void* ws, cudaStream_t st);
+                 float* grads, void* ws, cudaStream_t st, const BackwardOptions& opt = BackwardOptions());
 
 }  // namespace xf

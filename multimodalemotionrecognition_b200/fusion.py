@@ -138,12 +138,15 @@ class _XAttnFunction(torch.autograd.Function):
     @staticmethod
     def backward(ctx, dlogits):
         owner = ctx.owner
-        gflat = owner._launch_backward(ctx.state, dlogits.contiguous().float())
+        # ctx.needs_input_grad: (owner, video_emb, audio_emb, *params).  Stage 1 freezes the backbones (train.py:808-812), so the
+        # embeddings need no gradient; Stage 2 (train.py:815-830) unfreezes backbone layers and loss.backward() must reach them.
+        need_v, need_a = ctx.needs_input_grad[1], ctx.needs_input_grad[2]
+        gflat, d_video, d_audio = owner._launch_backward(ctx.state, dlogits.contiguous().float(), input_grads=(need_v, need_a))
         grads = []
         for p, (off, n) in zip(ctx.params, owner._xattn_slices):
             grads.append(gflat[off:off + n].view_as(p) if n > 0 else None)
         ctx.state = None
-        return (None, None, None, *grads)
+        return (None, d_video, d_audio, *grads)
 
 
 def softmax_top1(logits: torch.Tensor, probs: Optional[torch.Tensor] = None, top1: Optional[torch.Tensor] = None,
@@ -470,16 +473,37 @@ class XAttnKernelsMixin:
                                                  _stream_ptr(dev)))
         return logits, (cfg, video_emb, audio_emb, ws)
 
-    def _launch_backward(self, state, dlogits: torch.Tensor, grads: Optional[torch.Tensor] = None) -> torch.Tensor:
+    def _launch_backward(self, state, dlogits: torch.Tensor, grads: Optional[torch.Tensor] = None, input_grads=None,
+                         tail_stream: Optional["torch.cuda.Stream"] = None):
+        """``xattn_backward`` into the flat gradient buffer.  With ``input_grads=(need_video, need_audio)`` returns
+        ``(grads, d_video_emb, d_audio_emb)`` (``xattn_backward_ex``; gradients in the embeddings' dtype, None where not asked
+        for).  ``tail_stream``: made to wait for the point where every gradient but the input projections' is final; returns
+        ``(grads, tail_offset)`` then (the flat buffer from ``tail_offset`` on may be all-reduced on that stream)."""
         cfg, video_emb, audio_emb, ws = state
         dev = video_emb.device
         with torch.cuda.device(dev):
             flat = self.flat_parameters()
             if grads is None:
                 grads = torch.empty_like(flat)
-            _lib.check(_lib.load().xattn_backward(C.byref(cfg), _ptr(flat), _ptr(video_emb), _ptr(audio_emb), _ptr(dlogits),
-                                                  _ptr(grads), _ptr(ws), ws.numel(), _stream_ptr(dev)))
-        return grads
+            if input_grads is None and tail_stream is None:
+                _lib.check(_lib.load().xattn_backward(C.byref(cfg), _ptr(flat), _ptr(video_emb), _ptr(audio_emb), _ptr(dlogits),
+                                                      _ptr(grads), _ptr(ws), ws.numel(), _stream_ptr(dev)))
+                return grads
+            need_v, need_a = input_grads if input_grads is not None else (False, False)
+            dv = torch.empty(video_emb.shape, dtype=torch.float32, device=dev) if need_v else None
+            da = torch.empty(audio_emb.shape, dtype=torch.float32, device=dev) if need_a else None
+            tail_off = C.c_int64(0)
+            _lib.check(_lib.load().xattn_backward_ex(
+                C.byref(cfg), _ptr(flat), _ptr(video_emb), _ptr(audio_emb), _ptr(dlogits), _ptr(grads), _ptr(ws), ws.numel(),
+                _stream_ptr(dev), None if tail_stream is None else C.c_void_p(tail_stream.cuda_stream), C.byref(tail_off),
+                _ptr(dv), _ptr(da)))
+        if input_grads is None:
+            return grads, int(tail_off.value)
+        if dv is not None:
+            dv = dv.to(video_emb.dtype)
+        if da is not None:
+            da = da.to(audio_emb.dtype)
+        return grads, dv, da
 
     def graphed_forward(self, B: int, T: int = 16, Ta: int = 149, dtype: torch.dtype = torch.bfloat16,
                         device: Optional[torch.device] = None) -> GraphedForward:
@@ -609,12 +633,16 @@ class XAttnKernelsMixin:
         """logits from video embeddings and a mel spectrogram (``audio_frontend="mel"``, fusion.py:379-411)."""
         if self.audio_frontend != "mel":
             raise ValueError('xattn_forward_mel needs a head built with audio_frontend="mel"')
+        if mel.requires_grad and torch.is_grad_enabled():   # fusion.py:379-384 feeds the loader's spectrogram: data, not a model output
+            raise RuntimeError("the mel front end has no input gradient (its input is the spectrogram itself, fusion.py:379-384)")
         return self.xattn_forward_embeddings(video_emb, self.mel_unfold(mel))
 
     def xattn_forward_embeddings(self, video_emb: torch.Tensor, audio_emb: torch.Tensor) -> torch.Tensor:
-        """logits from backbone embeddings; differentiable w.r.t. the fusion parameters (not the embeddings)."""
+        """logits from backbone embeddings; differentiable w.r.t. the fusion parameters and — when they require grad (Stage 2
+        of the reference unfreezes backbone layers, train.py:815-830) — w.r.t. the embeddings (``xattn_backward_ex``)."""
         params = self._xattn_named_params()
-        need_grad = torch.is_grad_enabled() and any(p is not None and p.requires_grad for p in params)
+        need_grad = torch.is_grad_enabled() and (any(p is not None and p.requires_grad for p in params)
+                                                 or video_emb.requires_grad or audio_emb.requires_grad)
         if need_grad:
             self.flat_parameters()
             live = [p if p is not None else torch.empty(0) for p in params]

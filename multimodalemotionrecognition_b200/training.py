@@ -39,12 +39,18 @@ class Stage1Trainer:
 
     def __init__(self, head: XAttnKernelsMixin, lr: float = 1e-3, weight_decay: float = 1e-4, betas=(0.9, 0.999),
                  eps: float = 1e-8, label_smoothing: float = 0.0, decoupled: bool = False,
-                 process_group: Optional["dist.ProcessGroup"] = None) -> None:
+                 process_group: Optional["dist.ProcessGroup"] = None, overlap_allreduce: bool = True) -> None:
         self.head = head
         self.lr, self.weight_decay, self.betas, self.eps = float(lr), float(weight_decay), betas, float(eps)
         self.label_smoothing = float(label_smoothing)
         self.decoupled = bool(decoupled)
         self.group = process_group
+        # Data parallel: all-reduce the gradients of everything but the input projections on a side stream while the
+        # input-projection backward (the longest GEMMs of the step) still runs; False = one all-reduce after the backward.
+        self.overlap_allreduce = bool(overlap_allreduce)
+        self._side: Optional[torch.cuda.Stream] = None
+        self._tail_work = None
+        self._tail_offset = 0
         self.step_count = 0
         self.exp_avg: Optional[torch.Tensor] = None
         self.exp_avg_sq: Optional[torch.Tensor] = None
@@ -67,14 +73,34 @@ class Stage1Trainer:
         with torch.cuda.device(dev):
             _lib.check(_lib.load().xattn_ce_loss_fwd_bwd(_ptr(logits), _ptr(labels), B, Cn, self.label_smoothing,
                                                          1.0 / self._world(), _ptr(loss), _ptr(dlogits), _stream_ptr(dev)))
-        head._launch_backward(state, dlogits, grads)
+        self._tail_work = None
+        if self._world() > 1 and self.overlap_allreduce:
+            # Two buckets in backward order.  The tail bucket (attention blocks, norms, head, prior: the flat buffer from
+            # v2a_attn.in_proj_weight on) is final before the input-projection backward starts: the library makes the side
+            # stream wait for exactly that point, and its all-reduce runs beside those kernels.
+            if self._side is None or self._side.device != dev:
+                self._side = torch.cuda.Stream(dev)
+            _, self._tail_offset = head._launch_backward(state, dlogits, grads, tail_stream=self._side)
+            with torch.cuda.stream(self._side):
+                self._tail_work = dist.all_reduce(grads[self._tail_offset:], op=dist.ReduceOp.SUM, group=self.group, async_op=True)
+        else:
+            head._launch_backward(state, dlogits, grads)
         self._logits = logits
         return loss
 
     def allreduce_gradients(self) -> None:
-        """Sum the flat gradient bucket over ranks (each rank's loss gradient is pre-scaled by 1/world)."""
-        if self._world() > 1:
-            dist.all_reduce(self.head.flat_gradients(attach=False), op=dist.ReduceOp.SUM, group=self.group)
+        """Sum the flat gradient bucket over ranks (each rank's loss gradient is pre-scaled by 1/world).  With
+        ``overlap_allreduce`` the tail bucket is already in flight (``forward_backward``); this adds the input projections'
+        bucket and joins both before the optimizer."""
+        if self._world() <= 1:
+            return
+        grads = self.head.flat_gradients(attach=False)
+        if self._tail_work is not None:
+            dist.all_reduce(grads[:self._tail_offset], op=dist.ReduceOp.SUM, group=self.group)
+            self._tail_work.wait()            # the current stream waits for the side stream's collective
+            self._tail_work = None
+        else:
+            dist.all_reduce(grads, op=dist.ReduceOp.SUM, group=self.group)
 
     def optimizer_step(self) -> None:
         head = self.head

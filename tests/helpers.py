@@ -59,3 +59,37 @@ def digest(t) -> np.ndarray:
     t = torch.as_tensor(t).detach().double().flatten().cpu()
     idx = torch.linspace(0, t.numel() - 1, steps=8).long()
     return np.concatenate([[t.sum().item(), t.abs().sum().item(), t.norm().item()], t[idx].numpy()])
+
+
+def ws_f32_views(ws: torch.Tensor, cfg) -> dict:
+    """Typed views of the fp32 / tf32 workspace (mirror of compute_ws_f32, csrc/common.cu): name -> float32 tensor (device)."""
+    B, T, Ta, E, H = cfg.B, cfg.T, cfg.Ta, cfg.E, cfg.H
+    P = max(cfg.prior_dim, 1)
+    Hd = max(cfg.prior_hidden, 1)
+    HW = E if cfg.head_kind == 1 else cfg.common_dim
+    bwd = bool(cfg.training or cfg.save_for_backward)
+    spec = [("v0", (B, T, E)), ("aseq", (B, Ta, E)), ("a0", (B, Ta, E)), ("q1", (B, T, E)), ("kv1", (B, Ta, 2 * E)),
+            ("p1", (B, H, T, Ta) if bwd else None), ("o1", (B, T, E)), ("s1", (B, T, E)), ("mean1", (B, T)), ("rstd1", (B, T)),
+            ("v1", (B, T, E)), ("q2", (B, Ta, E)), ("kv2", (B, T, 2 * E)), ("p2", (B, H, Ta, T) if bwd else None),
+            ("o2", (B, Ta, E)), ("s2", (B, Ta, E)), ("mean2", (B, Ta)), ("rstd2", (B, Ta)), ("a1", (B, Ta, E)),
+            ("pooled0", (B, 2 * E)), ("phid", (B, Hd)), ("prior", (B, P)), ("qv", (B, T)), ("ka", (B, Ta)), ("qa", (B, Ta)),
+            ("kvs", (B, T)), ("pooled", (B, 2 * E)), ("hhid", (B, HW)), ("gate", (B,)), ("fusedg", (B, E)), ("dp1", (B,)),
+            ("dp2", (B,))]
+    if bwd:
+        spec += [("d_pooled", (B, 2 * E)), ("d_hh", (B, HW)), ("d_z", (B,)), ("d_fused", (B, E)), ("d_a0", (B, Ta, E)),
+                 ("d_br2", (B, Ta, E)), ("d_o2", (B, Ta, E)), ("d_q2", (B, Ta, E)), ("d_kv2", (B, T, 2 * E)), ("d_v1", (B, T, E)),
+                 ("d_v0", (B, T, E)), ("d_br1", (B, T, E)), ("d_o1", (B, T, E)), ("d_q1", (B, T, E)), ("d_kv1", (B, Ta, 2 * E)),
+                 ("d_aseq", (B, Ta, E)), ("d_qv", (B, T)), ("d_ka", (B, Ta)), ("d_qa", (B, Ta)), ("d_kvs", (B, T)),
+                 ("d_prior", (B, P)), ("d_phid", (B, Hd))]
+    spec += [("wbf", ((E * cfg.Da + E * cfg.Dv + 1) // 2 + 8,))]
+    pooled_tok = cfg.pool_mode != 0
+    spec += [("poolv", (B, E) if pooled_tok else None), ("poola", (B, E) if pooled_tok else None)]
+    f = ws.view(torch.float32) if ws.dtype != torch.float32 else ws
+    out, off = {}, 0
+    for name, shape in spec:
+        if shape is None:
+            continue
+        n = int(np.prod(shape))
+        out[name] = f[off:off + n].view(shape)
+        off += (n + 3) & ~3
+    return out

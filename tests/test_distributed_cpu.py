@@ -47,6 +47,13 @@ def _worker(rank: int, world: int, port: int, total: int):
         tr.allreduce_gradients()
         expect = sum(float(r + 1) for r in range(world)) / world
         assert torch.allclose(g_local, torch.full((10,), expect))
+        # 4. the two-bucket form (tail bucket in flight from forward_backward, head bucket + join in allreduce_gradients)
+        g2 = torch.full((10,), float(rank + 1)) / world
+        tr2 = Stage1Trainer(_FakeHead(g2), overlap_allreduce=True)
+        tr2._tail_offset = 4
+        tr2._tail_work = dist.all_reduce(g2[4:], op=dist.ReduceOp.SUM, async_op=True)
+        tr2.allreduce_gradients()
+        assert tr2._tail_work is None and torch.allclose(g2, torch.full((10,), expect))
     finally:
         dist.destroy_process_group()
 

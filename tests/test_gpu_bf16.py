@@ -127,13 +127,53 @@ def test_bf16_unsupported_shapes_raise_or_route(cuda_device):
     assert out.shape == (2, 8)
 
 
+def structured_inputs(B, seed=11):
+    """SURVEY 8d "structured" distribution: class c ~ U{0..7} per clip, x = N(0,1) + 2*mu_c with fixed per-modality unit
+    vectors mu_c (seed 2) — inputs that carry a class signal, so top-1 is meaningful under random-init weights."""
+    g2 = torch.Generator().manual_seed(2)
+    mu_v = torch.nn.functional.normalize(torch.randn(8, 512, generator=g2), dim=1)
+    mu_a = torch.nn.functional.normalize(torch.randn(8, 768, generator=g2), dim=1)
+    g = torch.Generator().manual_seed(seed)
+    cls = torch.randint(0, 8, (B,), generator=g)
+    xv = torch.randn(B, 16, 512, generator=g) + 2.0 * mu_v[cls][:, None, :]
+    xa = torch.randn(B, 149, 768, generator=g) + 2.0 * mu_a[cls][:, None, :]
+    return xv.bfloat16(), xa.bfloat16(), cls
+
+
+def matched_reference(m, xv, xa):
+    """The quantisation-matched oracle of SURVEY 7.2: the fp32 port of the reference fed the same bf16-rounded inputs AND
+    bf16-rounded weights (the kernels read every matrix as bf16; vectors — biases, LayerNorm affine, score heads — stay fp32)."""
+    sd = {k: (v.detach().cpu().bfloat16().float() if v.ndim >= 2 else v.detach().cpu().clone()) for k, v in m.state_dict().items()}
+    with torch.inference_mode():
+        return torch_port.xattn_forward(sd, xv.float(), xa.float(), num_heads=4)
+
+
+def top1_report(out, ref):
+    err = (out - ref).abs().max().item()
+    top2 = ref.topk(2, dim=1).values
+    margin = top2[:, 0] - top2[:, 1]
+    agree = (out.argmax(1) == ref.argmax(1)).float()
+    return {"max_abs_err": err, "raw_top1_agreement": agree.mean().item(), "disagreeing_clips": int((1 - agree).sum().item()),
+            "near_tie_fraction_margin_lt_2err": (margin < 2 * err).float().mean().item(),
+            "largest_margin_among_disagreements": (margin[agree == 0].max().item() if (agree == 0).any() else 0.0),
+            "median_margin": margin.median().item()}
+
+
 def test_bf16_full_batch_top1_and_tolerance(cuda_device):
-    """BASELINE configs[1] at B=4096: max-abs logit error vs the fp32 port on the same bf16-rounded inputs, top-1
-    agreement >= 99.9 % counted over clips whose reference top1-top2 margin exceeds the bf16 error bound (near-ties
-    reported), clip independence and determinism."""
+    """BASELINE configs[1] at B=4096 against the quantisation-matched oracle.  Gates, all on RAW top-1 agreement (no filtering):
+      * trained weights (the head fitted for 150 Stage-1 steps to the class-structured inputs of SURVEY 8d, so its margins are
+        those of a model that has learnt something): >= 99.9 % — north_star's bar, on a fixture where top-1 means something;
+      * random-init weights, iid N(0,1) and structured inputs: the top1-top2 margin is below 1e-3 for ~1-2 % of the clips by
+        construction (torch's own bf16 run of the reference agrees with fp32 on 99.7 %): >= 99.5 %,
+        and every disagreeing clip must be a near-tie (reference margin below twice the measured max error);
+      * max-abs logit error <= 1e-2 everywhere.
+    The numbers are written to gpurun_out/bf16_top1_report.json (kept under profiles/).  Also: determinism, clip independence."""
+    import json
+    from pathlib import Path
+
     m = make_head("concat", True, seed=0, precision="bf16").to(cuda_device).eval()
-    g = torch.Generator().manual_seed(11)
     B = 4096
+    g = torch.Generator().manual_seed(11)
     xv = torch.randn(B, 16, 512, generator=g).bfloat16()
     xa = torch.randn(B, 149, 768, generator=g).bfloat16()
     with torch.no_grad():
@@ -144,21 +184,45 @@ def test_bf16_full_batch_top1_and_tolerance(cuda_device):
     # Clips are independent.  A clip's position in the batch decides which row tiles of the a2v kernel it lands in, hence
     # the order of its fp32 partial sums: equal up to rounding, not bitwise.
     shift = (out[777:900] - part).abs().max().item()
-    print("batch-position sensitivity:", shift)
     assert shift <= 2e-5, shift
-    sd = {k: v.cpu() for k, v in m.state_dict().items()}
-    with torch.inference_mode():
-        ref = torch_port.xattn_forward(sd, xv.float(), xa.float(), num_heads=4)
-    err = (out.cpu() - ref).abs().max().item()
-    assert err <= BF16_TOL, err
-    top2 = ref.topk(2, dim=1).values
-    margin = top2[:, 0] - top2[:, 1]
-    agree = (out.cpu().argmax(1) == ref.argmax(1))
-    print(f"bf16 B=4096: max|err|={err:.3e} raw top-1 agreement={agree.float().mean().item():.5f} "
-          f"near-ties(margin<2*err)={(margin < 2 * err).float().mean().item():.5f}")
-    solid = margin > 2 * err
-    assert agree[solid].float().mean().item() >= 0.999
-    assert agree.float().mean().item() >= 0.98
+    report = {"batch_position_sensitivity": shift}
+    report["iid"] = top1_report(out.cpu(), matched_reference(m, xv, xa))
+    sxv, sxa, _ = structured_inputs(B)
+    with torch.no_grad():
+        sout = m(sxv.to(cuda_device), sxa.to(cuda_device))
+    report["structured"] = top1_report(sout.cpu(), matched_reference(m, sxv, sxa))
+    # trained fixture: fit the head to the structured data with the Stage-1 trainer, then compare on fresh clips
+    from multimodalemotionrecognition_b200.training import Stage1Trainer
+
+    mt = make_head("concat", True, seed=0, precision="tf32").to(cuda_device).train()
+    tr = Stage1Trainer(mt, lr=1e-3, weight_decay=1e-4)
+    for step in range(150):
+        bxv, bxa, bcls = structured_inputs(256, seed=1000 + step)
+        tr.step(bxv.to(cuda_device), bxa.to(cuda_device), bcls.to(cuda_device), training=True)
+    mt.eval()
+    mt.precision = "bf16"
+    txv, txa, tcls = structured_inputs(B, seed=7)
+    with torch.no_grad():
+        tout = mt(txv.to(cuda_device), txa.to(cuda_device)).cpu()
+    tref = matched_reference(mt, txv, txa)
+    report["trained"] = top1_report(tout, tref)
+    report["trained"]["accuracy_b200"] = (tout.argmax(1) == tcls).float().mean().item()
+    report["trained"]["accuracy_oracle"] = (tref.argmax(1) == tcls).float().mean().item()
+    outdir = Path(__file__).resolve().parents[1] / "gpurun_out"
+    if outdir.is_dir():
+        (outdir / "bf16_top1_report.json").write_text(json.dumps(report, indent=1))
+    print("bf16 B=4096 top-1 report:", json.dumps(report))
+    report["trained"]["max_abs_logit"] = tref.abs().max().item()
+    for name, r in report.items():
+        if name == "batch_position_sensitivity":
+            continue
+        # 1e-2 absolute is north_star's bar at random-init scale (|logit| < 1); the trained head's logits are ~20x larger
+        assert r["max_abs_err"] <= BF16_TOL * max(1.0, r.get("max_abs_logit", 0.0) / 4), (name, r)
+        assert r["largest_margin_among_disagreements"] <= 2 * r["max_abs_err"], (name, r)   # only near-ties may flip
+    assert report["trained"]["raw_top1_agreement"] >= 0.999, report
+    assert report["trained"]["accuracy_oracle"] >= 0.9, report          # the fixture really learnt the classes
+    assert report["structured"]["raw_top1_agreement"] >= 0.995, report
+    assert report["iid"]["raw_top1_agreement"] >= 0.995, report
 
 
 @pytest.mark.parametrize("mode,N,K", [(0, 160, 128), (1, 128, 160), (0, 64, 128), (1, 128, 64), (2, 160, 128), (3, 128, 160),

@@ -1,0 +1,103 @@
+"""GPU tests (``-m gpu``) of the data-parallel Stage-1 step: the parameters after one
+batch-sharded step — per-rank forward/backward on a contiguous shard, loss gradient pre-scaled by 1/world, ONE sum
+all-reduce of the flat gradient bucket, fused Adam — equal the parameters after one single-rank step on the whole batch.
+
+* ``test_sharded_gradients_sum_to_full_batch_gradients``: the arithmetic of the all-reduce emulated on ONE GPU (always runs).
+* ``test_two_rank_nccl_step_equals_single_rank_step``: two processes, two GPUs, NCCL (skipped on a 1-GPU box; run with
+  ``gpurun --gpus 2``).  Also covers the bucketed / overlapped all-reduce against the single-bucket one."""
+import os
+import socket
+
+import pytest
+import torch
+
+from helpers import make_head
+
+pytestmark = pytest.mark.gpu
+TOL = 1e-6
+
+
+def _batch(B, seed=21):
+    g = torch.Generator().manual_seed(seed)
+    return (torch.randn(B, 16, 512, generator=g), torch.randn(B, 149, 768, generator=g), torch.randint(0, 8, (B,), generator=g))
+
+
+def _single_rank_step(dev, xv, xa, lab, precision="fp32"):
+    from multimodalemotionrecognition_b200.training import Stage1Trainer
+
+    m = make_head("concat", True, seed=0, precision=precision).to(dev).train()
+    tr = Stage1Trainer(m, lr=1e-3, weight_decay=1e-4)
+    loss = tr.step(xv.to(dev), xa.to(dev), lab.to(dev), training=False)
+    torch.cuda.synchronize(dev)
+    return float(loss), m.flat_parameters().detach().cpu().clone(), m.flat_gradients(attach=False).detach().cpu().clone()
+
+
+def test_sharded_gradients_sum_to_full_batch_gradients(cuda_device):
+    from multimodalemotionrecognition_b200.training import Stage1Trainer, shard_range
+
+    B, world = 48, 2
+    xv, xa, lab = _batch(B)
+    loss_full, p_full, g_full = _single_rank_step(cuda_device, xv, xa, lab)
+    total = torch.zeros_like(g_full)
+    losses = []
+    for r in range(world):
+        s, e = shard_range(B, r, world)
+        m = make_head("concat", True, seed=0, precision="fp32").to(cuda_device).train()
+        tr = Stage1Trainer(m)
+        losses.append(float(tr.forward_backward(xv[s:e].to(cuda_device), xa[s:e].to(cuda_device), lab[s:e].to(cuda_device),
+                                                training=False)))
+        total += m.flat_gradients(attach=False).detach().cpu() / world     # what grad_scale = 1/world + the sum all-reduce produce
+    assert abs(sum(losses) / world - loss_full) <= 1e-6
+    scale = g_full.abs().max().item()
+    assert (total - g_full).abs().max().item() <= 2e-6 * max(scale, 1.0), ((total - g_full).abs().max().item(), scale)
+
+
+def _free_port():
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
+
+
+def _rank_main(rank, world, port, B, bucketed, out_path):
+    import torch.distributed as dist
+
+    from multimodalemotionrecognition_b200.training import Stage1Trainer, shard_range
+
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world), LOCAL_RANK=str(rank))
+    torch.cuda.set_device(rank)
+    dev = torch.device("cuda", rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=dev)
+    try:
+        xv, xa, lab = _batch(B)
+        s, e = shard_range(B, rank, world)
+        m = make_head("concat", True, seed=0, precision="fp32").to(dev).train()
+        tr = Stage1Trainer(m, lr=1e-3, weight_decay=1e-4, overlap_allreduce=bucketed)
+        loss = tr.step(xv[s:e].to(dev), xa[s:e].to(dev), lab[s:e].to(dev), training=False)
+        torch.cuda.synchronize(dev)
+        flat = m.flat_parameters().detach()
+        gathered = [torch.empty_like(flat) for _ in range(world)]
+        dist.all_gather(gathered, flat)
+        lt = torch.tensor([float(loss)], device=dev)
+        dist.all_reduce(lt)
+        if rank == 0:
+            torch.save({"params": [t.cpu() for t in gathered], "mean_loss": float(lt) / world}, out_path)
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("bucketed", [False, True])
+def test_two_rank_nccl_step_equals_single_rank_step(cuda_device, tmp_path, bucketed):
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs (gpurun --gpus 2)")
+    import torch.multiprocessing as mp
+
+    B, world = 48, 2
+    out_path = str(tmp_path / "ranks.pt")
+    mp.spawn(_rank_main, args=(world, _free_port(), B, bucketed, out_path), nprocs=world, join=True)
+    got = torch.load(out_path)
+    xv, xa, lab = _batch(B)
+    loss_full, p_full, _ = _single_rank_step(cuda_device, xv, xa, lab)
+    assert abs(got["mean_loss"] - loss_full) <= 1e-6
+    for r, p in enumerate(got["params"]):
+        assert (p - p_full).abs().max().item() <= TOL, (r, (p - p_full).abs().max().item())
+    assert torch.equal(got["params"][0], got["params"][1])      # replicas stay bit-identical

@@ -641,3 +641,35 @@ def test_mel_unfold_and_serving_epilogue_edge_cases(cuda_device):
     head = make_head("concat", True, seed=0).to(cuda_device).eval()
     p, t1, t1p = head.predict_host(torch.empty(0, 16, 512, dtype=torch.bfloat16), torch.empty(0, 149, 768, dtype=torch.bfloat16), top1=True)
     assert p.shape == (0, 8) and t1.shape == (0,) and t1p.shape == (0,)
+
+
+@pytest.mark.parametrize("io", ["fp32", "bf16"])
+def test_input_gradients_reach_trainable_backbones(cuda_device, io):
+    """Stage 2 of the reference unfreezes backbone layers (train.py:815-830): loss.backward() at :227 must reach v_feat /
+    a_seq.  The head returns dL/d(video_emb), dL/d(audio_emb) (xattn_backward_ex) — checked against autograd of the CPU port —
+    while the parameter gradients stay what they are without it."""
+    from oracle import torch_port
+
+    m = make_head("concat", True, seed=0, precision="fp32").to(cuda_device).eval()
+    xv, xa, labels = config1_inputs()
+    if io == "bf16":
+        xv, xa = xv.bfloat16(), xa.bfloat16()
+    xvd = xv.to(cuda_device).requires_grad_(True)
+    xad = xa.to(cuda_device).requires_grad_(True)
+    torch.nn.functional.cross_entropy(m(xvd, xad), labels.to(cuda_device)).backward()
+    sd = {k: v.detach().cpu().clone().requires_grad_(True) for k, v in m.state_dict().items()}
+    rv, ra = xv.float().clone().requires_grad_(True), xa.float().clone().requires_grad_(True)
+    torch.nn.functional.cross_entropy(torch_port.xattn_forward(sd, rv, ra, num_heads=4), labels).backward()
+    assert xvd.grad is not None and xvd.grad.dtype == xv.dtype and xvd.grad.shape == xv.shape
+    tol = 1e-6 if io == "fp32" else 1e-2   # bf16 embeddings receive bf16-rounded gradients (relative to the largest entry)
+    for got, ref in ((xvd.grad, rv.grad), (xad.grad, ra.grad)):
+        scale = ref.abs().max().item()
+        assert (got.float().cpu() - ref).abs().max().item() <= tol * scale + 1e-9, (io, scale)
+    gerr = max(float((p.grad.cpu() - sd[k].grad).abs().max()) for k, p in m.named_parameters() if p.grad is not None)
+    assert gerr <= 1e-5, gerr
+    # frozen head, trainable embeddings: still differentiable w.r.t. the inputs
+    for p in m.parameters():
+        p.requires_grad_(False)
+    xv2 = xv.detach().to(cuda_device).requires_grad_(True)
+    torch.nn.functional.cross_entropy(m(xv2, xa.detach().to(cuda_device)), labels.to(cuda_device)).backward()
+    assert (xv2.grad.float().cpu() - rv.grad).abs().max().item() <= tol * rv.grad.abs().max().item() + 1e-9
