@@ -1,3 +1,4 @@
+#include <stdlib.h>
 // fp32 backward of the xattn fusion head for the Stage-1 step (reference train.py:227: loss.backward()
 // with both backbones frozen, train.py:808-812 — so no gradient flows into video_emb / audio_emb).
 // Hand-derived reverse of fwd_f32.cu; activations come from the forward's workspace, dropout masks are
@@ -577,6 +578,11 @@ __global__ void __launch_bounds__(256, 2) attn_bwd32_kernel(AttnBwdArgs a) {
 
 // *bias_fused: the kernel accumulated a.dbq / a.dbkv itself (else the caller runs the column sums over dq / dkv)
 static int launch_attn_bwd(cudaStream_t st, const AttnBwdArgs& a, int B, bool* bias_fused) {
+  static const bool simt_env = getenv("XATTN_ATTN_SIMT") != nullptr;
+  if (g_tc_gemm && !simt_env && attn_mma_ok(a.L, a.S, a.E, a.H)) {
+    *bias_fused = a.dbq != nullptr;
+    return launch_attn_bwd_mma(st, a, B);
+  }
   const int dh = a.E / a.H;
   *bias_fused = dh == 32 && a.dbq != nullptr;
   if (dh == 32) {

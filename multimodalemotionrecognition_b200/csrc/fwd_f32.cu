@@ -1,3 +1,4 @@
+#include <stdlib.h>
 // fp32 forward of the xattn fusion head (parity + training path).
 // Stage map (reference src/models/fusion.py):
 //   v_in_proj :372 | audio_seq_proj :378 | a_in_proj :386 | EmotionPriorBiasAdapter :170-184 |
@@ -631,6 +632,8 @@ static inline int ew_grid(int64_t n) {
 size_t attn_smem_bytes(int L, int S, int dh, int nwarps) { return sizeof(float) * ((size_t)(L + 2 * S) * (dh + 1) + (size_t)nwarps * S); }
 
 int launch_attn_fwd(cudaStream_t st, const AttnArgs& a, int B) {
+  static const bool simt_env = getenv("XATTN_ATTN_SIMT") != nullptr;   // (comparison runs: keep the fp32 SIMT attention under tf32)
+  if (g_tc_gemm && !simt_env && attn_mma_ok(a.L, a.S, a.E, a.H)) return launch_attn_fwd_mma(st, a, B);
   if (a.E / a.H == 32) {   // one lane per head column: the register-tiled kernel
     const size_t smem = sizeof(float) * ((size_t)a.L * ((a.S + 3) & ~3) + (size_t)(a.L + 2 * a.S) * 33);
     if (smem > 200 * 1024) XF_FAIL(XATTN_ERR_SHAPE, "attention tile needs %zu B of shared memory (> 200 KiB)", smem);

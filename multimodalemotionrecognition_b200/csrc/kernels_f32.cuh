@@ -59,6 +59,11 @@ struct HeadArgs {
 
 size_t attn_smem_bytes(int L, int S, int dh, int nwarps);
 int launch_attn_fwd(cudaStream_t st, const AttnArgs& a, int B);
+// tensor-core (mma.sync tf32) versions for the shapes of the fusion block (attn_mma.cu); taken when precision = TF32
+bool attn_mma_ok(int L, int S, int E, int H);
+int launch_attn_fwd_mma(cudaStream_t st, const AttnArgs& a, int B);
+struct AttnBwdArgs;
+int launch_attn_bwd_mma(cudaStream_t st, const AttnBwdArgs& a, int B);
 
 int forward_f32(const xattn_config& c, const float* params, const void* xv, const void* xa, float* logits, void* ws,
                 cudaStream_t st);
