@@ -83,30 +83,34 @@ __device__ __forceinline__ void store_rows_x(const float (&o)[4][4], float* row0
 }
 
 // Row-major pass of a warp over its 16 x S tile: element (r, s) has the linear index base_r + s in the [B,H,L,S] tensor; the four
-// dropout factors of indices 4c .. 4c+3 come from ONE Philox evaluation (drop_factor4), so lanes walk aligned groups of four.
-// fn(r, s, factor) is called for every element of the valid rows.
-template <typename F>
+// dropout factors of indices 4c .. 4c+3 come from ONE Philox evaluation (drop_factor4), so a lane takes one aligned group of four
+// at a time — (row, group) pairs are dealt to the lanes flat, so short rows (S = 16: four groups) keep the whole warp busy.
+// fn4(r, s, f[4]) gets a whole group inside the row (s % 4 == 0 in index space), fn(r, s, f) single elements at the row ends.
+template <typename F4, typename F1>
 __device__ __forceinline__ void for_each_with_dropout(int rows_valid, int S, int64_t base0, int64_t row_stride, float p, uint64_t seed,
-                                                      uint64_t offset, uint32_t stream, int lane, F&& fn) {
-  for (int r = 0; r < rows_valid; ++r) {
+                                                      uint64_t offset, uint32_t stream, int lane, F4&& fn4, F1&& fn) {
+  const int G = (S + 6) >> 2;   // upper bound of the aligned groups a row can touch
+  for (int idx = lane; idx < rows_valid * G; idx += 32) {
+    const int r = idx / G, grp = idx - r * G;
     const int64_t base = base0 + (int64_t)r * row_stride;
     const int rem = (int)(base & 3);
-    const int ngroups = (S + rem + 3) >> 2;
-    for (int grp = lane; grp < ngroups; grp += 32) {
-      float f[4] = {1.f, 1.f, 1.f, 1.f};
-      if (p > 0.f) drop_factor4(p, seed, offset, stream, (uint64_t)(base - rem) + 4u * (uint64_t)grp, f);
+    if (grp >= ((S + rem + 3) >> 2)) continue;
+    float f[4] = {1.f, 1.f, 1.f, 1.f};
+    if (p > 0.f) drop_factor4(p, seed, offset, stream, (uint64_t)(base - rem) + 4u * (uint64_t)grp, f);
+    const int s0 = 4 * grp - rem;
+    if (s0 >= 0 && s0 + 3 < S) {
+      fn4(r, s0, f);
+    } else {
 #pragma unroll
-      for (int j = 0; j < 4; ++j) {
-        const int s = 4 * grp + j - rem;
-        if (s >= 0 && s < S) fn(r, s, f[j]);
-      }
+      for (int j = 0; j < 4; ++j)
+        if (s0 + j >= 0 && s0 + j < S) fn(r, s0 + j, f[j]);
     }
   }
 }
 
 // --------------------------------------------------------------------------------------------------------------------------
 template <int NT, int NW>
-__global__ void __launch_bounds__(NW * 32) attn_fwd_mma_kernel(AttnArgs a) {
+__global__ void __launch_bounds__(NW * 32, NW == 4 ? 4 : 2) attn_fwd_mma_kernel(AttnArgs a) {
   constexpr int PITCH = NT * 8 + 4;   // (≡ 4 mod 32: the canonical A-fragment reads of a tile are conflict-free)
   extern __shared__ __align__(16) float sm[];
   const int b = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, g = lane >> 2, t = lane & 3;
@@ -178,11 +182,29 @@ __global__ void __launch_bounds__(NW * 32) attn_fwd_mma_kernel(AttnArgs a) {
     const int rows_valid = min(16, L - m0);
     const int64_t base0 = (((int64_t)b * H + h) * L + m0) * S;
     if (a.P != nullptr || a.p_drop > 0.f) {
-      for_each_with_dropout(rows_valid, S, base0, S, a.p_drop, a.seed, a.offset, a.rng_stream, lane, [&](int r, int s, float f) {
-        const float p = ps[r * PITCH + s];
-        if (a.P != nullptr) a.P[base0 + (int64_t)r * S + s] = p;
-        ps[r * PITCH + s] = p * f;
-      });
+      const bool vec = (S & 3) == 0 && (reinterpret_cast<uintptr_t>(a.P) & 15) == 0;   // rows start on 16-byte boundaries
+      for_each_with_dropout(
+          rows_valid, S, base0, S, a.p_drop, a.seed, a.offset, a.rng_stream, lane,
+          [&](int r, int s, const float(&f)[4]) {
+            float* pp = ps + r * PITCH + s;
+            if (vec) {   // (s % 4 == 0 then, and the tile pitch keeps rows 16-byte aligned)
+              const float4 pv = *reinterpret_cast<const float4*>(pp);
+              if (a.P != nullptr) *reinterpret_cast<float4*>(a.P + base0 + (int64_t)r * S + s) = pv;
+              *reinterpret_cast<float4*>(pp) = make_float4(pv.x * f[0], pv.y * f[1], pv.z * f[2], pv.w * f[3]);
+            } else {
+#pragma unroll
+              for (int j = 0; j < 4; ++j) {
+                const float pj = pp[j];
+                if (a.P != nullptr) a.P[base0 + (int64_t)r * S + s + j] = pj;
+                pp[j] = pj * f[j];
+              }
+            }
+          },
+          [&](int r, int s, float f) {
+            const float pj = ps[r * PITCH + s];
+            if (a.P != nullptr) a.P[base0 + (int64_t)r * S + s] = pj;
+            ps[r * PITCH + s] = pj * f;
+          });
       __syncwarp();
     }
     // O = Pd V
@@ -202,13 +224,15 @@ __global__ void __launch_bounds__(NW * 32) attn_fwd_mma_kernel(AttnArgs a) {
 }
 
 // --------------------------------------------------------------------------------------------------------------------------
-// Backward.  Per item: dPd = dO V^T (accumulators), P and the dropout factors through the two warp tiles (row-major pass),
-// dS = P ⊙ (dP − rowsum(dP ⊙ P)) in registers, the bias gradients from dS at the same positions, then Pd and dS go back to the
-// tiles and feed dV = Pd^T dO, dK = dS^T Qs (A read transposed from the tile), dQ = scale · dS K (A read canonically).
-// ACC: dK / dV are summed over the query tiles of a head in shared memory (a2v: 10 tiles of 16 queries, 16 keys); otherwise the
-// single query tile writes them directly (v2a).
+// Backward.  Per item: dPd = dO V^T (accumulators); P and the dropout decisions come through the warp tile in ONE value per element
+// (row-major pass): x = +P where the element was kept, -P where it was dropped (P >= 0, so the sign is free; -0 counts as dropped).
+// dS = P ⊙ (dP − rowsum(dP ⊙ P)) stays in the accumulator registers; the bias gradients are taken from it in place.  The tile then
+// holds Pd for dV = Pd^T dO, is overwritten with dS for dK = dS^T Qs (A read transposed from the tile) and dQ = scale · dS K (A
+// read canonically).  A warp always works on the same head (NW % H == 0), so dK / dV of a head with several query tiles (a2v: 10
+// tiles of 16 queries, 16 keys) and the column sums for the in_proj bias gradients accumulate in registers across the warp's items
+// and meet the other warps of the head in shared memory once, after the last item.
 template <int NT, int NW, bool ACC>
-__global__ void __launch_bounds__(NW * 32) attn_bwd_mma_kernel(AttnBwdArgs a) {
+__global__ void __launch_bounds__(NW * 32, NW == 4 ? 3 : 2) attn_bwd_mma_kernel(AttnBwdArgs a) {
   constexpr int PITCH = NT * 8 + 4;
   extern __shared__ __align__(16) float sm[];
   const int b = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, g = lane >> 2, t = lane & 3;
@@ -217,9 +241,8 @@ __global__ void __launch_bounds__(NW * 32) attn_bwd_mma_kernel(AttnBwdArgs a) {
   const bool prior = a.qs != nullptr;
   float* bt = sm;                                           // [Lp][PITCH] tanh(qs_l + ks_s) (NOT scaled here)
   float* tiles = sm + (prior ? Lp * PITCH : 0);
-  float* ps = tiles + warp * 2 * 16 * PITCH;                // P, then Pd
-  float* fs = ps + 16 * PITCH;                              // dropout factors, then dS
-  float* accs = tiles + NW * 2 * 16 * PITCH;
+  float* ps = tiles + warp * 16 * PITCH;                    // ±P, then Pd, then dS
+  float* accs = tiles + NW * 16 * PITCH;
   float* dqs_acc = accs;                                    // [Lp]
   float* dks_acc = dqs_acc + Lp;                            // [NT*8]
   float* col_acc = dks_acc + NT * 8;                        // [3][E]: column sums of dq | dk | dv
@@ -229,6 +252,7 @@ __global__ void __launch_bounds__(NW * 32) attn_bwd_mma_kernel(AttnBwdArgs a) {
   const float* kv = a.kv + (int64_t)b * S * 2 * E;
   const float* dO = a.dO + (int64_t)b * L * E;
   const float bscale = prior ? a.bias_scale[0] : 0.f;
+  const float inv_keep = a.p_drop > 0.f ? 1.f / (1.f - a.p_drop) : 1.f;
   {
     const int nacc = Lp + NT * 8 + 3 * E + 4 + (ACC ? H * NT * 8 * 64 : 0);
     for (int i = tid; i < nacc; i += NW * 32) accs[i] = 0.f;
@@ -242,8 +266,53 @@ __global__ void __launch_bounds__(NW * 32) attn_bwd_mma_kernel(AttnBwdArgs a) {
     }
     __syncthreads();
   }
+  // per-warp accumulators over the warp's items (one head): column sums for the bias gradients, dK / dV of the (single) key tile
+  float bk[8], bv[8], bq[8], dka[4][4], dva[4][4];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) bk[i] = bv[i] = bq[i] = 0.f;
+#pragma unroll
+  for (int i = 0; i < 4; ++i) dka[i][0] = dka[i][1] = dka[i][2] = dka[i][3] = dva[i][0] = dva[i][1] = dva[i][2] = dva[i][3] = 0.f;
+  int cur_h = -1;
+  auto flush = [&]() {   // this warp's sums of head cur_h -> the CTA's accumulators
+    if (cur_h < 0) return;
+    if (ACC) {
+      float* d0 = dkv_acc + ((int64_t)cur_h * NT * 8 + g) * 64 + 8 * t;
+      float* d1 = d0 + 8 * 64;
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        atomicAdd(d0 + i, dka[i][0]); atomicAdd(d0 + 4 + i, dka[i][1]); atomicAdd(d0 + 32 + i, dva[i][0]); atomicAdd(d0 + 36 + i, dva[i][1]);
+        atomicAdd(d1 + i, dka[i][2]); atomicAdd(d1 + 4 + i, dka[i][3]); atomicAdd(d1 + 32 + i, dva[i][2]); atomicAdd(d1 + 36 + i, dva[i][3]);
+        dka[i][0] = dka[i][1] = dka[i][2] = dka[i][3] = dva[i][0] = dva[i][1] = dva[i][2] = dva[i][3] = 0.f;
+      }
+    }
+    if (a.dbq != nullptr) {   // in_proj bias gradients: sum the rows over g, one shared-memory add per column
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+#pragma unroll
+        for (int o2 = 4; o2 <= 16; o2 <<= 1) {
+          bq[i] += __shfl_xor_sync(0xffffffffu, bq[i], o2);
+          bk[i] += __shfl_xor_sync(0xffffffffu, bk[i], o2);
+          bv[i] += __shfl_xor_sync(0xffffffffu, bv[i], o2);
+        }
+      }
+      if (g == 0) {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          atomicAdd(col_acc + cur_h * 32 + 8 * t + i, bq[i]);
+          atomicAdd(col_acc + E + cur_h * 32 + 8 * t + i, bk[i]);
+          atomicAdd(col_acc + 2 * E + cur_h * 32 + 8 * t + i, bv[i]);
+        }
+      }
+    }
+#pragma unroll
+    for (int i = 0; i < 8; ++i) bk[i] = bv[i] = bq[i] = 0.f;
+  };
   for (int item = warp; item < H * n_mt; item += NW) {
     const int h = item % H, m0 = (item / H) * 16;
+    if (h != cur_h) {
+      flush();
+      cur_h = h;
+    }
     const int r0 = m0 + g, r1 = r0 + 8;
     const bool ok0 = r0 < L, ok1 = r1 < L;
     const int rows_valid = min(16, L - m0);
@@ -259,44 +328,63 @@ __global__ void __launch_bounds__(NW * 32) attn_bwd_mma_kernel(AttnBwdArgs a) {
         if (nt * 8 < S) mma_rows_nt(acc[nt], fo, kv + (int64_t)min(nt * 8 + g, S - 1) * 2 * E + E + h * 32, t);
       }
     }
-    // ---- P and the dropout factors into the tiles (row-major pass); rows / keys past the end are zero ----
-    __syncwarp();   // the previous item's products have finished reading the tiles
-    for (int i = lane; i < 16 * NT * 8; i += 32) {
-      const int r = i / (NT * 8), s = i - r * (NT * 8);
-      if (r >= rows_valid || s >= S) ps[r * PITCH + s] = 0.f, fs[r * PITCH + s] = 0.f;
+    // ---- ±P into the tile (row-major pass); rows / keys past the end are zero ----
+    __syncwarp();   // the previous item's products have finished reading the tile
+    if (rows_valid < 16 || S < NT * 8) {
+      for (int i = lane; i < 16 * NT * 8; i += 32) {
+        const int r = i / (NT * 8), s = i - r * (NT * 8);
+        if (r >= rows_valid || s >= S) ps[r * PITCH + s] = 0.f;
+      }
     }
-    for_each_with_dropout(rows_valid, S, base0, S, a.p_drop, a.seed, a.offset, a.rng_stream, lane, [&](int r, int s, float f) {
-      ps[r * PITCH + s] = a.P[base0 + (int64_t)r * S + s];
-      fs[r * PITCH + s] = f;
-    });
+    {
+      const bool vec = (S & 3) == 0 && (reinterpret_cast<uintptr_t>(a.P) & 15) == 0;
+      for_each_with_dropout(
+          rows_valid, S, base0, S, a.p_drop, a.seed, a.offset, a.rng_stream, lane,
+          [&](int r, int s, const float(&f)[4]) {
+            float* pp = ps + r * PITCH + s;
+            const float* gp = a.P + base0 + (int64_t)r * S + s;
+            if (vec) {
+              const float4 pv = *reinterpret_cast<const float4*>(gp);
+              *reinterpret_cast<float4*>(pp) = make_float4(f[0] > 0.f ? pv.x : -pv.x, f[1] > 0.f ? pv.y : -pv.y, f[2] > 0.f ? pv.z : -pv.z,
+                                                           f[3] > 0.f ? pv.w : -pv.w);
+            } else {
+#pragma unroll
+              for (int j = 0; j < 4; ++j) pp[j] = f[j] > 0.f ? gp[j] : -gp[j];
+            }
+          },
+          [&](int r, int s, float f) {
+            const float pv = a.P[base0 + (int64_t)r * S + s];
+            ps[r * PITCH + s] = f > 0.f ? pv : -pv;
+          });
+    }
     __syncwarp();
-    // ---- dS at the accumulator positions; bias gradients ----
+    // ---- dS at the accumulator positions (kept in acc); bias gradients; Pd into the tile ----
     float rd0 = 0.f, rd1 = 0.f;
 #pragma unroll
     for (int nt = 0; nt < NT; ++nt) {
       const int c = nt * 8 + 2 * t;
-      const float2 p0 = *reinterpret_cast<const float2*>(ps + g * PITCH + c), p1 = *reinterpret_cast<const float2*>(ps + (g + 8) * PITCH + c);
-      const float2 f0 = *reinterpret_cast<const float2*>(fs + g * PITCH + c), f1 = *reinterpret_cast<const float2*>(fs + (g + 8) * PITCH + c);
-      acc[nt][0] *= f0.x; acc[nt][1] *= f0.y; acc[nt][2] *= f1.x; acc[nt][3] *= f1.y;       // dP = dPd ⊙ mask
-      rd0 = fmaf(acc[nt][0], p0.x, fmaf(acc[nt][1], p0.y, rd0));
-      rd1 = fmaf(acc[nt][2], p1.x, fmaf(acc[nt][3], p1.y, rd1));
+      const float2 x0 = *reinterpret_cast<const float2*>(ps + g * PITCH + c), x1 = *reinterpret_cast<const float2*>(ps + (g + 8) * PITCH + c);
+      // dP = dPd ⊙ mask (0 where dropped, 1/keep where kept)
+      acc[nt][0] *= signbit(x0.x) ? 0.f : inv_keep; acc[nt][1] *= signbit(x0.y) ? 0.f : inv_keep;
+      acc[nt][2] *= signbit(x1.x) ? 0.f : inv_keep; acc[nt][3] *= signbit(x1.y) ? 0.f : inv_keep;
+      rd0 = fmaf(acc[nt][0], fabsf(x0.x), fmaf(acc[nt][1], fabsf(x0.y), rd0));
+      rd1 = fmaf(acc[nt][2], fabsf(x1.x), fmaf(acc[nt][3], fabsf(x1.y), rd1));
     }
     rd0 += __shfl_xor_sync(0xffffffffu, rd0, 1); rd0 += __shfl_xor_sync(0xffffffffu, rd0, 2);
     rd1 += __shfl_xor_sync(0xffffffffu, rd1, 1); rd1 += __shfl_xor_sync(0xffffffffu, rd1, 2);
     float dq0 = 0.f, dq1 = 0.f, dsc = 0.f;
-    __syncwarp();   // every lane has read its P / factor values: the tiles may be overwritten
 #pragma unroll
     for (int nt = 0; nt < NT; ++nt) {
       const int c = nt * 8 + 2 * t;
-      const float2 p0 = *reinterpret_cast<const float2*>(ps + g * PITCH + c), p1 = *reinterpret_cast<const float2*>(ps + (g + 8) * PITCH + c);
-      const float2 f0 = *reinterpret_cast<const float2*>(fs + g * PITCH + c), f1 = *reinterpret_cast<const float2*>(fs + (g + 8) * PITCH + c);
-      const float d00 = p0.x * (acc[nt][0] - rd0), d01 = p0.y * (acc[nt][1] - rd0);   // dS = P ⊙ (dP − rowdot)
-      const float d10 = p1.x * (acc[nt][2] - rd1), d11 = p1.y * (acc[nt][3] - rd1);
+      const float2 x0 = *reinterpret_cast<const float2*>(ps + g * PITCH + c), x1 = *reinterpret_cast<const float2*>(ps + (g + 8) * PITCH + c);
+      const float p00 = fabsf(x0.x), p01 = fabsf(x0.y), p10 = fabsf(x1.x), p11 = fabsf(x1.y);
+      acc[nt][0] = p00 * (acc[nt][0] - rd0); acc[nt][1] = p01 * (acc[nt][1] - rd0);   // dS = P ⊙ (dP − rowdot)
+      acc[nt][2] = p10 * (acc[nt][2] - rd1); acc[nt][3] = p11 * (acc[nt][3] - rd1);
       if (prior) {
         const float2 t0 = *reinterpret_cast<const float2*>(bt + (m0 + g) * PITCH + c), t1 = *reinterpret_cast<const float2*>(bt + (m0 + g + 8) * PITCH + c);
-        dsc = fmaf(d00, t0.x, fmaf(d01, t0.y, fmaf(d10, t1.x, fmaf(d11, t1.y, dsc))));
-        const float u00 = d00 * (1.f - t0.x * t0.x), u01 = d01 * (1.f - t0.y * t0.y);
-        const float u10 = d10 * (1.f - t1.x * t1.x), u11 = d11 * (1.f - t1.y * t1.y);
+        dsc = fmaf(acc[nt][0], t0.x, fmaf(acc[nt][1], t0.y, fmaf(acc[nt][2], t1.x, fmaf(acc[nt][3], t1.y, dsc))));
+        const float u00 = acc[nt][0] * (1.f - t0.x * t0.x), u01 = acc[nt][1] * (1.f - t0.y * t0.y);
+        const float u10 = acc[nt][2] * (1.f - t1.x * t1.x), u11 = acc[nt][3] * (1.f - t1.y * t1.y);
         dq0 += u00 + u01;
         dq1 += u10 + u11;
         float k0 = u00 + u10, k1 = u01 + u11;                                          // over this lane's two rows; then over g
@@ -307,11 +395,9 @@ __global__ void __launch_bounds__(NW * 32) attn_bwd_mma_kernel(AttnBwdArgs a) {
           atomicAdd(dks_acc + c + 1, k1 * bscale);
         }
       }
-      // Pd and dS replace P and the factors (same positions, same lane)
-      *reinterpret_cast<float2*>(ps + g * PITCH + c) = make_float2(p0.x * f0.x, p0.y * f0.y);
-      *reinterpret_cast<float2*>(ps + (g + 8) * PITCH + c) = make_float2(p1.x * f1.x, p1.y * f1.y);
-      *reinterpret_cast<float2*>(fs + g * PITCH + c) = make_float2(d00, d01);
-      *reinterpret_cast<float2*>(fs + (g + 8) * PITCH + c) = make_float2(d10, d11);
+      // Pd replaces ±P (same positions, same lane)
+      *reinterpret_cast<float2*>(ps + g * PITCH + c) = make_float2(signbit(x0.x) ? 0.f : p00 * inv_keep, signbit(x0.y) ? 0.f : p01 * inv_keep);
+      *reinterpret_cast<float2*>(ps + (g + 8) * PITCH + c) = make_float2(signbit(x1.x) ? 0.f : p10 * inv_keep, signbit(x1.y) ? 0.f : p11 * inv_keep);
     }
     if (prior) {
       dq0 += __shfl_xor_sync(0xffffffffu, dq0, 1); dq0 += __shfl_xor_sync(0xffffffffu, dq0, 2);
@@ -325,61 +411,94 @@ __global__ void __launch_bounds__(NW * 32) attn_bwd_mma_kernel(AttnBwdArgs a) {
       if (lane == 0) atomicAdd(dscale_acc, dsc);
     }
     __syncwarp();
-    // ---- dV = Pd^T dO and dK = dS^T Qs: rows = keys, reduction over the tile's 16 queries (two k-steps), N-permuted columns ----
-    float bk[8], bv[8], bq[8];   // column sums of this item's dk / dv / dq rows (physical columns 8t .. 8t+7), for the bias gradients
-#pragma unroll
-    for (int i = 0; i < 8; ++i) bk[i] = bv[i] = bq[i] = 0.f;
+    const int n_km = (S + 15) >> 4;
+    // ---- dV = Pd^T dO: rows = keys, reduction over the tile's 16 queries (two k-steps), N-permuted columns ----
     {
-      float4 on[2][2], qn[2][2];   // B operands: dO / scaled q rows of queries 8 k2 + t (+4), physical columns 4g .. 4g+3
+      float4 on[2][2];   // B operand: dO rows of queries 8 k2 + t (+4), physical columns 4g .. 4g+3
 #pragma unroll
       for (int k2 = 0; k2 < 2; ++k2)
 #pragma unroll
         for (int j = 0; j < 2; ++j) {
           const int r = m0 + 8 * k2 + t + 4 * j;
-          const bool ok = r < L;
-          const int rr = min(r, L - 1);
-          float4 x = ldg4(dO + (int64_t)rr * E + h * 32 + 4 * g), y = ldg4(q + (int64_t)rr * E + h * 32 + 4 * g);
-          const float s1 = ok ? 1.f : 0.f, s2 = ok ? a.scale : 0.f;
+          const float4 x = ldg4(dO + (int64_t)min(r, L - 1) * E + h * 32 + 4 * g);
+          const float s1 = r < L ? 1.f : 0.f;
           on[k2][j] = make_float4(x.x * s1, x.y * s1, x.z * s1, x.w * s1);
-          qn[k2][j] = make_float4(y.x * s2, y.y * s2, y.z * s2, y.w * s2);
         }
-      const int n_km = (S + 15) >> 4;
       for (int km = 0; km < n_km; ++km) {
-        float dv[4][4], dk[4][4];
+        float dv[4][4];
 #pragma unroll
-        for (int i = 0; i < 4; ++i) dv[i][0] = dv[i][1] = dv[i][2] = dv[i][3] = dk[i][0] = dk[i][1] = dk[i][2] = dk[i][3] = 0.f;
+        for (int i = 0; i < 4; ++i) dv[i][0] = dv[i][1] = dv[i][2] = dv[i][3] = 0.f;
 #pragma unroll
         for (int k2 = 0; k2 < 2; ++k2) {
-          // A[key][query] read transposed from the tiles: a0 (key g, query t)  a1 (key g+8, t)  a2 (g, t+4)  a3 (g+8, t+4)
+          // A[key][query] read transposed from the tile: a0 (key g, query t)  a1 (key g+8, t)  a2 (g, t+4)  a3 (g+8, t+4)
           const int qa = 8 * k2 + t, ka = 16 * km + g;
           const uint32_t p0 = fu(ps[qa * PITCH + ka]), p1 = fu(ps[qa * PITCH + ka + 8]), p2 = fu(ps[(qa + 4) * PITCH + ka]),
                          p3 = fu(ps[(qa + 4) * PITCH + ka + 8]);
-          const uint32_t s0 = fu(fs[qa * PITCH + ka]), s1 = fu(fs[qa * PITCH + ka + 8]), s2 = fu(fs[(qa + 4) * PITCH + ka]),
-                         s3 = fu(fs[(qa + 4) * PITCH + ka + 8]);
-          const float4 o0 = on[k2][0], o1 = on[k2][1], q0 = qn[k2][0], q1 = qn[k2][1];
+          const float4 o0 = on[k2][0], o1 = on[k2][1];
           mma_tf32(dv[0], p0, p1, p2, p3, fu(o0.x), fu(o1.x)); mma_tf32(dv[1], p0, p1, p2, p3, fu(o0.y), fu(o1.y));
           mma_tf32(dv[2], p0, p1, p2, p3, fu(o0.z), fu(o1.z)); mma_tf32(dv[3], p0, p1, p2, p3, fu(o0.w), fu(o1.w));
+        }
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {   // (rows past the last key hold exact zeros: Pd is zero there)
+          bv[i] += dv[i][0] + dv[i][2];
+          bv[4 + i] += dv[i][1] + dv[i][3];
+        }
+        if (ACC) {
+#pragma unroll
+          for (int i = 0; i < 4; ++i) { dva[i][0] += dv[i][0]; dva[i][1] += dv[i][1]; dva[i][2] += dv[i][2]; dva[i][3] += dv[i][3]; }
+        } else {
+          const int k0r = 16 * km + g, k1r = k0r + 8;
+          float* out = a.dkv + (int64_t)b * S * 2 * E + E + h * 32;
+          store_rows_x(dv, out + (int64_t)min(k0r, S - 1) * 2 * E, out + (int64_t)min(k1r, S - 1) * 2 * E, k0r < S, k1r < S, 1.f, t);
+        }
+      }
+    }
+    // ---- dS replaces Pd in the tile ----
+    __syncwarp();
+#pragma unroll
+    for (int nt = 0; nt < NT; ++nt) {
+      const int c = nt * 8 + 2 * t;
+      *reinterpret_cast<float2*>(ps + g * PITCH + c) = make_float2(acc[nt][0], acc[nt][1]);
+      *reinterpret_cast<float2*>(ps + (g + 8) * PITCH + c) = make_float2(acc[nt][2], acc[nt][3]);
+    }
+    __syncwarp();
+    // ---- dK = dS^T Qs ----
+    {
+      float4 qn[2][2];
+#pragma unroll
+      for (int k2 = 0; k2 < 2; ++k2)
+#pragma unroll
+        for (int j = 0; j < 2; ++j) {
+          const int r = m0 + 8 * k2 + t + 4 * j;
+          const float4 y = ldg4(q + (int64_t)min(r, L - 1) * E + h * 32 + 4 * g);
+          const float s2 = r < L ? a.scale : 0.f;
+          qn[k2][j] = make_float4(y.x * s2, y.y * s2, y.z * s2, y.w * s2);
+        }
+      for (int km = 0; km < n_km; ++km) {
+        float dk[4][4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) dk[i][0] = dk[i][1] = dk[i][2] = dk[i][3] = 0.f;
+#pragma unroll
+        for (int k2 = 0; k2 < 2; ++k2) {
+          const int qa = 8 * k2 + t, ka = 16 * km + g;
+          const uint32_t s0 = fu(ps[qa * PITCH + ka]), s1 = fu(ps[qa * PITCH + ka + 8]), s2 = fu(ps[(qa + 4) * PITCH + ka]),
+                         s3 = fu(ps[(qa + 4) * PITCH + ka + 8]);
+          const float4 q0 = qn[k2][0], q1 = qn[k2][1];
           mma_tf32(dk[0], s0, s1, s2, s3, fu(q0.x), fu(q1.x)); mma_tf32(dk[1], s0, s1, s2, s3, fu(q0.y), fu(q1.y));
           mma_tf32(dk[2], s0, s1, s2, s3, fu(q0.z), fu(q1.z)); mma_tf32(dk[3], s0, s1, s2, s3, fu(q0.w), fu(q1.w));
         }
-        const int k0r = 16 * km + g, k1r = k0r + 8;
 #pragma unroll
-        for (int i = 0; i < 4; ++i) {   // (rows past the last key hold exact zeros: Pd and dS are zero there)
-          bk[i] += dk[i][0] + dk[i][2]; bk[4 + i] += dk[i][1] + dk[i][3];
-          bv[i] += dv[i][0] + dv[i][2]; bv[4 + i] += dv[i][1] + dv[i][3];
+        for (int i = 0; i < 4; ++i) {
+          bk[i] += dk[i][0] + dk[i][2];
+          bk[4 + i] += dk[i][1] + dk[i][3];
         }
         if (ACC) {
-          float* d0 = dkv_acc + ((int64_t)h * NT * 8 + k0r) * 64 + 8 * t;
-          float* d1 = dkv_acc + ((int64_t)h * NT * 8 + k1r) * 64 + 8 * t;
 #pragma unroll
-          for (int i = 0; i < 4; ++i) {
-            atomicAdd(d0 + i, dk[i][0]); atomicAdd(d0 + 4 + i, dk[i][1]); atomicAdd(d0 + 32 + i, dv[i][0]); atomicAdd(d0 + 36 + i, dv[i][1]);
-            atomicAdd(d1 + i, dk[i][2]); atomicAdd(d1 + 4 + i, dk[i][3]); atomicAdd(d1 + 32 + i, dv[i][2]); atomicAdd(d1 + 36 + i, dv[i][3]);
-          }
+          for (int i = 0; i < 4; ++i) { dka[i][0] += dk[i][0]; dka[i][1] += dk[i][1]; dka[i][2] += dk[i][2]; dka[i][3] += dk[i][3]; }
         } else {
+          const int k0r = 16 * km + g, k1r = k0r + 8;
           float* out = a.dkv + (int64_t)b * S * 2 * E + h * 32;
           store_rows_x(dk, out + (int64_t)min(k0r, S - 1) * 2 * E, out + (int64_t)min(k1r, S - 1) * 2 * E, k0r < S, k1r < S, 1.f, t);
-          store_rows_x(dv, out + (int64_t)min(k0r, S - 1) * 2 * E + E, out + (int64_t)min(k1r, S - 1) * 2 * E + E, k0r < S, k1r < S, 1.f, t);
         }
       }
     }
@@ -393,7 +512,7 @@ __global__ void __launch_bounds__(NW * 32) attn_bwd_mma_kernel(AttnBwdArgs a) {
         if (kstep * 8 >= S) break;
         const float* k0 = kv + (int64_t)min(kstep * 8 + t, S - 1) * 2 * E + h * 32;      // (dS is zero past the last key)
         const float* k1 = kv + (int64_t)min(kstep * 8 + t + 4, S - 1) * 2 * E + h * 32;
-        mma_tile_x<PITCH>(dq, fs, kstep, k0, k1, g, t);
+        mma_tile_x<PITCH>(dq, ps, kstep, k0, k1, g, t);
       }
       float* out = a.dq + (int64_t)b * L * E + h * 32;
       store_rows_x(dq, out + (int64_t)min(r0, L - 1) * E, out + (int64_t)min(r1, L - 1) * E, ok0, ok1, a.scale, t);
@@ -403,26 +522,8 @@ __global__ void __launch_bounds__(NW * 32) attn_bwd_mma_kernel(AttnBwdArgs a) {
         bq[4 + i] += (dq[i][1] + dq[i][3]) * a.scale;
       }
     }
-    if (a.dbq != nullptr) {   // in_proj bias gradients: sum the rows over g, one shared-memory add per column and item
-#pragma unroll
-      for (int i = 0; i < 8; ++i) {
-#pragma unroll
-        for (int o2 = 4; o2 <= 16; o2 <<= 1) {
-          bq[i] += __shfl_xor_sync(0xffffffffu, bq[i], o2);
-          bk[i] += __shfl_xor_sync(0xffffffffu, bk[i], o2);
-          bv[i] += __shfl_xor_sync(0xffffffffu, bv[i], o2);
-        }
-      }
-      if (g == 0) {
-#pragma unroll
-        for (int i = 0; i < 8; ++i) {
-          atomicAdd(col_acc + h * 32 + 8 * t + i, bq[i]);
-          atomicAdd(col_acc + E + h * 32 + 8 * t + i, bk[i]);
-          atomicAdd(col_acc + 2 * E + h * 32 + 8 * t + i, bv[i]);
-        }
-      }
-    }
   }
+  flush();
   __syncthreads();
   if (ACC) {   // dK | dV of the clip, summed over its query tiles
     for (int i = tid; i < H * S * 16; i += NW * 32) {   // float4 pieces: [h][key][16 pieces of 4]
@@ -453,7 +554,7 @@ size_t fwd_smem(int L, bool prior) {
 template <int NT, int NW, bool ACC>
 size_t bwd_smem(int L, int E, int H, bool prior) {
   const int pitch = NT * 8 + 4, Lp = ((L + 15) / 16) * 16;
-  return sizeof(float) * ((prior ? (size_t)Lp * pitch : 0) + (size_t)NW * 2 * 16 * pitch + Lp + NT * 8 + 3 * E + 4 +
+  return sizeof(float) * ((prior ? (size_t)Lp * pitch : 0) + (size_t)NW * 16 * pitch + Lp + NT * 8 + 3 * E + 4 +
                           (ACC ? (size_t)H * NT * 8 * 64 : 0));
 }
 
