@@ -178,7 +178,8 @@ __global__ void __launch_bounds__(NW * 32, NW == 4 ? 4 : 2) attn_fwd_mma_kernel(
       *reinterpret_cast<float2*>(ps + (g + 8) * PITCH + c) = make_float2(acc[nt][2] * i1, acc[nt][3] * i1);
     }
     __syncwarp();
-    // save P (before dropout) for the backward, apply the dropout mask in place
+    // save P (before dropout) for the backward — with the dropout decision in its sign: +P kept, -P dropped (P >= 0, -0 counts
+    // as dropped), so the backward regenerates no Philox mask — and apply the mask to the tile in place
     const int rows_valid = min(16, L - m0);
     const int64_t base0 = (((int64_t)b * H + h) * L + m0) * S;
     if (a.P != nullptr || a.p_drop > 0.f) {
@@ -189,20 +190,22 @@ __global__ void __launch_bounds__(NW * 32, NW == 4 ? 4 : 2) attn_fwd_mma_kernel(
             float* pp = ps + r * PITCH + s;
             if (vec) {   // (s % 4 == 0 then, and the tile pitch keeps rows 16-byte aligned)
               const float4 pv = *reinterpret_cast<const float4*>(pp);
-              if (a.P != nullptr) *reinterpret_cast<float4*>(a.P + base0 + (int64_t)r * S + s) = pv;
+              if (a.P != nullptr)
+                *reinterpret_cast<float4*>(a.P + base0 + (int64_t)r * S + s) =
+                    make_float4(f[0] > 0.f ? pv.x : -pv.x, f[1] > 0.f ? pv.y : -pv.y, f[2] > 0.f ? pv.z : -pv.z, f[3] > 0.f ? pv.w : -pv.w);
               *reinterpret_cast<float4*>(pp) = make_float4(pv.x * f[0], pv.y * f[1], pv.z * f[2], pv.w * f[3]);
             } else {
 #pragma unroll
               for (int j = 0; j < 4; ++j) {
                 const float pj = pp[j];
-                if (a.P != nullptr) a.P[base0 + (int64_t)r * S + s + j] = pj;
+                if (a.P != nullptr) a.P[base0 + (int64_t)r * S + s + j] = f[j] > 0.f ? pj : -pj;
                 pp[j] = pj * f[j];
               }
             }
           },
           [&](int r, int s, float f) {
             const float pj = ps[r * PITCH + s];
-            if (a.P != nullptr) a.P[base0 + (int64_t)r * S + s] = pj;
+            if (a.P != nullptr) a.P[base0 + (int64_t)r * S + s] = f > 0.f ? pj : -pj;
             ps[r * PITCH + s] = pj * f;
           });
       __syncwarp();
@@ -224,8 +227,9 @@ __global__ void __launch_bounds__(NW * 32, NW == 4 ? 4 : 2) attn_fwd_mma_kernel(
 }
 
 // --------------------------------------------------------------------------------------------------------------------------
-// Backward.  Per item: dPd = dO V^T (accumulators); P and the dropout decisions come through the warp tile in ONE value per element
-// (row-major pass): x = +P where the element was kept, -P where it was dropped (P >= 0, so the sign is free; -0 counts as dropped).
+// Backward.  Per item: dPd = dO V^T (accumulators); P and the dropout decisions arrive in ONE value per element, written by the
+// forward: x = +P where the element was kept, -P where it was dropped (P >= 0, so the sign is free; -0 counts as dropped) — no
+// Philox evaluation here.
 // dS = P ⊙ (dP − rowsum(dP ⊙ P)) stays in the accumulator registers; the bias gradients are taken from it in place.  The tile then
 // holds Pd for dV = Pd^T dO, is overwritten with dS for dK = dS^T Qs (A read transposed from the tile) and dQ = scale · dS K (A
 // read canonically).  A warp always works on the same head (NW % H == 0), so dK / dV of a head with several query tiles (a2v: 10
@@ -328,42 +332,28 @@ __global__ void __launch_bounds__(NW * 32, NW == 4 ? 3 : 2) attn_bwd_mma_kernel(
         if (nt * 8 < S) mma_rows_nt(acc[nt], fo, kv + (int64_t)min(nt * 8 + g, S - 1) * 2 * E + E + h * 32, t);
       }
     }
-    // ---- ±P into the tile (row-major pass); rows / keys past the end are zero ----
+    // ---- ±P (sign = dropout decision, written by the forward) straight from global memory at the accumulator positions; it is
+    //      parked in the tile at the lane's own positions for the second sweep.  Rows / keys past the end are zero. ----
     __syncwarp();   // the previous item's products have finished reading the tile
-    if (rows_valid < 16 || S < NT * 8) {
-      for (int i = lane; i < 16 * NT * 8; i += 32) {
-        const int r = i / (NT * 8), s = i - r * (NT * 8);
-        if (r >= rows_valid || s >= S) ps[r * PITCH + s] = 0.f;
-      }
-    }
-    {
-      const bool vec = (S & 3) == 0 && (reinterpret_cast<uintptr_t>(a.P) & 15) == 0;
-      for_each_with_dropout(
-          rows_valid, S, base0, S, a.p_drop, a.seed, a.offset, a.rng_stream, lane,
-          [&](int r, int s, const float(&f)[4]) {
-            float* pp = ps + r * PITCH + s;
-            const float* gp = a.P + base0 + (int64_t)r * S + s;
-            if (vec) {
-              const float4 pv = *reinterpret_cast<const float4*>(gp);
-              *reinterpret_cast<float4*>(pp) = make_float4(f[0] > 0.f ? pv.x : -pv.x, f[1] > 0.f ? pv.y : -pv.y, f[2] > 0.f ? pv.z : -pv.z,
-                                                           f[3] > 0.f ? pv.w : -pv.w);
-            } else {
-#pragma unroll
-              for (int j = 0; j < 4; ++j) pp[j] = f[j] > 0.f ? gp[j] : -gp[j];
-            }
-          },
-          [&](int r, int s, float f) {
-            const float pv = a.P[base0 + (int64_t)r * S + s];
-            ps[r * PITCH + s] = f > 0.f ? pv : -pv;
-          });
-    }
-    __syncwarp();
     // ---- dS at the accumulator positions (kept in acc); bias gradients; Pd into the tile ----
     float rd0 = 0.f, rd1 = 0.f;
+    const float* prow0 = a.P + base0 + (int64_t)g * S;
+    const float* prow1 = a.P + base0 + (int64_t)(g + 8) * S;
+    const bool al0 = ((base0 + (int64_t)g * S) & 1) == 0, al1 = ((base0 + (int64_t)(g + 8) * S) & 1) == 0;   // 8-byte aligned rows
 #pragma unroll
     for (int nt = 0; nt < NT; ++nt) {
       const int c = nt * 8 + 2 * t;
-      const float2 x0 = *reinterpret_cast<const float2*>(ps + g * PITCH + c), x1 = *reinterpret_cast<const float2*>(ps + (g + 8) * PITCH + c);
+      float2 x0 = make_float2(0.f, 0.f), x1 = make_float2(0.f, 0.f);
+      if (ok0 && c < S) {
+        if (al0 && c + 1 < S) x0 = __ldg(reinterpret_cast<const float2*>(prow0 + c));
+        else { x0.x = __ldg(prow0 + c); if (c + 1 < S) x0.y = __ldg(prow0 + c + 1); }
+      }
+      if (ok1 && c < S) {
+        if (al1 && c + 1 < S) x1 = __ldg(reinterpret_cast<const float2*>(prow1 + c));
+        else { x1.x = __ldg(prow1 + c); if (c + 1 < S) x1.y = __ldg(prow1 + c + 1); }
+      }
+      *reinterpret_cast<float2*>(ps + g * PITCH + c) = x0;
+      *reinterpret_cast<float2*>(ps + (g + 8) * PITCH + c) = x1;
       // dP = dPd ⊙ mask (0 where dropped, 1/keep where kept)
       acc[nt][0] *= signbit(x0.x) ? 0.f : inv_keep; acc[nt][1] *= signbit(x0.y) ? 0.f : inv_keep;
       acc[nt][2] *= signbit(x1.x) ? 0.f : inv_keep; acc[nt][3] *= signbit(x1.y) ? 0.f : inv_keep;
