@@ -56,6 +56,14 @@ __device__ __forceinline__ void mma_rows_nt(float (&acc)[4], const RowFrag& f, c
 #pragma unroll
   for (int ks = 0; ks < 4; ++ks) mma_tf32(acc, f.a[ks][0], f.a[ks][1], f.a[ks][2], f.a[ks][3], fu(kk[2 * ks]), fu(kk[2 * ks + 1]));
 }
+__device__ __forceinline__ void mma_rows_nt_frag(float (&acc)[4], const RowFrag& f, const float (&kk)[8]) {
+#pragma unroll
+  for (int ks = 0; ks < 4; ++ks) mma_tf32(acc, f.a[ks][0], f.a[ks][1], f.a[ks][2], f.a[ks][3], fu(kk[2 * ks]), fu(kk[2 * ks + 1]));
+}
+__device__ __forceinline__ void load_row8(float (&kk)[8], const float* xrow, int t) {
+  const float4 k0 = ldg4(xrow + 8 * t), k1 = ldg4(xrow + 8 * t + 4);
+  kk[0] = k0.x; kk[1] = k0.y; kk[2] = k0.z; kk[3] = k0.w; kk[4] = k1.x; kk[5] = k1.y; kk[6] = k1.z; kk[7] = k1.w;
+}
 // out[16 x 32] += A[16 x 8 ksteps·8] (canonical, from the shared-memory tile `ps`, pitch P) · X[row = key][32]: "N-permuted"
 // output — logical column n of output tile i is physical column 4 n + i, so thread g fetches X[key][4g .. 4g+3] in one piece
 // and a thread ends up with the physical columns 8t .. 8t+7 of its two rows.
@@ -65,6 +73,15 @@ __device__ __forceinline__ void mma_tile_x(float (&o)[4][4], const float* ps, in
   const uint32_t a0 = fu(ps[g * PITCH + 8 * kstep + t]), a1 = fu(ps[(g + 8) * PITCH + 8 * kstep + t]);
   const uint32_t a2 = fu(ps[g * PITCH + 8 * kstep + t + 4]), a3 = fu(ps[(g + 8) * PITCH + 8 * kstep + t + 4]);
   const float4 v0 = ldg4(xrow0 + 4 * g), v1 = ldg4(xrow1 + 4 * g);
+  mma_tf32(o[0], a0, a1, a2, a3, fu(v0.x), fu(v1.x));
+  mma_tf32(o[1], a0, a1, a2, a3, fu(v0.y), fu(v1.y));
+  mma_tf32(o[2], a0, a1, a2, a3, fu(v0.z), fu(v1.z));
+  mma_tf32(o[3], a0, a1, a2, a3, fu(v0.w), fu(v1.w));
+}
+template <int PITCH>
+__device__ __forceinline__ void mma_tile_x_frag(float (&o)[4][4], const float* ps, int kstep, const float4& v0, const float4& v1, int g, int t) {
+  const uint32_t a0 = fu(ps[g * PITCH + 8 * kstep + t]), a1 = fu(ps[(g + 8) * PITCH + 8 * kstep + t]);
+  const uint32_t a2 = fu(ps[g * PITCH + 8 * kstep + t + 4]), a3 = fu(ps[(g + 8) * PITCH + 8 * kstep + t + 4]);
   mma_tf32(o[0], a0, a1, a2, a3, fu(v0.x), fu(v1.x));
   mma_tf32(o[1], a0, a1, a2, a3, fu(v0.y), fu(v1.y));
   mma_tf32(o[2], a0, a1, a2, a3, fu(v0.z), fu(v1.z));
@@ -130,8 +147,24 @@ __global__ void __launch_bounds__(NW * 32, NW == 4 ? 4 : 2) attn_fwd_mma_kernel(
     }
     __syncthreads();
   }
+  // Short key side (a2v: 16 video tokens): the K / V fragments of a head are the same for all of its query tiles, and a warp stays on
+  // one head (NW % H == 0) — they are fetched once per warp instead of once per item.
+  constexpr bool HOIST = NT <= 2;
+  constexpr int NH = HOIST ? NT : 1;
+  float kfr[NH][8];
+  float4 vfr[NH][2];
+  int cur_h = -1;
   for (int item = warp; item < H * n_mt; item += NW) {
     const int h = item % H, m0 = (item / H) * 16;
+    if (HOIST && h != cur_h) {
+      cur_h = h;
+#pragma unroll
+      for (int nt = 0; nt < NH; ++nt) {
+        load_row8(kfr[nt], kv + (int64_t)min(nt * 8 + g, S - 1) * 2 * E + h * 32, t);
+        vfr[nt][0] = ldg4(kv + (int64_t)min(nt * 8 + t, S - 1) * 2 * E + E + h * 32 + 4 * g);
+        vfr[nt][1] = ldg4(kv + (int64_t)min(nt * 8 + t + 4, S - 1) * 2 * E + E + h * 32 + 4 * g);
+      }
+    }
     const int r0 = m0 + g, r1 = r0 + 8;
     const bool ok0 = r0 < L, ok1 = r1 < L;
     RowFrag fq;   // q scaled before the product, as torch does
@@ -140,7 +173,10 @@ __global__ void __launch_bounds__(NW * 32, NW == 4 ? 4 : 2) attn_fwd_mma_kernel(
 #pragma unroll
     for (int nt = 0; nt < NT; ++nt) {
       acc[nt][0] = acc[nt][1] = acc[nt][2] = acc[nt][3] = 0.f;
-      if (nt * 8 < S) mma_rows_nt(acc[nt], fq, kv + (int64_t)min(nt * 8 + g, S - 1) * 2 * E + h * 32, t);
+      if (nt * 8 < S) {
+        if (HOIST) mma_rows_nt_frag(acc[nt], fq, kfr[nt < NH ? nt : 0]);
+        else mma_rows_nt(acc[nt], fq, kv + (int64_t)min(nt * 8 + g, S - 1) * 2 * E + h * 32, t);
+      }
     }
     // bias, key padding, row maxima (rows g and g+8; a row's scores sit in the four lanes of a quad)
     float mx0 = -INFINITY, mx1 = -INFINITY;
@@ -214,12 +250,18 @@ __global__ void __launch_bounds__(NW * 32, NW == 4 ? 4 : 2) attn_fwd_mma_kernel(
     float o[4][4];
 #pragma unroll
     for (int i = 0; i < 4; ++i) o[i][0] = o[i][1] = o[i][2] = o[i][3] = 0.f;
+    if (HOIST) {
+#pragma unroll
+      for (int kstep = 0; kstep < NH; ++kstep)
+        if (kstep * 8 < S) mma_tile_x_frag<PITCH>(o, ps, kstep, vfr[kstep][0], vfr[kstep][1], g, t);
+    } else {
 #pragma unroll 4
-    for (int kstep = 0; kstep < NT; ++kstep) {
-      if (kstep * 8 >= S) break;
-      const float* v0 = kv + (int64_t)min(kstep * 8 + t, S - 1) * 2 * E + E + h * 32;       // (P is zero past the last key)
-      const float* v1 = kv + (int64_t)min(kstep * 8 + t + 4, S - 1) * 2 * E + E + h * 32;
-      mma_tile_x<PITCH>(o, ps, kstep, v0, v1, g, t);
+      for (int kstep = 0; kstep < NT; ++kstep) {
+        if (kstep * 8 >= S) break;
+        const float* v0 = kv + (int64_t)min(kstep * 8 + t, S - 1) * 2 * E + E + h * 32;       // (P is zero past the last key)
+        const float* v1 = kv + (int64_t)min(kstep * 8 + t + 4, S - 1) * 2 * E + E + h * 32;
+        mma_tile_x<PITCH>(o, ps, kstep, v0, v1, g, t);
+      }
     }
     float* orow = a.O + (int64_t)b * L * E + h * 32;
     store_rows_x(o, orow + (int64_t)min(r0, L - 1) * E, orow + (int64_t)min(r1, L - 1) * E, ok0, ok1, 1.f, t);
@@ -276,6 +318,10 @@ __global__ void __launch_bounds__(NW * 32, NW == 4 ? 3 : 2) attn_bwd_mma_kernel(
   for (int i = 0; i < 8; ++i) bk[i] = bv[i] = bq[i] = 0.f;
 #pragma unroll
   for (int i = 0; i < 4; ++i) dka[i][0] = dka[i][1] = dka[i][2] = dka[i][3] = dva[i][0] = dva[i][1] = dva[i][2] = dva[i][3] = 0.f;
+  constexpr bool HOIST = false;   // (hoisting the head's V / K fragments as the forward does costs spills here: 217 -> 229 us measured)
+  constexpr int NH = HOIST ? NT : 1;
+  float vfr[NH][8];
+  float4 kfr[NH][2];
   int cur_h = -1;
   auto flush = [&]() {   // this warp's sums of head cur_h -> the CTA's accumulators
     if (cur_h < 0) return;
@@ -316,6 +362,14 @@ __global__ void __launch_bounds__(NW * 32, NW == 4 ? 3 : 2) attn_bwd_mma_kernel(
     if (h != cur_h) {
       flush();
       cur_h = h;
+      if (HOIST) {
+#pragma unroll
+        for (int nt = 0; nt < NH; ++nt) {
+          load_row8(vfr[nt], kv + (int64_t)min(nt * 8 + g, S - 1) * 2 * E + E + h * 32, t);
+          kfr[nt][0] = ldg4(kv + (int64_t)min(nt * 8 + t, S - 1) * 2 * E + h * 32 + 4 * g);
+          kfr[nt][1] = ldg4(kv + (int64_t)min(nt * 8 + t + 4, S - 1) * 2 * E + h * 32 + 4 * g);
+        }
+      }
     }
     const int r0 = m0 + g, r1 = r0 + 8;
     const bool ok0 = r0 < L, ok1 = r1 < L;
@@ -329,7 +383,10 @@ __global__ void __launch_bounds__(NW * 32, NW == 4 ? 3 : 2) attn_bwd_mma_kernel(
 #pragma unroll
       for (int nt = 0; nt < NT; ++nt) {
         acc[nt][0] = acc[nt][1] = acc[nt][2] = acc[nt][3] = 0.f;
-        if (nt * 8 < S) mma_rows_nt(acc[nt], fo, kv + (int64_t)min(nt * 8 + g, S - 1) * 2 * E + E + h * 32, t);
+        if (nt * 8 < S) {
+          if (HOIST) mma_rows_nt_frag(acc[nt], fo, vfr[nt < NH ? nt : 0]);
+          else mma_rows_nt(acc[nt], fo, kv + (int64_t)min(nt * 8 + g, S - 1) * 2 * E + E + h * 32, t);
+        }
       }
     }
     // ---- ±P (sign = dropout decision, written by the forward) straight from global memory at the accumulator positions; it is
@@ -497,12 +554,18 @@ __global__ void __launch_bounds__(NW * 32, NW == 4 ? 3 : 2) attn_bwd_mma_kernel(
       float dq[4][4];
 #pragma unroll
       for (int i = 0; i < 4; ++i) dq[i][0] = dq[i][1] = dq[i][2] = dq[i][3] = 0.f;
+      if (HOIST) {
+#pragma unroll
+        for (int kstep = 0; kstep < NH; ++kstep)
+          if (kstep * 8 < S) mma_tile_x_frag<PITCH>(dq, ps, kstep, kfr[kstep][0], kfr[kstep][1], g, t);
+      } else {
 #pragma unroll 4
-      for (int kstep = 0; kstep < NT; ++kstep) {
-        if (kstep * 8 >= S) break;
-        const float* k0 = kv + (int64_t)min(kstep * 8 + t, S - 1) * 2 * E + h * 32;      // (dS is zero past the last key)
-        const float* k1 = kv + (int64_t)min(kstep * 8 + t + 4, S - 1) * 2 * E + h * 32;
-        mma_tile_x<PITCH>(dq, ps, kstep, k0, k1, g, t);
+        for (int kstep = 0; kstep < NT; ++kstep) {
+          if (kstep * 8 >= S) break;
+          const float* k0 = kv + (int64_t)min(kstep * 8 + t, S - 1) * 2 * E + h * 32;      // (dS is zero past the last key)
+          const float* k1 = kv + (int64_t)min(kstep * 8 + t + 4, S - 1) * 2 * E + h * 32;
+          mma_tile_x<PITCH>(dq, ps, kstep, k0, k1, g, t);
+        }
       }
       float* out = a.dq + (int64_t)b * L * E + h * 32;
       store_rows_x(dq, out + (int64_t)min(r0, L - 1) * E, out + (int64_t)min(r1, L - 1) * E, ok0, ok1, a.scale, t);
