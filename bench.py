@@ -631,11 +631,18 @@ def run_sweep(cx: Ctx, args) -> None:
         steps = 100 if Bt <= 1024 else 30
         ms = cx.timed(step, steps, 10)
         ms_graph = None
-        if 0 < b <= 1024:   # launch-bound sizes: the same forward as one CUDA graph over static buffers (GraphedForward)
-            gf = head.graphed_forward(b)
-            gf.video.copy_(sets[0][0])
-            gf.audio.copy_(sets[0][1])
-            ms_graph = cx.timed(lambda i: gather_logits(gf(), Bt), steps, 10)
+        # launch-bound sizes: the same forward as one CUDA graph over static buffers (GraphedForward).  The decision must be the
+        # same on every rank (each timed call holds a collective): rank 0 owns the largest shard; ranks with an empty shard join
+        # the gathers with their eager (empty) step.
+        s0, e0 = shard_range(Bt, 0, cx.world)
+        if e0 - s0 <= 1024:
+            if b > 0:
+                gf = head.graphed_forward(b)
+                gf.video.copy_(sets[0][0])
+                gf.audio.copy_(sets[0][1])
+                ms_graph = cx.timed(lambda i: gather_logits(gf(), Bt), steps, 10)
+            else:
+                ms_graph = cx.timed(step, steps, 10)
         points.append({"B_total": Bt, "clips_rank0": b, "ms": ms, "clips_per_s": Bt / (ms * 1e-3), "ms_cuda_graph": ms_graph,
                        "l2": "two input sets rotated" if nsets == 2 else "inputs fit L2 (latency point)"})
         del sets
