@@ -227,7 +227,8 @@ XATTN_API int xattn_backward_ex(const xattn_config* cfg, const float* params, co
 /* ---- loss / optimizer ------------------------------------------------------------------------ */
 /* Mean-reduced cross entropy with label smoothing + its gradient w.r.t. logits.
  * Replaces nn.CrossEntropyLoss(label_smoothing) at train.py:1033 / :218.  loss_out: 1 float.
- * labels: int64[B]. grad_scale multiplies dlogits (1/world_size under data parallelism). */
+ * labels: int64[B], each in [0, C) — as with torch (which raises a device-side assert) anything else is a caller error and is
+ * not checked here.  grad_scale multiplies dlogits (1/world_size under data parallelism). */
 XATTN_API int xattn_ce_loss_fwd_bwd(const float* logits, const int64_t* labels, int32_t B, int32_t C, float label_smoothing,
                           float grad_scale, float* loss_out, float* dlogits, void* stream);
 

@@ -1000,6 +1000,7 @@ static int backward_f32_impl(const xattn_config& c, const float* params, const T
   const int HW = gated ? E : c.common_dim;
   const float scale = 1.0f / sqrtf((float)(E / H));
 
+  NvtxRange nvtx_bwd(g_tc_gemm ? "xattn_backward[tf32]" : "xattn_backward[fp32]");
   XF_CUDA(cudaMemsetAsync(grads, 0, sizeof(float) * pl.total, st));
 
   // ---- head (fusion.py:405-411) ----
@@ -1139,6 +1140,7 @@ static int backward_f32_impl(const xattn_config& c, const float* params, const T
     XF_CUDA(cudaEventRecord(ev, st));
     XF_CUDA(cudaStreamWaitEvent(opt.tail_stream, ev, 0));
   }
+  NvtxRange nvtx_in("input_projections_backward");
   // ---- input projections (fusion.py:386, :378, :372); dX only on request (Stage 1 freezes the backbones) ----
   linear_bwd_dw<float>(st, ws + w.d_a0, E, ws + w.aseq, E, G(XP_A_IN_W), B * Ta, E, E);
   if (!tok_bias_fused) launch_colsum(st, ws + w.d_a0, E, B * Ta, E, G(XP_A_IN_B));

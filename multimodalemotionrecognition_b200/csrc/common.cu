@@ -8,6 +8,8 @@
 #include <mutex>
 #include <vector>
 
+#include <nvtx3/nvToolsExt.h>
+
 namespace xf {
 
 static thread_local char g_err[512] = "";
@@ -59,6 +61,9 @@ int stage_timing_read(double* ms, int64_t* launches, int cap) {
   stage_drop();
   return ST_COUNT;
 }
+
+void nvtx_push(const char* name) { nvtxRangePushA(name); }
+void nvtx_pop() { nvtxRangePop(); }
 
 void set_error(const char* fmt, ...) {
   va_list ap;

@@ -77,19 +77,31 @@ inline cudaError_t launch_chain(void (*kernel)(KArgs...), dim3 grid, dim3 block,
   return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
 }
 void stage_mark(int stage, int end, cudaStream_t st);   // records an event on st (no-op unless timing is on)
+// NVTX range on the host thread that issues the launches (the reference has no tracing hooks; nsys / ncu --nvtx show
+// these).  nvtx3 is header-only and a no-op unless a tool is attached.  Defined in common.cu.
+void nvtx_push(const char* name);
+void nvtx_pop();
+struct NvtxRange {
+  explicit NvtxRange(const char* name) { nvtx_push(name); }
+  ~NvtxRange() { nvtx_pop(); }
+  NvtxRange(const NvtxRange&) = delete;
+  NvtxRange& operator=(const NvtxRange&) = delete;
+};
+const char* stage_name(int i);
 struct StageScope {
   int s;
   cudaStream_t st;
   StageScope(int stage, cudaStream_t stream) : s(stage), st(stream) {
+    nvtx_push(stage_name(s));
     if (g_stage_timing) stage_mark(s, 0, st);
   }
   ~StageScope() {
     if (g_stage_timing) stage_mark(s, 1, st);
+    nvtx_pop();
   }
 };
 int stage_timing_enable(int on);
 int stage_timing_read(double* ms, int64_t* launches, int cap);
-const char* stage_name(int i);
 
 // ---- parameter layout ----------------------------------------------------------------------------
 struct ParamLayout {

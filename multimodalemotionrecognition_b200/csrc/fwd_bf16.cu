@@ -269,6 +269,7 @@ int launch_video_update(const Bf16Ctx& x) {
 int forward_bf16(const xattn_config& c, const float* params, const void* packed, const void* xv, const void* xa, float* logits,
                  void* ws, cudaStream_t st, bool fork) {
   XF_TRY(bf16_supported(c));
+  NvtxRange nvtx_fwd("xattn_forward[bf16]");
   Bf16Ctx x;
   x.cfg = &c;
   x.params = params;

@@ -674,6 +674,7 @@ static int forward_f32_impl(const xattn_config& c, const float* params, const TI
   const float p_attn = train ? c.p_attn : 0.f, p_path = train ? c.p_path : 0.f, p_head = train ? c.p_head : 0.f,
               p_prior = train ? c.p_prior : 0.f;
 
+  NvtxRange nvtx_fwd(g_tc_gemm ? "xattn_forward[tf32]" : "xattn_forward[fp32]");
   // projections (fusion.py:372, :378, :386)
   if (g_tc_gemm && std::is_same<TIO, __nv_bfloat16>::value && E % 128 == 0 && c.Dv % 64 == 0 && c.Da % 64 == 0) {
     // bf16 embeddings: kind::f16 products against bf16-rounded copies of the two weights (gemm_tc.cu), fp32 out

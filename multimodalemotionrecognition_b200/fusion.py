@@ -169,6 +169,22 @@ def softmax_top1(logits: torch.Tensor, probs: Optional[torch.Tensor] = None, top
     return probs, top1, top1_prob
 
 
+class HostResult:
+    """Pending result of ``predict_host_async``: ``result()`` waits for the call's device->host copy and returns fresh host
+    tensors (logits / probabilities ``[B,C]``, or ``(probs, top1, top1_prob)``)."""
+
+    def __init__(self, event: "torch.cuda.Event", host: torch.Tensor, top1) -> None:
+        self._event, self._host, self._top1 = event, host, top1
+
+    def done(self) -> bool:
+        return self._event.query()
+
+    def result(self):
+        self._event.synchronize()
+        out = self._host.clone()
+        return out if self._top1 is None else (out, self._top1[0].clone(), self._top1[1].clone())
+
+
 class GraphedForward:
     """One CUDA graph of the bf16 forward at a fixed batch size ("CUDA-graph per batch size").
 
@@ -331,7 +347,12 @@ class XAttnKernelsMixin:
         cfg.p_attn, cfg.p_path = self.xattn_attn_dropout, self.xattn_stochastic_depth
         cfg.p_head, cfg.p_prior = self.xattn_head_dropout, self.xattn_prior_dropout
         cfg.p_pool = self.xattn_pool_dropout
-        cfg.seed = torch.initial_seed() & 0xFFFFFFFFFFFFFFFF
+        seed = torch.initial_seed() & 0xFFFFFFFFFFFFFFFF
+        if torch.distributed.is_available() and torch.distributed.is_initialized():
+            # data parallel: every rank holds different clips, so every rank must draw its own dropout masks (the same seed on
+            # all ranks would give shard r's clip i the mask of shard 0's clip i)
+            seed ^= ((torch.distributed.get_rank() + 1) * 0x9E3779B97F4A7C15) & 0xFFFFFFFFFFFFFFFF
+        cfg.seed = seed
         cfg.offset = self._rng_offset
         return cfg
 
@@ -523,7 +544,7 @@ class XAttnKernelsMixin:
             if key != g.key:
                 g = None
         if g is None:
-            if len(cache) >= 16:
+            if len(cache) >= 64:
                 cache.pop(next(iter(cache)))
             g = GraphedForward(self, B, T, Ta, dtype, device)
             cache[k] = g
@@ -536,9 +557,20 @@ class XAttnKernelsMixin:
         ``.to(device)`` -> model -> ``softmax`` -> ``.cpu()``) and the worker's ``torch.stack(...).to(device)``
         (``inference_worker.py:131-134``).  The host batch (pinned memory for full PCIe rate) is cut into ``chunk``-clip
         pieces that are copied on a side stream into two device staging slots while the previous piece is computed;
-        returns host logits (or probabilities) ``[B,C]`` after synchronising on the final device->host copy.
+        returns host logits (or probabilities) ``[B,C]`` after synchronising on the final device->host copy — a fresh tensor,
+        as the reference's ``.cpu()`` gives (the pinned staging buffers are reused by later calls).
         ``top1=True`` returns ``(probs [B,C], top1 int32 [B], top1_prob [B])`` on the host — the three things the worker
-        puts into its result (``inference_worker.py:136-143``), computed on the device in the same launch as the softmax."""
+        puts into its result (``inference_worker.py:136-143``), computed on the device in the same launch as the softmax.
+        ``predict_host_async`` is the same without the final wait."""
+        return self.predict_host_async(video_host, audio_host, chunk=chunk, probs=probs, graph_max=graph_max, top1=top1).result()
+
+    @torch.no_grad()
+    def predict_host_async(self, video_host: torch.Tensor, audio_host: torch.Tensor, chunk: int = 1024,
+                           probs: bool = False, graph_max: int = 256, top1: bool = False) -> "HostResult":
+        """``predict_host`` without the final synchronisation: enqueues H2D, forward and D2H and returns a ``HostResult``
+        whose ``result()`` waits for this call's D2H only.  Two calls may be in flight (the pinned output buffers and the
+        device staging slots alternate between calls), so a serving loop can issue batch i+1 — its H2D runs on the copy
+        stream beside the compute of batch i — before it collects batch i.  A third call waits for the first one."""
         probs = probs or top1
         if video_host.is_cuda or audio_host.is_cuda:
             raise ValueError("predict_host takes host tensors; call forward() for device tensors")
@@ -551,64 +583,71 @@ class XAttnKernelsMixin:
             raise RuntimeError("the B200 xattn fusion head has no CPU path: move the module to an sm_100 device")
         B, T_, Dv = video_host.shape
         Ta_, Da = audio_host.shape[1], audio_host.shape[2]
-        out_buf = getattr(self, "_host_out", None)
-        if out_buf is None or out_buf.shape[0] < B or out_buf.shape[1] != self.num_classes:
-            out_buf = torch.empty((max(B, 1), self.num_classes), dtype=torch.float32).pin_memory()
-            self._host_out = out_buf
-        t1_buf = getattr(self, "_host_top1", None)
-        if top1 and (t1_buf is None or t1_buf[0].shape[0] < B):
-            t1_buf = (torch.empty((max(B, 1),), dtype=torch.int32).pin_memory(), torch.empty((max(B, 1),), dtype=torch.float32).pin_memory())
-            self._host_top1 = t1_buf
-        if 0 < B <= min(graph_max, chunk) and video_host.dtype == torch.bfloat16 and self.precision in ("auto", "bf16") \
-                and self._bf16_supported(T_, Ta_):
-            # worker-sized batches (inference_worker.py:33-34) are launch-bound: H2D, one graph launch, D2H
-            with torch.cuda.device(dev):
-                g = self.graphed_forward(B, T_, Ta_, video_host.dtype, dev)
-                g.video.copy_(video_host, non_blocking=True)
-                g.audio.copy_(audio_host, non_blocking=True)
-                g()
-                host = out_buf[:B]
-                host.copy_(g.probs if probs else g.logits, non_blocking=True)
-                if top1:
-                    t1_buf[0][:B].copy_(g.top1, non_blocking=True)
-                    t1_buf[1][:B].copy_(g.top1_prob, non_blocking=True)
-                torch.cuda.current_stream(dev).synchronize()
-            return (host, t1_buf[0][:B], t1_buf[1][:B]) if top1 else host
-        key = (dev, chunk, T_, Dv, Ta_, Da, video_host.dtype)
-        pipe = getattr(self, "_host_pipe", None)
-        if pipe is None or pipe["key"] != key:
-            pipe = {"key": key, "stream": torch.cuda.Stream(dev),
-                    "v": [torch.empty((chunk, T_, Dv), dtype=video_host.dtype, device=dev) for _ in range(2)],
-                    "a": [torch.empty((chunk, Ta_, Da), dtype=audio_host.dtype, device=dev) for _ in range(2)],
-                    "ready": [torch.cuda.Event() for _ in range(2)], "done": [torch.cuda.Event() for _ in range(2)]}
-            self._host_pipe = pipe
+        # per-call output slot: pinned logits / top-1 buffers and the event that marks their D2H
+        slots = self.__dict__.setdefault("_host_slots", [None, None])
+        calls = self.__dict__.get("_host_calls", 0)
+        self._host_calls = calls + 1
+        si = calls & 1
+        slot = slots[si]
+        if slot is not None:
+            slot["event"].synchronize()          # the call that used this slot two calls ago has delivered
+        if slot is None or slot["out"].shape[0] < B or slot["out"].shape[1] != self.num_classes:
+            cap = max(B, 1)
+            slot = {"out": torch.empty((cap, self.num_classes), dtype=torch.float32).pin_memory(),
+                    "top1": torch.empty((cap,), dtype=torch.int32).pin_memory(),
+                    "top1p": torch.empty((cap,), dtype=torch.float32).pin_memory(), "event": torch.cuda.Event()}
+            slots[si] = slot
+        host = slot["out"][:B]
         with torch.cuda.device(dev):
             cur = torch.cuda.current_stream(dev)
-            side = pipe["stream"]
-            side.wait_stream(cur)
-            logits = torch.empty((B, self.num_classes), dtype=torch.float32, device=dev)
-            for i, s in enumerate(range(0, B, chunk)):
-                e = min(B, s + chunk)
-                slot = i & 1
-                with torch.cuda.stream(side):
-                    if i >= 2:
-                        side.wait_event(pipe["done"][slot])
-                    pipe["v"][slot][: e - s].copy_(video_host[s:e], non_blocking=True)
-                    pipe["a"][slot][: e - s].copy_(audio_host[s:e], non_blocking=True)
-                    pipe["ready"][slot].record(side)
-                cur.wait_event(pipe["ready"][slot])
-                self._launch_forward(pipe["v"][slot][: e - s], pipe["a"][slot][: e - s], save=False, training=False,
-                                     out=logits[s:e])
-                pipe["done"][slot].record(cur)
-            if probs:
-                _, t1, t1p = softmax_top1(logits, logits)
-            host = out_buf[:B]
-            host.copy_(logits, non_blocking=True)
-            if top1:
-                t1_buf[0][:B].copy_(t1, non_blocking=True)
-                t1_buf[1][:B].copy_(t1p, non_blocking=True)
-            cur.synchronize()
-        return (host, t1_buf[0][:B], t1_buf[1][:B]) if top1 else host
+            if 0 < B <= min(graph_max, chunk) and video_host.dtype == torch.bfloat16 and self.precision in ("auto", "bf16") \
+                    and self._bf16_supported(T_, Ta_):
+                # worker-sized batches (inference_worker.py:33-34) are launch-bound: H2D, one graph launch, D2H.  Graphs are kept
+                # per batch size rounded up to a multiple of 8 (clips are independent: the spare rows compute on stale data and
+                # are not read), so a worker whose batches vary in size re-uses a handful of graphs.
+                Bp = (B + 7) & ~7
+                g = self.graphed_forward(Bp, T_, Ta_, video_host.dtype, dev)
+                g.video[:B].copy_(video_host, non_blocking=True)
+                g.audio[:B].copy_(audio_host, non_blocking=True)
+                g()
+                host.copy_((g.probs if probs else g.logits)[:B], non_blocking=True)
+                if top1:
+                    slot["top1"][:B].copy_(g.top1[:B], non_blocking=True)
+                    slot["top1p"][:B].copy_(g.top1_prob[:B], non_blocking=True)
+            else:
+                key = (dev, chunk, T_, Dv, Ta_, Da, video_host.dtype)
+                pipe = getattr(self, "_host_pipe", None)
+                if pipe is None or pipe["key"] != key:
+                    pipe = {"key": key, "stream": torch.cuda.Stream(dev), "n": 0,
+                            "v": [torch.empty((chunk, T_, Dv), dtype=video_host.dtype, device=dev) for _ in range(2)],
+                            "a": [torch.empty((chunk, Ta_, Da), dtype=audio_host.dtype, device=dev) for _ in range(2)],
+                            "ready": [torch.cuda.Event() for _ in range(2)], "done": [torch.cuda.Event() for _ in range(2)]}
+                    self._host_pipe = pipe
+                side = pipe["stream"]
+                logits = torch.empty((B, self.num_classes), dtype=torch.float32, device=dev)
+                for s in range(0, B, chunk):
+                    e = min(B, s + chunk)
+                    n = pipe["n"]                 # pieces issued so far, over ALL calls: the staging slots alternate across calls
+                    pipe["n"] = n + 1
+                    st = n & 1
+                    with torch.cuda.stream(side):
+                        if n >= 2:
+                            side.wait_event(pipe["done"][st])      # the forward that read this slot two pieces ago is done
+                        pipe["v"][st][: e - s].copy_(video_host[s:e], non_blocking=True)
+                        pipe["a"][st][: e - s].copy_(audio_host[s:e], non_blocking=True)
+                        pipe["ready"][st].record(side)
+                    cur.wait_event(pipe["ready"][st])
+                    self._launch_forward(pipe["v"][st][: e - s], pipe["a"][st][: e - s], save=False, training=False,
+                                         out=logits[s:e])
+                    pipe["done"][st].record(cur)
+                if probs:
+                    _, t1, t1p = softmax_top1(logits, logits)
+                host.copy_(logits, non_blocking=True)
+                if top1:
+                    slot["top1"][:B].copy_(t1, non_blocking=True)
+                    slot["top1p"][:B].copy_(t1p, non_blocking=True)
+            slot["event"].record(cur)
+        return HostResult(slot["event"], host, (slot["top1"][:B], slot["top1p"][:B]) if top1 else None)
 
     def mel_unfold(self, mel: torch.Tensor) -> torch.Tensor:
         """mel [B, 1, n_mels, Ta] or [B, n_mels, Ta] -> time-unfolded rows [B, Ta, 3*n_mels] (csrc/mel_frontend.cu), the

@@ -171,10 +171,20 @@ class FrozenEmbeddingCache:
     @staticmethod
     @torch.no_grad()
     def embed(model, video: torch.Tensor, audio: torch.Tensor) -> tuple[torch.Tensor, torch.Tensor]:
-        """The frozen part of ``FusionModel.forward`` (``fusion.py:368-370``, ``:377``)."""
+        """The frozen part of ``FusionModel.forward`` (``fusion.py:368-370``, ``:377``), with both backbones in ``eval()`` for
+        the duration of the call.  This DIVERGES from the reference on purpose: there ``model.train()`` (``train.py:194``)
+        also flips the frozen ResNet's BatchNorms and WavLM's dropouts into training mode and recomputes the embeddings every
+        epoch; an embedding that is computed once and cached must not carry one epoch's batch statistics or dropout mask."""
         b, t, c, h, w = video.shape
-        v_feat = model.video_model.backbone(video.view(b * t, c, h, w)).view(b, t, -1)
-        a_seq = model.audio_model.encode_sequence(audio)
+        modes = [(m, m.training) for m in (model.video_model, model.audio_model)]
+        for m, _ in modes:
+            m.eval()
+        try:
+            v_feat = model.video_model.backbone(video.view(b * t, c, h, w)).view(b, t, -1)
+            a_seq = model.audio_model.encode_sequence(audio)
+        finally:
+            for m, was in modes:
+                m.train(was)
         return v_feat, a_seq
 
     def fetch_or_compute(self, model, indices: torch.Tensor, video: torch.Tensor, audio: torch.Tensor):
