@@ -26,7 +26,7 @@
 extern "C" {
 #endif
 
-#define XATTN_ABI_VERSION 16
+#define XATTN_ABI_VERSION 17
 
 #if defined(__GNUC__)
 #define XATTN_API __attribute__((visibility("default")))
@@ -297,6 +297,14 @@ XATTN_API int xattn_mel_unfold(const void* mel, void* unfolded, int32_t io_dtype
 XATTN_API int flat_head_alignment_workspace_bytes(const flat_head_config* cfg, int64_t* bytes);
 XATTN_API int flat_head_alignment_loss(const flat_head_config* cfg, const float* params, const float* logit_scale, const void* video_emb,
                                        const void* audio_emb, float* loss, void* workspace, int64_t workspace_bytes, void* stream);
+
+/* Backbone tail -> head hand-off (fusion.py:368-370, :377; video.py:23 AdaptiveAvgPool2d; wavlm_audio.py:183 last_hidden_state).
+ * x fp32 [n_clips · rows_per_clip, D, R] -> the mean over the R innermost values (R = h·w of ResNet18's last feature map, R = 1
+ * for WavLM hidden states), rounded to bf16, written to rows (dst_clip[c] · rows_per_clip + j) of out_bf16 [*, D] (dst_clip NULL:
+ * c itself; device int64).  The embeddings reach the tensor-core kernels without an fp32 round trip and land directly in a
+ * resident embedding table (FrozenEmbeddingCache). */
+XATTN_API int xattn_emit_embeddings_bf16(const float* x, void* out_bf16, const int64_t* dst_clip, int32_t n_clips, int32_t rows_per_clip,
+                               int32_t D, int32_t R, void* stream);
 
 /* ---- diagnostics ---------------------------------------------------------------------------------- */
 /* Kernel launches issued by this library since process start (bench.py's gpu_launches evidence). */

@@ -4,6 +4,7 @@
 #include "gemm_tc.cuh"
 
 namespace xf {
+int emit_embeddings_bf16(cudaStream_t st, const float* x, void* out, const int64_t* dst, int n_clips, int rows_per_clip, int D, int R);
 int ce_loss_fwd_bwd(const float* logits, const int64_t* labels, int B, int C, float label_smoothing, float grad_scale,
                     float* loss_out, float* dlogits, cudaStream_t st);
 int adam_step(float* p, const float* g, float* m, float* v, int64_t n, float lr, float beta1, float beta2, float eps, float wd,
@@ -163,4 +164,12 @@ extern "C" XATTN_API int xattn_adam_step(float* params, const float* grads, floa
     XF_FAIL(XATTN_ERR_ALIGN, "pointers must be 16-byte aligned");
   XF_TRY(check_device_sm100());
   return adam_step(params, grads, exp_avg, exp_avg_sq, n, lr, beta1, beta2, eps, weight_decay, step, decoupled, (cudaStream_t)stream);
+}
+
+extern "C" XATTN_API int xattn_emit_embeddings_bf16(const float* x, void* out_bf16, const int64_t* dst_clip, int32_t n_clips,
+                                                    int32_t rows_per_clip, int32_t D, int32_t R, void* stream) {
+  if (!x || !out_bf16) XF_FAIL(XATTN_ERR_NULL, "NULL pointer argument");
+  if (misaligned(x) || misaligned(out_bf16)) XF_FAIL(XATTN_ERR_ALIGN, "pointers must be 16-byte aligned");
+  XF_TRY(check_device_sm100());
+  return emit_embeddings_bf16((cudaStream_t)stream, x, out_bf16, dst_clip, n_clips, rows_per_clip, D, R);
 }

@@ -187,11 +187,46 @@ class FrozenEmbeddingCache:
                 m.train(was)
         return v_feat, a_seq
 
+    @torch.no_grad()
+    def embed_into(self, model, indices: torch.Tensor, video: torch.Tensor, audio: torch.Tensor) -> None:
+        """Runs the frozen backbones on (video, audio) and writes their outputs into the table rows ``indices`` through
+        ``xattn_emit_embeddings_bf16`` (csrc/embed_ops.cu): ResNet18's spatial mean — its trailing ``AdaptiveAvgPool2d``
+        (``video.py:23``) is skipped and done by the kernel — and the bf16 rounding of both modalities are fused with the
+        write into the table, so no fp32 embedding tensor exists between backbone and head.  CUDA bf16 tables only."""
+        idx = indices.to(device=self.valid.device, dtype=torch.int64).contiguous()
+        b, t, c, h, w = video.shape
+        modes = [(m, m.training) for m in (model.video_model, model.audio_model)]
+        for m, _ in modes:
+            m.eval()
+        try:
+            backbone = model.video_model.backbone
+            frames = video.view(b * t, c, h, w)
+            if isinstance(backbone, torch.nn.Sequential) and len(backbone) > 0 and isinstance(backbone[-1], torch.nn.AdaptiveAvgPool2d) \
+                    and backbone[-1].output_size in (1, (1, 1)):
+                fmap = backbone[:-1](frames).float().contiguous()                    # [B·T, Dv, h', w']
+            else:
+                fmap = backbone(frames).float().reshape(b * t, -1, 1).contiguous()   # already pooled: R = 1
+            a_seq = model.audio_model.encode_sequence(audio).float().contiguous()    # [B, Ta, Da]
+        finally:
+            for m, was in modes:
+                m.train(was)
+        dev = self.video.device
+        lib = _lib.load()
+        with torch.cuda.device(dev):
+            R = fmap[0, 0].numel()
+            _lib.check(lib.xattn_emit_embeddings_bf16(_ptr(fmap), _ptr(self.video), _ptr(idx), b, t, fmap.shape[1], R, _stream_ptr(dev)))
+            _lib.check(lib.xattn_emit_embeddings_bf16(_ptr(a_seq), _ptr(self.audio), _ptr(idx), b, a_seq.shape[1], a_seq.shape[2], 1,
+                                                      _stream_ptr(dev)))
+        self.valid[idx] = True
+
     def fetch_or_compute(self, model, indices: torch.Tensor, video: torch.Tensor, audio: torch.Tensor):
         """Embeddings of the batch; the backbones run only on the samples whose index is new."""
         miss = self.missing(indices)
         n_miss = int(miss.sum())
-        if n_miss:
+        if n_miss and self.video.is_cuda and self.video.dtype == torch.bfloat16 and video.is_cuda:
+            sel = miss.to(video.device)
+            self.embed_into(model, indices.to(self.valid.device)[miss], video[sel], audio[sel])
+        elif n_miss:
             sel = miss.to(video.device)
             v_feat, a_seq = self.embed(model, video[sel], audio[sel])
             self.put(indices.to(self.valid.device)[miss], v_feat, a_seq)

@@ -673,3 +673,62 @@ def test_input_gradients_reach_trainable_backbones(cuda_device, io):
     xv2 = xv.detach().to(cuda_device).requires_grad_(True)
     torch.nn.functional.cross_entropy(m(xv2, xa.detach().to(cuda_device)), labels.to(cuda_device)).backward()
     assert (xv2.grad.float().cpu() - rv.grad).abs().max().item() <= tol * rv.grad.abs().max().item() + 1e-9
+
+
+def test_frozen_embedding_cache_emits_bf16_from_the_backbone_tail(cuda_device):
+    """SURVEY 8f rank 1 on the GPU: the cache fills its bf16 table through xattn_emit_embeddings_bf16 (spatial mean of the
+    ResNet-style feature map + bf16 rounding + scatter by dataset index, csrc/embed_ops.cu), the backbones run once per
+    sample, and a cached Stage-1 step equals the step on embeddings computed the reference's way (fusion.py:368-370, :377)."""
+    from multimodalemotionrecognition_b200 import FusionModel
+    from multimodalemotionrecognition_b200.training import FrozenEmbeddingCache, Stage1Trainer
+
+    class Video(torch.nn.Module):
+        def __init__(self):
+            super().__init__()
+            self.embedding_dim = 512
+            self.backbone = torch.nn.Sequential(torch.nn.Conv2d(3, 512, 3, stride=2), torch.nn.ReLU(), torch.nn.AdaptiveAvgPool2d((1, 1)))
+            self.calls = 0
+
+        def encode(self, x):
+            raise NotImplementedError
+
+    class Audio(torch.nn.Module):
+        def __init__(self):
+            super().__init__()
+            self.sequence_dim = self.embedding_dim = 768
+            self.proj = torch.nn.Linear(40, 768)
+            self.calls = 0
+
+        def encode_sequence(self, x):          # [B, Ta, 40] "waveform frames" -> [B, Ta, 768]
+            self.calls += 1
+            return self.proj(x)
+
+    torch.manual_seed(0)
+    model = FusionModel(Audio(), Video(), 8, mode="xattn", audio_n_mels=768, xattn_use_emotion_prior=True, precision="tf32").to(cuda_device)
+    N, B, T, Ta = 24, 8, 16, 149
+    g = torch.Generator().manual_seed(4)
+    video = torch.randn(N, T, 3, 9, 9, generator=g).to(cuda_device)
+    audio = torch.randn(N, Ta, 40, generator=g).to(cuda_device)
+    labels = torch.randint(0, 8, (N,), generator=g).to(cuda_device)
+    cache = FrozenEmbeddingCache(N, T, Ta, device=cuda_device)
+    idx = torch.tensor([3, 20, 7, 11, 0, 5, 23, 9])
+    v_emb, a_emb = cache.fetch_or_compute(model, idx, video[idx], audio[idx])
+    assert cache.misses == B and cache.hits == 0 and model.audio_model.calls == 1
+    with torch.no_grad():   # the reference's way: full backbone (with its pooling), fp32, then the cast
+        v_ref = model.video_model.backbone(video[idx].view(B * T, 3, 9, 9)).view(B, T, 512)
+        a_ref = model.audio_model.proj(audio[idx])
+    assert v_emb.dtype == torch.bfloat16 and v_emb.shape == (B, T, 512) and a_emb.shape == (B, Ta, 768)
+    assert torch.equal(a_emb, a_ref.bfloat16())                               # a pure rounding: bit-identical
+    assert (v_emb.float() - v_ref).abs().max().item() <= 2.0 ** -8 * max(1.0, v_ref.abs().max().item())   # mean order + rounding
+    assert torch.equal(cache.video[idx], v_emb) and bool(cache.valid[idx].all()) and int(cache.valid.sum()) == B
+    again_v, again_a = cache.fetch_or_compute(model, idx, video[idx], audio[idx])
+    assert cache.hits == B and model.audio_model.calls == 1                   # second epoch: no backbone call
+    assert torch.equal(again_v, v_emb) and torch.equal(again_a, a_emb)
+    # a cached step == a step on the same embeddings
+    model.train()
+    tr = Stage1Trainer(model, lr=1e-3)
+    loss_c = float(tr.step_cached(cache, idx, video[idx], audio[idx], labels[idx], training=False))
+    torch.manual_seed(0)
+    model2 = FusionModel(Audio(), Video(), 8, mode="xattn", audio_n_mels=768, xattn_use_emotion_prior=True, precision="tf32").to(cuda_device).train()
+    loss_d = float(Stage1Trainer(model2, lr=1e-3).step(v_emb, a_emb, labels[idx], training=False))
+    assert abs(loss_c - loss_d) <= 1e-6
