@@ -461,6 +461,19 @@ def run_forward(cx: Ctx, args) -> None:
         e2e_all[eb] = {"value": eb * cx.world * e2e_steps / dt, "unit": "clips/s", "ms_per_call": dt / e2e_steps * 1e3,
                        "h2d_bytes_per_step": (hv.numel() + ha.numel()) * 2 * cx.world, "d2h_bytes_per_step": out.numel() * 4 * cx.world,
                        "steps": e2e_steps}
+        if eb != B:   # the same with two batches in flight (predict_host_async): batch i+1 is issued before batch i is collected
+            cx.barrier()
+            t0 = time.perf_counter()
+            prev = None
+            for _ in range(e2e_steps):
+                cur = head.predict_host_async(hv, ha)
+                if prev is not None:
+                    prev.result()
+                prev = cur
+            prev.result()
+            cx.barrier()
+            dt2 = cx.max_over_ranks(time.perf_counter() - t0)
+            e2e_all[eb]["two_in_flight"] = {"value": eb * cx.world * e2e_steps / dt2, "ms_per_call": dt2 / e2e_steps * 1e3}
     e2e = dict(e2e_all[B], api="XAttnFusionHead.predict_host (pinned host in, host logits out)", numa_node_rank0=cx.numa_node)
     if len(e2e_all) > 1:   # the worker batch sizes of the reference's serving path (inference_worker.py:33-34), latency view
         e2e["worker_batches"] = {f"B={k}": v for k, v in e2e_all.items() if k != B}
