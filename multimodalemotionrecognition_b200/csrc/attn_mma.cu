@@ -27,6 +27,19 @@ __device__ __forceinline__ void mma_tf32(float (&d)[4], uint32_t a0, uint32_t a1
                : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
 }
 __device__ __forceinline__ uint32_t fu(float x) { return __float_as_uint(x); }
+// global -> shared without a register round trip: the copy completes while the warp issues its first products
+__device__ __forceinline__ void cp_async4(float* smem_dst, const float* gsrc) {
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"((uint32_t)__cvta_generic_to_shared(smem_dst)), "l"(gsrc) : "memory");
+}
+__device__ __forceinline__ void cp_async16(float* smem_dst, const float* gsrc) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((uint32_t)__cvta_generic_to_shared(smem_dst)), "l"(gsrc) : "memory");
+}
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;" ::: "memory"); }
+// pull `bytes` of a clip's operand towards L2 ahead of the fragment loads that will want it (one line per thread and step)
+__device__ __forceinline__ void prefetch_l2(const float* base, int64_t bytes, int tid, int nthreads) {
+  const char* p = reinterpret_cast<const char*>(base);
+  for (int64_t o = (int64_t)tid * 128; o < bytes; o += (int64_t)nthreads * 128) asm volatile("prefetch.global.L2 [%0];" ::"l"(p + o));
+}
 __device__ __forceinline__ float4 ldg4(const float* p) { return __ldg(reinterpret_cast<const float4*>(p)); }
 
 // Fragment layouts of mma.m16n8k8 (lane = 4 g + t):
@@ -137,6 +150,7 @@ __global__ void __launch_bounds__(NW * 32, NW == 4 ? 4 : 2) attn_fwd_mma_kernel(
   float* ps = sm + (a.qs ? Lp * PITCH : 0) + warp * 16 * PITCH;
   const float* q = a.q + (int64_t)b * L * E;
   const float* kv = a.kv + (int64_t)b * S * 2 * E;
+  if (NT <= 2) prefetch_l2(q, (int64_t)L * E * 4, tid, NW * 32);   // a2v: ten query tiles per head, fetched item by item
   if (a.qs) {
     const float bscale = a.bias_scale[0];
     const float* qs = a.qs + (int64_t)b * L;
@@ -299,6 +313,10 @@ __global__ void __launch_bounds__(NW * 32, NW == 4 ? 3 : 2) attn_bwd_mma_kernel(
   const float* dO = a.dO + (int64_t)b * L * E;
   const float bscale = prior ? a.bias_scale[0] : 0.f;
   const float inv_keep = a.p_drop > 0.f ? 1.f / (1.f - a.p_drop) : 1.f;
+  prefetch_l2(kv, (int64_t)S * 2 * E * 4, tid, NW * 32);
+  prefetch_l2(dO, (int64_t)L * E * 4, tid, NW * 32);
+  prefetch_l2(q, (int64_t)L * E * 4, tid, NW * 32);
+  prefetch_l2(a.P + (int64_t)b * H * L * S, (int64_t)H * L * S * 4, tid, NW * 32);
   {
     const int nacc = Lp + NT * 8 + 3 * E + 4 + (ACC ? H * NT * 8 * 64 : 0);
     for (int i = tid; i < nacc; i += NW * 32) accs[i] = 0.f;
@@ -375,6 +393,25 @@ __global__ void __launch_bounds__(NW * 32, NW == 4 ? 3 : 2) attn_bwd_mma_kernel(
     const bool ok0 = r0 < L, ok1 = r1 < L;
     const int rows_valid = min(16, L - m0);
     const int64_t base0 = (((int64_t)b * H + h) * L + m0) * S;
+    // ---- ±P (sign = dropout decision, written by the forward) starts its way into the tile: asynchronous copies that land while
+    //      the dPd products below are issued; rows / keys past the end are zero ----
+    __syncwarp();   // the previous item's products have finished reading the tile
+    {
+      const float* pg = a.P + base0;
+      if ((S & 3) == 0 && (reinterpret_cast<uintptr_t>(a.P) & 15) == 0) {
+        for (int i = lane; i < 16 * NT * 2; i += 32) {   // 16-byte pieces
+          const int r = i / (NT * 2), s4 = (i - r * (NT * 2)) * 4;
+          if (r < rows_valid && s4 < S) cp_async16(ps + r * PITCH + s4, pg + (int64_t)r * S + s4);
+          else *reinterpret_cast<float4*>(ps + r * PITCH + s4) = make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+      } else {
+        for (int i = lane; i < 16 * NT * 8; i += 32) {
+          const int r = i / (NT * 8), s1 = i - r * (NT * 8);
+          if (r < rows_valid && s1 < S) cp_async4(ps + r * PITCH + s1, pg + (int64_t)r * S + s1);
+          else ps[r * PITCH + s1] = 0.f;
+        }
+      }
+    }
     // ---- dPd = dO V^T ----
     float acc[NT][4];
     {
@@ -389,28 +426,14 @@ __global__ void __launch_bounds__(NW * 32, NW == 4 ? 3 : 2) attn_bwd_mma_kernel(
         }
       }
     }
-    // ---- ±P (sign = dropout decision, written by the forward) straight from global memory at the accumulator positions; it is
-    //      parked in the tile at the lane's own positions for the second sweep.  Rows / keys past the end are zero. ----
-    __syncwarp();   // the previous item's products have finished reading the tile
+    cp_async_wait_all();
+    __syncwarp();
     // ---- dS at the accumulator positions (kept in acc); bias gradients; Pd into the tile ----
     float rd0 = 0.f, rd1 = 0.f;
-    const float* prow0 = a.P + base0 + (int64_t)g * S;
-    const float* prow1 = a.P + base0 + (int64_t)(g + 8) * S;
-    const bool al0 = ((base0 + (int64_t)g * S) & 1) == 0, al1 = ((base0 + (int64_t)(g + 8) * S) & 1) == 0;   // 8-byte aligned rows
 #pragma unroll
     for (int nt = 0; nt < NT; ++nt) {
       const int c = nt * 8 + 2 * t;
-      float2 x0 = make_float2(0.f, 0.f), x1 = make_float2(0.f, 0.f);
-      if (ok0 && c < S) {
-        if (al0 && c + 1 < S) x0 = __ldg(reinterpret_cast<const float2*>(prow0 + c));
-        else { x0.x = __ldg(prow0 + c); if (c + 1 < S) x0.y = __ldg(prow0 + c + 1); }
-      }
-      if (ok1 && c < S) {
-        if (al1 && c + 1 < S) x1 = __ldg(reinterpret_cast<const float2*>(prow1 + c));
-        else { x1.x = __ldg(prow1 + c); if (c + 1 < S) x1.y = __ldg(prow1 + c + 1); }
-      }
-      *reinterpret_cast<float2*>(ps + g * PITCH + c) = x0;
-      *reinterpret_cast<float2*>(ps + (g + 8) * PITCH + c) = x1;
+      const float2 x0 = *reinterpret_cast<const float2*>(ps + g * PITCH + c), x1 = *reinterpret_cast<const float2*>(ps + (g + 8) * PITCH + c);
       // dP = dPd ⊙ mask (0 where dropped, 1/keep where kept)
       acc[nt][0] *= signbit(x0.x) ? 0.f : inv_keep; acc[nt][1] *= signbit(x0.y) ? 0.f : inv_keep;
       acc[nt][2] *= signbit(x1.x) ? 0.f : inv_keep; acc[nt][3] *= signbit(x1.y) ? 0.f : inv_keep;
