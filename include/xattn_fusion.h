@@ -26,7 +26,7 @@
 extern "C" {
 #endif
 
-#define XATTN_ABI_VERSION 17
+#define XATTN_ABI_VERSION 18
 
 #if defined(__GNUC__)
 #define XATTN_API __attribute__((visibility("default")))
@@ -78,14 +78,18 @@ typedef struct xattn_config {
   int32_t pool_mode;    /* XATTN_POOL_MEAN (temporal.py:108-109) | XATTN_POOL_ATTN (TemporalAttentionPooling,
                            temporal.py:9-26: LN -> Linear -> GELU -> Dropout -> Linear -> softmax over time -> weighted
                            sum; fp32 / tf32 family, forward and backward)
-                           XATTN_POOL_TRANSFORMER (TemporalTransformerPooling, temporal.py:46-75: sinusoidal positions, one
-                           pre-norm TransformerEncoderLayer (GELU, FFN = 4·E), then the attention pooling; forward only) */
+                           XATTN_POOL_TRANSFORMER (TemporalTransformerPooling, temporal.py:46-75: sinusoidal positions,
+                           pool_layers pre-norm TransformerEncoderLayers (GELU, FFN = 4·E, dropout p_pool), then the attention
+                           pooling; fp32 / tf32 family, forward and backward) */
   int32_t pool_heads;   /* temporal_num_heads: heads of the pooler's self-attention (XATTN_POOL_TRANSFORMER) */
+  int32_t pool_layers;  /* temporal_num_layers: encoder layers of XATTN_POOL_TRANSFORMER, 1..XATTN_MAX_POOL_LAYERS (0 reads as 1) */
   float p_attn;         /* attention dropout            (fusion.py:277,280)          */
   float p_path;         /* stochastic depth             (fusion.py:282-283)          */
   float p_head;         /* head Dropout(0.2)            (fusion.py:315,322)          */
   float p_prior;        /* prior_net Dropout            (fusion.py:161)              */
-  float p_pool;         /* Dropout inside the attention pooler's score MLP (temporal.py:19; temporal_dropout) */
+  float p_pool;         /* temporal_dropout: Dropout inside the attention pooler's score MLP (temporal.py:19) and the dropouts of
+                           the transformer pooler's encoder layers (temporal.py:60-68: attention weights, both residual branches,
+                           the FFN activation) */
   uint64_t seed;        /* Philox seed for the dropouts                               */
   uint64_t offset;      /* Philox offset (advance per step)                           */
 } xattn_config;
@@ -144,8 +148,8 @@ typedef enum xattn_param_id {
   XP_APOOL_B1,
   XP_APOOL_W2,
   XP_APOOL_B2,
-  /* XATTN_POOL_TRANSFORMER: {v,a}_temporal_pool.pool.encoder.layers.0.* (one layer); the XP_?POOL_* ids above then hold
-   * {v,a}_temporal_pool.pool.pool.score.* */
+  /* XATTN_POOL_TRANSFORMER: {v,a}_temporal_pool.pool.encoder.layers.0.* (first layer); the XP_?POOL_* ids above then hold
+   * ...pool.pool.score.*.  Layers l >= 1 follow XP_COUNT: see xattn_param_count / XATTN_TX_PARAM_ID below. */
   XP_VTX_IN_W,     /* self_attn.in_proj_weight [3E,E] */
   XP_VTX_IN_B,     /* self_attn.in_proj_bias   [3E]   */
   XP_VTX_OUT_W,    /* self_attn.out_proj.weight [E,E] */
@@ -163,13 +167,24 @@ typedef enum xattn_param_id {
   XP_COUNT
 } xattn_param_id;
 
+/* temporal_num_layers > 1 (temporal.py:51, :69): the 12 tensors of encoder layer `layer` >= 1 of side 0 (video) / 1 (audio),
+ * k = 0..11 in the order of XP_VTX_IN_W .. XP_VTX_N2_B, take the ids after XP_COUNT; layer 0 keeps XP_VTX_* / XP_ATX_*. */
+#define XATTN_MAX_POOL_LAYERS 8
+#define XATTN_TX_PARAMS_PER_LAYER 12
+#define XATTN_TX_PARAM_ID(side, layer, k)                                                                      \
+  ((layer) == 0 ? ((side) == 0 ? XP_VTX_IN_W : XP_ATX_IN_W) + (k)                                               \
+                : XP_COUNT + (((layer)-1) * 2 + (side)) * XATTN_TX_PARAMS_PER_LAYER + (k))
+#define XATTN_PARAM_ID_MAX (XP_COUNT + 2 * XATTN_TX_PARAMS_PER_LAYER * (XATTN_MAX_POOL_LAYERS - 1))
+
 /* ---- library info ------------------------------------------------------------------------ */
 XATTN_API int xattn_abi_version(void);
 /* Text of the last error raised on this thread ("" if none). */
 XATTN_API const char* xattn_last_error(void);
 
 /* ---- layout queries (host only, no CUDA) --------------------------------------------------- */
-/* Fills offsets[XP_COUNT] / sizes[XP_COUNT] (in floats; each offset is a multiple of 4 floats so
+/* Number of parameter ids of cfg: XP_COUNT, plus 24 per transformer-pooler layer beyond the first. */
+XATTN_API int xattn_param_count(const xattn_config* cfg);
+/* Fills offsets[n] / sizes[n], n = xattn_param_count(cfg) (in floats; each offset is a multiple of 4 floats so
  * every tensor is 16-byte aligned) and *total_floats.  Replaces: the nn.Parameter tree built at
  * fusion.py:269-326 (state_dict layout). */
 XATTN_API int xattn_param_layout(const xattn_config* cfg, int64_t* offsets, int64_t* sizes, int64_t* total_floats);

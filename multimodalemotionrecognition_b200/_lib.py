@@ -13,7 +13,7 @@ from pathlib import Path
 LIB_NAME = "libxattn_fusion.so"
 LIB_PATH = Path(__file__).resolve().parent / LIB_NAME
 DEBUG_LIB_PATH = Path(__file__).resolve().parent / "libxattn_fusion_debug.so"
-ABI_VERSION = 17
+ABI_VERSION = 18
 
 # xattn_status
 OK, ERR_SHAPE, ERR_DTYPE, ERR_ALIGN, ERR_ARCH, ERR_CUDA, ERR_WORKSPACE, ERR_NULL = range(8)
@@ -42,10 +42,14 @@ XP_NAMES = [
     "v_temporal_pool.pool.score.1.bias", "v_temporal_pool.pool.score.4.weight", "v_temporal_pool.pool.score.4.bias",
     "a_temporal_pool.pool.score.0.weight", "a_temporal_pool.pool.score.0.bias", "a_temporal_pool.pool.score.1.weight",
     "a_temporal_pool.pool.score.1.bias", "a_temporal_pool.pool.score.4.weight", "a_temporal_pool.pool.score.4.bias",
-] + [f"{side}_temporal_pool.pool.encoder.layers.0.{n}" for side in ("v", "a") for n in (
-    # temporal_pooling="transformer" (temporal.py:46-75), one encoder layer; the score ids above then name ...pool.pool.score.*
-    "self_attn.in_proj_weight", "self_attn.in_proj_bias", "self_attn.out_proj.weight", "self_attn.out_proj.bias",
-    "linear1.weight", "linear1.bias", "linear2.weight", "linear2.bias", "norm1.weight", "norm1.bias", "norm2.weight", "norm2.bias")]
+]
+# temporal_pooling="transformer" (temporal.py:46-75): the 12 tensors of one encoder layer, first layer inside XP_COUNT, layers >= 1
+# after it (XATTN_TX_PARAM_ID in the header); the score ids above then name ...pool.pool.score.*
+TX_LAYER_NAMES = ("self_attn.in_proj_weight", "self_attn.in_proj_bias", "self_attn.out_proj.weight", "self_attn.out_proj.bias",
+                  "linear1.weight", "linear1.bias", "linear2.weight", "linear2.bias", "norm1.weight", "norm1.bias", "norm2.weight",
+                  "norm2.bias")
+MAX_POOL_LAYERS = 8
+XP_NAMES += [f"{side}_temporal_pool.pool.encoder.layers.0.{n}" for side in ("v", "a") for n in TX_LAYER_NAMES]
 XP_COUNT = len(XP_NAMES)
 
 FP_NAMES = [
@@ -57,10 +61,14 @@ FP_NAMES = [
 FP_COUNT = len(FP_NAMES)
 
 
-def xattn_param_names(head: str) -> list[str]:
-    """state_dict key of every xattn_param_id for the given head kind (reference fusion.py:311-326)."""
+def xattn_param_names(head: str, pool_layers: int = 1) -> list[str]:
+    """state_dict key of every parameter id for the given head kind (reference fusion.py:311-326); ``pool_layers`` > 1 appends the
+    transformer pooler's further encoder layers (layer-major, video before audio: XATTN_TX_PARAM_ID)."""
     h0, h1 = ("xattn_mlp.0", "xattn_mlp.3") if head == "concat" else ("xattn_gate.0", "xattn_gate.3")
-    return [n.replace("HEAD0", h0).replace("HEAD1", h1) for n in XP_NAMES]
+    names = [n.replace("HEAD0", h0).replace("HEAD1", h1) for n in XP_NAMES]
+    for layer in range(1, max(1, pool_layers)):
+        names += [f"{side}_temporal_pool.pool.encoder.layers.{layer}.{n}" for side in ("v", "a") for n in TX_LAYER_NAMES]
+    return names
 
 
 def flat_param_names(gated: bool) -> list[str]:
@@ -71,7 +79,7 @@ def flat_param_names(gated: bool) -> list[str]:
 class XAttnConfig(C.Structure):
     _fields_ = [(n, C.c_int32) for n in (
         "B", "T", "Ta", "Dv", "Da", "E", "H", "prior_dim", "prior_hidden", "common_dim", "C", "head_kind",
-        "use_prior", "io_dtype", "precision", "training", "save_for_backward", "pool_mode", "pool_heads")] + [
+        "use_prior", "io_dtype", "precision", "training", "save_for_backward", "pool_mode", "pool_heads", "pool_layers")] + [
         ("p_attn", C.c_float), ("p_path", C.c_float), ("p_head", C.c_float), ("p_prior", C.c_float), ("p_pool", C.c_float),
         ("seed", C.c_uint64), ("offset", C.c_uint64)]
 
@@ -89,6 +97,7 @@ _EXPORTS = {
     "xattn_stage_timing": (C.c_int, [C.c_int32]),
     "xattn_stage_timing_read": (C.c_int, [C.POINTER(C.c_double), C.POINTER(C.c_int64), C.c_int32]),
     "xattn_stage_name": (C.c_char_p, [C.c_int32]),
+    "xattn_param_count": (C.c_int, [C.POINTER(XAttnConfig)]),
     "xattn_param_layout": (C.c_int, [C.POINTER(XAttnConfig), C.POINTER(C.c_int64), C.POINTER(C.c_int64), C.POINTER(C.c_int64)]),
     "xattn_workspace_bytes": (C.c_int, [C.POINTER(XAttnConfig), C.POINTER(C.c_int64)]),
     "xattn_packed_bytes": (C.c_int, [C.POINTER(XAttnConfig), C.POINTER(C.c_int64)]),
@@ -216,8 +225,9 @@ def launch_count() -> int:
 
 
 def xattn_param_layout(cfg: XAttnConfig):
-    off = (C.c_int64 * XP_COUNT)()
-    size = (C.c_int64 * XP_COUNT)()
+    n = load().xattn_param_count(C.byref(cfg))
+    off = (C.c_int64 * n)()
+    size = (C.c_int64 * n)()
     total = C.c_int64(0)
     check(load().xattn_param_layout(C.byref(cfg), off, size, C.byref(total)))
     return list(off), list(size), int(total.value)

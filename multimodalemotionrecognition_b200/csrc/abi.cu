@@ -27,11 +27,17 @@ extern "C" XATTN_API int xattn_stage_timing_read(double* ms_total, int64_t* laun
 }
 extern "C" XATTN_API const char* xattn_stage_name(int32_t i) { return xf::stage_name(i); }
 
+extern "C" XATTN_API int xattn_param_count(const xattn_config* cfg) {
+  if (cfg == nullptr || cfg->pool_mode != XATTN_POOL_TRANSFORMER || cfg->pool_layers <= 1) return XP_COUNT;
+  const int layers = cfg->pool_layers > XATTN_MAX_POOL_LAYERS ? XATTN_MAX_POOL_LAYERS : cfg->pool_layers;
+  return XP_COUNT + 2 * XATTN_TX_PARAMS_PER_LAYER * (layers - 1);
+}
+
 extern "C" XATTN_API int xattn_param_layout(const xattn_config* cfg, int64_t* offsets, int64_t* sizes, int64_t* total_floats) {
   XF_TRY(validate_config(cfg));
   ParamLayout L;
   compute_param_layout(*cfg, L);
-  for (int i = 0; i < XP_COUNT; ++i) {
+  for (int i = 0; i < L.count; ++i) {
     if (offsets) offsets[i] = L.off[i];
     if (sizes) sizes[i] = L.size[i];
   }

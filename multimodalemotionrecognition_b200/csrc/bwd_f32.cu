@@ -584,6 +584,15 @@ static int launch_attn_bwd(cudaStream_t st, const AttnBwdArgs& a, int B, bool* b
     return launch_attn_bwd_mma(st, a, B);
   }
   const int dh = a.E / a.H;
+  {   // score matrices too large for the one-CTA-per-clip kernels (self-attention of the transformer pooler's audio side)
+    const int SP = (a.S + 3) & ~3;
+    const size_t need = dh == 32 ? sizeof(float) * (4 * (size_t)a.L * SP + (size_t)(2 * a.L + 2 * a.S) * 33)
+                                 : sizeof(float) * ((size_t)(2 * a.L + 2 * a.S) * (dh + 1) + 3 * (size_t)a.L * a.S);
+    if (need > 200 * 1024 && a.qs == nullptr) {
+      *bias_fused = false;
+      return launch_attn_bwd_rows(st, a, B);
+    }
+  }
   *bias_fused = dh == 32 && a.dbq != nullptr;
   if (dh == 32) {
     const int SP = (a.S + 3) & ~3;
@@ -1049,9 +1058,73 @@ static int backward_f32_impl(const xattn_config& c, const float* params, const T
     return XATTN_OK;
   };
   static_assert(XP_APOOL_B2 - XP_APOOL_LN_W == 5 && XP_VPOOL_B2 - XP_VPOOL_LN_W == 5, "pooler parameter ids are consecutive");
+  // TemporalTransformerPooling (temporal.py:46-75): the learned pooling's backward on the last layer's output, then the encoder
+  // layers in reverse (x2 = x1 + drop(W2·drop(GELU(W1·LN2(x1)))), x1 = x0 + drop(Wo·SA(LN1(x0)))); the sinusoidal positions pass
+  // the gradient through.  Leaves the gradient w.r.t. the side's tokens in ws + w.txb_dx.  h = LN(x) is recomputed, everything
+  // else comes from the layer's TxSaved block; the forward's scratch set (tx_h, tx_q, tx_kv, tx_f) holds the temporaries.
+  const bool tx_pool = c.pool_mode == XATTN_POOL_TRANSFORMER;
+  auto transformer_pool_bwd = [&](int side, const float* d_out) -> int {
+    const int L = side == 0 ? T : Ta, M = B * L, F = 4 * E, PH = c.pool_heads, layers = pool_layers(c);
+    const int64_t n = (int64_t)M * E;
+    float *dX = ws + w.txb_dx, *t1 = ws + w.txb_t1, *t2 = ws + w.txb_t2, *th = ws + w.tx_h, *dq = ws + w.tx_q, *dkv = ws + w.tx_kv,
+          *df = ws + w.tx_f;
+    XF_TRY(pool_bwd(ws + w.tx_out[side], d_out, dX, false, t1, ws + w.txb_dh, L, side == 0 ? XP_VPOOL_LN_W : XP_APOOL_LN_W,
+                    side == 0 ? RS_POOLV : RS_POOLA));
+    for (int layer = layers - 1; layer >= 0; --layer) {
+      const TxSaved sv = tx_saved(ws, w, c, side, layer);
+      auto TP = [&](int k) { return P(XATTN_TX_PARAM_ID(side, layer, k)); };
+      auto TG = [&](int k) { return G(XATTN_TX_PARAM_ID(side, layer, k)); };
+      // ---- feed-forward block ----
+      const float* dy = dX;
+      if (p_pool > 0.f) {
+        XF_TRY(launch_mul_drop(st, t1, dX, n, p_pool, c.seed, c.offset, rs_tx(side, layer, 3)));
+        dy = t1;
+      }
+      linear_bwd_dw<float>(st, dy, E, sv.f_act, F, TG(6), M, E, F);
+      launch_colsum(st, dy, E, M, E, TG(7));
+      linear_bwd_dx(st, dy, E, TP(6), df, M, E, F, false);
+      XF_TRY(launch_gelu_drop_bwd(st, df, sv.f_pre, (int64_t)M * F, p_pool, c.seed, c.offset, rs_tx(side, layer, 2)));
+      XF_TRY(launch_ln_rows(st, sv.x_mid, TP(10), TP(11), th, M, E));
+      linear_bwd_dw<float>(st, df, F, th, E, TG(4), M, F, E);
+      launch_colsum(st, df, F, M, F, TG(5));
+      linear_bwd_dx(st, df, F, TP(4), t2, M, F, E, false);
+      XF_TRY(launch_ln_rows_bwd(st, sv.x_mid, TP(10), t2, dX, TG(10), TG(11), M, E, true));
+      // ---- self-attention block ----
+      dy = dX;
+      if (p_pool > 0.f) {
+        XF_TRY(launch_mul_drop(st, t1, dX, n, p_pool, c.seed, c.offset, rs_tx(side, layer, 1)));
+        dy = t1;
+      }
+      linear_bwd_dw<float>(st, dy, E, sv.o, E, TG(2), M, E, E);
+      launch_colsum(st, dy, E, M, E, TG(3));
+      linear_bwd_dx(st, dy, E, TP(2), t2, M, E, E, false);
+      AttnBwdArgs aa;
+      aa.q = sv.q; aa.kv = sv.kv; aa.qs = nullptr; aa.ks = nullptr; aa.bias_scale = nullptr; aa.P = sv.P; aa.dO = t2;
+      aa.dq = dq; aa.dkv = dkv; aa.dqs = nullptr; aa.dks = nullptr; aa.dbias_scale = nullptr;
+      aa.L = L; aa.S = L; aa.E = E; aa.H = PH; aa.scale = 1.0f / sqrtf((float)(E / PH)); aa.p_drop = p_pool; aa.seed = c.seed;
+      aa.offset = c.offset; aa.rng_stream = rs_tx(side, layer, 0);
+      aa.dbq = TG(1); aa.dbkv = TG(1) + E;
+      bool in_bias_fused = false;
+      XF_TRY(launch_attn_bwd(st, aa, B, &in_bias_fused));
+      XF_TRY(launch_ln_rows(st, sv.x_in, TP(8), TP(9), th, M, E));
+      linear_bwd_dw<float>(st, dq, E, th, E, TG(0), M, E, E);
+      linear_bwd_dw<float>(st, dkv, 2 * E, th, E, TG(0) + (int64_t)E * E, M, 2 * E, E);
+      if (!in_bias_fused) {
+        launch_colsum(st, dq, E, M, E, TG(1));
+        launch_colsum(st, dkv, 2 * E, M, 2 * E, TG(1) + E);
+      }
+      linear_bwd_dx(st, dq, E, TP(0), t1, M, E, E, false);
+      linear_bwd_dx(st, dkv, 2 * E, TP(0) + (int64_t)E * E, t1, M, 2 * E, E, true);
+      XF_TRY(launch_ln_rows_bwd(st, sv.x_in, TP(8), t1, dX, TG(8), TG(9), M, E, true));
+      XF_LAUNCH_CHECK();
+    }
+    return XATTN_OK;
+  };
   if (attn_pool) XF_TRY(pool_bwd(ws + w.a1, ws + w.d_pooled + E, ws + w.d_q2, false, ws + w.d_br2, ws + w.d_o2, Ta, XP_APOOL_LN_W, RS_POOLA));   // (d_q2 is free until the a2v attention backward)
+  if (tx_pool) XF_TRY(transformer_pool_bwd(1, ws + w.d_pooled + E));
+  const bool tok_pool = attn_pool || tx_pool;   // the a_norm / v_norm outputs receive per-token gradients instead of d_pooled / L
   // ---- a_norm backward (fusion.py:399) + mean pool (temporal.py:108-109) ----
-  bool ob_fused = launch_ln_bwd(st, ln_grid, attn_pool ? ws + w.d_q2 : nullptr, attn_pool ? nullptr : ws + w.d_pooled + E, 2 * E,
+  bool ob_fused = launch_ln_bwd(st, ln_grid, tx_pool ? ws + w.txb_dx : attn_pool ? ws + w.d_q2 : nullptr, tok_pool ? nullptr : ws + w.d_pooled + E, 2 * E,
                                 1.f / (float)Ta, ws + w.s2, ws + w.mean2, ws + w.rstd2,
                                 P(XP_AN_W), ws + w.dp2, ws + w.d_a0, ws + w.d_br2, G(XP_AN_W), G(XP_AN_B), G(XP_A2V_OUT_B), B * Ta, Ta, E);
   // a2v out_proj
@@ -1080,8 +1153,12 @@ static int backward_f32_impl(const xattn_config& c, const float* params, const T
   linear_bwd_dx(st, ws + w.d_kv2, 2 * E, P(XP_A2V_IN_W) + (int64_t)E * E, ws + w.d_v1, B * T, 2 * E, E, false);
   XF_LAUNCH_CHECK();
   if (attn_pool) XF_TRY(pool_bwd(ws + w.v1, ws + w.d_pooled, ws + w.d_v1, true, ws + w.d_br1, ws + w.d_o1, T, XP_VPOOL_LN_W, RS_POOLV));
+  if (tx_pool) {
+    XF_TRY(transformer_pool_bwd(0, ws + w.d_pooled));
+    XF_TRY(launch_add_inplace(st, ws + w.d_v1, ws + w.txb_dx, (int64_t)B * T * E));
+  }
   // ---- v_norm backward (fusion.py:395) ----
-  ob_fused = launch_ln_bwd(st, ln_grid, ws + w.d_v1, attn_pool ? nullptr : ws + w.d_pooled, 2 * E, 1.f / (float)T, ws + w.s1, ws + w.mean1, ws + w.rstd1,
+  ob_fused = launch_ln_bwd(st, ln_grid, ws + w.d_v1, tok_pool ? nullptr : ws + w.d_pooled, 2 * E, 1.f / (float)T, ws + w.s1, ws + w.mean1, ws + w.rstd1,
                            P(XP_VN_W), ws + w.dp1, ws + w.d_v0, ws + w.d_br1, G(XP_VN_W), G(XP_VN_B), G(XP_V2A_OUT_B), B * T, T, E);
   linear_bwd_dw<float>(st, ws + w.d_br1, E, ws + w.o1, E, G(XP_V2A_OUT_W), B * T, E, E);
   if (!ob_fused) launch_colsum(st, ws + w.d_br1, E, B * T, E, G(XP_V2A_OUT_B));

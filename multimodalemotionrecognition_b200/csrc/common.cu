@@ -156,7 +156,8 @@ int validate_config(const xattn_config* c) {
   if (c->pool_mode != XATTN_POOL_MEAN && c->pool_mode != XATTN_POOL_ATTN && c->pool_mode != XATTN_POOL_TRANSFORMER)
     XF_FAIL(XATTN_ERR_SHAPE, "unknown pool_mode %d", c->pool_mode);
   if (c->pool_mode == XATTN_POOL_TRANSFORMER) {
-    if (c->training || c->save_for_backward) XF_FAIL(XATTN_ERR_SHAPE, "temporal_pooling=transformer is forward-only (no backward kernels)");
+    if (c->pool_layers < 0 || c->pool_layers > XATTN_MAX_POOL_LAYERS)
+      XF_FAIL(XATTN_ERR_SHAPE, "pool_layers=%d outside 1..%d", c->pool_layers, XATTN_MAX_POOL_LAYERS);
     if (c->pool_heads <= 0 || c->E % c->pool_heads != 0) XF_FAIL(XATTN_ERR_SHAPE, "pool_heads=%d must divide E=%d", c->pool_heads, c->E);
   }
   if (c->pool_mode != XATTN_POOL_MEAN && c->precision == XATTN_DTYPE_BF16)
@@ -173,8 +174,9 @@ void compute_param_layout(const xattn_config& c, ParamLayout& L) {
   const int64_t E = c.E, P = c.prior_dim, Hd = c.prior_hidden;
   const bool gated = c.head_kind == XATTN_HEAD_GATED;
   const int64_t HW = gated ? E : c.common_dim;
-  int64_t sz[XP_COUNT];
+  int64_t sz[XATTN_PARAM_ID_MAX];
   memset(sz, 0, sizeof(sz));
+  L.count = XP_COUNT;
   sz[XP_V_IN_W] = E * c.Dv; sz[XP_V_IN_B] = E;
   sz[XP_A_IN_W] = E * E; sz[XP_A_IN_B] = E;
   sz[XP_SEQ_W] = E * c.Da; sz[XP_SEQ_B] = E;
@@ -192,11 +194,15 @@ void compute_param_layout(const xattn_config& c, ParamLayout& L) {
   }
   if (c.pool_mode == XATTN_POOL_TRANSFORMER) {
     const int64_t F = 4 * E;   // max(2E, int(4.0·E)), temporal.py:58
-    for (int base : {(int)XP_VTX_IN_W, (int)XP_ATX_IN_W}) {
-      sz[base + 0] = 3 * E * E; sz[base + 1] = 3 * E; sz[base + 2] = E * E; sz[base + 3] = E;
-      sz[base + 4] = F * E; sz[base + 5] = F; sz[base + 6] = E * F; sz[base + 7] = E;
-      sz[base + 8] = sz[base + 9] = sz[base + 10] = sz[base + 11] = E;
-    }
+    const int layers = pool_layers(c);
+    L.count = XP_COUNT + 2 * XATTN_TX_PARAMS_PER_LAYER * (layers - 1);
+    for (int layer = 0; layer < layers; ++layer)
+      for (int side = 0; side < 2; ++side) {
+        const int base = XATTN_TX_PARAM_ID(side, layer, 0);
+        sz[base + 0] = 3 * E * E; sz[base + 1] = 3 * E; sz[base + 2] = E * E; sz[base + 3] = E;
+        sz[base + 4] = F * E; sz[base + 5] = F; sz[base + 6] = E * F; sz[base + 7] = E;
+        sz[base + 8] = sz[base + 9] = sz[base + 10] = sz[base + 11] = E;
+      }
   }
   if (c.pool_mode == XATTN_POOL_ATTN || c.pool_mode == XATTN_POOL_TRANSFORMER) {
     const int64_t H2 = E / 2 > 0 ? E / 2 : 1;
@@ -205,7 +211,7 @@ void compute_param_layout(const xattn_config& c, ParamLayout& L) {
     }
   }
   int64_t off = 0;
-  for (int i = 0; i < XP_COUNT; ++i) {
+  for (int i = 0; i < XATTN_PARAM_ID_MAX; ++i) {
     L.off[i] = off;
     L.size[i] = sz[i];
     off += al4(sz[i]);
@@ -251,6 +257,15 @@ void compute_ws_f32(const xattn_config& c, WsF32& w) {
   {
     const int64_t M = c.pool_mode == XATTN_POOL_TRANSFORMER ? B * (T > Ta ? T : Ta) : 0;   // rows of the longer side
     w.tx_x = take(M * E); w.tx_h = take(M * E); w.tx_q = take(M * E); w.tx_kv = take(M * 2 * E); w.tx_f = take(M * 4 * E);
+    const bool txb = bwd && M > 0;
+    for (int side = 0; side < 2; ++side) {
+      const int L = side == 0 ? c.T : c.Ta;
+      w.tx_layer_floats[side] = txb ? tx_layer_floats(c, L) : 0;
+      w.tx_save[side] = take(w.tx_layer_floats[side] * pool_layers(c));
+      w.tx_out[side] = take(txb ? B * L * E : 0);
+    }
+    w.txb_dx = take(txb ? M * E : 0); w.txb_t1 = take(txb ? M * E : 0); w.txb_t2 = take(txb ? M * E : 0);
+    w.txb_dh = take(txb ? M * (E / 2 > 0 ? E / 2 : 1) : 0);
   }
   w.total = off;
 }

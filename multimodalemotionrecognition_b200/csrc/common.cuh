@@ -105,10 +105,12 @@ int stage_timing_read(double* ms, int64_t* launches, int cap);
 
 // ---- parameter layout ----------------------------------------------------------------------------
 struct ParamLayout {
-  int64_t off[XP_COUNT];
-  int64_t size[XP_COUNT];
+  int64_t off[XATTN_PARAM_ID_MAX];
+  int64_t size[XATTN_PARAM_ID_MAX];
   int64_t total;
+  int count;   // ids in use: XP_COUNT + 24 per transformer-pooler layer beyond the first
 };
+inline int pool_layers(const xattn_config& c) { return c.pool_layers > 0 ? c.pool_layers : 1; }
 void compute_param_layout(const xattn_config& c, ParamLayout& L);
 
 // ---- fp32 workspace layout (activations saved for backward; floats) -------------------------------
@@ -123,9 +125,33 @@ struct WsF32 {
   int64_t wbf;    // bf16 scratch of the TF32 precision (see compute_ws_f32)
   int64_t poolv, poola;   // pool_mode != MEAN: pooled tokens [B,E] each
   int64_t tx_x, tx_h, tx_q, tx_kv, tx_f;   // pool_mode = TRANSFORMER: encoder-layer activations of one side at a time
+  // ... with training / save_for_backward: what the encoder layers keep for their backward, per side s (0 video, 1 audio) and
+  // layer l, at tx_save[s] + l * tx_layer_floats[s] (carved up by tx_saved() below); the output of the last layer at tx_out[s];
+  // and the backward's scratch (token gradient, two [M,E] temporaries, the pooler's d_h rows)
+  int64_t tx_save[2], tx_layer_floats[2], tx_out[2];
+  int64_t txb_dx, txb_t1, txb_t2, txb_dh;
   int64_t total;  // floats
 };
 void compute_ws_f32(const xattn_config& c, WsF32& w);
+// Saved activations of encoder layer `layer` of side `side` (M = B·L rows, F = 4E, PH = pool_heads):
+// x_in [M,E] layer input, q [M,E] | kv [M,2E] projected LN1(x_in), P [B,PH,L,L] attention probabilities (sign = dropped),
+// o [M,E] attention output before out_proj, x_mid [M,E] after the first residual, f_pre / f_act [M,F] around the GELU.
+struct TxSaved {
+  float *x_in, *q, *kv, *o, *x_mid, *f_pre, *f_act, *P;
+};
+inline int64_t tx_layer_floats(const xattn_config& c, int L) {
+  const int64_t ME = ((int64_t)c.B * L * c.E + 3) & ~(int64_t)3;
+  return 14 * ME + (((int64_t)c.B * c.pool_heads * L * L + 3) & ~(int64_t)3);
+}
+inline TxSaved tx_saved(float* ws, const WsF32& w, const xattn_config& c, int side, int layer) {
+  const int L = side == 0 ? c.T : c.Ta;
+  const int64_t ME = ((int64_t)c.B * L * c.E + 3) & ~(int64_t)3;
+  float* p = ws + w.tx_save[side] + layer * w.tx_layer_floats[side];
+  TxSaved s;
+  s.x_in = p; s.q = p + ME; s.kv = p + 2 * ME; s.o = p + 4 * ME; s.x_mid = p + 5 * ME; s.f_pre = p + 6 * ME; s.f_act = p + 10 * ME;
+  s.P = p + 14 * ME;
+  return s;
+}
 
 // ---- device helpers ------------------------------------------------------------------------------------
 __device__ __forceinline__ float warp_sum(float v) {
@@ -183,6 +209,10 @@ __device__ __forceinline__ void drop_factor4(float p, uint64_t seed, uint64_t of
   f[2] = (float)(r.z >> 8) * sc < p ? 0.f : keep;
   f[3] = (float)(r.w >> 8) * sc < p ? 0.f : keep;
 }
-enum : uint32_t { RS_ATTN1 = 1, RS_ATTN2 = 2, RS_PATH1 = 3, RS_PATH2 = 4, RS_HEAD = 5, RS_PRIOR = 6, RS_POOLV = 7, RS_POOLA = 8 };
+enum : uint32_t { RS_ATTN1 = 1, RS_ATTN2 = 2, RS_PATH1 = 3, RS_PATH2 = 4, RS_HEAD = 5, RS_PRIOR = 6, RS_POOLV = 7, RS_POOLA = 8,
+                  RS_TX_BASE = 16 };   // transformer pooler: RS_TX_BASE + (side·XATTN_MAX_POOL_LAYERS + layer)·4 + {attn, drop1, ffn, drop2}
+__host__ __device__ inline uint32_t rs_tx(int side, int layer, int which) {
+  return RS_TX_BASE + (uint32_t)((side * XATTN_MAX_POOL_LAYERS + layer) * 4 + which);
+}
 
 }  // namespace xf

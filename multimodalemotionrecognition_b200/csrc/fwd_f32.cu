@@ -581,10 +581,11 @@ static int launch_attn_pool(cudaStream_t st, const float* x, const float* const*
 }
 
 // ---------------------------------------------------------------------------------------------------------
-// TemporalTransformerPooling (temporal.py:46-75): x + sinusoidal positions -> one pre-norm nn.TransformerEncoderLayer
-// (x += SA(LN1(x)); x += W2·GELU(W1·LN2(x))) -> TemporalAttentionPooling.  The Linears go through linear_fwd (tensor cores
-// under PREC_TF32), the self-attention through the attention kernels of the fusion block (no bias, no dropout: eval); what is
-// left are the row-wise pieces below.  Forward only.
+// TemporalTransformerPooling (temporal.py:46-75): x + sinusoidal positions -> pool_layers pre-norm nn.TransformerEncoderLayers
+// (x += drop(SA(LN1(x))); x += drop(W2·drop(GELU(W1·LN2(x))))) -> TemporalAttentionPooling.  The Linears go through linear_fwd
+// (tensor cores under PREC_TF32), the self-attention through the attention kernels of the fusion block (no bias; attention
+// dropout p_pool when training); what is left are the row-wise pieces below.  With training / save_for_backward every layer
+// keeps its activations in the workspace (TxSaved) for transformer_pool_bwd (bwd_f32.cu).
 // ---------------------------------------------------------------------------------------------------------
 // out[row, e] = x[row, e] + pe[row % L, e],  pe[l, 2i] = sin(l·w_i), pe[l, 2i+1] = cos(l·w_i), w_i = exp(2i·(-ln 10000 / E))  (temporal.py:33-38)
 __global__ void posenc_add_kernel(const float* __restrict__ x, float* __restrict__ out, int64_t n, int L, int E) {
@@ -612,14 +613,24 @@ __global__ void __launch_bounds__(256) ln_rows_kernel(const float* __restrict__ 
   const float rstd = rsqrtf(warp_sum(var) / (float)E + 1e-5f);
   for (int e = lane; e < E; e += 32) y[(int64_t)row * E + e] = (xr[e] - mu) * rstd * gamma[e] + beta[e];
 }
-__global__ void gelu_kernel(float* __restrict__ x, int64_t n) {   // nn.GELU() (exact), in place
+int launch_ln_rows(cudaStream_t st, const float* x, const float* gamma, const float* beta, float* y, int rows, int E) {
+  ln_rows_kernel<<<(rows + 7) / 8, 256, 0, st>>>(x, gamma, beta, y, rows, E);
+  count_launch();
+  XF_LAUNCH_CHECK();
+  return XATTN_OK;
+}
+// act = Dropout(GELU(pre)): nn.GELU() (exact) and the FFN's inner dropout (TransformerEncoderLayer._ff_block); act may be pre
+__global__ void gelu_drop_kernel(const float* pre, float* act, int64_t n, float p, uint64_t seed, uint64_t offset, uint32_t stream) {
   for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
-    const float h = x[i];
-    x[i] = 0.5f * h * (1.f + erff(h * 0.70710678118654752f));
+    const float h = pre[i];
+    act[i] = 0.5f * h * (1.f + erff(h * 0.70710678118654752f)) * drop_factor(p, seed, offset, stream, (uint64_t)i);
   }
 }
-__global__ void add_inplace_kernel(float* __restrict__ x, const float* __restrict__ y, int64_t n) {
-  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) x[i] += y[i];
+// out = x + Dropout(y): the residual around a branch (dropout1 / dropout2 of the encoder layer); out may be x
+__global__ void add_drop_kernel(float* out, const float* x, const float* __restrict__ y, int64_t n, float p, uint64_t seed,
+                                uint64_t offset, uint32_t stream) {
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
+    out[i] = fmaf(y[i], drop_factor(p, seed, offset, stream, (uint64_t)i), x[i]);
 }
 static inline int ew_grid(int64_t n) {
   const int64_t g = (n + 255) / 256, cap = (int64_t)num_sms() * 16;
@@ -753,37 +764,53 @@ static int forward_f32_impl(const xattn_config& c, const float* params, const TI
     HeadArgs ha;
     ha.v1 = ws + w.v1; ha.a1 = ws + w.a1;
     int hT = T, hTa = Ta;
-    if (c.pool_mode == XATTN_POOL_TRANSFORMER) {   // encoder layer over each side's tokens, then the learned pooling
-      const int F = 4 * E, PH = c.pool_heads;
+    if (c.pool_mode == XATTN_POOL_TRANSFORMER) {   // encoder layers over each side's tokens, then the learned pooling
+      const int F = 4 * E, PH = c.pool_heads, layers = pool_layers(c);
+      const float p_tx = train ? c.p_pool : 0.f;
       const float* pv[6] = {P(XP_VPOOL_LN_W), P(XP_VPOOL_LN_B), P(XP_VPOOL_W1), P(XP_VPOOL_B1), P(XP_VPOOL_W2), P(XP_VPOOL_B2)};
       const float* pa[6] = {P(XP_APOOL_LN_W), P(XP_APOOL_LN_B), P(XP_APOOL_W1), P(XP_APOOL_B1), P(XP_APOOL_W2), P(XP_APOOL_B2)};
-      float *tx = ws + w.tx_x, *th = ws + w.tx_h, *tq = ws + w.tx_q, *tkv = ws + w.tx_kv, *tf = ws + w.tx_f;
+      float *th = ws + w.tx_h, *tmp = ws + w.tx_q;
       for (int side = 0; side < 2; ++side) {
-        const int L = side == 0 ? T : Ta, base = side == 0 ? (int)XP_VTX_IN_W : (int)XP_ATX_IN_W;
-        const float* x = side == 0 ? ws + w.v1 : ws + w.a1;
+        const int L = side == 0 ? T : Ta;
         const int M = B * L;
         const int64_t n = (int64_t)M * E;
-        posenc_add_kernel<<<ew_grid(n), 256, 0, st>>>(x, tx, n, L, E);                                          // temporal.py:72
-        ln_rows_kernel<<<(M + 7) / 8, 256, 0, st>>>(tx, P(base + 8), P(base + 9), th, M, E);                    // norm1 (norm_first)
-        count_launch(2);
-        linear_fwd<float>(st, th, P(base + 0), P(base + 1), tq, M, E, E);
-        linear_fwd<float>(st, th, P(base + 0) + (int64_t)E * E, P(base + 1) + E, tkv, M, 2 * E, E);
-        AttnArgs aa;
-        aa.q = tq; aa.kv = tkv; aa.qs = nullptr; aa.ks = nullptr; aa.bias_scale = nullptr; aa.P = nullptr; aa.O = th;
-        aa.L = L; aa.S = L; aa.E = E; aa.H = PH; aa.scale = 1.0f / sqrtf((float)(E / PH)); aa.p_drop = 0.f; aa.seed = c.seed;
-        aa.offset = c.offset; aa.rng_stream = 0;
-        XF_TRY(launch_attn_fwd(st, aa, B));
-        linear_fwd<float>(st, th, P(base + 2), P(base + 3), tq, M, E, E);                                       // out_proj
-        add_inplace_kernel<<<ew_grid(n), 256, 0, st>>>(tx, tq, n);                                              // x += SA(LN1(x))
-        ln_rows_kernel<<<(M + 7) / 8, 256, 0, st>>>(tx, P(base + 10), P(base + 11), th, M, E);                  // norm2
-        count_launch(2);
-        linear_fwd<float>(st, th, P(base + 4), P(base + 5), tf, M, F, E);
-        gelu_kernel<<<ew_grid((int64_t)M * F), 256, 0, st>>>(tf, (int64_t)M * F);
-        linear_fwd<float>(st, tf, P(base + 6), P(base + 7), tq, M, E, F);
-        add_inplace_kernel<<<ew_grid(n), 256, 0, st>>>(tx, tq, n);                                              // x += FF(LN2(x))
-        count_launch(2);
-        XF_LAUNCH_CHECK();
-        XF_TRY(launch_attn_pool(st, tx, side == 0 ? pv : pa, side == 0 ? ws + w.poolv : ws + w.poola, B, L, E, 0.f, c.seed, c.offset, 0));
+        // without a backward everything lives in one scratch set and x is updated in place
+        TxSaved sv;
+        sv.x_in = sv.x_mid = ws + w.tx_x; sv.q = ws + w.tx_q; sv.kv = ws + w.tx_kv; sv.o = th; sv.f_pre = sv.f_act = ws + w.tx_f;
+        sv.P = nullptr;
+        float* x_out = ws + w.tx_x;
+        if (save) sv = tx_saved(ws, w, c, side, 0);
+        posenc_add_kernel<<<ew_grid(n), 256, 0, st>>>(side == 0 ? ws + w.v1 : ws + w.a1, sv.x_in, n, L, E);   // temporal.py:72
+        count_launch();
+        for (int layer = 0; layer < layers; ++layer) {
+          auto TP = [&](int k) { return P(XATTN_TX_PARAM_ID(side, layer, k)); };
+          if (save) {
+            sv = tx_saved(ws, w, c, side, layer);
+            x_out = layer + 1 < layers ? tx_saved(ws, w, c, side, layer + 1).x_in : ws + w.tx_out[side];
+          }
+          ln_rows_kernel<<<(M + 7) / 8, 256, 0, st>>>(sv.x_in, TP(8), TP(9), th, M, E);                          // norm1 (norm_first)
+          count_launch();
+          linear_fwd<float>(st, th, TP(0), TP(1), sv.q, M, E, E);
+          linear_fwd<float>(st, th, TP(0) + (int64_t)E * E, TP(1) + E, sv.kv, M, 2 * E, E);
+          AttnArgs aa;
+          aa.q = sv.q; aa.kv = sv.kv; aa.qs = nullptr; aa.ks = nullptr; aa.bias_scale = nullptr; aa.P = sv.P; aa.O = sv.o;
+          aa.L = L; aa.S = L; aa.E = E; aa.H = PH; aa.scale = 1.0f / sqrtf((float)(E / PH)); aa.p_drop = p_tx; aa.seed = c.seed;
+          aa.offset = c.offset; aa.rng_stream = rs_tx(side, layer, 0);
+          XF_TRY(launch_attn_fwd(st, aa, B));
+          linear_fwd<float>(st, sv.o, TP(2), TP(3), tmp, M, E, E);                                               // out_proj (q is dead)
+          add_drop_kernel<<<ew_grid(n), 256, 0, st>>>(sv.x_mid, sv.x_in, tmp, n, p_tx, c.seed, c.offset, rs_tx(side, layer, 1));
+          ln_rows_kernel<<<(M + 7) / 8, 256, 0, st>>>(sv.x_mid, TP(10), TP(11), th, M, E);                       // norm2
+          count_launch(2);
+          linear_fwd<float>(st, th, TP(4), TP(5), sv.f_pre, M, F, E);
+          gelu_drop_kernel<<<ew_grid((int64_t)M * F), 256, 0, st>>>(sv.f_pre, sv.f_act, (int64_t)M * F, p_tx, c.seed, c.offset,
+                                                                     rs_tx(side, layer, 2));
+          linear_fwd<float>(st, sv.f_act, TP(6), TP(7), tmp, M, E, F);
+          add_drop_kernel<<<ew_grid(n), 256, 0, st>>>(x_out, sv.x_mid, tmp, n, p_tx, c.seed, c.offset, rs_tx(side, layer, 3));
+          count_launch(2);
+          XF_LAUNCH_CHECK();
+        }
+        XF_TRY(launch_attn_pool(st, x_out, side == 0 ? pv : pa, side == 0 ? ws + w.poolv : ws + w.poola, B, L, E, p_tx, c.seed,
+                                c.offset, side == 0 ? RS_POOLV : RS_POOLA));
       }
       ha.v1 = ws + w.poolv; ha.a1 = ws + w.poola;
       hT = hTa = 1;

@@ -65,6 +65,15 @@ int launch_attn_fwd_mma(cudaStream_t st, const AttnArgs& a, int B);
 struct AttnBwdArgs;
 int launch_attn_bwd_mma(cudaStream_t st, const AttnBwdArgs& a, int B);
 
+// row-wise pieces of the transformer pooler (fwd_f32.cu / tx_pool_bwd.cu)
+int launch_ln_rows(cudaStream_t st, const float* x, const float* gamma, const float* beta, float* y, int rows, int E);
+int launch_ln_rows_bwd(cudaStream_t st, const float* x, const float* gamma, const float* d_h, float* d_x, float* g_gamma,
+                       float* g_beta, int rows, int E, bool accumulate);
+int launch_gelu_drop_bwd(cudaStream_t st, float* d, const float* pre, int64_t n, float p, uint64_t seed, uint64_t offset, uint32_t stream);
+int launch_mul_drop(cudaStream_t st, float* out, const float* x, int64_t n, float p, uint64_t seed, uint64_t offset, uint32_t stream);
+int launch_add_inplace(cudaStream_t st, float* x, const float* y, int64_t n);
+int launch_attn_bwd_rows(cudaStream_t st, const AttnBwdArgs& a, int B);   // no prior bias; any L, S that fit a [32, S] tile
+
 int forward_f32(const xattn_config& c, const float* params, const void* xv, const void* xa, float* logits, void* ws,
                 cudaStream_t st);
 struct BackwardOptions {

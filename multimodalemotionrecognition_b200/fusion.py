@@ -73,12 +73,12 @@ class TemporalAttentionPooling(nn.Module):
 class TemporalTransformerPooling(nn.Module):
     """Parameter container of ``temporal.py:46-75``: sinusoidal positions (no parameters; the reference's ``pe`` buffer is
     non-persistent), ``nn.TransformerEncoder`` of pre-norm GELU layers, then ``TemporalAttentionPooling``.  Built from the same
-    torch modules as the reference so keys, shapes and same-seed initialisation are identical.  The B200 kernels run ONE layer."""
+    torch modules as the reference so keys, shapes and same-seed initialisation are identical.  Up to 8 layers."""
 
     def __init__(self, dim: int, num_heads: int = 4, num_layers: int = 1, dropout: float = 0.1, mlp_ratio: float = 4.0) -> None:
         super().__init__()
-        if num_layers != 1:
-            raise ValueError(f"the B200 transformer pooler runs one encoder layer (temporal_num_layers=1), got {num_layers}")
+        if not 1 <= num_layers <= _lib.MAX_POOL_LAYERS:
+            raise ValueError(f"the B200 transformer pooler runs 1..{_lib.MAX_POOL_LAYERS} encoder layers, got {num_layers}")
         if max(dim * 2, int(dim * mlp_ratio)) != 4 * dim:
             raise ValueError("the B200 transformer pooler is built for mlp_ratio=4")
         layer = nn.TransformerEncoderLayer(d_model=dim, nhead=num_heads, dim_feedforward=4 * dim, dropout=dropout, activation="gelu",
@@ -86,6 +86,7 @@ class TemporalTransformerPooling(nn.Module):
         self.encoder = nn.TransformerEncoder(layer, num_layers=num_layers)
         self.pool = TemporalAttentionPooling(dim=dim, dropout=dropout)
         self.num_heads = num_heads
+        self.num_layers = num_layers
 
     def forward(self, x: torch.Tensor) -> torch.Tensor:  # pragma: no cover - not on the kernel path
         raise RuntimeError("TemporalTransformerPooling runs inside the CUDA forward")
@@ -93,8 +94,8 @@ class TemporalTransformerPooling(nn.Module):
 
 class TemporalPooler(nn.Module):
     """``mean`` (``temporal.py:91-92, 108-109``; no parameters), ``attn`` (``temporal.py:93-94``: the learned pooling, forward
-    and backward in the fp32 / tf32 kernel family) and ``transformer`` (``temporal.py:95-102``: one encoder layer in front of
-    the learned pooling; forward only)."""
+    and backward in the fp32 / tf32 kernel family) and ``transformer`` (``temporal.py:95-102``: ``num_layers`` pre-norm encoder
+    layers in front of the learned pooling; forward and backward in the same family)."""
 
     def __init__(self, dim: int, mode: str = "mean", dropout: float = 0.1, num_heads: int = 4, num_layers: int = 1, **_unused) -> None:
         super().__init__()
@@ -271,6 +272,7 @@ class XAttnKernelsMixin:
                                               num_heads=temporal_num_heads, num_layers=temporal_num_layers)
         self._temporal_pooling = temporal_pooling
         self._temporal_num_heads = int(temporal_num_heads)
+        self._temporal_num_layers = int(temporal_num_layers)
         self.xattn_head = xattn_head
         if xattn_head == "concat":
             self.xattn_mlp = nn.Sequential(
@@ -301,7 +303,8 @@ class XAttnKernelsMixin:
 
     # ---- config / parameter plumbing ------------------------------------------------------------------------------
     def _xattn_param_names(self) -> list[str]:
-        names = _lib.xattn_param_names(self.xattn_head)
+        tx = getattr(self, "_temporal_pooling", "mean") == "transformer"
+        names = _lib.xattn_param_names(self.xattn_head, getattr(self, "_temporal_num_layers", 1) if tx else 1)
         if getattr(self, "audio_frontend", "seq") == "mel":
             names = [n.replace("audio_seq_proj.", "audio_time_conv.") for n in names]
         if getattr(self, "_temporal_pooling", "mean") == "transformer":   # the score MLP sits one module deeper (temporal.py:70)
@@ -344,6 +347,7 @@ class XAttnKernelsMixin:
         cfg.pool_mode = {"mean": _lib.POOL_MEAN, "attn": _lib.POOL_ATTN, "transformer": _lib.POOL_TRANSFORMER}[
             getattr(self, "_temporal_pooling", "mean")]
         cfg.pool_heads = getattr(self, "_temporal_num_heads", 4)
+        cfg.pool_layers = getattr(self, "_temporal_num_layers", 1)
         cfg.p_attn, cfg.p_path = self.xattn_attn_dropout, self.xattn_stochastic_depth
         cfg.p_head, cfg.p_prior = self.xattn_head_dropout, self.xattn_prior_dropout
         cfg.p_pool = self.xattn_pool_dropout
@@ -469,9 +473,6 @@ class XAttnKernelsMixin:
         B, T, _ = video_emb.shape
         Ta = audio_emb.shape[1]
         io = _io_dtype(video_emb)
-        if (save or training) and getattr(self, "_temporal_pooling", "mean") == "transformer":
-            raise ValueError("temporal_pooling='transformer' is forward-only on the B200 path (no backward kernels): call it in "
-                             "eval mode under torch.no_grad()")
         precision = self._pick_precision(io, save or training, T, Ta)
         if precision == _lib.DTYPE_BF16 and io != _lib.DTYPE_BF16:   # precision="bf16" forced on fp32 embeddings
             video_emb, audio_emb, io = video_emb.bfloat16(), audio_emb.bfloat16(), _lib.DTYPE_BF16

@@ -137,23 +137,31 @@ def gen_attnpool(FusionModel) -> None:
 
 
 def gen_txpool(FusionModel) -> None:
-    """temporal_pooling="transformer" (temporal.py:46-75), eval forward: a tiny case stored in full (2 pooler
-    heads) and the BASELINE config-1 dimensions with seed-0 weights (keys, digest of the pooler weights, full logits)."""
+    """temporal_pooling="transformer" (temporal.py:46-75), eval mode: a tiny case stored in full (2 pooler heads,
+    one layer) with its CE gradients and post-Adam parameters, the same with TWO encoder layers (``tiny2:``), and the BASELINE
+    config-1 dimensions with seed-0 weights (keys, digest of the pooler weights, full logits, loss, gradient digests and the pooler
+    gradients in full)."""
     blob = {}
-    torch.manual_seed(31)
-    m = FusionModel(StubAudio(8), StubVideo(16), 8, mode="xattn", common_dim=16, xattn_head="concat", d_model=8, num_heads=2,
-                    audio_n_mels=8, temporal_pooling="transformer", temporal_num_heads=2, xattn_use_emotion_prior=True,
-                    xattn_emotion_prior_dim=4, xattn_emotion_prior_hidden_dim=8).eval()
-    g = torch.Generator().manual_seed(32)
-    xv = torch.randn(3, 4, 16, generator=g)
-    xa = torch.randn(3, 12, 8, generator=g)
-    with torch.no_grad():
-        logits = m(xv[..., None, None], xa)
-    blob.update({"tiny:xv": xv.numpy(), "tiny:xa": xa.numpy(), "tiny:logits": logits.numpy()})
-    blob.update({"tiny:w:" + k: v.numpy() for k, v in fusion_state(m).items()})
+    for tag, layers, seed in (("tiny", 1, 31), ("tiny2", 2, 33)):
+        torch.manual_seed(seed)
+        m = FusionModel(StubAudio(8), StubVideo(16), 8, mode="xattn", common_dim=16, xattn_head="concat", d_model=8, num_heads=2,
+                        audio_n_mels=8, temporal_pooling="transformer", temporal_num_heads=2, temporal_num_layers=layers,
+                        xattn_use_emotion_prior=True, xattn_emotion_prior_dim=4, xattn_emotion_prior_hidden_dim=8).eval()
+        g = torch.Generator().manual_seed(seed + 1)
+        xv = torch.randn(3, 4, 16, generator=g)
+        xa = torch.randn(3, 12, 8, generator=g)
+        labels = torch.randint(0, 8, (3,), generator=g)
+        before = fusion_state(m)
+        logits, loss, grads, after = run_case(m, xv, xa, labels)
+        blob.update({f"{tag}:xv": xv.numpy(), f"{tag}:xa": xa.numpy(), f"{tag}:logits": logits.numpy(), f"{tag}:labels": labels.numpy(),
+                     f"{tag}:loss": loss.numpy()})
+        blob.update({f"{tag}:w:" + k: v.numpy() for k, v in before.items()})
+        blob.update({f"{tag}:g:" + k: v.numpy() for k, v in grads.items()})
+        blob.update({f"{tag}:after:" + k: v.numpy() for k, v in after.items()})
     g = torch.Generator().manual_seed(1)
     xv = torch.randn(8, 16, 512, generator=g)
     xa = torch.randn(8, 149, 768, generator=g)
+    labels = torch.randint(0, 8, (8,), generator=torch.Generator().manual_seed(2))
     for head in ("concat", "gated"):
         torch.manual_seed(0)
         m = build_ref(FusionModel, dv=512, da=768, d_model=128, heads=4, head=head, prior=True, pooling="transformer").eval()
@@ -163,6 +171,14 @@ def gen_txpool(FusionModel) -> None:
         blob[f"{head}:logits"] = logits.numpy()
         blob[f"{head}:keys"] = np.array(sorted(sd))
         blob[f"{head}:pool_digest"] = digest(torch.cat([v.flatten() for k, v in sorted(sd.items()) if "temporal_pool" in k]))
+        loss = nn.functional.cross_entropy(m(xv[..., None, None], xa), labels)   # eval mode: dropouts identity, autograd on
+        loss.backward()
+        blob[f"{head}:labels"] = labels.numpy()
+        blob[f"{head}:loss"] = loss.detach().numpy()
+        for k, v in grads_of(m).items():
+            blob[f"{head}:gd:{k}"] = digest(v)
+            if "temporal_pool" in k and v.numel() <= 8192:
+                blob[f"{head}:g:{k}"] = v.numpy()
     np.savez_compressed(OUT / "xattn_txpool.npz", **blob)
 
 

@@ -138,18 +138,20 @@ def sinusoidal_positions(length: int, dim: int) -> Array:
 
 
 def temporal_transformer_pool(sd: Dict[str, Array], prefix: str, x: Array, num_heads: int) -> Array:
-    """TemporalTransformerPooling, temporal.py:46-75, eval mode, one pre-norm GELU nn.TransformerEncoderLayer
-    (norm_first: x = x + SA(LN1(x)); x = x + W2·GELU(W1·LN2(x))), then the attention pooling (``prefix + "pool."``)."""
+    """TemporalTransformerPooling, temporal.py:46-75, eval mode: pre-norm GELU nn.TransformerEncoderLayers (as many as ``sd``
+    holds; norm_first: x = x + SA(LN1(x)); x = x + W2·GELU(W1·LN2(x))), then the attention pooling (``prefix + "pool."``)."""
     x = _f64(x) + sinusoidal_positions(x.shape[1], x.shape[2])[None]                          # :72
-    lp = prefix + "encoder.layers.0."
-    if (prefix + "encoder.layers.1.norm1.weight") in sd:
-        raise ValueError("oracle restates one encoder layer")
-    h = layer_norm(x, sd[lp + "norm1.weight"], sd[lp + "norm1.bias"])
-    x = x + multihead_attention(sd, lp + "self_attn.", h, h, num_heads, None)
-    h = layer_norm(x, sd[lp + "norm2.weight"], sd[lp + "norm2.bias"])
-    f = linear(h, sd[lp + "linear1.weight"], sd[lp + "linear1.bias"])
-    f = 0.5 * f * (1.0 + np.vectorize(math.erf, otypes=[np.float64])(f / math.sqrt(2.0)))                                             # activation="gelu" (exact)
-    x = x + linear(f, sd[lp + "linear2.weight"], sd[lp + "linear2.bias"])                    # :73
+    erf = np.vectorize(math.erf, otypes=[np.float64])
+    layer = 0
+    while (prefix + f"encoder.layers.{layer}.norm1.weight") in sd:                            # :69 nn.TransformerEncoder(num_layers)
+        lp = prefix + f"encoder.layers.{layer}."
+        h = layer_norm(x, sd[lp + "norm1.weight"], sd[lp + "norm1.bias"])
+        x = x + multihead_attention(sd, lp + "self_attn.", h, h, num_heads, None)
+        h = layer_norm(x, sd[lp + "norm2.weight"], sd[lp + "norm2.bias"])
+        f = linear(h, sd[lp + "linear1.weight"], sd[lp + "linear1.bias"])
+        f = 0.5 * f * (1.0 + erf(f / math.sqrt(2.0)))                                         # activation="gelu" (exact)
+        x = x + linear(f, sd[lp + "linear2.weight"], sd[lp + "linear2.bias"])                # :73
+        layer += 1
     return temporal_attention_pool(sd, prefix + "pool.", x)                                  # :74
 
 

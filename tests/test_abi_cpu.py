@@ -109,8 +109,8 @@ def test_unsupported_reference_options_raise_cleanly():
 
     with pytest.raises(ValueError, match="temporal pooling"):
         XAttnFusionHead(temporal_pooling="nope")                      # the reference's own message (temporal.py:104)
-    with pytest.raises(ValueError, match="one encoder layer"):
-        XAttnFusionHead(temporal_pooling="transformer", temporal_num_layers=2)
+    with pytest.raises(ValueError, match="encoder layers"):
+        XAttnFusionHead(temporal_pooling="transformer", temporal_num_layers=9)
     with pytest.raises(ValueError):
         XAttnFusionHead(xattn_head="nope")
 

@@ -577,7 +577,7 @@ def test_mel_front_end_matches_reference(cuda_device):
 def test_transformer_pooling_matches_reference(cuda_device):
     """temporal_pooling="transformer" (TemporalTransformerPooling, temporal.py:46-75), forward: the tiny case
     (generic attention kernel, 2 pooler heads) and the BASELINE config-1 dimensions against the reference's logits in fp32 (1e-4),
-    tf32 and with bf16 embeddings; gradients raise (forward only)."""
+    tf32 and with bf16 embeddings; two encoder layers (temporal_num_layers=2) on the second tiny case."""
     import warnings
 
     from multimodalemotionrecognition_b200 import XAttnFusionHead
@@ -609,8 +609,152 @@ def test_transformer_pooling_matches_reference(cuda_device):
         sdn = {k: v.cpu().numpy() for k, v in mm.state_dict().items()}
         refb = xattn_oracle.xattn_forward(sdn, xv.bfloat16().float().numpy(), xa.bfloat16().float().numpy(), num_heads=4, head=head)
         assert np.abs(outb.cpu().numpy() - refb).max() <= FP32_TOL
-    with pytest.raises(ValueError):
-        mm(xv.to(cuda_device), xa.to(cuda_device))     # autograd on: no backward kernels for this pooler
+    sd2 = {k[len("tiny2:w:"):]: torch.from_numpy(v) for k, v in blob.items() if k.startswith("tiny2:w:")}
+    m2 = XAttnFusionHead(num_classes=8, video_dim=16, audio_dim=8, common_dim=16, d_model=8, num_heads=2, audio_n_mels=8,
+                         xattn_use_emotion_prior=True, xattn_emotion_prior_dim=4, xattn_emotion_prior_hidden_dim=8,
+                         temporal_pooling="transformer", temporal_num_heads=2, temporal_num_layers=2)
+    m2.load_state_dict(sd2, strict=True)
+    m2 = m2.to(cuda_device).eval()
+    with torch.no_grad():
+        out2 = m2(torch.from_numpy(blob["tiny2:xv"]).to(cuda_device), torch.from_numpy(blob["tiny2:xa"]).to(cuda_device))
+    assert np.abs(out2.cpu().numpy() - blob["tiny2:logits"]).max() <= 1e-5
+    ref2 = xattn_oracle.xattn_forward({k: v.numpy() for k, v in sd2.items()}, blob["tiny2:xv"], blob["tiny2:xa"], num_heads=2,
+                                      temporal_num_heads=2)
+    assert np.abs(ref2 - blob["tiny2:logits"]).max() <= 1e-5
+
+
+def _tiny_tx_head(blob, tag, layers, cuda_device, **kw):
+    from multimodalemotionrecognition_b200 import XAttnFusionHead
+
+    sd = {k[len(tag) + 3:]: torch.from_numpy(v) for k, v in blob.items() if k.startswith(f"{tag}:w:")}
+    m = XAttnFusionHead(num_classes=8, video_dim=16, audio_dim=8, common_dim=16, d_model=8, num_heads=2, audio_n_mels=8,
+                        xattn_use_emotion_prior=True, xattn_emotion_prior_dim=4, xattn_emotion_prior_hidden_dim=8,
+                        temporal_pooling="transformer", temporal_num_heads=2, temporal_num_layers=layers, **kw)
+    m.load_state_dict(sd, strict=True)
+    return m.to(cuda_device)
+
+
+def test_transformer_pooling_backward_matches_reference(cuda_device):
+    """Backward through TemporalTransformerPooling (temporal.py:46-75: encoder layers + learned pooling): every gradient and the
+    post-Adam parameters of the tiny cases (one and TWO encoder layers) against the reference's autograd (eval mode, dropouts
+    identity); at the BASELINE config-1 dimensions (audio self-attention 149 x 149: the row-tiled backward kernel) the loss, the
+    pooler's small gradients element-wise and every gradient by digest in fp32, cosine in tf32."""
+    import warnings
+
+    from multimodalemotionrecognition_b200.training import Stage1Trainer
+
+    warnings.simplefilter("ignore")
+    blob = load_npz("xattn_txpool.npz")
+    for tag, layers in (("tiny", 1), ("tiny2", 2)):
+        m = _tiny_tx_head(blob, tag, layers, cuda_device).eval()
+        xv = torch.from_numpy(blob[f"{tag}:xv"]).to(cuda_device)
+        xa = torch.from_numpy(blob[f"{tag}:xa"]).to(cuda_device)
+        labels = torch.from_numpy(blob[f"{tag}:labels"]).to(cuda_device)
+        loss = torch.nn.functional.cross_entropy(m(xv, xa), labels)
+        assert abs(float(loss.detach()) - float(blob[f"{tag}:loss"])) < 1e-5
+        loss.backward()
+        named = dict(m.named_parameters())
+        n = 0
+        for k, v in blob.items():
+            if k.startswith(f"{tag}:g:"):
+                g = named[k[len(tag) + 3:]].grad
+                assert g is not None, k
+                np.testing.assert_allclose(g.cpu().numpy(), v, atol=2e-6, rtol=1e-4, err_msg=k)
+                n += 1
+        assert n >= 30 + 24 * layers and f"{tag}:g:a_temporal_pool.pool.encoder.layers.{layers - 1}.linear1.weight" in blob
+        # one Stage-1 step (CE + backward + Adam lr 1e-3 wd 1e-4) against the reference's post-step parameters
+        m2 = _tiny_tx_head(blob, tag, layers, cuda_device)
+        Stage1Trainer(m2, lr=1e-3, weight_decay=1e-4).step(xv, xa, labels, training=False)
+        sd2 = m2.state_dict()
+        for k, v in blob.items():
+            name = k[len(tag) + 7:]
+            if k.startswith(f"{tag}:after:") and (f"{tag}:g:" + name) in blob:
+                got, gr, w0 = sd2[name].cpu().numpy(), blob[f"{tag}:g:" + name], blob[f"{tag}:w:" + name]
+                solid = np.abs(gr) > 1e-5     # ~0 gradients (attention key bias): Adam's first step is the sign of rounding noise
+                np.testing.assert_allclose(got[solid], v[solid], atol=3e-6, rtol=0, err_msg=k)
+                assert np.all(np.abs(got - w0) <= 1e-3 * 1.001 + 1e-7), k
+    g = torch.Generator().manual_seed(1)
+    xv = torch.randn(8, 16, 512, generator=g).to(cuda_device)
+    xa = torch.randn(8, 149, 768, generator=g).to(cuda_device)
+    for head in ("concat", "gated"):
+        labels = torch.from_numpy(blob[f"{head}:labels"]).to(cuda_device)
+        for prec in ("fp32", "tf32"):
+            mm = make_head(head, True, seed=0, temporal_pooling="transformer", precision=prec).to(cuda_device).eval()
+            loss = torch.nn.functional.cross_entropy(mm(xv, xa), labels)
+            loss.backward()
+            named = dict(mm.named_parameters())
+            n = 0
+            for k, v in blob.items():
+                if prec == "fp32" and k.startswith(f"{head}:g:"):
+                    np.testing.assert_allclose(named[k[len(head) + 3:]].grad.cpu().numpy(), v, atol=2e-6, rtol=2e-4, err_msg=k)
+                    n += 1
+                elif prec == "fp32" and k.startswith(f"{head}:gd:"):
+                    np.testing.assert_allclose(digest(named[k[len(head) + 4:]].grad), v, atol=5e-5, rtol=2e-4, err_msg=k)
+                    n += 1
+                elif prec == "tf32" and k.startswith(f"{head}:g:") and v.size > 1:
+                    got = named[k[len(head) + 3:]].grad.flatten().double().cpu()
+                    want = torch.from_numpy(v).flatten().double()
+                    if float(want.norm()) > 1e-7:   # (the attention key bias has a zero gradient)
+                        assert float(torch.dot(got, want) / (got.norm() * want.norm() + 1e-30)) >= 0.99, k
+                    n += 1
+            assert n >= 26
+            if prec == "fp32":
+                assert abs(float(loss.detach()) - float(blob[f"{head}:loss"])) < 1e-5
+
+
+def test_transformer_pooling_training_mode_gradients_are_consistent(cuda_device):
+    """Training mode of the transformer pooler (four dropouts per encoder layer + the pooler's, temporal.py:60-68, :19): for a fixed
+    Philox offset the loss is a deterministic function of the parameters, so the analytic gradient must match central differences
+    along random directions — this ties every backward mask to its forward mask.  With temporal_dropout=0 (and the other dropouts
+    off) training mode reproduces the eval-mode gradients exactly."""
+    import warnings
+
+    warnings.simplefilter("ignore")
+    blob = load_npz("xattn_txpool.npz")
+    xv = torch.from_numpy(blob["tiny2:xv"]).to(cuda_device)
+    xa = torch.from_numpy(blob["tiny2:xa"]).to(cuda_device)
+    labels = torch.from_numpy(blob["tiny2:labels"]).to(cuda_device)
+    off = dict(xattn_attn_dropout=0.0, xattn_stochastic_depth=0.0, xattn_emotion_prior_dropout=0.0)
+    m = _tiny_tx_head(blob, "tiny2", 2, cuda_device, temporal_dropout=0.25, **off).train()
+    m.xattn_head_dropout = 0.0
+
+    def loss_at():
+        m._rng_offset = 40          # the forward advances it by one: every evaluation draws the masks of offset 41
+        return torch.nn.functional.cross_entropy(m(xv, xa), labels)
+
+    base = loss_at()
+    base.backward()
+    m.eval()
+    with torch.no_grad():
+        assert abs(float(torch.nn.functional.cross_entropy(m(xv, xa), labels)) - float(base)) > 1e-4   # the masks are active
+    m.train()
+    params = [(n, p) for n, p in m.named_parameters() if p.grad is not None and "temporal_pool" in n]
+    assert len(params) >= 2 * (24 + 6)
+    grads = {n: p.grad.detach().clone() for n, p in params}
+    gen = torch.Generator().manual_seed(5)
+    eps = 2e-2
+    for trial in range(6):
+        dirs = {n: torch.randn(p.shape, generator=gen).to(cuda_device) for n, p in params}
+        scale = 1.0 / float(sum(float(d.norm()) ** 2 for d in dirs.values())) ** 0.5
+        want = sum(float((grads[n] * dirs[n]).sum()) for n, _ in params) * scale
+        vals = []
+        for sign in (+1.0, -1.0):
+            with torch.no_grad():
+                for n, p in params:
+                    p.add_(dirs[n], alpha=sign * eps * scale)
+                vals.append(float(loss_at()))
+                for n, p in params:
+                    p.add_(dirs[n], alpha=-sign * eps * scale)
+        got = (vals[0] - vals[1]) / (2 * eps)
+        assert abs(got - want) <= 0.03 * abs(want) + 2e-4, (trial, got, want)
+    # dropout-free training mode == eval mode
+    m0 = _tiny_tx_head(blob, "tiny2", 2, cuda_device, temporal_dropout=0.0, **off).train()
+    m0.xattn_head_dropout = 0.0
+    torch.nn.functional.cross_entropy(m0(xv, xa), labels).backward()
+    named = dict(m0.named_parameters())
+    for k, v in blob.items():
+        if k.startswith("tiny2:g:"):
+            np.testing.assert_allclose(named[k[len("tiny2:g:"):]].grad.cpu().numpy(), v, atol=2e-6, rtol=1e-4, err_msg=k)
 
 
 def test_mel_unfold_and_serving_epilogue_edge_cases(cuda_device):
