@@ -786,6 +786,129 @@ __global__ void __launch_bounds__(256) prior_bwd_kernel(PriorBwdArgs a) {
   }
 }
 
+// The same for d_model = 128 with a short dependency chain in front of the token loop (the kernel above walks W0 with 64 dependent
+// rounds of loads per thread and runs at two CTAs per SM): the clip's score gradients are staged in shared memory once, the
+// Hd x 2E product for d_pooled runs as 4 x 64 threads with 16 float4 weight loads in flight each, and a warp covers a token row
+// with one float4 per lane.  Same arithmetic and outputs as the `vec` path of prior_bwd_kernel.
+__global__ void __launch_bounds__(256, 3) prior_bwd128_kernel(PriorBwdArgs a) {
+  extern __shared__ __align__(16) float sm[];
+  constexpr int E = 128;
+  const int b = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nw = blockDim.x >> 5;
+  const int P = a.P, Hd = a.Hd, T = a.T, Ta = a.Ta;
+  float* dpool = sm;                    // [2E]
+  float* part = dpool + 2 * E;          // [4][2E] partial d_pooled; later gred [nw][6][E] (starts here)
+  float* gred = part;
+  float* sd = gred + nw * 6 * E;        // [2T + 2Ta]: d_qv | d_kvs | d_ka | d_qa
+  float* sq = sd + 2 * (T + Ta);        // [4]
+  float* dprior = sq + 4;               // [P]
+  float* dphid = dprior + P;            // [Hd]
+  for (int i = tid; i < T; i += blockDim.x) {
+    sd[i] = a.d_qv[(int64_t)b * T + i];
+    sd[T + i] = a.d_kvs[(int64_t)b * T + i];
+  }
+  for (int j = tid; j < Ta; j += blockDim.x) {
+    sd[2 * T + j] = a.d_ka[(int64_t)b * Ta + j];
+    sd[2 * T + Ta + j] = a.d_qa[(int64_t)b * Ta + j];
+  }
+  __syncthreads();
+  if (warp < 4) {   // sums in the order of the score heads: v_query, a_key, a_query, v_key
+    const float* src = warp == 0 ? sd : warp == 1 ? sd + 2 * T : warp == 2 ? sd + 2 * T + Ta : sd + T;
+    const int n = (warp == 0 || warp == 3) ? T : Ta;
+    float s = 0.f;
+    for (int i = lane; i < n; i += 32) s += src[i];
+    s = warp_sum(s);
+    if (lane == 0) sq[warp] = s;
+  }
+  __syncthreads();
+  for (int p = tid; p < P; p += blockDim.x) {
+    float s = 0.f;
+    for (int k = 0; k < 4; ++k) s = fmaf(sq[k], a.wh[k][E + p], s);
+    dprior[p] = s;
+    a.d_prior[(int64_t)b * P + p] = s;
+    const float pr = a.prior[(int64_t)b * P + p];
+    for (int k = 0; k < 4; ++k) atomicAdd(a.g_wh[k] + E + p, sq[k] * pr);
+  }
+  if (tid < 4) atomicAdd(a.g_bh[tid], sq[tid]);
+  __syncthreads();
+  for (int h = tid; h < Hd; h += blockDim.x) {
+    float s = 0.f;
+    for (int p = 0; p < P; ++p) s = fmaf(dprior[p], a.w3[(int64_t)p * Hd + h], s);
+    s = a.phid[(int64_t)b * Hd + h] > 0.f ? s * a.inv_keep : 0.f;
+    dphid[h] = s;
+    a.d_phid[(int64_t)b * Hd + h] = s;
+  }
+  __syncthreads();
+  {   // d_pooled = d_phid · W0: thread (k4, hp) takes four columns and every fourth-of-the-range hidden unit
+    const int k4 = tid & 63, hp = tid >> 6;
+    float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+    for (int h0 = hp * 16; h0 < Hd; h0 += 64) {
+      float4 w[16];
+#pragma unroll
+      for (int q = 0; q < 16; ++q)
+        w[q] = h0 + q < Hd ? __ldg(reinterpret_cast<const float4*>(a.w0 + (int64_t)(h0 + q) * 2 * E) + k4) : make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+      for (int q = 0; q < 16; ++q) {
+        const float d = h0 + q < Hd ? dphid[h0 + q] : 0.f;
+        acc.x = fmaf(d, w[q].x, acc.x); acc.y = fmaf(d, w[q].y, acc.y); acc.z = fmaf(d, w[q].z, acc.z); acc.w = fmaf(d, w[q].w, acc.w);
+      }
+    }
+    *reinterpret_cast<float4*>(part + hp * 2 * E + 4 * k4) = acc;
+  }
+  __syncthreads();
+  dpool[tid] = part[tid] + part[2 * E + tid] + part[4 * E + tid] + part[6 * E + tid];   // (blockDim.x == 2E)
+  __syncthreads();
+  const float* v0 = a.v0 + (int64_t)b * T * E;
+  const float* a0 = a.a0 + (int64_t)b * Ta * E;
+  float* dv0 = a.d_v0 + (int64_t)b * T * E;
+  float* da0 = a.d_a0 + (int64_t)b * Ta * E;
+  float4 gA, gB, cs;   // a side's two score-head rows and the column sums of its finished token gradients
+  // x += dA·wA + dB·wB + pm over the side's tokens (four rows per warp in flight, all loads before the first store: the gradient
+  // pointers may alias the token pointers as far as the compiler knows)
+  auto side = [&](const float* x, float* dx, int L, const float* sA, const float* sB, const float* wAp, const float* wBp, const float* pool,
+                  float inv_L) {
+    const float4 wA = __ldg(reinterpret_cast<const float4*>(wAp) + lane), wB = __ldg(reinterpret_cast<const float4*>(wBp) + lane);
+    const float4 pl = *reinterpret_cast<const float4*>(pool + 4 * lane);
+    const float4 pm = make_float4(pl.x * inv_L, pl.y * inv_L, pl.z * inv_L, pl.w * inv_L);
+    gA = gB = cs = make_float4(0.f, 0.f, 0.f, 0.f);
+    for (int i0 = warp; i0 < L; i0 += 4 * nw) {
+      float4 xr[4], d[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const int i = i0 + u * nw;
+        if (i < L) {
+          xr[u] = __ldg(reinterpret_cast<const float4*>(x + (int64_t)i * E) + lane);
+          d[u] = *(reinterpret_cast<const float4*>(dx + (int64_t)i * E) + lane);
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const int i = i0 + u * nw;
+        if (i < L) {
+          const float dA = sA[i], dB = sB[i];
+          d[u].x += dA * wA.x + dB * wB.x + pm.x; d[u].y += dA * wA.y + dB * wB.y + pm.y;
+          d[u].z += dA * wA.z + dB * wB.z + pm.z; d[u].w += dA * wA.w + dB * wB.w + pm.w;
+          *(reinterpret_cast<float4*>(dx + (int64_t)i * E) + lane) = d[u];
+          cs.x += d[u].x; cs.y += d[u].y; cs.z += d[u].z; cs.w += d[u].w;
+          gA.x = fmaf(dA, xr[u].x, gA.x); gA.y = fmaf(dA, xr[u].y, gA.y); gA.z = fmaf(dA, xr[u].z, gA.z); gA.w = fmaf(dA, xr[u].w, gA.w);
+          gB.x = fmaf(dB, xr[u].x, gB.x); gB.y = fmaf(dB, xr[u].y, gB.y); gB.z = fmaf(dB, xr[u].z, gB.z); gB.w = fmaf(dB, xr[u].w, gB.w);
+        }
+      }
+    }
+  };
+  float* gr = gred + warp * 6 * E + 4 * lane;   // rows: v_query, a_key, a_query, v_key, colsum d_v0, colsum d_a0
+  side(v0, dv0, T, sd, sd + T, a.wh[0], a.wh[3], dpool, 1.f / (float)T);                        // dA = d_qv (v_query), dB = d_kvs (v_key)
+  *reinterpret_cast<float4*>(gr) = gA; *reinterpret_cast<float4*>(gr + 3 * E) = gB; *reinterpret_cast<float4*>(gr + 4 * E) = cs;
+  side(a0, da0, Ta, sd + 2 * T, sd + 2 * T + Ta, a.wh[1], a.wh[2], dpool + E, 1.f / (float)Ta);   // dA = d_ka (a_key), dB = d_qa (a_query)
+  *reinterpret_cast<float4*>(gr + E) = gA; *reinterpret_cast<float4*>(gr + 2 * E) = gB; *reinterpret_cast<float4*>(gr + 5 * E) = cs;
+  __syncthreads();
+  for (int idx = tid; idx < 6 * E; idx += blockDim.x) {
+    float t = 0.f;
+    for (int w2 = 0; w2 < nw; ++w2) t += gred[(int64_t)w2 * 6 * E + idx];
+    const int which = idx / E, e = idx - which * E;
+    atomicAdd(which < 4 ? a.g_wh[which] + e : which == 4 ? a.g_bv + e : a.g_ba + e, t);
+  }
+}
+
 // ---- TemporalAttentionPooling backward (temporal.py:9-26) ---------------------------------------------------------
 // out = Σ_l a_l x_l, a = softmax_l(s), s_l = w2·(GELU(h_l) ⊙ m_l) + b2, h_l = W1 y_l + b1, y_l = LN(x_l)·γ + β.  Nothing but x was
 // saved: a first pass over the clip's tokens recomputes the scores and d_a_l = <d_out, x_l>, the softmax backward gives d_s, a
@@ -819,7 +942,6 @@ __global__ void __launch_bounds__(256) attn_pool_bwd_kernel(AttnPoolBwdArgs a) {
   float* score = dhrow + nw * H2;     // [L]  s_l, then a_l
   float* da = score + L;              // [L]  <d_out, x_l>, then d_s_l
   float* red = da + L;                // [nw][2E + H2 + 1] partial dγ | dβ | dw2 | db2
-  __shared__ float s_stat[2];
   for (int i = tid; i < E * H2; i += blockDim.x) {
     const int j = i / E, e = i - j * E;
     const float w = a.w1[i];
@@ -1196,13 +1318,20 @@ static int backward_f32_impl(const xattn_config& c, const float* params, const T
     pa.d_qv = ws + w.d_qv; pa.d_ka = ws + w.d_ka; pa.d_qa = ws + w.d_qa; pa.d_kvs = ws + w.d_kvs;
     pa.d_v0 = ws + w.d_v0; pa.d_a0 = ws + w.d_a0; pa.d_prior = ws + w.d_prior; pa.d_phid = ws + w.d_phid;
     pa.T = T; pa.Ta = Ta; pa.E = E; pa.P = c.prior_dim; pa.Hd = c.prior_hidden; pa.inv_keep = 1.f / (1.f - p_prior);
-    size_t smem = sizeof(float) * (4 + c.prior_dim + c.prior_hidden + 2 * E);
-    const size_t smem_vec = smem + sizeof(float) * (2 * (T + Ta) + 8 * 6 * E);
-    pa.vec = (E % 4 == 0 && smem_vec <= 48 * 1024) ? 1 : 0;
     pa.g_bv = G(XP_V_IN_B); pa.g_ba = G(XP_A_IN_B);
-    tok_bias_fused = pa.vec != 0;   // d_v0 / d_a0 are final in that kernel: it leaves their column sums in the two bias gradients
-    if (pa.vec) smem = smem_vec;
-    prior_bwd_kernel<<<B, 256, smem, st>>>(pa);
+    const size_t smem128 = sizeof(float) * (2 * E + 8 * 6 * E + 2 * (T + Ta) + 4 + c.prior_dim + c.prior_hidden);
+    if (E == 128 && smem128 <= 48 * 1024) {
+      pa.vec = 1;
+      tok_bias_fused = true;   // d_v0 / d_a0 are final in that kernel: it leaves their column sums in the two bias gradients
+      prior_bwd128_kernel<<<B, 256, smem128, st>>>(pa);
+    } else {
+      size_t smem = sizeof(float) * (4 + c.prior_dim + c.prior_hidden + 2 * E);
+      const size_t smem_vec = smem + sizeof(float) * (2 * (T + Ta) + 8 * 6 * E);
+      pa.vec = (E % 4 == 0 && smem_vec <= 48 * 1024) ? 1 : 0;
+      tok_bias_fused = pa.vec != 0;
+      if (pa.vec) smem = smem_vec;
+      prior_bwd_kernel<<<B, 256, smem, st>>>(pa);
+    }
     count_launch();
     linear_bwd_dw<float>(st, ws + w.d_prior, c.prior_dim, ws + w.phid, c.prior_hidden, G(XP_PRIOR3_W), B, c.prior_dim, c.prior_hidden);
     launch_colsum(st, ws + w.d_prior, c.prior_dim, B, c.prior_dim, G(XP_PRIOR3_B));

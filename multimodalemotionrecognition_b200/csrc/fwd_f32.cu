@@ -125,6 +125,108 @@ __global__ void __launch_bounds__(256) prior_fwd_kernel(PriorArgs a) {
   }
 }
 
+// The same for d_model = 128 (a warp covers a token row with one float4 per lane) as ONE pass over the clip's tokens and a short
+// dependency chain: the column sums for the two means and the raw token dot products with the four score vectors come from the
+// same loads (four rows per warp in flight), the 2E -> Hd layer runs on all threads at once (four threads per hidden unit, 16
+// float4 weight loads each: one L2 round trip instead of Hd / 8 dependent ones), and the per-clip constants are added to the raw
+// dots at the end.  (The two-pass kernel above spent ~30 us per CTA on that chain; 1024 clips are two waves of CTAs.)
+__device__ __forceinline__ float dot4(const float4& a, const float4& b) { return fmaf(a.x, b.x, fmaf(a.y, b.y, fmaf(a.z, b.z, a.w * b.w))); }
+__global__ void __launch_bounds__(256, 4) prior_fwd128_kernel(PriorArgs a) {
+  extern __shared__ __align__(16) float sm[];
+  constexpr int E = 128;
+  const int b = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nw = blockDim.x >> 5;
+  const int P = a.P, Hd = a.Hd, T = a.T, Ta = a.Ta;
+  float* pooled = sm;                  // [2E]
+  float* scr = pooled + 2 * E;         // [2][nw][E] per-warp column sums (video | audio)
+  float* rawA = scr + 2 * nw * E;      // [T + Ta] token · wA  (v_query | a_key)
+  float* rawB = rawA + T + Ta;         // [T + Ta] token · wB  (v_key | a_query)
+  float* hid = rawB + T + Ta;          // [Hd]
+  float* prior = hid + Hd;             // [P]
+  float* pc = prior + P;               // [4]
+  const float* v0 = a.v0 + (int64_t)b * T * E;
+  const float* a0 = a.a0 + (int64_t)b * Ta * E;
+  auto rows = [&](const float* x, int L, const float4 wA, const float4 wB, float* outA, float* outB, float* colsum) {
+    float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
+    for (int i0 = warp; i0 < L; i0 += 4 * nw) {
+      float4 r[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const int i = i0 + u * nw;
+        r[u] = i < L ? __ldg(reinterpret_cast<const float4*>(x + (int64_t)i * E) + lane) : make_float4(0.f, 0.f, 0.f, 0.f);
+      }
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const int i = i0 + u * nw;
+        s.x += r[u].x; s.y += r[u].y; s.z += r[u].z; s.w += r[u].w;
+        const float dA = warp_sum(dot4(r[u], wA)), dB = warp_sum(dot4(r[u], wB));
+        if (lane == 0 && i < L) { outA[i] = dA; outB[i] = dB; }
+      }
+    }
+    *reinterpret_cast<float4*>(colsum + warp * E + 4 * lane) = s;
+  };
+  rows(v0, T, __ldg(reinterpret_cast<const float4*>(a.wh[0]) + lane), __ldg(reinterpret_cast<const float4*>(a.wh[3]) + lane), rawA, rawB, scr);
+  rows(a0, Ta, __ldg(reinterpret_cast<const float4*>(a.wh[1]) + lane), __ldg(reinterpret_cast<const float4*>(a.wh[2]) + lane), rawA + T,
+       rawB + T, scr + nw * E);
+  __syncthreads();
+  {   // thread e < E: video mean of column e; e >= E: audio mean (warps in order, as clip_mean sums them)
+    const float* src = scr + (tid >= E ? nw * E + (tid - E) : tid);
+    float s = 0.f;
+    for (int w = 0; w < nw; ++w) s += src[w * E];
+    const float m = s / (float)(tid >= E ? Ta : T);
+    pooled[tid] = m;
+    a.pooled0[(int64_t)b * 2 * E + tid] = m;
+  }
+  __syncthreads();
+  for (int h0 = 0; h0 < Hd; h0 += 64) {   // prior_net.0 + ReLU + Dropout: four threads per hidden unit
+    const int h = h0 + (tid >> 2), part = tid & 3;
+    float s = 0.f;
+    if (h < Hd) {
+      const float4* w = reinterpret_cast<const float4*>(a.w0 + (int64_t)h * 2 * E + part * 64);
+      const float4* x = reinterpret_cast<const float4*>(pooled + part * 64);
+      float4 wr[16];
+#pragma unroll
+      for (int q = 0; q < 16; ++q) wr[q] = __ldg(w + q);
+#pragma unroll
+      for (int q = 0; q < 16; ++q) s += dot4(wr[q], x[q]);
+    }
+    s += __shfl_xor_sync(0xffffffffu, s, 1);
+    s += __shfl_xor_sync(0xffffffffu, s, 2);
+    if (h < Hd && part == 0) {
+      float r = fmaxf(s + a.b0[h], 0.f);
+      r *= drop_factor(a.p_drop, a.seed, a.offset, RS_PRIOR, (uint64_t)b * Hd + h);
+      hid[h] = r;
+      a.phid[(int64_t)b * Hd + h] = r;
+    }
+  }
+  __syncthreads();
+  for (int p = warp; p < P; p += nw) {
+    const float* w = a.w3 + (int64_t)p * Hd;
+    float s = 0.f;
+    for (int k = lane; k < Hd; k += 32) s = fmaf(w[k], hid[k], s);
+    s = warp_sum(s);
+    if (lane == 0) {
+      prior[p] = s + a.b3[p];
+      a.prior[(int64_t)b * P + p] = s + a.b3[p];
+    }
+  }
+  __syncthreads();
+  if (tid < 4) {
+    const float* w = a.wh[tid] + E;
+    float s = a.bh[tid][0];
+    for (int p = 0; p < P; ++p) s = fmaf(w[p], prior[p], s);
+    pc[tid] = s;
+  }
+  __syncthreads();
+  for (int i = tid; i < T; i += blockDim.x) {
+    a.qv[(int64_t)b * T + i] = rawA[i] + pc[0];
+    a.kvs[(int64_t)b * T + i] = rawB[i] + pc[3];
+  }
+  for (int j = tid; j < Ta; j += blockDim.x) {
+    a.ka[(int64_t)b * Ta + j] = rawA[T + j] + pc[1];
+    a.qa[(int64_t)b * Ta + j] = rawB[T + j] + pc[2];
+  }
+}
+
 // ---------------------------------------------------------------------------------------------------------
 // Attention core of nn.MultiheadAttention (need_weights branch of F.multi_head_attention_forward):
 //   S_h = (Q_h / sqrt(dh)) K_h^T + bias ;  P_h = softmax(S_h) ;  O_h = dropout(P_h) V_h
@@ -712,8 +814,14 @@ static int forward_f32_impl(const xattn_config& c, const float* params, const TI
     pa.qv = ws + w.qv; pa.ka = ws + w.ka; pa.qa = ws + w.qa; pa.kvs = ws + w.kvs;
     pa.T = T; pa.Ta = Ta; pa.E = E; pa.P = c.prior_dim; pa.Hd = c.prior_hidden;
     pa.p_drop = p_prior; pa.seed = c.seed; pa.offset = c.offset;
-    const size_t smem = sizeof(float) * (2 * E + c.prior_hidden + c.prior_dim + 4 + 8 * E);
-    prior_fwd_kernel<<<B, 256, smem, st>>>(pa);
+    if (E == 128) {
+      const size_t smem128 = sizeof(float) * (2 * E + 2 * 8 * E + 2 * (T + Ta) + c.prior_hidden + c.prior_dim + 4);
+      if (smem128 > 48 * 1024) XF_FAIL(XATTN_ERR_SHAPE, "prior kernel needs %zu B of shared memory (T + Ta too large)", smem128);
+      prior_fwd128_kernel<<<B, 256, smem128, st>>>(pa);
+    } else {
+      const size_t smem = sizeof(float) * (2 * E + c.prior_hidden + c.prior_dim + 4 + 8 * E);
+      prior_fwd_kernel<<<B, 256, smem, st>>>(pa);
+    }
     count_launch();
     XF_LAUNCH_CHECK();
   }
