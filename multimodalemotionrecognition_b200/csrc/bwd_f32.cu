@@ -796,9 +796,9 @@ __global__ void __launch_bounds__(256, 3) prior_bwd128_kernel(PriorBwdArgs a) {
   const int b = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nw = blockDim.x >> 5;
   const int P = a.P, Hd = a.Hd, T = a.T, Ta = a.Ta;
   float* dpool = sm;                    // [2E]
-  float* part = dpool + 2 * E;          // [4][2E] partial d_pooled; later gred [nw][6][E] (starts here)
-  float* gred = part;
-  float* sd = gred + nw * 6 * E;        // [2T + 2Ta]: d_qv | d_kvs | d_ka | d_qa
+  float* part = dpool + 2 * E;          // [4][2E] partial d_pooled; later gred [6][E] (starts here): the CTA's sums of the four
+  float* gred = part;                   //   score-head rows and of the d_v0 / d_a0 columns, met by shared-memory atomics
+  float* sd = part + 4 * 2 * E;         // [2T + 2Ta]: d_qv | d_kvs | d_ka | d_qa
   float* sq = sd + 2 * (T + Ta);        // [4]
   float* dprior = sq + 4;               // [P]
   float* dphid = dprior + P;            // [Hd]
@@ -857,6 +857,8 @@ __global__ void __launch_bounds__(256, 3) prior_bwd128_kernel(PriorBwdArgs a) {
   __syncthreads();
   dpool[tid] = part[tid] + part[2 * E + tid] + part[4 * E + tid] + part[6 * E + tid];   // (blockDim.x == 2E)
   __syncthreads();
+  for (int i = tid; i < 6 * E; i += blockDim.x) gred[i] = 0.f;   // (part is dead)
+  __syncthreads();
   const float* v0 = a.v0 + (int64_t)b * T * E;
   const float* a0 = a.a0 + (int64_t)b * Ta * E;
   float* dv0 = a.d_v0 + (int64_t)b * T * E;
@@ -895,17 +897,19 @@ __global__ void __launch_bounds__(256, 3) prior_bwd128_kernel(PriorBwdArgs a) {
       }
     }
   };
-  float* gr = gred + warp * 6 * E + 4 * lane;   // rows: v_query, a_key, a_query, v_key, colsum d_v0, colsum d_a0
+  float* gr = gred + 4 * lane;   // rows: v_query, a_key, a_query, v_key, colsum d_v0, colsum d_a0
+  auto put = [&](int row, const float4& v) {
+    float* d = gr + row * E;
+    atomicAdd(d, v.x); atomicAdd(d + 1, v.y); atomicAdd(d + 2, v.z); atomicAdd(d + 3, v.w);
+  };
   side(v0, dv0, T, sd, sd + T, a.wh[0], a.wh[3], dpool, 1.f / (float)T);                        // dA = d_qv (v_query), dB = d_kvs (v_key)
-  *reinterpret_cast<float4*>(gr) = gA; *reinterpret_cast<float4*>(gr + 3 * E) = gB; *reinterpret_cast<float4*>(gr + 4 * E) = cs;
+  put(0, gA); put(3, gB); put(4, cs);
   side(a0, da0, Ta, sd + 2 * T, sd + 2 * T + Ta, a.wh[1], a.wh[2], dpool + E, 1.f / (float)Ta);   // dA = d_ka (a_key), dB = d_qa (a_query)
-  *reinterpret_cast<float4*>(gr + E) = gA; *reinterpret_cast<float4*>(gr + 2 * E) = gB; *reinterpret_cast<float4*>(gr + 5 * E) = cs;
+  put(1, gA); put(2, gB); put(5, cs);
   __syncthreads();
   for (int idx = tid; idx < 6 * E; idx += blockDim.x) {
-    float t = 0.f;
-    for (int w2 = 0; w2 < nw; ++w2) t += gred[(int64_t)w2 * 6 * E + idx];
     const int which = idx / E, e = idx - which * E;
-    atomicAdd(which < 4 ? a.g_wh[which] + e : which == 4 ? a.g_bv + e : a.g_ba + e, t);
+    atomicAdd(which < 4 ? a.g_wh[which] + e : which == 4 ? a.g_bv + e : a.g_ba + e, gred[idx]);
   }
 }
 
@@ -1298,12 +1302,17 @@ static int backward_f32_impl(const xattn_config& c, const float* params, const T
     aa.dbq = G(XP_V2A_IN_B); aa.dbkv = G(XP_V2A_IN_B) + E;
     XF_TRY(launch_attn_bwd(st, aa, B, &bias_fused));
   }
-  linear_bwd_dw<float>(st, ws + w.d_q1, E, ws + w.v0, E, G(XP_V2A_IN_W), B * T, E, E);
-  if (!bias_fused) launch_colsum(st, ws + w.d_q1, E, B * T, E, G(XP_V2A_IN_B));
+  // v2a in_proj: the token gradients first (the prior backward and the input projections wait for them) ...
   linear_bwd_dx(st, ws + w.d_q1, E, P(XP_V2A_IN_W), ws + w.d_v0, B * T, E, E, true);
-  linear_bwd_dw<float>(st, ws + w.d_kv1, 2 * E, ws + w.a0, E, G(XP_V2A_IN_W) + (int64_t)E * E, B * Ta, 2 * E, E);
-  if (!bias_fused) launch_colsum(st, ws + w.d_kv1, 2 * E, B * Ta, 2 * E, G(XP_V2A_IN_B) + E);
   linear_bwd_dx(st, ws + w.d_kv1, 2 * E, P(XP_V2A_IN_W) + (int64_t)E * E, ws + w.d_a0, B * Ta, 2 * E, E, true);
+  // ... then its weight gradients (HBM-bound tensor-core GEMMs nothing downstream reads) on the high-priority side stream under
+  // tf32, beside the latency-bound per-clip prior backward on `st`
+  SideFork sf;
+  if (opt.fork && c.use_prior && g_tc_gemm) XF_TRY(sf.begin(st));
+  linear_bwd_dw<float>(sf.side(), ws + w.d_q1, E, ws + w.v0, E, G(XP_V2A_IN_W), B * T, E, E);
+  if (!bias_fused) launch_colsum(sf.side(), ws + w.d_q1, E, B * T, E, G(XP_V2A_IN_B));
+  linear_bwd_dw<float>(sf.side(), ws + w.d_kv1, 2 * E, ws + w.a0, E, G(XP_V2A_IN_W) + (int64_t)E * E, B * Ta, 2 * E, E);
+  if (!bias_fused) launch_colsum(sf.side(), ws + w.d_kv1, 2 * E, B * Ta, 2 * E, G(XP_V2A_IN_B) + E);
   XF_LAUNCH_CHECK();
 
   bool tok_bias_fused = false;
@@ -1319,7 +1328,7 @@ static int backward_f32_impl(const xattn_config& c, const float* params, const T
     pa.d_v0 = ws + w.d_v0; pa.d_a0 = ws + w.d_a0; pa.d_prior = ws + w.d_prior; pa.d_phid = ws + w.d_phid;
     pa.T = T; pa.Ta = Ta; pa.E = E; pa.P = c.prior_dim; pa.Hd = c.prior_hidden; pa.inv_keep = 1.f / (1.f - p_prior);
     pa.g_bv = G(XP_V_IN_B); pa.g_ba = G(XP_A_IN_B);
-    const size_t smem128 = sizeof(float) * (2 * E + 8 * 6 * E + 2 * (T + Ta) + 4 + c.prior_dim + c.prior_hidden);
+    const size_t smem128 = sizeof(float) * (2 * E + 8 * E + 2 * (T + Ta) + 4 + c.prior_dim + c.prior_hidden);
     if (E == 128 && smem128 <= 48 * 1024) {
       pa.vec = 1;
       tok_bias_fused = true;   // d_v0 / d_a0 are final in that kernel: it leaves their column sums in the two bias gradients
@@ -1339,6 +1348,7 @@ static int backward_f32_impl(const xattn_config& c, const float* params, const T
     launch_colsum(st, ws + w.d_phid, c.prior_hidden, B, c.prior_hidden, G(XP_PRIOR0_B));
     XF_LAUNCH_CHECK();
   }
+  XF_TRY(sf.join());
 
   if (opt.tail_stream != nullptr) {   // everything but the input projections' gradients is final from here on
     cudaEvent_t ev = nullptr;

@@ -22,6 +22,59 @@ bool pdl_enabled() {
   static const bool off = getenv("XATTN_NO_PDL") != nullptr;
   return !off && !g_stage_timing;
 }
+struct SideForkRes {
+  cudaStream_t side = nullptr;
+  cudaEvent_t fork = nullptr, join = nullptr;
+  std::mutex enqueue;
+};
+int SideFork::begin(cudaStream_t st) {
+  static SideForkRes res[64];
+  static std::mutex mu;
+  static const bool off = getenv("XATTN_NO_FORK") != nullptr;
+  st_ = st;
+  side_ = st;
+  if (off || g_stage_timing) return XATTN_OK;
+  int dev = 0;
+  XF_CUDA(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= 64) XF_FAIL(XATTN_ERR_CUDA, "device index %d out of range", dev);
+  SideForkRes* r = &res[dev];
+  {
+    std::lock_guard<std::mutex> lock(mu);
+    if (r->side == nullptr) {
+      int lo = 0, hi = 0;
+      XF_CUDA(cudaDeviceGetStreamPriorityRange(&lo, &hi));
+      XF_CUDA(cudaStreamCreateWithPriority(&r->side, cudaStreamNonBlocking, hi));
+    }
+    if (r->fork == nullptr) XF_CUDA(cudaEventCreateWithFlags(&r->fork, cudaEventDisableTiming));
+    if (r->join == nullptr) XF_CUDA(cudaEventCreateWithFlags(&r->join, cudaEventDisableTiming));
+  }
+  r->enqueue.lock();
+  cudaError_t e = cudaEventRecord(r->fork, st);
+  if (e == cudaSuccess) e = cudaStreamWaitEvent(r->side, r->fork, 0);
+  if (e != cudaSuccess) {
+    r->enqueue.unlock();
+    set_error("side-stream fork failed: %s", cudaGetErrorString(e));
+    return XATTN_ERR_CUDA;
+  }
+  res_ = r;
+  side_ = r->side;
+  return XATTN_OK;
+}
+int SideFork::join() {
+  if (res_ == nullptr) return XATTN_OK;
+  SideForkRes* r = res_;
+  res_ = nullptr;
+  side_ = st_;
+  cudaError_t e = cudaEventRecord(r->join, r->side);
+  if (e == cudaSuccess) e = cudaStreamWaitEvent(st_, r->join, 0);
+  r->enqueue.unlock();
+  if (e != cudaSuccess) {
+    set_error("side-stream join failed: %s", cudaGetErrorString(e));
+    return XATTN_ERR_CUDA;
+  }
+  return XATTN_OK;
+}
+
 static std::vector<cudaEvent_t> g_stage_ev[ST_COUNT][2];
 static const char* const kStageNames[ST_COUNT] = {"gemm_v0", "gemm_a0", "video_pre", "prior", "v2a_attn", "video_update", "a2v_attn", "head"};
 

@@ -50,6 +50,29 @@ int num_sms();
 // library inserts itself (record on one stream, cudaStreamWaitEvent on another: the wait captures the record made before it).
 int device_event(int slot, cudaEvent_t* out);
 
+// Fork / join of a per-device side stream for the fp32 / tf32 kernel family (backward_f32 runs the latency-bound per-clip prior
+// backward beside HBM-bound tensor-core weight-gradient GEMMs that nothing downstream reads).  The side stream has the highest priority the device
+// offers, so its kernels' CTAs are placed first when both streams have work pending.  begin(): work enqueued on side() afterwards
+// starts after what is already on `st`; join(): `st` waits for the side work.  Stream and events are created once per device under
+// a lock and shared by every caller, so begin() .. join() holds a mutex.  Disabled (begin() leaves active() false, side() == st) by
+// XATTN_NO_FORK or while per-kernel timing brackets are on.
+struct SideForkRes;
+class SideFork {
+ public:
+  SideFork() = default;
+  ~SideFork() { join(); }
+  SideFork(const SideFork&) = delete;
+  SideFork& operator=(const SideFork&) = delete;
+  int begin(cudaStream_t st);
+  int join();
+  bool active() const { return res_ != nullptr; }
+  cudaStream_t side() const { return side_; }
+
+ private:
+  SideForkRes* res_ = nullptr;
+  cudaStream_t st_ = nullptr, side_ = nullptr;
+};
+
 // Count of kernels this library launched since process start (bench.py's gpu_launches claim).
 extern unsigned long long g_launch_count;
 inline void count_launch(int n = 1) { g_launch_count += (unsigned long long)n; }

@@ -804,6 +804,12 @@ static int forward_f32_impl(const xattn_config& c, const float* params, const TI
   linear_fwd<float>(st, ws + w.aseq, P(XP_A_IN_W), P(XP_A_IN_B), ws + w.a0, B * Ta, E, E);
   XF_LAUNCH_CHECK();
 
+  const float scale = 1.0f / sqrtf((float)(E / H));
+  // ---- video queries audio (fusion.py:394) ----
+  // (Running the prior kernel beside these two GEMMs on a side stream, as the backward does with its counterpart, was measured:
+  // no gain here — the prior CTAs reach the SMs first and hold every register until their first wave retires.)
+  linear_fwd<float>(st, ws + w.v0, P(XP_V2A_IN_W), P(XP_V2A_IN_B), ws + w.q1, B * T, E, E);
+  linear_fwd<float>(st, ws + w.a0, P(XP_V2A_IN_W) + (int64_t)E * E, P(XP_V2A_IN_B) + E, ws + w.kv1, B * Ta, 2 * E, E);
   if (c.use_prior) {
     PriorArgs pa;
     pa.v0 = ws + w.v0; pa.a0 = ws + w.a0;
@@ -826,10 +832,6 @@ static int forward_f32_impl(const xattn_config& c, const float* params, const TI
     XF_LAUNCH_CHECK();
   }
 
-  const float scale = 1.0f / sqrtf((float)(E / H));
-  // ---- video queries audio (fusion.py:394) ----
-  linear_fwd<float>(st, ws + w.v0, P(XP_V2A_IN_W), P(XP_V2A_IN_B), ws + w.q1, B * T, E, E);
-  linear_fwd<float>(st, ws + w.a0, P(XP_V2A_IN_W) + (int64_t)E * E, P(XP_V2A_IN_B) + E, ws + w.kv1, B * Ta, 2 * E, E);
   {
     AttnArgs aa;
     aa.q = ws + w.q1; aa.kv = ws + w.kv1;

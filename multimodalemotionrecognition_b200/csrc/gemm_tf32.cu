@@ -26,7 +26,7 @@ constexpr int TM = 128, TN = 128;
 constexpr int kRowBytes = 128;                    // one swizzle row: 32 fp32 or 64 bf16
 constexpr int kOpBytes = TM * kRowBytes;          // one operand tile of a stage: 16 KB
 constexpr int kStage = 2 * kOpBytes;              // 32 KB
-constexpr int kStages = 6;
+constexpr int kStages = 5;   // 160 KB of operands in flight per SM; leaves ~40 KB of shared memory for a co-resident small kernel (SideFork)
 constexpr int kAccs = 2;
 constexpr int kThreads = 64 + 128;
 constexpr int kEpiPitch = 36;                     // floats per staged row: 16-byte aligned, quarter-warp float4 accesses conflict-free

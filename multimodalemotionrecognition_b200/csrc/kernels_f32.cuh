@@ -80,6 +80,7 @@ struct BackwardOptions {
   cudaStream_t tail_stream = nullptr;   // see backward_f32_impl
   float* d_video = nullptr;             // [B,T,Dv] fp32 or nullptr
   float* d_audio = nullptr;             // [B,Ta,Da] fp32 or nullptr
+  bool fork = true;                     // the library may use its per-device side stream (SideFork)
 };
 int backward_f32(const xattn_config& c, const float* params, const void* xv, const void* xa, const float* dlogits,
                  float* grads, void* ws, cudaStream_t st, const BackwardOptions& opt = BackwardOptions());
