@@ -41,6 +41,11 @@ __device__ __forceinline__ void prefetch_l2(const float* base, int64_t bytes, in
   for (int64_t o = (int64_t)tid * 128; o < bytes; o += (int64_t)nthreads * 128) asm volatile("prefetch.global.L2 [%0];" ::"l"(p + o));
 }
 __device__ __forceinline__ float4 ldg4(const float* p) { return __ldg(reinterpret_cast<const float4*>(p)); }
+// tanh for the prior bias tile: 1 - 2 / (e^{2x} + 1) on ex2.approx / rcp.approx — absolute error < 1e-6 (the bias is an additive
+// score term next to tf32 products), exact limits ±1, six instructions instead of tanhf's ~35 with a divergent branch.  Forward and
+// backward use the same function, so (1 - t²) in the backward is the derivative of what the forward added.  (The fp32 SIMT kernels
+// keep tanhf.)
+__device__ __forceinline__ float tanh_fast(float x) { return 1.f - __fdividef(2.f, __expf(2.f * x) + 1.f); }
 
 // Fragment layouts of mma.m16n8k8 (lane = 4 g + t):
 //   A[16x8]: a0 (g, t)  a1 (g+8, t)  a2 (g, t+4)  a3 (g+8, t+4)      B[8x8]: b0 (k = t, n = g)  b1 (k = t+4, n = g)
@@ -120,20 +125,29 @@ template <typename F4, typename F1>
 __device__ __forceinline__ void for_each_with_dropout(int rows_valid, int S, int64_t base0, int64_t row_stride, float p, uint64_t seed,
                                                       uint64_t offset, uint32_t stream, int lane, F4&& fn4, F1&& fn) {
   const int G = (S + 6) >> 2;   // upper bound of the aligned groups a row can touch
-  for (int idx = lane; idx < rows_valid * G; idx += 32) {
-    const int r = idx / G, grp = idx - r * G;
+  // flat index lane, lane + 32, ... over (row, group) without a division per step: (r, grp) advance by 32 = dr·G + dg
+  const int dr = 32 / G, dg = 32 - dr * G;
+  int r = lane / G, grp = lane - r * G;
+  while (r < rows_valid) {
     const int64_t base = base0 + (int64_t)r * row_stride;
     const int rem = (int)(base & 3);
-    if (grp >= ((S + rem + 3) >> 2)) continue;
-    float f[4] = {1.f, 1.f, 1.f, 1.f};
-    if (p > 0.f) drop_factor4(p, seed, offset, stream, (uint64_t)(base - rem) + 4u * (uint64_t)grp, f);
-    const int s0 = 4 * grp - rem;
-    if (s0 >= 0 && s0 + 3 < S) {
-      fn4(r, s0, f);
-    } else {
+    if (grp < ((S + rem + 3) >> 2)) {
+      float f[4] = {1.f, 1.f, 1.f, 1.f};
+      if (p > 0.f) drop_factor4(p, seed, offset, stream, (uint64_t)(base - rem) + 4u * (uint64_t)grp, f);
+      const int s0 = 4 * grp - rem;
+      if (s0 >= 0 && s0 + 3 < S) {
+        fn4(r, s0, f);
+      } else {
 #pragma unroll
-      for (int j = 0; j < 4; ++j)
-        if (s0 + j >= 0 && s0 + j < S) fn(r, s0 + j, f[j]);
+        for (int j = 0; j < 4; ++j)
+          if (s0 + j >= 0 && s0 + j < S) fn(r, s0 + j, f[j]);
+      }
+    }
+    r += dr;
+    grp += dg;
+    if (grp >= G) {
+      grp -= G;
+      ++r;
     }
   }
 }
@@ -157,7 +171,7 @@ __global__ void __launch_bounds__(NW * 32, NW == 4 ? 4 : 2) attn_fwd_mma_kernel(
     const float* ks = a.ks + (int64_t)b * S;
     for (int i = tid; i < Lp * NT * 8; i += NW * 32) {
       const int l = i / (NT * 8), s = i - l * (NT * 8);
-      bt[l * PITCH + s] = (l < L && s < S) ? tanhf(qs[l] + ks[s]) * bscale : 0.f;
+      bt[l * PITCH + s] = (l < L && s < S) ? tanh_fast(qs[l] + ks[s]) * bscale : 0.f;
     }
     __syncthreads();
   }
@@ -307,7 +321,11 @@ __global__ void __launch_bounds__(NW * 32, NW == 4 ? 3 : 2) attn_bwd_mma_kernel(
   float* dks_acc = dqs_acc + Lp;                            // [NT*8]
   float* col_acc = dks_acc + NT * 8;                        // [3][E]: column sums of dq | dk | dv
   float* dscale_acc = col_acc + 3 * E;                      // [1] (+3 pad)
-  float* dkv_acc = dscale_acc + 4;                          // ACC: [H][NT*8][64] (dK | dV per key)
+  float* dkv_acc = dscale_acc + 4;                          // ACC: [NW / H or 1][H][NT*8][64] (dK | dV per key)
+  // NW % H == 0: a warp stays on head warp % H, and the NW / H warps of a head each own one slot of dkv_acc (plain stores, summed
+  // at the end); otherwise one slot, met by shared-memory atomics
+  const bool own_slot = ACC && (NW % H) == 0;
+  const int n_slot = own_slot ? NW / H : 1;
   const float* q = a.q + (int64_t)b * L * E;
   const float* kv = a.kv + (int64_t)b * S * 2 * E;
   const float* dO = a.dO + (int64_t)b * L * E;
@@ -318,14 +336,14 @@ __global__ void __launch_bounds__(NW * 32, NW == 4 ? 3 : 2) attn_bwd_mma_kernel(
   prefetch_l2(q, (int64_t)L * E * 4, tid, NW * 32);
   prefetch_l2(a.P + (int64_t)b * H * L * S, (int64_t)H * L * S * 4, tid, NW * 32);
   {
-    const int nacc = Lp + NT * 8 + 3 * E + 4 + (ACC ? H * NT * 8 * 64 : 0);
+    const int nacc = Lp + NT * 8 + 3 * E + 4 + (ACC ? n_slot * H * NT * 8 * 64 : 0);
     for (int i = tid; i < nacc; i += NW * 32) accs[i] = 0.f;
     if (prior) {
       const float* qs = a.qs + (int64_t)b * L;
       const float* ks = a.ks + (int64_t)b * S;
       for (int i = tid; i < Lp * NT * 8; i += NW * 32) {
         const int l = i / (NT * 8), s = i - l * (NT * 8);
-        bt[l * PITCH + s] = (l < L && s < S) ? tanhf(qs[l] + ks[s]) : 0.f;
+        bt[l * PITCH + s] = (l < L && s < S) ? tanh_fast(qs[l] + ks[s]) : 0.f;
       }
     }
     __syncthreads();
@@ -344,12 +362,24 @@ __global__ void __launch_bounds__(NW * 32, NW == 4 ? 3 : 2) attn_bwd_mma_kernel(
   auto flush = [&]() {   // this warp's sums of head cur_h -> the CTA's accumulators
     if (cur_h < 0) return;
     if (ACC) {
-      float* d0 = dkv_acc + ((int64_t)cur_h * NT * 8 + g) * 64 + 8 * t;
+      float* d0 = dkv_acc + (((int64_t)(own_slot ? warp / H : 0) * H + cur_h) * NT * 8 + g) * 64 + 8 * t;
       float* d1 = d0 + 8 * 64;
+      if (own_slot) {   // (flushed once: the head never changes)
+        *reinterpret_cast<float4*>(d0) = make_float4(dka[0][0], dka[1][0], dka[2][0], dka[3][0]);
+        *reinterpret_cast<float4*>(d0 + 4) = make_float4(dka[0][1], dka[1][1], dka[2][1], dka[3][1]);
+        *reinterpret_cast<float4*>(d0 + 32) = make_float4(dva[0][0], dva[1][0], dva[2][0], dva[3][0]);
+        *reinterpret_cast<float4*>(d0 + 36) = make_float4(dva[0][1], dva[1][1], dva[2][1], dva[3][1]);
+        *reinterpret_cast<float4*>(d1) = make_float4(dka[0][2], dka[1][2], dka[2][2], dka[3][2]);
+        *reinterpret_cast<float4*>(d1 + 4) = make_float4(dka[0][3], dka[1][3], dka[2][3], dka[3][3]);
+        *reinterpret_cast<float4*>(d1 + 32) = make_float4(dva[0][2], dva[1][2], dva[2][2], dva[3][2]);
+        *reinterpret_cast<float4*>(d1 + 36) = make_float4(dva[0][3], dva[1][3], dva[2][3], dva[3][3]);
+      }
 #pragma unroll
       for (int i = 0; i < 4; ++i) {
-        atomicAdd(d0 + i, dka[i][0]); atomicAdd(d0 + 4 + i, dka[i][1]); atomicAdd(d0 + 32 + i, dva[i][0]); atomicAdd(d0 + 36 + i, dva[i][1]);
-        atomicAdd(d1 + i, dka[i][2]); atomicAdd(d1 + 4 + i, dka[i][3]); atomicAdd(d1 + 32 + i, dva[i][2]); atomicAdd(d1 + 36 + i, dva[i][3]);
+        if (!own_slot) {
+          atomicAdd(d0 + i, dka[i][0]); atomicAdd(d0 + 4 + i, dka[i][1]); atomicAdd(d0 + 32 + i, dva[i][0]); atomicAdd(d0 + 36 + i, dva[i][1]);
+          atomicAdd(d1 + i, dka[i][2]); atomicAdd(d1 + 4 + i, dka[i][3]); atomicAdd(d1 + 32 + i, dva[i][2]); atomicAdd(d1 + 36 + i, dva[i][3]);
+        }
         dka[i][0] = dka[i][1] = dka[i][2] = dka[i][3] = dva[i][0] = dva[i][1] = dva[i][2] = dva[i][3] = 0.f;
       }
     }
@@ -604,7 +634,11 @@ __global__ void __launch_bounds__(NW * 32, NW == 4 ? 3 : 2) attn_bwd_mma_kernel(
   if (ACC) {   // dK | dV of the clip, summed over its query tiles
     for (int i = tid; i < H * S * 16; i += NW * 32) {   // float4 pieces: [h][key][16 pieces of 4]
       const int piece = i & 15, key = (i >> 4) % S, h = (i >> 4) / S;
-      const float4 v = *reinterpret_cast<const float4*>(dkv_acc + ((int64_t)h * NT * 8 + key) * 64 + 4 * piece);
+      float4 v = *reinterpret_cast<const float4*>(dkv_acc + ((int64_t)h * NT * 8 + key) * 64 + 4 * piece);
+      for (int sl = 1; sl < n_slot; ++sl) {
+        const float4 u = *reinterpret_cast<const float4*>(dkv_acc + (((int64_t)sl * H + h) * NT * 8 + key) * 64 + 4 * piece);
+        v.x += u.x; v.y += u.y; v.z += u.z; v.w += u.w;
+      }
       float* dst = a.dkv + ((int64_t)b * S + key) * 2 * E + (piece >= 8 ? E : 0) + h * 32 + 4 * (piece & 7);
       *reinterpret_cast<float4*>(dst) = v;
     }
@@ -631,7 +665,7 @@ template <int NT, int NW, bool ACC>
 size_t bwd_smem(int L, int E, int H, bool prior) {
   const int pitch = NT * 8 + 4, Lp = ((L + 15) / 16) * 16;
   return sizeof(float) * ((prior ? (size_t)Lp * pitch : 0) + (size_t)NW * 16 * pitch + Lp + NT * 8 + 3 * E + 4 +
-                          (ACC ? (size_t)H * NT * 8 * 64 : 0));
+                          (ACC ? (size_t)(NW % H == 0 ? NW / H : 1) * H * NT * 8 * 64 : 0));
 }
 
 template <typename K>
