@@ -245,31 +245,32 @@ __global__ void __launch_bounds__(NW * 32, NW == 4 ? 4 : 2) attn_fwd_mma_kernel(
     // save P (before dropout) for the backward — with the dropout decision in its sign: +P kept, -P dropped (P >= 0, -0 counts
     // as dropped), so the backward regenerates no Philox mask — and apply the mask to the tile in place
     const int rows_valid = min(16, L - m0);
-    const int64_t base0 = (((int64_t)b * H + h) * L + m0) * S;
+    const int ldp = a.ldp > 0 ? a.ldp : S;   // row stride of P = the index space of the Philox draws (a multiple of 4 under tf32)
+    const int64_t base0 = (((int64_t)b * H + h) * L + m0) * ldp;
     if (a.P != nullptr || a.p_drop > 0.f) {
-      const bool vec = (S & 3) == 0 && (reinterpret_cast<uintptr_t>(a.P) & 15) == 0;   // rows start on 16-byte boundaries
+      const bool vec = (ldp & 3) == 0 && (reinterpret_cast<uintptr_t>(a.P) & 15) == 0;   // rows start on 16-byte boundaries
       for_each_with_dropout(
-          rows_valid, S, base0, S, a.p_drop, a.seed, a.offset, a.rng_stream, lane,
+          rows_valid, S, base0, ldp, a.p_drop, a.seed, a.offset, a.rng_stream, lane,
           [&](int r, int s, const float(&f)[4]) {
             float* pp = ps + r * PITCH + s;
             if (vec) {   // (s % 4 == 0 then, and the tile pitch keeps rows 16-byte aligned)
               const float4 pv = *reinterpret_cast<const float4*>(pp);
               if (a.P != nullptr)
-                *reinterpret_cast<float4*>(a.P + base0 + (int64_t)r * S + s) =
+                *reinterpret_cast<float4*>(a.P + base0 + (int64_t)r * ldp + s) =
                     make_float4(f[0] > 0.f ? pv.x : -pv.x, f[1] > 0.f ? pv.y : -pv.y, f[2] > 0.f ? pv.z : -pv.z, f[3] > 0.f ? pv.w : -pv.w);
               *reinterpret_cast<float4*>(pp) = make_float4(pv.x * f[0], pv.y * f[1], pv.z * f[2], pv.w * f[3]);
             } else {
 #pragma unroll
               for (int j = 0; j < 4; ++j) {
                 const float pj = pp[j];
-                if (a.P != nullptr) a.P[base0 + (int64_t)r * S + s + j] = f[j] > 0.f ? pj : -pj;
+                if (a.P != nullptr) a.P[base0 + (int64_t)r * ldp + s + j] = f[j] > 0.f ? pj : -pj;
                 pp[j] = pj * f[j];
               }
             }
           },
           [&](int r, int s, float f) {
             const float pj = ps[r * PITCH + s];
-            if (a.P != nullptr) a.P[base0 + (int64_t)r * S + s] = f > 0.f ? pj : -pj;
+            if (a.P != nullptr) a.P[base0 + (int64_t)r * ldp + s] = f > 0.f ? pj : -pj;
             ps[r * PITCH + s] = pj * f;
           });
       __syncwarp();
@@ -334,7 +335,7 @@ __global__ void __launch_bounds__(NW * 32, NW == 4 ? 3 : 2) attn_bwd_mma_kernel(
   prefetch_l2(kv, (int64_t)S * 2 * E * 4, tid, NW * 32);
   prefetch_l2(dO, (int64_t)L * E * 4, tid, NW * 32);
   prefetch_l2(q, (int64_t)L * E * 4, tid, NW * 32);
-  prefetch_l2(a.P + (int64_t)b * H * L * S, (int64_t)H * L * S * 4, tid, NW * 32);
+  prefetch_l2(a.P + (int64_t)b * H * L * (a.ldp > 0 ? a.ldp : S), (int64_t)H * L * (a.ldp > 0 ? a.ldp : S) * 4, tid, NW * 32);
   {
     const int nacc = Lp + NT * 8 + 3 * E + 4 + (ACC ? n_slot * H * NT * 8 * 64 : 0);
     for (int i = tid; i < nacc; i += NW * 32) accs[i] = 0.f;
@@ -422,22 +423,32 @@ __global__ void __launch_bounds__(NW * 32, NW == 4 ? 3 : 2) attn_bwd_mma_kernel(
     const int r0 = m0 + g, r1 = r0 + 8;
     const bool ok0 = r0 < L, ok1 = r1 < L;
     const int rows_valid = min(16, L - m0);
-    const int64_t base0 = (((int64_t)b * H + h) * L + m0) * S;
+    const int ldp = a.ldp > 0 ? a.ldp : S;
+    const int64_t base0 = (((int64_t)b * H + h) * L + m0) * ldp;
     // ---- ±P (sign = dropout decision, written by the forward) starts its way into the tile: asynchronous copies that land while
     //      the dPd products below are issued; rows / keys past the end are zero ----
     __syncwarp();   // the previous item's products have finished reading the tile
     {
       const float* pg = a.P + base0;
-      if ((S & 3) == 0 && (reinterpret_cast<uintptr_t>(a.P) & 15) == 0) {
-        for (int i = lane; i < 16 * NT * 2; i += 32) {   // 16-byte pieces
+      if ((ldp & 3) == 0 && (reinterpret_cast<uintptr_t>(a.P) & 15) == 0) {
+        for (int i = lane; i < 16 * NT * 2; i += 32) {   // 16-byte pieces; the last piece of a row may straddle S (padding is not P)
           const int r = i / (NT * 2), s4 = (i - r * (NT * 2)) * 4;
-          if (r < rows_valid && s4 < S) cp_async16(ps + r * PITCH + s4, pg + (int64_t)r * S + s4);
-          else *reinterpret_cast<float4*>(ps + r * PITCH + s4) = make_float4(0.f, 0.f, 0.f, 0.f);
+          float* dst = ps + r * PITCH + s4;
+          const float* src = pg + (int64_t)r * ldp + s4;
+          if (r < rows_valid && s4 + 3 < S) {
+            cp_async16(dst, src);
+          } else {
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+              if (r < rows_valid && s4 + j < S) cp_async4(dst + j, src + j);
+              else dst[j] = 0.f;
+            }
+          }
         }
       } else {
         for (int i = lane; i < 16 * NT * 8; i += 32) {
           const int r = i / (NT * 8), s1 = i - r * (NT * 8);
-          if (r < rows_valid && s1 < S) cp_async4(ps + r * PITCH + s1, pg + (int64_t)r * S + s1);
+          if (r < rows_valid && s1 < S) cp_async4(ps + r * PITCH + s1, pg + (int64_t)r * ldp + s1);
           else ps[r * PITCH + s1] = 0.f;
         }
       }

@@ -1266,7 +1266,7 @@ static int backward_f32_impl(const xattn_config& c, const float* params, const T
     aa.dq = ws + w.d_q2; aa.dkv = ws + w.d_kv2; aa.dqs = ws + w.d_qa; aa.dks = ws + w.d_kvs;
     aa.dbias_scale = c.use_prior ? G(XP_BIAS_SCALE) : nullptr;
     aa.L = Ta; aa.S = T; aa.E = E; aa.H = H; aa.scale = scale; aa.p_drop = p_attn; aa.seed = c.seed; aa.offset = c.offset;
-    aa.rng_stream = RS_ATTN2;
+    aa.rng_stream = RS_ATTN2; aa.ldp = p_row_stride(c, T);
     aa.dbq = G(XP_A2V_IN_B); aa.dbkv = G(XP_A2V_IN_B) + E;
     XF_TRY(launch_attn_bwd(st, aa, B, &bias_fused));
   }
@@ -1298,7 +1298,7 @@ static int backward_f32_impl(const xattn_config& c, const float* params, const T
     aa.dq = ws + w.d_q1; aa.dkv = ws + w.d_kv1; aa.dqs = ws + w.d_qv; aa.dks = ws + w.d_ka;
     aa.dbias_scale = c.use_prior ? G(XP_BIAS_SCALE) : nullptr;
     aa.L = T; aa.S = Ta; aa.E = E; aa.H = H; aa.scale = scale; aa.p_drop = p_attn; aa.seed = c.seed; aa.offset = c.offset;
-    aa.rng_stream = RS_ATTN1;
+    aa.rng_stream = RS_ATTN1; aa.ldp = p_row_stride(c, Ta);
     aa.dbq = G(XP_V2A_IN_B); aa.dbkv = G(XP_V2A_IN_B) + E;
     XF_TRY(launch_attn_bwd(st, aa, B, &bias_fused));
   }

@@ -285,10 +285,10 @@ void compute_ws_f32(const xattn_config& c, WsF32& w) {
   };
   w.v0 = take(B * T * E); w.aseq = take(B * Ta * E); w.a0 = take(B * Ta * E);
   w.q1 = take(B * T * E); w.kv1 = take(B * Ta * 2 * E);
-  w.p1 = bwd ? take(B * H * T * Ta) : 0;
+  w.p1 = bwd ? take(B * H * T * p_row_stride(c, c.Ta)) : 0;
   w.o1 = take(B * T * E); w.s1 = take(B * T * E); w.mean1 = take(B * T); w.rstd1 = take(B * T); w.v1 = take(B * T * E);
   w.q2 = take(B * Ta * E); w.kv2 = take(B * T * 2 * E);
-  w.p2 = bwd ? take(B * H * Ta * T) : 0;
+  w.p2 = bwd ? take(B * H * Ta * p_row_stride(c, c.T)) : 0;
   w.o2 = take(B * Ta * E); w.s2 = take(B * Ta * E); w.mean2 = take(B * Ta); w.rstd2 = take(B * Ta); w.a1 = take(B * Ta * E);
   w.pooled0 = take(B * 2 * E); w.phid = take(B * Hd); w.prior = take(B * P);
   w.qv = take(B * T); w.ka = take(B * Ta); w.qa = take(B * Ta); w.kvs = take(B * T);

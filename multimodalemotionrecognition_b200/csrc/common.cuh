@@ -134,6 +134,10 @@ struct ParamLayout {
   int count;   // ids in use: XP_COUNT + 24 per transformer-pooler layer beyond the first
 };
 inline int pool_layers(const xattn_config& c) { return c.pool_layers > 0 ? c.pool_layers : 1; }
+// Row stride (floats) of the saved attention probabilities P [B,H,L,stride]: S, rounded up to 4 under precision = TF32 so that the
+// tensor-core attention kernels move whole 16-byte pieces of a row (S = 149 audio keys -> 152).  The fp32 SIMT kernels always
+// use S (inside the same buffer when they stand in under TF32).
+inline int p_row_stride(const xattn_config& c, int S) { return c.precision == XATTN_PREC_TF32 ? (S + 3) & ~3 : S; }
 void compute_param_layout(const xattn_config& c, ParamLayout& L);
 
 // ---- fp32 workspace layout (activations saved for backward; floats) -------------------------------

@@ -839,7 +839,7 @@ static int forward_f32_impl(const xattn_config& c, const float* params, const TI
     aa.bias_scale = c.use_prior ? P(XP_BIAS_SCALE) : nullptr;
     aa.P = save ? ws + w.p1 : nullptr; aa.O = ws + w.o1;
     aa.L = T; aa.S = Ta; aa.E = E; aa.H = H; aa.scale = scale;
-    aa.p_drop = p_attn; aa.seed = c.seed; aa.offset = c.offset; aa.rng_stream = RS_ATTN1;
+    aa.p_drop = p_attn; aa.seed = c.seed; aa.offset = c.offset; aa.rng_stream = RS_ATTN1; aa.ldp = p_row_stride(c, Ta);
     XF_TRY(launch_attn_fwd(st, aa, B));
   }
   linear_fwd<float>(st, ws + w.o1, P(XP_V2A_OUT_W), P(XP_V2A_OUT_B), ws + w.s1, B * T, E, E);
@@ -859,7 +859,7 @@ static int forward_f32_impl(const xattn_config& c, const float* params, const TI
     aa.bias_scale = c.use_prior ? P(XP_BIAS_SCALE) : nullptr;
     aa.P = save ? ws + w.p2 : nullptr; aa.O = ws + w.o2;
     aa.L = Ta; aa.S = T; aa.E = E; aa.H = H; aa.scale = scale;
-    aa.p_drop = p_attn; aa.seed = c.seed; aa.offset = c.offset; aa.rng_stream = RS_ATTN2;
+    aa.p_drop = p_attn; aa.seed = c.seed; aa.offset = c.offset; aa.rng_stream = RS_ATTN2; aa.ldp = p_row_stride(c, T);
     XF_TRY(launch_attn_fwd(st, aa, B));
   }
   linear_fwd<float>(st, ws + w.o2, P(XP_A2V_OUT_W), P(XP_A2V_OUT_B), ws + w.s2, B * Ta, E, E);

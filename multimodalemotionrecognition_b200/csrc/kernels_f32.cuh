@@ -23,6 +23,7 @@ struct AttnArgs {
   const float* ks;       // [B,S]
   const float* bias_scale;
   float* P;              // [B,H,L,S] softmax probabilities (pre-dropout) or nullptr
+  int ldp = 0;           // row stride of P for the tensor-core kernels (attn_mma.cu; 0 = S); the SIMT kernels always use S
   float* O;              // [B,L,E]
   int L, S, E, H;
   float scale, p_drop;
@@ -32,6 +33,7 @@ struct AttnArgs {
 
 struct AttnBwdArgs {
   const float *q, *kv, *qs, *ks, *bias_scale, *P;
+  int ldp = 0;           // as AttnArgs::ldp
   const float* dO;       // [B,L,E]
   float* dq;             // [B,L,E]
   float* dkv;            // [B,S,2E]

@@ -62,15 +62,17 @@ def digest(t) -> np.ndarray:
 
 
 def ws_f32_views(ws: torch.Tensor, cfg) -> dict:
-    """Typed views of the fp32 / tf32 workspace (mirror of compute_ws_f32, csrc/common.cu): name -> float32 tensor (device)."""
+    """Typed views of the fp32 / tf32 workspace (mirror of compute_ws_f32, csrc/common.cu): name -> float32 tensor (device).
+    Under tf32 the rows of p1 / p2 are padded to a multiple of 4 keys (only [..., :S] is written)."""
     B, T, Ta, E, H = cfg.B, cfg.T, cfg.Ta, cfg.E, cfg.H
     P = max(cfg.prior_dim, 1)
     Hd = max(cfg.prior_hidden, 1)
     HW = E if cfg.head_kind == 1 else cfg.common_dim
     bwd = bool(cfg.training or cfg.save_for_backward)
+    pad = (lambda n: (n + 3) & ~3) if cfg.precision == 2 else (lambda n: n)   # P row stride under tf32 (p_row_stride, common.cuh)
     spec = [("v0", (B, T, E)), ("aseq", (B, Ta, E)), ("a0", (B, Ta, E)), ("q1", (B, T, E)), ("kv1", (B, Ta, 2 * E)),
-            ("p1", (B, H, T, Ta) if bwd else None), ("o1", (B, T, E)), ("s1", (B, T, E)), ("mean1", (B, T)), ("rstd1", (B, T)),
-            ("v1", (B, T, E)), ("q2", (B, Ta, E)), ("kv2", (B, T, 2 * E)), ("p2", (B, H, Ta, T) if bwd else None),
+            ("p1", (B, H, T, pad(Ta)) if bwd else None), ("o1", (B, T, E)), ("s1", (B, T, E)), ("mean1", (B, T)), ("rstd1", (B, T)),
+            ("v1", (B, T, E)), ("q2", (B, Ta, E)), ("kv2", (B, T, 2 * E)), ("p2", (B, H, Ta, pad(T)) if bwd else None),
             ("o2", (B, Ta, E)), ("s2", (B, Ta, E)), ("mean2", (B, Ta)), ("rstd2", (B, Ta)), ("a1", (B, Ta, E)),
             ("pooled0", (B, 2 * E)), ("phid", (B, Hd)), ("prior", (B, P)), ("qv", (B, T)), ("ka", (B, Ta)), ("qa", (B, Ta)),
             ("kvs", (B, T)), ("pooled", (B, 2 * E)), ("hhid", (B, HW)), ("gate", (B,)), ("fusedg", (B, E)), ("dp1", (B,)),
