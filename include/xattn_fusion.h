@@ -26,7 +26,7 @@
 extern "C" {
 #endif
 
-#define XATTN_ABI_VERSION 18
+#define XATTN_ABI_VERSION 19
 
 #if defined(__GNUC__)
 #define XATTN_API __attribute__((visibility("default")))
@@ -252,6 +252,37 @@ XATTN_API int xattn_ce_loss_fwd_bwd(const float* logits, const int64_t* labels, 
 XATTN_API int xattn_adam_step(float* params, const float* grads, float* exp_avg, float* exp_avg_sq, int64_t n, float lr,
                     float beta1, float beta2, float eps, float weight_decay, int32_t step, int32_t decoupled,
                     void* stream);
+
+/* One whole Stage-1 step in ONE call: xattn_forward (cfg as given: training / save_for_backward, precision f32 or tf32) ->
+ * xattn_ce_loss_fwd_bwd -> xattn_backward -> xattn_adam_step, the loop body of train_one_epoch (train.py:204-228) for one rank.
+ * use_graph != 0: the launches of the step are stream-captured and run as one CUDA graph (the ~58 kernels of a step are 10-60 us
+ * each: replayed as a graph the gaps between them go, 1.73 -> 1.62 ms at B=1024).  The Philox offset and the Adam step count are
+ * kernel arguments, so every call re-captures (host work only, ~0.3 ms, overlapping the previous step's GPU time) and UPDATES the
+ * cached executable graph in place (cudaGraphExecUpdate: same topology, new arguments); it is re-instantiated only when the
+ * topology changes (another B, another config).  One cached graph per device; calls on a device are serialised by a mutex.
+ * All buffers are the caller's (nothing is allocated): logits [B,C], loss [1], dlogits [B,C], grads / exp_avg / exp_avg_sq
+ * [xattn_param_layout total], workspace as xattn_workspace_bytes(cfg).  Data-parallel training keeps the separate calls
+ * (the gradient all-reduce sits between backward and Adam). */
+typedef struct xattn_step_args {
+  const xattn_config* cfg;
+  float* params;
+  const void* video_emb;
+  const void* audio_emb;
+  const int64_t* labels;
+  float* logits;
+  float* loss;
+  float* dlogits;
+  float* grads;
+  float* exp_avg;
+  float* exp_avg_sq;
+  void* workspace;
+  int64_t workspace_bytes;
+  float lr, beta1, beta2, eps, weight_decay, label_smoothing;
+  int32_t step;       /* 1-based Adam step */
+  int32_t decoupled;  /* 0: torch.optim.Adam(weight_decay), 1: AdamW */
+  int32_t use_graph;
+} xattn_step_args;
+XATTN_API int xattn_stage1_step(const xattn_step_args* args, void* stream);
 
 /* ---- flat concat / gated heads (BASELINE config 5) -------------------------------------------- */
 typedef struct flat_head_config {

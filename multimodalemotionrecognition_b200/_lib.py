@@ -13,7 +13,7 @@ from pathlib import Path
 LIB_NAME = "libxattn_fusion.so"
 LIB_PATH = Path(__file__).resolve().parent / LIB_NAME
 DEBUG_LIB_PATH = Path(__file__).resolve().parent / "libxattn_fusion_debug.so"
-ABI_VERSION = 18
+ABI_VERSION = 19
 
 # xattn_status
 OK, ERR_SHAPE, ERR_DTYPE, ERR_ALIGN, ERR_ARCH, ERR_CUDA, ERR_WORKSPACE, ERR_NULL = range(8)
@@ -84,6 +84,15 @@ class XAttnConfig(C.Structure):
         ("seed", C.c_uint64), ("offset", C.c_uint64)]
 
 
+class XAttnStepArgs(C.Structure):
+    """include/xattn_fusion.h: struct xattn_step_args (xattn_stage1_step)."""
+    _fields_ = [("cfg", C.POINTER(XAttnConfig)), ("params", C.c_void_p), ("video_emb", C.c_void_p), ("audio_emb", C.c_void_p),
+                ("labels", C.c_void_p), ("logits", C.c_void_p), ("loss", C.c_void_p), ("dlogits", C.c_void_p), ("grads", C.c_void_p),
+                ("exp_avg", C.c_void_p), ("exp_avg_sq", C.c_void_p), ("workspace", C.c_void_p), ("workspace_bytes", C.c_int64),
+                ("lr", C.c_float), ("beta1", C.c_float), ("beta2", C.c_float), ("eps", C.c_float), ("weight_decay", C.c_float),
+                ("label_smoothing", C.c_float), ("step", C.c_int32), ("decoupled", C.c_int32), ("use_graph", C.c_int32)]
+
+
 class FlatHeadConfig(C.Structure):
     _fields_ = [(n, C.c_int32) for n in ("B", "T", "Ta", "Dv", "Da", "align_dim", "common_dim", "C", "gated", "io_dtype",
                                                  "precision")]
@@ -111,6 +120,7 @@ _EXPORTS = {
                                  C.c_void_p, C.c_int64, C.c_void_p]),
     "xattn_backward_ex": (C.c_int, [C.POINTER(XAttnConfig), C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
                                     C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.POINTER(C.c_int64), C.c_void_p, C.c_void_p]),
+    "xattn_stage1_step": (C.c_int, [C.POINTER(XAttnStepArgs), C.c_void_p]),
     "xattn_ce_loss_fwd_bwd": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_float, C.c_float, C.c_void_p,
                                         C.c_void_p, C.c_void_p]),
     "xattn_adam_step": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_float, C.c_float,

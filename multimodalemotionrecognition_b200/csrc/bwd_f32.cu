@@ -1307,8 +1307,8 @@ static int backward_f32_impl(const xattn_config& c, const float* params, const T
   linear_bwd_dx(st, ws + w.d_kv1, 2 * E, P(XP_V2A_IN_W) + (int64_t)E * E, ws + w.d_a0, B * Ta, 2 * E, E, true);
   // ... then its weight gradients (HBM-bound tensor-core GEMMs nothing downstream reads) on the high-priority side stream under
   // tf32, beside the latency-bound per-clip prior backward on `st`
-  SideFork sf;
-  if (opt.fork && c.use_prior && g_tc_gemm) XF_TRY(sf.begin(st));
+  SideFork sf(st);
+  if (opt.fork && c.use_prior && g_tc_gemm) XF_TRY(sf.begin());
   linear_bwd_dw<float>(sf.side(), ws + w.d_q1, E, ws + w.v0, E, G(XP_V2A_IN_W), B * T, E, E);
   if (!bias_fused) launch_colsum(sf.side(), ws + w.d_q1, E, B * T, E, G(XP_V2A_IN_B));
   linear_bwd_dw<float>(sf.side(), ws + w.d_kv1, 2 * E, ws + w.a0, E, G(XP_V2A_IN_W) + (int64_t)E * E, B * Ta, 2 * E, E);

@@ -27,13 +27,12 @@ struct SideForkRes {
   cudaEvent_t fork = nullptr, join = nullptr;
   std::mutex enqueue;
 };
-int SideFork::begin(cudaStream_t st) {
+int SideFork::begin() {
   static SideForkRes res[64];
   static std::mutex mu;
   static const bool off = getenv("XATTN_NO_FORK") != nullptr;
-  st_ = st;
-  side_ = st;
-  if (off || g_stage_timing) return XATTN_OK;
+  cudaStream_t st = st_;
+  if (off || g_stage_timing || res_ != nullptr) return XATTN_OK;
   int dev = 0;
   XF_CUDA(cudaGetDevice(&dev));
   if (dev < 0 || dev >= 64) XF_FAIL(XATTN_ERR_CUDA, "device index %d out of range", dev);

@@ -59,11 +59,11 @@ int device_event(int slot, cudaEvent_t* out);
 struct SideForkRes;
 class SideFork {
  public:
-  SideFork() = default;
+  explicit SideFork(cudaStream_t st) : st_(st), side_(st) {}   // until begin() succeeds side() IS the caller's stream
   ~SideFork() { join(); }
   SideFork(const SideFork&) = delete;
   SideFork& operator=(const SideFork&) = delete;
-  int begin(cudaStream_t st);
+  int begin();
   int join();
   bool active() const { return res_ != nullptr; }
   cudaStream_t side() const { return side_; }
