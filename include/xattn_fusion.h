@@ -26,7 +26,7 @@
 extern "C" {
 #endif
 
-#define XATTN_ABI_VERSION 19
+#define XATTN_ABI_VERSION 20
 
 #if defined(__GNUC__)
 #define XATTN_API __attribute__((visibility("default")))
@@ -261,8 +261,8 @@ XATTN_API int xattn_adam_step(float* params, const float* grads, float* exp_avg,
  * cached executable graph in place (cudaGraphExecUpdate: same topology, new arguments); it is re-instantiated only when the
  * topology changes (another B, another config).  One cached graph per device; calls on a device are serialised by a mutex.
  * All buffers are the caller's (nothing is allocated): logits [B,C], loss [1], dlogits [B,C], grads / exp_avg / exp_avg_sq
- * [xattn_param_layout total], workspace as xattn_workspace_bytes(cfg).  Data-parallel training keeps the separate calls
- * (the gradient all-reduce sits between backward and Adam). */
+ * [xattn_param_layout total], workspace as xattn_workspace_bytes(cfg).  Data-parallel training splits the step at the
+ * gradient all-reduce (phase 1 / phase 2 below) and runs Adam through xattn_adam_step. */
 typedef struct xattn_step_args {
   const xattn_config* cfg;
   float* params;
@@ -281,6 +281,11 @@ typedef struct xattn_step_args {
   int32_t step;       /* 1-based Adam step */
   int32_t decoupled;  /* 0: torch.optim.Adam(weight_decay), 1: AdamW */
   int32_t use_graph;
+  int32_t phase;      /* 0: the whole step.  Data parallel: 1 = forward + CE + the backward up to the point where every gradient
+                         but the input projections' (the flat buffer from XP_V2A_IN_W on) is final; 2 = the input-projection
+                         backward.  The caller all-reduces the tail bucket on another stream after phase 1, beside phase 2, then
+                         the head bucket, then calls xattn_adam_step.  One cached graph per device and phase. */
+  float grad_scale;   /* multiplies dlogits: 1 / world_size under data parallelism (0 reads as 1) */
 } xattn_step_args;
 XATTN_API int xattn_stage1_step(const xattn_step_args* args, void* stream);
 

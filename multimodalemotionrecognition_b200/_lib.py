@@ -13,7 +13,7 @@ from pathlib import Path
 LIB_NAME = "libxattn_fusion.so"
 LIB_PATH = Path(__file__).resolve().parent / LIB_NAME
 DEBUG_LIB_PATH = Path(__file__).resolve().parent / "libxattn_fusion_debug.so"
-ABI_VERSION = 19
+ABI_VERSION = 20
 
 # xattn_status
 OK, ERR_SHAPE, ERR_DTYPE, ERR_ALIGN, ERR_ARCH, ERR_CUDA, ERR_WORKSPACE, ERR_NULL = range(8)
@@ -90,7 +90,8 @@ class XAttnStepArgs(C.Structure):
                 ("labels", C.c_void_p), ("logits", C.c_void_p), ("loss", C.c_void_p), ("dlogits", C.c_void_p), ("grads", C.c_void_p),
                 ("exp_avg", C.c_void_p), ("exp_avg_sq", C.c_void_p), ("workspace", C.c_void_p), ("workspace_bytes", C.c_int64),
                 ("lr", C.c_float), ("beta1", C.c_float), ("beta2", C.c_float), ("eps", C.c_float), ("weight_decay", C.c_float),
-                ("label_smoothing", C.c_float), ("step", C.c_int32), ("decoupled", C.c_int32), ("use_graph", C.c_int32)]
+                ("label_smoothing", C.c_float), ("step", C.c_int32), ("decoupled", C.c_int32), ("use_graph", C.c_int32),
+                ("phase", C.c_int32), ("grad_scale", C.c_float)]
 
 
 class FlatHeadConfig(C.Structure):

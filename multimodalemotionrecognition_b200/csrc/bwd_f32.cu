@@ -1136,219 +1136,224 @@ static int backward_f32_impl(const xattn_config& c, const float* params, const T
   const float scale = 1.0f / sqrtf((float)(E / H));
 
   NvtxRange nvtx_bwd(g_tc_gemm ? "xattn_backward[tf32]" : "xattn_backward[fp32]");
-  XF_CUDA(cudaMemsetAsync(grads, 0, sizeof(float) * pl.total, st));
+  // d_v0 / d_a0 are final in the prior backward kernels' float4 paths: they leave the column sums in the two bias gradients
+  const bool tok_bias_fused =
+      c.use_prior && ((E == 128 && sizeof(float) * (2 * E + 8 * E + 2 * (T + Ta) + 4 + c.prior_dim + c.prior_hidden) <= 48 * 1024) ||
+                      (E % 4 == 0 && sizeof(float) * (4 + c.prior_dim + c.prior_hidden + 2 * E + 2 * (T + Ta) + 8 * 6 * E) <= 48 * 1024));
+  // opt.phase: 0 = the whole backward; 1 = up to the point where every gradient but the input projections' is final; 2 = the
+  // input projections only (after a phase-1 call on the same workspace and gradient buffer)
+  if (opt.phase != 2) {
+    XF_CUDA(cudaMemsetAsync(grads, 0, sizeof(float) * pl.total, st));
 
-  // ---- head (fusion.py:405-411) ----
-  if (!gated) {
-    linear_bwd_dw<float>(st, dlogits, C, ws + w.hhid, HW, G(XP_HEAD1_W), B, C, HW);
-    launch_colsum(st, dlogits, C, B, C, G(XP_HEAD1_B));
-    head_bwd_mid_kernel<<<B, 256, 0, st>>>(dlogits, P(XP_HEAD1_W), ws + w.hhid, nullptr, nullptr, nullptr, ws + w.d_hh, nullptr,
-                                           nullptr, E, HW, C, 0, 1.f / (1.f - p_head));
-    count_launch();
-    linear_bwd_dw<float>(st, ws + w.d_hh, HW, ws + w.pooled, 2 * E, G(XP_HEAD0_W), B, HW, 2 * E);
-    launch_colsum(st, ws + w.d_hh, HW, B, HW, G(XP_HEAD0_B));
-    linear_bwd_dx(st, ws + w.d_hh, HW, P(XP_HEAD0_W), ws + w.d_pooled, B, HW, 2 * E, false);
-  } else {
-    linear_bwd_dw<float>(st, dlogits, C, ws + w.fusedg, E, G(XP_CLS_W), B, C, E);
-    launch_colsum(st, dlogits, C, B, C, G(XP_CLS_B));
-    linear_bwd_dx(st, dlogits, C, P(XP_CLS_W), ws + w.d_fused, B, C, E, false);
-    head_bwd_mid_kernel<<<B, 256, 0, st>>>(nullptr, P(XP_HEAD1_W), ws + w.hhid, ws + w.pooled, ws + w.gate, ws + w.d_fused,
-                                           ws + w.d_hh, ws + w.d_pooled, ws + w.d_z, E, HW, C, 1, 1.f / (1.f - p_head));
-    count_launch();
-    linear_bwd_dw<float>(st, ws + w.d_z, 1, ws + w.hhid, HW, G(XP_HEAD1_W), B, 1, HW);
-    launch_colsum(st, ws + w.d_z, 1, B, 1, G(XP_HEAD1_B));
-    linear_bwd_dw<float>(st, ws + w.d_hh, HW, ws + w.pooled, 2 * E, G(XP_HEAD0_W), B, HW, 2 * E);
-    launch_colsum(st, ws + w.d_hh, HW, B, HW, G(XP_HEAD0_B));
-    linear_bwd_dx(st, ws + w.d_hh, HW, P(XP_HEAD0_W), ws + w.d_pooled, B, HW, 2 * E, true);
-  }
-  XF_LAUNCH_CHECK();
+    // ---- head (fusion.py:405-411) ----
+    if (!gated) {
+      linear_bwd_dw<float>(st, dlogits, C, ws + w.hhid, HW, G(XP_HEAD1_W), B, C, HW);
+      launch_colsum(st, dlogits, C, B, C, G(XP_HEAD1_B));
+      head_bwd_mid_kernel<<<B, 256, 0, st>>>(dlogits, P(XP_HEAD1_W), ws + w.hhid, nullptr, nullptr, nullptr, ws + w.d_hh, nullptr,
+                                             nullptr, E, HW, C, 0, 1.f / (1.f - p_head));
+      count_launch();
+      linear_bwd_dw<float>(st, ws + w.d_hh, HW, ws + w.pooled, 2 * E, G(XP_HEAD0_W), B, HW, 2 * E);
+      launch_colsum(st, ws + w.d_hh, HW, B, HW, G(XP_HEAD0_B));
+      linear_bwd_dx(st, ws + w.d_hh, HW, P(XP_HEAD0_W), ws + w.d_pooled, B, HW, 2 * E, false);
+    } else {
+      linear_bwd_dw<float>(st, dlogits, C, ws + w.fusedg, E, G(XP_CLS_W), B, C, E);
+      launch_colsum(st, dlogits, C, B, C, G(XP_CLS_B));
+      linear_bwd_dx(st, dlogits, C, P(XP_CLS_W), ws + w.d_fused, B, C, E, false);
+      head_bwd_mid_kernel<<<B, 256, 0, st>>>(nullptr, P(XP_HEAD1_W), ws + w.hhid, ws + w.pooled, ws + w.gate, ws + w.d_fused,
+                                             ws + w.d_hh, ws + w.d_pooled, ws + w.d_z, E, HW, C, 1, 1.f / (1.f - p_head));
+      count_launch();
+      linear_bwd_dw<float>(st, ws + w.d_z, 1, ws + w.hhid, HW, G(XP_HEAD1_W), B, 1, HW);
+      launch_colsum(st, ws + w.d_z, 1, B, 1, G(XP_HEAD1_B));
+      linear_bwd_dw<float>(st, ws + w.d_hh, HW, ws + w.pooled, 2 * E, G(XP_HEAD0_W), B, HW, 2 * E);
+      launch_colsum(st, ws + w.d_hh, HW, B, HW, G(XP_HEAD0_B));
+      linear_bwd_dx(st, ws + w.d_hh, HW, P(XP_HEAD0_W), ws + w.d_pooled, B, HW, 2 * E, true);
+    }
+    XF_LAUNCH_CHECK();
 
-  const int ln_grid = 4 * num_sms();
-  bool bias_fused = false;
-  const bool attn_pool = c.pool_mode == XATTN_POOL_ATTN;
-  const int H2 = E / 2 > 0 ? E / 2 : 1;
-  const float p_pool = train ? c.p_pool : 0.f;
-  // learned pooling (temporal.py:9-26): token gradients from attn_pool_bwd_kernel instead of d_pooled/L; its W1 / b1 gradients as
-  // a batch GEMM / column sum over the y and d_h rows it wrote into two buffers that are still free at that point
-  auto pool_bwd = [&](const float* x, const float* d_out, float* d_x, bool accumulate, float* y_buf, float* dh_buf, int L, int first_id,
-                      uint32_t stream) -> int {
-    AttnPoolBwdArgs pa;
-    pa.x = x; pa.ln_w = P(first_id); pa.ln_b = P(first_id + 1); pa.w1 = P(first_id + 2); pa.b1 = P(first_id + 3);
-    pa.w2 = P(first_id + 4); pa.b2 = P(first_id + 5);
-    pa.d_out = d_out; pa.ld_out = 2 * E; pa.d_x = d_x; pa.accumulate = accumulate ? 1 : 0; pa.y_out = y_buf; pa.dh_out = dh_buf;
-    pa.g_ln_w = G(first_id); pa.g_ln_b = G(first_id + 1); pa.g_w2 = G(first_id + 4); pa.g_b2 = G(first_id + 5);
-    pa.L = L; pa.E = E; pa.p_drop = p_pool; pa.seed = c.seed; pa.offset = c.offset; pa.rng_stream = stream;
-    XF_TRY(launch_attn_pool_bwd(st, pa, B));
-    linear_bwd_dw<float>(st, dh_buf, H2, y_buf, E, G(first_id + 2), B * L, H2, E);
-    launch_colsum(st, dh_buf, H2, B * L, H2, G(first_id + 3));
-    return XATTN_OK;
-  };
-  static_assert(XP_APOOL_B2 - XP_APOOL_LN_W == 5 && XP_VPOOL_B2 - XP_VPOOL_LN_W == 5, "pooler parameter ids are consecutive");
-  // TemporalTransformerPooling (temporal.py:46-75): the learned pooling's backward on the last layer's output, then the encoder
-  // layers in reverse (x2 = x1 + drop(W2·drop(GELU(W1·LN2(x1)))), x1 = x0 + drop(Wo·SA(LN1(x0)))); the sinusoidal positions pass
-  // the gradient through.  Leaves the gradient w.r.t. the side's tokens in ws + w.txb_dx.  h = LN(x) is recomputed, everything
-  // else comes from the layer's TxSaved block; the forward's scratch set (tx_h, tx_q, tx_kv, tx_f) holds the temporaries.
-  const bool tx_pool = c.pool_mode == XATTN_POOL_TRANSFORMER;
-  auto transformer_pool_bwd = [&](int side, const float* d_out) -> int {
-    const int L = side == 0 ? T : Ta, M = B * L, F = 4 * E, PH = c.pool_heads, layers = pool_layers(c);
-    const int64_t n = (int64_t)M * E;
-    float *dX = ws + w.txb_dx, *t1 = ws + w.txb_t1, *t2 = ws + w.txb_t2, *th = ws + w.tx_h, *dq = ws + w.tx_q, *dkv = ws + w.tx_kv,
-          *df = ws + w.tx_f;
-    XF_TRY(pool_bwd(ws + w.tx_out[side], d_out, dX, false, t1, ws + w.txb_dh, L, side == 0 ? XP_VPOOL_LN_W : XP_APOOL_LN_W,
-                    side == 0 ? RS_POOLV : RS_POOLA));
-    for (int layer = layers - 1; layer >= 0; --layer) {
-      const TxSaved sv = tx_saved(ws, w, c, side, layer);
-      auto TP = [&](int k) { return P(XATTN_TX_PARAM_ID(side, layer, k)); };
-      auto TG = [&](int k) { return G(XATTN_TX_PARAM_ID(side, layer, k)); };
-      // ---- feed-forward block ----
-      const float* dy = dX;
-      if (p_pool > 0.f) {
-        XF_TRY(launch_mul_drop(st, t1, dX, n, p_pool, c.seed, c.offset, rs_tx(side, layer, 3)));
-        dy = t1;
+    const int ln_grid = 4 * num_sms();
+    bool bias_fused = false;
+    const bool attn_pool = c.pool_mode == XATTN_POOL_ATTN;
+    const int H2 = E / 2 > 0 ? E / 2 : 1;
+    const float p_pool = train ? c.p_pool : 0.f;
+    // learned pooling (temporal.py:9-26): token gradients from attn_pool_bwd_kernel instead of d_pooled/L; its W1 / b1 gradients as
+    // a batch GEMM / column sum over the y and d_h rows it wrote into two buffers that are still free at that point
+    auto pool_bwd = [&](const float* x, const float* d_out, float* d_x, bool accumulate, float* y_buf, float* dh_buf, int L, int first_id,
+                        uint32_t stream) -> int {
+      AttnPoolBwdArgs pa;
+      pa.x = x; pa.ln_w = P(first_id); pa.ln_b = P(first_id + 1); pa.w1 = P(first_id + 2); pa.b1 = P(first_id + 3);
+      pa.w2 = P(first_id + 4); pa.b2 = P(first_id + 5);
+      pa.d_out = d_out; pa.ld_out = 2 * E; pa.d_x = d_x; pa.accumulate = accumulate ? 1 : 0; pa.y_out = y_buf; pa.dh_out = dh_buf;
+      pa.g_ln_w = G(first_id); pa.g_ln_b = G(first_id + 1); pa.g_w2 = G(first_id + 4); pa.g_b2 = G(first_id + 5);
+      pa.L = L; pa.E = E; pa.p_drop = p_pool; pa.seed = c.seed; pa.offset = c.offset; pa.rng_stream = stream;
+      XF_TRY(launch_attn_pool_bwd(st, pa, B));
+      linear_bwd_dw<float>(st, dh_buf, H2, y_buf, E, G(first_id + 2), B * L, H2, E);
+      launch_colsum(st, dh_buf, H2, B * L, H2, G(first_id + 3));
+      return XATTN_OK;
+    };
+    static_assert(XP_APOOL_B2 - XP_APOOL_LN_W == 5 && XP_VPOOL_B2 - XP_VPOOL_LN_W == 5, "pooler parameter ids are consecutive");
+    // TemporalTransformerPooling (temporal.py:46-75): the learned pooling's backward on the last layer's output, then the encoder
+    // layers in reverse (x2 = x1 + drop(W2·drop(GELU(W1·LN2(x1)))), x1 = x0 + drop(Wo·SA(LN1(x0)))); the sinusoidal positions pass
+    // the gradient through.  Leaves the gradient w.r.t. the side's tokens in ws + w.txb_dx.  h = LN(x) is recomputed, everything
+    // else comes from the layer's TxSaved block; the forward's scratch set (tx_h, tx_q, tx_kv, tx_f) holds the temporaries.
+    const bool tx_pool = c.pool_mode == XATTN_POOL_TRANSFORMER;
+    auto transformer_pool_bwd = [&](int side, const float* d_out) -> int {
+      const int L = side == 0 ? T : Ta, M = B * L, F = 4 * E, PH = c.pool_heads, layers = pool_layers(c);
+      const int64_t n = (int64_t)M * E;
+      float *dX = ws + w.txb_dx, *t1 = ws + w.txb_t1, *t2 = ws + w.txb_t2, *th = ws + w.tx_h, *dq = ws + w.tx_q, *dkv = ws + w.tx_kv,
+            *df = ws + w.tx_f;
+      XF_TRY(pool_bwd(ws + w.tx_out[side], d_out, dX, false, t1, ws + w.txb_dh, L, side == 0 ? XP_VPOOL_LN_W : XP_APOOL_LN_W,
+                      side == 0 ? RS_POOLV : RS_POOLA));
+      for (int layer = layers - 1; layer >= 0; --layer) {
+        const TxSaved sv = tx_saved(ws, w, c, side, layer);
+        auto TP = [&](int k) { return P(XATTN_TX_PARAM_ID(side, layer, k)); };
+        auto TG = [&](int k) { return G(XATTN_TX_PARAM_ID(side, layer, k)); };
+        // ---- feed-forward block ----
+        const float* dy = dX;
+        if (p_pool > 0.f) {
+          XF_TRY(launch_mul_drop(st, t1, dX, n, p_pool, c.seed, c.offset, rs_tx(side, layer, 3)));
+          dy = t1;
+        }
+        linear_bwd_dw<float>(st, dy, E, sv.f_act, F, TG(6), M, E, F);
+        launch_colsum(st, dy, E, M, E, TG(7));
+        linear_bwd_dx(st, dy, E, TP(6), df, M, E, F, false);
+        XF_TRY(launch_gelu_drop_bwd(st, df, sv.f_pre, (int64_t)M * F, p_pool, c.seed, c.offset, rs_tx(side, layer, 2)));
+        XF_TRY(launch_ln_rows(st, sv.x_mid, TP(10), TP(11), th, M, E));
+        linear_bwd_dw<float>(st, df, F, th, E, TG(4), M, F, E);
+        launch_colsum(st, df, F, M, F, TG(5));
+        linear_bwd_dx(st, df, F, TP(4), t2, M, F, E, false);
+        XF_TRY(launch_ln_rows_bwd(st, sv.x_mid, TP(10), t2, dX, TG(10), TG(11), M, E, true));
+        // ---- self-attention block ----
+        dy = dX;
+        if (p_pool > 0.f) {
+          XF_TRY(launch_mul_drop(st, t1, dX, n, p_pool, c.seed, c.offset, rs_tx(side, layer, 1)));
+          dy = t1;
+        }
+        linear_bwd_dw<float>(st, dy, E, sv.o, E, TG(2), M, E, E);
+        launch_colsum(st, dy, E, M, E, TG(3));
+        linear_bwd_dx(st, dy, E, TP(2), t2, M, E, E, false);
+        AttnBwdArgs aa;
+        aa.q = sv.q; aa.kv = sv.kv; aa.qs = nullptr; aa.ks = nullptr; aa.bias_scale = nullptr; aa.P = sv.P; aa.dO = t2;
+        aa.dq = dq; aa.dkv = dkv; aa.dqs = nullptr; aa.dks = nullptr; aa.dbias_scale = nullptr;
+        aa.L = L; aa.S = L; aa.E = E; aa.H = PH; aa.scale = 1.0f / sqrtf((float)(E / PH)); aa.p_drop = p_pool; aa.seed = c.seed;
+        aa.offset = c.offset; aa.rng_stream = rs_tx(side, layer, 0);
+        aa.dbq = TG(1); aa.dbkv = TG(1) + E;
+        bool in_bias_fused = false;
+        XF_TRY(launch_attn_bwd(st, aa, B, &in_bias_fused));
+        XF_TRY(launch_ln_rows(st, sv.x_in, TP(8), TP(9), th, M, E));
+        linear_bwd_dw<float>(st, dq, E, th, E, TG(0), M, E, E);
+        linear_bwd_dw<float>(st, dkv, 2 * E, th, E, TG(0) + (int64_t)E * E, M, 2 * E, E);
+        if (!in_bias_fused) {
+          launch_colsum(st, dq, E, M, E, TG(1));
+          launch_colsum(st, dkv, 2 * E, M, 2 * E, TG(1) + E);
+        }
+        linear_bwd_dx(st, dq, E, TP(0), t1, M, E, E, false);
+        linear_bwd_dx(st, dkv, 2 * E, TP(0) + (int64_t)E * E, t1, M, 2 * E, E, true);
+        XF_TRY(launch_ln_rows_bwd(st, sv.x_in, TP(8), t1, dX, TG(8), TG(9), M, E, true));
+        XF_LAUNCH_CHECK();
       }
-      linear_bwd_dw<float>(st, dy, E, sv.f_act, F, TG(6), M, E, F);
-      launch_colsum(st, dy, E, M, E, TG(7));
-      linear_bwd_dx(st, dy, E, TP(6), df, M, E, F, false);
-      XF_TRY(launch_gelu_drop_bwd(st, df, sv.f_pre, (int64_t)M * F, p_pool, c.seed, c.offset, rs_tx(side, layer, 2)));
-      XF_TRY(launch_ln_rows(st, sv.x_mid, TP(10), TP(11), th, M, E));
-      linear_bwd_dw<float>(st, df, F, th, E, TG(4), M, F, E);
-      launch_colsum(st, df, F, M, F, TG(5));
-      linear_bwd_dx(st, df, F, TP(4), t2, M, F, E, false);
-      XF_TRY(launch_ln_rows_bwd(st, sv.x_mid, TP(10), t2, dX, TG(10), TG(11), M, E, true));
-      // ---- self-attention block ----
-      dy = dX;
-      if (p_pool > 0.f) {
-        XF_TRY(launch_mul_drop(st, t1, dX, n, p_pool, c.seed, c.offset, rs_tx(side, layer, 1)));
-        dy = t1;
-      }
-      linear_bwd_dw<float>(st, dy, E, sv.o, E, TG(2), M, E, E);
-      launch_colsum(st, dy, E, M, E, TG(3));
-      linear_bwd_dx(st, dy, E, TP(2), t2, M, E, E, false);
+      return XATTN_OK;
+    };
+    if (attn_pool) XF_TRY(pool_bwd(ws + w.a1, ws + w.d_pooled + E, ws + w.d_q2, false, ws + w.d_br2, ws + w.d_o2, Ta, XP_APOOL_LN_W, RS_POOLA));   // (d_q2 is free until the a2v attention backward)
+    if (tx_pool) XF_TRY(transformer_pool_bwd(1, ws + w.d_pooled + E));
+    const bool tok_pool = attn_pool || tx_pool;   // the a_norm / v_norm outputs receive per-token gradients instead of d_pooled / L
+    // ---- a_norm backward (fusion.py:399) + mean pool (temporal.py:108-109) ----
+    bool ob_fused = launch_ln_bwd(st, ln_grid, tx_pool ? ws + w.txb_dx : attn_pool ? ws + w.d_q2 : nullptr, tok_pool ? nullptr : ws + w.d_pooled + E, 2 * E,
+                                  1.f / (float)Ta, ws + w.s2, ws + w.mean2, ws + w.rstd2,
+                                  P(XP_AN_W), ws + w.dp2, ws + w.d_a0, ws + w.d_br2, G(XP_AN_W), G(XP_AN_B), G(XP_A2V_OUT_B), B * Ta, Ta, E);
+    // a2v out_proj
+    linear_bwd_dw<float>(st, ws + w.d_br2, E, ws + w.o2, E, G(XP_A2V_OUT_W), B * Ta, E, E);
+    if (!ob_fused) launch_colsum(st, ws + w.d_br2, E, B * Ta, E, G(XP_A2V_OUT_B));
+    linear_bwd_dx(st, ws + w.d_br2, E, P(XP_A2V_OUT_W), ws + w.d_o2, B * Ta, E, E, false);
+    XF_LAUNCH_CHECK();
+    {
       AttnBwdArgs aa;
-      aa.q = sv.q; aa.kv = sv.kv; aa.qs = nullptr; aa.ks = nullptr; aa.bias_scale = nullptr; aa.P = sv.P; aa.dO = t2;
-      aa.dq = dq; aa.dkv = dkv; aa.dqs = nullptr; aa.dks = nullptr; aa.dbias_scale = nullptr;
-      aa.L = L; aa.S = L; aa.E = E; aa.H = PH; aa.scale = 1.0f / sqrtf((float)(E / PH)); aa.p_drop = p_pool; aa.seed = c.seed;
-      aa.offset = c.offset; aa.rng_stream = rs_tx(side, layer, 0);
-      aa.dbq = TG(1); aa.dbkv = TG(1) + E;
-      bool in_bias_fused = false;
-      XF_TRY(launch_attn_bwd(st, aa, B, &in_bias_fused));
-      XF_TRY(launch_ln_rows(st, sv.x_in, TP(8), TP(9), th, M, E));
-      linear_bwd_dw<float>(st, dq, E, th, E, TG(0), M, E, E);
-      linear_bwd_dw<float>(st, dkv, 2 * E, th, E, TG(0) + (int64_t)E * E, M, 2 * E, E);
-      if (!in_bias_fused) {
-        launch_colsum(st, dq, E, M, E, TG(1));
-        launch_colsum(st, dkv, 2 * E, M, 2 * E, TG(1) + E);
+      aa.q = ws + w.q2; aa.kv = ws + w.kv2;
+      aa.qs = c.use_prior ? ws + w.qa : nullptr; aa.ks = c.use_prior ? ws + w.kvs : nullptr;
+      aa.bias_scale = c.use_prior ? P(XP_BIAS_SCALE) : nullptr; aa.P = ws + w.p2; aa.dO = ws + w.d_o2;
+      aa.dq = ws + w.d_q2; aa.dkv = ws + w.d_kv2; aa.dqs = ws + w.d_qa; aa.dks = ws + w.d_kvs;
+      aa.dbias_scale = c.use_prior ? G(XP_BIAS_SCALE) : nullptr;
+      aa.L = Ta; aa.S = T; aa.E = E; aa.H = H; aa.scale = scale; aa.p_drop = p_attn; aa.seed = c.seed; aa.offset = c.offset;
+      aa.rng_stream = RS_ATTN2; aa.ldp = p_row_stride(c, T);
+      aa.dbq = G(XP_A2V_IN_B); aa.dbkv = G(XP_A2V_IN_B) + E;
+      XF_TRY(launch_attn_bwd(st, aa, B, &bias_fused));
+    }
+    // a2v in_proj: q from a0, k|v from v1
+    linear_bwd_dw<float>(st, ws + w.d_q2, E, ws + w.a0, E, G(XP_A2V_IN_W), B * Ta, E, E);
+    if (!bias_fused) launch_colsum(st, ws + w.d_q2, E, B * Ta, E, G(XP_A2V_IN_B));
+    linear_bwd_dx(st, ws + w.d_q2, E, P(XP_A2V_IN_W), ws + w.d_a0, B * Ta, E, E, true);
+    linear_bwd_dw<float>(st, ws + w.d_kv2, 2 * E, ws + w.v1, E, G(XP_A2V_IN_W) + (int64_t)E * E, B * T, 2 * E, E);
+    if (!bias_fused) launch_colsum(st, ws + w.d_kv2, 2 * E, B * T, 2 * E, G(XP_A2V_IN_B) + E);
+    linear_bwd_dx(st, ws + w.d_kv2, 2 * E, P(XP_A2V_IN_W) + (int64_t)E * E, ws + w.d_v1, B * T, 2 * E, E, false);
+    XF_LAUNCH_CHECK();
+    if (attn_pool) XF_TRY(pool_bwd(ws + w.v1, ws + w.d_pooled, ws + w.d_v1, true, ws + w.d_br1, ws + w.d_o1, T, XP_VPOOL_LN_W, RS_POOLV));
+    if (tx_pool) {
+      XF_TRY(transformer_pool_bwd(0, ws + w.d_pooled));
+      XF_TRY(launch_add_inplace(st, ws + w.d_v1, ws + w.txb_dx, (int64_t)B * T * E));
+    }
+    // ---- v_norm backward (fusion.py:395) ----
+    ob_fused = launch_ln_bwd(st, ln_grid, ws + w.d_v1, tok_pool ? nullptr : ws + w.d_pooled, 2 * E, 1.f / (float)T, ws + w.s1, ws + w.mean1, ws + w.rstd1,
+                             P(XP_VN_W), ws + w.dp1, ws + w.d_v0, ws + w.d_br1, G(XP_VN_W), G(XP_VN_B), G(XP_V2A_OUT_B), B * T, T, E);
+    linear_bwd_dw<float>(st, ws + w.d_br1, E, ws + w.o1, E, G(XP_V2A_OUT_W), B * T, E, E);
+    if (!ob_fused) launch_colsum(st, ws + w.d_br1, E, B * T, E, G(XP_V2A_OUT_B));
+    linear_bwd_dx(st, ws + w.d_br1, E, P(XP_V2A_OUT_W), ws + w.d_o1, B * T, E, E, false);
+    XF_LAUNCH_CHECK();
+    {
+      AttnBwdArgs aa;
+      aa.q = ws + w.q1; aa.kv = ws + w.kv1;
+      aa.qs = c.use_prior ? ws + w.qv : nullptr; aa.ks = c.use_prior ? ws + w.ka : nullptr;
+      aa.bias_scale = c.use_prior ? P(XP_BIAS_SCALE) : nullptr; aa.P = ws + w.p1; aa.dO = ws + w.d_o1;
+      aa.dq = ws + w.d_q1; aa.dkv = ws + w.d_kv1; aa.dqs = ws + w.d_qv; aa.dks = ws + w.d_ka;
+      aa.dbias_scale = c.use_prior ? G(XP_BIAS_SCALE) : nullptr;
+      aa.L = T; aa.S = Ta; aa.E = E; aa.H = H; aa.scale = scale; aa.p_drop = p_attn; aa.seed = c.seed; aa.offset = c.offset;
+      aa.rng_stream = RS_ATTN1; aa.ldp = p_row_stride(c, Ta);
+      aa.dbq = G(XP_V2A_IN_B); aa.dbkv = G(XP_V2A_IN_B) + E;
+      XF_TRY(launch_attn_bwd(st, aa, B, &bias_fused));
+    }
+    // v2a in_proj: the token gradients first (the prior backward and the input projections wait for them) ...
+    linear_bwd_dx(st, ws + w.d_q1, E, P(XP_V2A_IN_W), ws + w.d_v0, B * T, E, E, true);
+    linear_bwd_dx(st, ws + w.d_kv1, 2 * E, P(XP_V2A_IN_W) + (int64_t)E * E, ws + w.d_a0, B * Ta, 2 * E, E, true);
+    // ... then its weight gradients (HBM-bound tensor-core GEMMs nothing downstream reads) on the high-priority side stream under
+    // tf32, beside the latency-bound per-clip prior backward on `st`
+    SideFork sf(st);
+    if (opt.fork && c.use_prior && g_tc_gemm) XF_TRY(sf.begin());
+    linear_bwd_dw<float>(sf.side(), ws + w.d_q1, E, ws + w.v0, E, G(XP_V2A_IN_W), B * T, E, E);
+    if (!bias_fused) launch_colsum(sf.side(), ws + w.d_q1, E, B * T, E, G(XP_V2A_IN_B));
+    linear_bwd_dw<float>(sf.side(), ws + w.d_kv1, 2 * E, ws + w.a0, E, G(XP_V2A_IN_W) + (int64_t)E * E, B * Ta, 2 * E, E);
+    if (!bias_fused) launch_colsum(sf.side(), ws + w.d_kv1, 2 * E, B * Ta, 2 * E, G(XP_V2A_IN_B) + E);
+    XF_LAUNCH_CHECK();
+
+    // ---- emotion prior (fusion.py:170-184) ----
+    if (c.use_prior) {
+      PriorBwdArgs pa;
+      pa.v0 = ws + w.v0; pa.a0 = ws + w.a0; pa.phid = ws + w.phid; pa.prior = ws + w.prior;
+      pa.w0 = P(XP_PRIOR0_W); pa.w3 = P(XP_PRIOR3_W);
+      pa.wh[0] = P(XP_VQ_W); pa.wh[1] = P(XP_AK_W); pa.wh[2] = P(XP_AQ_W); pa.wh[3] = P(XP_VK_W);
+      pa.g_wh[0] = G(XP_VQ_W); pa.g_wh[1] = G(XP_AK_W); pa.g_wh[2] = G(XP_AQ_W); pa.g_wh[3] = G(XP_VK_W);
+      pa.g_bh[0] = G(XP_VQ_B); pa.g_bh[1] = G(XP_AK_B); pa.g_bh[2] = G(XP_AQ_B); pa.g_bh[3] = G(XP_VK_B);
+      pa.d_qv = ws + w.d_qv; pa.d_ka = ws + w.d_ka; pa.d_qa = ws + w.d_qa; pa.d_kvs = ws + w.d_kvs;
+      pa.d_v0 = ws + w.d_v0; pa.d_a0 = ws + w.d_a0; pa.d_prior = ws + w.d_prior; pa.d_phid = ws + w.d_phid;
+      pa.T = T; pa.Ta = Ta; pa.E = E; pa.P = c.prior_dim; pa.Hd = c.prior_hidden; pa.inv_keep = 1.f / (1.f - p_prior);
+      pa.g_bv = G(XP_V_IN_B); pa.g_ba = G(XP_A_IN_B);
+      const size_t smem128 = sizeof(float) * (2 * E + 8 * E + 2 * (T + Ta) + 4 + c.prior_dim + c.prior_hidden);
+      if (E == 128 && smem128 <= 48 * 1024) {
+        pa.vec = 1;
+        prior_bwd128_kernel<<<B, 256, smem128, st>>>(pa);
+      } else {
+        size_t smem = sizeof(float) * (4 + c.prior_dim + c.prior_hidden + 2 * E);
+        const size_t smem_vec = smem + sizeof(float) * (2 * (T + Ta) + 8 * 6 * E);
+        pa.vec = (E % 4 == 0 && smem_vec <= 48 * 1024) ? 1 : 0;
+        if (pa.vec) smem = smem_vec;
+        prior_bwd_kernel<<<B, 256, smem, st>>>(pa);
       }
-      linear_bwd_dx(st, dq, E, TP(0), t1, M, E, E, false);
-      linear_bwd_dx(st, dkv, 2 * E, TP(0) + (int64_t)E * E, t1, M, 2 * E, E, true);
-      XF_TRY(launch_ln_rows_bwd(st, sv.x_in, TP(8), t1, dX, TG(8), TG(9), M, E, true));
+      count_launch();
+      linear_bwd_dw<float>(st, ws + w.d_prior, c.prior_dim, ws + w.phid, c.prior_hidden, G(XP_PRIOR3_W), B, c.prior_dim, c.prior_hidden);
+      launch_colsum(st, ws + w.d_prior, c.prior_dim, B, c.prior_dim, G(XP_PRIOR3_B));
+      linear_bwd_dw<float>(st, ws + w.d_phid, c.prior_hidden, ws + w.pooled0, 2 * E, G(XP_PRIOR0_W), B, c.prior_hidden, 2 * E);
+      launch_colsum(st, ws + w.d_phid, c.prior_hidden, B, c.prior_hidden, G(XP_PRIOR0_B));
       XF_LAUNCH_CHECK();
     }
-    return XATTN_OK;
-  };
-  if (attn_pool) XF_TRY(pool_bwd(ws + w.a1, ws + w.d_pooled + E, ws + w.d_q2, false, ws + w.d_br2, ws + w.d_o2, Ta, XP_APOOL_LN_W, RS_POOLA));   // (d_q2 is free until the a2v attention backward)
-  if (tx_pool) XF_TRY(transformer_pool_bwd(1, ws + w.d_pooled + E));
-  const bool tok_pool = attn_pool || tx_pool;   // the a_norm / v_norm outputs receive per-token gradients instead of d_pooled / L
-  // ---- a_norm backward (fusion.py:399) + mean pool (temporal.py:108-109) ----
-  bool ob_fused = launch_ln_bwd(st, ln_grid, tx_pool ? ws + w.txb_dx : attn_pool ? ws + w.d_q2 : nullptr, tok_pool ? nullptr : ws + w.d_pooled + E, 2 * E,
-                                1.f / (float)Ta, ws + w.s2, ws + w.mean2, ws + w.rstd2,
-                                P(XP_AN_W), ws + w.dp2, ws + w.d_a0, ws + w.d_br2, G(XP_AN_W), G(XP_AN_B), G(XP_A2V_OUT_B), B * Ta, Ta, E);
-  // a2v out_proj
-  linear_bwd_dw<float>(st, ws + w.d_br2, E, ws + w.o2, E, G(XP_A2V_OUT_W), B * Ta, E, E);
-  if (!ob_fused) launch_colsum(st, ws + w.d_br2, E, B * Ta, E, G(XP_A2V_OUT_B));
-  linear_bwd_dx(st, ws + w.d_br2, E, P(XP_A2V_OUT_W), ws + w.d_o2, B * Ta, E, E, false);
-  XF_LAUNCH_CHECK();
-  {
-    AttnBwdArgs aa;
-    aa.q = ws + w.q2; aa.kv = ws + w.kv2;
-    aa.qs = c.use_prior ? ws + w.qa : nullptr; aa.ks = c.use_prior ? ws + w.kvs : nullptr;
-    aa.bias_scale = c.use_prior ? P(XP_BIAS_SCALE) : nullptr; aa.P = ws + w.p2; aa.dO = ws + w.d_o2;
-    aa.dq = ws + w.d_q2; aa.dkv = ws + w.d_kv2; aa.dqs = ws + w.d_qa; aa.dks = ws + w.d_kvs;
-    aa.dbias_scale = c.use_prior ? G(XP_BIAS_SCALE) : nullptr;
-    aa.L = Ta; aa.S = T; aa.E = E; aa.H = H; aa.scale = scale; aa.p_drop = p_attn; aa.seed = c.seed; aa.offset = c.offset;
-    aa.rng_stream = RS_ATTN2; aa.ldp = p_row_stride(c, T);
-    aa.dbq = G(XP_A2V_IN_B); aa.dbkv = G(XP_A2V_IN_B) + E;
-    XF_TRY(launch_attn_bwd(st, aa, B, &bias_fused));
+    XF_TRY(sf.join());
   }
-  // a2v in_proj: q from a0, k|v from v1
-  linear_bwd_dw<float>(st, ws + w.d_q2, E, ws + w.a0, E, G(XP_A2V_IN_W), B * Ta, E, E);
-  if (!bias_fused) launch_colsum(st, ws + w.d_q2, E, B * Ta, E, G(XP_A2V_IN_B));
-  linear_bwd_dx(st, ws + w.d_q2, E, P(XP_A2V_IN_W), ws + w.d_a0, B * Ta, E, E, true);
-  linear_bwd_dw<float>(st, ws + w.d_kv2, 2 * E, ws + w.v1, E, G(XP_A2V_IN_W) + (int64_t)E * E, B * T, 2 * E, E);
-  if (!bias_fused) launch_colsum(st, ws + w.d_kv2, 2 * E, B * T, 2 * E, G(XP_A2V_IN_B) + E);
-  linear_bwd_dx(st, ws + w.d_kv2, 2 * E, P(XP_A2V_IN_W) + (int64_t)E * E, ws + w.d_v1, B * T, 2 * E, E, false);
-  XF_LAUNCH_CHECK();
-  if (attn_pool) XF_TRY(pool_bwd(ws + w.v1, ws + w.d_pooled, ws + w.d_v1, true, ws + w.d_br1, ws + w.d_o1, T, XP_VPOOL_LN_W, RS_POOLV));
-  if (tx_pool) {
-    XF_TRY(transformer_pool_bwd(0, ws + w.d_pooled));
-    XF_TRY(launch_add_inplace(st, ws + w.d_v1, ws + w.txb_dx, (int64_t)B * T * E));
-  }
-  // ---- v_norm backward (fusion.py:395) ----
-  ob_fused = launch_ln_bwd(st, ln_grid, ws + w.d_v1, tok_pool ? nullptr : ws + w.d_pooled, 2 * E, 1.f / (float)T, ws + w.s1, ws + w.mean1, ws + w.rstd1,
-                           P(XP_VN_W), ws + w.dp1, ws + w.d_v0, ws + w.d_br1, G(XP_VN_W), G(XP_VN_B), G(XP_V2A_OUT_B), B * T, T, E);
-  linear_bwd_dw<float>(st, ws + w.d_br1, E, ws + w.o1, E, G(XP_V2A_OUT_W), B * T, E, E);
-  if (!ob_fused) launch_colsum(st, ws + w.d_br1, E, B * T, E, G(XP_V2A_OUT_B));
-  linear_bwd_dx(st, ws + w.d_br1, E, P(XP_V2A_OUT_W), ws + w.d_o1, B * T, E, E, false);
-  XF_LAUNCH_CHECK();
-  {
-    AttnBwdArgs aa;
-    aa.q = ws + w.q1; aa.kv = ws + w.kv1;
-    aa.qs = c.use_prior ? ws + w.qv : nullptr; aa.ks = c.use_prior ? ws + w.ka : nullptr;
-    aa.bias_scale = c.use_prior ? P(XP_BIAS_SCALE) : nullptr; aa.P = ws + w.p1; aa.dO = ws + w.d_o1;
-    aa.dq = ws + w.d_q1; aa.dkv = ws + w.d_kv1; aa.dqs = ws + w.d_qv; aa.dks = ws + w.d_ka;
-    aa.dbias_scale = c.use_prior ? G(XP_BIAS_SCALE) : nullptr;
-    aa.L = T; aa.S = Ta; aa.E = E; aa.H = H; aa.scale = scale; aa.p_drop = p_attn; aa.seed = c.seed; aa.offset = c.offset;
-    aa.rng_stream = RS_ATTN1; aa.ldp = p_row_stride(c, Ta);
-    aa.dbq = G(XP_V2A_IN_B); aa.dbkv = G(XP_V2A_IN_B) + E;
-    XF_TRY(launch_attn_bwd(st, aa, B, &bias_fused));
-  }
-  // v2a in_proj: the token gradients first (the prior backward and the input projections wait for them) ...
-  linear_bwd_dx(st, ws + w.d_q1, E, P(XP_V2A_IN_W), ws + w.d_v0, B * T, E, E, true);
-  linear_bwd_dx(st, ws + w.d_kv1, 2 * E, P(XP_V2A_IN_W) + (int64_t)E * E, ws + w.d_a0, B * Ta, 2 * E, E, true);
-  // ... then its weight gradients (HBM-bound tensor-core GEMMs nothing downstream reads) on the high-priority side stream under
-  // tf32, beside the latency-bound per-clip prior backward on `st`
-  SideFork sf(st);
-  if (opt.fork && c.use_prior && g_tc_gemm) XF_TRY(sf.begin());
-  linear_bwd_dw<float>(sf.side(), ws + w.d_q1, E, ws + w.v0, E, G(XP_V2A_IN_W), B * T, E, E);
-  if (!bias_fused) launch_colsum(sf.side(), ws + w.d_q1, E, B * T, E, G(XP_V2A_IN_B));
-  linear_bwd_dw<float>(sf.side(), ws + w.d_kv1, 2 * E, ws + w.a0, E, G(XP_V2A_IN_W) + (int64_t)E * E, B * Ta, 2 * E, E);
-  if (!bias_fused) launch_colsum(sf.side(), ws + w.d_kv1, 2 * E, B * Ta, 2 * E, G(XP_V2A_IN_B) + E);
-  XF_LAUNCH_CHECK();
-
-  bool tok_bias_fused = false;
-  // ---- emotion prior (fusion.py:170-184) ----
-  if (c.use_prior) {
-    PriorBwdArgs pa;
-    pa.v0 = ws + w.v0; pa.a0 = ws + w.a0; pa.phid = ws + w.phid; pa.prior = ws + w.prior;
-    pa.w0 = P(XP_PRIOR0_W); pa.w3 = P(XP_PRIOR3_W);
-    pa.wh[0] = P(XP_VQ_W); pa.wh[1] = P(XP_AK_W); pa.wh[2] = P(XP_AQ_W); pa.wh[3] = P(XP_VK_W);
-    pa.g_wh[0] = G(XP_VQ_W); pa.g_wh[1] = G(XP_AK_W); pa.g_wh[2] = G(XP_AQ_W); pa.g_wh[3] = G(XP_VK_W);
-    pa.g_bh[0] = G(XP_VQ_B); pa.g_bh[1] = G(XP_AK_B); pa.g_bh[2] = G(XP_AQ_B); pa.g_bh[3] = G(XP_VK_B);
-    pa.d_qv = ws + w.d_qv; pa.d_ka = ws + w.d_ka; pa.d_qa = ws + w.d_qa; pa.d_kvs = ws + w.d_kvs;
-    pa.d_v0 = ws + w.d_v0; pa.d_a0 = ws + w.d_a0; pa.d_prior = ws + w.d_prior; pa.d_phid = ws + w.d_phid;
-    pa.T = T; pa.Ta = Ta; pa.E = E; pa.P = c.prior_dim; pa.Hd = c.prior_hidden; pa.inv_keep = 1.f / (1.f - p_prior);
-    pa.g_bv = G(XP_V_IN_B); pa.g_ba = G(XP_A_IN_B);
-    const size_t smem128 = sizeof(float) * (2 * E + 8 * E + 2 * (T + Ta) + 4 + c.prior_dim + c.prior_hidden);
-    if (E == 128 && smem128 <= 48 * 1024) {
-      pa.vec = 1;
-      tok_bias_fused = true;   // d_v0 / d_a0 are final in that kernel: it leaves their column sums in the two bias gradients
-      prior_bwd128_kernel<<<B, 256, smem128, st>>>(pa);
-    } else {
-      size_t smem = sizeof(float) * (4 + c.prior_dim + c.prior_hidden + 2 * E);
-      const size_t smem_vec = smem + sizeof(float) * (2 * (T + Ta) + 8 * 6 * E);
-      pa.vec = (E % 4 == 0 && smem_vec <= 48 * 1024) ? 1 : 0;
-      tok_bias_fused = pa.vec != 0;
-      if (pa.vec) smem = smem_vec;
-      prior_bwd_kernel<<<B, 256, smem, st>>>(pa);
-    }
-    count_launch();
-    linear_bwd_dw<float>(st, ws + w.d_prior, c.prior_dim, ws + w.phid, c.prior_hidden, G(XP_PRIOR3_W), B, c.prior_dim, c.prior_hidden);
-    launch_colsum(st, ws + w.d_prior, c.prior_dim, B, c.prior_dim, G(XP_PRIOR3_B));
-    linear_bwd_dw<float>(st, ws + w.d_phid, c.prior_hidden, ws + w.pooled0, 2 * E, G(XP_PRIOR0_W), B, c.prior_hidden, 2 * E);
-    launch_colsum(st, ws + w.d_phid, c.prior_hidden, B, c.prior_hidden, G(XP_PRIOR0_B));
-    XF_LAUNCH_CHECK();
-  }
-  XF_TRY(sf.join());
 
   if (opt.tail_stream != nullptr) {   // everything but the input projections' gradients is final from here on
     cudaEvent_t ev = nullptr;
@@ -1356,6 +1361,7 @@ static int backward_f32_impl(const xattn_config& c, const float* params, const T
     XF_CUDA(cudaEventRecord(ev, st));
     XF_CUDA(cudaStreamWaitEvent(opt.tail_stream, ev, 0));
   }
+  if (opt.phase == 1) return XATTN_OK;
   NvtxRange nvtx_in("input_projections_backward");
   // ---- input projections (fusion.py:386, :378, :372); dX only on request (Stage 1 freezes the backbones) ----
   linear_bwd_dw<float>(st, ws + w.d_a0, E, ws + w.aseq, E, G(XP_A_IN_W), B * Ta, E, E);

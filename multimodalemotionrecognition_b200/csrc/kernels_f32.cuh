@@ -83,6 +83,7 @@ struct BackwardOptions {
   float* d_video = nullptr;             // [B,T,Dv] fp32 or nullptr
   float* d_audio = nullptr;             // [B,Ta,Da] fp32 or nullptr
   bool fork = true;                     // the library may use its per-device side stream (SideFork)
+  int phase = 0;                        // 0 whole backward; 1 up to the tail point; 2 the input projections only (backward_f32_impl)
 };
 int backward_f32(const xattn_config& c, const float* params, const void* xv, const void* xa, const float* dlogits,
                  float* grads, void* ws, cudaStream_t st, const BackwardOptions& opt = BackwardOptions());

@@ -22,13 +22,18 @@ struct StepGraph {
   cudaGraphExec_t exec = nullptr;
   std::mutex mu;
 };
-StepGraph g_step_graph[64];
+StepGraph g_step_graph[64][3];   // per device and phase
 
 int enqueue_step(const xattn_step_args& a, int64_t n_params, cudaStream_t st) {
   const xattn_config& c = *a.cfg;
-  XF_TRY(forward_f32(c, a.params, a.video_emb, a.audio_emb, a.logits, a.workspace, st));
-  XF_TRY(ce_loss_fwd_bwd(a.logits, a.labels, c.B, c.C, a.label_smoothing, 1.f, a.loss, a.dlogits, st));
-  XF_TRY(backward_f32(c, a.params, a.video_emb, a.audio_emb, a.dlogits, a.grads, a.workspace, st));
+  BackwardOptions opt;
+  opt.phase = a.phase;
+  if (a.phase != 2) {
+    XF_TRY(forward_f32(c, a.params, a.video_emb, a.audio_emb, a.logits, a.workspace, st));
+    XF_TRY(ce_loss_fwd_bwd(a.logits, a.labels, c.B, c.C, a.label_smoothing, a.grad_scale > 0.f ? a.grad_scale : 1.f, a.loss, a.dlogits, st));
+  }
+  XF_TRY(backward_f32(c, a.params, a.video_emb, a.audio_emb, a.dlogits, a.grads, a.workspace, st, opt));
+  if (a.phase != 0) return XATTN_OK;
   return adam_step(a.params, a.grads, a.exp_avg, a.exp_avg_sq, n_params, a.lr, a.beta1, a.beta2, a.eps, a.weight_decay, a.step,
                    a.decoupled, st);
 }
@@ -39,15 +44,16 @@ extern "C" XATTN_API int xattn_stage1_step(const xattn_step_args* a, void* strea
   if (a == nullptr) XF_FAIL(XATTN_ERR_NULL, "args is NULL");
   XF_TRY(validate_config(a->cfg));
   const xattn_config& c = *a->cfg;
-  if (!a->params || !a->video_emb || !a->audio_emb || !a->labels || !a->logits || !a->loss || !a->dlogits || !a->grads || !a->exp_avg ||
-      !a->exp_avg_sq || !a->workspace)
+  if (a->phase < 0 || a->phase > 2) XF_FAIL(XATTN_ERR_SHAPE, "phase %d outside 0..2", a->phase);
+  if (!a->params || !a->video_emb || !a->audio_emb || !a->labels || !a->logits || !a->loss || !a->dlogits || !a->grads || !a->workspace ||
+      (a->phase == 0 && (!a->exp_avg || !a->exp_avg_sq)))
     XF_FAIL(XATTN_ERR_NULL, "NULL pointer argument");
   for (const void* p : {(const void*)a->params, a->video_emb, a->audio_emb, (const void*)a->logits, (const void*)a->dlogits,
                         (const void*)a->grads, (const void*)a->exp_avg, (const void*)a->exp_avg_sq, (const void*)a->workspace})
     if (((uintptr_t)p & 15) != 0) XF_FAIL(XATTN_ERR_ALIGN, "pointers must be 16-byte aligned");
   if (c.precision == XATTN_DTYPE_BF16) XF_FAIL(XATTN_ERR_DTYPE, "the training step runs with precision=f32 or tf32");
   if (!c.training && !c.save_for_backward) XF_FAIL(XATTN_ERR_SHAPE, "cfg needs training or save_for_backward for a training step");
-  if (a->step < 1) XF_FAIL(XATTN_ERR_SHAPE, "Adam step count is 1-based (got %d)", a->step);
+  if (a->phase == 0 && a->step < 1) XF_FAIL(XATTN_ERR_SHAPE, "Adam step count is 1-based (got %d)", a->step);
   XF_TRY(check_device_sm100());
   int64_t need = 0;
   XF_TRY(xattn_workspace_bytes(a->cfg, &need));
@@ -62,7 +68,7 @@ extern "C" XATTN_API int xattn_stage1_step(const xattn_step_args* a, void* strea
   int dev = 0;
   XF_CUDA(cudaGetDevice(&dev));
   if (dev < 0 || dev >= 64) XF_FAIL(XATTN_ERR_CUDA, "device index %d out of range", dev);
-  StepGraph& sg = g_step_graph[dev];
+  StepGraph& sg = g_step_graph[dev][a->phase];
   std::lock_guard<std::mutex> lock(sg.mu);
   if (sg.capture == nullptr) XF_CUDA(cudaStreamCreateWithFlags(&sg.capture, cudaStreamNonBlocking));
   // thread-local capture mode: other threads of the process may keep calling CUDA while this one captures

@@ -49,9 +49,9 @@ class Stage1Trainer:
         # Data parallel: all-reduce the gradients of everything but the input projections on a side stream while the
         # input-projection backward (the longest GEMMs of the step) still runs; False = one all-reduce after the backward.
         self.overlap_allreduce = bool(overlap_allreduce)
-        # Single rank: the whole step (forward, CE, backward, Adam) goes through ONE library call that replays it as a CUDA graph
-        # (``xattn_stage1_step``; the gaps between the step's ~58 short kernels go: 1.73 -> 1.62 ms at B=1024).  None = on when
-        # there is no process group to all-reduce over; False = the separate calls.
+        # The step goes through ``xattn_stage1_step``, which replays it as a CUDA graph (the gaps between the step's ~58 short
+        # kernels go: 1.73 -> 1.62 ms at B=1024): one graph on a single rank, two around the overlapped all-reduce under data
+        # parallelism.  None / True = on; False = the separate calls (always with overlap_allreduce=False).
         self.graph = graph
         self._static = None
         self._side: Optional[torch.cuda.Stream] = None
@@ -132,7 +132,11 @@ class Stage1Trainer:
 
     def _fused_step(self, video_emb: torch.Tensor, audio_emb: torch.Tensor, labels: torch.Tensor, training: bool) -> torch.Tensor:
         """``xattn_stage1_step`` with ``use_graph``: one call, one CUDA graph launch.  Buffers the graph's kernels point at
-        (workspace, logits, loss, dlogits) are kept across steps, so a step allocates nothing."""
+        (workspace, logits, loss, dlogits) are kept across steps, so a step allocates nothing.
+
+        Data parallel (world > 1): two graphs with the gradient all-reduce between and beside them — phase 1 (forward, CE, the
+        backward up to the point where the tail bucket is final), the tail bucket's all-reduce on a side stream beside phase 2
+        (the input-projection backward), then the head bucket's all-reduce and Adam."""
         from .fusion import _io_dtype
 
         head = self.head
@@ -161,6 +165,7 @@ class Stage1Trainer:
                       "dlogits": torch.empty((B, head.num_classes), dtype=torch.float32, device=dev),
                       "loss": torch.empty((), dtype=torch.float32, device=dev)}
                 self._static = st
+            world = self._world()
             self.step_count += 1
             a = _lib.XAttnStepArgs()
             a.cfg = C.pointer(cfg)
@@ -171,17 +176,39 @@ class Stage1Trainer:
             a.lr, a.beta1, a.beta2, a.eps = self.lr, self.betas[0], self.betas[1], self.eps
             a.weight_decay, a.label_smoothing = self.weight_decay, self.label_smoothing
             a.step, a.decoupled, a.use_graph = self.step_count, int(self.decoupled), 1
-            _lib.check(_lib.load().xattn_stage1_step(C.byref(a), _stream_ptr(dev)))
+            a.grad_scale = 1.0 / world
+            lib = _lib.load()
+            if world <= 1:
+                _lib.check(lib.xattn_stage1_step(C.byref(a), _stream_ptr(dev)))
+            else:
+                if "tail" not in st:
+                    st["tail"] = _lib.xattn_param_layout(cfg)[0][_lib.XP_NAMES.index("v2a_attn.in_proj_weight")]
+                tail = st["tail"]
+                a.phase = 1
+                _lib.check(lib.xattn_stage1_step(C.byref(a), _stream_ptr(dev)))
+                if self._side is None or self._side.device != dev:
+                    self._side = torch.cuda.Stream(dev)
+                self._side.wait_stream(torch.cuda.current_stream(dev))     # the tail bucket is final
+                with torch.cuda.stream(self._side):
+                    tail_work = dist.all_reduce(grads[tail:], op=dist.ReduceOp.SUM, group=self.group, async_op=True)
+                a.phase = 2
+                _lib.check(lib.xattn_stage1_step(C.byref(a), _stream_ptr(dev)))
+                dist.all_reduce(grads[:tail], op=dist.ReduceOp.SUM, group=self.group)
+                tail_work.wait()
+                _lib.check(lib.xattn_adam_step(_ptr(flat), _ptr(grads), _ptr(self.exp_avg), _ptr(self.exp_avg_sq), flat.numel(),
+                                               self.lr, self.betas[0], self.betas[1], self.eps, self.weight_decay, self.step_count,
+                                               int(self.decoupled), _stream_ptr(dev)))
             head.mark_parameters_updated()
             self._logits = st["logits"]
             return st["loss"].clone()
 
     def step(self, video_emb: torch.Tensor, audio_emb: torch.Tensor, labels: torch.Tensor, training: bool = True) -> torch.Tensor:
         """One full Stage-1 step; returns this rank's mean loss as a 0-dim CUDA tensor (no host sync)."""
-        use_graph = self.graph if self.graph is not None else self._world() <= 1
-        if use_graph and self._world() <= 1 and video_emb.is_cuda:
+        use_graph = self.graph if self.graph is not None else True
+        if use_graph and video_emb.is_cuda and (self._world() <= 1 or self.overlap_allreduce):
             if self.step_count == 0:   # first step eagerly: one-time function attributes and tensor maps are set outside a capture
                 loss = self.forward_backward(video_emb, audio_emb, labels, training=training)
+                self.allreduce_gradients()
                 self.optimizer_step()
                 return loss
             return self._fused_step(video_emb, audio_emb, labels, training)

@@ -108,3 +108,61 @@ def test_two_rank_nccl_step_equals_single_rank_step(cuda_device, tmp_path, bucke
     for r, p in enumerate(got["params"]):
         assert (p - p_full).abs().max().item() <= PARAM_TOL, (r, (p - p_full).abs().max().item())
     assert torch.equal(got["params"][0], got["params"][1])      # replicas stay bit-identical
+
+
+def _rank_main_steps(rank, world, port, B, steps, out_path):
+    import torch.distributed as dist
+
+    from multimodalemotionrecognition_b200.training import Stage1Trainer, shard_range
+
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world), LOCAL_RANK=str(rank))
+    torch.cuda.set_device(rank)
+    dev = torch.device("cuda", rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=dev)
+    try:
+        s, e = shard_range(B, rank, world)
+        m = make_head("concat", True, seed=0, precision="tf32").to(dev).train()
+        tr = Stage1Trainer(m, lr=1e-3, weight_decay=1e-4, eps=1e-3)            # graph on: two graphs around the all-reduce
+        losses = []
+        for k in range(steps):
+            xv, xa, lab = _batch(B, seed=21 + (k % 2))
+            losses.append(tr.step(xv[s:e].bfloat16().to(dev), xa[s:e].bfloat16().to(dev), lab[s:e].to(dev), training=False))
+        torch.cuda.synchronize(dev)
+        flat = m.flat_parameters().detach()
+        gathered = [torch.empty_like(flat) for _ in range(world)]
+        dist.all_gather(gathered, flat)
+        lt = torch.stack(losses)
+        dist.all_reduce(lt)
+        if rank == 0:
+            torch.save({"params": [t.cpu() for t in gathered], "mean_losses": (lt / world).cpu()}, out_path)
+    finally:
+        dist.destroy_process_group()
+
+
+def test_two_rank_graphed_steps_track_the_single_rank_separate_calls(cuda_device, tmp_path):
+    """Four data-parallel tf32 steps on two GPUs — the first through the separate calls, the rest through the two CUDA graphs of
+    ``xattn_stage1_step`` (phase 1 | tail-bucket all-reduce beside phase 2 | head-bucket all-reduce | Adam) — against four
+    single-rank steps on the whole batch through the separate calls: losses and parameters."""
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs (gpurun --gpus 2)")
+    import torch.multiprocessing as mp
+
+    from multimodalemotionrecognition_b200.training import Stage1Trainer
+
+    B, world, steps = 48, 2, 4
+    out_path = str(tmp_path / "ranks_steps.pt")
+    mp.spawn(_rank_main_steps, args=(world, _free_port(), B, steps, out_path), nprocs=world, join=True)
+    got = torch.load(out_path)
+    m = make_head("concat", True, seed=0, precision="tf32").to(cuda_device).train()
+    tr = Stage1Trainer(m, lr=1e-3, weight_decay=1e-4, eps=1e-3, graph=False)
+    ref = []
+    for k in range(steps):
+        xv, xa, lab = _batch(B, seed=21 + (k % 2))
+        ref.append(float(tr.step(xv.bfloat16().to(cuda_device), xa.bfloat16().to(cuda_device), lab.to(cuda_device), training=False)))
+    p_full = m.flat_parameters().detach().cpu()
+    for k in range(steps):
+        assert abs(float(got["mean_losses"][k]) - ref[k]) <= 2e-4 * max(1.0, abs(ref[k])), (k, float(got["mean_losses"][k]), ref[k])
+    assert ref[-1] < ref[0]
+    for r, p in enumerate(got["params"]):
+        assert (p - p_full).abs().max().item() <= 1e-3, (r, (p - p_full).abs().max().item())
+    assert torch.equal(got["params"][0], got["params"][1])      # replicas stay bit-identical
