@@ -578,7 +578,7 @@ def run_train(cx: Ctx, args) -> None:
         "hbm": {"algorithmic_bytes_per_clip": BYTES_TRAIN_BF16, "gbs": gbs, "frac": gbs / peaks["hbm_gbs"]},
         "stages": stages, "unbracketed_ms_per_step": ms_local,
         "note": "per-kernel times of the step: profiles/ ncu launch list (README); phases here are CUDA-event brackets of a second pass "
-                "with a synchronous all-reduce",
+                "through the SEPARATE calls (eager launches, synchronous all-reduce): they sum to more than the graphed step",
     }
     # e2e: pinned host embeddings + labels in, loss out
     hv = torch.empty((B, T, DV), dtype=torch.bfloat16).pin_memory()
@@ -613,6 +613,9 @@ def run_train(cx: Ctx, args) -> None:
                               ("NCCL all-reduce of the flat fp32 gradient bucket (398,581 floats) in two buckets: attention / norm / "
                                "head / prior gradients on a side stream beside the input-projection backward, then the input projections"
                                if not args.no_overlap else "one NCCL all-reduce of the flat fp32 gradient bucket after the backward"))
+        line["step_api"] = ("Stage1Trainer.step -> xattn_stage1_step: the step's launches captured every step and replayed as CUDA graph(s) "
+                            "(cudaGraphExecUpdate; one graph on a single rank, two around the overlapped all-reduce)"
+                            if (cx.world == 1 or not args.no_overlap) else "Stage1Trainer.step, separate calls (--no-overlap)")
         line.update({"roofline": roofline, "e2e": e2e, "cpu_baseline": cpu})
         print(json.dumps(line), flush=True)
 
