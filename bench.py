@@ -586,24 +586,45 @@ def run_train(cx: Ctx, args) -> None:
     hl = torch.empty((B,), dtype=torch.int64).pin_memory()
     hv.copy_(sets[0][0]); ha.copy_(sets[0][1]); hl.copy_(sets[0][2])
 
+    from multimodalemotionrecognition_b200.training import HostBatchPrefetcher
+
     def e2e_step():
         dv = hv.to(dev, non_blocking=True)
         da = ha.to(dev, non_blocking=True)
         dl = hl.to(dev, non_blocking=True)
         return float(tr.step(dv, da, dl, training=True))     # .item(): the loss comes back to the host every step (train.py:230)
 
+    pre = HostBatchPrefetcher(dev)
+
+    def e2e_step_prefetch():   # the copy of the NEXT batch is in flight while this one trains; still one .item() per step
+        dv, da, dl = pre.get()
+        loss = tr.step(dv, da, dl, training=True)
+        pre.release()
+        pre.put(hv, ha, hl)
+        return float(loss)
+
+    def timed(fn, n):
+        cx.barrier()
+        t0 = time.perf_counter()
+        for _ in range(n):
+            fn()
+        cx.barrier()
+        return cx.max_over_ranks(time.perf_counter() - t0)
+
+    e2e_steps = max(3, min(args.steps, 20))
     for _ in range(3):
         e2e_step()
-    cx.barrier()
-    e2e_steps = max(3, min(args.steps, 20))
-    t0 = time.perf_counter()
-    for _ in range(e2e_steps):
-        e2e_step()
-    cx.barrier()
-    dt = cx.max_over_ranks(time.perf_counter() - t0)
+    dt_serial = timed(e2e_step, e2e_steps)
+    pre.put(hv, ha, hl)
+    for _ in range(3):
+        e2e_step_prefetch()
+    dt = timed(e2e_step_prefetch, e2e_steps)
     e2e = {"value": B * cx.world * e2e_steps / dt, "unit": "clips/s", "ms_per_step": dt / e2e_steps * 1e3,
            "h2d_bytes_per_step": ((hv.numel() + ha.numel()) * 2 + hl.numel() * 8) * cx.world, "d2h_bytes_per_step": 4 * cx.world,
-           "steps": e2e_steps, "api": "Stage1Trainer.step on tensors copied from pinned host memory; loss read back with .item()"}
+           "steps": e2e_steps,
+           "api": "HostBatchPrefetcher (pinned host -> device copy of the next batch beside the step) + Stage1Trainer.step; loss read "
+                  "back with .item() every step",
+           "serial_copy_then_step": {"value": B * cx.world * e2e_steps / dt_serial, "ms_per_step": dt_serial / e2e_steps * 1e3}}
     cpu = None
     if cx.rank == 0 and cx.world == 1 and not args.no_cpu_baseline:
         cpu, _ = cpu_baseline(args, budget_s=20.0, steps=20, warmup=1)

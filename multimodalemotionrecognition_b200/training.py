@@ -218,6 +218,55 @@ class Stage1Trainer:
         return loss
 
 
+class HostBatchPrefetcher:
+    """Host -> device double buffering for the Stage-1 loop when the embeddings come from (pinned) host memory: the copy of
+    batch i+1 runs on its own stream while batch i trains, so a step costs max(copy, compute) instead of their sum (at B=1024 the
+    251 MB of bf16 embeddings take 4.6 ms over PCIe against 1.6 ms of compute).  ``put`` enqueues the copies of the next batch;
+    ``get`` makes the current stream wait for them and returns the device tensors, which stay valid until the second ``put``
+    after it (two buffer sets, alternating)."""
+
+    def __init__(self, device) -> None:
+        self.device = torch.device(device)
+        self.stream = torch.cuda.Stream(self.device)
+        self._slots = [None, None]
+        self._ready = [torch.cuda.Event(), torch.cuda.Event()]
+        self._freed = [None, None]
+        self._n = 0
+        self._pending = None
+
+    def put(self, *host_tensors: torch.Tensor) -> None:
+        k = self._n & 1
+        self._n += 1
+        slot = self._slots[k]
+        if slot is None or any(d.shape != h.shape or d.dtype != h.dtype for d, h in zip(slot, host_tensors)):
+            slot = tuple(torch.empty(h.shape, dtype=h.dtype, device=self.device) for h in host_tensors)
+            self._slots[k] = slot
+            self.stream.wait_stream(torch.cuda.current_stream(self.device))   # (the allocator may recycle memory still in use there)
+        with torch.cuda.stream(self.stream):
+            if self._freed[k] is not None:            # the step that read this slot two batches ago has finished with it
+                self.stream.wait_event(self._freed[k])
+            for d, h in zip(slot, host_tensors):
+                d.copy_(h, non_blocking=True)
+            self._ready[k].record(self.stream)
+        self._pending = k
+
+    def get(self):
+        k = self._pending
+        if k is None:
+            raise RuntimeError("HostBatchPrefetcher.get() without a put()")
+        cur = torch.cuda.current_stream(self.device)
+        cur.wait_event(self._ready[k])
+        self._last = k
+        return self._slots[k]
+
+    def release(self) -> None:
+        """Call after the step that consumed the last ``get`` has been enqueued: marks the point after which its slot may be
+        overwritten."""
+        ev = torch.cuda.Event()
+        ev.record(torch.cuda.current_stream(self.device))
+        self._freed[self._last] = ev
+
+
 class FrozenEmbeddingCache:
     """Backbone outputs of a Stage-1 dataset, resident in HBM in the dtype the tensor-core kernels read.
 

@@ -100,3 +100,30 @@ def test_training_step_on_a_non_default_stream(cuda_device, precision):
     tol = 1e-6 if precision == "fp32" else 2e-5
     for n, g0 in grads[0].items():
         assert (g0 - grads[1][n]).abs().max().item() <= tol * max(1.0, g0.abs().max().item()), n
+
+
+def test_host_batch_prefetcher_delivers_each_batch_once_and_intact(cuda_device):
+    """HostBatchPrefetcher: the copy of batch i+1 runs beside the work on batch i; every ``get`` returns exactly the batch of the
+    matching ``put``, also when the consumer is slow (a long kernel between get and release) or fast."""
+    from multimodalemotionrecognition_b200.training import HostBatchPrefetcher
+
+    g = torch.Generator().manual_seed(3)
+    host = [(torch.randn(64, 149, 768, generator=g).bfloat16().pin_memory(), torch.randint(0, 8, (64,), generator=g).pin_memory())
+            for _ in range(5)]
+    pre = HostBatchPrefetcher(cuda_device)
+    pre.put(*host[0])
+    sums = []
+    big = torch.randn(4096, 4096, device=cuda_device)
+    for i in range(5):
+        x, lab = pre.get()
+        if i % 2 == 0:
+            big = big @ big * 1e-4                # a slow consumer: the next copy must not overtake the read below
+        sums.append((x.float().sum(), lab.sum(), x[7, 3, :5].float().clone()))
+        pre.release()
+        if i + 1 < 5:
+            pre.put(*host[i + 1])
+    torch.cuda.synchronize(cuda_device)
+    for i, (s, ls, piece) in enumerate(sums):
+        assert abs(float(s) - float(host[i][0].float().sum())) <= 1e-2 * max(1.0, abs(float(s))), i
+        assert int(ls) == int(host[i][1].sum()), i
+        assert torch.equal(piece.cpu(), host[i][0][7, 3, :5].float()), i
