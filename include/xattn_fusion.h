@@ -26,7 +26,7 @@
 extern "C" {
 #endif
 
-#define XATTN_ABI_VERSION 20
+#define XATTN_ABI_VERSION 21
 
 #if defined(__GNUC__)
 #define XATTN_API __attribute__((visibility("default")))
@@ -300,6 +300,13 @@ typedef struct flat_head_config {
   int32_t precision;        /* XATTN_DTYPE_F32: fp32 SIMT arithmetic; XATTN_DTYPE_BF16: temporal mean -> bf16, every Linear
                                of width >= 128 on the tcgen05 projection GEMM (bf16 embeddings, dims %% 64 / %% 128);
                                XATTN_PREC_TF32: fp32 arithmetic with the Linears on tcgen05 tf32 where dims allow  */
+  /* training (precision F32 / TF32 only; fusion.py:246, :255, :430): */
+  int32_t training;         /* 1: Dropout(p_drop) behind the hidden layer's ReLU (fusion.2 / gate.2) is active (Philox)       */
+  int32_t drop_audio;       /* ModalityDropout (fusion.py:29-55, gated mode, training): the caller draws the two host-side   */
+  int32_t drop_video;       /*   Bernoulli decisions as the reference does (torch.rand(1).item() < p) and passes them here    */
+  float p_drop;             /* 0.2 in the reference                                                                           */
+  uint64_t seed;            /* Philox seed / offset of the hidden-layer dropout                                               */
+  uint64_t offset;
 } flat_head_config;
 
 typedef enum flat_param_id {
@@ -324,9 +331,17 @@ XATTN_API int flat_head_param_layout(const flat_head_config* cfg, int64_t* offse
 XATTN_API int flat_head_workspace_bytes(const flat_head_config* cfg, int64_t* bytes);
 /* logits[B,C] for mode in {"concat","gated"} with the temporal mean (the parameter-free last step
  * of audio_model.encode / video_model.encode, fusion.py:414-415) fused in.  Replaces
- * fusion.py:413-435 (+ :137-139).  Eval mode (ModalityDropout / Dropout identity). */
+ * fusion.py:413-435 (+ :137-139).  cfg->training = 0: eval mode (ModalityDropout / Dropout identity); 1 (precision F32 / TF32):
+ * the hidden Dropout and the caller's ModalityDropout decisions apply, and the workspace keeps what flat_head_backward reads. */
 XATTN_API int flat_head_forward(const flat_head_config* cfg, const float* params, const void* video_emb, const void* audio_emb,
                       float* logits, void* workspace, int64_t workspace_bytes, void* stream);
+/* Backward of flat_head_forward (precision F32 / TF32; `workspace` is the buffer that forward filled, same cfg): the part of
+ * loss.backward() (train.py:227) that runs through fusion.py:413-435.  grads (flat, flat_head_param_layout) is OVERWRITTEN.
+ * d_video_emb [B,T,Dv] / d_audio_emb [B,Ta,Da] (fp32, may be NULL): gradients w.r.t. the embeddings — the temporal mean spreads
+ * d_pooled / L over the tokens — for trainable backbones. */
+XATTN_API int flat_head_backward(const flat_head_config* cfg, const float* params, const void* video_emb, const void* audio_emb,
+                       const float* dlogits, float* grads, float* d_video_emb, float* d_audio_emb, void* workspace,
+                       int64_t workspace_bytes, void* stream);
 
 /* Serving epilogue (optimized_runtime.py:99-108 softmax(dim=1); inference_worker.py:136-143 row.argmax() and the probability at
  * it) in one launch: probs[B,C] = softmax(logits) (may alias logits; NULL to skip), top1[B] = first maximal class, top1_prob[B]
@@ -348,6 +363,15 @@ XATTN_API int xattn_mel_unfold(const void* mel, void* unfolded, int32_t io_dtype
 XATTN_API int flat_head_alignment_workspace_bytes(const flat_head_config* cfg, int64_t* bytes);
 XATTN_API int flat_head_alignment_loss(const flat_head_config* cfg, const float* params, const float* logit_scale, const void* video_emb,
                                        const void* audio_emb, float* loss, void* workspace, int64_t workspace_bytes, void* stream);
+/* Backward of flat_head_alignment_loss: `dloss` is a DEVICE scalar (the upstream gradient, fusion_align_weight · dL, train.py:225).
+ * grads (flat, flat_head_param_layout) is OVERWRITTEN: the four semantic_alignment.*_proj entries hold their gradients, everything
+ * else zero; *d_logit_scale (device scalar) the gradient of semantic_alignment.logit_scale (zero where exp(logit_scale) is clamped
+ * at 100).  d_video_emb / d_audio_emb as in flat_head_backward (may be NULL).  Recomputes the forward quantities: needs only the
+ * workspace size of flat_head_alignment_workspace_bytes, not the forward call's buffer. */
+XATTN_API int flat_head_alignment_backward(const flat_head_config* cfg, const float* params, const float* logit_scale,
+                                 const void* video_emb, const void* audio_emb, const float* dloss, float* grads,
+                                 float* d_logit_scale, float* d_video_emb, float* d_audio_emb, void* workspace,
+                                 int64_t workspace_bytes, void* stream);
 
 /* Backbone tail -> head hand-off (fusion.py:368-370, :377; video.py:23 AdaptiveAvgPool2d; wavlm_audio.py:183 last_hidden_state).
  * x fp32 [n_clips · rows_per_clip, D, R] -> the mean over the R innermost values (R = h·w of ResNet18's last feature map, R = 1

@@ -13,7 +13,7 @@ from pathlib import Path
 LIB_NAME = "libxattn_fusion.so"
 LIB_PATH = Path(__file__).resolve().parent / LIB_NAME
 DEBUG_LIB_PATH = Path(__file__).resolve().parent / "libxattn_fusion_debug.so"
-ABI_VERSION = 20
+ABI_VERSION = 21
 
 # xattn_status
 OK, ERR_SHAPE, ERR_DTYPE, ERR_ALIGN, ERR_ARCH, ERR_CUDA, ERR_WORKSPACE, ERR_NULL = range(8)
@@ -96,7 +96,8 @@ class XAttnStepArgs(C.Structure):
 
 class FlatHeadConfig(C.Structure):
     _fields_ = [(n, C.c_int32) for n in ("B", "T", "Ta", "Dv", "Da", "align_dim", "common_dim", "C", "gated", "io_dtype",
-                                                 "precision")]
+                                                 "precision", "training", "drop_audio", "drop_video")] + [
+        ("p_drop", C.c_float), ("seed", C.c_uint64), ("offset", C.c_uint64)]
 
 
 _EXPORTS = {
@@ -137,6 +138,10 @@ _EXPORTS = {
     "xattn_mel_unfold": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_void_p]),
     "flat_head_forward": (C.c_int, [C.POINTER(FlatHeadConfig), C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
                                     C.c_int64, C.c_void_p]),
+    "flat_head_backward": (C.c_int, [C.POINTER(FlatHeadConfig), C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
+                                     C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p]),
+    "flat_head_alignment_backward": (C.c_int, [C.POINTER(FlatHeadConfig), C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
+                                               C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p]),
 }
 # test-only entry points of libxattn_fusion_debug.so (include/xattn_fusion_debug.h); the product library does not export them
 _DEBUG_EXPORTS = {

@@ -237,6 +237,7 @@ __device__ __forceinline__ void drop_factor4(float p, uint64_t seed, uint64_t of
   f[3] = (float)(r.w >> 8) * sc < p ? 0.f : keep;
 }
 enum : uint32_t { RS_ATTN1 = 1, RS_ATTN2 = 2, RS_PATH1 = 3, RS_PATH2 = 4, RS_HEAD = 5, RS_PRIOR = 6, RS_POOLV = 7, RS_POOLA = 8,
+                  RS_FLAT = 9,   // hidden-layer Dropout of the flat concat / gated heads
                   RS_TX_BASE = 16 };   // transformer pooler: RS_TX_BASE + (side·XATTN_MAX_POOL_LAYERS + layer)·4 + {attn, drop1, ffn, drop2}
 __host__ __device__ inline uint32_t rs_tx(int side, int layer, int which) {
   return RS_TX_BASE + (uint32_t)((side * XATTN_MAX_POOL_LAYERS + layer) * 4 + which);

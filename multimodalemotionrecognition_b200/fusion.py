@@ -742,8 +742,70 @@ class ClipStyleAlignment(nn.Module):
         self.logit_scale = nn.Parameter(torch.tensor(math.log(1.0 / safe_temp), dtype=torch.float32))
 
 
+class _FlatFunction(torch.autograd.Function):
+    """Autograd bridge of the flat concat / gated heads: forward keeps its activations in the kernel workspace, backward calls
+    ``flat_head_backward`` (flat gradient buffer -> one view per parameter; input gradients when the embeddings require them)."""
+
+    @staticmethod
+    def forward(ctx, owner, video_emb, audio_emb, *params):
+        logits, state = owner._flat_launch_forward(video_emb, audio_emb, save=True)
+        ctx.owner, ctx.state = owner, state
+        return logits
+
+    @staticmethod
+    def backward(ctx, dlogits):
+        owner = ctx.owner
+        cfg, video_emb, audio_emb, ws, flat = ctx.state
+        dev = video_emb.device
+        need_v, need_a = ctx.needs_input_grad[1], ctx.needs_input_grad[2]
+        with torch.cuda.device(dev):
+            grads = torch.empty_like(flat)
+            dv = torch.empty(video_emb.shape, dtype=torch.float32, device=dev) if need_v else None
+            da = torch.empty(audio_emb.shape, dtype=torch.float32, device=dev) if need_a else None
+            dl = dlogits.contiguous().float()
+            _lib.check(_lib.load().flat_head_backward(C.byref(cfg), _ptr(flat), _ptr(video_emb), _ptr(audio_emb), _ptr(dl), _ptr(grads),
+                                                      _ptr(dv), _ptr(da), _ptr(ws), ws.numel(), _stream_ptr(dev)))
+        out = [grads[off:off + n].view(shape) if n > 0 else None for off, n, shape in owner._flat_slices]
+        ctx.state = None
+        return (None, None if dv is None else dv.to(video_emb.dtype), None if da is None else da.to(audio_emb.dtype), *out)
+
+
+class _FlatAlignFunction(torch.autograd.Function):
+    """Autograd bridge of the ClipStyleAlignment loss (``fusion.py:141-149``): ``flat_head_alignment_loss`` forward,
+    ``flat_head_alignment_backward`` backward (gradients of the two alignment projections, ``logit_scale`` and the embeddings)."""
+
+    @staticmethod
+    def forward(ctx, owner, video_emb, audio_emb, logit_scale, *align_params):
+        loss, state = owner._flat_launch_alignment(video_emb, audio_emb)
+        ctx.owner, ctx.state = owner, state
+        return loss
+
+    @staticmethod
+    def backward(ctx, dloss):
+        owner = ctx.owner
+        cfg, video_emb, audio_emb, flat, scale = ctx.state
+        dev = video_emb.device
+        need_v, need_a = ctx.needs_input_grad[1], ctx.needs_input_grad[2]
+        with torch.cuda.device(dev):
+            n = C.c_int64()
+            _lib.check(_lib.load().flat_head_alignment_workspace_bytes(C.byref(cfg), C.byref(n)))
+            ws = torch.empty(n.value, dtype=torch.uint8, device=dev)
+            grads = torch.empty_like(flat)
+            dscale = torch.empty((), dtype=torch.float32, device=dev)
+            dv = torch.empty(video_emb.shape, dtype=torch.float32, device=dev) if need_v else None
+            da = torch.empty(audio_emb.shape, dtype=torch.float32, device=dev) if need_a else None
+            g = dloss.detach().to(device=dev, dtype=torch.float32).contiguous()
+            _lib.check(_lib.load().flat_head_alignment_backward(C.byref(cfg), _ptr(flat), _ptr(scale), _ptr(video_emb), _ptr(audio_emb),
+                                                                _ptr(g), _ptr(grads), _ptr(dscale), _ptr(dv), _ptr(da), _ptr(ws),
+                                                                ws.numel(), _stream_ptr(dev)))
+        out = [grads[off:off + n_].view(shape) for off, n_, shape in owner._flat_slices[:4]]   # FP_ALIGN_A_W .. FP_ALIGN_V_B
+        ctx.state = None
+        return (None, None if dv is None else dv.to(video_emb.dtype), None if da is None else da.to(audio_emb.dtype), dscale, *out)
+
+
 class FlatHeadKernelsMixin:
-    """``mode in {"concat","gated"}`` heads (``fusion.py:226-260``, ``:413-435``) on the CUDA extension (eval forward)."""
+    """``mode in {"concat","gated"}`` heads (``fusion.py:226-260``, ``:413-435``) on the CUDA extension: eval and training forward
+    (hidden-layer ``Dropout(0.2)``, ``ModalityDropout`` in gated mode), backward and the alignment loss with its backward."""
 
     def _build_flat(self, *, audio_dim: int, video_dim: int, num_classes: int, common_dim: int, mode: str,
                     fusion_align_mode: str, fusion_align_dim: int, fusion_align_temperature: float,
@@ -783,6 +845,25 @@ class FlatHeadKernelsMixin:
         cfg.align_dim, cfg.common_dim, cfg.C = self._flat_align, self._flat_common, self._flat_classes
         cfg.gated, cfg.io_dtype = int(self._flat_gated), io_dtype
         cfg.precision = self._flat_pick_precision(io_dtype)
+        return cfg
+
+    flat_dropout_p = 0.2            # nn.Dropout(0.2) of fusion.2 / gate.2 (fusion.py:246, :255)
+    modality_dropout_p = (0.2, 0.2)  # ModalityDropout(audio_dropout_p, video_dropout_p) (fusion.py:251)
+
+    def _flat_train_cfg(self, cfg: _lib.FlatHeadConfig) -> _lib.FlatHeadConfig:
+        """Training-mode fields of a config: fp32 kernels, the Philox state of the hidden-layer dropout, and — gated mode — the two
+        ModalityDropout decisions, drawn exactly as the reference draws them (``torch.rand(1).item() < p``, audio first;
+        ``fusion.py:47-53``), so the same torch seed drops the same modalities."""
+        if cfg.precision == _lib.DTYPE_BF16:
+            cfg.precision = _lib.DTYPE_F32
+        if self.training:
+            cfg.training = 1
+            cfg.p_drop = float(self.flat_dropout_p)
+            self._flat_rng_offset = getattr(self, "_flat_rng_offset", 0) + 1
+            cfg.seed, cfg.offset = torch.initial_seed() & 0xFFFFFFFFFFFFFFFF, self._flat_rng_offset
+            if self._flat_gated:
+                cfg.drop_audio = int(torch.rand(1).item() < self.modality_dropout_p[0])
+                cfg.drop_video = int(torch.rand(1).item() < self.modality_dropout_p[1])
         return cfg
 
     def _flat_tc_supported(self) -> bool:
@@ -825,7 +906,12 @@ class FlatHeadKernelsMixin:
                     view.copy_(p.detach().to(device=dev, dtype=torch.float32))
                     p.data = view
             self._flat_buf = flat
+        self._flat_slices = [(off, n, tuple(own[name].shape) if n else ()) for name, off, n in zip(names, offs, sizes)]
         return self._flat_buf
+
+    def _flat_named_params(self) -> list:
+        own = dict(self.named_parameters(recurse=True))
+        return [own[name] if n else None for name, (off, n, _) in zip(_lib.flat_param_names(self._flat_gated), self._flat_slices)]
 
     def flat_forward_sequences(self, video_emb: torch.Tensor, audio_emb: torch.Tensor) -> torch.Tensor:
         """logits from sequence embeddings [B,T,Dv] / [B,Ta,Da]; the temporal mean is fused into the kernels."""
@@ -837,23 +923,47 @@ class FlatHeadKernelsMixin:
             raise ValueError("embedding dims do not match the head")
         if video_emb.dtype != audio_emb.dtype or video_emb.shape[0] != audio_emb.shape[0]:
             raise ValueError("video_emb / audio_emb must share dtype and batch size")
-        video_emb, audio_emb = video_emb.contiguous(), audio_emb.contiguous()
+        flat = self._flat_params(video_emb.device)
+        params = self._flat_named_params()
+        need_grad = torch.is_grad_enabled() and (video_emb.requires_grad or audio_emb.requires_grad or
+                                                 any(p is not None and p.requires_grad for p in params))
+        if need_grad:
+            return _FlatFunction.apply(self, video_emb, audio_emb, *[p for p in params])
+        if self.training:
+            return self._flat_launch_forward(video_emb, audio_emb, save=True)[0]
+        return self._flat_launch_forward(video_emb, audio_emb, save=False)[0]
+
+    def _flat_launch_forward(self, video_emb: torch.Tensor, audio_emb: torch.Tensor, save: bool):
+        """``flat_head_forward``.  ``save``: the fp32 kernels with the training-mode fields (their workspace is what
+        ``flat_head_backward`` reads); else the inference path (bf16 tensor cores where the dimensions allow)."""
+        video_emb, audio_emb = video_emb.detach().contiguous(), audio_emb.detach().contiguous()
         dev = video_emb.device
         with torch.cuda.device(dev):
             cfg = self._flat_cfg(video_emb.shape[0], video_emb.shape[1], audio_emb.shape[1], _io_dtype(video_emb))
+            if save:
+                cfg = self._flat_train_cfg(cfg)
             flat = self._flat_params(dev)
             ws = torch.empty(_lib.flat_workspace_bytes(cfg), dtype=torch.uint8, device=dev)
             logits = torch.empty((cfg.B, cfg.C), dtype=torch.float32, device=dev)
             _lib.check(_lib.load().flat_head_forward(C.byref(cfg), _ptr(flat), _ptr(video_emb), _ptr(audio_emb), _ptr(logits),
                                                      _ptr(ws), ws.numel(), _stream_ptr(dev)))
-        return logits
+        return logits, (cfg, video_emb, audio_emb, ws, flat)
 
-    @torch.no_grad()
     def flat_alignment_loss(self, video_emb: torch.Tensor, audio_emb: torch.Tensor) -> torch.Tensor:
         """The CLIP-style alignment loss of ``ClipStyleAlignment.forward`` (``fusion.py:141-149``) for a batch of sequence
         ``[B,T,Dv]`` / ``[B,Ta,Da]`` (or pooled ``[B,1,D]``) embeddings: a 0-dim CUDA tensor, no host sync.  It is a B x B
-        cross-sample term — under batch sharding gather the embeddings first.  Forward value only (the flat
-        heads are inference-only here)."""
+        cross-sample term — under batch sharding gather the embeddings first.  Differentiable (alignment projections,
+        ``logit_scale``, embeddings) when autograd is recording."""
+        sa = self.semantic_alignment
+        if sa is not None and torch.is_grad_enabled() and (
+                video_emb.requires_grad or audio_emb.requires_grad or any(p.requires_grad for p in sa.parameters())):
+            self._flat_params(video_emb.device)
+            return _FlatAlignFunction.apply(self, video_emb, audio_emb, sa.logit_scale, sa.audio_proj.weight, sa.audio_proj.bias,
+                                            sa.video_proj.weight, sa.video_proj.bias)
+        return self._flat_launch_alignment(video_emb, audio_emb)[0]
+
+    @torch.no_grad()
+    def _flat_launch_alignment(self, video_emb: torch.Tensor, audio_emb: torch.Tensor):
         if self.semantic_alignment is None:
             raise ValueError("the alignment loss needs fusion_align_mode=\"clip\"")
         if video_emb.ndim != 3 or audio_emb.ndim != 3 or video_emb.shape[0] != audio_emb.shape[0] or video_emb.shape[0] == 0:
@@ -862,7 +972,7 @@ class FlatHeadKernelsMixin:
             raise RuntimeError("the B200 flat fusion heads have no CPU path: inputs must be CUDA tensors")
         if video_emb.dtype != audio_emb.dtype:
             raise ValueError("video_emb / audio_emb must share dtype")
-        video_emb, audio_emb = video_emb.contiguous(), audio_emb.contiguous()
+        video_emb, audio_emb = video_emb.detach().contiguous(), audio_emb.detach().contiguous()
         dev = video_emb.device
         with torch.cuda.device(dev):
             cfg = self._flat_cfg(video_emb.shape[0], video_emb.shape[1], audio_emb.shape[1], _io_dtype(video_emb))
@@ -878,7 +988,7 @@ class FlatHeadKernelsMixin:
             scale = self.semantic_alignment.logit_scale.detach().to(device=dev, dtype=torch.float32).contiguous()
             _lib.check(_lib.load().flat_head_alignment_loss(C.byref(cfg), _ptr(flat), _ptr(scale), _ptr(video_emb), _ptr(audio_emb),
                                                             _ptr(loss), _ptr(ws), ws.numel(), _stream_ptr(dev)))
-        return loss
+        return loss, (cfg, video_emb, audio_emb, flat, scale)
 
     def flat_forward_pooled(self, audio_pooled: torch.Tensor, video_pooled: torch.Tensor) -> torch.Tensor:
         """logits from already pooled [B,Da] / [B,Dv] embeddings (what ``audio_model.encode`` returns)."""
@@ -976,8 +1086,6 @@ class FusionModel(XAttnKernelsMixin, FlatHeadKernelsMixin, nn.Module):
             a_seq = self.audio_model.encode_sequence(audio)                                          # fusion.py:377
             return self.xattn_forward_embeddings(v_feat, a_seq)
         if self.mode in {"concat", "gated"}:
-            if self.training:
-                raise RuntimeError("the B200 flat concat/gated heads are inference-only (eval forward, BASELINE config 5)")
             a_emb = self.audio_model.encode(audio)                                                   # fusion.py:414-415
             v_emb = self.video_model.encode(video)
             if self.semantic_alignment is not None:

@@ -228,6 +228,76 @@ def gen_mel(FusionModel) -> None:
     np.savez_compressed(OUT / "xattn_mel.npz", **blob)
 
 
+def gen_flat_train(FusionModel) -> None:
+    """Trainable flat concat / gated heads (fusion.py:226-260, :413-435, :29-55, :127-150; train.py:218-227): logits, CE loss,
+    alignment loss and the gradients of ``CE + 0.1 * alignment`` w.r.t. every parameter and both (sequence) inputs — eval mode, and
+    training mode with the hidden Dropout's p set to 0 on the instance (torch's mask cannot be reproduced) for torch seeds whose two
+    ``torch.rand(1)`` draws make ModalityDropout drop the audio, the video, both and neither.  Tiny dimensions stored in full;
+    BASELINE config-5 dimensions by digest (+ the small tensors in full)."""
+    blob = {}
+
+    def run(m, xv, xa, labels, tag):
+        m.zero_grad(set_to_none=True)
+        xv = xv.clone().requires_grad_(True)
+        xa = xa.clone().requires_grad_(True)
+        logits = m(xv.mean(dim=1), xa.mean(dim=1))
+        cls = nn.functional.cross_entropy(logits, labels)
+        align = m.pop_alignment_loss()
+        total = cls + 0.1 * align
+        total.backward()
+        blob[f"{tag}:logits"] = logits.detach().numpy()
+        blob[f"{tag}:cls"] = cls.detach().numpy()
+        blob[f"{tag}:align"] = align.detach().numpy()
+        return {k: p.grad.detach().clone() for k, p in m.named_parameters() if p.grad is not None}, xv.grad.clone(), xa.grad.clone()
+
+    for mode in ("concat", "gated"):
+        torch.manual_seed(40)
+        m = build_ref(FusionModel, dv=12, da=10, d_model=8, heads=2, head="concat", prior=False, mode=mode, align="clip", common=16)
+        g = torch.Generator().manual_seed(41)
+        xa = torch.randn(5, 5, 10, generator=g)
+        xv = torch.randn(5, 4, 12, generator=g)
+        labels = torch.randint(0, 8, (5,), generator=g)
+        blob.update({f"tiny_{mode}:xa": xa.numpy(), f"tiny_{mode}:xv": xv.numpy(), f"tiny_{mode}:labels": labels.numpy()})
+        blob.update({f"tiny_{mode}:w:" + k: v.numpy() for k, v in fusion_state(m).items()})
+        m.eval()
+        grads, dxv, dxa = run(m, xv, xa, labels, f"tiny_{mode}:eval")
+        blob.update({f"tiny_{mode}:eval:g:" + k: v.numpy() for k, v in grads.items()})
+        blob[f"tiny_{mode}:eval:dxv"], blob[f"tiny_{mode}:eval:dxa"] = dxv.numpy(), dxa.numpy()
+        if mode == "gated":
+            m.gate[2].p = 0.0      # instance attribute only: the hidden Dropout's mask is torch RNG, not reproducible elsewhere
+            m.train()
+            want = {(1, 0): None, (0, 1): None, (1, 1): None, (0, 0): None}
+            for seed in range(400):
+                torch.manual_seed(seed)
+                d = (int(torch.rand(1).item() < 0.2), int(torch.rand(1).item() < 0.2))
+                if want[d] is None:
+                    want[d] = seed
+                if all(v is not None for v in want.values()):
+                    break
+            for (da_, dv_), seed in want.items():
+                tag = f"tiny_gated:train_a{da_}v{dv_}"
+                torch.manual_seed(seed)
+                grads, dxv, dxa = run(m, xv, xa, labels, tag)
+                blob[f"{tag}:seed"] = np.array(seed)
+                blob.update({f"{tag}:g:" + k: v.numpy() for k, v in grads.items()})
+                blob[f"{tag}:dxv"], blob[f"{tag}:dxa"] = dxv.numpy(), dxa.numpy()
+    g = torch.Generator().manual_seed(3)
+    ap = torch.randn(6, 1, 768, generator=g)
+    vp = torch.randn(6, 1, 512, generator=g)
+    labels = torch.randint(0, 8, (6,), generator=torch.Generator().manual_seed(4))
+    blob["c5:labels"] = labels.numpy()
+    for mode in ("concat", "gated"):
+        torch.manual_seed(0)
+        m = build_ref(FusionModel, dv=512, da=768, d_model=128, heads=4, head="concat", prior=False, mode=mode, align="clip").eval()
+        grads, dxv, dxa = run(m, vp, ap, labels, f"c5_{mode}:eval")
+        for k, v in grads.items():
+            blob[f"c5_{mode}:eval:gd:{k}"] = digest(v)
+            if v.numel() <= 2048:
+                blob[f"c5_{mode}:eval:g:{k}"] = v.numpy()
+        blob[f"c5_{mode}:eval:dxv"], blob[f"c5_{mode}:eval:dxa"] = digest(dxv), digest(dxa)
+    np.savez_compressed(OUT / "flat_train.npz", **blob)
+
+
 def main() -> None:
     sys.path.insert(0, REF)
     sys.dont_write_bytecode = True
@@ -235,6 +305,9 @@ def main() -> None:
 
     OUT.mkdir(parents=True, exist_ok=True)
     torch.set_num_threads(1)
+    if "--only-flat-train" in sys.argv:
+        gen_flat_train(FusionModel)
+        return
     if "--only-txpool" in sys.argv:
         gen_txpool(FusionModel)
         return
@@ -246,6 +319,7 @@ def main() -> None:
         return
     gen_mel(FusionModel)
     gen_txpool(FusionModel)
+    gen_flat_train(FusionModel)
 
     # ---- tiny case: everything stored in full (d_model=8, heads=2 as the reference's own shape tests) -------------
     for head in ("concat", "gated"):
