@@ -77,7 +77,7 @@ typedef struct xattn_config {
                                 (gradient parity in eval mode)            */
   int32_t pool_mode;    /* XATTN_POOL_MEAN (temporal.py:108-109) | XATTN_POOL_ATTN (TemporalAttentionPooling,
                            temporal.py:9-26: LN -> Linear -> GELU -> Dropout -> Linear -> softmax over time -> weighted
-                           sum; fp32 / tf32 family, forward and backward)
+                           sum; forward and backward in the fp32 / tf32 family, forward also on the bf16 tensor-core path)
                            XATTN_POOL_TRANSFORMER (TemporalTransformerPooling, temporal.py:46-75: sinusoidal positions,
                            pool_layers pre-norm TransformerEncoderLayers (GELU, FFN = 4·E, dropout p_pool), then the attention
                            pooling; fp32 / tf32 family, forward and backward) */

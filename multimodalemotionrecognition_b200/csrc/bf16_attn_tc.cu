@@ -409,10 +409,12 @@ struct A2VTcArgs {
   const float *tok, *tkv, *pc, *cv;    // [2,B,160], [B,16], [B,4], [B,64]
   const float* bias_scale;
   float* poolp;                        // [B][kPoolSlots][128] partial sums of xhat over a warp's rows
+  __nv_bfloat16* xhat_out;             // [B][Ta][128] the normalised rows themselves (learned pooling, temporal.py:9-26) or nullptr
   int B, Ta, T, use_prior;
   unsigned long long* trace;
 };
 
+template <bool EMIT>   // EMIT: also write the normalised audio rows (A2VTcArgs::xhat_out) for the learned pooling
 __global__ void __launch_bounds__(kA2VThreads, 1) a2v_tc_kernel(const __grid_constant__ CUtensorMap tmA0,
                                                                  const __grid_constant__ CUtensorMap tmKt,
                                                                  const __grid_constant__ CUtensorMap tmVt, A2VTcArgs a) {
@@ -751,6 +753,21 @@ __global__ void __launch_bounds__(kA2VThreads, 1) a2v_tc_kernel(const __grid_con
       const uint64_t rs2 = tc::f2_pack(rs, rs), nmr2 = tc::f2_pack(nmr, nmr);
 #pragma unroll
       for (int i = 0; i < HP; ++i) xp[i] = tc::f2_fma(xp[i], rs2, nmr2);
+      if (EMIT && valid) {   // the learned pooler wants the tokens: this thread's 64 columns of its row, 128 bytes
+        uint4* dst = reinterpret_cast<uint4*>(a.xhat_out + ((int64_t)c * Ta + (R - BTAP * ci)) * BE + HC * hf);
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+          uint32_t w4[4];
+#pragma unroll
+          for (int e = 0; e < 4; ++e) {
+            float lo, hi;
+            tc::f2_unpack(xp[4 * k + e], lo, hi);
+            const __nv_bfloat162 h2 = __floats2bfloat162_rn(lo, hi);
+            w4[e] = *reinterpret_cast<const uint32_t*>(&h2);
+          }
+          dst[k] = make_uint4(w4[0], w4[1], w4[2], w4[3]);
+        }
+      }
       // sum over the warp's 32 rows: butterfly, the live columns halve at every step (pairs stay pairs down to the last step)
 #pragma unroll
       for (int off = 16, cnt = HP / 2; off >= 1; off >>= 1, cnt >>= 1) {
@@ -851,6 +868,7 @@ int launch_a2v_tc(const Bf16Ctx& x) {
   a.cv = reinterpret_cast<const float*>(x.ws + x.w.cv);
   a.bias_scale = P(XP_BIAS_SCALE);
   a.poolp = reinterpret_cast<float*>(x.ws + x.w.poolp);
+  a.xhat_out = c.pool_mode == XATTN_POOL_ATTN ? reinterpret_cast<__nv_bfloat16*>(x.ws + x.w.xhat) : nullptr;
   a.B = c.B; a.Ta = c.Ta; a.T = c.T; a.use_prior = c.use_prior;
   a.trace = nullptr;
   static unsigned long long* trace_buf = nullptr;
@@ -866,12 +884,16 @@ int launch_a2v_tc(const Bf16Ctx& x) {
   XF_TRY(make_tmap_bf16_2d(&tmVt, x.ws + x.w.vt, (int64_t)c.B * 64, BE, 64, 64, BOP));
   static bool configured = false;
   if (!configured) {
-    XF_CUDA(cudaFuncSetAttribute(a2v_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kA2VSmem));
+    XF_CUDA(cudaFuncSetAttribute(a2v_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kA2VSmem));
+    XF_CUDA(cudaFuncSetAttribute(a2v_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kA2VSmem));
     configured = true;
   }
   const int npairs = (c.B + 1) / 2;
   const int grid = npairs < num_sms() ? npairs : num_sms();
-  XF_CUDA(launch_chain(a2v_tc_kernel, dim3(grid), dim3(kA2VThreads), kA2VSmem, x.st, tmA0, tmKt, tmVt, a));
+  if (a.xhat_out != nullptr)
+    XF_CUDA(launch_chain(a2v_tc_kernel<true>, dim3(grid), dim3(kA2VThreads), kA2VSmem, x.st, tmA0, tmKt, tmVt, a));
+  else
+    XF_CUDA(launch_chain(a2v_tc_kernel<false>, dim3(grid), dim3(kA2VThreads), kA2VSmem, x.st, tmA0, tmKt, tmVt, a));
   count_launch();
   XF_LAUNCH_CHECK();
   if (tracing) {   // debugging aid: timeline of CTA 0 by row tile, microseconds from its first load

@@ -66,6 +66,7 @@ struct WsBf16 {
   int64_t pooled;   // f32  [B,2E]
   int64_t poolp;    // f32  [B,8,E]    per-warp partial sums of LayerNorm-ed audio rows (a2v_tc -> head)
   int64_t v1;       // bf16 [B*16, E]  updated video tokens (fusion.py:395), 16 slots per clip
+  int64_t xhat;     // bf16 [B*Ta, E]  pool_mode = ATTN only: the audio tokens after a_norm without its affine (a2v_tc -> attn_pool)
   int64_t total;
 };
 void compute_ws_bf16(const xattn_config& c, WsBf16& w);
@@ -86,7 +87,9 @@ struct Bf16Ctx {
 int launch_video_pre(const Bf16Ctx& x);
 int launch_prior(const Bf16Ctx& x);
 int launch_v2a_tc(const Bf16Ctx& x);
-int launch_a2v_tc(const Bf16Ctx& x);     // leaves pooled_a as per-warp partial sums in ws.poolp (finalised by the head kernel)
+int launch_a2v_tc(const Bf16Ctx& x);     // leaves pooled_a as per-warp partial sums in ws.poolp (finalised by the head kernel);
+                                         // pool_mode = ATTN: also the normalised audio tokens in ws.xhat
+int launch_learned_pool(const Bf16Ctx& x);   // pool_mode = ATTN: TemporalAttentionPooling of v1 and of the audio tokens into ws.pooled
 int launch_video_update(const Bf16Ctx& x);   // the video_mix + video_kv GEMMs (gemm_tc.cuh)
 int launch_head_pooled(const Bf16Ctx& x, float* logits);
 

@@ -23,6 +23,9 @@ int bf16_supported(const xattn_config& c) {
     XF_FAIL(XATTN_ERR_SHAPE, "bf16 path head supports hidden widths 64/128/192/256 and <= 16 classes (got %d, %d)", HW, c.C);
   if (c.use_prior && (c.prior_hidden > 128 || c.prior_dim > 32))
     XF_FAIL(XATTN_ERR_SHAPE, "bf16 path supports prior_hidden <= 128, prior_dim <= 32");
+  if (c.pool_mode != XATTN_POOL_MEAN && c.pool_mode != XATTN_POOL_ATTN)
+    XF_FAIL(XATTN_ERR_SHAPE, "bf16 path pools by mean or by the learned attention pooling; temporal_pooling=transformer runs in the "
+                             "fp32 kernel family (precision f32 / tf32)");
   return XATTN_OK;
 }
 
@@ -74,6 +77,7 @@ void compute_ws_bf16(const xattn_config& c, WsBf16& w) {
   w.pooled = take(B * 2 * E * 4);
   w.poolp = take(B * 8 * E * 4);
   w.v1 = take(B * 16 * E * 2);
+  w.xhat = take(c.pool_mode == XATTN_POOL_ATTN ? B * c.Ta * E * 2 : 0);
   w.total = off + 256;
 }
 

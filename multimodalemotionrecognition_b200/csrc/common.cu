@@ -212,8 +212,8 @@ int validate_config(const xattn_config* c) {
       XF_FAIL(XATTN_ERR_SHAPE, "pool_layers=%d outside 1..%d", c->pool_layers, XATTN_MAX_POOL_LAYERS);
     if (c->pool_heads <= 0 || c->E % c->pool_heads != 0) XF_FAIL(XATTN_ERR_SHAPE, "pool_heads=%d must divide E=%d", c->pool_heads, c->E);
   }
-  if (c->pool_mode != XATTN_POOL_MEAN && c->precision == XATTN_DTYPE_BF16)
-    XF_FAIL(XATTN_ERR_SHAPE, "temporal_pooling=attn runs in the fp32 kernel family (precision f32 / tf32)");
+  if (c->pool_mode == XATTN_POOL_TRANSFORMER && c->precision == XATTN_DTYPE_BF16)
+    XF_FAIL(XATTN_ERR_SHAPE, "temporal_pooling=transformer runs in the fp32 kernel family (precision f32 / tf32)");
   if (c->precision != XATTN_DTYPE_F32 && c->precision != XATTN_DTYPE_BF16 && c->precision != XATTN_PREC_TF32)
     XF_FAIL(XATTN_ERR_DTYPE, "unknown precision %d", c->precision);
   if ((int64_t)c->B * c->Ta * c->Da >= ((int64_t)1 << 40)) XF_FAIL(XATTN_ERR_SHAPE, "input too large");

@@ -8,6 +8,7 @@
 #include "bf16_layout.cuh"
 #include "gemm_tc.cuh"
 #include "kernels_bf16.cuh"
+#include "kernels_f32.cuh"
 #include "tc.cuh"
 
 namespace xf {
@@ -211,7 +212,8 @@ int launch_head_pooled(const Bf16Ctx& x, float* logits) {
   auto P = [&](int id) { return x.params + x.pl.off[id]; };
   HeadPooledArgs a;
   a.pooled = reinterpret_cast<float*>(x.ws + x.w.pooled);
-  a.poolp = reinterpret_cast<const float*>(x.ws + x.w.poolp);
+  // learned pooling: pooled_a is final (launch_learned_pool); mean pooling: the a2v kernel's partials are summed here
+  a.poolp = c.pool_mode == XATTN_POOL_ATTN ? nullptr : reinterpret_cast<const float*>(x.ws + x.w.poolp);
   a.an_w = P(XP_AN_W); a.an_b = P(XP_AN_B);
   a.Ta = c.Ta;
   a.w0b = reinterpret_cast<const __nv_bfloat16*>(x.packed + x.pk.W0b);
@@ -228,6 +230,19 @@ int launch_head_pooled(const Bf16Ctx& x, float* logits) {
   count_launch();
   XF_LAUNCH_CHECK();
   return XATTN_OK;
+}
+
+// TemporalAttentionPooling (temporal.py:9-26) on the tensor-core path: the SIMT pooling kernel of the fp32 family over the bf16
+// token rows this path leaves — v1 (a_norm's twin v_norm applied by video_mix) and the audio tokens as a2v_tc normalised them
+// (a_norm's affine is applied on load) — into the two halves of the pooled buffer the head reads.
+int launch_learned_pool(const Bf16Ctx& x) {
+  const xattn_config& c = *x.cfg;
+  auto P = [&](int id) { return x.params + x.pl.off[id]; };
+  const float* pv[6] = {P(XP_VPOOL_LN_W), P(XP_VPOOL_LN_B), P(XP_VPOOL_W1), P(XP_VPOOL_B1), P(XP_VPOOL_W2), P(XP_VPOOL_B2)};
+  const float* pa[6] = {P(XP_APOOL_LN_W), P(XP_APOOL_LN_B), P(XP_APOOL_W1), P(XP_APOOL_B1), P(XP_APOOL_W2), P(XP_APOOL_B2)};
+  float* pooled = reinterpret_cast<float*>(x.ws + x.w.pooled);
+  XF_TRY(launch_attn_pool_bf16(x.st, x.ws + x.w.v1, 16 * BE, nullptr, nullptr, pv, pooled, 2 * BE, c.B, c.T, BE));
+  return launch_attn_pool_bf16(x.st, x.ws + x.w.xhat, (int64_t)c.Ta * BE, P(XP_AN_W), P(XP_AN_B), pa, pooled + BE, 2 * BE, c.B, c.Ta, BE);
 }
 
 // Per-device resources of the forked video branch: one private non-blocking stream and the fork / join events, created once
@@ -323,7 +338,11 @@ int forward_bf16(const xattn_config& c, const float* params, const void* packed,
   { StageScope t(ST_V2A, st); XF_TRY(launch_v2a_tc(x)); }
   { StageScope t(ST_VIDEO_UPD, st); XF_TRY(launch_video_update(x)); }
   { StageScope t(ST_A2V, st); XF_TRY(launch_a2v_tc(x)); }
-  { StageScope t(ST_HEAD, st); XF_TRY(launch_head_pooled(x, logits)); }
+  {
+    StageScope t(ST_HEAD, st);
+    if (c.pool_mode == XATTN_POOL_ATTN) XF_TRY(launch_learned_pool(x));
+    XF_TRY(launch_head_pooled(x, logits));
+  }
   return XATTN_OK;
 }
 

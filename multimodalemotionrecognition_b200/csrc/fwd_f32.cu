@@ -599,11 +599,16 @@ __global__ void __launch_bounds__(256) pool_head_fwd_kernel(HeadArgs a) {
 // ([e][j], so lane j walks a column without bank conflicts), one warp per token row.  The Dropout of the score MLP
 // (temporal.py:19) multiplies GELU's output by a Philox mask indexed (clip, token, hidden unit); attn_pool_bwd_kernel regenerates it.
 // ---------------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256) attn_pool_kernel(const float* __restrict__ x, const float* __restrict__ ln_w,
+// TIN = float: the fp32 family's token tensors.  TIN = bf16 (the tensor-core inference path): `x` holds the tokens as that path
+// leaves them — clips `clip_stride` elements apart, optionally still without the affine of the LayerNorm that produced them
+// (pre_g / pre_b: token = pre_g ⊙ x + pre_b; nullptr = identity) — and `out` is a slice of the [B, 2E] pooled buffer (ld_out).
+template <typename TIN>
+__global__ void __launch_bounds__(256) attn_pool_kernel(const TIN* __restrict__ x, int64_t clip_stride, const float* __restrict__ pre_g,
+                                                        const float* __restrict__ pre_b, const float* __restrict__ ln_w,
                                                         const float* __restrict__ ln_b, const float* __restrict__ w1,
                                                         const float* __restrict__ b1, const float* __restrict__ w2,
-                                                        const float* __restrict__ b2, float* __restrict__ out, int L, int E,
-                                                        float p_drop, uint64_t seed, uint64_t offset, uint32_t rng_stream) {
+                                                        const float* __restrict__ b2, float* __restrict__ out, int64_t ld_out, int L,
+                                                        int E, float p_drop, uint64_t seed, uint64_t offset, uint32_t rng_stream) {
   extern __shared__ float sm[];
   const int b = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nw = blockDim.x >> 5;
   const int H2 = E / 2 > 0 ? E / 2 : 1;
@@ -616,20 +621,24 @@ __global__ void __launch_bounds__(256) attn_pool_kernel(const float* __restrict_
     w1t[e * H2 + j] = w1[i];
   }
   __syncthreads();
-  const float* xb = x + (int64_t)b * L * E;
+  const TIN* xb = x + (int64_t)b * clip_stride;
+  auto tokv = [&](const TIN* row, int e) -> float {
+    const float v = to_f32(row[e]);
+    return pre_g != nullptr ? fmaf(pre_g[e], v, pre_b[e]) : v;
+  };
   float* y = yrow + warp * E;
   for (int l = warp; l < L; l += nw) {
-    const float* xr = xb + (int64_t)l * E;
+    const TIN* xr = xb + (int64_t)l * E;
     float sum = 0.f;
-    for (int e = lane; e < E; e += 32) sum += xr[e];
+    for (int e = lane; e < E; e += 32) sum += tokv(xr, e);
     const float mu = warp_sum(sum) / (float)E;
     float var = 0.f;
     for (int e = lane; e < E; e += 32) {
-      const float d = xr[e] - mu;
+      const float d = tokv(xr, e) - mu;
       var = fmaf(d, d, var);
     }
     const float rstd = rsqrtf(warp_sum(var) / (float)E + 1e-5f);
-    for (int e = lane; e < E; e += 32) y[e] = (xr[e] - mu) * rstd * ln_w[e] + ln_b[e];
+    for (int e = lane; e < E; e += 32) y[e] = (tokv(xr, e) - mu) * rstd * ln_w[e] + ln_b[e];
     __syncwarp();
     float sc = 0.f;
     for (int j = lane; j < H2; j += 32) {
@@ -661,25 +670,38 @@ __global__ void __launch_bounds__(256) attn_pool_kernel(const float* __restrict_
   const float inv = s_stat[0];
   for (int e = tid; e < E; e += blockDim.x) {
     float acc = 0.f;
-    for (int l = 0; l < L; ++l) acc = fmaf(score[l], xb[(int64_t)l * E + e], acc);
-    out[(int64_t)b * E + e] = acc * inv;
+    for (int l = 0; l < L; ++l) acc = fmaf(score[l], tokv(xb + (int64_t)l * E, e), acc);
+    out[(int64_t)b * ld_out + e] = acc * inv;
   }
 }
 
-static int launch_attn_pool(cudaStream_t st, const float* x, const float* const* p, float* out, int B, int L, int E, float p_drop,
-                            uint64_t seed, uint64_t offset, uint32_t rng_stream) {
+template <typename TIN>
+static int launch_attn_pool_t(cudaStream_t st, const TIN* x, int64_t clip_stride, const float* pre_g, const float* pre_b,
+                              const float* const* p, float* out, int64_t ld_out, int B, int L, int E, float p_drop, uint64_t seed,
+                              uint64_t offset, uint32_t rng_stream) {
   const int H2 = E / 2 > 0 ? E / 2 : 1;
   const size_t smem = sizeof(float) * ((size_t)E * H2 + 8 * (size_t)E + (size_t)L);
   if (smem > 200 * 1024) XF_FAIL(XATTN_ERR_SHAPE, "attention pooling needs %zu B of shared memory (> 200 KiB)", smem);
   static size_t configured = 0;
   if (smem > 48 * 1024 && smem > configured) {
-    XF_CUDA(cudaFuncSetAttribute(attn_pool_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    XF_CUDA(cudaFuncSetAttribute(attn_pool_kernel<TIN>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     configured = smem;
   }
-  attn_pool_kernel<<<B, 256, smem, st>>>(x, p[0], p[1], p[2], p[3], p[4], p[5], out, L, E, p_drop, seed, offset, rng_stream);
+  attn_pool_kernel<TIN><<<B, 256, smem, st>>>(x, clip_stride, pre_g, pre_b, p[0], p[1], p[2], p[3], p[4], p[5], out, ld_out, L, E, p_drop,
+                                              seed, offset, rng_stream);
   count_launch();
   XF_LAUNCH_CHECK();
   return XATTN_OK;
+}
+static int launch_attn_pool(cudaStream_t st, const float* x, const float* const* p, float* out, int B, int L, int E, float p_drop,
+                            uint64_t seed, uint64_t offset, uint32_t rng_stream) {
+  return launch_attn_pool_t<float>(st, x, (int64_t)L * E, nullptr, nullptr, p, out, E, B, L, E, p_drop, seed, offset, rng_stream);
+}
+// The learned pooling over bf16 token rows of the tensor-core inference path (fwd_bf16.cu), eval mode
+int launch_attn_pool_bf16(cudaStream_t st, const void* x_bf16, int64_t clip_stride, const float* pre_g, const float* pre_b,
+                          const float* const* p, float* out, int64_t ld_out, int B, int L, int E) {
+  return launch_attn_pool_t<__nv_bfloat16>(st, reinterpret_cast<const __nv_bfloat16*>(x_bf16), clip_stride, pre_g, pre_b, p, out, ld_out,
+                                           B, L, E, 0.f, 0, 0, 0);
 }
 
 // ---------------------------------------------------------------------------------------------------------

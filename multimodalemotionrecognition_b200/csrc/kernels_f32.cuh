@@ -67,6 +67,8 @@ int launch_attn_fwd_mma(cudaStream_t st, const AttnArgs& a, int B);
 struct AttnBwdArgs;
 int launch_attn_bwd_mma(cudaStream_t st, const AttnBwdArgs& a, int B);
 
+int launch_attn_pool_bf16(cudaStream_t st, const void* x_bf16, int64_t clip_stride, const float* pre_g, const float* pre_b,
+                          const float* const* p, float* out, int64_t ld_out, int B, int L, int E);   // fwd_f32.cu
 // row-wise pieces of the transformer pooler (fwd_f32.cu / tx_pool_bwd.cu)
 int launch_ln_rows(cudaStream_t st, const float* x, const float* gamma, const float* beta, float* y, int rows, int E);
 int launch_ln_rows_bwd(cudaStream_t st, const float* x, const float* gamma, const float* d_h, float* d_x, float* g_gamma,

@@ -443,7 +443,7 @@ class XAttnKernelsMixin:
     def _bf16_supported(self, T: int, Ta: int) -> bool:
         """Shapes the bf16 tensor-core kernels are specialised for (csrc/bf16_pack.cu: bf16_supported)."""
         hw = self.d_model if self.xattn_head == "gated" else self.common_dim
-        if getattr(self, "_temporal_pooling", "mean") != "mean":   # the learned pooling lives in the fp32 kernel family
+        if getattr(self, "_temporal_pooling", "mean") == "transformer":   # the encoder layers live in the fp32 kernel family
             return False
         return (self.d_model == 128 and self.num_heads == 4 and T <= 16 and Ta <= 160 and self.v_dim % 64 == 0
                 and self._kernel_audio_dim % 64 == 0 and hw <= 256 and hw % 64 == 0 and self.num_classes <= 16

@@ -391,8 +391,8 @@ def test_flat_alignment_loss_matches_reference(cuda_device, mode):
 
 def test_attention_pooling_matches_reference(cuda_device):
     """temporal_pooling="attn" (TemporalAttentionPooling, temporal.py:9-26) in the fp32 kernel family: the tiny
-    golden case and the BASELINE config-1 dimensions against the reference's logits (1e-4); bf16 embeddings route to the same
-    kernels (the bf16 tensor-core path pools by mean only)."""
+    golden case and the BASELINE config-1 dimensions against the reference's logits (1e-4), also with bf16 embeddings; with those
+    the tensor-core path runs too (its a2v kernel emits the normalised audio tokens, the pooling kernel reads them in bf16): 1e-2."""
     from multimodalemotionrecognition_b200 import XAttnFusionHead
 
     blob = load_npz("xattn_attnpool.npz")
@@ -412,11 +412,20 @@ def test_attention_pooling_matches_reference(cuda_device):
         mm = make_head(head, True, seed=0, temporal_pooling="attn").to(cuda_device).eval()
         with torch.no_grad():
             out = mm(xv.to(cuda_device), xa.to(cuda_device))
-            outb = mm(xv.bfloat16().to(cuda_device), xa.bfloat16().to(cuda_device))
+            mm.precision = "fp32"
+            outb = mm(xv.bfloat16().to(cuda_device), xa.bfloat16().to(cuda_device))      # fp32 kernels on bf16 embeddings
+            mm.precision = "auto"
+            mm(xv.bfloat16().to(cuda_device), xa.bfloat16().to(cuda_device))             # (packs the bf16 weights once)
+            n0 = _lib.launch_count()
+            outtc = mm(xv.bfloat16().to(cuda_device), xa.bfloat16().to(cuda_device))     # tcgen05 path + the pooling kernel
+            n_tc = _lib.launch_count() - n0
         assert np.abs(out.cpu().numpy() - blob[f"{head}:logits"]).max() <= FP32_TOL
         sdn = {k: v.cpu().numpy() for k, v in mm.state_dict().items()}
         refb = xattn_oracle.xattn_forward(sdn, xv.bfloat16().float().numpy(), xa.bfloat16().float().numpy(), num_heads=4, head=head)
         assert np.abs(outb.cpu().numpy() - refb).max() <= FP32_TOL
+        assert mm._pick_precision(_lib.DTYPE_BF16, False, 16, 149) == _lib.DTYPE_BF16 and n_tc == 11   # 9 launches + 2 poolings
+        assert np.abs(outtc.cpu().numpy() - refb).max() <= BF16_TOL
+        assert np.abs(outtc.cpu().numpy() - outb.cpu().numpy()).max() > 0
 
 
 def test_attention_pooling_backward_matches_reference(cuda_device):
