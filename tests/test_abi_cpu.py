@@ -168,3 +168,40 @@ def test_flat_parameter_views_follow_load_state_dict():
     assert torch.all(flat[off:off + n] == 0.5)
     g = m.flat_gradients()
     assert m.v_in_proj.weight.grad.data_ptr() == g.data_ptr() + 4 * off
+
+
+def test_flat_head_training_config_and_modality_dropout_draws():
+    """Host logic of the trainable flat heads (no GPU): the config struct carries the training fields behind the inference ones
+    (layout as in include/xattn_fusion.h), and the two ModalityDropout decisions are drawn like the reference draws them —
+    ``torch.rand(1).item() < p``, audio first (fusion.py:47-53) — so a torch seed decides the same drops on both sides."""
+    from multimodalemotionrecognition_b200 import FlatFusionHead, _lib
+
+    assert C.sizeof(_lib.FlatHeadConfig) == 80 and _lib.FlatHeadConfig.training.offset == 44 and _lib.FlatHeadConfig.seed.offset == 64
+    m = FlatFusionHead(num_classes=8, video_dim=12, audio_dim=10, common_dim=16, mode="gated", fusion_align_mode="clip", fusion_align_dim=32)
+    m.train()
+    seen = set()
+    for seed in range(40):
+        torch.manual_seed(seed)
+        want = (int(torch.rand(1).item() < 0.2), int(torch.rand(1).item() < 0.2))
+        torch.manual_seed(seed)
+        cfg = m._flat_train_cfg(m._flat_cfg(4, 3, 5, _lib.DTYPE_F32))
+        assert (cfg.drop_audio, cfg.drop_video) == want and cfg.training == 1 and abs(cfg.p_drop - 0.2) < 1e-7
+        assert cfg.precision == _lib.DTYPE_F32 and cfg.offset == seed + 1
+        seen.add(want)
+    assert len(seen) >= 3
+    m.eval()
+    cfg = m._flat_train_cfg(m._flat_cfg(4, 3, 5, _lib.DTYPE_F32))
+    assert cfg.training == 0 and cfg.drop_audio == 0 and cfg.drop_video == 0
+    mc = FlatFusionHead(num_classes=8, video_dim=12, audio_dim=10, common_dim=16, mode="concat", fusion_align_mode="none").train()
+    st = torch.get_rng_state()
+    cfg = mc._flat_train_cfg(mc._flat_cfg(4, 3, 5, _lib.DTYPE_F32))
+    assert torch.equal(st, torch.get_rng_state()) and cfg.drop_audio == 0      # concat mode has no ModalityDropout: no draw
+
+
+def test_step_args_struct_matches_the_header():
+    from multimodalemotionrecognition_b200 import _lib
+
+    a = _lib.XAttnStepArgs
+    # 12 pointers, int64, 6 floats, 4 int32, float -> 96 + 8 + 24 + 16 + 4 = 148 -> padded to 152
+    assert C.sizeof(a) == 152 and a.workspace_bytes.offset == 96 and a.lr.offset == 104 and a.step.offset == 128
+    assert a.phase.offset == 140 and a.grad_scale.offset == 144
