@@ -680,12 +680,8 @@ size_t bwd_smem(int L, int E, int H, bool prior) {
 }
 
 template <typename K>
-int set_smem(K kernel, size_t bytes, size_t* configured) {
-  if (bytes > 48 * 1024 && bytes > *configured) {
-    XF_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
-    *configured = bytes;
-  }
-  return XATTN_OK;
+int set_smem(K kernel, size_t bytes, size_t*) {
+  return ensure_dyn_smem(kernel, bytes);
 }
 
 }  // namespace

@@ -829,11 +829,7 @@ int launch_v2a_tc(const Bf16Ctx& x) {
   XF_TRY(make_tmap_bf16_2d(&tmA0, x.ws + x.w.a0, (int64_t)c.B * c.Ta, BE, BTAP, 64, BOP));
   XF_TRY(make_tmap_bf16_2d(&tmQt, x.ws + x.w.qt, (int64_t)c.B * 64, BE, 64, 64, BOP));
   XF_TRY(make_tmap_bf16_2d(&tmU, x.ws + x.w.u, (int64_t)c.B * 16, 4 * BE, 32, 64));
-  static bool configured = false;
-  if (!configured) {
-    XF_CUDA(cudaFuncSetAttribute(v2a_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kV2ASmem));
-    configured = true;
-  }
+  XF_TRY(ensure_dyn_smem(v2a_tc_kernel, kV2ASmem));
   const int npairs = (c.B + 1) / 2;
   const int grid = npairs < num_sms() ? npairs : num_sms();
   XF_CUDA(launch_chain(v2a_tc_kernel, dim3(grid), dim3(kV2AThreads), kV2ASmem, x.st, tmA0, tmQt, tmU, a));
@@ -882,12 +878,8 @@ int launch_a2v_tc(const Bf16Ctx& x) {
   XF_TRY(make_tmap_bf16_2d(&tmA0, x.ws + x.w.a0, (int64_t)c.B * c.Ta, BE, BTAP, 64, BOP));
   XF_TRY(make_tmap_bf16_2d(&tmKt, x.ws + x.w.kt, (int64_t)c.B * 64, BE, 64, 64, BOP));
   XF_TRY(make_tmap_bf16_2d(&tmVt, x.ws + x.w.vt, (int64_t)c.B * 64, BE, 64, 64, BOP));
-  static bool configured = false;
-  if (!configured) {
-    XF_CUDA(cudaFuncSetAttribute(a2v_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kA2VSmem));
-    XF_CUDA(cudaFuncSetAttribute(a2v_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kA2VSmem));
-    configured = true;
-  }
+  XF_TRY(ensure_dyn_smem(a2v_tc_kernel<false>, kA2VSmem));
+  XF_TRY(ensure_dyn_smem(a2v_tc_kernel<true>, kA2VSmem));
   const int npairs = (c.B + 1) / 2;
   const int grid = npairs < num_sms() ? npairs : num_sms();
   if (a.xhat_out != nullptr)

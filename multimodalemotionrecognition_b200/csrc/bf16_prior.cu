@@ -186,11 +186,7 @@ int launch_prior(const Bf16Ctx& x) {
   a.pc = reinterpret_cast<float*>(x.ws + x.w.pc);
   a.B = c.B; a.Ta = c.Ta; a.P = c.prior_dim; a.Hd = c.prior_hidden;
   constexpr int dyn = kPriorSmem;
-  static bool configured = false;
-  if (!configured) {
-    XF_CUDA(cudaFuncSetAttribute(prior_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, dyn));
-    configured = true;
-  }
+  XF_TRY(ensure_dyn_smem(prior_kernel, dyn));
   XF_CUDA(launch_chain(prior_kernel, dim3((c.B + kPriorClips - 1) / kPriorClips), dim3(kPriorThreads), dyn, x.st, a));
   count_launch();
   XF_LAUNCH_CHECK();

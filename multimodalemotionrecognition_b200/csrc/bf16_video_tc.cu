@@ -272,11 +272,7 @@ int launch_video_pre(const Bf16Ctx& x) {
   alignas(64) CUtensorMap tmWq, tmWk;
   XF_TRY(make_tmap_bf16_2d(&tmWq, x.packed + x.pk.Wq1, BE, BE, 128, 64, BEP));
   XF_TRY(make_tmap_bf16_2d(&tmWk, x.packed + x.pk.Wk1, BE, BE, 128, 64, BEP));
-  static bool configured = false;
-  if (!configured) {
-    XF_CUDA(cudaFuncSetAttribute(video_pre_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kVSmem));
-    configured = true;
-  }
+  XF_TRY(ensure_dyn_smem(video_pre_tc_kernel, kVSmem));
   const int ntiles = (c.B + 7) / 8;
   const int cap = 2 * num_sms();
   video_pre_tc_kernel<<<ntiles < cap ? ntiles : cap, kVThreads, kVSmem, x.st>>>(tmWq, tmWk, a);

@@ -598,11 +598,7 @@ static int launch_attn_bwd(cudaStream_t st, const AttnBwdArgs& a, int B, bool* b
     const int SP = (a.S + 3) & ~3;
     const size_t smem32 = sizeof(float) * (4 * (size_t)a.L * SP + (size_t)(2 * a.L + 2 * a.S) * 33);
     if (smem32 > 200 * 1024) XF_FAIL(XATTN_ERR_SHAPE, "attention backward tile needs %zu B of shared memory (> 200 KiB)", smem32);
-    static size_t configured32 = 0;
-    if (smem32 > 48 * 1024 && smem32 > configured32) {
-      XF_CUDA(cudaFuncSetAttribute(attn_bwd32_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem32));
-      configured32 = smem32;
-    }
+    XF_TRY(ensure_dyn_smem(attn_bwd32_kernel, smem32));
     attn_bwd32_kernel<<<B, 256, smem32, st>>>(a);
     count_launch();
     XF_LAUNCH_CHECK();
@@ -610,11 +606,7 @@ static int launch_attn_bwd(cudaStream_t st, const AttnBwdArgs& a, int B, bool* b
   }
   const size_t smem = sizeof(float) * ((size_t)(2 * a.L + 2 * a.S) * (dh + 1) + 3 * (size_t)a.L * a.S);
   if (smem > 200 * 1024) XF_FAIL(XATTN_ERR_SHAPE, "attention backward tile needs %zu B of shared memory (> 200 KiB)", smem);
-  static size_t configured = 0;
-  if (smem > 48 * 1024 && smem > configured) {
-    XF_CUDA(cudaFuncSetAttribute(attn_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    configured = smem;
-  }
+  XF_TRY(ensure_dyn_smem(attn_bwd_kernel, smem));
   attn_bwd_kernel<<<B, 256, smem, st>>>(a);
   count_launch();
   XF_LAUNCH_CHECK();
@@ -1103,11 +1095,7 @@ static int launch_attn_pool_bwd(cudaStream_t st, const AttnPoolBwdArgs& a, int B
   if (E > 512) XF_FAIL(XATTN_ERR_SHAPE, "attention pooling backward supports d_model <= 512 (got %d)", E);
   const size_t smem = sizeof(float) * (2 * (size_t)E * H2 + 2 * (size_t)nw * E + (size_t)nw * H2 + 2 * (size_t)a.L + (size_t)nw * (2 * E + H2 + 1));
   if (smem > 200 * 1024) XF_FAIL(XATTN_ERR_SHAPE, "attention pooling backward needs %zu B of shared memory (> 200 KiB)", smem);
-  static size_t configured = 0;
-  if (smem > 48 * 1024 && smem > configured) {
-    XF_CUDA(cudaFuncSetAttribute(attn_pool_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    configured = smem;
-  }
+  XF_TRY(ensure_dyn_smem(attn_pool_bwd_kernel, smem));
   attn_pool_bwd_kernel<<<B, 256, smem, st>>>(a);
   count_launch();
   XF_LAUNCH_CHECK();

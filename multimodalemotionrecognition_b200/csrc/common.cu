@@ -22,6 +22,29 @@ bool pdl_enabled() {
   static const bool off = getenv("XATTN_NO_PDL") != nullptr;
   return !off && !g_stage_timing;
 }
+int ensure_dyn_smem_impl(const void* func, size_t bytes) {
+  if (bytes <= 48 * 1024) return XATTN_OK;
+  struct Rec { const void* func; size_t bytes[64]; };
+  static std::vector<Rec> recs;
+  static std::mutex mu;
+  int dev = 0;
+  XF_CUDA(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= 64) XF_FAIL(XATTN_ERR_CUDA, "device index %d out of range", dev);
+  std::lock_guard<std::mutex> lock(mu);
+  Rec* r = nullptr;
+  for (Rec& x : recs)
+    if (x.func == func) { r = &x; break; }
+  if (r == nullptr) {
+    recs.push_back(Rec{func, {}});
+    r = &recs.back();
+  }
+  if (bytes > r->bytes[dev]) {
+    XF_CUDA(cudaFuncSetAttribute(func, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
+    r->bytes[dev] = bytes;
+  }
+  return XATTN_OK;
+}
+
 struct SideForkRes {
   cudaStream_t side = nullptr;
   cudaEvent_t fork = nullptr, join = nullptr;

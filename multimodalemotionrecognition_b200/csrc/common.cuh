@@ -73,6 +73,12 @@ class SideFork {
   cudaStream_t st_ = nullptr, side_ = nullptr;
 };
 
+// cudaFuncAttributeMaxDynamicSharedMemorySize is a property of a kernel ON ONE DEVICE: remembered per (function, device) — not per
+// process — so a process that drives several GPUs configures each of them.  No-op up to 48 KB (the default limit).
+int ensure_dyn_smem_impl(const void* func, size_t bytes);
+template <typename K>
+inline int ensure_dyn_smem(K kernel, size_t bytes) { return ensure_dyn_smem_impl(reinterpret_cast<const void*>(kernel), bytes); }
+
 // Count of kernels this library launched since process start (bench.py's gpu_launches claim).
 extern unsigned long long g_launch_count;
 inline void count_launch(int n = 1) { g_launch_count += (unsigned long long)n; }

@@ -221,11 +221,7 @@ int launch_head_pooled(const Bf16Ctx& x, float* logits) {
   a.logits = logits;
   a.B = c.B; a.C = c.C; a.gated = c.head_kind == XATTN_HEAD_GATED;
   a.HW = a.gated ? c.E : c.common_dim;
-  static bool configured = false;
-  if (!configured) {
-    XF_CUDA(cudaFuncSetAttribute(head_pooled_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kHeadSmem));
-    configured = true;
-  }
+  XF_TRY(ensure_dyn_smem(head_pooled_kernel, kHeadSmem));
   XF_CUDA(launch_chain(head_pooled_kernel, dim3((c.B + kHeadClips - 1) / kHeadClips), dim3(kHeadThreads), kHeadSmem, x.st, a));
   count_launch();
   XF_LAUNCH_CHECK();

@@ -682,11 +682,7 @@ static int launch_attn_pool_t(cudaStream_t st, const TIN* x, int64_t clip_stride
   const int H2 = E / 2 > 0 ? E / 2 : 1;
   const size_t smem = sizeof(float) * ((size_t)E * H2 + 8 * (size_t)E + (size_t)L);
   if (smem > 200 * 1024) XF_FAIL(XATTN_ERR_SHAPE, "attention pooling needs %zu B of shared memory (> 200 KiB)", smem);
-  static size_t configured = 0;
-  if (smem > 48 * 1024 && smem > configured) {
-    XF_CUDA(cudaFuncSetAttribute(attn_pool_kernel<TIN>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    configured = smem;
-  }
+  XF_TRY(ensure_dyn_smem(attn_pool_kernel<TIN>, smem));
   attn_pool_kernel<TIN><<<B, 256, smem, st>>>(x, clip_stride, pre_g, pre_b, p[0], p[1], p[2], p[3], p[4], p[5], out, ld_out, L, E, p_drop,
                                               seed, offset, rng_stream);
   count_launch();
@@ -772,11 +768,7 @@ int launch_attn_fwd(cudaStream_t st, const AttnArgs& a, int B) {
   if (a.E / a.H == 32) {   // one lane per head column: the register-tiled kernel
     const size_t smem = sizeof(float) * ((size_t)a.L * ((a.S + 3) & ~3) + (size_t)(a.L + 2 * a.S) * 33);
     if (smem > 200 * 1024) XF_FAIL(XATTN_ERR_SHAPE, "attention tile needs %zu B of shared memory (> 200 KiB)", smem);
-    static size_t configured32 = 0;
-    if (smem > 48 * 1024 && smem > configured32) {
-      XF_CUDA(cudaFuncSetAttribute(attn_fwd32_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-      configured32 = smem;
-    }
+    XF_TRY(ensure_dyn_smem(attn_fwd32_kernel, smem));
     attn_fwd32_kernel<<<B, 256, smem, st>>>(a);
     count_launch();
     XF_LAUNCH_CHECK();
@@ -784,11 +776,7 @@ int launch_attn_fwd(cudaStream_t st, const AttnArgs& a, int B) {
   }
   const size_t smem = attn_smem_bytes(a.L, a.S, a.E / a.H, 8);
   if (smem > 200 * 1024) XF_FAIL(XATTN_ERR_SHAPE, "attention tile needs %zu B of shared memory (> 200 KiB)", smem);
-  static size_t configured = 0;
-  if (smem > 48 * 1024 && smem > configured) {
-    XF_CUDA(cudaFuncSetAttribute(attn_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    configured = smem;
-  }
+  XF_TRY(ensure_dyn_smem(attn_fwd_kernel, smem));
   attn_fwd_kernel<<<B, 256, smem, st>>>(a);
   count_launch();
   XF_LAUNCH_CHECK();

@@ -473,11 +473,7 @@ int launch_gemm_tc(cudaStream_t st, const CUtensorMap& tmA, const CUtensorMap& t
   if (tmO2 == nullptr) tmO2 = &tmA;
   constexpr int smem = gemm_smem_bytes(EPI, STAGES);
   static_assert(smem <= 227 * 1024, "projection GEMM: shared memory");
-  static bool configured = false;
-  if (!configured) {
-    XF_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<EPI, STAGES, EPG>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-    configured = true;
-  }
+  XF_TRY(ensure_dyn_smem(gemm_tc_kernel<EPI, STAGES, EPG>, smem));
   const int tiles = ((M + BM - 1) / BM) * (N / BN);
   const int grid = tiles < num_sms() ? tiles : num_sms();
   if (chain)

@@ -371,8 +371,7 @@ int make_tmap(CUtensorMap* tm, const void* base, bool f32, int64_t rows, int64_t
 
 template <typename K>
 int set_smem(K kernel) {
-  XF_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem));
-  return XATTN_OK;
+  return ensure_dyn_smem(kernel, kSmem);
 }
 
 }  // namespace
@@ -391,12 +390,8 @@ int gemm_tf32_rows(cudaStream_t st, const float* A, int64_t lda, const float* W,
   XF_TRY(make_tmap(&tmA, A, true, M, K, lda, TM));
   if (!w_is_kn) XF_TRY(make_tmap(&tmB, W, true, N, K, K, TN));          // W[N,K]
   else XF_TRY(make_tmap(&tmB, W, true, K, N, N, kRedRows, true));       // W[K,N]
-  static bool configured = false;
-  if (!configured) {
-    XF_TRY(set_smem(gemm_tf32_rows_kernel<false>));
-    XF_TRY(set_smem(gemm_tf32_rows_kernel<true>));
-    configured = true;
-  }
+  XF_TRY(set_smem(gemm_tf32_rows_kernel<false>));
+  XF_TRY(set_smem(gemm_tf32_rows_kernel<true>));
   const int tiles = ((M + TM - 1) / TM) * (N / TN);
   const int grid = tiles < num_sms() ? tiles : num_sms();
   if (!w_is_kn)
@@ -414,12 +409,8 @@ int gemm_cols(cudaStream_t st, const void* A, int64_t lda, const void* B, int64_
   alignas(64) CUtensorMap tmA, tmB;
   XF_TRY(make_tmap(&tmA, A, !bf16, M, N1, lda, kRedRows, true));
   XF_TRY(make_tmap(&tmB, B, !bf16, M, N2, ldb, kRedRows, true));
-  static bool configured = false;
-  if (!configured) {
-    XF_TRY(set_smem(gemm_cols_kernel<false>));
-    XF_TRY(set_smem(gemm_cols_kernel<true>));
-    configured = true;
-  }
+  XF_TRY(set_smem(gemm_cols_kernel<false>));
+  XF_TRY(set_smem(gemm_cols_kernel<true>));
   const int tiles = (N1 / TM) * (N2 / TN);
   int splits = (2 * num_sms() + tiles - 1) / tiles;            // ~2 work items per CTA
   const int max_splits = (M + 4 * kRedRows - 1) / (4 * kRedRows);

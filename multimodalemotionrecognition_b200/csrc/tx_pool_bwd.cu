@@ -211,11 +211,7 @@ int launch_attn_bwd_rows(cudaStream_t st, const AttnBwdArgs& a, int B) {
   while (RT > 1 && bytes(RT) > 200 * 1024) RT >>= 1;
   const size_t smem = bytes(RT);
   if (smem > 200 * 1024) XF_FAIL(XATTN_ERR_SHAPE, "attention backward needs %zu B of shared memory (> 200 KiB) at S=%d", smem, a.S);
-  static size_t configured = 0;
-  if (smem > 48 * 1024 && smem > configured) {
-    XF_CUDA(cudaFuncSetAttribute(attn_bwd_rows_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    configured = smem;
-  }
+  XF_TRY(ensure_dyn_smem(attn_bwd_rows_kernel, smem));
   attn_bwd_rows_kernel<<<B * a.H, 256, smem, st>>>(a, RT);
   count_launch();
   XF_LAUNCH_CHECK();
