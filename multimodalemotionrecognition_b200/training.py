@@ -389,3 +389,36 @@ def gather_logits(local_logits: torch.Tensor, total: int, group=None) -> torch.T
         s, e = shard_range(total, r, world)
         pieces.append(out[r * per: r * per + (e - s)])
     return torch.cat(pieces, dim=0)
+
+
+class _GatherBatch(torch.autograd.Function):
+    """All-gather along the batch dimension with a backward: every rank holds the whole batch in the forward; in the backward the
+    gradient of a rank's own rows is the SUM over ranks of the gradients that rank's rows received (every rank's loss saw them)."""
+
+    @staticmethod
+    def forward(ctx, x, total, group):
+        world = dist.get_world_size(group)
+        rank = dist.get_rank(group)
+        ctx.group, ctx.total, ctx.rows = group, total, x.shape[0]
+        ctx.range = shard_range(total, rank, world)
+        width = 1
+        for d in x.shape[1:]:
+            width *= int(d)
+        return gather_logits(x.reshape(x.shape[0], width), total, group).reshape((total,) + tuple(x.shape[1:]))
+
+    @staticmethod
+    def backward(ctx, g):
+        g = g.contiguous().clone()
+        dist.all_reduce(g, op=dist.ReduceOp.SUM, group=ctx.group)
+        s, e = ctx.range
+        return g[s:e], None, None
+
+
+def gather_batch(x: torch.Tensor, total: int, group=None) -> torch.Tensor:
+    """The B x B alignment loss of the flat heads (``ClipStyleAlignment``, ``fusion.py:141-149``) is a cross-sample term: under batch
+    sharding ("exception") each rank gathers the embeddings of the whole batch — contiguous shards in rank order,
+    ``shard_range`` — before calling ``flat_alignment_loss``.  Differentiable: the gathered tensor's gradient flows back to this
+    rank's rows, summed over the ranks (divide the loss by the world size if every rank adds the same global term)."""
+    if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size(group) == 1:
+        return x
+    return _GatherBatch.apply(x, total, group)

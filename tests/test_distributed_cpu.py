@@ -9,7 +9,7 @@ import torch
 import torch.distributed as dist
 import torch.multiprocessing as mp
 
-from multimodalemotionrecognition_b200.training import Stage1Trainer, gather_logits, shard_range
+from multimodalemotionrecognition_b200.training import Stage1Trainer, gather_batch, gather_logits, shard_range
 
 
 def _free_port() -> int:
@@ -54,6 +54,25 @@ def _worker(rank: int, world: int, port: int, total: int):
         tr2._tail_work = dist.all_reduce(g2[4:], op=dist.ReduceOp.SUM, async_op=True)
         tr2.allreduce_gradients()
         assert tr2._tail_work is None and torch.allclose(g2, torch.full((10,), expect))
+        # 5. differentiable batch gather for the cross-sample alignment loss: a B x B term on the gathered rows, each rank adding
+        #    1/world of it, gives every rank's rows the gradient of the single-process loss
+        gen = torch.Generator().manual_seed(5)
+        xa_full = torch.randn(total, 6, generator=gen, dtype=torch.float64)
+        xv_full = torch.randn(total, 6, generator=gen, dtype=torch.float64)
+
+        def clip_like(a, v):
+            logits = a @ v.t()
+            return (logits.logsumexp(dim=1) - logits.diagonal()).mean() + (logits.logsumexp(dim=0) - logits.diagonal()).mean()
+
+        a_ref = xa_full.clone().requires_grad_(True)
+        v_ref = xv_full.clone().requires_grad_(True)
+        clip_like(a_ref, v_ref).backward()
+        a_loc = xa_full[s:e].clone().requires_grad_(True)
+        v_loc = xv_full[s:e].clone().requires_grad_(True)
+        loss = clip_like(gather_batch(a_loc, total), gather_batch(v_loc, total)) / world
+        loss.backward()
+        if e > s:
+            assert torch.allclose(a_loc.grad, a_ref.grad[s:e], atol=1e-12) and torch.allclose(v_loc.grad, v_ref.grad[s:e], atol=1e-12)
     finally:
         dist.destroy_process_group()
 
