@@ -47,6 +47,7 @@ BYTES_FWD_BF16 = T * DV * 2 + TA * DA * 2 + NCLS * 4   # 245,280 B/clip: inputs 
 BYTES_TRAIN_BF16 = 2 * (T * DV * 2 + TA * DA * 2) + NCLS * 4 + 8   # inputs read twice (forward, first-layer dW) + labels
 E_, H_, HW_ = 128, 4, 256
 TRAFFIC_FILE = ROOT / "profiles" / "r02_ncu_traffic_bf16.json"   # written from an `ncu --set full` capture (profiles/README.md)
+TRAFFIC_FILE_TRAIN = ROOT / "profiles" / "r02_ncu_traffic_train_tf32.json"   # scripts/ncu_traffic_train.py (one metrics pass)
 METRIC = "xattn fusion clips/sec at 1/2/4/8 B200; % of tensor/HBM roofline vs CPU ref"
 
 
@@ -87,6 +88,14 @@ def load_traffic(batch: int):
         return None
     d = json.loads(TRAFFIC_FILE.read_text())
     return d if int(d.get("batch", -1)) == batch else None
+
+
+def load_traffic_train(batch: int, precision: str):
+    """DRAM bytes of one Stage-1 step (every launch between two Adam kernels) from the committed ncu metrics pass."""
+    if not TRAFFIC_FILE_TRAIN.exists():
+        return None
+    d = json.loads(TRAFFIC_FILE_TRAIN.read_text())
+    return d if int(d.get("batch", -1)) == batch and d.get("precision") == precision else None
 
 
 class ClockSampler:
@@ -569,13 +578,18 @@ def run_train(cx: Ctx, args) -> None:
     tot = sum(acc.values()) or 1.0
     stages = [{"phase": n, "us": acc[n] / args.steps * 1e3, "share": acc[n] / tot} for n in names]
     tflops = FLOP_TRAIN * B / (ms_local * 1e-3) / 1e12
+    traffic = load_traffic_train(B, args.precision)
     gbs = BYTES_TRAIN_BF16 * B / (ms_local * 1e-3) / 1e9
     roofline = {
         "bound": "tensor", "achieved": tflops, "peak": peaks["bf16_tflops_sustained"], "unit": "TFLOP/s",
-        "frac": tflops / peaks["bf16_tflops_sustained"], "traffic": None, "kernel": "whole Stage-1 step (every launch)",
+        "frac": tflops / peaks["bf16_tflops_sustained"], "traffic": None if traffic is None else traffic["step_total_bytes"],
+        "traffic_source": None if traffic is None else traffic["source"], "kernel": "whole Stage-1 step (every launch)",
         "algorithmic_flops_per_clip": FLOP_TRAIN, "peak_kind": f"sustained bf16 ({peaks['source']}); the Linears run as tf32 products "
         "(half the bf16 rate), the first layer as bf16",
-        "hbm": {"algorithmic_bytes_per_clip": BYTES_TRAIN_BF16, "gbs": gbs, "frac": gbs / peaks["hbm_gbs"]},
+        "hbm": {"algorithmic_bytes_per_clip": BYTES_TRAIN_BF16, "gbs": gbs, "frac": gbs / peaks["hbm_gbs"],
+                # the same step on the DRAM bytes it actually moves (fp32 activations are stored and re-read for the backward)
+                "gbs_on_traffic": None if traffic is None else traffic["step_total_bytes"] / (ms_local * 1e-3) / 1e9,
+                "frac_on_traffic": None if traffic is None else traffic["step_total_bytes"] / (ms_local * 1e-3) / 1e9 / peaks["hbm_gbs"]},
         "stages": stages, "unbracketed_ms_per_step": ms_local,
         "note": "per-kernel times of the step: profiles/ ncu launch list (README); phases here are CUDA-event brackets of a second pass "
                 "through the SEPARATE calls (eager launches, synchronous all-reduce): they sum to more than the graphed step",
